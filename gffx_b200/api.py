@@ -1,0 +1,408 @@
+"""Host-side mirror of the reference's public interface for the hot path, over the C ABI.
+
+Names follow the reference's Rust API (``src/lib.rs:7-22``): ``TreeIndexData.load_tree_index``,
+``parse_bed_file``, ``parse_region``, ``query_features``, ``OverlapMode``, ``IntersectArgs`` /
+``run`` (``src/commands/intersect.rs``), ``DepthArgs`` / ``CoverageArgs`` and their ``run``
+(``src/commands/depth.rs``, ``src/commands/coverage.rs``).  Errors surface as ``GffxError`` with
+the message the engine reports (the reference's ``anyhow::Error`` reaching ``main``).
+"""
+import ctypes as C
+import enum
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+from ._lib import lib
+
+
+class GffxError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"[{code}] {msg}")
+        self.code = code
+        self.msg = msg
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise GffxError(rc, _lib.last_error())
+
+
+class OverlapMode(enum.IntEnum):
+    """src/commands/intersect.rs:74-78"""
+
+    Contained = 0
+    ContainsRegion = 1
+    Overlap = 2
+
+
+def _is_torch_cuda(x) -> bool:
+    return hasattr(x, "is_cuda") and bool(x.is_cuda)
+
+
+def _as_region_ptrs(regions, keep: list):
+    """regions = (chr, start, end) as numpy uint32 arrays (host) or torch cuda int32/uint32 tensors."""
+    chr_, s, e = regions
+    if _is_torch_cuda(chr_):
+        for t in (chr_, s, e):
+            if not t.is_contiguous() or t.element_size() != 4:
+                raise ValueError("device regions must be contiguous 4-byte tensors")
+        n = int(chr_.numel())
+        if int(s.numel()) != n or int(e.numel()) != n:
+            raise ValueError("region arrays differ in length")
+        keep.extend([chr_, s, e])
+        return chr_.data_ptr(), s.data_ptr(), e.data_ptr(), n, _lib.F_DEVICE_INPUT
+    if hasattr(chr_, "data_ptr") and hasattr(chr_, "numel"):  # torch CPU tensor (e.g. pinned)
+        n = int(chr_.numel())
+        keep.extend([chr_, s, e])
+        return chr_.data_ptr(), s.data_ptr(), e.data_ptr(), n, 0
+    arrs = [np.ascontiguousarray(a, dtype=np.uint32) for a in (chr_, s, e)]
+    n = arrs[0].shape[0]
+    if arrs[1].shape[0] != n or arrs[2].shape[0] != n:
+        raise ValueError("region arrays differ in length")
+    keep.extend(arrs)
+    return arrs[0].ctypes.data, arrs[1].ctypes.data, arrs[2].ctypes.data, n, 0
+
+
+@dataclass
+class Result:
+    """What one join / intersect call produced."""
+
+    n_queries: int = 0
+    n_pairs: int = 0
+    pairs: Optional[np.ndarray] = None  # (n_pairs, 3) uint32: root_fid, start, end
+    pairs_device_ptr: int = 0
+    n_roots: int = 0
+    n_ranges: int = 0
+    ranges: Optional[np.ndarray] = None  # (n_ranges, 2) uint64 byte ranges, output order
+    bytes_out: int = 0
+    warn_fids: List[int] = field(default_factory=list)
+    kernel_ms: float = 0.0
+    stage_ms: Tuple[float, ...] = ()
+    launches: int = 0
+
+
+def _take_result(h) -> Result:
+    try:
+        r = Result()
+        r.n_queries = lib.gffx_result_n_queries(h)
+        r.n_pairs = lib.gffx_result_n_pairs(h)
+        p = lib.gffx_result_pairs(h)
+        if p and r.n_pairs:
+            r.pairs = np.ctypeslib.as_array(p, shape=(r.n_pairs, 3)).copy()
+        r.pairs_device_ptr = lib.gffx_result_pairs_device(h) or 0
+        r.n_roots = lib.gffx_result_n_roots(h)
+        r.n_ranges = lib.gffx_result_n_ranges(h)
+        q = lib.gffx_result_ranges(h)
+        if q and r.n_ranges:
+            r.ranges = np.ctypeslib.as_array(q, shape=(r.n_ranges, 2)).copy()
+        elif r.n_ranges == 0:
+            r.ranges = np.zeros((0, 2), dtype=np.uint64)
+        r.bytes_out = lib.gffx_result_bytes_out(h)
+        nw = lib.gffx_result_n_warn(h)
+        if nw:
+            r.warn_fids = list(np.ctypeslib.as_array(lib.gffx_result_warn_fids(h), shape=(nw,)))
+        r.kernel_ms = lib.gffx_result_kernel_ms(h)
+        r.stage_ms = tuple(lib.gffx_result_stage_ms(h, k) for k in range(5))
+        r.launches = lib.gffx_result_launches(h)
+        return r
+    finally:
+        lib.gffx_result_free(h)
+
+
+class TreeIndexData:
+    """Device-resident index: ``TreeIndexData`` (src/utils/tree_index.rs:12-16) + ``GofMap``
+    (src/index_loader/gof.rs:20-27) + the GFF text's line table."""
+
+    def __init__(self, handle):
+        self._h = handle
+
+    # -- construction ---------------------------------------------------------------------
+    @classmethod
+    def load_tree_index(cls, gff_path: str, device: int = 0) -> "TreeIndexData":
+        h = C.c_void_p()
+        _check(lib.gffx_index_open(str(gff_path).encode(), int(device), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def create(cls, seq_names: Sequence[str], root_seq, root_start, root_end, root_fid, gof_fid, gof_start, gof_end,
+               gff_text: Optional[bytes] = None, device: int = 0) -> "TreeIndexData":
+        names = (C.c_char_p * len(seq_names))(*[s.encode() for s in seq_names])
+        arrs32 = [np.ascontiguousarray(a, dtype=np.uint32) for a in (root_seq, root_start, root_end, root_fid, gof_fid)]
+        arrs64 = [np.ascontiguousarray(a, dtype=np.uint64) for a in (gof_start, gof_end)]
+        d = _lib.IndexDesc()
+        d.n_seqs = len(seq_names)
+        d.seq_names = names
+        d.n_roots = arrs32[0].shape[0]
+        d.root_seq, d.root_start, d.root_end, d.root_fid = (a.ctypes.data for a in arrs32[:4])
+        d.n_gof = arrs32[4].shape[0]
+        d.gof_fid = arrs32[4].ctypes.data
+        d.gof_start, d.gof_end = (a.ctypes.data for a in arrs64)
+        buf = None
+        if gff_text:
+            buf = C.create_string_buffer(gff_text, len(gff_text))
+            d.gff_text = C.addressof(buf)
+            d.gff_len = len(gff_text)
+        d.device = int(device)
+        h = C.c_void_p()
+        _check(lib.gffx_index_create(C.byref(d), C.byref(h)))
+        obj = cls(h)
+        obj._text_keepalive = buf  # the library borrows the text for the index's lifetime
+        return obj
+
+    def close(self):
+        if self._h:
+            lib.gffx_index_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- accessors ------------------------------------------------------------------------
+    @property
+    def num_to_seqid(self) -> List[str]:
+        return [lib.gffx_index_seq_name(self._h, i).decode() for i in range(lib.gffx_index_n_seqs(self._h))]
+
+    @property
+    def seqid_to_num(self) -> dict:
+        return {n: lib.gffx_index_seq_num(self._h, n.encode()) for n in self.num_to_seqid}
+
+    n_seqs = property(lambda self: lib.gffx_index_n_seqs(self._h))
+    n_roots = property(lambda self: lib.gffx_index_n_roots(self._h))
+    n_blocks = property(lambda self: lib.gffx_index_n_blocks(self._h))
+    n_lines = property(lambda self: lib.gffx_index_n_lines(self._h))
+    n_ids = property(lambda self: lib.gffx_index_n_ids(self._h))
+    device_bytes = property(lambda self: lib.gffx_index_device_bytes(self._h))
+
+    def seq_roots(self, seq: int) -> np.ndarray:
+        p = _lib.u32p()
+        n = C.c_uint64()
+        _check(lib.gffx_index_seq_roots(self._h, seq, C.byref(p), C.byref(n)))
+        if n.value == 0:
+            return np.zeros((0, 3), dtype=np.uint32)
+        return np.ctypeslib.as_array(p, shape=(n.value, 3)).copy()
+
+    # -- BED parsing ----------------------------------------------------------------------
+    def _parse(self, fn, path):
+        ps = [_lib.u32p() for _ in range(3)]
+        n = C.c_uint64()
+        _check(fn(self._h, str(path).encode(), C.byref(ps[0]), C.byref(ps[1]), C.byref(ps[2]), C.byref(n)))
+        try:
+            out = tuple(np.ctypeslib.as_array(p, shape=(max(n.value, 1),))[: n.value].copy() for p in ps)
+        finally:
+            for p in ps:
+                lib.gffx_free(p)
+        return out
+
+    def parse_bed_file(self, bed_path):
+        """src/commands/intersect.rs:201-230"""
+        return self._parse(lib.gffx_parse_bed_intersect, bed_path)
+
+    def parse_bed_counts(self, bed_path):
+        """BED dialect of depth/coverage: src/commands/depth.rs:449-495, src/commands/coverage.rs:222-255"""
+        return self._parse(lib.gffx_parse_bed_counts, bed_path)
+
+    def parse_region(self, region: str):
+        """src/commands/intersect.rs:172-198"""
+        c, s, e = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _check(lib.gffx_parse_region(self._h, region.encode(), C.byref(c), C.byref(s), C.byref(e)))
+        return c.value, s.value, e.value
+
+    # -- compute --------------------------------------------------------------------------
+    def query_features(self, regions, mode: OverlapMode = OverlapMode.Overlap, invert: bool = False, *, want_pairs: bool = True,
+                       flags: int = 0) -> Result:
+        """src/commands/intersect.rs:105-169"""
+        keep: list = []
+        pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
+        f |= flags | (_lib.F_WANT_PAIRS if want_pairs else 0)
+        h = C.c_void_p()
+        _check(lib.gffx_query_features(self._h, pc, ps, pe, n, int(mode), int(bool(invert)), f, C.byref(h)))
+        return _take_result(h)
+
+    def intersect(self, regions, mode: OverlapMode = OverlapMode.Overlap, invert: bool = False, entire_group: bool = False,
+                  types: Optional[str] = None, *, want_pairs: bool = False, flags: int = 0) -> Result:
+        """run() after BED parsing, src/commands/intersect.rs:586-654"""
+        keep: list = []
+        pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
+        f |= flags | (_lib.F_WANT_PAIRS if want_pairs else 0)
+        h = C.c_void_p()
+        _check(lib.gffx_intersect(self._h, pc, ps, pe, n, int(mode), int(bool(invert)), int(bool(entire_group)),
+                                  types.encode() if types is not None else None, f, C.byref(h)))
+        return _take_result(h)
+
+    def write_ranges(self, ranges: np.ndarray, out_path: Optional[str]):
+        r = np.ascontiguousarray(ranges, dtype=np.uint64)
+        _check(lib.gffx_write_ranges(self._h, r.ctypes.data, r.shape[0], str(out_path).encode() if out_path else None))
+
+    def _counts(self, kind: int, regions, batches: int = 1):
+        st = C.c_void_p()
+        _check(lib.gffx_counts_begin(self._h, kind, C.byref(st)))
+        try:
+            keep: list = []
+            pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
+            if batches <= 1 or n == 0:
+                _check(lib.gffx_counts_add(st, pc, ps, pe, n, f))
+            else:
+                step = (n + batches - 1) // batches
+                for b0 in range(0, n, step):
+                    m = min(step, n - b0)
+                    _check(lib.gffx_counts_add(st, pc + 4 * b0, ps + 4 * b0, pe + 4 * b0, m, f))
+            nr = C.c_uint64()
+            pid, pch, pst, pen = (_lib.u32p() for _ in range(4))
+            pv = _lib.u64p()
+            _check(lib.gffx_counts_finish(st, C.byref(nr), C.byref(pid), C.byref(pch), C.byref(pst), C.byref(pen), C.byref(pv)))
+            k = nr.value
+
+            def arr(p, dt):
+                return np.ctypeslib.as_array(p, shape=(k,)).astype(dt, copy=True) if k else np.zeros(0, dtype=dt)
+
+            rows = CountRows(arr(pid, np.uint32), arr(pch, np.uint32), arr(pst, np.uint32), arr(pen, np.uint32), arr(pv, np.uint64),
+                             lib.gffx_counts_kernel_ms(st), lib.gffx_counts_launches(st), kind, self)
+            return rows
+        finally:
+            lib.gffx_counts_free(st)
+
+    def depth(self, regions, batches: int = 1) -> "CountRows":
+        """compute_hit_depth over all batches, src/commands/depth.rs:222-293,429-512"""
+        return self._counts(0, regions, batches)
+
+    def coverage(self, regions, batches: int = 1) -> "CountRows":
+        """collect_by_root + finalize_compute_breadth, src/commands/coverage.rs:208-450"""
+        return self._counts(1, regions, batches)
+
+    def id_string(self, i: int) -> bytes:
+        n = C.c_uint32()
+        p = lib.gffx_index_id_string(self._h, int(i), C.byref(n))
+        return C.string_at(p, n.value) if p else b""
+
+    def chrom_string(self, i: int) -> bytes:
+        n = C.c_uint32()
+        p = lib.gffx_index_chrom_string(self._h, int(i), C.byref(n))
+        return C.string_at(p, n.value) if p else b""
+
+    # -- synthetic workloads --------------------------------------------------------------
+    def synth_regions(self, seed: int, n: int, length: int, first: int = 0):
+        out = [np.empty(n, dtype=np.uint32) for _ in range(3)]
+        _check(lib.gffx_synth_regions_host(self._h, seed, first, n, length, *(a.ctypes.data for a in out)))
+        return tuple(out)
+
+    def synth_regions_device(self, seed: int, n: int, length: int, first: int = 0, device=None):
+        import torch
+
+        dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        out = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(3)]
+        _check(lib.gffx_synth_regions_device(self._h, seed, first, n, length, *(t.data_ptr() for t in out)))
+        return tuple(out)
+
+
+@dataclass
+class CountRows:
+    id_idx: np.ndarray
+    chrom_idx: np.ndarray
+    start: np.ndarray
+    end: np.ndarray
+    value: np.ndarray
+    kernel_ms: float
+    launches: int
+    kind: int
+    index: "TreeIndexData"
+
+    def to_tsv(self, sort_rows: bool = True) -> bytes:
+        """The reference's TSV (write_depth_results / write_breadth_results); rows sorted bytewise when asked,
+        because the reference's own row order is hash order."""
+        rows = []
+        for i in range(self.id_idx.shape[0]):
+            ident = self.index.id_string(self.id_idx[i])
+            chrom = self.index.chrom_string(self.chrom_idx[i])
+            s, e, v = int(self.start[i]), int(self.end[i]), int(self.value[i])
+            if self.kind == 0:
+                rows.append(ident + b"\t" + chrom + b"\t%d\t%d\t%d\n" % (s, e, v))
+            else:
+                length = e - s if e > s else 0
+                frac = (v / length) if length > 0 else 0.0
+                rows.append(ident + b"\t" + chrom + b"\t%d\t%d\t%d\t%s\n" % (s, e, v, ("%.6f" % frac).encode()))
+        if sort_rows:
+            rows.sort()
+        head = b"id\tchr\tstart\tend\tdepth\n" if self.kind == 0 else b"id\tchr\tstart\tend\tbreadth\tfraction\n"
+        return head + b"".join(rows)
+
+
+def synth_gff(path: str, seed: int = 20260001, n_genes: int = 60000, quirks: bool = False) -> int:
+    n = C.c_uint64()
+    _check(lib.gffx_synth_gff(str(path).encode(), seed, n_genes, int(quirks), C.byref(n)))
+    return n.value
+
+
+# ---- command level: the reference's Args structs and run() functions ------------------------------
+@dataclass
+class IntersectArgs:
+    """src/commands/intersect.rs:43-70 + CommonArgs src/utils/common.rs:17-52"""
+
+    input: str
+    output: Optional[str] = None
+    bed: Optional[str] = None
+    region: Optional[str] = None
+    contained: bool = False
+    contains_region: bool = False
+    overlap: bool = False
+    invert: bool = False
+    entire_group: bool = False
+    types: Optional[str] = None
+    threads: int = 12
+    verbose: bool = False
+    device: int = 0
+
+
+def run_intersect(args: IntersectArgs):
+    """src/commands/intersect.rs:541-655"""
+    if sum([args.contained, args.contains_region, args.overlap]) > 1:
+        raise GffxError(-1, "--contained, --contains-region and --overlap cannot be used together")
+    mode = OverlapMode.Contained if args.contained else OverlapMode.ContainsRegion if args.contains_region else OverlapMode.Overlap
+    a = _lib.IntersectArgs(
+        str(args.input).encode(), str(args.output).encode() if args.output else None, str(args.bed).encode() if args.bed else None,
+        args.region.encode() if args.region else None, int(mode), int(args.invert), int(args.entire_group),
+        args.types.encode() if args.types is not None else None, int(args.verbose), int(args.device))
+    _check(lib.gffx_intersect_run(C.byref(a)))
+
+
+@dataclass
+class DepthArgs:
+    """src/commands/depth.rs:40-74"""
+
+    input: str
+    source: str
+    output: Optional[str] = None
+    bin_shift: int = 12
+    threads: int = 12
+    verbose: bool = False
+    device: int = 0
+
+
+CoverageArgs = DepthArgs  # src/commands/coverage.rs:37-57 has the same fields minus bin_shift
+
+
+def _counts_args(args):
+    return _lib.CountsArgs(str(args.input).encode(), str(args.source).encode(), str(args.output).encode() if args.output else None,
+                           int(args.bin_shift), int(args.threads), int(args.verbose), int(args.device))
+
+
+def run_depth(args: DepthArgs):
+    """src/commands/depth.rs:548-635"""
+    a = _counts_args(args)
+    _check(lib.gffx_depth_run(C.byref(a)))
+
+
+def run_coverage(args: DepthArgs):
+    """src/commands/coverage.rs:493-582"""
+    a = _counts_args(args)
+    _check(lib.gffx_coverage_run(C.byref(a)))

@@ -1,0 +1,524 @@
+// engine.cu — index upload and the intersect pipeline (join -> block select -> line filter / merge).
+#include <algorithm>
+#include <numeric>
+#include "engine_impl.cuh"
+#include "synth_common.h"
+
+namespace gffx {
+
+constexpr int JOIN_K = 16;        // an interval that reaches past the start of its JOIN_K-th successor is "long"
+constexpr int JOIN_MAX_LISTS = 8; // per sequence
+constexpr uint32_t WARN_CAP = 1u << 16;
+
+// small kernels -------------------------------------------------------------------------------
+struct TileCountLoad {
+    const uint32_t* p;
+    __device__ uint64_t operator()(uint64_t i) const { return (uint64_t)p[i]; }
+};
+struct MarkLoad {  // next-set scan input: the cell's own index when marked
+    const uint8_t* m;
+    __device__ uint32_t operator()(uint64_t i) const { return m[i] ? (uint32_t)i : 0xFFFFFFFFu; }
+};
+
+__global__ void fill_u64_kernel(unsigned long long* p, uint64_t n, unsigned long long v) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// ------------------------------------------------------------------------------------------------
+EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::move(host)), dev(device) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        throw Err(E_CUDA, std::string("no usable CUDA device (") + cudaGetErrorString(e) + "); this engine has no CPU fallback");
+    if (device < 0 || device >= ndev) throw Err(E_ARG, "device ordinal out of range");
+    GFFX_CUDA(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    GFFX_CUDA(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) throw Err(E_CUDA, std::string("device ") + prop.name + " is not sm_100-class; the kernels are built for sm_100a only");
+    sm_count = prop.multiProcessorCount;
+    GFFX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
+    GFFX_CUDA(cudaMallocHost(&h_small, 256));
+    for (DBuf* b : {&d_seq_list0, &d_lists, &d_ent_se, &d_ent_fid, &d_ent_blk, &d_dir, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
+                    &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
+                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
+        b->total = &dev_bytes;
+    build_join();
+    build_blocks();
+    build_lines();
+    d_small.ensure(256);
+    d_warn.ensure(WARN_CAP * 4);
+    GFFX_CUDA(cudaStreamSynchronize(st));
+}
+
+EngineImpl::~EngineImpl() {
+    cudaSetDevice(dev);
+    if (st) cudaStreamSynchronize(st);
+    for (DBuf* b : {&d_seq_list0, &d_lists, &d_ent_se, &d_ent_fid, &d_ent_blk, &d_dir, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
+                    &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
+                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
+        b->release();
+    counts_release(this);
+    if (h_small) cudaFreeHost(h_small);
+    for (auto& x : ev) cudaEventDestroy(x);
+    if (st) cudaStreamDestroy(st);
+}
+
+// Join index: per sequence sort by start, peel "long" intervals into further lists, build the
+// running-max-end directory of each list.
+void EngineImpl::build_join() {
+    const size_t n_seqs = H->seq_names.size();
+    std::vector<std::vector<uint32_t>> by_seq(n_seqs);
+    for (size_t i = 0; i < H->roots.size(); i++) by_seq[H->roots[i].seq].push_back((uint32_t)i);
+    std::vector<uint32_t> seq_list0(n_seqs + 1, 0), ent_fid, ent_blk, dir;
+    std::vector<uint2> ent_se;
+    std::vector<JoinList> lists;
+    seq_sorted_roots.assign(n_seqs, {});
+    for (size_t s = 0; s < n_seqs; s++) {
+        seq_list0[s] = (uint32_t)lists.size();
+        std::vector<uint32_t>& ids = by_seq[s];
+        const auto& R = H->roots;
+        std::stable_sort(ids.begin(), ids.end(), [&](uint32_t a, uint32_t b) {
+            if (R[a].start != R[b].start) return R[a].start < R[b].start;
+            return R[a].end < R[b].end;
+        });
+        auto& flat = seq_sorted_roots[s];
+        flat.reserve(ids.size() * 3);
+        for (uint32_t i : ids) { flat.push_back(R[i].start); flat.push_back(R[i].end); flat.push_back(R[i].fid); }
+        std::vector<uint32_t> cur = ids, keep, longs;
+        for (int level = 0; !cur.empty(); level++) {
+            keep.clear();
+            longs.clear();
+            if (level == JOIN_MAX_LISTS - 1 || cur.size() <= 4 * JOIN_K) keep = cur;
+            else {
+                for (size_t i = 0; i < cur.size(); i++) {
+                    bool is_long = i + JOIN_K < cur.size() && R[cur[i]].end > R[cur[i + JOIN_K]].start;
+                    (is_long ? longs : keep).push_back(cur[i]);
+                }
+            }
+            if (!keep.empty()) {
+                JoinList L{};
+                L.base = (uint32_t)ent_se.size();
+                L.count = (uint32_t)keep.size();
+                uint32_t maxend = 0;
+                for (uint32_t i : keep) maxend = std::max(maxend, R[i].end);
+                uint32_t shift = 6;
+                while (((uint64_t)maxend >> shift) + 1 > std::max<uint64_t>(64, 4ull * keep.size())) shift++;
+                L.shift = shift;
+                L.nbins = (maxend >> shift) + 1;
+                L.dir_base = (uint32_t)dir.size();
+                for (uint32_t i : keep) {
+                    ent_se.push_back(make_uint2(R[i].start, R[i].end));
+                    ent_fid.push_back(R[i].fid);
+                    ent_blk.push_back(H->root_blk[i]);
+                }
+                // dir[b] = first j (absolute) whose inclusive running max-end exceeds b<<shift
+                uint32_t j = 0, pm = 0;
+                std::vector<uint32_t> pmax(keep.size());
+                for (size_t k = 0; k < keep.size(); k++) { pm = std::max(pm, R[keep[k]].end); pmax[k] = pm; }
+                for (uint32_t b = 0; b < L.nbins; b++) {
+                    const uint64_t lo = (uint64_t)b << shift;
+                    while (j < keep.size() && (uint64_t)pmax[j] <= lo) j++;
+                    dir.push_back(L.base + j);
+                }
+                lists.push_back(L);
+            }
+            cur = longs;
+        }
+    }
+    seq_list0[n_seqs] = (uint32_t)lists.size();
+    n_ent = (uint32_t)ent_se.size();
+    n_lists = (uint32_t)lists.size();
+    upload(d_seq_list0, seq_list0, st);
+    upload(d_lists, lists, st);
+    upload(d_ent_se, ent_se, st);
+    upload(d_ent_fid, ent_fid, st);
+    upload(d_ent_blk, ent_blk, st);
+    upload(d_dir, dir, st);
+    d_ent_hit.ensure(std::max<uint32_t>(n_ent, 1));
+    GFFX_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
+    J.seq_list0 = d_seq_list0.as<uint32_t>();
+    J.lists = d_lists.as<JoinList>();
+    J.ent_se = d_ent_se.as<uint2>();
+    J.ent_fid = d_ent_fid.as<uint32_t>();
+    J.dir = d_dir.as<uint32_t>();
+    J.n_seqs = (uint32_t)n_seqs;
+}
+
+void EngineImpl::build_blocks() {
+    n_blocks = (uint32_t)H->blocks.size();
+    std::vector<uint64_t> bs(n_blocks), be(n_blocks);
+    for (uint32_t b = 0; b < n_blocks; b++) { bs[b] = H->blocks[b].start; be[b] = H->blocks[b].end; }
+    upload(d_bstart, bs, st);
+    upload(d_bend, be, st);
+    d_blk_sel.ensure(std::max<uint32_t>(n_blocks, 1));
+    d_ranges.ensure(std::max<uint32_t>(n_blocks, 1) * 16ull);
+    GFFX_CUDA(cudaStreamSynchronize(st));
+}
+
+// Lines + the filter rank space (see filter.cuh).
+void EngineImpl::build_lines() {
+    const LineTable& L = H->lines;
+    const size_t n = L.size(), n_seqs = H->seq_names.size();
+    // per sequence: sorted distinct S/E of usable lines
+    std::vector<std::vector<uint32_t>> xs(n_seqs);
+    for (size_t i = 0; i < n; i++)
+        if (L.flags[i] & LN_I_OK) { xs[L.iseq[i]].push_back(L.S[i]); xs[L.iseq[i]].push_back(L.E[i]); }
+    std::vector<RankSeq> seqs(n_seqs);
+    std::vector<uint32_t> X, dir;
+    uint32_t slot = 0;
+    for (size_t s = 0; s < n_seqs; s++) {
+        auto& v = xs[s];
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+        RankSeq& r = seqs[s];
+        r.x0 = (uint32_t)X.size();
+        r.cnt = (uint32_t)v.size();
+        r.slot0 = slot;
+        slot += r.cnt + 1;
+        // a name listed twice in .sqs resolves to its LAST number (intersect.rs:622-625): regions carrying
+        // the earlier number never reach the line filter
+        r.canon = H->seq_num.at(H->seq_names[s]) == s ? 1u : 0u;
+        r.dir_base = (uint32_t)dir.size();
+        if (v.empty()) { r.nb = 0; r.shift = 0; dir.push_back(0); continue; }
+        uint32_t maxv = v.back(), shift = 4;
+        while (((uint64_t)maxv >> shift) + 1 > std::max<uint64_t>(64, 2ull * v.size())) shift++;
+        r.shift = shift;
+        r.nb = (maxv >> shift) + 1;
+        uint32_t j = 0;
+        for (uint32_t b = 0; b <= r.nb; b++) {  // nb+1 entries: dir[b] = #(X < b<<shift)
+            const uint64_t lo = (uint64_t)b << shift;
+            while (j < v.size() && (uint64_t)v[j] < lo) j++;
+            dir.push_back(j);
+        }
+        X.insert(X.end(), v.begin(), v.end());
+    }
+    f_slots = slot;
+    std::vector<uint32_t> iS(n, 0), iE(n, 0);
+    for (size_t i = 0; i < n; i++)
+        if (L.flags[i] & LN_I_OK) {
+            const auto& v = xs[L.iseq[i]];
+            const RankSeq& r = seqs[L.iseq[i]];
+            iS[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.S[i]) - v.begin());
+            iE[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.E[i]) - v.begin());
+        }
+    upload(d_ln_flags, L.flags, st);
+    upload(d_ln_blk, L.blk, st);
+    upload(d_ln_type, L.type_id, st);
+    upload(d_ln_iseq, L.iseq, st);
+    upload(d_ln_S, L.S, st);
+    upload(d_ln_E, L.E, st);
+    upload(d_ln_iS, iS, st);
+    upload(d_ln_iE, iE, st);
+    upload(d_ln_off, L.off, st);
+    upload(d_ln_len, L.len, st);
+    upload(d_fX, X, st);
+    upload(d_fdir, dir, st);
+    upload(d_fseqs, seqs, st);
+    const size_t ns = std::max<uint32_t>(f_slots, 1);
+    d_A.ensure(ns * 8); d_B.ensure(ns * 8); d_PMX.ensure(ns * 8); d_SMN.ensure((ns + 1) * 8);
+    d_Ms.ensure(ns * 2); d_Me.ensure(ns * 2); d_NS.ensure(ns * 8); d_NE.ensure(ns * 8);
+    d_keep.ensure(std::max<size_t>(n, 1));
+    d_type_allow.ensure(std::max<size_t>(H->types.size(), 1));
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    FR.X = d_fX.as<uint32_t>();
+    FR.dir = d_fdir.as<uint32_t>();
+    FR.seqs = d_fseqs.as<RankSeq>();
+    FR.n_seqs = (uint32_t)n_seqs;
+    LA.flags = d_ln_flags.as<uint8_t>();
+    LA.blk = d_ln_blk.as<uint32_t>();
+    LA.type_id = d_ln_type.as<uint32_t>();
+    LA.iseq = d_ln_iseq.as<uint32_t>();
+    LA.S = d_ln_S.as<uint32_t>();
+    LA.E = d_ln_E.as<uint32_t>();
+    LA.iS = d_ln_iS.as<uint32_t>();
+    LA.iE = d_ln_iE.as<uint32_t>();
+    LA.off = d_ln_off.as<uint64_t>();
+    LA.len = d_ln_len.as<uint32_t>();
+    LA.n = n;
+}
+
+void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
+                               const uint32_t** dc, const uint32_t** ds, const uint32_t** de) {
+    if (flags & 1u) {  // GFFX_F_DEVICE_INPUT
+        *dc = chr; *ds = start; *de = end;
+        return;
+    }
+    const uint32_t* src[3] = {chr, start, end};
+    for (int k = 0; k < 3; k++) {
+        d_q[k].ensure(std::max<uint64_t>(n, 1) * 4);
+        if (n) GFFX_CUDA(cudaMemcpyAsync(d_q[k].p, src[k], n * 4, cudaMemcpyHostToDevice, st));
+    }
+    *dc = d_q[0].as<uint32_t>(); *ds = d_q[1].as<uint32_t>(); *de = d_q[2].as<uint32_t>();
+}
+
+template <int MODE, bool INV>
+static void launch_join_count(EngineImpl* E, const uint32_t* c, const uint32_t* s, const uint32_t* e, uint64_t n, bool aligned,
+                              unsigned tiles, uint32_t* err) {
+    join_count_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, s, e, n, aligned, E->d_ent_hit.as<uint8_t>(),
+                                                                   E->d_tile_count.as<uint32_t>(), err);
+}
+template <int MODE, bool INV>
+static void launch_join_emit(EngineImpl* E, const uint32_t* c, const uint32_t* s, const uint32_t* e, uint64_t n, bool aligned,
+                             unsigned tiles) {
+    join_emit_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, s, e, n, aligned, E->d_tile_off.as<uint64_t>(),
+                                                                  E->d_pairs.as<uint32_t>());
+}
+
+void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
+                           bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out) {
+    if (mode < 0 || mode > 2) throw Err(E_ARG, "mode must be 0 (contained), 1 (contains-region) or 2 (overlap)");
+    if (n && (!chr || !start || !end)) throw Err(E_ARG, "NULL region arrays");
+    if (n >= (1ull << 40)) throw Err(E_ARG, "too many regions in one call");
+    GFFX_CUDA(cudaSetDevice(dev));
+    *out = IntersectResult();
+    out->n_queries = n;
+    const bool want_pairs_host = flags & 2u, pairs_dev = (flags & 8u) || want_pairs_host, no_host = flags & 4u;
+    uint32_t launches = 0;
+    const uint32_t *dc, *ds, *de;
+    stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
+    const bool aligned = (((uintptr_t)dc | (uintptr_t)ds | (uintptr_t)de) & 15) == 0;
+    unsigned long long* small = d_small.as<unsigned long long>();  // [0] n_pairs [1..3] merge counts [4] bytes_out [5] n_emit (u64); u32 view: [12] err [13] n_warn
+    uint32_t* small32 = d_small.as<uint32_t>();
+    GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 256, st));
+    GFFX_CUDA(cudaEventRecord(ev[0], st));
+
+    // ---- stage 0: join ---------------------------------------------------------------------
+    const bool nothing = (mode == 2 && invert) || n == 0 || n_ent == 0;  // -I with overlap selects nothing (intersect.rs:161)
+    const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
+    if (n_ent) GFFX_CUDA(cudaMemsetAsync(d_ent_hit.p, 0, n_ent, st));
+    if (!nothing) {
+        d_tile_count.ensure((size_t)tiles * 4);
+        d_tile_off.ensure((size_t)tiles * 8);
+        d_scan_scratch.ensure(scan_scratch_elems(std::max<uint64_t>(tiles, LA.n / LINE_THREADS + 1)) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
+        uint32_t* err = small32 + 12;
+        switch (mode * 2 + (invert ? 1 : 0)) {
+            case 0: launch_join_count<0, false>(this, dc, ds, de, n, aligned, tiles, err); break;
+            case 1: launch_join_count<0, true>(this, dc, ds, de, n, aligned, tiles, err); break;
+            case 2: launch_join_count<1, false>(this, dc, ds, de, n, aligned, tiles, err); break;
+            case 3: launch_join_count<1, true>(this, dc, ds, de, n, aligned, tiles, err); break;
+            default: launch_join_count<2, false>(this, dc, ds, de, n, aligned, tiles, err); break;
+        }
+        launches++;
+        launches += device_scan<uint64_t, OpSum, TileCountLoad, PtrStore<uint64_t>, false, false>(
+            TileCountLoad{d_tile_count.as<uint32_t>()}, PtrStore<uint64_t>{d_tile_off.as<uint64_t>()}, tiles, OpSum(), 0ull,
+            d_scan_scratch.as<uint64_t>(), (uint64_t*)small, st);
+        GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
+        GFFX_CUDA(cudaStreamSynchronize(st));
+        if (((uint32_t*)h_small)[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
+        out->n_pairs = ((uint64_t*)h_small)[0];
+        if (pairs_dev && out->n_pairs) {
+            d_pairs.ensure(out->n_pairs * 12);
+            switch (mode * 2 + (invert ? 1 : 0)) {
+                case 0: launch_join_emit<0, false>(this, dc, ds, de, n, aligned, tiles); break;
+                case 1: launch_join_emit<0, true>(this, dc, ds, de, n, aligned, tiles); break;
+                case 2: launch_join_emit<1, false>(this, dc, ds, de, n, aligned, tiles); break;
+                case 3: launch_join_emit<1, true>(this, dc, ds, de, n, aligned, tiles); break;
+                default: launch_join_emit<2, false>(this, dc, ds, de, n, aligned, tiles); break;
+            }
+            launches++;
+            out->d_pairs = d_pairs.as<uint32_t>();
+        }
+    }
+    GFFX_CUDA(cudaEventRecord(ev[1], st));
+
+    // ---- stage 1: root -> block selection, merged ranges (-e) ---------------------------------
+    const bool match_only = !entire_group || types_csv != nullptr;  // intersect.rs:619
+    if (n_blocks) GFFX_CUDA(cudaMemsetAsync(d_blk_sel.p, 0, n_blocks, st));
+    if (!nothing) {
+        select_blocks_kernel<<<(n_ent + 255) / 256, 256, 0, st>>>(d_ent_hit.as<uint8_t>(), d_ent_blk.as<uint32_t>(), J.ent_fid, n_ent,
+                                                                 d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
+        launches++;
+        if (n_blocks) {
+            merge_blocks_kernel<<<1, 1024, 0, st>>>(d_bstart.as<uint64_t>(), d_bend.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks,
+                                                   H->gff_len, !match_only && !join_only, d_ranges.as<ulonglong2>(), small + 1);
+            launches++;
+        }
+    }
+    GFFX_CUDA(cudaEventRecord(ev[2], st));
+
+    // ---- stages 2-4: line filter ---------------------------------------------------------------
+    uint64_t n_emit_tiles = 0;
+    const bool run_filter = !nothing && !join_only && match_only && LA.n > 0;
+    if (run_filter) {
+        // -T: comma-split, trimmed, non-empty tokens (intersect.rs:252-259)
+        const bool have_types = types_csv != nullptr;
+        if (have_types) {
+            std::vector<uint8_t> allow(std::max<size_t>(H->types.size(), 1), 0);
+            std::string_view s(types_csv);
+            size_t i = 0;
+            while (i <= s.size()) {
+                size_t j = s.find(',', i);
+                if (j == std::string_view::npos) j = s.size();
+                std::string_view t = trim_unicode(s.substr(i, j - i));
+                if (!t.empty()) {
+                    int64_t id = H->types.find(t);
+                    if (id >= 0) allow[(size_t)id] = 1;
+                }
+                i = j + 1;
+            }
+            GFFX_CUDA(cudaMemcpyAsync(d_type_allow.p, allow.data(), allow.size(), cudaMemcpyHostToDevice, st));
+            GFFX_CUDA(cudaStreamSynchronize(st));  // `allow` is a stack-local
+        }
+        FilterArrays F{d_A.as<unsigned long long>(), d_B.as<unsigned long long>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
+        const uint64_t ns = f_slots;
+        if (mode == 0 || mode == 2) GFFX_CUDA(cudaMemsetAsync(d_A.p, 0, ns * 8, st));
+        if (mode == 1) GFFX_CUDA(cudaMemsetAsync(d_B.p, 0xFF, ns * 8, st));
+        if (mode == 2) {
+            GFFX_CUDA(cudaMemsetAsync(d_Ms.p, 0, ns * 2, st));
+            GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
+        }
+        const unsigned sblocks = (unsigned)((n + (uint64_t)FILT_THREADS * FILT_QPT - 1) / ((uint64_t)FILT_THREADS * FILT_QPT));
+        if (mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
+        else if (mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
+        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
+        launches++;
+        GFFX_CUDA(cudaEventRecord(ev[3], st));
+
+        typedef unsigned long long ull;
+        ull* scr = d_scan_scratch.as<ull>();
+        FilterScans P{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>()};
+        if (mode == 0 || mode == 2)
+            launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
+                                                                                         OpMax(), 0ull, scr, nullptr, st);
+        if (mode == 1) {
+            launches += device_scan<ull, OpMin, PtrLoad<ull>, PtrStore<ull>, true, true>(PtrLoad<ull>{F.B}, PtrStore<ull>{d_SMN.as<ull>()}, ns,
+                                                                                        OpMin(), ~0ull, scr, nullptr, st);
+            fill_u64_kernel<<<1, 32, 0, st>>>(d_SMN.as<ull>() + ns, 1, ~0ull);  // SMN[iS+1] may index one past the last slot
+            launches++;
+        }
+        if (mode == 2) {
+            launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
+                MarkLoad{F.Ms}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
+            launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
+                MarkLoad{F.Me}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
+        }
+        GFFX_CUDA(cudaEventRecord(ev[4], st));
+
+        n_emit_tiles = (LA.n + LINE_THREADS - 1) / LINE_THREADS;
+        d_tile_count.ensure(n_emit_tiles * 4);
+        d_tile_off.ensure(n_emit_tiles * 8);
+        const uint8_t* sel = d_blk_sel.as<uint8_t>();
+        const uint8_t* ta = d_type_allow.as<uint8_t>();
+        if (mode == 0) eval_lines_kernel<0><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, have_types, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        else if (mode == 1) eval_lines_kernel<1><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, have_types, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        else eval_lines_kernel<2><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, have_types, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        launches++;
+        launches += device_scan<uint64_t, OpSum, TileCountLoad, PtrStore<uint64_t>, false, false>(
+            TileCountLoad{d_tile_count.as<uint32_t>()}, PtrStore<uint64_t>{d_tile_off.as<uint64_t>()}, n_emit_tiles, OpSum(), 0ull,
+            d_scan_scratch.as<uint64_t>(), (uint64_t*)(small + 5), st);
+        // the compacted list can never exceed the number of lines
+        d_ranges.ensure(std::max<uint64_t>(LA.n, n_blocks) * 16);
+        emit_ranges_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, d_keep.as<uint8_t>(), d_tile_off.as<uint64_t>(),
+                                                                          d_ranges.as<ulonglong2>(), small + 4);
+        launches++;
+    } else {
+        GFFX_CUDA(cudaEventRecord(ev[3], st));
+        GFFX_CUDA(cudaEventRecord(ev[4], st));
+    }
+    GFFX_CUDA(cudaEventRecord(ev[5], st));
+
+    // ---- results -----------------------------------------------------------------------------
+    GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    {
+        cudaError_t le = cudaGetLastError();
+        if (le != cudaSuccess) throw Err(E_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(le));
+    }
+    const uint64_t* hs = (const uint64_t*)h_small;
+    const uint32_t* hs32 = (const uint32_t*)h_small;
+    const uint32_t n_warn = std::min<uint32_t>(hs32[13], WARN_CAP);
+    if (n_warn) {
+        std::vector<uint32_t> w(n_warn);
+        GFFX_CUDA(cudaMemcpy(w.data(), d_warn.p, n_warn * 4ull, cudaMemcpyDeviceToHost));
+        std::sort(w.begin(), w.end());
+        w.erase(std::unique(w.begin(), w.end()), w.end());
+        out->warn_fids = std::move(w);
+    }
+    out->n_roots = hs[2] + out->warn_fids.size();
+    if (!join_only && !nothing) {
+        if (match_only) { out->n_ranges = hs[5]; out->bytes_out = hs[4]; }
+        else { out->n_ranges = hs[1]; out->bytes_out = hs[3]; }
+    }
+    if (out->n_ranges && !no_host) {
+        out->ranges.resize(out->n_ranges * 2);
+        GFFX_CUDA(cudaMemcpyAsync(out->ranges.data(), d_ranges.p, out->n_ranges * 16, cudaMemcpyDeviceToHost, st));
+    }
+    if (want_pairs_host && out->n_pairs && !no_host) {
+        out->pairs.resize(out->n_pairs * 3);
+        GFFX_CUDA(cudaMemcpyAsync(out->pairs.data(), d_pairs.p, out->n_pairs * 12, cudaMemcpyDeviceToHost, st));
+    }
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    float ms;
+    for (int k = 0; k < 5; k++) {
+        GFFX_CUDA(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
+        out->stage_ms[k] = ms;
+    }
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[5]));
+    out->kernel_ms = ms;
+    out->launches = launches;
+}
+
+// ------------------------------------------------------------------------------------------------
+// synthetic regions straight into HBM (same function of (seed, index) as the host generator)
+__global__ void synth_regions_kernel(uint64_t seed, uint64_t first, uint64_t n, uint32_t length, const uint64_t* __restrict__ cum,
+                                     const uint32_t* __restrict__ extent, uint32_t n_seq, uint32_t* __restrict__ chr,
+                                     uint32_t* __restrict__ start, uint32_t* __restrict__ end) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t c, s, e;
+    synth_region(seed, first + i, length, cum, extent, n_seq, &c, &s, &e);
+    chr[i] = c; start[i] = s; end[i] = e;
+}
+
+void Engine::synth_regions_device(uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* d_chr, uint32_t* d_start,
+                                  uint32_t* d_end) {
+    EngineImpl* E = impl_.get();
+    GFFX_CUDA(cudaSetDevice(E->dev));
+    std::vector<uint32_t> ext;
+    std::vector<uint64_t> cum;
+    synth_seq_table(*E->H, &ext, &cum);
+    if (ext.empty() || cum.back() == 0) throw Err(E_ARG, "index has no root intervals to place regions on");
+    DBuf dcum, dext;
+    upload(dcum, cum, E->st);
+    upload(dext, ext, E->st);
+    if (n) synth_regions_kernel<<<(unsigned)((n + 255) / 256), 256, 0, E->st>>>(seed, first, n, length, dcum.as<uint64_t>(), dext.as<uint32_t>(),
+                                                                             (uint32_t)ext.size(), d_chr, d_start, d_end);
+    GFFX_CUDA(cudaStreamSynchronize(E->st));
+    GFFX_CUDA(cudaGetLastError());
+    dcum.release();
+    dext.release();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Engine facade
+// ------------------------------------------------------------------------------------------------
+Engine::Engine(std::unique_ptr<HostIndex> host, int device) : impl_(new EngineImpl(std::move(host), device)) {}
+Engine::~Engine() = default;
+const HostIndex& Engine::host() const { return *impl_->H; }
+int Engine::device() const { return impl_->dev; }
+uint64_t Engine::device_bytes() const { return impl_->dev_bytes; }
+const std::vector<uint32_t>& Engine::sorted_roots(uint32_t seq) const {
+    if (seq >= impl_->seq_sorted_roots.size()) throw Err(E_ARG, "sequence number out of range");
+    return impl_->seq_sorted_roots[seq];
+}
+int cuda_device_count() {
+    int n = 0;
+    return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
+}
+void Engine::counts_begin(int kind) { counts_begin_impl(impl_.get(), kind); }
+void Engine::counts_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags) {
+    counts_add_impl(impl_.get(), chr, start, end, n, flags);
+}
+void Engine::counts_finish(CountRows* rows) { counts_finish_impl(impl_.get(), rows); }
+double Engine::counts_kernel_ms() const { return counts_ms_impl(impl_.get()); }
+uint32_t Engine::counts_launches() const { return counts_launches_impl(impl_.get()); }
+void Engine::intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
+                       bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out) {
+    impl_->intersect(chr, start, end, n, mode, invert, entire_group, types_csv, flags, join_only, out);
+}
+
+}  // namespace gffx

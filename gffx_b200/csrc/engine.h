@@ -1,0 +1,69 @@
+// engine.h — the device-resident index and the GPU pipelines behind the C ABI (include/gffx_b200.h).
+// Host-only declarations: CUDA types stay inside engine.cu.
+#pragma once
+#include <memory>
+#include "host_index.h"
+
+namespace gffx {
+
+struct IntersectResult {
+    uint64_t n_queries = 0;
+    uint64_t n_pairs = 0;
+    std::vector<uint32_t> pairs;      // host copy (WANT_PAIRS)
+    const uint32_t* d_pairs = nullptr;  // device copy (PAIRS_ON_DEVICE / WANT_PAIRS), owned by the engine until the next call
+    uint64_t n_roots = 0;
+    uint64_t n_ranges = 0;
+    std::vector<uint64_t> ranges;     // host copy unless NO_HOST_COPY
+    uint64_t bytes_out = 0;
+    std::vector<uint32_t> warn_fids;
+    double kernel_ms = 0;
+    double stage_ms[5] = {0, 0, 0, 0, 0};
+    uint32_t launches = 0;
+};
+
+struct CountRows {
+    std::vector<uint32_t> id_idx, chrom_idx, start, end;
+    std::vector<uint64_t> value;
+};
+
+class EngineImpl;
+
+class Engine {
+   public:
+    // takes ownership of a fully built HostIndex and uploads it to `device`
+    Engine(std::unique_ptr<HostIndex> host, int device);
+    ~Engine();
+    const HostIndex& host() const;
+    int device() const;
+    uint64_t device_bytes() const;
+    // (start,end,root_fid) triples of one sequence's tree intervals, sorted by start
+    const std::vector<uint32_t>& sorted_roots(uint32_t seq) const;
+
+    // mode: 0 contained, 1 contains-region, 2 overlap.  join_only: stop after the root-level join.
+    void intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
+                   bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out);
+
+    // depth (kind 0) / coverage (kind 1)
+    void counts_begin(int kind);
+    void counts_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags);
+    void counts_finish(CountRows* rows);
+    double counts_kernel_ms() const;
+    uint32_t counts_launches() const;
+
+    void synth_regions_device(uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* d_chr, uint32_t* d_start,
+                              uint32_t* d_end);
+
+   private:
+    std::unique_ptr<EngineImpl> impl_;
+};
+
+int cuda_device_count();
+
+// synthetic workloads (synth.cpp)
+uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes, bool quirks);
+void synth_regions_host(const HostIndex& H, uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* chr,
+                        uint32_t* start, uint32_t* end);
+// per-sequence extent table shared by the host and device region generators
+void synth_seq_table(const HostIndex& H, std::vector<uint32_t>* seq_extent, std::vector<uint64_t>* cum);
+
+}  // namespace gffx

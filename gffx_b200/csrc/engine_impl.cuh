@@ -1,0 +1,101 @@
+// engine_impl.cuh — device state of one index (shared by engine.cu and counts.cu)
+#pragma once
+#include <cuda_runtime.h>
+#include "engine.h"
+#include "filter.cuh"
+#include "join.cuh"
+
+namespace gffx {
+
+#define GFFX_CUDA(call)                                                                                              \
+    do {                                                                                                             \
+        cudaError_t _e = (call);                                                                                     \
+        if (_e != cudaSuccess)                                                                                       \
+            throw Err(E_CUDA, std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " + __FILE__ + ":" +       \
+                                  std::to_string(__LINE__) + " (" #call ")");                                        \
+    } while (0)
+
+// grow-only device buffer
+struct DBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    size_t* total = nullptr;  // accounting
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+    void ensure(size_t bytes) {
+        if (bytes <= cap) return;
+        if (p) { cudaFree(p); if (total) *total -= cap; }
+        p = nullptr;
+        size_t want = bytes + bytes / 8 + 256;
+        GFFX_CUDA(cudaMalloc(&p, want));
+        cap = want;
+        if (total) *total += cap;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+template <class T> inline void upload(DBuf& b, const std::vector<T>& v, cudaStream_t st) {
+    b.ensure(std::max<size_t>(v.size(), 1) * sizeof(T));
+    if (!v.empty()) GFFX_CUDA(cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st));
+}
+
+struct CountsState;  // counts.cu
+
+class EngineImpl {
+   public:
+    std::unique_ptr<HostIndex> H;
+    int dev = 0;
+    cudaStream_t st = nullptr;
+    size_t dev_bytes = 0;
+    int sm_count = 148;
+
+    // ---- join index -------------------------------------------------------------------------
+    DBuf d_seq_list0, d_lists, d_ent_se, d_ent_fid, d_ent_blk, d_dir, d_ent_hit;
+    uint32_t n_ent = 0, n_lists = 0;
+    JoinIndex J{};
+    std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
+
+    // ---- blocks ------------------------------------------------------------------------------
+    DBuf d_bstart, d_bend, d_blk_sel;
+    uint32_t n_blocks = 0;
+
+    // ---- lines + filter rank space -----------------------------------------------------------
+    DBuf d_ln_flags, d_ln_blk, d_ln_type, d_ln_iseq, d_ln_S, d_ln_E, d_ln_iS, d_ln_iE, d_ln_off, d_ln_len;
+    DBuf d_fX, d_fdir, d_fseqs;
+    uint32_t f_slots = 0;
+    RankSpace FR{};
+    LineArrays LA{};
+    DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_type_allow;
+
+    // ---- per-call scratch --------------------------------------------------------------------
+    DBuf d_q[3], d_tile_count, d_tile_off, d_scan_scratch, d_pairs, d_ranges, d_small, d_warn;
+    void* h_small = nullptr;  // pinned, 256 B
+    cudaEvent_t ev[8];
+
+    // ---- counts (depth / coverage) -----------------------------------------------------------
+    CountsState* counts = nullptr;  // owned; freed by counts_release()
+
+    EngineImpl(std::unique_ptr<HostIndex> host, int device);
+    ~EngineImpl();
+    void build_join();
+    void build_blocks();
+    void build_lines();
+    void intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
+                   bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out);
+    // stage the regions on the device; returns device pointers (either the caller's or the staging buffers)
+    void stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
+                       const uint32_t** dc, const uint32_t** ds, const uint32_t** de);
+};
+
+// counts.cu
+void counts_release(EngineImpl* E);
+void counts_begin_impl(EngineImpl* E, int kind);
+void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags);
+void counts_finish_impl(EngineImpl* E, CountRows* rows);
+double counts_ms_impl(const EngineImpl* E);
+uint32_t counts_launches_impl(const EngineImpl* E);
+
+}  // namespace gffx

@@ -1,0 +1,290 @@
+// filter.cuh — K3/K4/K5: the line-level filter of write_gff_match_only_by_coords
+// (src/commands/intersect.rs:232-438; predicate gff_line_overlaps_queries :441-523, type filter
+// gff_type_allowed :80-102) and the block merge of write_gff_output (src/utils/common.rs:199-229).
+//
+// The reference tests every line of every selected block against EVERY region of the line's
+// sequence (O(L_sel x Q_seq)).  Here the fixed side (the lines) is turned into a rank space per
+// sequence at index-build time and the regions are scattered onto it in one streaming pass:
+//
+//   X_seq   sorted distinct raw column-4/5 values of the sequence's lines (L2-resident)
+//   slot k  of a sequence, k in [0,|X|], stands for "lb = #(X < v) == k"
+//   A[slot] (u64, atomicMax)  tag(seq)|(qe+1) at slot lb(qs)   -> prefix-max  PMX
+//   B[slot] (u64, atomicMin)  tag(seq)|qe     at slot ub(qs)   -> suffix-min  SMN
+//   Ms/Me[cell] (u8 marks)    cell = 2*slot + (v == X[k])      -> next-set    NS/NE
+//
+// and each line (rank iS, iE of its raw S, E precomputed) is decided with O(1) look-ups:
+//   Contained       exists q: qs<=S && E<=qe   <=>  PMX[iS] carries seq and value >= E+1
+//   ContainsRegion  exists q: S<=qs && qe<=E   <=>  SMN[iS+1] carries seq and value <= E
+//   Overlap  c1 qs<=S<=qe <=> PMX[iS]>=S+1 ; c2 same with E ; c3 some qs in [S,E] <=> NS[2iS+1] <= 2iE+1 ;
+//            c4 some qe in [S,E] <=> NE[..] (only regions with qs>qe are marked in Me: for qs<=qe
+//            c4 implies c1 or c3).
+// Every clause is the reference's clause translated literally, so inverted regions (qs>qe) and
+// inverted lines (S>E) behave as in the reference.  The sequence tag in the high bits lets one
+// plain (unsegmented) scan serve all sequences.
+#pragma once
+#include "scan.cuh"
+
+namespace gffx {
+
+struct RankSeq {  // per sequence, 32 B
+    uint32_t x0, cnt, dir_base, nb, shift, slot0, canon, pad;
+};
+
+struct RankSpace {
+    const uint32_t* X;
+    const uint32_t* dir;
+    const RankSeq* seqs;
+    uint32_t n_seqs;
+};
+
+// lb = #(X_seq < v) as a local index in [0,cnt]; *eq = (X_seq[lb] == v)
+__device__ __forceinline__ uint32_t rank_lb(const RankSpace& R, const RankSeq& S, uint32_t v, bool* eq) {
+    const uint32_t b = v >> S.shift;
+    *eq = false;
+    if (b >= S.nb) return S.cnt;
+    const uint2 d = make_uint2(__ldg(R.dir + S.dir_base + b), __ldg(R.dir + S.dir_base + b + 1));
+    uint32_t lo = d.x, hi = d.y;  // X[lo..hi) are the values inside bin b
+    const uint32_t* X = R.X + S.x0;
+    while (hi - lo > 4) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(X + mid) < v) lo = mid + 1; else hi = mid;
+    }
+    while (lo < hi && __ldg(X + lo) < v) lo++;
+    if (lo < S.cnt && __ldg(X + lo) == v) *eq = true;
+    return lo;
+}
+
+__device__ __forceinline__ RankSeq load_rank_seq(const RankSpace& R, uint32_t seq) {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(R.seqs + seq));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(R.seqs + seq) + 1);
+    RankSeq S;
+    S.x0 = a.x; S.cnt = a.y; S.dir_base = a.z; S.nb = a.w;
+    S.shift = b.x; S.slot0 = b.y; S.canon = b.z; S.pad = 0;
+    return S;
+}
+
+constexpr int FILT_THREADS = 256;
+constexpr int FILT_QPT = 4;
+constexpr uint64_t TAG_MAX_SHIFT = 33;  // A keys: seq<<33 | (qe+1)
+constexpr uint64_t TAG_MIN_SHIFT = 32;  // B keys: seq<<32 | qe
+
+struct FilterArrays {
+    unsigned long long* A;  // n_slots
+    unsigned long long* B;  // n_slots
+    uint8_t* Ms;            // 2*n_slots
+    uint8_t* Me;            // 2*n_slots
+};
+
+// one streaming pass over the regions (12 B read per region, 1-3 scattered L2 updates)
+template <int MODE>
+__global__ void __launch_bounds__(FILT_THREADS)
+    scatter_regions_kernel(RankSpace R, FilterArrays F, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs,
+                           const uint32_t* __restrict__ qe, uint64_t n, bool aligned) {
+    const uint64_t q0 = ((uint64_t)blockIdx.x * FILT_THREADS + threadIdx.x) * FILT_QPT;
+    if (q0 >= n) return;
+    uint32_t c[FILT_QPT], s[FILT_QPT], e[FILT_QPT];
+    int m = 0;
+    if (q0 + FILT_QPT <= n && aligned) {
+        const uint4 a = __ldcs(reinterpret_cast<const uint4*>(chr + q0));
+        const uint4 b = __ldcs(reinterpret_cast<const uint4*>(qs + q0));
+        const uint4 d = __ldcs(reinterpret_cast<const uint4*>(qe + q0));
+        c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w;
+        s[0] = b.x; s[1] = b.y; s[2] = b.z; s[3] = b.w;
+        e[0] = d.x; e[1] = d.y; e[2] = d.z; e[3] = d.w;
+        m = FILT_QPT;
+    } else {
+        for (int k = 0; k < FILT_QPT; k++)
+            if (q0 + k < n) { c[k] = chr[q0 + k]; s[k] = qs[q0 + k]; e[k] = qe[q0 + k]; m = k + 1; }
+    }
+#pragma unroll
+    for (int k = 0; k < FILT_QPT; k++) {
+        if (k >= m || c[k] >= R.n_seqs) continue;
+        const RankSeq S = load_rank_seq(R, c[k]);
+        if (!S.canon || S.cnt == 0) continue;  // no line of this sequence can ever match
+        bool eq;
+        const uint32_t lb = rank_lb(R, S, s[k], &eq);
+        const uint32_t slot = S.slot0 + lb;
+        if (MODE == 0) {
+            atomicMax(F.A + slot, ((unsigned long long)c[k] << TAG_MAX_SHIFT) | ((unsigned long long)e[k] + 1ull));
+        } else if (MODE == 1) {
+            atomicMin(F.B + slot + (eq ? 1u : 0u), ((unsigned long long)c[k] << TAG_MIN_SHIFT) | (unsigned long long)e[k]);
+        } else {
+            atomicMax(F.A + slot, ((unsigned long long)c[k] << TAG_MAX_SHIFT) | ((unsigned long long)e[k] + 1ull));
+            F.Ms[2ull * slot + (eq ? 1u : 0u)] = 1;
+            if (s[k] > e[k]) {
+                bool eq2;
+                const uint32_t lb2 = rank_lb(R, S, e[k], &eq2);
+                F.Me[2ull * (S.slot0 + lb2) + (eq2 ? 1u : 0u)] = 1;
+            }
+        }
+    }
+}
+
+struct LineArrays {
+    const uint8_t* flags;    // LN_I_OK bit
+    const uint32_t* blk;
+    const uint32_t* type_id;
+    const uint32_t* iseq;
+    const uint32_t* S;
+    const uint32_t* E;
+    const uint32_t* iS;      // global slot of rank(S)  (slot0 + local rank)
+    const uint32_t* iE;
+    const uint64_t* off;
+    const uint32_t* len;
+    uint64_t n;
+};
+
+struct FilterScans {
+    const unsigned long long* PMX;  // inclusive prefix max of A
+    const unsigned long long* SMN;  // inclusive suffix min of B
+    const uint32_t* NS;             // next marked cell >= c in Ms
+    const uint32_t* NE;             // same for Me
+};
+
+template <int MODE>
+__device__ __forceinline__ bool line_matches(const LineArrays& L, const FilterScans& P, uint64_t i) {
+    const uint32_t seq = L.iseq[i], S = L.S[i], E = L.E[i], iS = L.iS[i], iE = L.iE[i];
+    if (MODE == 0) {
+        const unsigned long long k = P.PMX[iS];
+        return (k >> TAG_MAX_SHIFT) == seq && (k & ((1ull << TAG_MAX_SHIFT) - 1)) >= (unsigned long long)E + 1ull;
+    } else if (MODE == 1) {
+        const unsigned long long k = P.SMN[iS + 1];
+        return (k >> TAG_MIN_SHIFT) == seq && (uint32_t)k <= E;
+    } else {
+        const unsigned long long mask = (1ull << TAG_MAX_SHIFT) - 1;
+        const unsigned long long k1 = P.PMX[iS];
+        if ((k1 >> TAG_MAX_SHIFT) == seq && (k1 & mask) >= (unsigned long long)S + 1ull) return true;  // qs<=S<=qe
+        const unsigned long long k2 = P.PMX[iE];
+        if ((k2 >> TAG_MAX_SHIFT) == seq && (k2 & mask) >= (unsigned long long)E + 1ull) return true;  // qs<=E<=qe
+        if (S <= E) {
+            const uint32_t c0 = 2u * iS + 1u, c1 = 2u * iE + 1u;
+            if (P.NS[c0] <= c1) return true;  // S<=qs<=E
+            if (P.NE[c0] <= c1) return true;  // S<=qe<=E
+        }
+        return false;
+    }
+}
+
+constexpr int LINE_THREADS = 256;
+
+// pass 1: per-line decision -> keep flag (byte) + per-CTA count
+template <int MODE>
+__global__ void __launch_bounds__(LINE_THREADS)
+    eval_lines_kernel(LineArrays L, FilterScans P, const uint8_t* __restrict__ blk_sel, const uint8_t* __restrict__ type_allow,
+                      bool have_types, uint8_t* __restrict__ keep, uint32_t* __restrict__ tile_count) {
+    __shared__ uint32_t sm[LINE_THREADS / 32 + 1];
+    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
+    uint32_t k = 0;
+    if (i < L.n) {
+        bool ok = (L.flags[i] & 1) && blk_sel[L.blk[i]];
+        if (ok && have_types) {
+            const uint32_t t = L.type_id[i];
+            ok = t != 0xFFFFFFFFu && type_allow[t];
+        }
+        if (ok) ok = line_matches<MODE>(L, P, i);
+        k = ok ? 1u : 0u;
+        keep[i] = (uint8_t)k;
+    }
+    uint32_t tot;
+    block_scan_excl(k, OpSum(), 0u, sm, &tot);
+    if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
+}
+
+// pass 2: order-preserving compaction of (offset, offset+len)
+static __global__ void __launch_bounds__(LINE_THREADS)
+    emit_ranges_kernel(LineArrays L, const uint8_t* __restrict__ keep, const uint64_t* __restrict__ tile_off,
+                       ulonglong2* __restrict__ ranges, unsigned long long* __restrict__ bytes_out) {
+    __shared__ uint32_t sm[LINE_THREADS / 32 + 1];
+    __shared__ unsigned long long sb[LINE_THREADS / 32 + 1];
+    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
+    const uint32_t k = (i < L.n && keep[i]) ? 1u : 0u;
+    uint32_t tot;
+    const uint32_t pos = block_scan_excl(k, OpSum(), 0u, sm, &tot);
+    unsigned long long len = 0;
+    if (k) {
+        const uint64_t o = L.off[i];
+        len = L.len[i];
+        ranges[tile_off[blockIdx.x] + pos] = make_ulonglong2(o, o + len);
+    }
+    unsigned long long btot;
+    block_scan_excl(len, OpSum(), 0ull, sb, &btot);
+    if (threadIdx.x == 0 && btot) atomicAdd(bytes_out, btot);
+}
+
+// K5, one CTA: selected blocks (sorted by start) -> merged byte ranges, rules of common.rs:199-245:
+// drop sentinel starts, merge while s <= current_end, keep cs < ce and ce <= file_len.
+// Also counts the selected blocks.  out_counts[0] = n_ranges, [1] = n_selected, [2..3] = bytes (u64).
+static __global__ void __launch_bounds__(1024)
+    merge_blocks_kernel(const uint64_t* __restrict__ bstart, const uint64_t* __restrict__ bend, const uint8_t* __restrict__ blk_sel,
+                        uint32_t n_blocks, uint64_t file_len, bool emit, ulonglong2* __restrict__ ranges,
+                        unsigned long long* __restrict__ out_counts) {
+    __shared__ unsigned long long smax[1024 / 32 + 1];
+    __shared__ uint32_t ssum[1024 / 32 + 1];
+    __shared__ unsigned long long sbytes[1024 / 32 + 1];
+    // carried across chunks (same value in every thread)
+    unsigned long long run_max = 0;      // max end over selected blocks so far
+    uint32_t n_sel = 0, n_out = 0;
+    unsigned long long cur_start = 0;    // start of the open segment
+    bool open = false;
+    unsigned long long bytes = 0;
+    for (uint32_t base = 0; base < n_blocks; base += 1024) {
+        const uint32_t b = base + threadIdx.x;
+        const bool sel = b < n_blocks && blk_sel[b] && bstart[b] != 0xFFFFFFFFFFFFFFFFull;
+        const unsigned long long s = sel ? bstart[b] : 0, e = sel ? bend[b] : 0;
+        unsigned long long tot_max;
+        unsigned long long ex_max = block_scan_excl((unsigned long long)e, OpMax(), 0ull, smax, &tot_max);
+        __syncthreads();
+        uint32_t tot_sel;
+        const uint32_t ex_sel = block_scan_excl(sel ? 1u : 0u, OpSum(), 0u, ssum, &tot_sel);
+        __syncthreads();
+        const unsigned long long prev_max = ex_max > run_max ? ex_max : run_max;   // max end of selected blocks before b
+        const bool first = sel && (n_sel + ex_sel == 0);
+        const bool head = sel && (first || s > prev_max);
+        // a head closes the previous segment [seg_start, prev_max); find seg_start: it is the start of the
+        // previous head — carried via a second scan over (head ? index : 0) would need another pass, so
+        // instead every head publishes itself and the NEXT head (or the tail) closes it.
+        // Step 1: exclusive count of heads -> slot of each segment in `ranges` (unfiltered).
+        uint32_t tot_head;
+        const uint32_t ex_head = block_scan_excl(head ? 1u : 0u, OpSum(), 0u, ssum, &tot_head);
+        __syncthreads();
+        (void)ex_head;
+        // Close segments: a segment ends right before each head (with end prev_max) and at the very end.
+        // Thread with a head at b closes the segment that was open before it.
+        // Its start is the most recent head start before b: exclusive max-scan of (head ? s+1 : 0).
+        unsigned long long tot_hs;
+        unsigned long long ex_hs = block_scan_excl(head ? s + 1ull : 0ull, OpMax(), 0ull, smax, &tot_hs);
+        __syncthreads();
+        unsigned long long seg_start_p1 = ex_hs ? ex_hs : (open ? cur_start + 1ull : 0ull);
+        const bool closes = head && seg_start_p1 != 0;
+        const unsigned long long cs = seg_start_p1 - 1ull, ce = prev_max;
+        const bool good = closes && cs < ce && ce <= file_len;
+        uint32_t tot_good;
+        const uint32_t ex_good = block_scan_excl(good ? 1u : 0u, OpSum(), 0u, ssum, &tot_good);
+        __syncthreads();
+        if (good && emit) ranges[n_out + ex_good] = make_ulonglong2(cs, ce);
+        unsigned long long tot_b;
+        block_scan_excl(good ? ce - cs : 0ull, OpSum(), 0ull, sbytes, &tot_b);
+        __syncthreads();
+        bytes += tot_b;
+        n_out += tot_good;
+        // carry
+        if (tot_hs) { cur_start = tot_hs - 1ull; open = true; }
+        run_max = tot_max > run_max ? tot_max : run_max;
+        n_sel += tot_sel;
+    }
+    if (threadIdx.x == 0) {
+        if (open) {
+            const unsigned long long cs = cur_start, ce = run_max;
+            if (cs < ce && ce <= file_len) {
+                if (emit) ranges[n_out] = make_ulonglong2(cs, ce);
+                n_out++;
+                bytes += ce - cs;
+            }
+        }
+        out_counts[0] = n_out;
+        out_counts[1] = n_sel;
+        out_counts[2] = bytes;
+    }
+}
+
+}  // namespace gffx

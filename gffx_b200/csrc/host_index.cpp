@@ -1,0 +1,561 @@
+#include "host_index.h"
+#include <algorithm>
+#include <thread>
+#include <fcntl.h>
+#include <sys/uio.h>
+#include <unistd.h>
+
+namespace gffx {
+
+// ------------------------------------------------------------------------------------------
+// StringPool
+// ------------------------------------------------------------------------------------------
+uint32_t StringPool::intern(std::string_view s) {
+    auto it = map.find(s);
+    if (it != map.end()) return it->second;
+    keys.push_back(std::make_unique<std::string>(s));
+    uint32_t id = (uint32_t)(keys.size() - 1);
+    map.emplace(std::string_view(*keys.back()), id);
+    return id;
+}
+int64_t StringPool::find(std::string_view s) const {
+    auto it = map.find(s);
+    return it == map.end() ? -1 : (int64_t)it->second;
+}
+
+// ------------------------------------------------------------------------------------------
+// On-disk files
+// ------------------------------------------------------------------------------------------
+void load_sqs_file(const std::string& path, std::vector<std::string>* names) {
+    Mapped m;
+    if (!m.try_open(path)) throw Err(E_IO, "Failed to open SQS file: \"" + path + "\"");
+    names->clear();
+    const uint8_t* p = m.data();
+    const uint8_t* end = p + m.size();
+    while (p < end) {  // BufRead::lines(): '\n' terminated, one trailing '\r' stripped
+        const uint8_t* nl = find_byte(p, end, '\n');
+        const uint8_t* stop = nl ? nl : end;
+        const uint8_t* last = stop;
+        if (nl && last > p && last[-1] == '\r') last--;
+        names->emplace_back((const char*)p, (size_t)(last - p));
+        p = stop + 1;
+    }
+}
+
+static std::vector<uint64_t> read_rix(const std::string& path) {
+    Mapped m;
+    if (!m.try_open(path)) throw Err(E_IO, "open " + path);
+    // a JSON array of unsigned integers, compact or pretty-printed (src/utils/tree_io.rs:57-63)
+    std::vector<uint64_t> v;
+    const uint8_t* p = m.data();
+    const uint8_t* end = p + m.size();
+    auto ws = [&] { while (p < end && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) p++; };
+    ws();
+    if (p >= end || *p != '[') throw Err(E_FORMAT, "parse json " + path);
+    p++;
+    ws();
+    if (p < end && *p == ']') return v;
+    for (;;) {
+        ws();
+        if (p >= end || *p < '0' || *p > '9') throw Err(E_FORMAT, "parse json " + path);
+        uint64_t x = 0;
+        while (p < end && *p >= '0' && *p <= '9') x = x * 10 + (uint64_t)(*p++ - '0');
+        v.push_back(x);
+        ws();
+        if (p < end && *p == ',') { p++; continue; }
+        if (p < end && *p == ']') break;
+        throw Err(E_FORMAT, "parse json " + path);
+    }
+    return v;
+}
+
+// Flattens one bincode2-encoded IntervalTree<u32> (grammar in SURVEY.md App. B) without building
+// nodes: every OptNode still owed is counted in `owed`; a present node owes two more.
+static void flatten_tree(const uint8_t* p, size_t n, uint32_t seq, size_t tree_no, std::vector<RootIv>* out) {
+    size_t pos = 0;
+    uint64_t owed = 1;
+    auto fail = [&]() -> void { throw Err(E_FORMAT, "bincode2 deserialize tree #" + std::to_string(tree_no)); };
+    while (owed > 0) {
+        if (pos >= n) fail();
+        uint8_t tag = p[pos++];
+        owed--;
+        if (tag == 0) continue;
+        if (tag != 1) fail();
+        if (n - pos < 12) fail();
+        pos += 4;  // center: only needed by the pointer tree, not by the flat layout
+        uint64_t cnt;
+        memcpy(&cnt, p + pos, 8);
+        pos += 8;
+        if (cnt > (n - pos) / 12) fail();
+        for (uint64_t i = 0; i < cnt; i++) {
+            uint32_t t[3];
+            memcpy(t, p + pos, 12);
+            pos += 12;
+            out->push_back(RootIv{seq, t[0], t[1], t[2]});
+        }
+        owed += 2;
+    }
+}
+
+void load_trees_flat(const std::string& rit_path, const std::string& rix_path, std::vector<RootIv>* out, uint32_t* n_trees) {
+    Mapped rit;
+    if (!rit.try_open(rit_path)) throw Err(E_IO, "open " + rit_path);
+    std::vector<uint64_t> offs = read_rix(rix_path);
+    *n_trees = (uint32_t)offs.size();
+    if (offs.empty()) return;
+    for (size_t i = 1; i < offs.size(); i++)
+        if (offs[i - 1] > offs[i]) throw Err(E_FORMAT, "offsets not sorted ascending");
+    if (offs.back() > rit.size()) throw Err(E_FORMAT, "last offset out of file size");
+    for (size_t i = 0; i < offs.size(); i++) {
+        uint64_t s = offs[i], e = i + 1 < offs.size() ? offs[i + 1] : rit.size();
+        flatten_tree(rit.data() + s, (size_t)(e - s), (uint32_t)i, i, out);
+    }
+}
+
+void load_gof_file(const std::string& path, std::vector<uint32_t>* fid, std::vector<uint64_t>* s, std::vector<uint64_t>* e) {
+    Mapped m;
+    if (!m.try_open(path)) throw Err(E_IO, "Failed to mmap " + path);
+    if (m.size() % 24 != 0)
+        throw Err(E_FORMAT, "Corrupted GOF (" + path + "): length " + std::to_string(m.size()) + " not multiple of 24");
+    size_t n = m.size() / 24;
+    fid->resize(n);
+    s->resize(n);
+    e->resize(n);
+    for (size_t i = 0; i < n; i++) {
+        const uint8_t* r = m.data() + 24 * i;
+        memcpy(&(*fid)[i], r, 4);  // bytes 4..8: seq number (0 in files of older writers) — unused here
+        memcpy(&(*s)[i], r + 8, 8);
+        memcpy(&(*e)[i], r + 16, 8);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// HostIndex
+// ------------------------------------------------------------------------------------------
+void HostIndex::open(const std::string& path, int threads) {
+    gff_path = path;
+    load_sqs_file(path + ".sqs", &seq_names);
+    uint32_t n_trees = 0;
+    load_trees_flat(path + ".rit", path + ".rix", &roots, &n_trees);
+    std::vector<uint32_t> gfid;
+    std::vector<uint64_t> gs, ge;
+    load_gof_file(path + ".gof", &gfid, &gs, &ge);
+    if (gff_map.try_open(path)) {
+        gff = gff_map.data();
+        gff_len = gff_map.size();
+    }
+    finish(gfid, gs, ge, threads);
+}
+
+void HostIndex::create(uint32_t n_seqs, const char* const* names, uint64_t n_roots, const uint32_t* rseq, const uint32_t* rs,
+                       const uint32_t* re, const uint32_t* rfid, uint64_t n_gof, const uint32_t* gfid, const uint64_t* gs,
+                       const uint64_t* ge, const uint8_t* text, uint64_t text_len, int threads) {
+    seq_names.assign(names, names + n_seqs);
+    roots.resize(n_roots);
+    for (uint64_t i = 0; i < n_roots; i++) roots[i] = RootIv{rseq[i], rs[i], re[i], rfid[i]};
+    gff = text;
+    gff_len = text ? text_len : 0;
+    finish(std::vector<uint32_t>(gfid, gfid + n_gof), std::vector<uint64_t>(gs, gs + n_gof), std::vector<uint64_t>(ge, ge + n_gof),
+           threads);
+}
+
+void HostIndex::finish(const std::vector<uint32_t>& gfid, const std::vector<uint64_t>& gs, const std::vector<uint64_t>& ge,
+                       int threads) {
+    seq_num.clear();
+    for (size_t i = 0; i < seq_names.size(); i++) seq_num[seq_names[i]] = (uint32_t)i;
+    // trees beyond .sqs would make the reference index out of bounds (intersect.rs:125); refuse them here
+    for (const RootIv& r : roots)
+        if (r.seq >= seq_names.size()) throw Err(E_FORMAT, "tree sequence number beyond the .sqs list");
+
+    // reachable blocks: the last .gof record of each fid (GofMap::index, gof.rs:32-37)
+    std::unordered_map<uint32_t, size_t> last;
+    last.reserve(gfid.size() * 2);
+    for (size_t i = 0; i < gfid.size(); i++) last[gfid[i]] = i;
+    std::vector<size_t> keep;
+    keep.reserve(last.size());
+    for (size_t i = 0; i < gfid.size(); i++)
+        if (last[gfid[i]] == i) keep.push_back(i);
+    std::stable_sort(keep.begin(), keep.end(), [&](size_t a, size_t b) { return gs[a] < gs[b]; });
+    blocks.resize(keep.size());
+    std::unordered_map<uint32_t, uint32_t> fid_blk;
+    fid_blk.reserve(keep.size() * 2);
+    for (size_t k = 0; k < keep.size(); k++) {
+        blocks[k] = Block{gfid[keep[k]], gs[keep[k]], ge[keep[k]]};
+        fid_blk[blocks[k].fid] = (uint32_t)k;
+    }
+    root_blk.resize(roots.size());
+    for (size_t i = 0; i < roots.size(); i++) {
+        auto it = fid_blk.find(roots[i].fid);
+        root_blk[i] = it == fid_blk.end() ? NONE32 : it->second;
+    }
+    build_lines(threads);
+}
+
+namespace {
+
+struct LocalDict {
+    std::vector<std::string> items;
+    std::unordered_map<std::string, uint32_t> map;
+    std::string last;
+    uint32_t last_id = NONE32;
+    uint32_t get(const uint8_t* p, size_t n) {
+        if (last_id != NONE32 && last.size() == n && memcmp(last.data(), p, n) == 0) return last_id;
+        last.assign((const char*)p, n);
+        auto it = map.find(last);
+        if (it == map.end()) {
+            last_id = (uint32_t)items.size();
+            items.push_back(last);
+            map.emplace(last, last_id);
+        } else {
+            last_id = it->second;
+        }
+        return last_id;
+    }
+};
+
+struct Part {  // lines of a contiguous range of blocks
+    LineTable t;
+    std::vector<uint64_t> id_off;  // absolute offset of the ID string (d_ok lines)
+    std::vector<uint32_t> id_len;
+    LocalDict types, chroms;
+    std::vector<uint64_t> blk_nlines;
+    std::vector<uint8_t> blk_utf8;
+};
+
+// fast_id of src/commands/depth.rs:104-118: first "ID=" anywhere in column 9, value up to ; space tab
+inline bool find_id(const uint8_t* a, size_t n, size_t* vs, size_t* vn) {
+    for (size_t i = 0; i + 2 < n; i++) {
+        if (a[i] == 'I' && a[i + 1] == 'D' && a[i + 2] == '=') {
+            size_t j = i + 3;
+            while (j < n && a[j] != ';' && a[j] != ' ' && a[j] != '\t') j++;
+            *vs = i + 3;
+            *vn = j - (i + 3);
+            return true;
+        }
+    }
+    return false;
+}
+
+}  // namespace
+
+void HostIndex::build_lines(int threads) {
+    const size_t nb = blocks.size();
+    blk_utf8.assign(nb, 0);
+    blk_line0.assign(nb + 1, 0);
+    lines = LineTable();
+    if (!gff || gff_len == 0 || nb == 0) return;
+    if (threads < 1) threads = 1;
+    size_t nparts = std::min<size_t>((size_t)threads, std::max<size_t>(1, nb / 64));
+    std::vector<Part> parts(nparts);
+    // split blocks so that each part scans about the same number of bytes
+    std::vector<size_t> cut(nparts + 1, nb);
+    {
+        uint64_t total = 0;
+        for (size_t b = 0; b < nb; b++) if (block_scannable(b)) total += std::min<uint64_t>(blocks[b].end, gff_len) - blocks[b].start;
+        uint64_t acc = 0;
+        size_t k = 0;
+        cut[0] = 0;
+        for (size_t b = 0; b < nb && k + 1 < nparts; b++) {
+            if (acc >= (total / nparts) * (k + 1)) cut[++k] = b;
+            if (block_scannable(b)) acc += std::min<uint64_t>(blocks[b].end, gff_len) - blocks[b].start;
+        }
+        for (size_t j = k + 1; j < nparts; j++) cut[j] = nb;
+        cut[nparts] = nb;
+    }
+    auto work = [&](size_t pi) {
+        Part& P = parts[pi];
+        size_t b0 = cut[pi], b1 = cut[pi + 1];
+        P.blk_nlines.assign(b1 - b0, 0);
+        P.blk_utf8.assign(b1 - b0, 0);
+        for (size_t b = b0; b < b1; b++) {
+            if (!block_scannable(b)) continue;
+            const uint64_t bs = blocks[b].start, be = std::min<uint64_t>(blocks[b].end, gff_len);
+            const bool u8ok = utf8_ok(gff + bs, (size_t)(be - bs));
+            P.blk_utf8[b - b0] = u8ok;
+            const bool countable = block_countable(b) && blocks[b].end <= gff_len;
+            const uint8_t* p = gff + bs;
+            const uint8_t* end = gff + be;
+            uint64_t nl_count = 0;
+            while (p < end) {
+                const uint8_t* nl = find_byte(p, end, '\n');
+                const uint8_t* next = nl ? nl + 1 : end;
+                const uint8_t* q = nl ? nl : end;  // line body [p,q)
+                if (q > p && p[0] != '#') {
+                    const uint8_t* tab[8];
+                    int nt = 0;
+                    const uint8_t* c = p;
+                    while (nt < 8) {
+                        const uint8_t* t = find_byte(c, q, '\t');
+                        if (!t) break;
+                        tab[nt++] = t;
+                        c = t + 1;
+                    }
+                    uint8_t fl = 0;
+                    uint32_t S = 0, E = 0, iseq = NONE32, ty = NONE32, fs = 0, fe = 0, chrom = NONE32;
+                    bool numok = false;
+                    if (nt >= 3 && utf8_ok(tab[1] + 1, (size_t)(tab[2] - tab[1] - 1)))
+                        ty = P.types.get(tab[1] + 1, (size_t)(tab[2] - tab[1] - 1));
+                    if (nt >= 5) {
+                        numok = parse_u32_strict(tab[2] + 1, (size_t)(tab[3] - tab[2] - 1), &S) &&
+                                parse_u32_strict(tab[3] + 1, (size_t)(tab[4] - tab[3] - 1), &E);
+                        if (numok && utf8_ok(p, (size_t)(tab[0] - p))) {
+                            auto it = seq_num.find(std::string((const char*)p, (size_t)(tab[0] - p)));
+                            if (it != seq_num.end()) { iseq = it->second; fl |= LN_I_OK; }
+                        }
+                    }
+                    size_t ivs = 0, ivn = 0;
+                    if (nt >= 8 && numok && E != 0 && u8ok && countable &&
+                        find_id(tab[7] + 1, (size_t)(q - tab[7] - 1), &ivs, &ivn)) {
+                        uint32_t a = std::min(S, E), z = std::max(S, E);
+                        fs = a == 0 ? 0 : a - 1;
+                        fe = z;
+                        chrom = P.chroms.get(p, (size_t)(tab[0] - p));
+                        fl |= LN_D_OK;
+                    }
+                    LineTable& t = P.t;
+                    t.off.push_back((uint64_t)(p - gff));
+                    t.len.push_back((uint32_t)(next - p));
+                    t.blk.push_back((uint32_t)b);
+                    t.flags.push_back(fl);
+                    t.S.push_back(S); t.E.push_back(E); t.iseq.push_back(iseq); t.type_id.push_back(ty);
+                    t.fs.push_back(fs); t.fe.push_back(fe); t.chrom.push_back(chrom);
+                    if (fl & LN_D_OK) {
+                        P.id_off.push_back((uint64_t)(tab[7] + 1 + ivs - gff));
+                        P.id_len.push_back((uint32_t)ivn);
+                    } else {
+                        P.id_off.push_back(0);
+                        P.id_len.push_back(0);
+                    }
+                    nl_count++;
+                }
+                p = next;
+            }
+            P.blk_nlines[b - b0] = nl_count;
+        }
+    };
+    if (nparts == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (size_t i = 0; i < nparts; i++) th.emplace_back(work, i);
+        for (auto& t : th) t.join();
+    }
+    // concatenate, remapping the per-part dictionaries; intern IDs serially (dictionary order = file order)
+    size_t total = 0;
+    for (auto& P : parts) total += P.t.size();
+    LineTable& L = lines;
+    L.off.reserve(total); L.len.reserve(total); L.blk.reserve(total); L.flags.reserve(total);
+    L.S.reserve(total); L.E.reserve(total); L.iseq.reserve(total); L.type_id.reserve(total);
+    L.fs.reserve(total); L.fe.reserve(total); L.id.reserve(total); L.chrom.reserve(total);
+    ids.map.reserve(total);
+    for (size_t pi = 0; pi < nparts; pi++) {
+        Part& P = parts[pi];
+        std::vector<uint32_t> tmap(P.types.items.size()), cmap(P.chroms.items.size());
+        for (size_t i = 0; i < tmap.size(); i++) tmap[i] = types.intern(P.types.items[i]);
+        for (size_t i = 0; i < cmap.size(); i++) cmap[i] = chroms.intern(P.chroms.items[i]);
+        for (size_t b = cut[pi]; b < cut[pi + 1]; b++) {
+            blk_utf8[b] = P.blk_utf8[b - cut[pi]];
+            blk_line0[b + 1] = P.blk_nlines[b - cut[pi]];
+        }
+        const LineTable& t = P.t;
+        for (size_t i = 0; i < t.size(); i++) {
+            L.off.push_back(t.off[i]); L.len.push_back(t.len[i]); L.blk.push_back(t.blk[i]); L.flags.push_back(t.flags[i]);
+            L.S.push_back(t.S[i]); L.E.push_back(t.E[i]); L.iseq.push_back(t.iseq[i]);
+            L.type_id.push_back(t.type_id[i] == NONE32 ? NONE32 : tmap[t.type_id[i]]);
+            L.fs.push_back(t.fs[i]); L.fe.push_back(t.fe[i]);
+            L.chrom.push_back(t.chrom[i] == NONE32 ? NONE32 : cmap[t.chrom[i]]);
+            if (t.flags[i] & LN_D_OK)
+                L.id.push_back(ids.intern(std::string_view((const char*)gff + P.id_off[i], P.id_len[i])));
+            else
+                L.id.push_back(NONE32);
+        }
+        P = Part();
+    }
+    for (size_t b = 0; b < nb; b++) blk_line0[b + 1] += blk_line0[b];
+}
+
+// ------------------------------------------------------------------------------------------
+// BED parsing
+// ------------------------------------------------------------------------------------------
+void parse_bed_intersect(const std::string& path, const std::unordered_map<std::string, uint32_t>& seq_num, Regions* out) {
+    Mapped m;
+    m.open(path);
+    const uint8_t* p = m.data();
+    const uint8_t* end = p + m.size();
+    std::string name, last_name;
+    uint32_t last_chr = NONE32;
+    bool have_last = false;
+    while (p < end) {
+        const uint8_t* nl = find_byte(p, end, '\n');
+        const uint8_t* q = nl ? nl : end;
+        const uint8_t* line = p;
+        p = q + 1;
+        if (q == line || line[0] == '#') continue;
+        if (!utf8_ok(line, (size_t)(q - line))) throw Err(E_FORMAT, "invalid utf-8 sequence in BED file " + path);
+        const uint8_t* f[3];
+        size_t fl[3];
+        int nf = 0;
+        const uint8_t* c = line;
+        while (nf < 3) {  // split_ascii_whitespace
+            while (c < q && ascii_ws(*c)) c++;
+            if (c >= q) break;
+            const uint8_t* s = c;
+            while (c < q && !ascii_ws(*c)) c++;
+            f[nf] = s;
+            fl[nf] = (size_t)(c - s);
+            nf++;
+        }
+        if (nf < 3) continue;
+        uint32_t chr;
+        if (have_last && last_name.size() == fl[0] && memcmp(last_name.data(), f[0], fl[0]) == 0) {
+            chr = last_chr;
+        } else {
+            last_name.assign((const char*)f[0], fl[0]);
+            auto it = seq_num.find(last_name);
+            last_chr = it == seq_num.end() ? NONE32 : it->second;
+            have_last = true;
+            chr = last_chr;
+        }
+        if (chr == NONE32) continue;  // unknown chromosome: skipped BEFORE the numbers are looked at
+        uint32_t s, e;
+        if (!parse_u32_strict(f[1], fl[1], &s))
+            throw Err(E_FORMAT, "BED " + path + ": cannot parse start '" + std::string((const char*)f[1], fl[1]) + "' as u32");
+        if (!parse_u32_strict(f[2], fl[2], &e))
+            throw Err(E_FORMAT, "BED " + path + ": cannot parse end '" + std::string((const char*)f[2], fl[2]) + "' as u32");
+        out->chr.push_back(chr);
+        out->start.push_back(s);
+        out->end.push_back(e);
+    }
+}
+
+static bool bed_counts_line(const uint8_t* line, const uint8_t* q, const std::unordered_map<std::string, uint32_t>& seq_num,
+                            std::string& scratch, uint32_t* chr, uint32_t* s, uint32_t* e) {
+    if (q == line || line[0] == '#') return false;
+    const uint8_t* f[3];
+    size_t fl[3];
+    int nf = 0;
+    const uint8_t* c = line;
+    while (nf < 3) {  // split on '\t' or ' ', empty fields dropped; '\n' and '\r' stay inside fields
+        while (c < q && (*c == '\t' || *c == ' ')) c++;
+        if (c >= q) break;
+        const uint8_t* st = c;
+        while (c < q && *c != '\t' && *c != ' ') c++;
+        f[nf] = st;
+        fl[nf] = (size_t)(c - st);
+        nf++;
+    }
+    if (nf < 3) return false;
+    if (!utf8_ok(f[0], fl[0]) || !utf8_ok(f[1], fl[1]) || !utf8_ok(f[2], fl[2])) return false;
+    if (!parse_u32_rust(std::string_view((const char*)f[1], fl[1]), s)) return false;
+    if (!parse_u32_rust(rtrim_unicode(std::string_view((const char*)f[2], fl[2])), e)) return false;
+    if (*s >= *e) return false;
+    scratch.assign((const char*)f[0], fl[0]);
+    auto it = seq_num.find(scratch);
+    if (it == seq_num.end()) return false;
+    *chr = it->second;
+    return true;
+}
+
+void parse_bed_counts(const std::string& path, const std::unordered_map<std::string, uint32_t>& seq_num, int threads, Regions* out) {
+    Mapped m;
+    m.open(path);
+    const uint8_t* base = m.data();
+    const size_t n = m.size();
+    if (threads < 1) threads = 1;
+    size_t nparts = std::min<size_t>((size_t)threads, std::max<size_t>(1, n >> 20));
+    std::vector<size_t> cut(nparts + 1);
+    cut[0] = 0;
+    cut[nparts] = n;
+    for (size_t k = 1; k < nparts; k++) {  // cut at line starts
+        size_t c = n / nparts * k;
+        const uint8_t* nl = find_byte(base + c, base + n, '\n');
+        cut[k] = nl ? (size_t)(nl - base) + 1 : n;
+    }
+    std::vector<Regions> parts(nparts);
+    auto work = [&](size_t k) {
+        std::string scratch;
+        const uint8_t* p = base + cut[k];
+        const uint8_t* end = base + cut[k + 1];
+        Regions& R = parts[k];
+        while (p < end) {
+            const uint8_t* nl = find_byte(p, end, '\n');
+            const uint8_t* q = nl ? nl + 1 : end;  // the reference's line slice keeps its '\n'
+            uint32_t c, s, e;
+            if (bed_counts_line(p, q, seq_num, scratch, &c, &s, &e)) {
+                R.chr.push_back(c);
+                R.start.push_back(s);
+                R.end.push_back(e);
+            }
+            p = q;
+        }
+    };
+    if (nparts == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (size_t k = 0; k < nparts; k++) th.emplace_back(work, k);
+        for (auto& t : th) t.join();
+    }
+    for (auto& R : parts) {
+        out->chr.insert(out->chr.end(), R.chr.begin(), R.chr.end());
+        out->start.insert(out->start.end(), R.start.begin(), R.start.end());
+        out->end.insert(out->end.end(), R.end.begin(), R.end.end());
+    }
+}
+
+void parse_region_arg(const std::string& region, const std::unordered_map<std::string, uint32_t>& seq_num, uint32_t* chr,
+                      uint32_t* start, uint32_t* end) {
+    size_t colon = region.find(':');
+    if (colon == std::string::npos) throw Err(E_ARG, "Invalid region format, expected 'chr:start-end'");
+    std::string_view rest = std::string_view(region).substr(colon + 1);
+    size_t dash = rest.find('-');
+    if (dash == std::string_view::npos) throw Err(E_ARG, "Invalid range format, expected 'start-end'");
+    if (!parse_u32_rust(rest.substr(0, dash), start) || !parse_u32_rust(rest.substr(dash + 1), end))
+        throw Err(E_ARG, "invalid digit found in string");
+    auto it = seq_num.find(region.substr(0, colon));
+    if (it == seq_num.end()) throw Err(E_ARG, "Sequence ID not found: " + region.substr(0, colon));
+    if (*start >= *end)
+        throw Err(E_ARG, "Region start must be less than end (" + std::to_string(*start) + " >= " + std::to_string(*end) + ")");
+    *chr = it->second;
+}
+
+// ------------------------------------------------------------------------------------------
+// Emission
+// ------------------------------------------------------------------------------------------
+void write_ranges_to(const uint8_t* text, uint64_t text_len, const uint64_t* ranges, uint64_t n, const char* out_path) {
+    int fd = out_path ? ::open(out_path, O_WRONLY | O_CREAT | O_TRUNC, 0644) : 1;
+    if (fd < 0) throw Err(E_IO, std::string("cannot create output file ") + out_path);
+    const size_t BATCH = 1024;  // IOV_MAX
+    std::vector<iovec> iov;
+    iov.reserve(BATCH);
+    auto flush = [&]() {
+        size_t i = 0;
+        while (i < iov.size()) {
+            ssize_t w = ::writev(fd, iov.data() + i, (int)std::min<size_t>(iov.size() - i, BATCH));
+            if (w < 0) {
+                if (out_path) ::close(fd);
+                throw Err(E_IO, "write failed");
+            }
+            size_t left = (size_t)w;
+            while (i < iov.size() && left >= iov[i].iov_len) { left -= iov[i].iov_len; i++; }
+            if (left > 0) {
+                iov[i].iov_base = (char*)iov[i].iov_base + left;
+                iov[i].iov_len -= left;
+            }
+        }
+        iov.clear();
+    };
+    for (uint64_t k = 0; k < n; k++) {
+        uint64_t s = ranges[2 * k], e = ranges[2 * k + 1];
+        if (s >= e || e > text_len) continue;
+        // coalesce with the previous slice when contiguous: fewer iovecs, same bytes
+        if (!iov.empty() && (const uint8_t*)iov.back().iov_base + iov.back().iov_len == text + s) {
+            iov.back().iov_len += (size_t)(e - s);
+        } else {
+            if (iov.size() == BATCH) flush();
+            iov.push_back(iovec{(void*)(text + s), (size_t)(e - s)});
+        }
+    }
+    flush();
+    if (out_path) ::close(fd);
+}
+
+}  // namespace gffx

@@ -1,0 +1,110 @@
+// host_index.h — host-side model of a GFFx index: the on-disk files (.sqs .rix .rit .gof, read
+// unchanged) plus the line table derived from the GFF text.  This is the input of the device
+// upload in engine.cu.  Reference formats: SURVEY.md App. B; src/utils/tree_io.rs:37-63,
+// src/index_loader/{core.rs:19-34,gof.rs:95-128}, src/utils/tree_index.rs:36-82.
+#pragma once
+#include <memory>
+#include <unordered_map>
+#include "util.h"
+
+namespace gffx {
+
+struct RootIv {  // one Interval<u32> of src/utils/tree.rs:6-10, tagged with the tree (seq) it sits in
+    uint32_t seq, start, end, fid;
+};
+
+struct Block {  // one reachable .gof record (GofMap::index keeps the LAST record of a fid, gof.rs:32-37)
+    uint32_t fid;
+    uint64_t start, end;
+};
+
+// bits of LineTable::flags
+enum : uint8_t {
+    LN_I_OK = 1,   // columns 1..5 usable by gff_line_overlaps_queries (intersect.rs:441-489)
+    LN_D_OK = 2,   // line contributes to depth/coverage (depth.rs:131-157 / coverage.rs:296-323)
+};
+
+// Struct-of-arrays over every non-empty, non-'#' line that lies inside a reachable block, in
+// output order (blocks by ascending start offset, lines in file order).
+struct LineTable {
+    std::vector<uint64_t> off;     // absolute byte offset of the line
+    std::vector<uint32_t> len;     // byte length including the '\n' when present
+    std::vector<uint32_t> blk;     // index into HostIndex::blocks
+    std::vector<uint8_t> flags;
+    // intersect view: RAW columns 4,5 (no swap, no -1) and column 1 resolved by NAME against .sqs
+    std::vector<uint32_t> S, E, iseq, type_id;
+    // depth/coverage view: swapped, 0-based half-open; ID dictionary index; column-1 dictionary index
+    std::vector<uint32_t> fs, fe, id, chrom;
+    size_t size() const { return off.size(); }
+};
+
+struct StringPool {  // append-only dictionary: string -> dense index
+    std::vector<char> bytes;
+    std::vector<uint64_t> start;  // start[i]..start[i+1]
+    std::unordered_map<std::string_view, uint32_t> map;  // views into `keys` (stable storage)
+    std::vector<std::unique_ptr<std::string>> keys;
+    uint32_t intern(std::string_view s);
+    int64_t find(std::string_view s) const;
+    std::string_view get(uint32_t i) const { return std::string_view(keys[i]->data(), keys[i]->size()); }
+    size_t size() const { return keys.size(); }
+};
+
+struct HostIndex {
+    std::string gff_path;
+    std::vector<std::string> seq_names;                     // num_to_seqid
+    std::unordered_map<std::string, uint32_t> seq_num;      // seqid_to_num (later duplicate wins)
+    std::vector<RootIv> roots;                              // all tree intervals, grouped by seq, any order
+    std::vector<Block> blocks;                              // reachable blocks sorted by start (stable)
+    std::vector<uint32_t> root_blk;                         // per root: block index or NONE32 (fid absent from .gof)
+    std::vector<uint8_t> blk_utf8;                          // per block: whole slice is valid UTF-8 (depth.rs:131)
+    std::vector<uint64_t> blk_line0;                        // per block: first line index (blocks.size()+1 entries)
+    Mapped gff_map;                                         // owned mapping when opened from a path
+    const uint8_t* gff = nullptr;
+    uint64_t gff_len = 0;
+    LineTable lines;
+    StringPool types, ids, chroms;
+
+    // load .sqs/.rix/.rit/.gof beside `path` and (when the text is there) build the line table
+    void open(const std::string& path, int threads);
+    // from caller arrays (gffx_index_desc)
+    void create(uint32_t n_seqs, const char* const* names, uint64_t n_roots, const uint32_t* rseq, const uint32_t* rs,
+                const uint32_t* re, const uint32_t* rfid, uint64_t n_gof, const uint32_t* gfid, const uint64_t* gs,
+                const uint64_t* ge, const uint8_t* text, uint64_t text_len, int threads);
+    // true when block b may be scanned by the match-only path (intersect.rs:268-277)
+    bool block_scannable(size_t b) const {
+        const Block& k = blocks[b];
+        return k.start != MISSING64 && k.start < std::min<uint64_t>(k.end, gff_len);
+    }
+    // true when block b is accepted by depth/coverage routing (depth.rs:243-244, coverage.rs:407)
+    bool block_countable(size_t b) const {
+        const Block& k = blocks[b];
+        return k.start != MISSING64 && k.end != MISSING64 && k.end > k.start;
+    }
+
+   private:
+    void finish(const std::vector<uint32_t>& gfid, const std::vector<uint64_t>& gs, const std::vector<uint64_t>& ge, int threads);
+    void build_lines(int threads);
+};
+
+// .rit/.rix decoding: flatten every tree into RootIv records (seq = position in .rix)
+void load_trees_flat(const std::string& rit_path, const std::string& rix_path, std::vector<RootIv>* out, uint32_t* n_trees);
+void load_sqs_file(const std::string& path, std::vector<std::string>* names);
+void load_gof_file(const std::string& path, std::vector<uint32_t>* fid, std::vector<uint64_t>* s, std::vector<uint64_t>* e);
+
+// ---- BED parsing -------------------------------------------------------
+struct Regions {
+    std::vector<uint32_t> chr, start, end;
+    size_t size() const { return chr.size(); }
+};
+// intersect dialect: src/commands/intersect.rs:201-230 — throws Err(E_FORMAT) where the reference aborts
+void parse_bed_intersect(const std::string& path, const std::unordered_map<std::string, uint32_t>& seq_num, Regions* out);
+// depth/coverage dialect: src/commands/depth.rs:449-495 == src/commands/coverage.rs:222-255
+void parse_bed_counts(const std::string& path, const std::unordered_map<std::string, uint32_t>& seq_num, int threads, Regions* out);
+// src/commands/intersect.rs:172-198
+void parse_region_arg(const std::string& region, const std::unordered_map<std::string, uint32_t>& seq_num, uint32_t* chr,
+                      uint32_t* start, uint32_t* end);
+
+// Writes the byte ranges of `text` in order with writev batches (intersect.rs:385-429, common.rs:231-278)
+void write_ranges_to(const uint8_t* text, uint64_t text_len, const uint64_t* ranges, uint64_t n, const char* out_path);
+
+}  // namespace gffx

@@ -1,0 +1,193 @@
+// scan.cuh — device-wide scans used by the join (tile offsets), the rank-space post-passes
+// (prefix-max, suffix-min, next-set) and the order-preserving compactions.
+//
+// Scheme: reduce-then-scan in three launches (tile reduce -> scan of tile aggregates, recursive
+// above one tile of aggregates -> tile rescan with carry-in).  Warp shuffles inside a warp, one
+// shared-memory pass across the warps of a CTA.  No spin-waits between CTAs, so nothing here can
+// hang a device.  Every array these run over is small next to the query stream (<= a few
+// hundred MB); the streaming kernels do their own block scans in registers/shared memory.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace gffx {
+
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+struct OpSum {
+    template <class T> __host__ __device__ T operator()(T a, T b) const { return a + b; }
+};
+struct OpMax {
+    template <class T> __host__ __device__ T operator()(T a, T b) const { return a > b ? a : b; }
+};
+struct OpMin {
+    template <class T> __host__ __device__ T operator()(T a, T b) const { return a < b ? a : b; }
+};
+
+template <class T> __device__ __forceinline__ T shfl_up_any(T v, int d) {
+    if constexpr (sizeof(T) == 8) {
+        unsigned long long x = (unsigned long long)v;
+        x = __shfl_up_sync(0xffffffffu, x, d);
+        return (T)x;
+    } else {
+        return (T)__shfl_up_sync(0xffffffffu, v, d);
+    }
+}
+template <class T> __device__ __forceinline__ T shfl_idx_any(T v, int l) {
+    if constexpr (sizeof(T) == 8) {
+        unsigned long long x = (unsigned long long)v;
+        x = __shfl_sync(0xffffffffu, x, l);
+        return (T)x;
+    } else {
+        return (T)__shfl_sync(0xffffffffu, v, l);
+    }
+}
+
+// inclusive scan across the warp
+template <class T, class Op> __device__ __forceinline__ T warp_scan_incl(T v, Op op) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        T o = shfl_up_any(v, d);
+        if (lane >= d) v = op(o, v);
+    }
+    return v;
+}
+
+// CTA-wide exclusive scan of one value per thread; returns the exclusive prefix and writes the CTA total.
+// `smem` must hold blockDim.x/32 + 1 elements of T.  Contains two __syncthreads().
+template <class T, class Op> __device__ __forceinline__ T block_scan_excl(T v, Op op, T identity, T* smem, T* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    T incl = warp_scan_incl(v, op);
+    if (lane == 31) smem[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        T w = lane < nwarps ? smem[lane] : identity;
+        T wi = warp_scan_incl(w, op);
+        if (lane < nwarps) smem[lane] = wi;
+        if (lane == nwarps - 1) smem[nwarps] = wi;
+    }
+    __syncthreads();
+    T excl = shfl_up_any(incl, 1);
+    if (lane == 0) excl = identity;
+    if (warp > 0) excl = op(smem[warp - 1], excl);
+    *total = smem[nwarps];
+    return excl;
+}
+
+// ---- device-wide scan -----------------------------------------------------------------------
+// Load(i) -> T gives element i; REVERSE scans from the high end (suffix scan).  Element j of the
+// scan order is array index (REVERSE ? n-1-j : j).
+template <class T, class Op, class Load, bool REVERSE>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(Load load, uint64_t n, Op op, T identity, T* __restrict__ agg) {
+    __shared__ T sm[SCAN_THREADS / 32 + 1];
+    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
+    T acc = identity;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        uint64_t j = base + (uint64_t)k * SCAN_THREADS + threadIdx.x;
+        if (j < n) acc = op(acc, load(REVERSE ? n - 1 - j : j));
+    }
+    // order inside the tile does not matter for a reduction (ops are commutative)
+    T tot;
+    block_scan_excl(acc, op, identity, sm, &tot);
+    if (threadIdx.x == 0) agg[blockIdx.x] = tot;
+}
+
+// single CTA: in-place exclusive scan of `agg[0..m)`; writes the grand total to agg[m]
+template <class T, class Op>
+__global__ void __launch_bounds__(1024) scan_agg_kernel(T* __restrict__ agg, uint32_t m, Op op, T identity) {
+    __shared__ T sm[1024 / 32 + 1];
+    T carry = identity;
+    for (uint32_t base = 0; base < m; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        T v = i < m ? agg[i] : identity;
+        T tot;
+        T ex = block_scan_excl(v, op, identity, sm, &tot);
+        if (i < m) agg[i] = op(carry, ex);
+        carry = op(carry, tot);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) agg[m] = carry;
+}
+
+template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE>
+__global__ void __launch_bounds__(SCAN_THREADS)
+    scan_apply_kernel(Load load, Store store, uint64_t n, Op op, T identity, const T* __restrict__ agg) {
+    __shared__ T sm[SCAN_THREADS / 32 + 1];
+    // thread t owns SCAN_ITEMS consecutive elements of the scan order -> blocked arrangement
+    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
+    T v[SCAN_ITEMS];
+    T acc = identity;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        uint64_t j = base + k;
+        v[k] = j < n ? load(REVERSE ? n - 1 - j : j) : identity;
+        acc = op(acc, v[k]);
+    }
+    T tot;
+    T ex = block_scan_excl(acc, op, identity, sm, &tot);
+    T run = op(agg[blockIdx.x], ex);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        uint64_t j = base + k;
+        T inc = op(run, v[k]);
+        if (j < n) store(REVERSE ? n - 1 - j : j, INCLUSIVE ? inc : run);
+        run = inc;
+    }
+}
+
+struct ScanScratch {  // caller-provided aggregate storage: needs scan_scratch_elems(n) elements of T
+    void* ptr;
+};
+inline uint64_t scan_scratch_elems(uint64_t n) {
+    uint64_t tot = 0;
+    while (true) {
+        uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+        if (tiles == 0) tiles = 1;
+        tot += tiles + 1;
+        if (tiles <= 1024 * 64) break;  // one CTA finishes the rest
+        n = tiles;
+    }
+    return tot + 8;
+}
+
+template <class T> struct PtrLoad {
+    const T* p;
+    __device__ T operator()(uint64_t i) const { return p[i]; }
+};
+template <class T> struct PtrStore {
+    T* p;
+    __device__ void operator()(uint64_t i, T v) const { p[i] = v; }
+};
+
+// Scans n elements; `scratch` holds scan_scratch_elems(n) Ts.  If total_out != nullptr the grand
+// total (device pointer) is written there.  Returns the number of kernels launched.
+template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE>
+int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratch, T* total_out, cudaStream_t st) {
+    int launches = 0;
+    uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (tiles == 0) tiles = 1;
+    T* agg = scratch;
+    scan_reduce_kernel<T, Op, Load, REVERSE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, n, op, identity, agg);
+    launches++;
+    if (tiles <= 1024 * 64) {
+        scan_agg_kernel<T, Op><<<1, 1024, 0, st>>>(agg, (uint32_t)tiles, op, identity);
+        launches++;
+    } else {
+        // scan the aggregates with the same machinery (exclusive, forward), in place
+        T* next = agg + tiles + 1;
+        launches += device_scan<T, Op, PtrLoad<T>, PtrStore<T>, false, false>(PtrLoad<T>{agg}, PtrStore<T>{agg}, tiles, op, identity,
+                                                                             next, agg + tiles, st);
+    }
+    scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg);
+    launches++;
+    if (total_out) {
+        cudaMemcpyAsync(total_out, agg + tiles, sizeof(T), cudaMemcpyDeviceToDevice, st);
+    }
+    return launches;
+}
+
+}  // namespace gffx

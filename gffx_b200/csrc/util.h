@@ -1,0 +1,55 @@
+// util.h — small host-side helpers shared by the engine's C++ sources.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <string_view>
+#include <vector>
+
+namespace gffx {
+
+enum Status : int { OK = 0, E_ARG = -1, E_IO = -2, E_FORMAT = -3, E_CUDA = -4, E_STATE = -5 };
+
+struct Err : std::runtime_error {
+    int code;
+    Err(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+static constexpr uint64_t MISSING64 = UINT64_MAX;  // sentinel of src/index_loader/gof.rs:7
+static constexpr uint32_t NONE32 = UINT32_MAX;
+
+// read-only mmap of a whole file (the reference mmaps every input, src/index_loader/core.rs:14-17)
+class Mapped {
+   public:
+    Mapped() = default;
+    ~Mapped();
+    Mapped(const Mapped&) = delete;
+    Mapped& operator=(const Mapped&) = delete;
+    void open(const std::string& path);          // throws Err(E_IO)
+    bool try_open(const std::string& path);      // false when the file cannot be opened
+    const uint8_t* data() const { return p_; }
+    size_t size() const { return n_; }
+
+   private:
+    const uint8_t* p_ = nullptr;
+    size_t n_ = 0;
+    int fd_ = -1;
+};
+
+// ---- text predicates that mirror the Rust std calls the reference uses -------------------
+bool utf8_ok(const uint8_t* s, size_t n);                    // std::str::from_utf8(..).is_ok()
+inline bool ascii_ws(uint8_t c) {                            // u8::is_ascii_whitespace
+    return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\x0c';
+}
+std::string_view rtrim_unicode(std::string_view s);          // str::trim_end
+std::string_view trim_unicode(std::string_view s);           // str::trim
+bool parse_u32_strict(const uint8_t* s, size_t n, uint32_t* out);   // digits only, checked (intersect.rs:526-538)
+bool parse_u32_rust(std::string_view s, uint32_t* out);              // str::parse::<u32> ('+' allowed)
+
+inline const uint8_t* find_byte(const uint8_t* p, const uint8_t* end, uint8_t c) {
+    return p < end ? (const uint8_t*)memchr(p, c, (size_t)(end - p)) : nullptr;
+}
+
+}  // namespace gffx

@@ -1,0 +1,219 @@
+/* gffx_b200.h — C ABI of the B200-native interval-overlap engine for GFFx's hot path.
+ *
+ * The reference (pure Rust, /root/reference) has no FFI; the path is reached through its CLI and
+ * the public functions re-exported in src/lib.rs:7-22.  Each entry point below names the reference
+ * item it replaces (file:line relative to the reference root).  INTEGRATION.md shows the Rust
+ * `extern "C"` block + safe wrappers a maintainer adds to call them from `run()`.
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative gffx_status on failure;
+ *     gffx_last_error() then returns a thread-local, NUL-terminated message (the reference's
+ *     anyhow::Error text bubbling to main, src/main.rs:28-43).  Nothing throws across the ABI.
+ *   - inputs are borrowed (the library copies what it keeps); outputs are library-owned and
+ *     released by the matching *_free / *_destroy call.
+ *   - a handle may be used from one thread at a time; distinct handles (e.g. one per GPU) are
+ *     independent.  CUDA streams are internal.
+ *   - there is NO CPU fallback: every compute entry point fails with GFFX_E_CUDA when no
+ *     sm_100-class device is usable.
+ */
+#ifndef GFFX_B200_H
+#define GFFX_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    GFFX_OK = 0,
+    GFFX_E_ARG = -1,    /* bad argument (NULL, bad mode, chromosome number out of range …) */
+    GFFX_E_IO = -2,     /* file open / mmap / write failure                                 */
+    GFFX_E_FORMAT = -3, /* corrupt index file, BED number parse error (intersect dialect)   */
+    GFFX_E_CUDA = -4,   /* no usable GPU, CUDA runtime error, out of device memory          */
+    GFFX_E_STATE = -5   /* call sequence error                                              */
+} gffx_status;
+
+/* OverlapMode, src/commands/intersect.rs:74-78 (CLI -c / -C / -O). */
+typedef enum { GFFX_MODE_CONTAINED = 0, GFFX_MODE_CONTAINS_REGION = 1, GFFX_MODE_OVERLAP = 2 } gffx_mode;
+
+/* flags for the compute calls */
+enum {
+    GFFX_F_DEVICE_INPUT = 1u << 0, /* chr/start/end are device pointers on the handle's GPU (HBM-resident queries) */
+    GFFX_F_WANT_PAIRS = 1u << 1,   /* materialise the (root_fid,start,end) pairs and copy them to the host         */
+    GFFX_F_NO_HOST_COPY = 1u << 2, /* leave pairs / ranges on the device (bench: kernel-only timing)               */
+    GFFX_F_PAIRS_ON_DEVICE = 1u << 3 /* materialise pairs in HBM but do not copy them to the host                  */
+};
+
+typedef struct gffx_index gffx_index;     /* device-resident index: TreeIndexData + GofMap + GFF line table */
+typedef struct gffx_result gffx_result;   /* result of one intersect / query_features call                 */
+typedef struct gffx_counts gffx_counts;   /* accumulation state of a depth or coverage job                 */
+
+const char* gffx_last_error(void);
+const char* gffx_version(void);
+int gffx_device_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Index: replaces TreeIndexData::load_tree_index (src/utils/tree_index.rs:21-82), load_sqs
+ * (src/index_loader/core.rs:19-34), load_gof (src/index_loader/gof.rs:95-128) and the GFF mmap
+ * (src/commands/intersect.rs:242-249, src/commands/depth.rs:563-566); builds the flattened
+ * struct-of-arrays and uploads them to `device`.
+ * ------------------------------------------------------------------------------------------ */
+/* device -1 opens the index host-only (loaders, BED parsers, accessors; compute calls fail) */
+int gffx_index_open(const char* gff_path, int device, gffx_index** out);
+
+/* Same, from what a Rust caller already holds in memory (TreeIndexData, GofMap, &Mmap). */
+typedef struct {
+    uint32_t n_seqs;
+    const char* const* seq_names;   /* .sqs order = seq number (TreeIndexData.num_to_seqid)        */
+    uint64_t n_roots;               /* all tree intervals, any order                               */
+    const uint32_t* root_seq;       /* seq number of each interval (tree it came from)             */
+    const uint32_t* root_start;     /* Interval.start (0-based)            src/utils/tree.rs:6-10  */
+    const uint32_t* root_end;       /* Interval.end   (exclusive)                                  */
+    const uint32_t* root_fid;       /* Interval.root_fid                                           */
+    uint64_t n_gof;                 /* .gof records in file order (last duplicate fid wins)        */
+    const uint32_t* gof_fid;
+    const uint64_t* gof_start;
+    const uint64_t* gof_end;
+    const uint8_t* gff_text;        /* the mmap'd GFF (may be NULL with gff_len 0: join-only use)  */
+    uint64_t gff_len;
+    int device;
+} gffx_index_desc;
+int gffx_index_create(const gffx_index_desc* desc, gffx_index** out);
+void gffx_index_destroy(gffx_index* idx);
+
+uint32_t gffx_index_n_seqs(const gffx_index* idx);
+const char* gffx_index_seq_name(const gffx_index* idx, uint32_t seq);
+/* seqid_to_num lookup (TreeIndexData.seqid_to_num); returns -1 when unknown */
+int64_t gffx_index_seq_num(const gffx_index* idx, const char* name);
+uint64_t gffx_index_n_roots(const gffx_index* idx);
+uint64_t gffx_index_n_blocks(const gffx_index* idx);
+uint64_t gffx_index_n_lines(const gffx_index* idx);
+uint64_t gffx_index_n_ids(const gffx_index* idx);
+uint64_t gffx_index_device_bytes(const gffx_index* idx);
+/* flattened tree intervals of one sequence as (start,end,root_fid) triples, sorted by start */
+int gffx_index_seq_roots(const gffx_index* idx, uint32_t seq, const uint32_t** triples, uint64_t* n);
+
+/* ------------------------------------------------------------------------------------------
+ * BED parsing on the host: the three dialects of the reference.
+ *   intersect: parse_bed_file, src/commands/intersect.rs:201-230 (number errors abort: GFFX_E_FORMAT)
+ *   counts   : src/commands/depth.rs:449-495 == src/commands/coverage.rs:222-255 (bad lines dropped)
+ * Output arrays are library-owned; free with gffx_free().
+ * ------------------------------------------------------------------------------------------ */
+int gffx_parse_bed_intersect(const gffx_index* idx, const char* bed_path, uint32_t** chr, uint32_t** start, uint32_t** end,
+                             uint64_t* n);
+int gffx_parse_bed_counts(const gffx_index* idx, const char* bed_path, uint32_t** chr, uint32_t** start, uint32_t** end,
+                          uint64_t* n);
+/* parse_region, src/commands/intersect.rs:172-198 */
+int gffx_parse_region(const gffx_index* idx, const char* region, uint32_t* chr, uint32_t* start, uint32_t* end);
+void gffx_free(void* p);
+
+/* ------------------------------------------------------------------------------------------
+ * Root-level join: replaces query_features (src/commands/intersect.rs:105-169) and the
+ * IntervalTree::query_interval calls under it (src/utils/tree.rs:98-121).
+ * Pairs come back in query order (the reference's order is hash-map order: unspecified).
+ * ------------------------------------------------------------------------------------------ */
+int gffx_query_features(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n,
+                        int mode, int invert, uint32_t flags, gffx_result** out);
+
+/* ------------------------------------------------------------------------------------------
+ * Full intersect: replaces the body of run() after BED parsing (src/commands/intersect.rs:586-654):
+ * query_features, root dedup + GofMap::roots_to_offsets (src/index_loader/gof.rs:54-84), then
+ * write_gff_match_only_by_coords (src/commands/intersect.rs:232-438) when !entire_group || types,
+ * else write_gff_output's sort+merge (src/utils/common.rs:199-229).  The result holds the byte
+ * ranges [start,end) of the GFF to write, in output order.
+ * `types_csv` = the -T value or NULL.
+ * ------------------------------------------------------------------------------------------ */
+int gffx_intersect(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode,
+                   int invert, int entire_group, const char* types_csv, uint32_t flags, gffx_result** out);
+
+uint64_t gffx_result_n_queries(const gffx_result* r);
+uint64_t gffx_result_n_pairs(const gffx_result* r);
+/* n_pairs (root_fid, start, end) u32 triples on the host; NULL unless GFFX_F_WANT_PAIRS */
+const uint32_t* gffx_result_pairs(const gffx_result* r);
+const uint32_t* gffx_result_pairs_device(const gffx_result* r);
+uint64_t gffx_result_n_roots(const gffx_result* r);   /* distinct selected root fids */
+uint64_t gffx_result_n_ranges(const gffx_result* r);
+/* n_ranges (byte_start, byte_end) u64 pairs on the host, output order */
+const uint64_t* gffx_result_ranges(const gffx_result* r);
+uint64_t gffx_result_bytes_out(const gffx_result* r);
+/* fids skipped for a sentinel offset (the reference prints "[WARN] skipped fid=…", intersect.rs:269-272) */
+uint64_t gffx_result_n_warn(const gffx_result* r);
+const uint32_t* gffx_result_warn_fids(const gffx_result* r);
+/* device time of the call's kernels in ms (CUDA events on the engine's stream) and launch count */
+double gffx_result_kernel_ms(const gffx_result* r);
+uint32_t gffx_result_launches(const gffx_result* r);
+/* per-stage device ms: 0 join, 1 root/block select, 2 query scatter, 3 rank scans, 4 line filter + compaction */
+double gffx_result_stage_ms(const gffx_result* r, int stage);
+void gffx_result_free(gffx_result* r);
+
+/* Write the selected byte ranges of the GFF (write_vectored loops of intersect.rs:385-429 and
+ * common.rs:231-278). out_path NULL = stdout. */
+int gffx_write_ranges(const gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, const char* out_path);
+
+/* ------------------------------------------------------------------------------------------
+ * depth / coverage: replace compute_hit_depth + compute_root_depth (src/commands/depth.rs:121-293)
+ * and collect_by_root_* + finalize_compute_breadth (src/commands/coverage.rs:208-450).
+ * kind: 0 = depth, 1 = coverage (breadth).  *_add may be called once per batch of regions
+ * (the reference batches 100k BED lines, depth.rs:24,462); regions with start >= end are ignored
+ * as both BED dialects drop them before the engine is reached.
+ * ------------------------------------------------------------------------------------------ */
+int gffx_counts_begin(gffx_index* idx, int kind, gffx_counts** out);
+int gffx_counts_add(gffx_counts* st, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n,
+                    uint32_t flags);
+/* rows: parallel arrays, library-owned until gffx_counts_free; order = ID dictionary order */
+int gffx_counts_finish(gffx_counts* st, uint64_t* n_rows, const uint32_t** id_idx, const uint32_t** chrom_idx,
+                       const uint32_t** start, const uint32_t** end, const uint64_t** value);
+double gffx_counts_kernel_ms(const gffx_counts* st);
+uint32_t gffx_counts_launches(const gffx_counts* st);
+void gffx_counts_free(gffx_counts* st);
+const char* gffx_index_id_string(const gffx_index* idx, uint32_t id_idx, uint32_t* len);
+const char* gffx_index_chrom_string(const gffx_index* idx, uint32_t chrom_idx, uint32_t* len);
+/* write_depth_results (depth.rs:515-545) / write_breadth_results (coverage.rs:453-490) */
+int gffx_counts_write(gffx_counts* st, const char* out_path);
+
+/* ------------------------------------------------------------------------------------------
+ * Command level: the reference's run() functions (src/commands/intersect.rs:541-655,
+ * src/commands/depth.rs:548-635, src/commands/coverage.rs:493-582) with the GPU engine inside.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+    const char* input;       /* -i */
+    const char* output;      /* -o, NULL = stdout */
+    const char* bed;         /* -b  | exactly one  */
+    const char* region;      /* -r  | of the two   */
+    int mode;                /* gffx_mode */
+    int invert;              /* -I */
+    int entire_group;        /* -e */
+    const char* types;       /* -T or NULL */
+    int verbose;             /* -v */
+    int device;
+} gffx_intersect_args;
+int gffx_intersect_run(const gffx_intersect_args* args);
+
+typedef struct {
+    const char* input;   /* -i */
+    const char* source;  /* -s (.bed; .bam/.sam/.cram need htslib: GFFX_E_ARG here) */
+    const char* output;  /* -o, NULL = stdout */
+    uint32_t bin_shift;  /* accepted, cannot change results (depth.rs:163-191) */
+    int threads;         /* -t: host parse threads */
+    int verbose;
+    int device;
+} gffx_counts_args;
+int gffx_depth_run(const gffx_counts_args* args);
+int gffx_coverage_run(const gffx_counts_args* args);
+
+/* ------------------------------------------------------------------------------------------
+ * Synthetic workload generators, counter-based splitmix64 so any shard can be
+ * generated independently, on the host or straight into HBM.
+ * ------------------------------------------------------------------------------------------ */
+/* human-like GFF3 text written to `path`; returns number of lines through *n_lines */
+int gffx_synth_gff(const char* path, uint64_t seed, uint32_t n_genes, int quirks, uint64_t* n_lines);
+/* regions for sequences of the index (placement proportional to sequence extent); host arrays */
+int gffx_synth_regions_host(const gffx_index* idx, uint64_t seed, uint64_t first, uint64_t n, uint32_t length,
+                            uint32_t* chr, uint32_t* start, uint32_t* end);
+/* same, generated by a kernel into device arrays d_chr/d_start/d_end on the handle's GPU */
+int gffx_synth_regions_device(gffx_index* idx, uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* d_chr,
+                              uint32_t* d_start, uint32_t* d_end);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
