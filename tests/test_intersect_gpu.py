@@ -1,0 +1,151 @@
+"""Parity of the CUDA intersect path (through the C ABI) with the CPU oracle: root-level join pairs,
+selected byte ranges for every mode x invert x -e x -T combination, quirk inputs, edge cases."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from tests._oracle import Oracle, sorted_pairs
+from tests.conftest import GOLDEN
+from tests.test_oracle_kat import pair_checksum
+
+pytestmark = pytest.mark.gpu
+
+MODES = [(0, False), (0, True), (1, False), (1, True), (2, False), (2, True)]
+
+
+def mixed_regions(idx, seed, n):
+    """20 kb windows + short reads + a few degenerate regions (start >= end, beyond every root, huge)."""
+    a = idx.synth_regions(seed, n, 20000)
+    b = idx.synth_regions(seed + 1, n, 150)
+    c = idx.synth_regions(seed + 2, max(n // 10, 4), 3_000_000)
+    chr_ = np.concatenate([a[0], b[0], c[0]])
+    s = np.concatenate([a[1], b[1], c[1]])
+    e = np.concatenate([a[2], b[2], c[2]])
+    k = len(chr_) // 50
+    rng = np.random.default_rng(seed)
+    pick = rng.choice(len(chr_), size=k, replace=False)
+    s[pick[: k // 2]], e[pick[: k // 2]] = e[pick[: k // 2]].copy(), s[pick[: k // 2]].copy()  # inverted (BED keeps them)
+    e[pick[k // 2:]] = s[pick[k // 2:]]                                                     # empty
+    s[pick[:2]] = 0xFFFFFF00
+    e[pick[:2]] = 0xFFFFFFFF
+    perm = rng.permutation(len(chr_))
+    return chr_[perm].copy(), s[perm].copy(), e[perm].copy()
+
+
+@pytest.fixture(scope="module")
+def quirk(gffx, synth_quirk_gff):
+    idx = gffx.TreeIndexData.load_tree_index(synth_quirk_gff, device=0)
+    o = Oracle(synth_quirk_gff)
+    yield idx, o, synth_quirk_gff
+    o.close()
+    idx.close()
+
+
+@pytest.mark.parametrize("mode,invert", MODES)
+def test_query_features_pairs(quirk, mode, invert):
+    idx, o, _ = quirk
+    regs = mixed_regions(idx, 100 + mode, 5000)
+    r = idx.query_features(regs, mode, invert)
+    want = o.query_features(regs, mode, invert)
+    assert r.n_pairs == want.shape[0]
+    got = r.pairs if r.pairs is not None else np.zeros((0, 3), dtype=np.uint32)
+    assert np.array_equal(sorted_pairs(got), sorted_pairs(want))
+    assert r.n_roots == len(np.unique(want[:, 0]))
+    assert r.launches > 0 or (mode == 2 and invert)
+
+
+@pytest.mark.parametrize("mode,invert", MODES)
+@pytest.mark.parametrize("entire,types", [(False, None), (True, None), (False, "gene,mRNA,exon"), (True, "exon, CDS ,,nosuchtype")])
+def test_intersect_ranges(quirk, mode, invert, entire, types):
+    idx, o, path = quirk
+    regs = mixed_regions(idx, 7 + mode, 3000)
+    r = idx.intersect(regs, mode, invert, entire, types)
+    want, n_pairs, n_warn = o.intersect(regs, mode, invert, entire, types)
+    assert r.n_pairs == n_pairs
+    assert r.n_ranges == want.shape[0]
+    assert np.array_equal(r.ranges, want)
+    assert r.bytes_out == int((want[:, 1] - want[:, 0]).sum())
+    assert len(r.warn_fids) == n_warn
+
+
+def test_few_regions_and_single_chromosome(quirk):
+    idx, o, _ = quirk
+    for regs in [(np.array([3], dtype=np.uint32), np.array([0], dtype=np.uint32), np.array([0xFFFFFFFF], dtype=np.uint32)),
+                 (np.array([0, 0], dtype=np.uint32), np.array([5, 5], dtype=np.uint32), np.array([5, 4], dtype=np.uint32))]:
+        for mode, invert in MODES:
+            r = idx.intersect(regs, mode, invert, False, None, want_pairs=True)
+            want, n_pairs, _ = o.intersect(regs, mode, invert, False, None)
+            assert r.n_pairs == n_pairs and np.array_equal(r.ranges, want)
+
+
+def test_empty_input(quirk):
+    idx, _, _ = quirk
+    z = np.zeros(0, dtype=np.uint32)
+    r = idx.intersect((z, z, z), 2, False, False, None, want_pairs=True)
+    assert r.n_pairs == 0 and r.n_ranges == 0 and r.n_roots == 0 and r.bytes_out == 0
+
+
+def test_bad_chromosome_number_is_an_error(gffx, quirk):
+    idx, _, _ = quirk
+    with pytest.raises(gffx.GffxError) as ei:
+        idx.query_features((np.array([999], dtype=np.uint32), np.array([1], dtype=np.uint32), np.array([2], dtype=np.uint32)))
+    assert ei.value.code == -1
+
+
+def test_device_resident_regions_give_the_same_answer(quirk):
+    import torch
+
+    idx, o, _ = quirk
+    regs = idx.synth_regions(5, 40001, 20000)  # odd length: exercises the unaligned tail
+    dev = tuple(torch.from_numpy(a.view(np.int32)).cuda() for a in regs)
+    a = idx.intersect(regs, 2, False, False, "exon", want_pairs=True)
+    b = idx.intersect(dev, 2, False, False, "exon", want_pairs=True)
+    assert a.n_pairs == b.n_pairs and np.array_equal(a.ranges, b.ranges)
+    assert np.array_equal(sorted_pairs(a.pairs), sorted_pairs(b.pairs))
+    # unaligned device views (offset by one element)
+    dev1 = tuple(t[1:] for t in dev)
+    c = idx.intersect(dev1, 2, False, False, "exon")
+    want, _, _ = o.intersect(tuple(x[1:] for x in regs), 2, False, False, "exon")
+    assert np.array_equal(c.ranges, want)
+    # the device generator is the same function of (seed, index) as the host generator
+    g = idx.synth_regions_device(5, 40001, 20000)
+    for x, y in zip(g, regs):
+        assert np.array_equal(x.cpu().numpy().view(np.uint32), y)
+
+
+def test_reference_index_files_root_join(gffx, ps_index):
+    """Root-level join on the reference's own ps index files against the brute-force golden numbers."""
+    gold = json.load(open(os.path.join(GOLDEN, "ps", "golden.json")))
+    gff, bed = ps_index
+    idx = gffx.TreeIndexData.load_tree_index(gff, device=0)
+    regs = idx.parse_bed_file(bed)
+    for case, want in gold["cases"].items():
+        mode = {"contained": 0, "contains_region": 1, "overlap": 2}[case.split("+")[0]]
+        r = idx.query_features(regs, mode, case.endswith("+invert"))
+        assert r.n_pairs == want["pairs"], case
+        assert r.n_roots == want["roots"], case
+        p = r.pairs if r.pairs is not None else np.zeros((0, 3), dtype=np.uint32)
+        assert pair_checksum(p) == want["checksum"], case
+    idx.close()
+
+
+def test_cli_run_writes_the_same_file_as_the_oracle(gffx, quirk, tmp_path):
+    """gffx_intersect_run (the reference's run(), src/commands/intersect.rs:541-655) end to end: BED file in, GFF out."""
+    idx, o, path = quirk
+    regs = idx.synth_regions(77, 2000, 20000)
+    names = idx.num_to_seqid
+    bed = tmp_path / "r.bed"
+    with open(bed, "w") as f:
+        f.write("track name=x\n")
+        for c, s, e in zip(*regs):
+            f.write(f"{names[c]}\t{s}\t{e}\tr\t0\t+\n")
+        f.write("chrNope\tzz\tyy\n")
+    text = open(path, "rb").read()
+    for kw in ({}, {"contained": True}, {"contains_region": True, "invert": True}, {"entire_group": True}, {"types": "CDS"}):
+        out = tmp_path / "out.gff"
+        gffx.run_intersect(gffx.IntersectArgs(input=path, bed=str(bed), output=str(out), **kw))
+        mode = 0 if kw.get("contained") else 1 if kw.get("contains_region") else 2
+        want, _, _ = o.intersect(o.parse_bed_intersect(str(bed)), mode, kw.get("invert", False), kw.get("entire_group", False), kw.get("types"))
+        assert out.read_bytes() == b"".join(text[s:e] for s, e in want.tolist())
