@@ -120,7 +120,7 @@ uint64_t gffx_index_n_roots(const gffx_index* idx) { return idx ? idx->host().ro
 uint64_t gffx_index_n_blocks(const gffx_index* idx) { return idx ? idx->host().blocks.size() : 0; }
 uint64_t gffx_index_n_lines(const gffx_index* idx) { return idx ? idx->host().lines.size() : 0; }
 uint64_t gffx_index_n_ids(const gffx_index* idx) { return idx ? idx->host().ids.size() : 0; }
-uint64_t gffx_index_device_bytes(const gffx_index* idx) { return idx ? idx->engine()->device_bytes() : 0; }
+uint64_t gffx_index_device_bytes(const gffx_index* idx) { return idx && idx->eng_ ? idx->eng_->device_bytes() : 0; }
 
 int gffx_index_seq_roots(const gffx_index* idx, uint32_t seq, const uint32_t** triples, uint64_t* n) {
     return guard([&] {

@@ -1,20 +1,256 @@
-// counts.cu — depth / coverage pipelines (K6/K7).
+// counts.cu — depth / coverage pipelines (K6 / K7): index upload, per-batch scatter, finish.
+#include <algorithm>
+#include "counts.cuh"
+#include "counts_index.h"
 #include "engine_impl.cuh"
 
 namespace gffx {
 
 struct CountsState {
-    int kind = 0;
+    // ---- index (built lazily by the first counts_begin, kept for the engine's lifetime) ----
+    bool built = false;
+    CountsIndexHost host;  // scalars are read after the upload; the big vectors are released
+    DBuf d_rank, d_cov, d_X, d_dir;
+    DBuf d_u_space, d_u_chrom, d_u_blk, d_u_line0, d_u_seg0, d_l_fs, d_l_fe, d_l_sfs, d_l_sfe, d_g_s, d_g_e, d_g_ss, d_g_se;
+    DBuf d_id_unit0, d_id_units, d_irr_grp, d_irr_pos, d_grp_off, d_grp_seq, d_grp_s, d_grp_e, d_blk_space;
+    DJoin gaps, irr;
+    // ---- accumulators of the running job ----
+    DBuf d_Hs, d_He, d_G, d_S, d_E, d_bits, d_diff, d_P, d_routed, d_scratch, d_err;
+    DBuf r_chrom, r_start, r_end, r_value, r_flag, r_pos, o_id, o_chrom, o_start, o_end, o_value;
+    int kind = -1;
+    bool active = false;
+    uint64_t n_regions = 0;
     double ms = 0;
     uint32_t launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    std::vector<DBuf*> all() {
+        return {&d_rank, &d_cov, &d_X, &d_dir, &d_u_space, &d_u_chrom, &d_u_blk, &d_u_line0, &d_u_seg0, &d_l_fs, &d_l_fe, &d_l_sfs,
+                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
+                &d_grp_s, &d_grp_e, &d_blk_space, &d_Hs, &d_He, &d_G, &d_S, &d_E, &d_bits, &d_diff, &d_P, &d_routed, &d_scratch, &d_err,
+                &r_chrom, &r_start, &r_end, &r_value, &r_flag, &r_pos, &o_id, &o_chrom, &o_start, &o_end, &o_value};
+    }
 };
 
-void counts_release(EngineImpl* E) { delete E->counts; E->counts = nullptr; }
-void counts_begin_impl(EngineImpl* E, int kind) { throw Err(E_STATE, "depth/coverage engine not built yet"); }
-void counts_add_impl(EngineImpl* E, const uint32_t*, const uint32_t*, const uint32_t*, uint64_t, uint32_t) {
-    throw Err(E_STATE, "depth/coverage engine not built yet");
+void counts_release(EngineImpl* E) {
+    CountsState* C = E->counts;
+    if (!C) return;
+    for (DBuf* b : C->all()) b->release();
+    C->gaps.release();
+    C->irr.release();
+    if (C->ev0) cudaEventDestroy(C->ev0);
+    if (C->ev1) cudaEventDestroy(C->ev1);
+    delete C;
+    E->counts = nullptr;
 }
-void counts_finish_impl(EngineImpl* E, CountRows*) { throw Err(E_STATE, "depth/coverage engine not built yet"); }
+
+static void build_counts(EngineImpl* E, CountsState* C) {
+    for (DBuf* b : C->all()) b->total = &E->dev_bytes;
+    CountsIndexHost& h = C->host;
+    build_counts_index(*E->H, &h);
+    cudaStream_t st = E->st;
+    upload(C->d_rank, h.rank, st);
+    upload(C->d_cov, h.cov, st);
+    upload(C->d_X, h.X, st);
+    upload(C->d_dir, h.dir, st);
+    upload(C->d_u_space, h.u_space, st);
+    upload(C->d_u_chrom, h.u_chrom, st);
+    upload(C->d_u_blk, h.u_blk, st);
+    upload(C->d_u_line0, h.u_line0, st);
+    upload(C->d_u_seg0, h.u_seg0, st);
+    upload(C->d_l_fs, h.l_fs, st);
+    upload(C->d_l_fe, h.l_fe, st);
+    upload(C->d_l_sfs, h.l_sfs, st);
+    upload(C->d_l_sfe, h.l_sfe, st);
+    upload(C->d_g_s, h.g_s, st);
+    upload(C->d_g_e, h.g_e, st);
+    upload(C->d_g_ss, h.g_ss, st);
+    upload(C->d_g_se, h.g_se, st);
+    upload(C->d_id_unit0, h.id_unit0, st);
+    upload(C->d_id_units, h.id_units, st);
+    upload(C->d_irr_grp, h.irr_grp, st);
+    upload(C->d_irr_pos, h.irr_pos, st);
+    upload(C->d_grp_off, h.grp_off, st);
+    upload(C->d_grp_seq, h.grp_seq, st);
+    upload(C->d_grp_s, h.grp_s, st);
+    upload(C->d_grp_e, h.grp_e, st);
+    upload(C->d_blk_space, h.blk_space, st);
+    C->gaps.upload_from(h.gaps, st, &E->dev_bytes);
+    C->irr.upload_from(h.irr, st, &E->dev_bytes);
+    C->d_err.ensure(256);
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    GFFX_CUDA(cudaEventCreate(&C->ev0));
+    GFFX_CUDA(cudaEventCreate(&C->ev1));
+    // keep the scalars, drop the bulk
+    for (auto* v : {&h.X, &h.dir, &h.u_space, &h.u_chrom, &h.u_blk, &h.u_line0, &h.u_seg0, &h.l_fs, &h.l_fe, &h.l_sfs, &h.l_sfe, &h.g_s,
+                    &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space})
+        std::vector<uint32_t>().swap(*v);
+    h.gaps = JoinHost();
+    h.irr = JoinHost();
+    C->built = true;
+}
+
+void counts_begin_impl(EngineImpl* E, int kind) {
+    GFFX_CUDA(cudaSetDevice(E->dev));
+    if (!E->H->gff) throw Err(E_STATE, "depth/coverage need the GFF text (the index was opened without it)");
+    if (!E->counts) E->counts = new CountsState();
+    CountsState* C = E->counts;
+    if (!C->built) build_counts(E, C);
+    const CountsIndexHost& h = C->host;
+    cudaStream_t st = E->st;
+    C->kind = kind;
+    C->ms = 0;
+    C->launches = 0;
+    C->n_regions = 0;
+    GFFX_CUDA(cudaMemsetAsync(C->d_err.p, 0, 256, st));
+    if (kind == 0) {
+        const size_t ns = std::max<size_t>(h.n_slots, 1), ng = std::max<size_t>(h.n_segs, 1);
+        C->d_Hs.ensure(ns * 4); C->d_He.ensure(ns * 4); C->d_S.ensure(ns * 4); C->d_E.ensure(ns * 4);
+        C->d_G.ensure(ng * 4);
+        GFFX_CUDA(cudaMemsetAsync(C->d_Hs.p, 0, ns * 4, st));
+        GFFX_CUDA(cudaMemsetAsync(C->d_He.p, 0, ns * 4, st));
+        GFFX_CUDA(cudaMemsetAsync(C->d_G.p, 0, ng * 4, st));
+    } else {
+        const size_t nw = std::max<uint64_t>(h.n_words, 1);
+        C->d_bits.ensure(nw * 8); C->d_diff.ensure(nw * 4); C->d_P.ensure(nw * 4);
+        C->d_routed.ensure(std::max<uint32_t>(E->n_blocks, 1));
+        GFFX_CUDA(cudaMemsetAsync(C->d_bits.p, 0, nw * 8, st));
+        GFFX_CUDA(cudaMemsetAsync(C->d_diff.p, 0, nw * 4, st));
+        GFFX_CUDA(cudaMemsetAsync(C->d_routed.p, 0, std::max<uint32_t>(E->n_blocks, 1), st));
+    }
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    C->active = true;
+}
+
+static CountsDev make_dev(EngineImpl* E, CountsState* C) {
+    CountsDev D{};
+    D.R.X = C->d_X.as<uint32_t>();
+    D.R.dir = C->d_dir.as<uint32_t>();
+    D.R.seqs = C->d_rank.as<RankSeq>();
+    D.R.n_seqs = C->host.n_spaces;
+    D.cov = C->d_cov.as<CovSpace>();
+    D.JG = C->gaps.J;
+    D.JI = C->irr.J;
+    D.irr_grp = C->d_irr_grp.as<uint32_t>();
+    D.irr_pos = C->d_irr_pos.as<uint32_t>();
+    D.grp_off = C->d_grp_off.as<uint32_t>();
+    D.grp_seq = C->d_grp_seq.as<uint32_t>();
+    D.grp_s = C->d_grp_s.as<uint32_t>();
+    D.grp_e = C->d_grp_e.as<uint32_t>();
+    D.JR = E->J;
+    D.ent_blk = E->d_ent_blk.as<uint32_t>();
+    D.blk_space = C->d_blk_space.as<uint32_t>();
+    D.n_seqs = (uint32_t)E->H->seq_names.size();
+    D.Hs = C->d_Hs.as<uint32_t>();
+    D.He = C->d_He.as<uint32_t>();
+    D.G = C->d_G.as<uint32_t>();
+    D.bits = C->d_bits.as<unsigned long long>();
+    D.diff = C->d_diff.as<int>();
+    D.blk_routed = C->d_routed.as<uint8_t>();
+    return D;
+}
+
+void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags) {
+    CountsState* C = E->counts;
+    if (!C || !C->active) throw Err(E_STATE, "gffx_counts_add without gffx_counts_begin");
+    if (n == 0) return;
+    if (!chr || !start || !end) throw Err(E_ARG, "NULL region arrays");
+    if (C->n_regions + n >= (1ull << 32)) throw Err(E_ARG, "more than 2^32-1 regions in one depth/coverage job (32-bit histogram slots)");
+    GFFX_CUDA(cudaSetDevice(E->dev));
+    const uint32_t *dc, *ds, *de;
+    E->stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
+    const bool aligned = (((uintptr_t)dc | (uintptr_t)ds | (uintptr_t)de) & 15) == 0;
+    const CountsDev D = make_dev(E, C);
+    const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
+    GFFX_CUDA(cudaEventRecord(C->ev0, E->st));
+    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, dc, ds, de, n, aligned, C->d_err.as<uint32_t>());
+    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, dc, ds, de, n, aligned, C->d_err.as<uint32_t>());
+    GFFX_CUDA(cudaEventRecord(C->ev1, E->st));
+    GFFX_CUDA(cudaMemcpyAsync(E->h_small, C->d_err.p, 4, cudaMemcpyDeviceToHost, E->st));
+    GFFX_CUDA(cudaStreamSynchronize(E->st));
+    GFFX_CUDA(cudaGetLastError());
+    float ms;
+    GFFX_CUDA(cudaEventElapsedTime(&ms, C->ev0, C->ev1));
+    C->ms += ms;
+    C->launches += 1;
+    C->n_regions += n;
+    if (*(uint32_t*)E->h_small) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
+}
+
+void counts_finish_impl(EngineImpl* E, CountRows* rows) {
+    CountsState* C = E->counts;
+    if (!C || !C->active) throw Err(E_STATE, "gffx_counts_finish without gffx_counts_begin");
+    GFFX_CUDA(cudaSetDevice(E->dev));
+    const CountsIndexHost& h = C->host;
+    cudaStream_t st = E->st;
+    *rows = CountRows();
+    C->active = false;
+    const uint32_t n_ids = h.n_ids;
+    if (n_ids == 0 || h.n_units == 0) return;
+    typedef unsigned long long ull;
+    const uint64_t scan_n = std::max<uint64_t>({(uint64_t)h.n_slots, h.n_words, (uint64_t)n_ids, 1});
+    C->d_scratch.ensure(scan_scratch_elems(scan_n) * 8);
+    C->r_chrom.ensure(n_ids * 4ull); C->r_start.ensure(n_ids * 4ull); C->r_end.ensure(n_ids * 4ull); C->r_value.ensure(n_ids * 8ull);
+    C->r_flag.ensure(n_ids); C->r_pos.ensure(n_ids * 4ull);
+    GFFX_CUDA(cudaEventRecord(C->ev0, st));
+    CountsFin F{};
+    F.id_unit0 = C->d_id_unit0.as<uint32_t>(); F.id_units = C->d_id_units.as<uint32_t>();
+    F.u_space = C->d_u_space.as<uint32_t>(); F.u_chrom = C->d_u_chrom.as<uint32_t>(); F.u_blk = C->d_u_blk.as<uint32_t>();
+    F.u_line0 = C->d_u_line0.as<uint32_t>(); F.u_seg0 = C->d_u_seg0.as<uint32_t>();
+    F.l_fs = C->d_l_fs.as<uint32_t>(); F.l_fe = C->d_l_fe.as<uint32_t>(); F.l_sfs = C->d_l_sfs.as<uint32_t>(); F.l_sfe = C->d_l_sfe.as<uint32_t>();
+    F.g_s = C->d_g_s.as<uint32_t>(); F.g_e = C->d_g_e.as<uint32_t>(); F.g_ss = C->d_g_ss.as<uint32_t>(); F.g_se = C->d_g_se.as<uint32_t>();
+    F.cov = C->d_cov.as<CovSpace>();
+    F.n_ids = n_ids;
+    if (C->kind == 0) {
+        const uint64_t ns = h.n_slots;
+        C->launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, true>(
+            PtrLoad<uint32_t>{C->d_Hs.as<uint32_t>()}, PtrStore<uint32_t>{C->d_S.as<uint32_t>()}, ns, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
+        C->launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, true>(
+            PtrLoad<uint32_t>{C->d_He.as<uint32_t>()}, PtrStore<uint32_t>{C->d_E.as<uint32_t>()}, ns, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
+        F.S = C->d_S.as<uint32_t>(); F.E = C->d_E.as<uint32_t>(); F.G = C->d_G.as<uint32_t>();
+    } else {
+        const uint64_t nw = h.n_words;
+        C->launches += device_scan<int, OpSum, DiffLoad, CoverStore, false, true>(DiffLoad{C->d_diff.as<int>()}, CoverStore{C->d_bits.as<ull>()}, nw,
+                                                                                OpSum(), 0, C->d_scratch.as<int>(), nullptr, st);
+        C->launches += device_scan<uint32_t, OpSum, PopcLoad, PtrStore<uint32_t>, false, false>(
+            PopcLoad{C->d_bits.as<ull>()}, PtrStore<uint32_t>{C->d_P.as<uint32_t>()}, nw, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
+        F.bits = C->d_bits.as<ull>(); F.P = C->d_P.as<uint32_t>(); F.blk_routed = C->d_routed.as<uint8_t>();
+    }
+    RowArrays R{C->r_chrom.as<uint32_t>(), C->r_start.as<uint32_t>(), C->r_end.as<uint32_t>(), C->r_value.as<ull>(), C->r_flag.as<uint8_t>()};
+    const unsigned nb = (n_ids + 255) / 256;
+    if (C->kind == 0) counts_rows_kernel<0><<<nb, 256, 0, st>>>(F, R);
+    else counts_rows_kernel<1><<<nb, 256, 0, st>>>(F, R);
+    C->launches++;
+    uint32_t* d_total = C->d_err.as<uint32_t>() + 8;
+    C->launches += device_scan<uint32_t, OpSum, FlagLoad, PtrStore<uint32_t>, false, false>(FlagLoad{R.flag}, PtrStore<uint32_t>{C->r_pos.as<uint32_t>()}, n_ids,
+                                                                                         OpSum(), 0u, C->d_scratch.as<uint32_t>(), d_total, st);
+    GFFX_CUDA(cudaMemcpyAsync(E->h_small, d_total, 4, cudaMemcpyDeviceToHost, st));
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    GFFX_CUDA(cudaGetLastError());
+    const uint32_t n_rows = *(uint32_t*)E->h_small;
+    if (n_rows) {
+        C->o_id.ensure(n_rows * 4ull); C->o_chrom.ensure(n_rows * 4ull); C->o_start.ensure(n_rows * 4ull); C->o_end.ensure(n_rows * 4ull);
+        C->o_value.ensure(n_rows * 8ull);
+        counts_compact_kernel<<<nb, 256, 0, st>>>(R, C->r_pos.as<uint32_t>(), n_ids, C->o_id.as<uint32_t>(), C->o_chrom.as<uint32_t>(),
+                                                  C->o_start.as<uint32_t>(), C->o_end.as<uint32_t>(), C->o_value.as<ull>());
+        C->launches++;
+    }
+    GFFX_CUDA(cudaEventRecord(C->ev1, st));
+    if (n_rows) {
+        rows->id_idx.resize(n_rows); rows->chrom_idx.resize(n_rows); rows->start.resize(n_rows); rows->end.resize(n_rows); rows->value.resize(n_rows);
+        GFFX_CUDA(cudaMemcpyAsync(rows->id_idx.data(), C->o_id.p, n_rows * 4ull, cudaMemcpyDeviceToHost, st));
+        GFFX_CUDA(cudaMemcpyAsync(rows->chrom_idx.data(), C->o_chrom.p, n_rows * 4ull, cudaMemcpyDeviceToHost, st));
+        GFFX_CUDA(cudaMemcpyAsync(rows->start.data(), C->o_start.p, n_rows * 4ull, cudaMemcpyDeviceToHost, st));
+        GFFX_CUDA(cudaMemcpyAsync(rows->end.data(), C->o_end.p, n_rows * 4ull, cudaMemcpyDeviceToHost, st));
+        GFFX_CUDA(cudaMemcpyAsync(rows->value.data(), C->o_value.p, n_rows * 8ull, cudaMemcpyDeviceToHost, st));
+    }
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    GFFX_CUDA(cudaGetLastError());
+    float ms;
+    GFFX_CUDA(cudaEventElapsedTime(&ms, C->ev0, C->ev1));
+    C->ms += ms;
+}
+
 double counts_ms_impl(const EngineImpl* E) { return E->counts ? E->counts->ms : 0.0; }
 uint32_t counts_launches_impl(const EngineImpl* E) { return E->counts ? E->counts->launches : 0; }
 

@@ -1,0 +1,249 @@
+// counts.cuh — K6 / K7: depth (src/commands/depth.rs:121-293) and coverage breadth
+// (src/commands/coverage.rs:208-450) as a difference-array / histogram scatter over the regions,
+// prefix scans, and a per-ID reduction over the units of counts_index.h.
+//
+//   depth     per region and space: Hs[ub(start)]++, He[lb(end)]++ (rank slots of the space's line
+//             coordinates, L2-resident), and G[gap]++ for every inter-segment gap that contains the
+//             region.  With S, E the prefix sums:  #regions overlapping [X_i, X_j) = S[j] - E[i]
+//             (every region has start < end, so "ends at or before X_i" and "starts at or after X_j"
+//             exclude each other), and a multi-segment ID is hit by S[last end] - E[first start] - sum G.
+//   coverage  per region and space: the partial first/last 64-base words are OR-ed into a bitmap, the
+//             fully covered words in between go through a word-granular difference array; a scan turns
+//             positive counts into all-ones words, a second scan gives the covered-base prefix P, and
+//             covered bases in [s,e) = C(e) - C(s) with C(x) = P[word] + popc(bits below x).
+#pragma once
+#include "filter.cuh"
+#include "join.cuh"
+
+namespace gffx {
+
+struct CovSpace {  // 16 B, same layout as CovSpaceHost
+    uint32_t lo, nbits;
+    unsigned long long word0;
+};
+
+struct CountsDev {
+    RankSpace R;            // spaces as "sequences": X, dir, descriptors
+    const CovSpace* cov;
+    JoinIndex JG;           // gaps, seq = space, payload = left segment index
+    JoinIndex JI;           // tree intervals of irregular blocks, seq = sequence, payload = private space
+    const uint32_t* irr_grp;
+    const uint32_t* irr_pos;
+    const uint32_t* grp_off;
+    const uint32_t* grp_seq;
+    const uint32_t* grp_s;
+    const uint32_t* grp_e;
+    JoinIndex JR;           // all root intervals (coverage routing)
+    const uint32_t* ent_blk;
+    const uint32_t* blk_space;
+    uint32_t n_seqs;
+    // accumulators
+    uint32_t* Hs;
+    uint32_t* He;
+    uint32_t* G;
+    unsigned long long* bits;
+    int* diff;
+    uint8_t* blk_routed;
+};
+
+__device__ __forceinline__ void depth_space_update(const CountsDev& D, uint32_t sp, uint32_t rs, uint32_t re) {
+    const RankSeq S = load_rank_seq(D.R, sp);
+    if (S.cnt == 0) return;
+    bool eq;
+    uint32_t lb = rank_lb(D.R, S, rs, &eq);
+    atomicAdd(D.Hs + S.slot0 + lb + (eq ? 1u : 0u), 1u);  // slot ub(start): counted by S[k] for every X_k > start
+    lb = rank_lb(D.R, S, re, &eq);
+    atomicAdd(D.He + S.slot0 + lb, 1u);                   // slot lb(end):   counted by E[k] for every X_k >= end
+    // gaps [a,b] with a <= start and end <= b: the region lies between two segments of that ID
+    join_query<2, false>(D.JG, sp, rs, rs + 1u, [&](uint32_t j, uint2 se) {
+        if (se.y >= re) atomicAdd(D.G + __ldg(D.JG.ent_fid + j), 1u);
+    });
+}
+
+__device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp, uint32_t rs, uint32_t re) {
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(D.cov + sp));
+    const uint32_t lo = raw.x, nbits = raw.y;
+    if (nbits == 0) return;
+    const unsigned long long word0 = ((unsigned long long)raw.w << 32) | raw.z;
+    const uint32_t a = rs > lo ? rs : lo, hi = lo + nbits, b = re < hi ? re : hi;
+    if (a >= b) return;
+    const uint32_t p0 = a - lo, p1 = b - lo - 1u;  // first and last covered bit
+    const unsigned long long wa = word0 + (p0 >> 6), wb = word0 + (p1 >> 6);
+    const unsigned long long ma = ~0ull << (p0 & 63), mb = ~0ull >> (63 - (p1 & 63));
+    // bits are only ever set during a job, so a word that already shows the mask needs no atomic
+    if (wa == wb) {
+        const unsigned long long m = ma & mb;
+        if ((__ldcg(D.bits + wa) & m) != m) atomicOr(D.bits + wa, m);
+    } else {
+        if ((__ldcg(D.bits + wa) & ma) != ma) atomicOr(D.bits + wa, ma);
+        if ((__ldcg(D.bits + wb) & mb) != mb) atomicOr(D.bits + wb, mb);
+        if (wb > wa + 1) {
+            atomicAdd(D.diff + wa + 1, 1);
+            atomicAdd(D.diff + wb, -1);
+        }
+    }
+}
+
+// KIND 0 depth, 1 coverage.  Regions with start >= end are ignored (both BED dialects of the
+// counting commands drop them: depth.rs:488, coverage.rs:253).
+template <int KIND>
+__global__ void __launch_bounds__(JOIN_THREADS)
+    counts_scatter_kernel(CountsDev D, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
+                          uint64_t n, bool aligned, uint32_t* __restrict__ err) {
+    const uint64_t q0 = (uint64_t)blockIdx.x * JOIN_TILE + (uint64_t)threadIdx.x * JOIN_QPT;
+    if (q0 >= n) return;
+    Query4 Q;
+    load_queries(chr, qs, qe, n, q0, aligned, Q);
+#pragma unroll
+    for (int k = 0; k < JOIN_QPT; k++) {
+        if (k >= Q.n) continue;
+        const uint32_t c = Q.c[k], rs = Q.s[k], re = Q.e[k];
+        if (rs >= re) continue;
+        if (c >= D.n_seqs) { *err = 1; continue; }
+        if (KIND == 0) {
+            depth_space_update(D, c, rs, re);
+            join_query<2, false>(D.JI, c, rs, re, [&](uint32_t j, uint2) {
+                // a root fid with several tree intervals is routed once per region (depth.rs:239-241):
+                // only the lowest-ranked interval of the group that the region overlaps does the update
+                const uint32_t g = __ldg(D.irr_grp + j);
+                if (g != 0xFFFFFFFFu) {
+                    const uint32_t m0 = __ldg(D.grp_off + g), m1 = m0 + __ldg(D.irr_pos + j);
+                    for (uint32_t m = m0; m < m1; m++)
+                        if (__ldg(D.grp_seq + m) == c && __ldg(D.grp_s + m) < re && __ldg(D.grp_e + m) > rs) return;
+                }
+                depth_space_update(D, __ldg(D.JI.ent_fid + j), rs, re);
+            });
+        } else {
+            cov_space_update(D, c, rs, re);
+            join_query<2, false>(D.JR, c, rs, re, [&](uint32_t j, uint2) {
+                const uint32_t blk = __ldg(D.ent_blk + j);
+                if (blk == 0xFFFFFFFFu) return;
+                if (!D.blk_routed[blk]) D.blk_routed[blk] = 1;
+                const uint32_t sp = __ldg(D.blk_space + blk);
+                if (sp != 0xFFFFFFFFu) cov_space_update(D, sp, rs, re);  // OR / +-1 updates tolerate repeats: no dedup needed
+            });
+        }
+    }
+}
+
+// ---- finish -----------------------------------------------------------------------------------
+struct DiffLoad {
+    const int* d;
+    __device__ int operator()(uint64_t i) const { return d[i]; }
+};
+struct CoverStore {  // inclusive prefix of the word difference array > 0  =>  the whole word is covered
+    unsigned long long* bits;
+    __device__ void operator()(uint64_t i, int v) const {
+        if (v > 0) bits[i] = ~0ull;
+    }
+};
+struct PopcLoad {
+    const unsigned long long* bits;
+    __device__ uint32_t operator()(uint64_t i) const { return (uint32_t)__popcll(bits[i]); }
+};
+
+struct CountsFin {
+    const uint32_t* id_unit0;
+    const uint32_t* id_units;
+    const uint32_t* u_space;
+    const uint32_t* u_chrom;
+    const uint32_t* u_blk;
+    const uint32_t* u_line0;
+    const uint32_t* u_seg0;
+    const uint32_t* l_fs;
+    const uint32_t* l_fe;
+    const uint32_t* l_sfs;
+    const uint32_t* l_sfe;
+    const uint32_t* g_s;
+    const uint32_t* g_e;
+    const uint32_t* g_ss;
+    const uint32_t* g_se;
+    const CovSpace* cov;
+    // scanned accumulators
+    const uint32_t* S;
+    const uint32_t* E;
+    const uint32_t* G;
+    const unsigned long long* bits;
+    const uint32_t* P;
+    const uint8_t* blk_routed;
+    uint32_t n_ids;
+};
+
+struct RowArrays {
+    uint32_t* chrom;
+    uint32_t* start;
+    uint32_t* end;
+    unsigned long long* value;
+    uint8_t* flag;
+};
+
+__device__ __forceinline__ uint32_t covered_before(const CountsFin& F, const CovSpace& cv, uint32_t x) {
+    const uint32_t p = x - cv.lo;
+    const unsigned long long w = cv.word0 + (p >> 6);
+    return F.P[w] + (uint32_t)__popcll(F.bits[w] & ((1ull << (p & 63)) - 1ull));
+}
+
+// one thread per ID: reduce its units (ascending block order) into one row
+template <int KIND>
+__global__ void __launch_bounds__(256) counts_rows_kernel(CountsFin F, RowArrays R) {
+    const uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= F.n_ids) return;
+    unsigned long long value = 0;
+    uint32_t mn = 0xFFFFFFFFu, mx = 0, chrom = 0xFFFFFFFFu;
+    bool any = false;
+    for (uint32_t k = F.id_unit0[id]; k < F.id_unit0[id + 1]; k++) {
+        const uint32_t u = F.id_units[k];
+        const uint32_t s0 = F.u_seg0[u], s1 = F.u_seg0[u + 1];
+        if (KIND == 0) {
+            uint32_t d = F.S[F.g_se[s1 - 1]] - F.E[F.g_ss[s0]];  // mod 2^32; the true value is below 2^32
+            for (uint32_t g = s0; g + 1 < s1; g++) d -= F.G[g];
+            if (d == 0) continue;
+            value += d;
+            any = true;
+            if (chrom == 0xFFFFFFFFu) chrom = F.u_chrom[u];
+            // hull over the lines that were hit (depth.rs:198-199)
+            for (uint32_t l = F.u_line0[u]; l < F.u_line0[u + 1]; l++)
+                if (F.S[F.l_sfe[l]] - F.E[F.l_sfs[l]] != 0) {
+                    mn = min(mn, F.l_fs[l]);
+                    mx = max(mx, F.l_fe[l]);
+                }
+        } else {
+            if (!F.blk_routed[F.u_blk[u]]) continue;
+            any = true;
+            if (chrom == 0xFFFFFFFFu) chrom = F.u_chrom[u];
+            const CovSpace cv = F.cov[F.u_space[u]];
+            for (uint32_t g = s0; g < s1; g++) value += (uint32_t)(covered_before(F, cv, F.g_e[g]) - covered_before(F, cv, F.g_s[g]));
+            mn = min(mn, F.g_s[s0]);       // hull over ALL lines (coverage.rs:345-346): segments are sorted and disjoint
+            mx = max(mx, F.g_e[s1 - 1]);
+        }
+    }
+    R.flag[id] = any ? 1 : 0;
+    if (any) {
+        R.chrom[id] = chrom;
+        R.start[id] = mn == 0xFFFFFFFFu ? 0u : mn;
+        R.end[id] = mx;
+        R.value[id] = value;
+    }
+}
+
+struct FlagLoad {
+    const uint8_t* f;
+    __device__ uint32_t operator()(uint64_t i) const { return f[i]; }
+};
+
+// order-preserving compaction of the flagged rows (ID dictionary order)
+static __global__ void __launch_bounds__(256)
+    counts_compact_kernel(RowArrays R, const uint32_t* __restrict__ pos, uint32_t n_ids, uint32_t* __restrict__ o_id,
+                          uint32_t* __restrict__ o_chrom, uint32_t* __restrict__ o_start, uint32_t* __restrict__ o_end,
+                          unsigned long long* __restrict__ o_value) {
+    const uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n_ids || !R.flag[id]) return;
+    const uint32_t p = pos[id];
+    o_id[p] = id;
+    o_chrom[p] = R.chrom[id];
+    o_start[p] = R.start[id];
+    o_end[p] = R.end[id];
+    o_value[p] = R.value[id];
+}
+
+}  // namespace gffx

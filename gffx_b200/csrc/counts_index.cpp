@@ -1,0 +1,178 @@
+#include "counts_index.h"
+#include <algorithm>
+#include <numeric>
+
+namespace gffx {
+
+void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
+    CountsIndexHost& C = *out;
+    C = CountsIndexHost();
+    const LineTable& L = H.lines;
+    const uint32_t n_seqs = (uint32_t)H.seq_names.size();
+    const size_t nb = H.blocks.size();
+    C.n_ids = (uint32_t)H.ids.size();
+
+    // tree intervals per block
+    std::vector<uint32_t> br_off(nb + 1, 0), br_list(0);
+    for (size_t i = 0; i < H.roots.size(); i++)
+        if (H.root_blk[i] != NONE32) br_off[H.root_blk[i] + 1]++;
+    for (size_t b = 0; b < nb; b++) br_off[b + 1] += br_off[b];
+    br_list.resize(br_off[nb]);
+    {
+        std::vector<uint32_t> fill(br_off.begin(), br_off.end() - 1);
+        for (size_t i = 0; i < H.roots.size(); i++)
+            if (H.root_blk[i] != NONE32) br_list[fill[H.root_blk[i]]++] = (uint32_t)i;
+    }
+
+    C.blk_space.assign(nb, NONE32);
+    uint32_t n_spaces = n_seqs;
+    std::vector<std::vector<uint32_t>> id_units(C.n_ids);
+    std::vector<JoinItem> gap_items, irr_items;
+    std::vector<uint32_t> irr_item_grp, irr_item_pos;
+    std::vector<uint32_t> ord;
+    C.u_line0.push_back(0);
+    C.u_seg0.push_back(0);
+    C.grp_off.push_back(0);
+
+    for (size_t b = 0; b < nb; b++) {
+        const uint32_t nroots = br_off[b + 1] - br_off[b];
+        if (nroots == 0) continue;  // never routed
+        const uint64_t l0 = H.blk_line0[b], l1 = H.blk_line0[b + 1];
+        ord.clear();
+        for (uint64_t i = l0; i < l1; i++)
+            if (L.flags[i] & LN_D_OK) ord.push_back((uint32_t)i);
+        if (ord.empty()) continue;
+        // regular <=> one tree interval and every line nested inside it
+        bool regular = nroots == 1;
+        const RootIv& r0 = H.roots[br_list[br_off[b]]];
+        if (regular)
+            for (uint32_t i : ord)
+                if (L.fs[i] < r0.start || L.fe[i] > r0.end) { regular = false; break; }
+        uint32_t space;
+        if (regular) space = r0.seq;
+        else {
+            space = n_spaces++;
+            C.blk_space[b] = space;
+            C.n_irregular++;
+            const uint32_t grp = nroots > 1 ? (uint32_t)(C.grp_off.size() - 1) : NONE32;
+            for (uint32_t k = 0; k < nroots; k++) {
+                const RootIv& r = H.roots[br_list[br_off[b] + k]];
+                irr_items.push_back(JoinItem{r.seq, r.start, r.end, space});
+                irr_item_grp.push_back(grp);
+                irr_item_pos.push_back(k);
+                if (grp != NONE32) { C.grp_seq.push_back(r.seq); C.grp_s.push_back(r.start); C.grp_e.push_back(r.end); }
+            }
+            if (grp != NONE32) C.grp_off.push_back((uint32_t)C.grp_seq.size());
+        }
+        // units: lines grouped by ID; chrom = column 1 of the ID's first line in the block (depth.rs:148-153)
+        std::stable_sort(ord.begin(), ord.end(), [&](uint32_t a, uint32_t c) { return L.id[a] < L.id[c]; });
+        size_t p = 0;
+        while (p < ord.size()) {
+            size_t q = p;
+            while (q < ord.size() && L.id[ord[q]] == L.id[ord[p]]) q++;
+            const uint32_t u = (uint32_t)C.u_space.size();
+            C.u_space.push_back(space);
+            C.u_chrom.push_back(L.chrom[ord[p]]);  // stable sort: ord[p] is the first line in file order
+            C.u_blk.push_back((uint32_t)b);
+            id_units[L.id[ord[p]]].push_back(u);
+            std::sort(ord.begin() + p, ord.begin() + q, [&](uint32_t a, uint32_t c) {
+                if (L.fs[a] != L.fs[c]) return L.fs[a] < L.fs[c];
+                return L.fe[a] < L.fe[c];
+            });
+            const uint32_t seg_first = (uint32_t)C.g_s.size();
+            uint32_t cs = L.fs[ord[p]], ce = L.fe[ord[p]];
+            for (size_t k = p; k < q; k++) {
+                const uint32_t s = L.fs[ord[k]], e = L.fe[ord[k]];
+                C.l_fs.push_back(s);
+                C.l_fe.push_back(e);
+                if (s <= ce) ce = std::max(ce, e);
+                else {
+                    C.g_s.push_back(cs); C.g_e.push_back(ce);
+                    cs = s; ce = e;
+                }
+            }
+            C.g_s.push_back(cs); C.g_e.push_back(ce);
+            for (uint32_t g = seg_first; g + 1 < C.g_s.size(); g++) gap_items.push_back(JoinItem{space, C.g_e[g], C.g_s[g + 1], g});
+            C.u_line0.push_back((uint32_t)C.l_fs.size());
+            C.u_seg0.push_back((uint32_t)C.g_s.size());
+            p = q;
+        }
+    }
+    C.n_units = (uint32_t)C.u_space.size();
+    C.n_segs = (uint32_t)C.g_s.size();
+    C.n_clines = (uint32_t)C.l_fs.size();
+    C.n_spaces = n_spaces;
+
+    // per-space coordinate sets
+    std::vector<std::vector<uint32_t>> xs(n_spaces);
+    for (uint32_t u = 0; u < C.n_units; u++) {
+        auto& v = xs[C.u_space[u]];
+        for (uint32_t i = C.u_line0[u]; i < C.u_line0[u + 1]; i++) { v.push_back(C.l_fs[i]); v.push_back(C.l_fe[i]); }
+    }
+    C.rank.assign(n_spaces, RankSeqHost{});
+    C.cov.assign(n_spaces, CovSpaceHost{});
+    uint32_t slot = 0;
+    uint64_t word = 0;
+    for (uint32_t s = 0; s < n_spaces; s++) {
+        auto& v = xs[s];
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+        RankSeqHost& r = C.rank[s];
+        r.x0 = (uint32_t)C.X.size();
+        r.cnt = (uint32_t)v.size();
+        r.slot0 = slot;
+        slot += r.cnt + 1;
+        r.canon = 1;
+        r.dir_base = (uint32_t)C.dir.size();
+        CovSpaceHost& cv = C.cov[s];
+        cv.word0 = word;
+        if (v.empty()) { r.nb = 0; r.shift = 0; C.dir.push_back(0); cv.lo = 0; cv.nbits = 0; continue; }
+        const uint32_t maxv = v.back();
+        uint32_t shift = 4;
+        while (((uint64_t)maxv >> shift) + 1 > std::max<uint64_t>(64, 2ull * v.size())) shift++;
+        r.shift = shift;
+        r.nb = (maxv >> shift) + 1;
+        uint32_t j = 0;
+        for (uint32_t bq = 0; bq <= r.nb; bq++) {  // nb+1 entries: dir[b] = #(X < b<<shift)
+            const uint64_t lo = (uint64_t)bq << shift;
+            while (j < v.size() && (uint64_t)v[j] < lo) j++;
+            C.dir.push_back(j);
+        }
+        C.X.insert(C.X.end(), v.begin(), v.end());
+        cv.lo = v.front();
+        cv.nbits = v.back() - v.front();
+        word += (uint64_t)cv.nbits / 64 + 1;
+    }
+    C.n_slots = slot;
+    C.n_words = word;
+
+    auto slot_of = [&](uint32_t space, uint32_t v) {
+        const auto& x = xs[space];
+        return C.rank[space].slot0 + (uint32_t)(std::lower_bound(x.begin(), x.end(), v) - x.begin());
+    };
+    C.l_sfs.resize(C.l_fs.size());
+    C.l_sfe.resize(C.l_fs.size());
+    C.g_ss.resize(C.g_s.size());
+    C.g_se.resize(C.g_s.size());
+    for (uint32_t u = 0; u < C.n_units; u++) {
+        const uint32_t sp = C.u_space[u];
+        for (uint32_t i = C.u_line0[u]; i < C.u_line0[u + 1]; i++) { C.l_sfs[i] = slot_of(sp, C.l_fs[i]); C.l_sfe[i] = slot_of(sp, C.l_fe[i]); }
+        for (uint32_t i = C.u_seg0[u]; i < C.u_seg0[u + 1]; i++) { C.g_ss[i] = slot_of(sp, C.g_s[i]); C.g_se[i] = slot_of(sp, C.g_e[i]); }
+    }
+
+    C.id_unit0.assign((size_t)C.n_ids + 1, 0);
+    for (uint32_t i = 0; i < C.n_ids; i++) C.id_unit0[i + 1] = C.id_unit0[i] + (uint32_t)id_units[i].size();
+    C.id_units.reserve(C.n_units);
+    for (uint32_t i = 0; i < C.n_ids; i++) C.id_units.insert(C.id_units.end(), id_units[i].begin(), id_units[i].end());
+
+    build_join_host(n_spaces, gap_items, 16, 8, &C.gaps);
+    build_join_host(n_seqs, irr_items, 16, 8, &C.irr);
+    C.irr_grp.resize(C.irr.n_entries());
+    C.irr_pos.resize(C.irr.n_entries());
+    for (size_t k = 0; k < C.irr.n_entries(); k++) {
+        C.irr_grp[k] = irr_item_grp[C.irr.ent_item[k]];
+        C.irr_pos[k] = irr_item_pos[C.irr.ent_item[k]];
+    }
+}
+
+}  // namespace gffx

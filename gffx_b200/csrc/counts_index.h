@@ -1,0 +1,60 @@
+// counts_index.h — index-time layout for depth / coverage (K6 / K7), derived once from the line table.
+//
+// Reference semantics (src/commands/depth.rs:121-293,
+// src/commands/coverage.rs:208-450): a region is ROUTED to every root whose tree interval it overlaps
+// (deduplicated by root fid); inside the root's block every line carrying an ID is tested against the
+// routed regions; results are keyed by the ID STRING and merged across blocks.
+//
+// Layout:
+//   unit    = (block, ID) — the lines of one ID inside one block, sorted by start, plus their merged
+//             segments (touching lines merge; the gaps between segments are what a region must not
+//             fall into to be counted once).
+//   space   = a set of regions + a coordinate set.  Space c < n_seqs is "every valid region on
+//             sequence c" and holds the units of REGULAR blocks (exactly one tree interval, every
+//             line nested inside it — then overlapping a line implies being routed).  Every other
+//             block with usable lines gets a private space fed only by the regions routed to it.
+//   X       = per space the sorted distinct line coordinates; slot k of a space = "rank k in X".
+//             depth: histograms of region starts / ends over the slots (prefix sums S, E) give the
+//             number of regions overlapping any [X_i, X_j); coverage: a bitmap over the space's
+//             coordinate hull gives the covered bases.
+#pragma once
+#include "host_index.h"
+#include "join_build.h"
+
+namespace gffx {
+
+struct RankSeqHost {  // same 32-byte layout as RankSeq (filter.cuh)
+    uint32_t x0, cnt, dir_base, nb, shift, slot0, canon, pad;
+};
+struct CovSpaceHost {  // 16 B
+    uint32_t lo, nbits;   // bitmap covers coordinates [lo, lo+nbits)
+    uint64_t word0;       // first 64-bit word of the space; the space owns nbits/64+1 words
+};
+
+struct CountsIndexHost {
+    uint32_t n_spaces = 0, n_slots = 0, n_units = 0, n_ids = 0, n_segs = 0, n_clines = 0;
+    uint64_t n_words = 0;
+    std::vector<RankSeqHost> rank;
+    std::vector<CovSpaceHost> cov;
+    std::vector<uint32_t> X, dir;
+    // units
+    std::vector<uint32_t> u_space, u_chrom, u_blk, u_line0, u_seg0;   // u_line0/u_seg0: n_units+1
+    // lines grouped by unit, sorted by start: coordinates and global slots of both ends
+    std::vector<uint32_t> l_fs, l_fe, l_sfs, l_sfe;
+    // merged segments grouped by unit
+    std::vector<uint32_t> g_s, g_e, g_ss, g_se;
+    // per ID: its units in ascending block (= file offset) order
+    std::vector<uint32_t> id_unit0, id_units;
+    // gaps between consecutive segments of a unit: seq = space, [start,end] = [seg.e, next.s], payload = left segment
+    JoinHost gaps;
+    // tree intervals of irregular blocks: seq = sequence number, payload = private space
+    JoinHost irr;
+    std::vector<uint32_t> irr_grp, irr_pos;          // per irr entry: duplicate-fid group (NONE32 = single) and rank inside it
+    std::vector<uint32_t> grp_off, grp_seq, grp_s, grp_e;  // group members in rank order
+    std::vector<uint32_t> blk_space;                 // per block: private space of an irregular block, else NONE32
+    uint64_t n_irregular = 0;
+};
+
+void build_counts_index(const HostIndex& H, CountsIndexHost* out);
+
+}  // namespace gffx

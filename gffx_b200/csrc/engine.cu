@@ -6,8 +6,6 @@
 
 namespace gffx {
 
-constexpr int JOIN_K = 16;        // an interval that reaches past the start of its JOIN_K-th successor is "long"
-constexpr int JOIN_MAX_LISTS = 8; // per sequence
 constexpr uint32_t WARN_CAP = 1u << 16;
 
 // small kernels -------------------------------------------------------------------------------
@@ -40,7 +38,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     GFFX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
-    for (DBuf* b : {&d_seq_list0, &d_lists, &d_ent_se, &d_ent_fid, &d_ent_blk, &d_dir, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
+    for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
@@ -56,96 +54,50 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
 EngineImpl::~EngineImpl() {
     cudaSetDevice(dev);
     if (st) cudaStreamSynchronize(st);
-    for (DBuf* b : {&d_seq_list0, &d_lists, &d_ent_se, &d_ent_fid, &d_ent_blk, &d_dir, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
+    for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
+    dj.release();
     counts_release(this);
     if (h_small) cudaFreeHost(h_small);
     for (auto& x : ev) cudaEventDestroy(x);
     if (st) cudaStreamDestroy(st);
 }
 
-// Join index: per sequence sort by start, peel "long" intervals into further lists, build the
-// running-max-end directory of each list.
+// Join index over the root intervals (see join_build.h / join.cuh).
 void EngineImpl::build_join() {
     const size_t n_seqs = H->seq_names.size();
-    std::vector<std::vector<uint32_t>> by_seq(n_seqs);
-    for (size_t i = 0; i < H->roots.size(); i++) by_seq[H->roots[i].seq].push_back((uint32_t)i);
-    std::vector<uint32_t> seq_list0(n_seqs + 1, 0), ent_fid, ent_blk, dir;
-    std::vector<uint2> ent_se;
-    std::vector<JoinList> lists;
+    const auto& R = H->roots;
+    std::vector<JoinItem> items(R.size());
+    for (size_t i = 0; i < R.size(); i++) items[i] = JoinItem{R[i].seq, R[i].start, R[i].end, R[i].fid};
+    JoinHost jh;
+    build_join_host((uint32_t)n_seqs, items, JOIN_LONG_K, JOIN_MAX_LISTS, &jh);
+    // accessor copy: per sequence (start,end,fid) sorted by (start,end)
     seq_sorted_roots.assign(n_seqs, {});
-    for (size_t s = 0; s < n_seqs; s++) {
-        seq_list0[s] = (uint32_t)lists.size();
-        std::vector<uint32_t>& ids = by_seq[s];
-        const auto& R = H->roots;
-        std::stable_sort(ids.begin(), ids.end(), [&](uint32_t a, uint32_t b) {
-            if (R[a].start != R[b].start) return R[a].start < R[b].start;
-            return R[a].end < R[b].end;
-        });
-        auto& flat = seq_sorted_roots[s];
-        flat.reserve(ids.size() * 3);
-        for (uint32_t i : ids) { flat.push_back(R[i].start); flat.push_back(R[i].end); flat.push_back(R[i].fid); }
-        std::vector<uint32_t> cur = ids, keep, longs;
-        for (int level = 0; !cur.empty(); level++) {
-            keep.clear();
-            longs.clear();
-            if (level == JOIN_MAX_LISTS - 1 || cur.size() <= 4 * JOIN_K) keep = cur;
-            else {
-                for (size_t i = 0; i < cur.size(); i++) {
-                    bool is_long = i + JOIN_K < cur.size() && R[cur[i]].end > R[cur[i + JOIN_K]].start;
-                    (is_long ? longs : keep).push_back(cur[i]);
-                }
-            }
-            if (!keep.empty()) {
-                JoinList L{};
-                L.base = (uint32_t)ent_se.size();
-                L.count = (uint32_t)keep.size();
-                uint32_t maxend = 0;
-                for (uint32_t i : keep) maxend = std::max(maxend, R[i].end);
-                uint32_t shift = 6;
-                while (((uint64_t)maxend >> shift) + 1 > std::max<uint64_t>(64, 4ull * keep.size())) shift++;
-                L.shift = shift;
-                L.nbins = (maxend >> shift) + 1;
-                L.dir_base = (uint32_t)dir.size();
-                for (uint32_t i : keep) {
-                    ent_se.push_back(make_uint2(R[i].start, R[i].end));
-                    ent_fid.push_back(R[i].fid);
-                    ent_blk.push_back(H->root_blk[i]);
-                }
-                // dir[b] = first j (absolute) whose inclusive running max-end exceeds b<<shift
-                uint32_t j = 0, pm = 0;
-                std::vector<uint32_t> pmax(keep.size());
-                for (size_t k = 0; k < keep.size(); k++) { pm = std::max(pm, R[keep[k]].end); pmax[k] = pm; }
-                for (uint32_t b = 0; b < L.nbins; b++) {
-                    const uint64_t lo = (uint64_t)b << shift;
-                    while (j < keep.size() && (uint64_t)pmax[j] <= lo) j++;
-                    dir.push_back(L.base + j);
-                }
-                lists.push_back(L);
-            }
-            cur = longs;
+    {
+        std::vector<std::vector<uint32_t>> by_seq(n_seqs);
+        for (size_t i = 0; i < R.size(); i++) by_seq[R[i].seq].push_back((uint32_t)i);
+        for (size_t s = 0; s < n_seqs; s++) {
+            auto& ids = by_seq[s];
+            std::stable_sort(ids.begin(), ids.end(), [&](uint32_t a, uint32_t b) {
+                if (R[a].start != R[b].start) return R[a].start < R[b].start;
+                return R[a].end < R[b].end;
+            });
+            auto& flat = seq_sorted_roots[s];
+            flat.reserve(ids.size() * 3);
+            for (uint32_t i : ids) { flat.push_back(R[i].start); flat.push_back(R[i].end); flat.push_back(R[i].fid); }
         }
     }
-    seq_list0[n_seqs] = (uint32_t)lists.size();
-    n_ent = (uint32_t)ent_se.size();
-    n_lists = (uint32_t)lists.size();
-    upload(d_seq_list0, seq_list0, st);
-    upload(d_lists, lists, st);
-    upload(d_ent_se, ent_se, st);
-    upload(d_ent_fid, ent_fid, st);
+    std::vector<uint32_t> ent_blk(jh.n_entries());
+    for (size_t k = 0; k < ent_blk.size(); k++) ent_blk[k] = H->root_blk[jh.ent_item[k]];
+    dj.upload_from(jh, st, &dev_bytes);
+    n_ent = dj.n_ent;
+    J = dj.J;
     upload(d_ent_blk, ent_blk, st);
-    upload(d_dir, dir, st);
     d_ent_hit.ensure(std::max<uint32_t>(n_ent, 1));
     GFFX_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
-    J.seq_list0 = d_seq_list0.as<uint32_t>();
-    J.lists = d_lists.as<JoinList>();
-    J.ent_se = d_ent_se.as<uint2>();
-    J.ent_fid = d_ent_fid.as<uint32_t>();
-    J.dir = d_dir.as<uint32_t>();
-    J.n_seqs = (uint32_t)n_seqs;
 }
 
 void EngineImpl::build_blocks() {

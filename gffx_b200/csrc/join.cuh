@@ -24,6 +24,8 @@ constexpr int JOIN_THREADS = 256;
 constexpr int JOIN_QPT = 4;                       // consecutive queries per thread (one 16 B load per column)
 constexpr int JOIN_TILE = JOIN_THREADS * JOIN_QPT;
 constexpr int JOIN_STAGE_PAIRS = 3072;            // 36 KB of shared memory for pair staging
+constexpr int JOIN_LONG_K = 16;     // an interval that reaches past the start of its 16th successor is "long"
+constexpr int JOIN_MAX_LISTS = 8;   // per sequence
 
 struct JoinList {
     uint32_t base, count, dir_base, nbins, shift, pad0, pad1, pad2;
