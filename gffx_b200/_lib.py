@@ -85,6 +85,8 @@ SIGNATURES = {
     "gffx_index_open": (C.c_int, C.c_char_p, C.c_int, C.POINTER(vp)),
     "gffx_index_create": (C.c_int, C.POINTER(IndexDesc), C.POINTER(vp)),
     "gffx_index_destroy": (None, vp),
+    "gffx_index_cuda_stream": (vp, vp),
+    "gffx_index_build": (C.c_int, C.c_char_p, C.c_char_p, C.c_char_p),
     "gffx_index_n_seqs": (C.c_uint32, vp),
     "gffx_index_seq_name": (C.c_char_p, vp, C.c_uint32),
     "gffx_index_seq_num": (C.c_int64, vp, C.c_char_p),

@@ -104,7 +104,7 @@ def _take_result(h) -> Result:
         if nw:
             r.warn_fids = list(np.ctypeslib.as_array(lib.gffx_result_warn_fids(h), shape=(nw,)))
         r.kernel_ms = lib.gffx_result_kernel_ms(h)
-        r.stage_ms = tuple(lib.gffx_result_stage_ms(h, k) for k in range(5))
+        r.stage_ms = tuple(lib.gffx_result_stage_ms(h, k) for k in range(8))
         r.launches = lib.gffx_result_launches(h)
         return r
     finally:
@@ -183,6 +183,7 @@ class TreeIndexData:
     n_lines = property(lambda self: lib.gffx_index_n_lines(self._h))
     n_ids = property(lambda self: lib.gffx_index_n_ids(self._h))
     device_bytes = property(lambda self: lib.gffx_index_device_bytes(self._h))
+    cuda_stream = property(lambda self: lib.gffx_index_cuda_stream(self._h) or 0)
 
     def seq_roots(self, seq: int) -> np.ndarray:
         p = _lib.u32p()
@@ -335,6 +336,11 @@ class CountRows:
             rows.sort()
         head = b"id\tchr\tstart\tend\tdepth\n" if self.kind == 0 else b"id\tchr\tstart\tend\tbreadth\tfraction\n"
         return head + b"".join(rows)
+
+
+def build_index(gff_path: str, attribute: str = "gene_name", skip_types: Optional[str] = None):
+    """`gffx index` (src/commands/index.rs:25-37): writes the eight index files beside the GFF."""
+    _check(lib.gffx_index_build(str(gff_path).encode(), attribute.encode(), skip_types.encode() if skip_types is not None else None))
 
 
 def synth_gff(path: str, seed: int = 20260001, n_genes: int = 60000, quirks: bool = False) -> int:

@@ -105,6 +105,15 @@ int gffx_index_create(const gffx_index_desc* d, gffx_index** out) {
 }
 
 void gffx_index_destroy(gffx_index* idx) { delete idx; }
+void* gffx_index_cuda_stream(const gffx_index* idx) { return idx && idx->eng_ ? idx->eng_->cuda_stream() : nullptr; }
+
+int gffx_index_build(const char* gff_path, const char* attr_key, const char* skip_types) {
+    return guard([&] {
+        need(gff_path, "gff_path");
+        build_index_files(gff_path, attr_key ? attr_key : "gene_name",
+                          skip_types ? skip_types : "remark,note,comment,region,gap,assembly_gap,contig,scaffold,source");
+    });
+}
 
 uint32_t gffx_index_n_seqs(const gffx_index* idx) { return idx ? (uint32_t)idx->host().seq_names.size() : 0; }
 const char* gffx_index_seq_name(const gffx_index* idx, uint32_t seq) {
@@ -191,7 +200,7 @@ uint64_t gffx_result_n_warn(const gffx_result* r) { return r ? r->r.warn_fids.si
 const uint32_t* gffx_result_warn_fids(const gffx_result* r) { return r && !r->r.warn_fids.empty() ? r->r.warn_fids.data() : nullptr; }
 double gffx_result_kernel_ms(const gffx_result* r) { return r ? r->r.kernel_ms : 0; }
 uint32_t gffx_result_launches(const gffx_result* r) { return r ? r->r.launches : 0; }
-double gffx_result_stage_ms(const gffx_result* r, int stage) { return (r && stage >= 0 && stage < 5) ? r->r.stage_ms[stage] : 0; }
+double gffx_result_stage_ms(const gffx_result* r, int stage) { return (r && stage >= 0 && stage < 8) ? r->r.stage_ms[stage] : 0; }
 void gffx_result_free(gffx_result* r) { delete r; }
 
 int gffx_write_ranges(const gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, const char* out_path) {

@@ -230,6 +230,7 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     out->n_queries = n;
     const bool want_pairs_host = flags & 2u, pairs_dev = (flags & 8u) || want_pairs_host, no_host = flags & 4u;
     uint32_t launches = 0;
+    bool emitted = false;
     const uint32_t *dc, *ds, *de;
     stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
     const bool aligned = (((uintptr_t)dc | (uintptr_t)ds | (uintptr_t)de) & 15) == 0;
@@ -255,15 +256,19 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             default: launch_join_count<2, false>(this, dc, ds, de, n, aligned, tiles, err); break;
         }
         launches++;
+        GFFX_CUDA(cudaEventRecord(ev[1], st));
         launches += device_scan<uint64_t, OpSum, TileCountLoad, PtrStore<uint64_t>, false, false>(
             TileCountLoad{d_tile_count.as<uint32_t>()}, PtrStore<uint64_t>{d_tile_off.as<uint64_t>()}, tiles, OpSum(), 0ull,
             d_scan_scratch.as<uint64_t>(), (uint64_t*)small, st);
+        GFFX_CUDA(cudaEventRecord(ev[2], st));
         GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
         GFFX_CUDA(cudaStreamSynchronize(st));
         if (((uint32_t*)h_small)[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
         out->n_pairs = ((uint64_t*)h_small)[0];
         if (pairs_dev && out->n_pairs) {
             d_pairs.ensure(out->n_pairs * 12);
+            emitted = true;
+            GFFX_CUDA(cudaEventRecord(ev[8], st));
             switch (mode * 2 + (invert ? 1 : 0)) {
                 case 0: launch_join_emit<0, false>(this, dc, ds, de, n, aligned, tiles); break;
                 case 1: launch_join_emit<0, true>(this, dc, ds, de, n, aligned, tiles); break;
@@ -271,11 +276,15 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
                 case 3: launch_join_emit<1, true>(this, dc, ds, de, n, aligned, tiles); break;
                 default: launch_join_emit<2, false>(this, dc, ds, de, n, aligned, tiles); break;
             }
+            GFFX_CUDA(cudaEventRecord(ev[9], st));
             launches++;
             out->d_pairs = d_pairs.as<uint32_t>();
         }
+    } else {
+        GFFX_CUDA(cudaEventRecord(ev[1], st));
+        GFFX_CUDA(cudaEventRecord(ev[2], st));
     }
-    GFFX_CUDA(cudaEventRecord(ev[1], st));
+    GFFX_CUDA(cudaEventRecord(ev[3], st));
 
     // ---- stage 1: root -> block selection, merged ranges (-e) ---------------------------------
     const bool match_only = !entire_group || types_csv != nullptr;  // intersect.rs:619
@@ -290,9 +299,9 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             launches++;
         }
     }
-    GFFX_CUDA(cudaEventRecord(ev[2], st));
+    GFFX_CUDA(cudaEventRecord(ev[4], st));
 
-    // ---- stages 2-4: line filter ---------------------------------------------------------------
+    // ---- stages 4-6: line filter ---------------------------------------------------------------
     uint64_t n_emit_tiles = 0;
     const bool run_filter = !nothing && !join_only && match_only && LA.n > 0;
     if (run_filter) {
@@ -328,7 +337,7 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
         else if (mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
         else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
         launches++;
-        GFFX_CUDA(cudaEventRecord(ev[3], st));
+        GFFX_CUDA(cudaEventRecord(ev[5], st));
 
         typedef unsigned long long ull;
         ull* scr = d_scan_scratch.as<ull>();
@@ -348,7 +357,7 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
                 MarkLoad{F.Me}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
         }
-        GFFX_CUDA(cudaEventRecord(ev[4], st));
+        GFFX_CUDA(cudaEventRecord(ev[6], st));
 
         n_emit_tiles = (LA.n + LINE_THREADS - 1) / LINE_THREADS;
         d_tile_count.ensure(n_emit_tiles * 4);
@@ -368,10 +377,10 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
                                                                           d_ranges.as<ulonglong2>(), small + 4);
         launches++;
     } else {
-        GFFX_CUDA(cudaEventRecord(ev[3], st));
-        GFFX_CUDA(cudaEventRecord(ev[4], st));
+        GFFX_CUDA(cudaEventRecord(ev[5], st));
+        GFFX_CUDA(cudaEventRecord(ev[6], st));
     }
-    GFFX_CUDA(cudaEventRecord(ev[5], st));
+    GFFX_CUDA(cudaEventRecord(ev[7], st));
 
     // ---- results -----------------------------------------------------------------------------
     GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
@@ -405,11 +414,15 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     }
     GFFX_CUDA(cudaStreamSynchronize(st));
     float ms;
-    for (int k = 0; k < 5; k++) {
+    for (int k = 0; k < 7; k++) {
         GFFX_CUDA(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
         out->stage_ms[k] = ms;
     }
-    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[5]));
+    if (emitted) {
+        GFFX_CUDA(cudaEventElapsedTime(&ms, ev[8], ev[9]));
+        out->stage_ms[7] = ms;
+    }
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[7]));
     out->kernel_ms = ms;
     out->launches = launches;
 }
@@ -453,6 +466,7 @@ Engine::~Engine() = default;
 const HostIndex& Engine::host() const { return *impl_->H; }
 int Engine::device() const { return impl_->dev; }
 uint64_t Engine::device_bytes() const { return impl_->dev_bytes; }
+void* Engine::cuda_stream() const { return (void*)impl_->st; }
 const std::vector<uint32_t>& Engine::sorted_roots(uint32_t seq) const {
     if (seq >= impl_->seq_sorted_roots.size()) throw Err(E_ARG, "sequence number out of range");
     return impl_->seq_sorted_roots[seq];

@@ -17,7 +17,7 @@ struct IntersectResult {
     uint64_t bytes_out = 0;
     std::vector<uint32_t> warn_fids;
     double kernel_ms = 0;
-    double stage_ms[5] = {0, 0, 0, 0, 0};
+    double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     uint32_t launches = 0;
 };
 
@@ -36,6 +36,7 @@ class Engine {
     const HostIndex& host() const;
     int device() const;
     uint64_t device_bytes() const;
+    void* cuda_stream() const;
     // (start,end,root_fid) triples of one sequence's tree intervals, sorted by start
     const std::vector<uint32_t>& sorted_roots(uint32_t seq) const;
 
@@ -58,6 +59,9 @@ class Engine {
 };
 
 int cuda_device_count();
+
+// index_builder.cpp
+void build_index_files(const std::string& gff_path, const std::string& attr_key, const std::string& skip_types);
 
 // synthetic workloads (synth.cpp)
 uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes, bool quirks);

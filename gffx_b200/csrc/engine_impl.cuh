@@ -103,7 +103,7 @@ class EngineImpl {
     // ---- per-call scratch --------------------------------------------------------------------
     DBuf d_q[3], d_tile_count, d_tile_off, d_scan_scratch, d_pairs, d_ranges, d_small, d_warn;
     void* h_small = nullptr;  // pinned, 256 B
-    cudaEvent_t ev[8];
+    cudaEvent_t ev[10];  // [0..7] stage boundaries of one intersect call, [8],[9] around the join emit kernel alone
 
     // ---- counts (depth / coverage) -----------------------------------------------------------
     CountsState* counts = nullptr;  // owned; freed by counts_release()

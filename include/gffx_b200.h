@@ -80,6 +80,15 @@ typedef struct {
 int gffx_index_create(const gffx_index_desc* desc, gffx_index** out);
 void gffx_index_destroy(gffx_index* idx);
 
+/* The engine's CUDA stream (a cudaStream_t) so that a caller can record its own events around calls;
+ * NULL for a host-only index. */
+void* gffx_index_cuda_stream(const gffx_index* idx);
+
+/* `gffx index` (src/commands/index.rs:25-37 -> build_index, src/index_builder/core.rs:41-242): writes
+ * .fts .prt .a2f .atn .sqs .gof .rit .rix beside the GFF, byte-compatible with the reference's files.
+ * attr_key NULL = "gene_name", skip_types NULL = the reference's default list (src/commands/index.rs:18). */
+int gffx_index_build(const char* gff_path, const char* attr_key, const char* skip_types);
+
 uint32_t gffx_index_n_seqs(const gffx_index* idx);
 const char* gffx_index_seq_name(const gffx_index* idx, uint32_t seq);
 /* seqid_to_num lookup (TreeIndexData.seqid_to_num); returns -1 when unknown */
@@ -141,7 +150,9 @@ const uint32_t* gffx_result_warn_fids(const gffx_result* r);
 /* device time of the call's kernels in ms (CUDA events on the engine's stream) and launch count */
 double gffx_result_kernel_ms(const gffx_result* r);
 uint32_t gffx_result_launches(const gffx_result* r);
-/* per-stage device ms: 0 join, 1 root/block select, 2 query scatter, 3 rank scans, 4 line filter + compaction */
+/* per-stage device ms: 0 join count kernel, 1 tile-offset scan, 2 join emit kernel, 3 root/block select + merge,
+ * 4 region scatter onto the line rank space, 5 rank scans, 6 line filter + compaction, 7 the join emit kernel alone
+ * (stage 2 also holds the host read-back of the pair count); stages that did not run report 0 */
 double gffx_result_stage_ms(const gffx_result* r, int stage);
 void gffx_result_free(gffx_result* r);
 

@@ -105,3 +105,36 @@ def test_synth_regions_are_a_pure_function_of_seed_and_index(gffx, synth_plain_g
         assert np.array_equal(x[600:], y)
     assert np.all(a[2] - a[1] == 20000) and a[0].max() < idx.n_seqs
     assert len(np.unique(a[0])) > 10
+
+
+@pytest.mark.parametrize("fixture", ["synth_quirk_gff", "synth_plain_gff", "kat_gff"])
+def test_index_builder_is_byte_compatible(gffx, request, fixture, tmp_path):
+    """gffx_index_build (src/index_builder/core.rs:41-242) writes the same bytes as the oracle's restatement."""
+    import shutil
+
+    src = request.getfixturevalue(fixture)
+    dst = str(tmp_path / "copy.gff")
+    shutil.copy(src, dst)
+    gffx.build_index(dst)
+    for ext in ("sqs", "gof", "rit", "rix", "fts", "prt"):
+        assert open(dst + "." + ext, "rb").read() == open(src + "." + ext, "rb").read(), ext
+    # attribute table: header + distinct values in first-seen order; a2f = one u32 per indexed line
+    gffx.build_index(dst, attribute="gene")
+    atn = open(dst + ".atn", "rb").read().split(b"\n")
+    assert atn[0] == b"#attribute=gene"
+    a2f = np.fromfile(dst + ".a2f", dtype="<u4")
+    assert a2f.shape[0] == np.fromfile(dst + ".prt", dtype="<u4").shape[0]
+    used = a2f[a2f != 0xFFFFFFFF]
+    assert (len(atn) - 2 == (used.max() + 1 if len(used) else 0))
+
+
+def test_index_builder_errors(gffx, tmp_path):
+    p = tmp_path / "bad.gff"
+    p.write_bytes(b"chr1\tsrc\tgene\t1\t9\t.\t+\t.\n")  # 8 columns
+    with pytest.raises(gffx.GffxError):
+        gffx.build_index(str(p))
+    p.write_bytes(b"chr1\tsrc\tgene\t1\t9\t.\t+\t.\tName=x\n")  # no ID
+    with pytest.raises(gffx.GffxError):
+        gffx.build_index(str(p))
+    with pytest.raises(gffx.GffxError):
+        gffx.build_index(str(tmp_path / "missing.gff"))
