@@ -292,7 +292,14 @@ class TreeIndexData:
         return C.string_at(p, n.value) if p else b""
 
     # -- synthetic workloads --------------------------------------------------------------
-    def synth_regions(self, seed: int, n: int, length: int, first: int = 0):
+    def synth_regions(self, seed: int, n: int, length: int, first: int = 0, out=None):
+        """regions [first, first+n) of the counter-based stream `seed`; `out` = three 4-byte host tensors
+        (e.g. pinned torch tensors) to fill in place instead of fresh numpy arrays"""
+        if out is not None:
+            if any(int(t.numel()) != n or t.element_size() != 4 or t.is_cuda for t in out):
+                raise ValueError("out must be three host tensors of n 4-byte elements")
+            _check(lib.gffx_synth_regions_host(self._h, seed, first, n, length, *(t.data_ptr() for t in out)))
+            return tuple(out)
         out = [np.empty(n, dtype=np.uint32) for _ in range(3)]
         _check(lib.gffx_synth_regions_host(self._h, seed, first, n, length, *(a.ctypes.data for a in out)))
         return tuple(out)
