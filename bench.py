@@ -182,6 +182,7 @@ def workload_config(args, idx, q):
 # read once, every output written once; re-reads and scan passes the implementation adds are NOT credited)
 def stage_table(q, p, l_sel, e_out):
     return {
+        8: ("window partition (hist + scan + scatter)", 0),  # an implementation pass: no algorithmic bytes credited
         0: ("join_count_kernel", 12 * q),                  # regions (3 x u32) read once
         7: ("join_emit_kernel", 12 * p),                   # pairs (3 x u32) written once; its re-read of the regions is not credited
         1: ("tile-offset scan (3 launches)", 0),
@@ -232,14 +233,14 @@ def run_gpu(args, rank, world, local_rank):
         for (name, mode, inv), regs in zip(PASSES, sets):
             r = idx.intersect(regs, mode, inv, False, None, flags=flags)
             if acc is not None:
-                a = acc.setdefault(name, {"calls": 0, "pairs": 0, "ranges": 0, "roots": 0, "launches": 0, "kernel_ms": 0.0, "stage_ms": [0.0] * 8})
+                a = acc.setdefault(name, {"calls": 0, "pairs": 0, "ranges": 0, "roots": 0, "launches": 0, "kernel_ms": 0.0, "stage_ms": [0.0] * 12})
                 a["calls"] += 1
                 a["pairs"] += r.n_pairs
                 a["ranges"] += r.n_ranges
                 a["roots"] += r.n_roots
                 a["launches"] += r.launches
                 a["kernel_ms"] += r.kernel_ms
-                for s in range(8):
+                for s in range(12):
                     a["stage_ms"][s] += r.stage_ms[s]
 
     # ---- device-resident arm: K steps between two events on the engine's stream --------------------

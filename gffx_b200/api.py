@@ -104,7 +104,7 @@ def _take_result(h) -> Result:
         if nw:
             r.warn_fids = list(np.ctypeslib.as_array(lib.gffx_result_warn_fids(h), shape=(nw,)))
         r.kernel_ms = lib.gffx_result_kernel_ms(h)
-        r.stage_ms = tuple(lib.gffx_result_stage_ms(h, k) for k in range(8))
+        r.stage_ms = tuple(lib.gffx_result_stage_ms(h, k) for k in range(12))
         r.launches = lib.gffx_result_launches(h)
         return r
     finally:

@@ -200,7 +200,7 @@ uint64_t gffx_result_n_warn(const gffx_result* r) { return r ? r->r.warn_fids.si
 const uint32_t* gffx_result_warn_fids(const gffx_result* r) { return r && !r->r.warn_fids.empty() ? r->r.warn_fids.data() : nullptr; }
 double gffx_result_kernel_ms(const gffx_result* r) { return r ? r->r.kernel_ms : 0; }
 uint32_t gffx_result_launches(const gffx_result* r) { return r ? r->r.launches : 0; }
-double gffx_result_stage_ms(const gffx_result* r, int stage) { return (r && stage >= 0 && stage < 8) ? r->r.stage_ms[stage] : 0; }
+double gffx_result_stage_ms(const gffx_result* r, int stage) { return (r && stage >= 0 && stage < 12) ? r->r.stage_ms[stage] : 0; }
 void gffx_result_free(gffx_result* r) { delete r; }
 
 int gffx_write_ranges(const gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, const char* out_path) {

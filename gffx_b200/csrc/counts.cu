@@ -159,12 +159,14 @@ void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, 
     GFFX_CUDA(cudaSetDevice(E->dev));
     const uint32_t *dc, *ds, *de;
     E->stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
-    const bool aligned = (((uintptr_t)dc | (uintptr_t)ds | (uintptr_t)de) & 15) == 0;
     const CountsDev D = make_dev(E, C);
     const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
     GFFX_CUDA(cudaEventRecord(C->ev0, E->st));
-    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, dc, ds, de, n, aligned, C->d_err.as<uint32_t>());
-    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, dc, ds, de, n, aligned, C->d_err.as<uint32_t>());
+    const uint32_t* bc = nullptr;  // K0: window-bucketed regions keep every look-up below in L1
+    const uint2* bse = nullptr;
+    C->launches += E->partition(dc, ds, de, n, &bc, &bse);
+    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, C->d_err.as<uint32_t>());
+    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, C->d_err.as<uint32_t>());
     GFFX_CUDA(cudaEventRecord(C->ev1, E->st));
     GFFX_CUDA(cudaMemcpyAsync(E->h_small, C->d_err.p, 4, cudaMemcpyDeviceToHost, E->st));
     GFFX_CUDA(cudaStreamSynchronize(E->st));

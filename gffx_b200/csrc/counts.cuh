@@ -88,12 +88,12 @@ __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp
 // counting commands drop them: depth.rs:488, coverage.rs:253).
 template <int KIND>
 __global__ void __launch_bounds__(JOIN_THREADS)
-    counts_scatter_kernel(CountsDev D, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
-                          uint64_t n, bool aligned, uint32_t* __restrict__ err) {
+    counts_scatter_kernel(CountsDev D, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n,
+                          uint32_t* __restrict__ err) {
     const uint64_t q0 = (uint64_t)blockIdx.x * JOIN_TILE + (uint64_t)threadIdx.x * JOIN_QPT;
     if (q0 >= n) return;
     Query4 Q;
-    load_queries(chr, qs, qe, n, q0, aligned, Q);
+    load_queries(chr, se, n, q0, Q);
 #pragma unroll
     for (int k = 0; k < JOIN_QPT; k++) {
         if (k >= Q.n) continue;

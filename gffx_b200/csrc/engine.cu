@@ -41,8 +41,10 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_win0, &d_poff, &d_prank, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
+    build_windows();
     build_join();
     build_blocks();
     build_lines();
@@ -57,6 +59,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_win0, &d_poff, &d_prank, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
     dj.release();
@@ -64,6 +67,58 @@ EngineImpl::~EngineImpl() {
     if (h_small) cudaFreeHost(h_small);
     for (auto& x : ev) cudaEventDestroy(x);
     if (st) cudaStreamDestroy(st);
+}
+
+// Window grid of the partition pass (partition.cuh): windows of 2^shift bases over each sequence's extent
+// (largest root end), the finest grid with at most PART_MAX_WINDOWS windows.  Windows are a locality device
+// only: a region that starts beyond the extent falls into the sequence's last window.
+void EngineImpl::build_windows() {
+    const size_t n_seqs = H->seq_names.size();
+    std::vector<uint32_t> extent(n_seqs, 0);
+    for (const auto& r : H->roots) extent[r.seq] = std::max(extent[r.seq], r.end);
+    uint32_t shift = 12;
+    for (;; shift++) {
+        uint64_t tot = 0;
+        for (size_t s = 0; s < n_seqs; s++) tot += ((uint64_t)extent[s] >> shift) + 1;
+        if (tot <= PART_MAX_WINDOWS || shift == 31) break;
+    }
+    h_win0.assign(n_seqs + 1, 0);
+    for (size_t s = 0; s < n_seqs; s++) h_win0[s + 1] = h_win0[s] + (uint32_t)(((uint64_t)extent[s] >> shift) + 1);
+    if (h_win0[n_seqs] > PART_MAX_WINDOWS) throw Err(E_ARG, "index has more sequences than the partition pass supports (4095)");
+    upload(d_win0, h_win0, st);
+    WG.win0 = d_win0.as<uint32_t>();
+    WG.n_seqs = (uint32_t)n_seqs;
+    WG.shift = shift;
+    WG.n_win = h_win0[n_seqs];
+    d_poff.ensure(((size_t)WG.n_win + 2) * 4);
+    GFFX_CUDA(cudaStreamSynchronize(st));
+}
+
+uint32_t EngineImpl::partition(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, const uint32_t** bchr,
+                               const uint2** bse) {
+    *bchr = nullptr; *bse = nullptr;
+    if (n == 0) return 0;
+    if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
+    const uint32_t nb = WG.n_win + 1;
+    const unsigned tiles = (unsigned)((n + PART_TILE - 1) / PART_TILE);
+    const uint64_t cells = (uint64_t)nb * tiles;
+    d_bchr.ensure(n * 4 + 16);
+    d_bse.ensure(n * 8 + 32);
+    d_prank.ensure(n * 2);
+    d_pmat.ensure(cells * 4);
+    d_pscan.ensure(cells * 4);
+    d_pscratch.ensure(scan_scratch_elems(cells) * 4);
+    const size_t smem = (size_t)nb * 4;
+    part_rank_kernel<<<tiles, PART_THREADS, smem, st>>>(WG, dc, ds, (uint32_t)n, tiles, d_prank.as<uint16_t>(), d_pmat.as<uint32_t>());
+    uint32_t launches = 1;
+    launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, false>(
+        PtrLoad<uint32_t>{d_pmat.as<uint32_t>()}, PtrStore<uint32_t>{d_pscan.as<uint32_t>()}, cells, OpSum(), 0u, d_pscratch.as<uint32_t>(), nullptr, st);
+    part_scatter_kernel<<<tiles, PART_THREADS, smem, st>>>(WG, dc, ds, de, (uint32_t)n, tiles, d_prank.as<uint16_t>(), d_pscan.as<uint32_t>(),
+                                                            d_bchr.as<uint32_t>(), d_bse.as<uint2>());
+    part_offsets_kernel<<<(nb + 1 + 255) / 256, 256, 0, st>>>(d_pscan.as<uint32_t>(), nb, tiles, (uint32_t)n, d_poff.as<uint32_t>());
+    *bchr = d_bchr.as<uint32_t>();
+    *bse = d_bse.as<uint2>();
+    return launches + 2;
 }
 
 // Join index over the root intervals (see join_build.h / join.cuh).
@@ -208,15 +263,13 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
 }
 
 template <int MODE, bool INV>
-static void launch_join_count(EngineImpl* E, const uint32_t* c, const uint32_t* s, const uint32_t* e, uint64_t n, bool aligned,
-                              unsigned tiles, uint32_t* err) {
-    join_count_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, s, e, n, aligned, E->d_ent_hit.as<uint8_t>(),
+static void launch_join_count(EngineImpl* E, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles, uint32_t* err) {
+    join_count_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, se, n, E->d_ent_hit.as<uint8_t>(),
                                                                    E->d_tile_count.as<uint32_t>(), err);
 }
 template <int MODE, bool INV>
-static void launch_join_emit(EngineImpl* E, const uint32_t* c, const uint32_t* s, const uint32_t* e, uint64_t n, bool aligned,
-                             unsigned tiles) {
-    join_emit_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, s, e, n, aligned, E->d_tile_off.as<uint64_t>(),
+static void launch_join_emit(EngineImpl* E, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles) {
+    join_emit_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, se, n, E->d_tile_off.as<uint64_t>(),
                                                                   E->d_pairs.as<uint32_t>());
 }
 
@@ -233,14 +286,17 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     bool emitted = false;
     const uint32_t *dc, *ds, *de;
     stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
-    const bool aligned = (((uintptr_t)dc | (uintptr_t)ds | (uintptr_t)de) & 15) == 0;
     unsigned long long* small = d_small.as<unsigned long long>();  // [0] n_pairs [1..3] merge counts [4] bytes_out [5] n_emit (u64); u32 view: [12] err [13] n_warn
     uint32_t* small32 = d_small.as<uint32_t>();
     GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 256, st));
     GFFX_CUDA(cudaEventRecord(ev[0], st));
+    const bool nothing = (mode == 2 && invert) || n == 0 || n_ent == 0;  // -I with overlap selects nothing (intersect.rs:161)
+    const uint32_t* bc = nullptr;  // window-bucketed regions (partition.cuh)
+    const uint2* bse = nullptr;
+    if (!nothing) launches += partition(dc, ds, de, n, &bc, &bse);
+    GFFX_CUDA(cudaEventRecord(ev[10], st));
 
     // ---- stage 0: join ---------------------------------------------------------------------
-    const bool nothing = (mode == 2 && invert) || n == 0 || n_ent == 0;  // -I with overlap selects nothing (intersect.rs:161)
     const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
     if (n_ent) GFFX_CUDA(cudaMemsetAsync(d_ent_hit.p, 0, n_ent, st));
     if (!nothing) {
@@ -249,11 +305,11 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
         d_scan_scratch.ensure(scan_scratch_elems(std::max<uint64_t>(tiles, LA.n / LINE_THREADS + 1)) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
         uint32_t* err = small32 + 12;
         switch (mode * 2 + (invert ? 1 : 0)) {
-            case 0: launch_join_count<0, false>(this, dc, ds, de, n, aligned, tiles, err); break;
-            case 1: launch_join_count<0, true>(this, dc, ds, de, n, aligned, tiles, err); break;
-            case 2: launch_join_count<1, false>(this, dc, ds, de, n, aligned, tiles, err); break;
-            case 3: launch_join_count<1, true>(this, dc, ds, de, n, aligned, tiles, err); break;
-            default: launch_join_count<2, false>(this, dc, ds, de, n, aligned, tiles, err); break;
+            case 0: launch_join_count<0, false>(this, bc, bse, n, tiles, err); break;
+            case 1: launch_join_count<0, true>(this, bc, bse, n, tiles, err); break;
+            case 2: launch_join_count<1, false>(this, bc, bse, n, tiles, err); break;
+            case 3: launch_join_count<1, true>(this, bc, bse, n, tiles, err); break;
+            default: launch_join_count<2, false>(this, bc, bse, n, tiles, err); break;
         }
         launches++;
         GFFX_CUDA(cudaEventRecord(ev[1], st));
@@ -270,11 +326,11 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             emitted = true;
             GFFX_CUDA(cudaEventRecord(ev[8], st));
             switch (mode * 2 + (invert ? 1 : 0)) {
-                case 0: launch_join_emit<0, false>(this, dc, ds, de, n, aligned, tiles); break;
-                case 1: launch_join_emit<0, true>(this, dc, ds, de, n, aligned, tiles); break;
-                case 2: launch_join_emit<1, false>(this, dc, ds, de, n, aligned, tiles); break;
-                case 3: launch_join_emit<1, true>(this, dc, ds, de, n, aligned, tiles); break;
-                default: launch_join_emit<2, false>(this, dc, ds, de, n, aligned, tiles); break;
+                case 0: launch_join_emit<0, false>(this, bc, bse, n, tiles); break;
+                case 1: launch_join_emit<0, true>(this, bc, bse, n, tiles); break;
+                case 2: launch_join_emit<1, false>(this, bc, bse, n, tiles); break;
+                case 3: launch_join_emit<1, true>(this, bc, bse, n, tiles); break;
+                default: launch_join_emit<2, false>(this, bc, bse, n, tiles); break;
             }
             GFFX_CUDA(cudaEventRecord(ev[9], st));
             launches++;
@@ -294,8 +350,11 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
                                                                  d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
         launches++;
         if (n_blocks) {
-            merge_blocks_kernel<<<1, 1024, 0, st>>>(d_bstart.as<uint64_t>(), d_bend.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks,
-                                                   H->gff_len, !match_only && !join_only, d_ranges.as<ulonglong2>(), small + 1);
+            if (!match_only && !join_only)
+                merge_blocks_kernel<<<1, 1024, 0, st>>>(d_bstart.as<uint64_t>(), d_bend.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks,
+                                                       H->gff_len, true, d_ranges.as<ulonglong2>(), small + 1);
+            else
+                count_selected_kernel<<<(n_blocks + 255) / 256, 256, 0, st>>>(d_bstart.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks, small + 1);
             launches++;
         }
     }
@@ -333,9 +392,9 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
         }
         const unsigned sblocks = (unsigned)((n + (uint64_t)FILT_THREADS * FILT_QPT - 1) / ((uint64_t)FILT_THREADS * FILT_QPT));
-        if (mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
-        else if (mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
-        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, dc, ds, de, n, aligned);
+        if (mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n);
+        else if (mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n);
+        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n);
         launches++;
         GFFX_CUDA(cudaEventRecord(ev[5], st));
 
@@ -422,6 +481,10 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
         GFFX_CUDA(cudaEventElapsedTime(&ms, ev[8], ev[9]));
         out->stage_ms[7] = ms;
     }
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[10]));
+    out->stage_ms[8] = ms;
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[10], ev[1]));
+    out->stage_ms[0] = ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[7]));
     out->kernel_ms = ms;
     out->launches = launches;

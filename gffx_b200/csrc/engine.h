@@ -17,7 +17,7 @@ struct IntersectResult {
     uint64_t bytes_out = 0;
     std::vector<uint32_t> warn_fids;
     double kernel_ms = 0;
-    double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    double stage_ms[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     uint32_t launches = 0;
 };
 

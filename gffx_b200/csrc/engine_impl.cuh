@@ -5,6 +5,7 @@
 #include "filter.cuh"
 #include "join.cuh"
 #include "join_build.h"
+#include "partition.cuh"
 
 namespace gffx {
 
@@ -100,16 +101,22 @@ class EngineImpl {
     LineArrays LA{};
     DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_type_allow;
 
+    // ---- window grid + partition scratch (partition.cuh) --------------------------------------
+    DBuf d_win0, d_poff, d_prank, d_pmat, d_pscan, d_pscratch, d_bchr, d_bse;
+    std::vector<uint32_t> h_win0;
+    WinGrid WG{};
+
     // ---- per-call scratch --------------------------------------------------------------------
     DBuf d_q[3], d_tile_count, d_tile_off, d_scan_scratch, d_pairs, d_ranges, d_small, d_warn;
     void* h_small = nullptr;  // pinned, 256 B
-    cudaEvent_t ev[10];  // [0..7] stage boundaries of one intersect call, [8],[9] around the join emit kernel alone
+    cudaEvent_t ev[12];  // [0..7] stage boundaries of one intersect call, [8],[9] around the join emit kernel alone, [10] end of the partition pass
 
     // ---- counts (depth / coverage) -----------------------------------------------------------
     CountsState* counts = nullptr;  // owned; freed by counts_release()
 
     EngineImpl(std::unique_ptr<HostIndex> host, int device);
     ~EngineImpl();
+    void build_windows();
     void build_join();
     void build_blocks();
     void build_lines();
@@ -118,6 +125,9 @@ class EngineImpl {
     // stage the regions on the device; returns device pointers (either the caller's or the staging buffers)
     void stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                        const uint32_t** dc, const uint32_t** ds, const uint32_t** de);
+    // K0: bucket n (< 2^31) device-resident regions by window; returns the bucketed arrays (engine-owned
+    // scratch, valid until the next call) and the number of kernels launched
+    uint32_t partition(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, const uint32_t** bchr, const uint2** bse);
 };
 
 // counts.cu

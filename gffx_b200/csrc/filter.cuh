@@ -78,23 +78,22 @@ struct FilterArrays {
 // one streaming pass over the regions (12 B read per region, 1-3 scattered L2 updates)
 template <int MODE>
 __global__ void __launch_bounds__(FILT_THREADS)
-    scatter_regions_kernel(RankSpace R, FilterArrays F, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs,
-                           const uint32_t* __restrict__ qe, uint64_t n, bool aligned) {
+    scatter_regions_kernel(RankSpace R, FilterArrays F, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n) {
     const uint64_t q0 = ((uint64_t)blockIdx.x * FILT_THREADS + threadIdx.x) * FILT_QPT;
     if (q0 >= n) return;
     uint32_t c[FILT_QPT], s[FILT_QPT], e[FILT_QPT];
     int m = 0;
-    if (q0 + FILT_QPT <= n && aligned) {
+    if (q0 + FILT_QPT <= n) {
         const uint4 a = __ldcs(reinterpret_cast<const uint4*>(chr + q0));
-        const uint4 b = __ldcs(reinterpret_cast<const uint4*>(qs + q0));
-        const uint4 d = __ldcs(reinterpret_cast<const uint4*>(qe + q0));
+        const uint4 b = __ldcs(reinterpret_cast<const uint4*>(se + q0));
+        const uint4 d = __ldcs(reinterpret_cast<const uint4*>(se + q0) + 1);
         c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w;
-        s[0] = b.x; s[1] = b.y; s[2] = b.z; s[3] = b.w;
-        e[0] = d.x; e[1] = d.y; e[2] = d.z; e[3] = d.w;
+        s[0] = b.x; e[0] = b.y; s[1] = b.z; e[1] = b.w;
+        s[2] = d.x; e[2] = d.y; s[3] = d.z; e[3] = d.w;
         m = FILT_QPT;
     } else {
         for (int k = 0; k < FILT_QPT; k++)
-            if (q0 + k < n) { c[k] = chr[q0 + k]; s[k] = qs[q0 + k]; e[k] = qe[q0 + k]; m = k + 1; }
+            if (q0 + k < n) { const uint2 v = se[q0 + k]; c[k] = chr[q0 + k]; s[k] = v.x; e[k] = v.y; m = k + 1; }
     }
 #pragma unroll
     for (int k = 0; k < FILT_QPT; k++) {
@@ -209,6 +208,19 @@ static __global__ void __launch_bounds__(LINE_THREADS)
     unsigned long long btot;
     block_scan_excl(len, OpSum(), 0ull, sb, &btot);
     if (threadIdx.x == 0 && btot) atomicAdd(bytes_out, btot);
+}
+
+// number of selected blocks with a usable start (what merge_blocks_kernel reports as out_counts[1]) when no
+// merged ranges are wanted: the match-only path and join-only calls
+static __global__ void __launch_bounds__(256)
+    count_selected_kernel(const uint64_t* __restrict__ bstart, const uint8_t* __restrict__ blk_sel, uint32_t n_blocks,
+                          unsigned long long* __restrict__ out_counts) {
+    __shared__ uint32_t sm[256 / 32 + 1];
+    const uint32_t b = blockIdx.x * 256 + threadIdx.x;
+    const uint32_t k = (b < n_blocks && blk_sel[b] && bstart[b] != 0xFFFFFFFFFFFFFFFFull) ? 1u : 0u;
+    uint32_t tot;
+    block_scan_excl(k, OpSum(), 0u, sm, &tot);
+    if (threadIdx.x == 0 && tot) atomicAdd(out_counts + 1, (unsigned long long)tot);
 }
 
 // K5, one CTA: selected blocks (sorted by start) -> merged byte ranges, rules of common.rs:199-245:

@@ -69,23 +69,25 @@ struct Query4 {
     int n;
 };
 
-// thread t of tile `tile` owns queries [tile*JOIN_TILE + t*4, +4)
-__device__ __forceinline__ void load_queries(const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs,
-                                             const uint32_t* __restrict__ qe, uint64_t n, uint64_t q0, bool aligned, Query4& Q) {
-    if (q0 + JOIN_QPT <= n && aligned) {
+// thread t of tile `tile` owns queries [tile*JOIN_TILE + t*4, +4) of the window-bucketed arrays
+// (partition.cuh: chr[] and (start,end)[]; cudaMalloc'ed, so the vector loads are aligned)
+__device__ __forceinline__ void load_queries(const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n, uint64_t q0,
+                                             Query4& Q) {
+    if (q0 + JOIN_QPT <= n) {
         const uint4 c = __ldcs(reinterpret_cast<const uint4*>(chr + q0));
-        const uint4 s = __ldcs(reinterpret_cast<const uint4*>(qs + q0));
-        const uint4 e = __ldcs(reinterpret_cast<const uint4*>(qe + q0));
+        const uint4 a = __ldcs(reinterpret_cast<const uint4*>(se + q0));
+        const uint4 b = __ldcs(reinterpret_cast<const uint4*>(se + q0) + 1);
         Q.c[0] = c.x; Q.c[1] = c.y; Q.c[2] = c.z; Q.c[3] = c.w;
-        Q.s[0] = s.x; Q.s[1] = s.y; Q.s[2] = s.z; Q.s[3] = s.w;
-        Q.e[0] = e.x; Q.e[1] = e.y; Q.e[2] = e.z; Q.e[3] = e.w;
+        Q.s[0] = a.x; Q.e[0] = a.y; Q.s[1] = a.z; Q.e[1] = a.w;
+        Q.s[2] = b.x; Q.e[2] = b.y; Q.s[3] = b.z; Q.e[3] = b.w;
         Q.n = JOIN_QPT;
     } else {
         Q.n = 0;
 #pragma unroll
         for (int k = 0; k < JOIN_QPT; k++)
             if (q0 + k < n) {
-                Q.c[k] = chr[q0 + k]; Q.s[k] = qs[q0 + k]; Q.e[k] = qe[q0 + k];
+                const uint2 v = se[q0 + k];
+                Q.c[k] = chr[q0 + k]; Q.s[k] = v.x; Q.e[k] = v.y;
                 Q.n = k + 1;
             }
     }
@@ -93,14 +95,14 @@ __device__ __forceinline__ void load_queries(const uint32_t* __restrict__ chr, c
 
 template <int MODE, bool INVERT>
 __global__ void __launch_bounds__(JOIN_THREADS)
-    join_count_kernel(JoinIndex J, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
-                      uint64_t n, bool aligned, uint8_t* __restrict__ ent_hit, uint32_t* __restrict__ tile_count,
+    join_count_kernel(JoinIndex J, const uint32_t* __restrict__ chr, const uint2* __restrict__ se,
+                      uint64_t n, uint8_t* __restrict__ ent_hit, uint32_t* __restrict__ tile_count,
                       uint32_t* __restrict__ err) {
     __shared__ uint32_t sm[JOIN_THREADS / 32 + 1];
     const uint64_t q0 = (uint64_t)blockIdx.x * JOIN_TILE + (uint64_t)threadIdx.x * JOIN_QPT;
     Query4 Q;
     Q.n = 0;
-    if (q0 < n) load_queries(chr, qs, qe, n, q0, aligned, Q);
+    if (q0 < n) load_queries(chr, se, n, q0, Q);
     uint32_t cnt = 0;
 #pragma unroll
     for (int k = 0; k < JOIN_QPT; k++) {
@@ -108,7 +110,8 @@ __global__ void __launch_bounds__(JOIN_THREADS)
             if (Q.c[k] >= J.n_seqs) { *err = 1; continue; }
             join_query<MODE, INVERT>(J, Q.c[k], Q.s[k], Q.e[k], [&](uint32_t j, uint2) {
                 cnt++;
-                ent_hit[j] = 1;
+                // ~230 regions hit every root: test in L2 first so that the byte is stored O(1) times, not O(hits)
+                if (!__ldcg(ent_hit + j)) ent_hit[j] = 1;
             });
         }
     }
@@ -119,14 +122,14 @@ __global__ void __launch_bounds__(JOIN_THREADS)
 
 template <int MODE, bool INVERT>
 __global__ void __launch_bounds__(JOIN_THREADS)
-    join_emit_kernel(JoinIndex J, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
-                     uint64_t n, bool aligned, const uint64_t* __restrict__ tile_off, uint32_t* __restrict__ pairs) {
+    join_emit_kernel(JoinIndex J, const uint32_t* __restrict__ chr, const uint2* __restrict__ se,
+                     uint64_t n, const uint64_t* __restrict__ tile_off, uint32_t* __restrict__ pairs) {
     __shared__ uint32_t sm[JOIN_THREADS / 32 + 1];
     __shared__ uint32_t stage[JOIN_STAGE_PAIRS * 3];
     const uint64_t q0 = (uint64_t)blockIdx.x * JOIN_TILE + (uint64_t)threadIdx.x * JOIN_QPT;
     Query4 Q;
     Q.n = 0;
-    if (q0 < n) load_queries(chr, qs, qe, n, q0, aligned, Q);
+    if (q0 < n) load_queries(chr, se, n, q0, Q);
     uint32_t cnt = 0;
 #pragma unroll
     for (int k = 0; k < JOIN_QPT; k++)

@@ -152,7 +152,8 @@ double gffx_result_kernel_ms(const gffx_result* r);
 uint32_t gffx_result_launches(const gffx_result* r);
 /* per-stage device ms: 0 join count kernel, 1 tile-offset scan, 2 join emit kernel, 3 root/block select + merge,
  * 4 region scatter onto the line rank space, 5 rank scans, 6 line filter + compaction, 7 the join emit kernel alone
- * (stage 2 also holds the host read-back of the pair count); stages that did not run report 0 */
+ * (stage 2 also holds the host read-back of the pair count), 8 the window partition pass (hist + scan + scatter);
+ * stages that did not run report 0 */
 double gffx_result_stage_ms(const gffx_result* r, int stage);
 void gffx_result_free(gffx_result* r);
 
