@@ -183,9 +183,7 @@ def workload_config(args, idx, q):
 def stage_table(q, p, l_sel, e_out):
     return {
         8: ("window partition (hist + scan + scatter)", 0),  # an implementation pass: no algorithmic bytes credited
-        0: ("join_count_kernel", 12 * q),                  # regions (3 x u32) read once
-        7: ("join_emit_kernel", 12 * p),                   # pairs (3 x u32) written once; its re-read of the regions is not credited
-        1: ("tile-offset scan (3 launches)", 0),
+        0: ("wj_join_kernel", 12 * q + 12 * p),            # regions (3 x u32) read once, pairs (3 x u32) written once
         3: ("select_blocks + merge_blocks", 0),
         4: ("scatter_regions_kernel", 12 * q),             # regions read once by the line-filter stage
         5: ("rank-space scans", 0),

@@ -41,6 +41,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
                     &d_win0, &d_poff, &d_prank, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
@@ -59,6 +60,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
                     &d_win0, &d_poff, &d_prank, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
@@ -153,6 +155,38 @@ void EngineImpl::build_join() {
     upload(d_ent_blk, ent_blk, st);
     d_ent_hit.ensure(std::max<uint32_t>(n_ent, 1));
     GFFX_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
+
+    // the window-addressed form of the same intervals (winjoin.cuh), used by intersect
+    WinJoinHost wh;
+    build_win_join((uint32_t)n_seqs, items, h_win0, WG.shift, 8, 3, &wh);
+    std::vector<uint2> se(wh.n_entries()), ase(wh.alw_id.size());
+    for (size_t i = 0; i < se.size(); i++) se[i] = make_uint2(wh.ent_start[i], wh.ent_end[i]);
+    for (size_t i = 0; i < ase.size(); i++) ase[i] = make_uint2(wh.alw_start[i], wh.alw_end[i]);
+    std::vector<uint32_t> wblk(wh.n_entries());
+    for (size_t k = 0; k < wblk.size(); k++) wblk[k] = H->root_blk[wh.ent_item[k]];
+    upload(d_wj_send, wh.seq_send, st);
+    upload(d_wj_se, se, st);
+    upload(d_wj_fid, wh.ent_payload, st);
+    upload(d_wj_sdir, wh.sdir, st);
+    upload(d_wj_alw0, wh.alw0, st);
+    upload(d_wj_alwse, ase, st);
+    upload(d_wj_alwid, wh.alw_id, st);
+    upload(d_wj_blk, wblk, st);
+    wj_n_ent = (uint32_t)wh.n_entries();
+    d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    WJ.win0 = d_win0.as<uint32_t>();
+    WJ.seq_send = d_wj_send.as<uint32_t>();
+    WJ.ent_se = d_wj_se.as<uint2>();
+    WJ.ent_fid = d_wj_fid.as<uint32_t>();
+    WJ.sdir = d_wj_sdir.as<uint32_t>();
+    WJ.alw0 = d_wj_alw0.as<uint32_t>();
+    WJ.alw_se = d_wj_alwse.as<uint2>();
+    WJ.alw_id = d_wj_alwid.as<uint32_t>();
+    WJ.n_seqs = (uint32_t)n_seqs;
+    WJ.shift = wh.shift;
+    WJ.sub_bits = wh.sub_bits;
+    WJ.n_ent = wj_n_ent;
 }
 
 void EngineImpl::build_blocks() {
@@ -263,14 +297,23 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
 }
 
 template <int MODE, bool INV>
-static void launch_join_count(EngineImpl* E, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles, uint32_t* err) {
-    join_count_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, se, n, E->d_ent_hit.as<uint8_t>(),
-                                                                   E->d_tile_count.as<uint32_t>(), err);
+static void launch_wj(EngineImpl* E, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs,
+                      unsigned long long cap, uint32_t* err) {
+    if (emit)
+        wj_join_kernel<MODE, INV, true><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs,
+                                                                         E->d_pairs.as<uint32_t>(), cap, err);
+    else
+        wj_join_kernel<MODE, INV, false><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, nullptr, 0, err);
 }
-template <int MODE, bool INV>
-static void launch_join_emit(EngineImpl* E, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles) {
-    join_emit_kernel<MODE, INV><<<tiles, JOIN_THREADS, 0, E->st>>>(E->J, c, se, n, E->d_tile_off.as<uint64_t>(),
-                                                                  E->d_pairs.as<uint32_t>());
+static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles,
+                           unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
+    switch (mode * 2 + (invert ? 1 : 0)) {
+        case 0: launch_wj<0, false>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
+        case 1: launch_wj<0, true>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
+        case 2: launch_wj<1, false>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
+        case 3: launch_wj<1, true>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
+        default: launch_wj<2, false>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
+    }
 }
 
 void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
@@ -296,58 +339,29 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     if (!nothing) launches += partition(dc, ds, de, n, &bc, &bse);
     GFFX_CUDA(cudaEventRecord(ev[10], st));
 
-    // ---- stage 0: join ---------------------------------------------------------------------
-    const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
-    if (n_ent) GFFX_CUDA(cudaMemsetAsync(d_ent_hit.p, 0, n_ent, st));
+    // ---- stage 0: join (one fused kernel: search, CTA scan, tile range claim, staged emit) --------
+    const unsigned tiles = (unsigned)((n + WJ_TILE - 1) / WJ_TILE);
+    if (wj_n_ent) GFFX_CUDA(cudaMemsetAsync(d_wj_hit.p, 0, wj_n_ent, st));
+    unsigned long long pair_cap = 0;
     if (!nothing) {
-        d_tile_count.ensure((size_t)tiles * 4);
-        d_tile_off.ensure((size_t)tiles * 8);
-        d_scan_scratch.ensure(scan_scratch_elems(std::max<uint64_t>(tiles, LA.n / LINE_THREADS + 1)) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
-        uint32_t* err = small32 + 12;
-        switch (mode * 2 + (invert ? 1 : 0)) {
-            case 0: launch_join_count<0, false>(this, bc, bse, n, tiles, err); break;
-            case 1: launch_join_count<0, true>(this, bc, bse, n, tiles, err); break;
-            case 2: launch_join_count<1, false>(this, bc, bse, n, tiles, err); break;
-            case 3: launch_join_count<1, true>(this, bc, bse, n, tiles, err); break;
-            default: launch_join_count<2, false>(this, bc, bse, n, tiles, err); break;
+        d_scan_scratch.ensure(scan_scratch_elems(LA.n / LINE_THREADS + 1) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
+        if (pairs_dev) {
+            d_pairs.ensure(std::max<uint64_t>(2 * n, 1024) * 12);  // grow-only; a larger result re-runs the kernel below
+            pair_cap = d_pairs.cap / 12;
         }
+        launch_wj_mode(this, mode, invert, pairs_dev, bc, bse, n, tiles, small, pair_cap, small32 + 12);
         launches++;
-        GFFX_CUDA(cudaEventRecord(ev[1], st));
-        launches += device_scan<uint64_t, OpSum, TileCountLoad, PtrStore<uint64_t>, false, false>(
-            TileCountLoad{d_tile_count.as<uint32_t>()}, PtrStore<uint64_t>{d_tile_off.as<uint64_t>()}, tiles, OpSum(), 0ull,
-            d_scan_scratch.as<uint64_t>(), (uint64_t*)small, st);
-        GFFX_CUDA(cudaEventRecord(ev[2], st));
-        GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
-        GFFX_CUDA(cudaStreamSynchronize(st));
-        if (((uint32_t*)h_small)[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
-        out->n_pairs = ((uint64_t*)h_small)[0];
-        if (pairs_dev && out->n_pairs) {
-            d_pairs.ensure(out->n_pairs * 12);
-            emitted = true;
-            GFFX_CUDA(cudaEventRecord(ev[8], st));
-            switch (mode * 2 + (invert ? 1 : 0)) {
-                case 0: launch_join_emit<0, false>(this, bc, bse, n, tiles); break;
-                case 1: launch_join_emit<0, true>(this, bc, bse, n, tiles); break;
-                case 2: launch_join_emit<1, false>(this, bc, bse, n, tiles); break;
-                case 3: launch_join_emit<1, true>(this, bc, bse, n, tiles); break;
-                default: launch_join_emit<2, false>(this, bc, bse, n, tiles); break;
-            }
-            GFFX_CUDA(cudaEventRecord(ev[9], st));
-            launches++;
-            out->d_pairs = d_pairs.as<uint32_t>();
-        }
-    } else {
-        GFFX_CUDA(cudaEventRecord(ev[1], st));
-        GFFX_CUDA(cudaEventRecord(ev[2], st));
     }
+    GFFX_CUDA(cudaEventRecord(ev[1], st));
+    GFFX_CUDA(cudaEventRecord(ev[2], st));
     GFFX_CUDA(cudaEventRecord(ev[3], st));
 
     // ---- stage 1: root -> block selection, merged ranges (-e) ---------------------------------
     const bool match_only = !entire_group || types_csv != nullptr;  // intersect.rs:619
     if (n_blocks) GFFX_CUDA(cudaMemsetAsync(d_blk_sel.p, 0, n_blocks, st));
     if (!nothing) {
-        select_blocks_kernel<<<(n_ent + 255) / 256, 256, 0, st>>>(d_ent_hit.as<uint8_t>(), d_ent_blk.as<uint32_t>(), J.ent_fid, n_ent,
-                                                                 d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
+        wj_select_blocks_kernel<<<(wj_n_ent + 255) / 256, 256, 0, st>>>(d_wj_hit.as<uint8_t>(), d_wj_blk.as<uint32_t>(), WJ.ent_fid, wj_n_ent,
+                                                                       d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
         launches++;
         if (n_blocks) {
             if (!match_only && !join_only)
@@ -450,6 +464,19 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     }
     const uint64_t* hs = (const uint64_t*)h_small;
     const uint32_t* hs32 = (const uint32_t*)h_small;
+    if (hs32[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
+    out->n_pairs = hs[0];
+    if (pairs_dev && out->n_pairs > pair_cap) {
+        // the pair buffer was too small for this result: grow it to the exact size and run the join again
+        // (hit flags are idempotent; only the pair counter restarts)
+        d_pairs.ensure(out->n_pairs * 12);
+        GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 8, st));
+        launch_wj_mode(this, mode, invert, true, bc, bse, n, tiles, small, d_pairs.cap / 12, small32 + 12);
+        launches++;
+        GFFX_CUDA(cudaStreamSynchronize(st));
+        GFFX_CUDA(cudaGetLastError());
+    }
+    if (pairs_dev && out->n_pairs) { out->d_pairs = d_pairs.as<uint32_t>(); emitted = true; }
     const uint32_t n_warn = std::min<uint32_t>(hs32[13], WARN_CAP);
     if (n_warn) {
         std::vector<uint32_t> w(n_warn);
@@ -477,14 +504,12 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
         GFFX_CUDA(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
         out->stage_ms[k] = ms;
     }
-    if (emitted) {
-        GFFX_CUDA(cudaEventElapsedTime(&ms, ev[8], ev[9]));
-        out->stage_ms[7] = ms;
-    }
+    (void)emitted;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[10]));
     out->stage_ms[8] = ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[10], ev[1]));
     out->stage_ms[0] = ms;
+    if (pairs_dev) out->stage_ms[7] = ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[7]));
     out->kernel_ms = ms;
     out->launches = launches;

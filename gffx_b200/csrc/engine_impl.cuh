@@ -6,6 +6,8 @@
 #include "join.cuh"
 #include "join_build.h"
 #include "partition.cuh"
+#include "winjoin.cuh"
+#include "winjoin_build.h"
 
 namespace gffx {
 
@@ -88,6 +90,11 @@ class EngineImpl {
     uint32_t n_ent = 0;
     JoinIndex J{};
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
+
+    // ---- window-addressed root join (winjoin.cuh): what intersect uses -------------------------
+    DBuf d_wj_send, d_wj_se, d_wj_fid, d_wj_sdir, d_wj_alw0, d_wj_alwse, d_wj_alwid, d_wj_blk, d_wj_hit;
+    WinJoin WJ{};
+    uint32_t wj_n_ent = 0;
 
     // ---- blocks ------------------------------------------------------------------------------
     DBuf d_bstart, d_bend, d_blk_sel;
