@@ -41,8 +41,8 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
-                    &d_win0, &d_poff, &d_prank, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
+                    &d_wj_win0, &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
+                    &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
     build_windows();
@@ -60,8 +60,8 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
-                    &d_win0, &d_poff, &d_prank, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
+                    &d_wj_win0, &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
+                    &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
     dj.release();
@@ -78,21 +78,24 @@ void EngineImpl::build_windows() {
     const size_t n_seqs = H->seq_names.size();
     std::vector<uint32_t> extent(n_seqs, 0);
     for (const auto& r : H->roots) extent[r.seq] = std::max(extent[r.seq], r.end);
+    uint64_t max_win = PART_MAX_WINDOWS;
+    if (const char* e = getenv("GFFX_MAX_WINDOWS")) max_win = std::min<uint64_t>(PART_MAX_WINDOWS, std::max<uint64_t>(n_seqs, strtoull(e, nullptr, 10)));
     uint32_t shift = 12;
     for (;; shift++) {
         uint64_t tot = 0;
         for (size_t s = 0; s < n_seqs; s++) tot += ((uint64_t)extent[s] >> shift) + 1;
-        if (tot <= PART_MAX_WINDOWS || shift == 31) break;
+        if (tot <= max_win || shift == 31) break;
     }
     h_win0.assign(n_seqs + 1, 0);
     for (size_t s = 0; s < n_seqs; s++) h_win0[s + 1] = h_win0[s] + (uint32_t)(((uint64_t)extent[s] >> shift) + 1);
-    if (h_win0[n_seqs] > PART_MAX_WINDOWS) throw Err(E_ARG, "index has more sequences than the partition pass supports (4095)");
+    if (h_win0[n_seqs] > PART_MAX_WINDOWS) throw Err(E_ARG, "index has more sequences than the partition pass supports (511)");
     upload(d_win0, h_win0, st);
     WG.win0 = d_win0.as<uint32_t>();
     WG.n_seqs = (uint32_t)n_seqs;
     WG.shift = shift;
     WG.n_win = h_win0[n_seqs];
     d_poff.ensure(((size_t)WG.n_win + 2) * 4);
+    GFFX_CUDA(cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PART_SCATTER_SMEM));
     GFFX_CUDA(cudaStreamSynchronize(st));
 }
 
@@ -106,17 +109,15 @@ uint32_t EngineImpl::partition(const uint32_t* dc, const uint32_t* ds, const uin
     const uint64_t cells = (uint64_t)nb * tiles;
     d_bchr.ensure(n * 4 + 16);
     d_bse.ensure(n * 8 + 32);
-    d_prank.ensure(n * 2);
     d_pmat.ensure(cells * 4);
     d_pscan.ensure(cells * 4);
     d_pscratch.ensure(scan_scratch_elems(cells) * 4);
-    const size_t smem = (size_t)nb * 4;
-    part_rank_kernel<<<tiles, PART_THREADS, smem, st>>>(WG, dc, ds, (uint32_t)n, tiles, d_prank.as<uint16_t>(), d_pmat.as<uint32_t>());
+    part_count_kernel<<<tiles, PART_THREADS, 0, st>>>(WG, dc, ds, (uint32_t)n, tiles, d_pmat.as<uint32_t>());
     uint32_t launches = 1;
     launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, false>(
         PtrLoad<uint32_t>{d_pmat.as<uint32_t>()}, PtrStore<uint32_t>{d_pscan.as<uint32_t>()}, cells, OpSum(), 0u, d_pscratch.as<uint32_t>(), nullptr, st);
-    part_scatter_kernel<<<tiles, PART_THREADS, smem, st>>>(WG, dc, ds, de, (uint32_t)n, tiles, d_prank.as<uint16_t>(), d_pscan.as<uint32_t>(),
-                                                            d_bchr.as<uint32_t>(), d_bse.as<uint2>());
+    part_scatter_kernel<<<tiles, PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, tiles, d_pmat.as<uint32_t>(), d_pscan.as<uint32_t>(),
+                                                         d_bchr.as<uint32_t>(), d_bse.as<uint2>());
     part_offsets_kernel<<<(nb + 1 + 255) / 256, 256, 0, st>>>(d_pscan.as<uint32_t>(), nb, tiles, (uint32_t)n, d_poff.as<uint32_t>());
     *bchr = d_bchr.as<uint32_t>();
     *bse = d_bse.as<uint2>();
@@ -157,8 +158,23 @@ void EngineImpl::build_join() {
     GFFX_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
 
     // the window-addressed form of the same intervals (winjoin.cuh), used by intersect
+    // its own fine grid (<= 16384 windows): the partition grid is coarse for store efficiency, the join kernel
+    // sorts each tile again by these windows in shared memory
+    std::vector<uint32_t> jwin0(n_seqs + 1, 0);
+    uint32_t jshift = 10;
+    {
+        std::vector<uint32_t> extent(n_seqs, 0);
+        for (const auto& r : R) extent[r.seq] = std::max(extent[r.seq], r.end);
+        for (;; jshift++) {
+            uint64_t tot = 0;
+            for (size_t s = 0; s < n_seqs; s++) tot += ((uint64_t)extent[s] >> jshift) + 1;
+            if (tot <= std::max<uint64_t>(16384, 2 * n_seqs) || jshift == 31) break;
+        }
+        for (size_t s = 0; s < n_seqs; s++) jwin0[s + 1] = jwin0[s] + (uint32_t)(((uint64_t)extent[s] >> jshift) + 1);
+    }
     WinJoinHost wh;
-    build_win_join((uint32_t)n_seqs, items, h_win0, WG.shift, 8, 3, &wh);
+    build_win_join((uint32_t)n_seqs, items, jwin0, jshift, 8, 3, &wh);
+    upload(d_wj_win0, jwin0, st);
     std::vector<uint2> se(wh.n_entries()), ase(wh.alw_id.size());
     for (size_t i = 0; i < se.size(); i++) se[i] = make_uint2(wh.ent_start[i], wh.ent_end[i]);
     for (size_t i = 0; i < ase.size(); i++) ase[i] = make_uint2(wh.alw_start[i], wh.alw_end[i]);
@@ -175,7 +191,7 @@ void EngineImpl::build_join() {
     wj_n_ent = (uint32_t)wh.n_entries();
     d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));
     GFFX_CUDA(cudaStreamSynchronize(st));
-    WJ.win0 = d_win0.as<uint32_t>();
+    WJ.win0 = d_wj_win0.as<uint32_t>();
     WJ.seq_send = d_wj_send.as<uint32_t>();
     WJ.ent_se = d_wj_se.as<uint2>();
     WJ.ent_fid = d_wj_fid.as<uint32_t>();

@@ -92,7 +92,7 @@ class EngineImpl {
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
 
     // ---- window-addressed root join (winjoin.cuh): what intersect uses -------------------------
-    DBuf d_wj_send, d_wj_se, d_wj_fid, d_wj_sdir, d_wj_alw0, d_wj_alwse, d_wj_alwid, d_wj_blk, d_wj_hit;
+    DBuf d_wj_win0, d_wj_send, d_wj_se, d_wj_fid, d_wj_sdir, d_wj_alw0, d_wj_alwse, d_wj_alwid, d_wj_blk, d_wj_hit;
     WinJoin WJ{};
     uint32_t wj_n_ent = 0;
 
@@ -109,7 +109,7 @@ class EngineImpl {
     DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_type_allow;
 
     // ---- window grid + partition scratch (partition.cuh) --------------------------------------
-    DBuf d_win0, d_poff, d_prank, d_pmat, d_pscan, d_pscratch, d_bchr, d_bse;
+    DBuf d_win0, d_poff, d_pmat, d_pscan, d_pscratch, d_bchr, d_bse;
     std::vector<uint32_t> h_win0;
     WinGrid WG{};
 
