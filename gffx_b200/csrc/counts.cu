@@ -165,8 +165,8 @@ void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, 
     const uint32_t* bc = nullptr;  // K0: window-bucketed regions keep every look-up below in L1
     const uint2* bse = nullptr;
     C->launches += E->partition(dc, ds, de, n, &bc, &bse);
-    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, C->d_err.as<uint32_t>());
-    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, C->d_err.as<uint32_t>());
+    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, C->d_err.as<uint32_t>());
+    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, C->d_err.as<uint32_t>());
     GFFX_CUDA(cudaEventRecord(C->ev1, E->st));
     GFFX_CUDA(cudaMemcpyAsync(E->h_small, C->d_err.p, 4, cudaMemcpyDeviceToHost, E->st));
     GFFX_CUDA(cudaStreamSynchronize(E->st));

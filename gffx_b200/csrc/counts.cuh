@@ -88,15 +88,21 @@ __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp
 // counting commands drop them: depth.rs:488, coverage.rs:253).
 template <int KIND>
 __global__ void __launch_bounds__(JOIN_THREADS)
-    counts_scatter_kernel(CountsDev D, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n,
+    counts_scatter_kernel(CountsDev D, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n, uint32_t key_shift,
                           uint32_t* __restrict__ err) {
-    const uint64_t q0 = (uint64_t)blockIdx.x * JOIN_TILE + (uint64_t)threadIdx.x * JOIN_QPT;
-    if (q0 >= n) return;
+    __shared__ TileSortSmem<JOIN_THREADS, JOIN_QPT> ts;
+    const uint64_t tile0 = (uint64_t)blockIdx.x * JOIN_TILE;
+    const uint32_t tm = (uint32_t)min((uint64_t)JOIN_TILE, n - tile0);
+    const uint64_t q0 = tile0 + (uint64_t)threadIdx.x * JOIN_QPT;
     Query4 Q;
-    load_queries(chr, se, n, q0, Q);
+    Q.n = 0;
+    if (q0 < n) load_queries(chr, se, n, q0, Q);
+    bool valid[JOIN_QPT];
+    // a warp's 32 regions next to each other on the genome (tilesort.cuh): shared cache lines for every look-up below
+    tile_sort<JOIN_THREADS, JOIN_QPT>(ts, key_shift, tm, Q.n, Q.c, Q.s, Q.e, valid);
 #pragma unroll
     for (int k = 0; k < JOIN_QPT; k++) {
-        if (k >= Q.n) continue;
+        if (!valid[k]) continue;
         const uint32_t c = Q.c[k], rs = Q.s[k], re = Q.e[k];
         if (rs >= re) continue;
         if (c >= D.n_seqs) { *err = 1; continue; }

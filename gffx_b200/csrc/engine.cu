@@ -179,7 +179,7 @@ void EngineImpl::build_join() {
     for (size_t i = 0; i < se.size(); i++) se[i] = make_uint2(wh.ent_start[i], wh.ent_end[i]);
     for (size_t i = 0; i < ase.size(); i++) ase[i] = make_uint2(wh.alw_start[i], wh.alw_end[i]);
     std::vector<uint32_t> wblk(wh.n_entries());
-    for (size_t k = 0; k < wblk.size(); k++) wblk[k] = H->root_blk[wh.ent_item[k]];
+    for (size_t k = 0; k < wblk.size(); k++) wblk[k] = wh.ent_item[k] == 0xFFFFFFFFu ? 0xFFFFFFFFu : H->root_blk[wh.ent_item[k]];
     upload(d_wj_send, wh.seq_send, st);
     upload(d_wj_se, se, st);
     upload(d_wj_fid, wh.ent_payload, st);
@@ -316,10 +316,10 @@ template <int MODE, bool INV>
 static void launch_wj(EngineImpl* E, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs,
                       unsigned long long cap, uint32_t* err) {
     if (emit)
-        wj_join_kernel<MODE, INV, true><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs,
+        wj_join_kernel<MODE, INV, true><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, E->d_wj_hit.as<uint8_t>(), n_pairs,
                                                                          E->d_pairs.as<uint32_t>(), cap, err);
     else
-        wj_join_kernel<MODE, INV, false><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, nullptr, 0, err);
+        wj_join_kernel<MODE, INV, false><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, E->d_wj_hit.as<uint8_t>(), n_pairs, nullptr, 0, err);
 }
 static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles,
                            unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
@@ -422,9 +422,9 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
         }
         const unsigned sblocks = (unsigned)((n + (uint64_t)FILT_THREADS * FILT_QPT - 1) / ((uint64_t)FILT_THREADS * FILT_QPT));
-        if (mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n);
-        else if (mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n);
-        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n);
+        if (mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n, WG.shift > 8 ? WG.shift - 8 : 0);
+        else if (mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n, WG.shift > 8 ? WG.shift - 8 : 0);
+        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n, WG.shift > 8 ? WG.shift - 8 : 0);
         launches++;
         GFFX_CUDA(cudaEventRecord(ev[5], st));
 

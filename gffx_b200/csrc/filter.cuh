@@ -23,6 +23,7 @@
 // plain (unsegmented) scan serve all sequences.
 #pragma once
 #include "scan.cuh"
+#include "tilesort.cuh"
 
 namespace gffx {
 
@@ -78,10 +79,14 @@ struct FilterArrays {
 // one streaming pass over the regions (12 B read per region, 1-3 scattered L2 updates)
 template <int MODE>
 __global__ void __launch_bounds__(FILT_THREADS)
-    scatter_regions_kernel(RankSpace R, FilterArrays F, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n) {
-    const uint64_t q0 = ((uint64_t)blockIdx.x * FILT_THREADS + threadIdx.x) * FILT_QPT;
-    if (q0 >= n) return;
+    scatter_regions_kernel(RankSpace R, FilterArrays F, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n,
+                           uint32_t key_shift) {
+    __shared__ TileSortSmem<FILT_THREADS, FILT_QPT> ts;
+    const uint64_t tile0 = (uint64_t)blockIdx.x * FILT_THREADS * FILT_QPT;
+    const uint32_t tm = (uint32_t)min((uint64_t)FILT_THREADS * FILT_QPT, n - tile0);
+    const uint64_t q0 = tile0 + (uint64_t)threadIdx.x * FILT_QPT;
     uint32_t c[FILT_QPT], s[FILT_QPT], e[FILT_QPT];
+    bool valid[FILT_QPT];
     int m = 0;
     if (q0 + FILT_QPT <= n) {
         const uint4 a = __ldcs(reinterpret_cast<const uint4*>(chr + q0));
@@ -95,9 +100,11 @@ __global__ void __launch_bounds__(FILT_THREADS)
         for (int k = 0; k < FILT_QPT; k++)
             if (q0 + k < n) { const uint2 v = se[q0 + k]; c[k] = chr[q0 + k]; s[k] = v.x; e[k] = v.y; m = k + 1; }
     }
+    // a warp's 32 regions next to each other on the genome: the rank look-ups below share their cache lines
+    tile_sort<FILT_THREADS, FILT_QPT>(ts, key_shift, tm, m, c, s, e, valid);
 #pragma unroll
     for (int k = 0; k < FILT_QPT; k++) {
-        if (k >= m || c[k] >= R.n_seqs) continue;
+        if (!valid[k] || c[k] >= R.n_seqs) continue;
         const RankSeq S = load_rank_seq(R, c[k]);
         if (!S.canon || S.cnt == 0) continue;  // no line of this sequence can ever match
         bool eq;

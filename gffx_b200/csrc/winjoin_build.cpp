@@ -36,7 +36,7 @@ void build_win_join(uint32_t n_seqs, const std::vector<JoinItem>& items, const s
         shorts[s] = std::move(cur);
         n_short += shorts[s].size();
     }
-    out->n_short = (uint32_t)n_short;
+    out->n_short = (uint32_t)n_short + n_seqs;  // + one sentinel per sequence
 
     // directory resolution: about 4 bins per short entry, at most 2^10 per window
     uint32_t sub_bits = 0;
@@ -65,6 +65,11 @@ void build_win_join(uint32_t n_seqs, const std::vector<JoinItem>& items, const s
             pmax[k] = pm;
         }
         out->seq_send[s] = base + (uint32_t)sh.size();
+        // sentinel: stops every forward scan (start >= any region end) without a bounds check
+        out->ent_start.push_back(0xFFFFFFFFu);
+        out->ent_end.push_back(0);
+        out->ent_payload.push_back(0);
+        out->ent_item.push_back(0xFFFFFFFFu);
         // sdir[(w << sub_bits) + b] = first short entry whose inclusive running max-end exceeds the bin's first base
         size_t j = 0;
         for (uint32_t w = win0[s]; w < win0[s + 1]; w++) {
