@@ -41,7 +41,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit,
                     &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
@@ -60,7 +60,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_send, &d_wj_se, &d_wj_fid, &d_wj_sdir, &d_wj_alw0, &d_wj_alwse, &d_wj_alwid, &d_wj_blk, &d_wj_hit,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit,
                     &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
@@ -157,52 +157,42 @@ void EngineImpl::build_join() {
     d_ent_hit.ensure(std::max<uint32_t>(n_ent, 1));
     GFFX_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
 
-    // the window-addressed form of the same intervals (winjoin.cuh), used by intersect
-    // its own fine grid (<= 16384 windows): the partition grid is coarse for store efficiency, the join kernel
-    // sorts each tile again by these windows in shared memory
-    std::vector<uint32_t> jwin0(n_seqs + 1, 0);
-    uint32_t jshift = 10;
-    {
-        std::vector<uint32_t> extent(n_seqs, 0);
-        for (const auto& r : R) extent[r.seq] = std::max(extent[r.seq], r.end);
-        for (;; jshift++) {
-            uint64_t tot = 0;
-            for (size_t s = 0; s < n_seqs; s++) tot += ((uint64_t)extent[s] >> jshift) + 1;
-            if (tot <= std::max<uint64_t>(16384, 2 * n_seqs) || jshift == 31) break;
-        }
-        for (size_t s = 0; s < n_seqs; s++) jwin0[s + 1] = jwin0[s] + (uint32_t)(((uint64_t)extent[s] >> jshift) + 1);
-    }
-    WinJoinHost wh;
-    build_win_join((uint32_t)n_seqs, items, jwin0, jshift, 8, 3, &wh);
+    // the window-addressed form of the same intervals (winjoin.cuh), used by intersect: on the PARTITION's grid, so that
+    // the bucketed regions of one window find their whole index slice in one contiguous piece (copied to shared memory)
+    const std::vector<uint32_t>& jwin0 = h_win0;
+    const uint32_t jshift = WG.shift;
+    WinBinsHost bh;
+    uint32_t max_sub = 9;  // GFFX_WJ_SUB=0..9: coarser bins (tests: long lists, slices beyond the shared-memory capacity)
+    if (const char* e = getenv("GFFX_WJ_SUB")) max_sub = (uint32_t)std::min(9, std::max(0, atoi(e)));
+    build_win_bins((uint32_t)n_seqs, items, jwin0, jshift, max_sub, 1ull << 27, &bh);
+    std::vector<uint4> ent4(bh.n_entries()), list4(std::max<size_t>(bh.list.size(), 1));
+    for (size_t i = 0; i < ent4.size(); i++) ent4[i] = make_uint4(bh.ent_start[i], bh.ent_end[i], bh.ent_payload[i], (uint32_t)i);
+    for (size_t i = 0; i < bh.list.size(); i++) list4[i] = ent4[bh.list[i]];
+    std::vector<uint32_t> wblk(bh.n_entries());
+    for (size_t k = 0; k < wblk.size(); k++) wblk[k] = bh.ent_item[k] == 0xFFFFFFFFu ? 0xFFFFFFFFu : H->root_blk[bh.ent_item[k]];
     upload(d_wj_win0, jwin0, st);
-    std::vector<uint2> se(wh.n_entries()), ase(wh.alw_id.size());
-    for (size_t i = 0; i < se.size(); i++) se[i] = make_uint2(wh.ent_start[i], wh.ent_end[i]);
-    for (size_t i = 0; i < ase.size(); i++) ase[i] = make_uint2(wh.alw_start[i], wh.alw_end[i]);
-    std::vector<uint32_t> wblk(wh.n_entries());
-    for (size_t k = 0; k < wblk.size(); k++) wblk[k] = wh.ent_item[k] == 0xFFFFFFFFu ? 0xFFFFFFFFu : H->root_blk[wh.ent_item[k]];
-    upload(d_wj_send, wh.seq_send, st);
-    upload(d_wj_se, se, st);
-    upload(d_wj_fid, wh.ent_payload, st);
-    upload(d_wj_sdir, wh.sdir, st);
-    upload(d_wj_alw0, wh.alw0, st);
-    upload(d_wj_alwse, ase, st);
-    upload(d_wj_alwid, wh.alw_id, st);
+    upload(d_wj_winseq, bh.win_seq, st);
+    upload(d_wj_ent4, ent4, st);
+    upload(d_wj_list4, list4, st);
+    upload(d_wj_fid, bh.ent_payload, st);
+    upload(d_wj_first, bh.first, st);
+    upload(d_wj_boff, bh.boff, st);
     upload(d_wj_blk, wblk, st);
-    wj_n_ent = (uint32_t)wh.n_entries();
+    wj_n_ent = (uint32_t)bh.n_entries();
     d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));
     GFFX_CUDA(cudaStreamSynchronize(st));
-    WJ.win0 = d_wj_win0.as<uint32_t>();
-    WJ.seq_send = d_wj_send.as<uint32_t>();
-    WJ.ent_se = d_wj_se.as<uint2>();
-    WJ.ent_fid = d_wj_fid.as<uint32_t>();
-    WJ.sdir = d_wj_sdir.as<uint32_t>();
-    WJ.alw0 = d_wj_alw0.as<uint32_t>();
-    WJ.alw_se = d_wj_alwse.as<uint2>();
-    WJ.alw_id = d_wj_alwid.as<uint32_t>();
-    WJ.n_seqs = (uint32_t)n_seqs;
-    WJ.shift = wh.shift;
-    WJ.sub_bits = wh.sub_bits;
-    WJ.n_ent = wj_n_ent;
+    WC = WinBins{};
+    WC.win_seq = d_wj_winseq.as<uint32_t>();
+    WC.win0 = d_wj_win0.as<uint32_t>();
+    WC.ent4 = d_wj_ent4.as<uint4>();
+    WC.ent_fid = d_wj_fid.as<uint32_t>();
+    WC.list4 = d_wj_list4.as<uint4>();
+    WC.first = d_wj_first.as<uint32_t>();
+    WC.boff = d_wj_boff.as<uint32_t>();
+    WC.shift = bh.shift;
+    WC.sub = bh.sub;
+    WC.n_win = bh.n_win;
+    WC.n_ent = wj_n_ent;
 }
 
 void EngineImpl::build_blocks() {
@@ -315,11 +305,11 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
 template <int MODE, bool INV>
 static void launch_wj(EngineImpl* E, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs,
                       unsigned long long cap, uint32_t* err) {
+    const uint32_t* poff = E->d_poff.as<uint32_t>();
     if (emit)
-        wj_join_kernel<MODE, INV, true><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, E->d_wj_hit.as<uint8_t>(), n_pairs,
-                                                                         E->d_pairs.as<uint32_t>(), cap, err);
+        wj_join_kernel<MODE, INV, true><<<tiles, WJ_THREADS, 0, E->st>>>(E->WC, poff, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, E->d_pairs.as<uint32_t>(), cap, err);
     else
-        wj_join_kernel<MODE, INV, false><<<tiles, WJ_THREADS, 0, E->st>>>(E->WJ, c, se, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, E->d_wj_hit.as<uint8_t>(), n_pairs, nullptr, 0, err);
+        wj_join_kernel<MODE, INV, false><<<tiles, WJ_THREADS, 0, E->st>>>(E->WC, poff, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, nullptr, 0, err);
 }
 static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles,
                            unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
@@ -376,7 +366,7 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     const bool match_only = !entire_group || types_csv != nullptr;  // intersect.rs:619
     if (n_blocks) GFFX_CUDA(cudaMemsetAsync(d_blk_sel.p, 0, n_blocks, st));
     if (!nothing) {
-        wj_select_blocks_kernel<<<(wj_n_ent + 255) / 256, 256, 0, st>>>(d_wj_hit.as<uint8_t>(), d_wj_blk.as<uint32_t>(), WJ.ent_fid, wj_n_ent,
+        wj_select_blocks_kernel<<<(wj_n_ent + 255) / 256, 256, 0, st>>>(d_wj_hit.as<uint8_t>(), d_wj_blk.as<uint32_t>(), WC.ent_fid, wj_n_ent,
                                                                        d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
         launches++;
         if (n_blocks) {

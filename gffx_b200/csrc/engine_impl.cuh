@@ -92,8 +92,8 @@ class EngineImpl {
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
 
     // ---- window-addressed root join (winjoin.cuh): what intersect uses -------------------------
-    DBuf d_wj_win0, d_wj_send, d_wj_se, d_wj_fid, d_wj_sdir, d_wj_alw0, d_wj_alwse, d_wj_alwid, d_wj_blk, d_wj_hit;
-    WinJoin WJ{};
+    DBuf d_wj_win0, d_wj_winseq, d_wj_ent4, d_wj_list4, d_wj_fid, d_wj_first, d_wj_boff, d_wj_blk, d_wj_hit;
+    WinBins WC{};
     uint32_t wj_n_ent = 0;
 
     // ---- blocks ------------------------------------------------------------------------------

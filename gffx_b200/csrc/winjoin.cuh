@@ -2,134 +2,23 @@
 // IntervalTree::query_interval (src/utils/tree.rs:98-121) and the per-region loop of query_features
 // (src/commands/intersect.rs:139-165).
 //
-// Index layout (winjoin_build.h; all of it L2-resident, the slice one CTA touches L1-resident):
-//   ent_se[j]   (start,end) of the SHORT root intervals, per sequence sorted by start   8 B
-//   sdir[w,b]   first short entry whose running max-end exceeds the first base of directory bin b of
-//               window w: every earlier entry ends at or before the bin                 4 B
-//   alw_*[a]    the LONG intervals (those reaching past their long_k-th successor, e.g. a
-//               chromosome-spanning `region` root) listed once per window they overlap
-// A region (seq, rs, re) of window w = win(seq, rs) reads sdir[w, bin(rs)], scans ent_se forward while
-// start < re testing end > rs, then tests the window's long list; if it reaches into later windows it
-// also takes the long intervals that START there.  Together that is exactly the set
-// { iv : iv.start < re && iv.end > rs } of tree.rs:110 for any rs/re (rs >= re included).
-// The chain is two dependent loads deep (sdir -> ent_se) instead of the tree's ~12 node hops, and a warp's
-// 32 regions share the same few cache lines because partition.cuh put them in the same window.
-//
-// One fused kernel per call (wj_join_kernel below).
+// The index, the search and the kernel are described at wj_join_kernel below; the result is exactly the set
+// { iv : iv.start < re && iv.end > rs } of tree.rs:110 for any rs/re (rs >= re included), filtered by the mode
+// test of intersect.rs:145-163.
 #pragma once
 #include "scan.cuh"
-#include "tilesort.cuh"
 
 namespace gffx {
 
 constexpr int WJ_THREADS = 256;
 constexpr int WJ_QPT = 4;  // consecutive bucketed regions per thread: one 16 B load of chr, two of (start,end)
 constexpr int WJ_TILE = WJ_THREADS * WJ_QPT;
-constexpr int WJ_STAGE_PAIRS = 2048;  // 24 KB of shared memory
-
-struct WinJoin {
-    const uint32_t* win0;      // n_seqs+1
-    const uint32_t* seq_send;  // n_seqs
-    const uint2* ent_se;       // n_ent (shorts then longs)
-    const uint32_t* ent_fid;   // n_ent
-    const uint32_t* sdir;      // n_win << sub_bits
-    const uint32_t* alw0;      // n_win+1
-    const uint2* alw_se;
-    const uint32_t* alw_id;
-    uint32_t n_seqs, shift, sub_bits, n_ent;
-};
+constexpr int WJ_STAGE_PAIRS = 1792;  // 21 KB of shared memory (5 CTAs per SM with the 20 KB window slice)
 
 // mode test of src/commands/intersect.rs:145-158 and the XOR of :161
 template <int MODE, bool INVERT> __device__ __forceinline__ bool wj_keep(uint32_t s, uint32_t e, uint32_t rs, uint32_t re) {
     const bool keep = MODE == 0 ? (s >= rs && e <= re) : MODE == 1 ? (s <= rs && e >= re) : true;
     return INVERT != keep;
-}
-
-template <int MODE, bool INVERT, class F>
-__device__ __forceinline__ void wj_query(const WinJoin& J, uint32_t c, uint32_t rs, uint32_t re, F&& f) {
-    const uint32_t w0 = __ldg(J.win0 + c), nw = __ldg(J.win0 + c + 1) - w0;
-    const uint32_t jend = __ldg(J.seq_send + c);
-    uint32_t wl = rs >> J.shift;
-    if (wl >= nw) wl = nw - 1;  // beyond the sequence's extent: its last window
-    const uint32_t w = w0 + wl;
-    uint32_t b = (rs - (wl << J.shift)) >> (J.shift - J.sub_bits);
-    const uint32_t bmax = (1u << J.sub_bits) - 1u;
-    if (b > bmax) b = bmax;
-    uint32_t j = __ldg(J.sdir + (((size_t)w) << J.sub_bits) + b);
-    const uint32_t a0 = __ldg(J.alw0 + w), a1 = __ldg(J.alw0 + w + 1);
-    for (; j < jend; j++) {
-        const uint2 se = __ldg(J.ent_se + j);
-        if (se.x >= re) break;
-        if (se.y > rs && wj_keep<MODE, INVERT>(se.x, se.y, rs, re)) f(j, se);
-    }
-    for (uint32_t a = a0; a < a1; a++) {
-        const uint2 se = __ldg(J.alw_se + a);
-        if (se.x < re && se.y > rs && wj_keep<MODE, INVERT>(se.x, se.y, rs, re)) f(__ldg(J.alw_id + a), se);
-    }
-    if (re != 0 && wl + 1 < nw) {  // long intervals that START in the later windows the region reaches into
-        uint32_t wr = (re - 1u) >> J.shift;
-        if (wr >= nw) wr = nw - 1;
-        for (uint32_t ww = wl + 1; ww <= wr; ww++) {
-            const uint32_t lo2 = ww << J.shift;
-            const uint32_t b0 = __ldg(J.alw0 + w0 + ww), b1 = __ldg(J.alw0 + w0 + ww + 1);
-            for (uint32_t a = b0; a < b1; a++) {
-                const uint2 se = __ldg(J.alw_se + a);
-                if (se.x >= lo2 && se.x < re && se.y > rs && wj_keep<MODE, INVERT>(se.x, se.y, rs, re)) f(__ldg(J.alw_id + a), se);
-            }
-        }
-    }
-}
-
-// First pass of the fused kernel: the same search, but instead of calling back it RECORDS which candidates hit, so
-// that the emit pass walks hits only (no second directory look-up, no failed candidates).  Bit i (< 16) of the mask:
-// short entry j0+i hit; bit 16+i (i < 15): entry a0+i of the window's long list hit; bit 31: something did not fit
-// (more candidates than bits, or a hit in a later window's long list) and the emit pass repeats the full search.
-template <int MODE, bool INVERT, class F>
-__device__ __forceinline__ uint32_t wj_probe(const WinJoin& J, uint32_t c, uint32_t rs, uint32_t re, uint32_t& j0, uint32_t& a0, F&& on_hit) {
-    const uint32_t w0 = __ldg(J.win0 + c), nw = __ldg(J.win0 + c + 1) - w0;
-    uint32_t wl = rs >> J.shift;
-    if (wl >= nw) wl = nw - 1;  // beyond the sequence's extent: its last window
-    const uint32_t w = w0 + wl;
-    uint32_t b = (rs - (wl << J.shift)) >> (J.shift - J.sub_bits);
-    const uint32_t bmax = (1u << J.sub_bits) - 1u;
-    if (b > bmax) b = bmax;
-    j0 = __ldg(J.sdir + (((size_t)w) << J.sub_bits) + b);
-    a0 = __ldg(J.alw0 + w);
-    const uint32_t a1 = __ldg(J.alw0 + w + 1);
-    uint32_t mask = 0;
-    uint32_t bit = 1u;
-    for (uint32_t j = j0;; j++, bit <<= 1) {  // ends at the sequence's sentinel entry (start 0xFFFFFFFF) at the latest
-        const uint2 se = __ldg(J.ent_se + j);
-        if (se.x >= re) break;
-        if (se.y > rs && wj_keep<MODE, INVERT>(se.x, se.y, rs, re)) {
-            mask |= (bit & 0xFFFFu) ? bit : 0x80000000u;
-            on_hit(j);
-        }
-    }
-    bit = 1u << 16;
-    for (uint32_t a = a0; a < a1; a++, bit <<= 1) {
-        const uint2 se = __ldg(J.alw_se + a);
-        if (se.x < re && se.y > rs && wj_keep<MODE, INVERT>(se.x, se.y, rs, re)) {
-            mask |= (bit & 0x7FFF0000u) ? bit : 0x80000000u;
-            on_hit(__ldg(J.alw_id + a));
-        }
-    }
-    if (re != 0 && wl + 1 < nw) {  // long intervals that START in the later windows the region reaches into
-        uint32_t wr = (re - 1u) >> J.shift;
-        if (wr >= nw) wr = nw - 1;
-        for (uint32_t ww = wl + 1; ww <= wr; ww++) {
-            const uint32_t lo2 = ww << J.shift;
-            const uint32_t b0 = __ldg(J.alw0 + w0 + ww), b1 = __ldg(J.alw0 + w0 + ww + 1);
-            for (uint32_t a = b0; a < b1; a++) {
-                const uint2 se = __ldg(J.alw_se + a);
-                if (se.x >= lo2 && se.x < re && se.y > rs && wj_keep<MODE, INVERT>(se.x, se.y, rs, re)) {
-                    mask |= 0x80000000u;
-                    on_hit(__ldg(J.alw_id + a));
-                }
-            }
-        }
-    }
-    return mask;
 }
 
 // thread t loads tile elements t*4 .. t*4+3 (one 16 B load of chr, two of (start,end)); returns how many exist
@@ -156,88 +45,211 @@ __device__ __forceinline__ int wj_load(const uint32_t* __restrict__ chr, const u
     return m;
 }
 
+// ------------------------------------------------------------------------------------------------
+// K1, bin lists in shared memory.
+//
+// Index (winjoin_build.h, WinBinsHost): every window of the partition grid is cut into 2^sub bins; a bin owns the list
+// of the intervals overlapping it, and `first` points into the sequence's start-sorted interval array.  The intervals
+// that overlap a region starting in bin b are the members of b's list that pass the test, then the run of the sorted
+// array from first[b+1] while start < re.  Long genes, nested genes and chromosome-spanning roots cost nothing
+// extra: no running max-end to back-track over (r01h/r01i profiles: 400-900 instructions per region went into
+// candidates that an earlier long gene dragged in, or into probing one chain per nesting level).
+//
+// After K0 the bucketed regions of one window are CONTIGUOUS, so a tile of WJ_TILE regions lies in one window
+// (rarely a few: the sum over all tiles of extra windows is <= n_win).  The CTA copies the window's slice — bin
+// offsets, `first`, the list members and the run, as 16-byte (start,end,fid,id) records — into shared memory once,
+// and every region resolves with shared-memory reads only; whatever exceeds the slice capacity is read from global
+// memory, so the result is the same set for any input.
+constexpr int WJ_BINS_MAX = 512;    // bins per window (sub <= 9)
+constexpr int WJ_LIST_CAP = 768;    // list members of the window held in shared memory (12 KB)
+constexpr int WJ_RUN_CAP = 256;     // start-sorted intervals from the window's first held in shared memory (4 KB)
+
+struct WinBins {
+    const uint32_t* win_seq;   // n_win
+    const uint32_t* win0;      // n_seqs + 1
+    const uint4* ent4;         // start-sorted intervals per sequence + sentinel: (start, end, root_fid, id)
+    const uint32_t* ent_fid;   // the same root_fid by id (block selection / warn list)
+    const uint4* list4;        // bin lists as records
+    const uint32_t* first;     // n_win * (nb + 1)
+    const uint32_t* boff;      // n_win * (nb + 1)
+    uint32_t shift, sub, n_win, n_ent;
+};
+
+struct WjSlice {
+    uint4 list[WJ_LIST_CAP];
+    uint4 run[WJ_RUN_CAP];
+    uint32_t boff[WJ_BINS_MAX + 1];
+    uint32_t first[WJ_BINS_MAX + 1];
+    uint32_t lhit[WJ_LIST_CAP / 32], rhit[WJ_RUN_CAP / 32];
+    uint32_t w_first, w_last, lo, l0, nlist, j0, nrun;
+};
+
+// visits, in order, the intervals with start < re && end > rs that pass the mode test: f(record, bit) where bit is the
+// position code of the hit (list member i < 16 -> bit i, run member i < 15 -> bit 16+i, else bit 31 = "does not fit")
+template <int MODE, bool INVERT, class F>
+__device__ __forceinline__ void wj_visit(const WinBins& C, const WjSlice& S, uint32_t b, uint32_t rs, uint32_t re, F&& f) {
+    const uint32_t o0 = S.boff[b], o1 = S.boff[b + 1];
+    uint32_t bit = 1u;
+    for (uint32_t a = o0; a < o1; a++, bit <<= 1) {
+        const uint32_t i = a - S.l0;
+        const uint4 v = i < S.nlist ? S.list[i] : __ldg(C.list4 + a);
+        if (v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) f(v, (bit & 0xFFFFu) ? bit : 0x80000000u, i, true);
+    }
+    bit = 1u << 16;
+    for (uint32_t j = S.first[b + 1];; j++, bit <<= 1) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
+        const uint32_t i = j - S.j0;
+        const uint4 v = i < S.nrun ? S.run[i] : __ldg(C.ent4 + j);
+        if (v.x >= re) break;
+        if (v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) f(v, (bit & 0x7FFF0000u) ? bit : 0x80000000u, i, false);
+    }
+}
+
 // EMIT = false: pair count + per-entry hit flags only (the CLI path needs no pairs).
-// EMIT = true : also writes the pairs; a tile whose claimed range does not fit `cap` writes nothing (the host
-//               grows the buffer to the reported total and runs the kernel again).
-// Per tile: load -> shared-memory sort -> probe (count, hit masks, hit-root flags) -> CTA exclusive scan -> ONE global
-// atomic claims the tile's output range -> the recorded hits are staged as (root_fid,start,end) in shared memory ->
-// coalesced stores.
+// EMIT = true : also writes the pairs; a (tile, window) whose claimed range does not fit `cap` writes nothing (the
+//               host grows the buffer to the reported total and runs the kernel again).
 template <int MODE, bool INVERT, bool EMIT>
 __global__ void __launch_bounds__(WJ_THREADS)
-    wj_join_kernel(WinJoin J, const uint32_t* __restrict__ chr, const uint2* __restrict__ qse, uint64_t n, uint32_t key_shift,
-                   uint8_t* ent_hit, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ pairs, unsigned long long cap,
-                   uint32_t* __restrict__ err) {
-    union Smem {
-        TileSortSmem<WJ_THREADS, WJ_QPT> sort;
-        uint32_t stage[EMIT ? WJ_STAGE_PAIRS * 3 : 1];
-    };
-    __shared__ Smem U;
+    wj_join_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint32_t* __restrict__ chr, const uint2* __restrict__ qse,
+                   uint64_t n, uint8_t* ent_hit, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ pairs,
+                   unsigned long long cap, uint32_t* __restrict__ err) {
+    __shared__ WjSlice S;
+    __shared__ __align__(16) uint32_t stage[EMIT ? WJ_STAGE_PAIRS * 3 : 4];
     __shared__ uint32_t sm[WJ_THREADS / 32 + 1];
     __shared__ unsigned long long sbase;
-    const uint64_t tile0 = (uint64_t)blockIdx.x * WJ_TILE;
+    const uint32_t tile0 = blockIdx.x * (uint32_t)WJ_TILE;
     const uint32_t m = (uint32_t)min((uint64_t)WJ_TILE, n - tile0);
+    const uint32_t n_win = C.n_win, nb = 1u << C.sub, bsh = C.shift - C.sub;
     uint32_t c[WJ_QPT], s[WJ_QPT], e[WJ_QPT];
-    bool valid[WJ_QPT];
-    const int n_in = wj_load(chr, qse, n, tile0 + (uint64_t)threadIdx.x * WJ_QPT, c, s, e);
-    tile_sort<WJ_THREADS, WJ_QPT>(U.sort, key_shift, m, n_in, c, s, e, valid);
-    uint32_t cnt = 0;
-    uint32_t mask[WJ_QPT], j0[WJ_QPT], a0[WJ_QPT];
-#pragma unroll
-    for (int k = 0; k < WJ_QPT; k++) {
-        mask[k] = 0;
-        if (!valid[k]) continue;
-        if (c[k] >= J.n_seqs) { *err = 1; continue; }
-        mask[k] = wj_probe<MODE, INVERT>(J, c[k], s[k], e[k], j0[k], a0[k], [&](uint32_t id) {
-            cnt++;
-            // ~230 regions hit every root: an L1-cached test keeps the store count O(1) per root and SM
-            // (a stale 0 only repeats an idempotent store)
-            if (!ent_hit[id]) ent_hit[id] = 1;
-        });
+    const uint32_t q0 = tile0 + threadIdx.x * WJ_QPT;
+    wj_load(chr, qse, n, q0, c, s, e);
+    // windows of the tile's first and last region: (number of window offsets <= position) - 1; poff has n_win + 2 cells
+    {
+        int nf = 0, nl = 0;
+        for (uint32_t i0 = 0; i0 < n_win + 2; i0 += WJ_THREADS) {
+            const uint32_t i = i0 + threadIdx.x;
+            const uint32_t o = i < n_win + 2 ? __ldg(poff + i) : 0xFFFFFFFFu;
+            nf += __syncthreads_count(o <= tile0);
+            nl += __syncthreads_count(o <= tile0 + m - 1);
+        }
+        if (threadIdx.x == 0) { S.w_first = (uint32_t)nf - 1u; S.w_last = (uint32_t)nl - 1u; }
     }
-    uint32_t tot;
-    uint32_t pos = block_scan_excl(cnt, OpSum(), 0u, sm, &tot);  // its barriers also retire U.sort before U.stage is written
-    if (tot == 0) return;
-    if (threadIdx.x == 0) sbase = atomicAdd(n_pairs, (unsigned long long)tot);
-    if (!EMIT) return;
     __syncthreads();
-    const unsigned long long gbase = sbase;
-    if (gbase + tot > cap) return;
-    if (tot <= WJ_STAGE_PAIRS) {
-        uint32_t* dst = U.stage + 3 * pos;
+    const uint32_t w_first = S.w_first, w_last = S.w_last;
+    for (uint32_t w = w_first; w <= w_last; w++) {
+        const uint32_t p_lo = max(__ldg(poff + w), tile0), p_hi = min(__ldg(poff + w + 1), tile0 + m);
+        if (p_lo >= p_hi) continue;   // empty window (uniform)
+        if (w >= n_win) {             // bucket of the regions whose sequence number is out of range
+            if (threadIdx.x == 0) *err = 1;
+            continue;
+        }
+        const size_t row = (size_t)w * (nb + 1);
+        if (threadIdx.x == 0) {
+            const uint32_t cw = __ldg(C.win_seq + w);
+            S.lo = (w - __ldg(C.win0 + cw)) << C.shift;
+            const uint32_t l0 = __ldg(C.boff + row), l1 = __ldg(C.boff + row + nb);
+            const uint32_t j0 = __ldg(C.first + row), j1 = __ldg(C.first + row + nb);
+            S.l0 = l0; S.nlist = min(l1 - l0, (uint32_t)WJ_LIST_CAP);
+            S.j0 = j0; S.nrun = min(min(j1 - j0 + 8u, (uint32_t)WJ_RUN_CAP), C.n_ent - j0);
+        }
+        for (uint32_t i = threadIdx.x; i <= nb; i += WJ_THREADS) {
+            S.boff[i] = __ldg(C.boff + row + i);
+            S.first[i] = __ldg(C.first + row + i);
+        }
+        if (threadIdx.x < WJ_LIST_CAP / 32) S.lhit[threadIdx.x] = 0;
+        if (threadIdx.x < WJ_RUN_CAP / 32) S.rhit[threadIdx.x] = 0;
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < S.nlist; i += WJ_THREADS) S.list[i] = __ldg(C.list4 + S.l0 + i);
+        for (uint32_t i = threadIdx.x; i < S.nrun; i += WJ_THREADS) S.run[i] = __ldg(C.ent4 + S.j0 + i);
+        __syncthreads();
+        const uint32_t lo = S.lo;
+        uint32_t cnt = 0;
+        uint32_t mask[WJ_QPT], bin[WJ_QPT];
 #pragma unroll
         for (int k = 0; k < WJ_QPT; k++) {
-            if (mask[k] & 0x80000000u) {
-                wj_query<MODE, INVERT>(J, c[k], s[k], e[k], [&](uint32_t id, uint2 se) {
-                    dst[0] = __ldg(J.ent_fid + id); dst[1] = se.x; dst[2] = se.y;
-                    dst += 3;
-                });
-                continue;
-            }
-            for (uint32_t mm = mask[k] & 0xFFFFu; mm; mm &= mm - 1) {
-                const uint32_t id = j0[k] + (uint32_t)__ffs(mm) - 1u;
-                const uint2 se = __ldg(J.ent_se + id);
-                dst[0] = __ldg(J.ent_fid + id); dst[1] = se.x; dst[2] = se.y;
-                dst += 3;
-            }
-            for (uint32_t mm = mask[k] >> 16; mm; mm &= mm - 1) {
-                const uint32_t a = a0[k] + (uint32_t)__ffs(mm) - 1u;
-                const uint2 se = __ldg(J.alw_se + a);
-                dst[0] = __ldg(J.ent_fid + __ldg(J.alw_id + a)); dst[1] = se.x; dst[2] = se.y;
-                dst += 3;
+            mask[k] = 0;
+            const uint32_t q = q0 + k;
+            if (q < p_lo || q >= p_hi) continue;
+            uint32_t b = (s[k] - lo) >> bsh;
+            if (b > nb - 1) b = nb - 1;
+            bin[k] = b;
+            uint32_t mk = 0;
+            wj_visit<MODE, INVERT>(C, S, b, s[k], e[k], [&](const uint4& v, uint32_t bit, uint32_t i, bool in_list) {
+                mk |= bit;
+                cnt++;
+                if (in_list ? i < S.nlist : i < S.nrun) {
+                    uint32_t* h = (in_list ? S.lhit : S.rhit) + (i >> 5);
+                    const uint32_t hb = 1u << (i & 31);
+                    if (!(*h & hb)) atomicOr(h, hb);
+                } else if (!ent_hit[v.w]) ent_hit[v.w] = 1;
+            });
+            mask[k] = mk;
+        }
+        uint32_t tot;
+        const uint32_t pos = block_scan_excl(cnt, OpSum(), 0u, sm, &tot);
+        if (tot != 0) {   // uniform
+            // hit flags of the slice: one idempotent byte store per hit root and CTA
+            for (uint32_t i = threadIdx.x; i < S.nlist; i += WJ_THREADS)
+                if ((S.lhit[i >> 5] >> (i & 31)) & 1u) {
+                    uint8_t* h = ent_hit + S.list[i].w;
+                    if (!*h) *h = 1;
+                }
+            for (uint32_t i = threadIdx.x; i < S.nrun; i += WJ_THREADS)
+                if ((S.rhit[i >> 5] >> (i & 31)) & 1u) {
+                    uint8_t* h = ent_hit + S.j0 + i;
+                    if (!*h) *h = 1;
+                }
+            if (threadIdx.x == 0) sbase = atomicAdd(n_pairs, (unsigned long long)tot);
+            if (EMIT) {
+                __syncthreads();
+                const unsigned long long gbase = sbase;
+                if (gbase + tot <= cap) {
+                    const bool staged = tot <= WJ_STAGE_PAIRS;
+                    uint32_t* dst = staged ? stage + 3 * pos : pairs + 3 * (gbase + pos);
+#pragma unroll
+                    for (int k = 0; k < WJ_QPT; k++) {
+                        const uint32_t mk = mask[k];
+                        if (!mk) continue;
+                        if (mk & 0x80000000u) {   // more hits than position bits: the same walk again
+                            wj_visit<MODE, INVERT>(C, S, bin[k], s[k], e[k], [&](const uint4& v, uint32_t, uint32_t, bool) {
+                                dst[0] = v.z; dst[1] = v.x; dst[2] = v.y;
+                                dst += 3;
+                            });
+                            continue;
+                        }
+                        const uint32_t o0 = S.boff[bin[k]], f1 = S.first[bin[k] + 1];
+                        for (uint32_t mm = mk & 0xFFFFu; mm; mm &= mm - 1) {
+                            const uint32_t a = o0 + (uint32_t)__ffs(mm) - 1u, i = a - S.l0;
+                            const uint4 v = i < S.nlist ? S.list[i] : __ldg(C.list4 + a);
+                            dst[0] = v.z; dst[1] = v.x; dst[2] = v.y;
+                            dst += 3;
+                        }
+                        for (uint32_t mm = mk >> 16; mm; mm &= mm - 1) {
+                            const uint32_t j = f1 + (uint32_t)__ffs(mm) - 1u, i = j - S.j0;
+                            const uint4 v = i < S.nrun ? S.run[i] : __ldg(C.ent4 + j);
+                            dst[0] = v.z; dst[1] = v.x; dst[2] = v.y;
+                            dst += 3;
+                        }
+                    }
+                    if (staged) {
+                        __syncthreads();
+                        // 3*tot words to pairs + 3*gbase: scalar head up to 16-byte alignment, 16-byte body, scalar tail
+                        uint32_t* g = pairs + 3 * gbase;
+                        const uint32_t nwords = 3 * tot;
+                        const uint32_t head = min(nwords, (uint32_t)((4u - ((uint32_t)(3ull * gbase) & 3u)) & 3u));
+                        if (threadIdx.x < head) __stcs(g + threadIdx.x, stage[threadIdx.x]);
+                        const uint32_t nvec = (nwords - head) >> 2;
+                        uint4* gv = reinterpret_cast<uint4*>(g + head);
+                        for (uint32_t i = threadIdx.x; i < nvec; i += WJ_THREADS) {
+                            const uint32_t* sp = stage + head + 4 * i;   // shared reads are word-aligned only
+                            __stcs(gv + i, make_uint4(sp[0], sp[1], sp[2], sp[3]));
+                        }
+                        const uint32_t done = head + 4 * nvec;
+                        if (threadIdx.x < nwords - done) __stcs(g + done + threadIdx.x, stage[done + threadIdx.x]);
+                    }
+                }
             }
         }
-        __syncthreads();
-        uint32_t* g = pairs + 3 * gbase;
-        for (uint32_t i = threadIdx.x; i < 3 * tot; i += WJ_THREADS) __stcs(g + i, U.stage[i]);
-    } else {  // a tile denser than the staging buffer: the same walk straight to global memory
-        uint32_t* dst = pairs + 3 * (gbase + pos);
-#pragma unroll
-        for (int k = 0; k < WJ_QPT; k++)
-            if (mask[k])
-                wj_query<MODE, INVERT>(J, c[k], s[k], e[k], [&](uint32_t id, uint2 se) {
-                    dst[0] = __ldg(J.ent_fid + id); dst[1] = se.x; dst[2] = se.y;
-                    dst += 3;
-                });
+        __syncthreads();  // the slice, the stage and sbase are reused by the next window of this tile
     }
 }
 

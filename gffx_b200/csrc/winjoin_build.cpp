@@ -3,112 +3,88 @@
 
 namespace gffx {
 
-void build_win_join(uint32_t n_seqs, const std::vector<JoinItem>& items, const std::vector<uint32_t>& win0, uint32_t shift, int long_k,
-                    int levels, WinJoinHost* out) {
-    *out = WinJoinHost();
+void build_win_bins(uint32_t n_seqs, const std::vector<JoinItem>& items, const std::vector<uint32_t>& win0, uint32_t shift,
+                    uint32_t max_sub, uint64_t max_list, WinBinsHost* out) {
+    *out = WinBinsHost();
     out->shift = shift;
-    out->win0 = win0;
     const uint32_t n_win = win0[n_seqs];
+    out->n_win = n_win;
+    out->win_seq.assign(n_win, 0);
+    for (uint32_t s = 0; s < n_seqs; s++)
+        for (uint32_t w = win0[s]; w < win0[s + 1]; w++) out->win_seq[w] = s;
+
+    // ---- start-sorted entries per sequence --------------------------------------------------------
     std::vector<std::vector<uint32_t>> by_seq(n_seqs);
     for (size_t i = 0; i < items.size(); i++) by_seq[items[i].seq].push_back((uint32_t)i);
-
-    // ---- split every sequence into its short list and its long entries ---------------------------
-    std::vector<std::vector<uint32_t>> shorts(n_seqs), longs(n_seqs);
-    size_t n_short = 0;
+    std::vector<uint32_t> base(n_seqs + 1, 0);
     for (uint32_t s = 0; s < n_seqs; s++) {
         std::vector<uint32_t>& ids = by_seq[s];
         std::stable_sort(ids.begin(), ids.end(), [&](uint32_t a, uint32_t b) {
             if (items[a].start != items[b].start) return items[a].start < items[b].start;
             return items[a].end < items[b].end;
         });
-        std::vector<uint32_t> cur = ids, keep;
-        for (int level = 0; level < levels && cur.size() > (size_t)long_k; level++) {
-            keep.clear();
-            size_t peeled = 0;
-            for (size_t i = 0; i < cur.size(); i++) {
-                const bool is_long = i + long_k < cur.size() && items[cur[i]].end > items[cur[i + long_k]].start;
-                if (is_long) { longs[s].push_back(cur[i]); peeled++; }
-                else keep.push_back(cur[i]);
-            }
-            cur.swap(keep);
-            if (!peeled) break;
+        base[s] = (uint32_t)out->ent_start.size();
+        for (uint32_t id : ids) {
+            out->ent_start.push_back(items[id].start);
+            out->ent_end.push_back(items[id].end);
+            out->ent_payload.push_back(items[id].payload);
+            out->ent_item.push_back(id);
         }
-        shorts[s] = std::move(cur);
-        n_short += shorts[s].size();
-    }
-    out->n_short = (uint32_t)n_short + n_seqs;  // + one sentinel per sequence
-
-    // directory resolution: about 4 bins per short entry, at most 2^10 per window
-    uint32_t sub_bits = 0;
-    while (sub_bits < 10 && sub_bits < shift && ((uint64_t)n_win << sub_bits) < 4ull * std::max<size_t>(n_short, 1)) sub_bits++;
-    out->sub_bits = sub_bits;
-    const uint32_t sub_shift = shift - sub_bits;
-
-    // ---- unified entry arrays: shorts of all sequences, then the longs ---------------------------
-    auto push_entry = [&](uint32_t item) {
-        out->ent_start.push_back(items[item].start);
-        out->ent_end.push_back(items[item].end);
-        out->ent_payload.push_back(items[item].payload);
-        out->ent_item.push_back(item);
-    };
-    out->seq_send.assign(n_seqs, 0);
-    out->sdir.assign((size_t)n_win << sub_bits, 0);
-    std::vector<uint32_t> pmax;
-    for (uint32_t s = 0; s < n_seqs; s++) {
-        const uint32_t base = (uint32_t)out->ent_start.size();
-        const std::vector<uint32_t>& sh = shorts[s];
-        pmax.resize(sh.size());
-        uint32_t pm = 0;
-        for (size_t k = 0; k < sh.size(); k++) {
-            push_entry(sh[k]);
-            pm = std::max(pm, items[sh[k]].end);
-            pmax[k] = pm;
-        }
-        out->seq_send[s] = base + (uint32_t)sh.size();
-        // sentinel: stops every forward scan (start >= any region end) without a bounds check
-        out->ent_start.push_back(0xFFFFFFFFu);
-        out->ent_end.push_back(0);
+        out->ent_start.push_back(0xFFFFFFFFu);  // sentinel: start >= any region end stops every run
+        out->ent_end.push_back(0xFFFFFFFFu);
         out->ent_payload.push_back(0);
         out->ent_item.push_back(0xFFFFFFFFu);
-        // sdir[(w << sub_bits) + b] = first short entry whose inclusive running max-end exceeds the bin's first base
+    }
+    base[n_seqs] = (uint32_t)out->ent_start.size();
+
+    // ---- bin resolution: about 4 bins per interval, at most 2^max_sub per window, lists within max_list ---------
+    uint32_t sub = 0;
+    while (sub < max_sub && sub < shift && ((uint64_t)n_win << sub) < 4ull * std::max<size_t>(items.size(), 1)) sub++;
+    for (;; sub--) {
+        const uint32_t bsh = shift - sub;
+        uint64_t tot = 0;
+        for (const JoinItem& it : items) {
+            const uint32_t last = it.end > it.start ? it.end - 1 : it.start;
+            tot += (uint64_t)(last >> bsh) - (it.start >> bsh) + 1;
+        }
+        if (tot <= max_list || sub == 0) break;
+    }
+    out->sub = sub;
+    const uint32_t nb = 1u << sub, bsh = shift - sub;
+
+    // ---- per window: first[] and the bin lists -----------------------------------------------------
+    out->first.assign((size_t)n_win * (nb + 1), 0);
+    out->boff.assign((size_t)n_win * (nb + 1), 0);
+    std::vector<std::vector<uint32_t>> bins;  // bins of one sequence (all its windows)
+    for (uint32_t s = 0; s < n_seqs; s++) {
+        const uint32_t nw = win0[s + 1] - win0[s];
+        const uint64_t n_bins = (uint64_t)nw << sub;
+        const uint32_t b0 = base[s], cnt = base[s + 1] - base[s] - 1;  // without the sentinel
+        bins.assign((size_t)n_bins, {});
+        for (uint32_t k = 0; k < cnt; k++) {
+            const uint32_t st = out->ent_start[b0 + k], en = out->ent_end[b0 + k];
+            // an interval hits a region iff start < re && end > rs (tree.rs:110), which an EMPTY or inverted interval
+            // (end <= start; never written by `gffx index`, but gffx_index_create takes any arrays) can satisfy too: it is
+            // listed in the bin of its start only.  Intervals starting beyond the grid are reached by the runs alone.
+            if ((uint64_t)(st >> bsh) >= n_bins) continue;
+            const uint64_t bf = st >> bsh, bl = en > st ? std::min<uint64_t>((en - 1) >> bsh, n_bins - 1) : bf;
+            for (uint64_t b = bf; b <= bl; b++) bins[(size_t)b].push_back(b0 + k);
+        }
         size_t j = 0;
-        for (uint32_t w = win0[s]; w < win0[s + 1]; w++) {
-            const uint64_t lo = (uint64_t)(w - win0[s]) << shift;
-            for (uint32_t b = 0; b < (1u << sub_bits); b++) {
-                const uint64_t x = lo + ((uint64_t)b << sub_shift);
-                while (j < sh.size() && (uint64_t)pmax[j] <= x) j++;
-                out->sdir[((size_t)w << sub_bits) + b] = base + (uint32_t)j;
+        for (uint32_t w = 0; w < nw; w++) {
+            const size_t row = (size_t)(win0[s] + w) * (nb + 1);
+            for (uint32_t b = 0; b <= nb; b++) {
+                const uint64_t x = ((uint64_t)w << shift) + ((uint64_t)b << bsh);  // first base of the bin (b == nb: of the next window)
+                while (j < cnt && (uint64_t)out->ent_start[b0 + j] < x) j++;
+                out->first[row + b] = b0 + (uint32_t)j;
+                out->boff[row + b] = (uint32_t)out->list.size();
+                if (b < nb) {
+                    const std::vector<uint32_t>& v = bins[((size_t)w << sub) + b];
+                    out->list.insert(out->list.end(), v.begin(), v.end());
+                }
             }
         }
     }
-    // long entries: unified ids continue after the shorts; per window the ones that overlap it
-    std::vector<std::vector<uint32_t>> per_win(n_win);
-    for (uint32_t s = 0; s < n_seqs; s++) {
-        const uint32_t nw = win0[s + 1] - win0[s];
-        for (uint32_t item : longs[s]) {
-            const uint32_t id = (uint32_t)out->ent_start.size();
-            push_entry(item);
-            const uint32_t st = items[item].start, en = items[item].end;
-            const uint32_t w_first = std::min(st >> shift, nw - 1);
-            const uint32_t w_last = std::min((en > st ? en - 1 : st) >> shift, nw - 1);
-            for (uint32_t w = w_first; w <= w_last; w++) per_win[win0[s] + w].push_back(id);
-        }
-    }
-    out->alw0.assign((size_t)n_win + 1, 0);
-    for (uint32_t w = 0; w < n_win; w++) {
-        out->alw0[w] = (uint32_t)out->alw_id.size();
-        std::vector<uint32_t>& v = per_win[w];
-        std::sort(v.begin(), v.end(), [&](uint32_t a, uint32_t b) {
-            if (out->ent_start[a] != out->ent_start[b]) return out->ent_start[a] < out->ent_start[b];
-            return a < b;
-        });
-        for (uint32_t id : v) {
-            out->alw_start.push_back(out->ent_start[id]);
-            out->alw_end.push_back(out->ent_end[id]);
-            out->alw_id.push_back(id);
-        }
-    }
-    out->alw0[n_win] = (uint32_t)out->alw_id.size();
 }
 
 }  // namespace gffx

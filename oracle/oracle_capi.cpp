@@ -87,6 +87,27 @@ uint64_t orc_n_roots(void* h) {
     return n;
 }
 
+// Pin of IntervalTree::build (src/utils/tree.rs:30-64) + the bincode2 encoding (src/utils/tree_io.rs:37-54)
+// against bytes the reference itself wrote: decode every tree of <gff>.rit, rebuild each tree from its flattened
+// intervals with the restated constructor, encode, and return the concatenation — equal to the file iff both
+// restatements reproduce the reference's.  (Ties in `start` keep their within-node order under the stable sort;
+// across nodes the order cannot change node membership.)
+int orc_reencode_rit(void* hv, uint8_t** out, uint64_t* n) {
+    return guard([&] {
+        Handle* h = (Handle*)hv;
+        std::string bytes;
+        for (uint32_t i = 0; i < h->idx.num_to_seqid.size(); i++) {
+            auto it = h->idx.chr_entries.find(i);
+            if (it == h->idx.chr_entries.end()) { bytes.push_back('\0'); continue; }
+            IntervalTree t = IntervalTree::from_intervals(it->second.flatten());
+            encode_opt_node(t.root.get(), bytes);
+        }
+        uint8_t* p = (uint8_t*)malloc(std::max<size_t>(1, bytes.size()));
+        memcpy(p, bytes.data(), bytes.size());
+        *out = p; *n = bytes.size();
+    });
+}
+
 // Flattened tree intervals of one sequence (for cross-checks of the product's own .rit decoder).
 int orc_seq_intervals(void* hv, uint32_t seq, uint32_t** out, uint64_t* n) {
     return guard([&] {

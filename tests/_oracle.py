@@ -25,6 +25,7 @@ _lib.orc_parse_bed_dc.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(_u32p), _u64
 _lib.orc_query_features.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.POINTER(_u32p), _u64p]
 _lib.orc_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_char_p,
                                C.POINTER(_u64p), _u64p, _u64p, _u64p]
+_lib.orc_reencode_rit.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), _u64p]
 _lib.orc_depth.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.POINTER(C.c_void_p), _u64p]
 _lib.orc_coverage.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), _u64p]
 
@@ -93,6 +94,15 @@ class Oracle:
         p, n = _u32p(), C.c_uint64()
         _check(_lib.orc_seq_intervals(self._h, seq, C.byref(p), C.byref(n)))
         return _take_triples(p, n.value)
+
+    def reencode_rit(self) -> bytes:
+        """the index's trees rebuilt by the restated IntervalTree::new and re-serialised (must equal the .rit file)"""
+        p, n = C.c_void_p(), C.c_uint64()
+        _check(_lib.orc_reencode_rit(self._h, C.byref(p), C.byref(n)))
+        try:
+            return C.string_at(p, n.value)
+        finally:
+            _lib.orc_free(p)
 
     def parse_bed_intersect(self, bed):
         p, n = _u32p(), C.c_uint64()

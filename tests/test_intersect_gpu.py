@@ -149,3 +149,26 @@ def test_cli_run_writes_the_same_file_as_the_oracle(gffx, quirk, tmp_path):
         mode = 0 if kw.get("contained") else 1 if kw.get("contains_region") else 2
         want, _, _ = o.intersect(o.parse_bed_intersect(str(bed)), mode, kw.get("invert", False), kw.get("entire_group", False), kw.get("types"))
         assert out.read_bytes() == b"".join(text[s:e] for s, e in want.tolist())
+
+
+@pytest.mark.parametrize("sub", ["0", "3"])
+def test_join_coarse_bins_overflow_the_slice(gffx, synth_quirk_gff, sub, monkeypatch):
+    """GFFX_WJ_SUB caps the bins per window of the K1 index (winjoin_build.h): with one or eight bins per window the
+    lists outgrow both the 16 position bits of the hit masks and the shared-memory slice, so the global-memory tails
+    and the second walk of the emit pass are exercised.  Same pairs, same ranges."""
+    monkeypatch.setenv("GFFX_WJ_SUB", sub)
+    idx = gffx.TreeIndexData.load_tree_index(synth_quirk_gff, device=0)
+    try:
+        with Oracle(synth_quirk_gff) as o:
+            regs = mixed_regions(idx, 777, 4000)
+            for mode, invert in MODES:
+                r = idx.query_features(regs, mode, invert)
+                want = o.query_features(regs, mode, invert)
+                got = r.pairs if r.pairs is not None else np.zeros((0, 3), dtype=np.uint32)
+                assert np.array_equal(sorted_pairs(got), sorted_pairs(want))
+                ri = idx.intersect(regs, mode, invert, False, None)
+                want_ranges, n_pairs, _ = o.intersect(regs, mode, invert, False, None)
+                assert ri.n_pairs == n_pairs
+                assert np.array_equal(ri.ranges, want_ranges)
+    finally:
+        idx.close()

@@ -100,3 +100,17 @@ def test_oracle_on_reference_index_files(ps_index, case):
         assert p.shape[0] == want["pairs"]
         assert len(np.unique(p[:, 0])) == want["roots"]
         assert pair_checksum(p) == want["checksum"]
+
+
+def test_oracle_tree_build_reproduces_reference_rit_bytes(ps_index):
+    """Reference-written bytes as the golden vector: the restated IntervalTree::new (src/utils/tree.rs:30-64) + bincode2
+    encoder (src/utils/tree_io.rs:37-54), fed the decoded intervals of the reference's own ps.gff.rit, must write the
+    very same file (also true for benchmark/at and benchmark/dm, checked when /root/reference is present)."""
+    gff, _ = ps_index
+    with Oracle(gff) as o:
+        assert o.reencode_rit() == open(gff + ".rit", "rb").read()
+    for ds in ("at", "dm"):
+        ref = f"/root/reference/benchmark/{ds}.gff"
+        if os.path.exists(ref + ".rit") and os.path.exists(ref + ".gof"):
+            with Oracle(ref) as o:
+                assert o.reencode_rit() == open(ref + ".rit", "rb").read()
