@@ -229,7 +229,8 @@ def run_gpu(args, rank, world, local_rank):
 
     def step(sets, flags, acc=None):
         for (name, mode, inv), regs in zip(PASSES, sets):
-            r = idx.intersect(regs, mode, inv, False, None, flags=flags)
+            # copy=False: the byte ranges stay in the result's page-locked buffer (what a Rust caller of the C ABI reads too)
+            r = idx.intersect(regs, mode, inv, False, None, flags=flags, copy=False)
             if acc is not None:
                 a = acc.setdefault(name, {"calls": 0, "pairs": 0, "ranges": 0, "roots": 0, "launches": 0, "kernel_ms": 0.0, "stage_ms": [0.0] * 12})
                 a["calls"] += 1
@@ -240,6 +241,7 @@ def run_gpu(args, rank, world, local_rank):
                 a["kernel_ms"] += r.kernel_ms
                 for s in range(12):
                     a["stage_ms"][s] += r.stage_ms[s]
+            r.close()
 
     # ---- device-resident arm: K steps between two events on the engine's stream --------------------
     for _ in range(args.warmup):

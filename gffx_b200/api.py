@@ -81,22 +81,43 @@ class Result:
     kernel_ms: float = 0.0
     stage_ms: Tuple[float, ...] = ()
     launches: int = 0
+    _h: object = None  # the C result handle when `pairs` / `ranges` are zero-copy views of library-owned (pinned) memory
+
+    def close(self):
+        """release the library-owned arrays behind zero-copy `pairs` / `ranges` views (they must not be used afterwards)"""
+        if self._h is not None:
+            h, self._h = self._h, None
+            self.pairs = self.ranges = None
+            lib.gffx_result_free(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
-def _take_result(h) -> Result:
+def _take_result(h, copy: bool = True) -> Result:
+    """copy=False: `pairs` / `ranges` are views of the result's page-locked buffers, valid until Result.close() (or its
+    collection); the default copies them into ordinary numpy arrays and frees the handle at once."""
+    done = False
     try:
         r = Result()
         r.n_queries = lib.gffx_result_n_queries(h)
         r.n_pairs = lib.gffx_result_n_pairs(h)
         p = lib.gffx_result_pairs(h)
         if p and r.n_pairs:
-            r.pairs = np.ctypeslib.as_array(p, shape=(r.n_pairs, 3)).copy()
+            r.pairs = np.ctypeslib.as_array(p, shape=(r.n_pairs, 3))
+            if copy:
+                r.pairs = r.pairs.copy()
         r.pairs_device_ptr = lib.gffx_result_pairs_device(h) or 0
         r.n_roots = lib.gffx_result_n_roots(h)
         r.n_ranges = lib.gffx_result_n_ranges(h)
         q = lib.gffx_result_ranges(h)
         if q and r.n_ranges:
-            r.ranges = np.ctypeslib.as_array(q, shape=(r.n_ranges, 2)).copy()
+            r.ranges = np.ctypeslib.as_array(q, shape=(r.n_ranges, 2))
+            if copy:
+                r.ranges = r.ranges.copy()
         elif r.n_ranges == 0:
             r.ranges = np.zeros((0, 2), dtype=np.uint64)
         r.bytes_out = lib.gffx_result_bytes_out(h)
@@ -106,9 +127,13 @@ def _take_result(h) -> Result:
         r.kernel_ms = lib.gffx_result_kernel_ms(h)
         r.stage_ms = tuple(lib.gffx_result_stage_ms(h, k) for k in range(12))
         r.launches = lib.gffx_result_launches(h)
+        if not copy:
+            r._h = h
+            done = True
         return r
     finally:
-        lib.gffx_result_free(h)
+        if not done:
+            lib.gffx_result_free(h)
 
 
 class TreeIndexData:
@@ -221,17 +246,17 @@ class TreeIndexData:
 
     # -- compute --------------------------------------------------------------------------
     def query_features(self, regions, mode: OverlapMode = OverlapMode.Overlap, invert: bool = False, *, want_pairs: bool = True,
-                       flags: int = 0) -> Result:
+                       flags: int = 0, copy: bool = True) -> Result:
         """src/commands/intersect.rs:105-169"""
         keep: list = []
         pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
         f |= flags | (_lib.F_WANT_PAIRS if want_pairs else 0)
         h = C.c_void_p()
         _check(lib.gffx_query_features(self._h, pc, ps, pe, n, int(mode), int(bool(invert)), f, C.byref(h)))
-        return _take_result(h)
+        return _take_result(h, copy)
 
     def intersect(self, regions, mode: OverlapMode = OverlapMode.Overlap, invert: bool = False, entire_group: bool = False,
-                  types: Optional[str] = None, *, want_pairs: bool = False, flags: int = 0) -> Result:
+                  types: Optional[str] = None, *, want_pairs: bool = False, flags: int = 0, copy: bool = True) -> Result:
         """run() after BED parsing, src/commands/intersect.rs:586-654"""
         keep: list = []
         pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
@@ -239,7 +264,7 @@ class TreeIndexData:
         h = C.c_void_p()
         _check(lib.gffx_intersect(self._h, pc, ps, pe, n, int(mode), int(bool(invert)), int(bool(entire_group)),
                                   types.encode() if types is not None else None, f, C.byref(h)))
-        return _take_result(h)
+        return _take_result(h, copy)
 
     def write_ranges(self, ranges: np.ndarray, out_path: Optional[str]):
         r = np.ascontiguousarray(ranges, dtype=np.uint64)

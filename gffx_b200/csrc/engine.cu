@@ -1,6 +1,7 @@
 // engine.cu — index upload and the intersect pipeline (join -> block select -> line filter / merge).
 #include <algorithm>
 #include <numeric>
+#include <mutex>
 #include "engine_impl.cuh"
 #include "synth_common.h"
 
@@ -36,6 +37,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     if (prop.major < 10) throw Err(E_CUDA, std::string("device ") + prop.name + " is not sm_100-class; the kernels are built for sm_100a only");
     sm_count = prop.multiProcessorCount;
     GFFX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    GFFX_CUDA(cudaStreamCreateWithFlags(&st_copy, cudaStreamNonBlocking));
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
@@ -68,6 +70,9 @@ EngineImpl::~EngineImpl() {
     counts_release(this);
     if (h_small) cudaFreeHost(h_small);
     for (auto& x : ev) cudaEventDestroy(x);
+    for (auto& x : ev_chunk) cudaEventDestroy(x);
+    for (auto& x : ev_copy) cudaEventDestroy(x);
+    if (st_copy) cudaStreamDestroy(st_copy);
     if (st) cudaStreamDestroy(st);
 }
 
@@ -103,12 +108,23 @@ uint32_t EngineImpl::partition(const uint32_t* dc, const uint32_t* ds, const uin
                                const uint2** bse) {
     *bchr = nullptr; *bse = nullptr;
     if (n == 0) return 0;
+    d_bchr.ensure(n * 4 + 16);
+    d_bse.ensure(n * 8 + 32);
+    const uint32_t launches = partition_into(dc, ds, de, n, d_bchr.as<uint32_t>(), d_bse.as<uint2>(), d_poff.as<uint32_t>());
+    *bchr = d_bchr.as<uint32_t>();
+    *bse = d_bse.as<uint2>();
+    return launches;
+}
+
+// the same pass with caller-chosen outputs: `oc`/`ose` take the n bucketed regions, `poff` the n_win + 2 window offsets.
+// The count matrix and its scan are scratch that the NEXT call on the stream reuses (stream order keeps that safe).
+uint32_t EngineImpl::partition_into(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, uint32_t* oc, uint2* ose,
+                                    uint32_t* poff) {
+    if (n == 0) return 0;
     if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
     const uint32_t nb = WG.n_win + 1;
     const unsigned tiles = (unsigned)((n + PART_TILE - 1) / PART_TILE);
     const uint64_t cells = (uint64_t)nb * tiles;
-    d_bchr.ensure(n * 4 + 16);
-    d_bse.ensure(n * 8 + 32);
     d_pmat.ensure(cells * 4);
     d_pscan.ensure(cells * 4);
     d_pscratch.ensure(scan_scratch_elems(cells) * 4);
@@ -117,10 +133,8 @@ uint32_t EngineImpl::partition(const uint32_t* dc, const uint32_t* ds, const uin
     launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, false>(
         PtrLoad<uint32_t>{d_pmat.as<uint32_t>()}, PtrStore<uint32_t>{d_pscan.as<uint32_t>()}, cells, OpSum(), 0u, d_pscratch.as<uint32_t>(), nullptr, st);
     part_scatter_kernel<<<tiles, PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, tiles, d_pmat.as<uint32_t>(), d_pscan.as<uint32_t>(),
-                                                         d_bchr.as<uint32_t>(), d_bse.as<uint2>());
-    part_offsets_kernel<<<(nb + 1 + 255) / 256, 256, 0, st>>>(d_pscan.as<uint32_t>(), nb, tiles, (uint32_t)n, d_poff.as<uint32_t>());
-    *bchr = d_bchr.as<uint32_t>();
-    *bse = d_bse.as<uint2>();
+                                                                       oc, ose);
+    part_offsets_kernel<<<(nb + 1 + 255) / 256, 256, 0, st>>>(d_pscan.as<uint32_t>(), nb, tiles, (uint32_t)n, poff);
     return launches + 2;
 }
 
@@ -288,6 +302,63 @@ void EngineImpl::build_lines() {
     LA.n = n;
 }
 
+// ---- pinned host pool ---------------------------------------------------------------------------
+namespace {
+struct PinnedPool {
+    std::mutex mu;
+    std::vector<std::pair<void*, size_t>> free_list;
+    size_t pooled = 0;
+    static constexpr size_t MAX_POOLED = 4ull << 30;
+    ~PinnedPool() {
+        // the CUDA context may already be gone at process exit: leave the blocks to the driver
+    }
+};
+PinnedPool& pinned_pool() {
+    static PinnedPool* P = new PinnedPool();  // never destroyed: results may outlive static destruction order
+    return *P;
+}
+}  // namespace
+
+void* pinned_acquire(size_t bytes, size_t* cap) {
+    PinnedPool& P = pinned_pool();
+    {
+        std::lock_guard<std::mutex> g(P.mu);
+        size_t best = SIZE_MAX;
+        for (size_t i = 0; i < P.free_list.size(); i++)
+            if (P.free_list[i].second >= bytes && (best == SIZE_MAX || P.free_list[i].second < P.free_list[best].second)) best = i;
+        if (best != SIZE_MAX && P.free_list[best].second <= 4 * std::max<size_t>(bytes, 1 << 20)) {
+            auto b = P.free_list[best];
+            P.free_list.erase(P.free_list.begin() + (long)best);
+            P.pooled -= b.second;
+            *cap = b.second;
+            return b.first;
+        }
+    }
+    size_t want = std::max<size_t>(bytes, 1 << 16);
+    want = (want + (want >> 3) + 0xFFFF) & ~(size_t)0xFFFF;  // 12 % slack: a slightly larger next result reuses the block
+    void* p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocPortable);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        throw Err(E_CUDA, std::string("cudaHostAlloc failed: ") + cudaGetErrorString(e));
+    }
+    *cap = want;
+    return p;
+}
+
+void pinned_release(void* p, size_t cap) {
+    PinnedPool& P = pinned_pool();
+    {
+        std::lock_guard<std::mutex> g(P.mu);
+        if (P.pooled + cap <= PinnedPool::MAX_POOLED && P.free_list.size() < 64) {
+            P.free_list.emplace_back(p, cap);
+            P.pooled += cap;
+            return;
+        }
+    }
+    cudaFreeHost(p);
+}
+
 void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                                const uint32_t** dc, const uint32_t** ds, const uint32_t** de) {
     if (flags & 1u) {  // GFFX_F_DEVICE_INPUT
@@ -303,97 +374,68 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
 }
 
 template <int MODE, bool INV>
-static void launch_wj(EngineImpl* E, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs,
-                      unsigned long long cap, uint32_t* err) {
-    const uint32_t* poff = E->d_poff.as<uint32_t>();
+static void launch_wj(EngineImpl* E, bool emit, const uint32_t* poff, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles,
+                      unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
     if (emit)
         wj_join_kernel<MODE, INV, true><<<tiles, WJ_THREADS, 0, E->st>>>(E->WC, poff, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, E->d_pairs.as<uint32_t>(), cap, err);
     else
         wj_join_kernel<MODE, INV, false><<<tiles, WJ_THREADS, 0, E->st>>>(E->WC, poff, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, nullptr, 0, err);
 }
-static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool emit, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles,
-                           unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
+static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool emit, const uint32_t* poff, const uint32_t* c, const uint2* se, uint64_t n,
+                           unsigned tiles, unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
     switch (mode * 2 + (invert ? 1 : 0)) {
-        case 0: launch_wj<0, false>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
-        case 1: launch_wj<0, true>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
-        case 2: launch_wj<1, false>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
-        case 3: launch_wj<1, true>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
-        default: launch_wj<2, false>(E, emit, c, se, n, tiles, n_pairs, cap, err); break;
+        case 0: launch_wj<0, false>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
+        case 1: launch_wj<0, true>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
+        case 2: launch_wj<1, false>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
+        case 3: launch_wj<1, true>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
+        default: launch_wj<2, false>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
     }
 }
 
-void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
-                           bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out) {
+// ------------------------------------------------------------------------------------------------
+// One intersect JOB = ix_begin, any number of ix_add (each a batch of device-resident regions: K0 partition, K1 join,
+// K3a scatter onto the line rank space — all of them accumulate), ix_finish (root -> block selection, rank-space scans,
+// line filter, ordered compaction, read-back).  gffx_intersect is one job whose batches are the chunks of the host ->
+// device copy (the copy of chunk i+1 overlaps the kernels of chunk i); the shard API (gffx_shard_*) exposes the three
+// steps so that the accumulators of several GPUs can be combined before ix_finish.
+void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags, bool join_only,
+                          uint64_t n_retained, uint32_t n_chunks) {
     if (mode < 0 || mode > 2) throw Err(E_ARG, "mode must be 0 (contained), 1 (contains-region) or 2 (overlap)");
-    if (n && (!chr || !start || !end)) throw Err(E_ARG, "NULL region arrays");
-    if (n >= (1ull << 40)) throw Err(E_ARG, "too many regions in one call");
     GFFX_CUDA(cudaSetDevice(dev));
-    *out = IntersectResult();
-    out->n_queries = n;
-    const bool want_pairs_host = flags & 2u, pairs_dev = (flags & 8u) || want_pairs_host, no_host = flags & 4u;
-    uint32_t launches = 0;
-    bool emitted = false;
-    const uint32_t *dc, *ds, *de;
-    stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
-    unsigned long long* small = d_small.as<unsigned long long>();  // [0] n_pairs [1..3] merge counts [4] bytes_out [5] n_emit (u64); u32 view: [12] err [13] n_warn
-    uint32_t* small32 = d_small.as<uint32_t>();
+    IxJob& jb = job;
+    jb = IxJob();
+    jb.mode = mode; jb.invert = invert; jb.entire_group = entire_group; jb.join_only = join_only;
+    jb.want_pairs_host = flags & 2u;
+    jb.pairs_dev = (flags & 8u) || jb.want_pairs_host;
+    jb.no_host = flags & 4u;
+    jb.match_only = !entire_group || types_csv != nullptr;  // intersect.rs:619
+    jb.nothing = (mode == 2 && invert) || wj_n_ent == 0;    // -I with overlap selects nothing (intersect.rs:161)
+    jb.run_filter = !jb.nothing && !join_only && jb.match_only && LA.n > 0;
+    jb.have_types = types_csv != nullptr;
+    jb.retained = n_retained;
+    jb.active = true;
+    while (ev_chunk.size() < 4 * (size_t)std::max<uint32_t>(n_chunks, 1)) {
+        cudaEvent_t e;
+        GFFX_CUDA(cudaEventCreate(&e));
+        ev_chunk.push_back(e);
+    }
+    if (n_retained) {  // the bucketed form of every batch is kept (a too-small pair buffer re-runs the join)
+        d_bchr.ensure(n_retained * 4 + 16);
+        d_bse.ensure(n_retained * 8 + 32);
+    }
+    d_poff.ensure((size_t)std::max<uint32_t>(n_chunks, 1) * (WG.n_win + 2) * 4);
     GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 256, st));
     GFFX_CUDA(cudaEventRecord(ev[0], st));
-    const bool nothing = (mode == 2 && invert) || n == 0 || n_ent == 0;  // -I with overlap selects nothing (intersect.rs:161)
-    const uint32_t* bc = nullptr;  // window-bucketed regions (partition.cuh)
-    const uint2* bse = nullptr;
-    if (!nothing) launches += partition(dc, ds, de, n, &bc, &bse);
-    GFFX_CUDA(cudaEventRecord(ev[10], st));
-
-    // ---- stage 0: join (one fused kernel: search, CTA scan, tile range claim, staged emit) --------
-    const unsigned tiles = (unsigned)((n + WJ_TILE - 1) / WJ_TILE);
     if (wj_n_ent) GFFX_CUDA(cudaMemsetAsync(d_wj_hit.p, 0, wj_n_ent, st));
-    unsigned long long pair_cap = 0;
-    if (!nothing) {
-        d_scan_scratch.ensure(scan_scratch_elems(LA.n / LINE_THREADS + 1) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
-        if (pairs_dev) {
-            d_pairs.ensure(std::max<uint64_t>(2 * n, 1024) * 12);  // grow-only; a larger result re-runs the kernel below
-            pair_cap = d_pairs.cap / 12;
-        }
-        launch_wj_mode(this, mode, invert, pairs_dev, bc, bse, n, tiles, small, pair_cap, small32 + 12);
-        launches++;
-    }
-    GFFX_CUDA(cudaEventRecord(ev[1], st));
-    GFFX_CUDA(cudaEventRecord(ev[2], st));
-    GFFX_CUDA(cudaEventRecord(ev[3], st));
-
-    // ---- stage 1: root -> block selection, merged ranges (-e) ---------------------------------
-    const bool match_only = !entire_group || types_csv != nullptr;  // intersect.rs:619
-    if (n_blocks) GFFX_CUDA(cudaMemsetAsync(d_blk_sel.p, 0, n_blocks, st));
-    if (!nothing) {
-        wj_select_blocks_kernel<<<(wj_n_ent + 255) / 256, 256, 0, st>>>(d_wj_hit.as<uint8_t>(), d_wj_blk.as<uint32_t>(), WC.ent_fid, wj_n_ent,
-                                                                       d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
-        launches++;
-        if (n_blocks) {
-            if (!match_only && !join_only)
-                merge_blocks_kernel<<<1, 1024, 0, st>>>(d_bstart.as<uint64_t>(), d_bend.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks,
-                                                       H->gff_len, true, d_ranges.as<ulonglong2>(), small + 1);
-            else
-                count_selected_kernel<<<(n_blocks + 255) / 256, 256, 0, st>>>(d_bstart.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks, small + 1);
-            launches++;
-        }
-    }
-    GFFX_CUDA(cudaEventRecord(ev[4], st));
-
-    // ---- stages 4-6: line filter ---------------------------------------------------------------
-    uint64_t n_emit_tiles = 0;
-    const bool run_filter = !nothing && !join_only && match_only && LA.n > 0;
-    if (run_filter) {
-        // -T: comma-split, trimmed, non-empty tokens (intersect.rs:252-259)
-        const bool have_types = types_csv != nullptr;
-        if (have_types) {
+    if (jb.run_filter) {
+        if (jb.have_types) {  // -T: comma-split, trimmed, non-empty tokens (intersect.rs:252-259)
             std::vector<uint8_t> allow(std::max<size_t>(H->types.size(), 1), 0);
-            std::string_view s(types_csv);
+            std::string_view sv(types_csv);
             size_t i = 0;
-            while (i <= s.size()) {
-                size_t j = s.find(',', i);
-                if (j == std::string_view::npos) j = s.size();
-                std::string_view t = trim_unicode(s.substr(i, j - i));
+            while (i <= sv.size()) {
+                size_t j = sv.find(',', i);
+                if (j == std::string_view::npos) j = sv.size();
+                std::string_view t = trim_unicode(sv.substr(i, j - i));
                 if (!t.empty()) {
                     int64_t id = H->types.find(t);
                     if (id >= 0) allow[(size_t)id] = 1;
@@ -403,7 +445,6 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             GFFX_CUDA(cudaMemcpyAsync(d_type_allow.p, allow.data(), allow.size(), cudaMemcpyHostToDevice, st));
             GFFX_CUDA(cudaStreamSynchronize(st));  // `allow` is a stack-local
         }
-        FilterArrays F{d_A.as<unsigned long long>(), d_B.as<unsigned long long>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
         const uint64_t ns = f_slots;
         if (mode == 0 || mode == 2) GFFX_CUDA(cudaMemsetAsync(d_A.p, 0, ns * 8, st));
         if (mode == 1) GFFX_CUDA(cudaMemsetAsync(d_B.p, 0xFF, ns * 8, st));
@@ -411,14 +452,95 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
             GFFX_CUDA(cudaMemsetAsync(d_Ms.p, 0, ns * 2, st));
             GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
         }
-        const unsigned sblocks = (unsigned)((n + (uint64_t)FILT_THREADS * FILT_QPT - 1) / ((uint64_t)FILT_THREADS * FILT_QPT));
-        if (mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n, WG.shift > 8 ? WG.shift - 8 : 0);
-        else if (mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n, WG.shift > 8 ? WG.shift - 8 : 0);
-        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, bc, bse, n, WG.shift > 8 ? WG.shift - 8 : 0);
-        launches++;
-        GFFX_CUDA(cudaEventRecord(ev[5], st));
+    }
+}
 
+// regions already on the device; asynchronous on the engine's stream
+void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n) {
+    IxJob& jb = job;
+    if (!jb.active) throw Err(E_STATE, "intersect batch without a job");
+    if (n == 0) return;
+    if (jb.n_total + n >= (1ull << 40)) throw Err(E_ARG, "too many regions in one job");
+    const uint32_t slot = (uint32_t)jb.chunks.size();
+    const bool timed = 4 * (size_t)slot + 3 < ev_chunk.size();
+    IxChunk ck;
+    ck.n = n;
+    ck.off = jb.retained ? jb.n_total : 0;
+    if (jb.retained) {
+        if (jb.n_total + n > jb.retained) throw Err(E_STATE, "more regions than announced at the job's begin");
+        if ((size_t)(slot + 1) * (WG.n_win + 2) * 4 > d_poff.cap) throw Err(E_STATE, "more batches than announced at the job's begin");
+    } else {
+        d_bchr.ensure(n * 4 + 16);
+        d_bse.ensure(n * 8 + 32);
+    }
+    uint32_t* oc = d_bchr.as<uint32_t>() + ck.off;
+    uint2* ose = d_bse.as<uint2>() + ck.off;
+    uint32_t* poff = d_poff.as<uint32_t>() + (jb.retained ? (size_t)slot * (WG.n_win + 2) : 0);
+    jb.n_total += n;
+    jb.chunks.push_back(ck);
+    if (jb.nothing) return;
+    unsigned long long* small = d_small.as<unsigned long long>();
+    uint32_t* small32 = d_small.as<uint32_t>();
+    if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot], st));
+    jb.launches += partition_into(dc, ds, de, n, oc, ose, poff);
+    if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 1], st));
+    if (jb.pairs_dev && jb.pair_cap == 0) {
+        d_pairs.ensure(std::max<uint64_t>(2 * std::max<uint64_t>(jb.retained, n), 1024) * 12);  // grow-only; a larger result re-runs the join
+        jb.pair_cap = d_pairs.cap / 12;
+    }
+    const unsigned tiles = (unsigned)((n + WJ_TILE - 1) / WJ_TILE);
+    launch_wj_mode(this, jb.mode, jb.invert, jb.pairs_dev, poff, oc, ose, n, tiles, small, jb.pair_cap, small32 + 12);
+    jb.launches++;
+    if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 2], st));
+    if (jb.run_filter) {
+        FilterArrays F{d_A.as<unsigned long long>(), d_B.as<unsigned long long>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
+        const unsigned sblocks = (unsigned)((n + (uint64_t)FILT_THREADS * FILT_QPT - 1) / ((uint64_t)FILT_THREADS * FILT_QPT));
+        const uint32_t ks = WG.shift > 8 ? WG.shift - 8 : 0;
+        if (jb.mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, oc, ose, n, ks);
+        else if (jb.mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, oc, ose, n, ks);
+        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, oc, ose, n, ks);
+        jb.launches++;
+    }
+    if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 3], st));
+}
+
+void EngineImpl::ix_finish(IntersectResult* out) {
+    IxJob& jb = job;
+    if (!jb.active) throw Err(E_STATE, "intersect finish without a job");
+    jb.active = false;
+    GFFX_CUDA(cudaSetDevice(dev));
+    *out = IntersectResult();
+    out->n_queries = jb.n_total;
+    const int mode = jb.mode;
+    const bool nothing = jb.nothing || jb.n_total == 0;
+    uint32_t launches = jb.launches;
+    unsigned long long* small = d_small.as<unsigned long long>();  // [0] n_pairs [1..3] merge counts [4] bytes_out [5] n_emit (u64); u32 view: [12] err [13] n_warn
+    uint32_t* small32 = d_small.as<uint32_t>();
+    GFFX_CUDA(cudaEventRecord(ev[3], st));
+
+    // ---- root -> block selection, merged ranges (-e) --------------------------------------------
+    if (n_blocks) GFFX_CUDA(cudaMemsetAsync(d_blk_sel.p, 0, n_blocks, st));
+    if (!nothing) {
+        d_scan_scratch.ensure(scan_scratch_elems(LA.n / LINE_THREADS + 1) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
+        wj_select_blocks_kernel<<<(wj_n_ent + 255) / 256, 256, 0, st>>>(d_wj_hit.as<uint8_t>(), d_wj_blk.as<uint32_t>(), WC.ent_fid, wj_n_ent,
+                                                                       d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
+        launches++;
+        if (n_blocks) {
+            if (!jb.match_only && !jb.join_only)
+                merge_blocks_kernel<<<1, 1024, 0, st>>>(d_bstart.as<uint64_t>(), d_bend.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks,
+                                                       H->gff_len, true, d_ranges.as<ulonglong2>(), small + 1);
+            else
+                count_selected_kernel<<<(n_blocks + 255) / 256, 256, 0, st>>>(d_bstart.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks, small + 1);
+            launches++;
+        }
+    }
+    GFFX_CUDA(cudaEventRecord(ev[4], st));
+
+    // ---- line filter: rank-space scans, per-line decision, ordered compaction --------------------
+    if (jb.run_filter && !nothing) {
         typedef unsigned long long ull;
+        const uint64_t ns = f_slots;
+        FilterArrays F{d_A.as<ull>(), d_B.as<ull>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
         ull* scr = d_scan_scratch.as<ull>();
         FilterScans P{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>()};
         if (mode == 0 || mode == 2)
@@ -438,14 +560,15 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
         }
         GFFX_CUDA(cudaEventRecord(ev[6], st));
 
-        n_emit_tiles = (LA.n + LINE_THREADS - 1) / LINE_THREADS;
+        const uint64_t n_emit_tiles = (LA.n + LINE_THREADS - 1) / LINE_THREADS;
         d_tile_count.ensure(n_emit_tiles * 4);
         d_tile_off.ensure(n_emit_tiles * 8);
         const uint8_t* sel = d_blk_sel.as<uint8_t>();
         const uint8_t* ta = d_type_allow.as<uint8_t>();
-        if (mode == 0) eval_lines_kernel<0><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, have_types, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
-        else if (mode == 1) eval_lines_kernel<1><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, have_types, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
-        else eval_lines_kernel<2><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, have_types, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        const bool ht = jb.have_types;
+        if (mode == 0) eval_lines_kernel<0><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        else if (mode == 1) eval_lines_kernel<1><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        else eval_lines_kernel<2><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         launches++;
         launches += device_scan<uint64_t, OpSum, TileCountLoad, PtrStore<uint64_t>, false, false>(
             TileCountLoad{d_tile_count.as<uint32_t>()}, PtrStore<uint64_t>{d_tile_off.as<uint64_t>()}, n_emit_tiles, OpSum(), 0ull,
@@ -456,7 +579,6 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
                                                                           d_ranges.as<ulonglong2>(), small + 4);
         launches++;
     } else {
-        GFFX_CUDA(cudaEventRecord(ev[5], st));
         GFFX_CUDA(cudaEventRecord(ev[6], st));
     }
     GFFX_CUDA(cudaEventRecord(ev[7], st));
@@ -472,17 +594,22 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     const uint32_t* hs32 = (const uint32_t*)h_small;
     if (hs32[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
     out->n_pairs = hs[0];
-    if (pairs_dev && out->n_pairs > pair_cap) {
-        // the pair buffer was too small for this result: grow it to the exact size and run the join again
-        // (hit flags are idempotent; only the pair counter restarts)
+    if (jb.pairs_dev && out->n_pairs > jb.pair_cap) {
+        // the pair buffer was too small for this result: grow it to the exact size and run the join again over the
+        // retained bucketed batches (hit flags are idempotent; only the pair counter restarts)
+        if (!jb.retained) throw Err(E_STATE, "pair buffer overflow in a streaming job");
         d_pairs.ensure(out->n_pairs * 12);
         GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 8, st));
-        launch_wj_mode(this, mode, invert, true, bc, bse, n, tiles, small, d_pairs.cap / 12, small32 + 12);
-        launches++;
+        for (size_t k = 0; k < jb.chunks.size(); k++) {
+            const IxChunk& ck = jb.chunks[k];
+            launch_wj_mode(this, mode, jb.invert, true, d_poff.as<uint32_t>() + k * (WG.n_win + 2), d_bchr.as<uint32_t>() + ck.off,
+                           d_bse.as<uint2>() + ck.off, ck.n, (unsigned)((ck.n + WJ_TILE - 1) / WJ_TILE), small, d_pairs.cap / 12, small32 + 12);
+            launches++;
+        }
         GFFX_CUDA(cudaStreamSynchronize(st));
         GFFX_CUDA(cudaGetLastError());
     }
-    if (pairs_dev && out->n_pairs) { out->d_pairs = d_pairs.as<uint32_t>(); emitted = true; }
+    if (jb.pairs_dev && out->n_pairs) out->d_pairs = d_pairs.as<uint32_t>();
     const uint32_t n_warn = std::min<uint32_t>(hs32[13], WARN_CAP);
     if (n_warn) {
         std::vector<uint32_t> w(n_warn);
@@ -492,33 +619,78 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
         out->warn_fids = std::move(w);
     }
     out->n_roots = hs[2] + out->warn_fids.size();
-    if (!join_only && !nothing) {
-        if (match_only) { out->n_ranges = hs[5]; out->bytes_out = hs[4]; }
+    if (!jb.join_only && !nothing) {
+        if (jb.match_only) { out->n_ranges = hs[5]; out->bytes_out = hs[4]; }
         else { out->n_ranges = hs[1]; out->bytes_out = hs[3]; }
     }
-    if (out->n_ranges && !no_host) {
+    if (out->n_ranges && !jb.no_host) {
         out->ranges.resize(out->n_ranges * 2);
         GFFX_CUDA(cudaMemcpyAsync(out->ranges.data(), d_ranges.p, out->n_ranges * 16, cudaMemcpyDeviceToHost, st));
     }
-    if (want_pairs_host && out->n_pairs && !no_host) {
+    if (jb.want_pairs_host && out->n_pairs && !jb.no_host) {
         out->pairs.resize(out->n_pairs * 3);
         GFFX_CUDA(cudaMemcpyAsync(out->pairs.data(), d_pairs.p, out->n_pairs * 12, cudaMemcpyDeviceToHost, st));
     }
     GFFX_CUDA(cudaStreamSynchronize(st));
+    // per-stage device time: the batches' partition / join / scatter intervals add up; the rest is measured once
     float ms;
-    for (int k = 0; k < 7; k++) {
-        GFFX_CUDA(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
-        out->stage_ms[k] = ms;
+    for (size_t k = 0; k < jb.chunks.size() && 4 * k + 3 < ev_chunk.size() && !jb.nothing; k++) {
+        GFFX_CUDA(cudaEventElapsedTime(&ms, ev_chunk[4 * k], ev_chunk[4 * k + 1]));
+        out->stage_ms[8] += ms;
+        GFFX_CUDA(cudaEventElapsedTime(&ms, ev_chunk[4 * k + 1], ev_chunk[4 * k + 2]));
+        out->stage_ms[0] += ms;
+        GFFX_CUDA(cudaEventElapsedTime(&ms, ev_chunk[4 * k + 2], ev_chunk[4 * k + 3]));
+        out->stage_ms[4] += ms;
     }
-    (void)emitted;
-    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[10]));
-    out->stage_ms[8] = ms;
-    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[10], ev[1]));
-    out->stage_ms[0] = ms;
-    if (pairs_dev) out->stage_ms[7] = ms;
+    if (jb.pairs_dev) out->stage_ms[7] = out->stage_ms[0];
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[3], ev[4]));
+    out->stage_ms[3] = ms;
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[4], ev[6]));
+    out->stage_ms[5] = ms;
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[6], ev[7]));
+    out->stage_ms[6] = ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[7]));
     out->kernel_ms = ms;
     out->launches = launches;
+}
+
+void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
+                           bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out) {
+    if (n && (!chr || !start || !end)) throw Err(E_ARG, "NULL region arrays");
+    if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
+    GFFX_CUDA(cudaSetDevice(dev));
+    const bool dev_in = flags & 1u;  // GFFX_F_DEVICE_INPUT
+    // host input: the copy is cut into chunks so that chunk i+1 crosses PCIe while chunk i is partitioned and joined
+    uint32_t n_chunks = 1;
+    if (!dev_in && n >= (1u << 21)) n_chunks = (uint32_t)std::min<uint64_t>(8, n >> 20);
+    uint64_t chunk = (n + n_chunks - 1) / std::max<uint32_t>(n_chunks, 1);
+    chunk = (chunk + PART_TILE - 1) / PART_TILE * PART_TILE;
+    if (chunk == 0) chunk = PART_TILE;
+    n_chunks = (uint32_t)std::max<uint64_t>(1, (n + chunk - 1) / chunk);
+    ix_begin(mode, invert, entire_group, types_csv, flags, join_only, std::max<uint64_t>(n, 1), n_chunks);
+    if (dev_in) {
+        ix_add(chr, start, end, n);
+    } else if (n) {
+        const uint32_t* src[3] = {chr, start, end};
+        for (int k = 0; k < 3; k++) d_q[k].ensure(n * 4);
+        while (ev_copy.size() < n_chunks) {
+            cudaEvent_t e;
+            GFFX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            ev_copy.push_back(e);
+        }
+        for (uint32_t c = 0; c < n_chunks; c++) {
+            const uint64_t o = (uint64_t)c * chunk, m = std::min<uint64_t>(chunk, n - o);
+            for (int k = 0; k < 3; k++)
+                GFFX_CUDA(cudaMemcpyAsync(d_q[k].as<uint32_t>() + o, src[k] + o, m * 4, cudaMemcpyHostToDevice, st_copy));
+            GFFX_CUDA(cudaEventRecord(ev_copy[c], st_copy));
+        }
+        for (uint32_t c = 0; c < n_chunks; c++) {
+            const uint64_t o = (uint64_t)c * chunk, m = std::min<uint64_t>(chunk, n - o);
+            GFFX_CUDA(cudaStreamWaitEvent(st, ev_copy[c], 0));
+            ix_add(d_q[0].as<uint32_t>() + o, d_q[1].as<uint32_t>() + o, d_q[2].as<uint32_t>() + o, m);
+        }
+    }
+    ix_finish(out);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -76,11 +76,25 @@ struct DJoin {
 
 struct CountsState;  // counts.cu
 
+struct IxChunk {
+    uint64_t off = 0, n = 0;  // position of the batch in the job's bucketed arrays (retained jobs), regions in it
+};
+struct IxJob {  // state of one intersect job between ix_begin and ix_finish
+    bool active = false;
+    int mode = 2;
+    bool invert = false, entire_group = false, join_only = false, match_only = true, run_filter = false, have_types = false;
+    bool pairs_dev = false, want_pairs_host = false, no_host = false, nothing = false;
+    uint64_t n_total = 0, retained = 0;
+    unsigned long long pair_cap = 0;
+    uint32_t launches = 0;
+    std::vector<IxChunk> chunks;
+};
+
 class EngineImpl {
    public:
     std::unique_ptr<HostIndex> H;
     int dev = 0;
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, st_copy = nullptr;  // st: every kernel; st_copy: host -> device chunks of the regions
     size_t dev_bytes = 0;
     int sm_count = 148;
 
@@ -118,6 +132,9 @@ class EngineImpl {
     void* h_small = nullptr;  // pinned, 256 B
     cudaEvent_t ev[12];  // [0..7] stage boundaries of one intersect call, [8],[9] around the join emit kernel alone, [10] end of the partition pass
 
+    IxJob job;
+    std::vector<cudaEvent_t> ev_chunk, ev_copy;  // 4 timing events per batch of a job; one copy-done event per chunk
+
     // ---- counts (depth / coverage) -----------------------------------------------------------
     CountsState* counts = nullptr;  // owned; freed by counts_release()
 
@@ -129,12 +146,17 @@ class EngineImpl {
     void build_lines();
     void intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
                    bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out);
+    void ix_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags, bool join_only, uint64_t n_retained,
+                  uint32_t n_chunks);
+    void ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n);
+    void ix_finish(IntersectResult* out);
     // stage the regions on the device; returns device pointers (either the caller's or the staging buffers)
     void stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                        const uint32_t** dc, const uint32_t** ds, const uint32_t** de);
     // K0: bucket n (< 2^31) device-resident regions by window; returns the bucketed arrays (engine-owned
     // scratch, valid until the next call) and the number of kernels launched
     uint32_t partition(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, const uint32_t** bchr, const uint2** bse);
+    uint32_t partition_into(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, uint32_t* oc, uint2* ose, uint32_t* poff);
 };
 
 // counts.cu
