@@ -266,11 +266,47 @@ class TreeIndexData:
                                   types.encode() if types is not None else None, f, C.byref(h)))
         return _take_result(h, copy)
 
+    # -- batched / sharded jobs (gffx_shard_*, gffx_job_buffer) ----------------------------------
+    def job_buffers(self, counts_handle=None):
+        """accumulators of the open intersect job (or of the depth / coverage job `counts_handle`): (device ptr, elements, op)"""
+        out = []
+        k = 0
+        while True:
+            p, n, op = C.c_void_p(), C.c_uint64(), C.c_int()
+            rc = lib.gffx_job_buffer(self._h, counts_handle, k, C.byref(p), C.byref(n), C.byref(op))
+            if rc == 1:
+                return out
+            _check(rc)
+            out.append((p.value or 0, n.value, op.value))
+            k += 1
+
+    def shard_intersect(self, regions, mode: OverlapMode = OverlapMode.Overlap, invert: bool = False, entire_group: bool = False,
+                        types: Optional[str] = None, *, combine=None, batches: int = 1, flags: int = 0, copy: bool = True) -> Result:
+        """The same result as intersect() over the union of every shard's regions: begin, add this shard's regions (in
+        `batches` pieces), `combine(buffers)` exchanges the accumulators (gffx_b200.shard.Combiner; None = single shard),
+        finish.  Result.n_pairs counts THIS shard's pairs."""
+        keep: list = []
+        pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
+        _check(lib.gffx_shard_begin(self._h, int(mode), int(bool(invert)), int(bool(entire_group)),
+                                    types.encode() if types is not None else None, flags))
+        step = max(1, (n + max(1, batches) - 1) // max(1, batches))
+        for b0 in range(0, n, step):
+            m = min(step, n - b0)
+            _check(lib.gffx_shard_add(self._h, pc + 4 * b0, ps + 4 * b0, pe + 4 * b0, m, f, None))
+        if combine is not None:
+            combine(self.job_buffers())
+        h = C.c_void_p()
+        _check(lib.gffx_shard_finish(self._h, C.byref(h)))
+        return _take_result(h, copy)
+
+    def sync(self):
+        _check(lib.gffx_index_sync(self._h))
+
     def write_ranges(self, ranges: np.ndarray, out_path: Optional[str]):
         r = np.ascontiguousarray(ranges, dtype=np.uint64)
         _check(lib.gffx_write_ranges(self._h, r.ctypes.data, r.shape[0], str(out_path).encode() if out_path else None))
 
-    def _counts(self, kind: int, regions, batches: int = 1):
+    def _counts(self, kind: int, regions, batches: int = 1, combine=None):
         st = C.c_void_p()
         _check(lib.gffx_counts_begin(self._h, kind, C.byref(st)))
         try:
@@ -283,6 +319,8 @@ class TreeIndexData:
                 for b0 in range(0, n, step):
                     m = min(step, n - b0)
                     _check(lib.gffx_counts_add(st, pc + 4 * b0, ps + 4 * b0, pe + 4 * b0, m, f))
+            if combine is not None:  # multi-GPU: exchange the accumulators, then every rank finishes with the global state
+                combine(self.job_buffers(st))
             nr = C.c_uint64()
             pid, pch, pst, pen = (_lib.u32p() for _ in range(4))
             pv = _lib.u64p()
@@ -298,13 +336,13 @@ class TreeIndexData:
         finally:
             lib.gffx_counts_free(st)
 
-    def depth(self, regions, batches: int = 1) -> "CountRows":
+    def depth(self, regions, batches: int = 1, combine=None) -> "CountRows":
         """compute_hit_depth over all batches, src/commands/depth.rs:222-293,429-512"""
-        return self._counts(0, regions, batches)
+        return self._counts(0, regions, batches, combine)
 
-    def coverage(self, regions, batches: int = 1) -> "CountRows":
+    def coverage(self, regions, batches: int = 1, combine=None) -> "CountRows":
         """collect_by_root + finalize_compute_breadth, src/commands/coverage.rs:208-450"""
-        return self._counts(1, regions, batches)
+        return self._counts(1, regions, batches, combine)
 
     def id_string(self, i: int) -> bytes:
         n = C.c_uint32()

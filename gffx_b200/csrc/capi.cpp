@@ -188,6 +188,49 @@ int gffx_intersect(gffx_index* idx, const uint32_t* chr, const uint32_t* start, 
     });
 }
 
+int gffx_shard_begin(gffx_index* idx, int mode, int invert, int entire_group, const char* types_csv, uint32_t flags) {
+    return guard([&] {
+        need(idx, "idx");
+        idx->engine()->shard_begin(mode, invert != 0, entire_group != 0, types_csv, flags);
+    });
+}
+int gffx_shard_add(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
+                   uint64_t* n_pairs_total) {
+    return guard([&] {
+        need(idx, "idx");
+        idx->engine()->shard_add(chr, start, end, n, flags, n_pairs_total);
+    });
+}
+int gffx_shard_finish(gffx_index* idx, gffx_result** out) {
+    return guard([&] {
+        need(idx, "idx"); need(out, "out");
+        auto r = std::make_unique<gffx_result>();
+        idx->engine()->shard_finish(&r->r);
+        *out = r.release();
+    });
+}
+int gffx_job_buffer(gffx_index* idx, gffx_counts* counts, uint32_t k, void** dptr, uint64_t* n_elems, int* op) {
+    int past = 0;
+    int rc = guard([&] {
+        need(idx, "idx"); need(dptr, "dptr"); need(n_elems, "n_elems"); need(op, "op");
+        if (counts && counts->idx != idx) throw Err(E_ARG, "the counts job belongs to another index");
+        past = idx->engine()->shard_buffer(counts ? 1 : 0, k, dptr, n_elems, op) ? 0 : 1;
+    });
+    return rc ? rc : past;
+}
+int gffx_fold(gffx_index* idx, void* dst, const void* src, uint32_t rows, uint64_t stride_elems, uint64_t n_elems, int op) {
+    return guard([&] {
+        need(idx, "idx"); need(dst, "dst"); need(src, "src");
+        idx->engine()->fold(dst, src, rows, stride_elems, n_elems, op);
+    });
+}
+int gffx_index_sync(gffx_index* idx) {
+    return guard([&] {
+        need(idx, "idx");
+        idx->engine()->sync();
+    });
+}
+
 uint64_t gffx_result_n_queries(const gffx_result* r) { return r ? r->r.n_queries : 0; }
 uint64_t gffx_result_n_pairs(const gffx_result* r) { return r ? r->r.n_pairs : 0; }
 const uint32_t* gffx_result_pairs(const gffx_result* r) { return r && !r->r.pairs.empty() ? r->r.pairs.data() : nullptr; }

@@ -253,6 +253,27 @@ void counts_finish_impl(EngineImpl* E, CountRows* rows) {
     C->ms += ms;
 }
 
+// accumulators of the running depth / coverage job and how shards combine them (engine.h ReduceOp)
+bool counts_buffer_impl(EngineImpl* E, uint32_t k, void** dptr, uint64_t* n_elems, int* op) {
+    CountsState* C = E->counts;
+    if (!C || !C->active) throw Err(E_STATE, "no depth / coverage job is open");
+    const CountsIndexHost& h = C->host;
+    struct B { void* p; uint64_t n; int op; };
+    B v[3];
+    if (C->kind == 0) {
+        v[0] = {C->d_Hs.p, h.n_slots, RED_SUM_U32};   // region starts per rank slot
+        v[1] = {C->d_He.p, h.n_slots, RED_SUM_U32};   // region ends per rank slot
+        v[2] = {C->d_G.p, h.n_segs, RED_SUM_U32};     // regions lying inside the gap after each segment
+    } else {
+        v[0] = {C->d_bits.p, h.n_words, RED_OR_U64};  // covered bases (partial words)
+        v[1] = {C->d_diff.p, h.n_words, RED_SUM_I32}; // fully covered words, difference array
+        v[2] = {C->d_routed.p, E->n_blocks, RED_MAX_U8};
+    }
+    if (k >= 3) return false;
+    *dptr = v[k].p; *n_elems = v[k].n; *op = v[k].op;
+    return true;
+}
+
 double counts_ms_impl(const EngineImpl* E) { return E->counts ? E->counts->ms : 0.0; }
 uint32_t counts_launches_impl(const EngineImpl* E) { return E->counts ? E->counts->launches : 0; }
 

@@ -741,6 +741,83 @@ int cuda_device_count() {
     int n = 0;
     return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
 }
+// ---- shards ---------------------------------------------------------------------------------------
+void Engine::shard_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags) {
+    if (flags & (2u | 8u)) throw Err(E_ARG, "a sharded / batched intersect job counts the pairs but does not materialise them (use gffx_query_features per batch)");
+    impl_->ix_begin(mode, invert, entire_group, types_csv, flags, false, 0, 1);
+}
+void Engine::shard_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags, uint64_t* n_pairs_total) {
+    EngineImpl* E = impl_.get();
+    if (n && (!chr || !start || !end)) throw Err(E_ARG, "NULL region arrays");
+    if (!E->job.active) throw Err(E_STATE, "gffx_shard_add without gffx_shard_begin");
+    GFFX_CUDA(cudaSetDevice(E->dev));
+    const uint32_t *dc, *ds, *de;
+    E->stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
+    E->ix_add(dc, ds, de, n);
+    // the caller's arrays (host or device) are free again when this returns
+    GFFX_CUDA(cudaMemcpyAsync(E->h_small, E->d_small.p, 64, cudaMemcpyDeviceToHost, E->st));
+    GFFX_CUDA(cudaStreamSynchronize(E->st));
+    GFFX_CUDA(cudaGetLastError());
+    if (((const uint32_t*)E->h_small)[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
+    if (n_pairs_total) *n_pairs_total = *(const uint64_t*)E->h_small;
+}
+void Engine::shard_finish(IntersectResult* out) { impl_->ix_finish(out); }
+void Engine::sync() {
+    GFFX_CUDA(cudaSetDevice(impl_->dev));
+    GFFX_CUDA(cudaStreamSynchronize(impl_->st));
+}
+bool Engine::shard_buffer(int which, uint32_t k, void** dptr, uint64_t* n_elems, int* op) {
+    EngineImpl* E = impl_.get();
+    if (which == 1) return counts_buffer_impl(E, k, dptr, n_elems, op);
+    const IxJob& jb = E->job;
+    if (!jb.active) throw Err(E_STATE, "no intersect job is open");
+    struct B { void* p; uint64_t n; int op; };
+    std::vector<B> v;
+    if (!jb.nothing) {
+        v.push_back({E->d_wj_hit.p, E->wj_n_ent, RED_MAX_U8});  // which roots were hit -> selected blocks, warn list
+        if (jb.run_filter) {                                    // the regions as seen from the line rank space (filter.cuh)
+            const uint64_t ns = E->f_slots;
+            if (jb.mode == 0 || jb.mode == 2) v.push_back({E->d_A.p, ns, RED_MAX_U64});
+            if (jb.mode == 1) v.push_back({E->d_B.p, ns, RED_MIN_U64});
+            if (jb.mode == 2) { v.push_back({E->d_Ms.p, 2 * ns, RED_MAX_U8}); v.push_back({E->d_Me.p, 2 * ns, RED_MAX_U8}); }
+        }
+    }
+    if (k >= v.size()) return false;
+    *dptr = v[k].p; *n_elems = v[k].n; *op = v[k].op;
+    return true;
+}
+
+template <class T, class F>
+__global__ void fold_kernel(T* __restrict__ dst, const T* __restrict__ src, uint32_t rows, uint64_t stride, uint64_t n, F f) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        T a = src[i];
+        for (uint32_t r = 1; r < rows; r++) a = f(a, src[(uint64_t)r * stride + i]);
+        dst[i] = a;
+    }
+}
+struct FMax { template <class T> __device__ T operator()(T a, T b) const { return a > b ? a : b; } };
+struct FMin { template <class T> __device__ T operator()(T a, T b) const { return a < b ? a : b; } };
+struct FSum { template <class T> __device__ T operator()(T a, T b) const { return a + b; } };
+struct FOr { template <class T> __device__ T operator()(T a, T b) const { return a | b; } };
+
+void Engine::fold(void* dst, const void* src, uint32_t rows, uint64_t stride, uint64_t n, int op) {
+    EngineImpl* E = impl_.get();
+    if (n == 0 || rows == 0) return;
+    GFFX_CUDA(cudaSetDevice(E->dev));
+    const unsigned blocks = (unsigned)std::min<uint64_t>((n + 255) / 256, (uint64_t)E->sm_count * 16);
+    typedef unsigned long long ull;
+    switch (op) {
+        case RED_MAX_U8: fold_kernel<<<blocks, 256, 0, E->st>>>((uint8_t*)dst, (const uint8_t*)src, rows, stride, n, FMax()); break;
+        case RED_MAX_U64: fold_kernel<<<blocks, 256, 0, E->st>>>((ull*)dst, (const ull*)src, rows, stride, n, FMax()); break;
+        case RED_MIN_U64: fold_kernel<<<blocks, 256, 0, E->st>>>((ull*)dst, (const ull*)src, rows, stride, n, FMin()); break;
+        case RED_SUM_U32: fold_kernel<<<blocks, 256, 0, E->st>>>((uint32_t*)dst, (const uint32_t*)src, rows, stride, n, FSum()); break;
+        case RED_SUM_I32: fold_kernel<<<blocks, 256, 0, E->st>>>((int*)dst, (const int*)src, rows, stride, n, FSum()); break;
+        case RED_OR_U64: fold_kernel<<<blocks, 256, 0, E->st>>>((ull*)dst, (const ull*)src, rows, stride, n, FOr()); break;
+        default: throw Err(E_ARG, "unknown reduce op");
+    }
+    GFFX_CUDA(cudaGetLastError());
+}
+
 void Engine::counts_begin(int kind) { counts_begin_impl(impl_.get(), kind); }
 void Engine::counts_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags) {
     counts_add_impl(impl_.get(), chr, start, end, n, flags);

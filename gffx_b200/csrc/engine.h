@@ -60,6 +60,9 @@ struct CountRows {
     std::vector<uint64_t> value;
 };
 
+// how the shards' copies of an accumulator combine (gffx_reduce_op of the C ABI)
+enum ReduceOp { RED_MAX_U8 = 0, RED_MAX_U64 = 1, RED_MIN_U64 = 2, RED_SUM_U32 = 3, RED_SUM_I32 = 4, RED_OR_U64 = 5 };
+
 class EngineImpl;
 
 class Engine {
@@ -77,6 +80,18 @@ class Engine {
     // mode: 0 contained, 1 contains-region, 2 overlap.  join_only: stop after the root-level join.
     void intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
                    bool entire_group, const char* types_csv, uint32_t flags, bool join_only, IntersectResult* out);
+
+    // The same pipeline in three steps, for jobs whose regions arrive in batches or are spread over several GPUs: begin,
+    // any number of adds (accumulate), [combine the accumulators of the shards: shard_buffer + fold], finish.
+    void shard_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags);
+    void shard_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags, uint64_t* n_pairs_total);
+    void shard_finish(IntersectResult* out);
+    // accumulator k of the running intersect job (which = 0) or depth / coverage job (which = 1): device pointer, element
+    // count and how shards combine it (ReduceOp).  false when k is past the last one.
+    bool shard_buffer(int which, uint32_t k, void** dptr, uint64_t* n_elems, int* op);
+    // dst[i] = op over r < rows of src[r * stride + i], i < n_elems (device pointers on this engine's GPU, engine stream)
+    void fold(void* dst, const void* src, uint32_t rows, uint64_t stride_elems, uint64_t n_elems, int op);
+    void sync();
 
     // depth (kind 0) / coverage (kind 1)
     void counts_begin(int kind);

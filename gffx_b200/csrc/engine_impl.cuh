@@ -165,6 +165,7 @@ void counts_begin_impl(EngineImpl* E, int kind);
 void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags);
 void counts_finish_impl(EngineImpl* E, CountRows* rows);
 double counts_ms_impl(const EngineImpl* E);
+bool counts_buffer_impl(EngineImpl* E, uint32_t k, void** dptr, uint64_t* n_elems, int* op);
 uint32_t counts_launches_impl(const EngineImpl* E);
 
 }  // namespace gffx

@@ -183,6 +183,33 @@ const char* gffx_index_chrom_string(const gffx_index* idx, uint32_t chrom_idx, u
 int gffx_counts_write(gffx_counts* st, const char* out_path);
 
 /* ------------------------------------------------------------------------------------------
+ * Batched / sharded jobs.  The reference runs one process over one BED (intersect.rs:586-654) and batches only in
+ * depth (100k lines, depth.rs:24,462).  Here the same job can take its regions in any number of batches and can be
+ * spread over several GPUs (one handle per GPU, each fed its own share of the regions):
+ *     gffx_shard_begin -> gffx_shard_add ... -> [combine] -> gffx_shard_finish
+ * [combine], multi-GPU only: for every accumulator k reported by gffx_job_buffer, exchange the shards' copies and
+ * reduce them element-wise with the reported op (gffx_fold is the reduction kernel; gffx_b200/shard.py drives it over
+ * torch.distributed: all-to-all of 1/W slices, fold, all-gather).  Every shard then finishes with the job's global
+ * state and produces the complete result.  Pairs are counted, not materialised, by a sharded job.
+ * ------------------------------------------------------------------------------------------ */
+typedef enum {
+    GFFX_RED_MAX_U8 = 0, GFFX_RED_MAX_U64 = 1, GFFX_RED_MIN_U64 = 2, GFFX_RED_SUM_U32 = 3, GFFX_RED_SUM_I32 = 4, GFFX_RED_OR_U64 = 5
+} gffx_reduce_op;
+int gffx_shard_begin(gffx_index* idx, int mode, int invert, int entire_group, const char* types_csv, uint32_t flags);
+/* n_pairs_total (may be NULL): pairs counted so far by this shard.  The arrays may be reused when the call returns. */
+int gffx_shard_add(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
+                   uint64_t* n_pairs_total);
+int gffx_shard_finish(gffx_index* idx, gffx_result** out);
+/* accumulator k of the open intersect job (counts == NULL) or of a depth / coverage job: device pointer, element count,
+ * gffx_reduce_op.  Returns 1 when k is past the last accumulator, 0 when filled in, negative on error. */
+int gffx_job_buffer(gffx_index* idx, gffx_counts* counts, uint32_t k, void** dptr, uint64_t* n_elems, int* op);
+/* dst[i] = op over r < rows of src[r * stride_elems + i] for i < n_elems; device pointers on the handle's GPU,
+ * asynchronous on the engine's stream (gffx_index_cuda_stream) */
+int gffx_fold(gffx_index* idx, void* dst, const void* src, uint32_t rows, uint64_t stride_elems, uint64_t n_elems, int op);
+/* wait for the engine's stream */
+int gffx_index_sync(gffx_index* idx);
+
+/* ------------------------------------------------------------------------------------------
  * Command level: the reference's run() functions (src/commands/intersect.rs:541-655,
  * src/commands/depth.rs:548-635, src/commands/coverage.rs:493-582) with the GPU engine inside.
  * ------------------------------------------------------------------------------------------ */
