@@ -12,8 +12,8 @@ finds its inputs cached).  value = query intervals/s = n_gpus * 4 * Q * steps / 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
 N > 1 is launched by torchrun, one rank per GPU; every rank joins its own regions against a replicated
-index (weak scaling; shards are independent, the only exchange is the OR of the per-shard block/line
-flags before the final compaction).
+index (weak scaling; shards are independent, the only exchange is the element-wise combination of the job's
+accumulators — root hit flags, line rank-space keys — before the final line filter; gffx_b200/shard.py).
 
 --impl reference times the CPU implementation of the path (the C++ restatement under oracle/: the Rust
 reference cannot be built in this image) on the box's host cores, on a bounded sample of the workload.
@@ -171,7 +171,9 @@ def workload_config(args, idx, q):
                     f"20 kb BED regions per pass per GPU; step = overlap | --contained | --contains-region | --contained --invert",
         "regions_per_pass_per_gpu": q, "passes_per_step": len(PASSES), "region_len": REGION_LEN, "n_roots": idx.n_roots,
         "n_lines": idx.n_lines, "pairs": "materialised in HBM", "l2": "inputs larger than L2: 4 x 12 B x Q region sets rotate (no flush needed)",
-        "sharding": "regions split across ranks (counter-based stream, rank r owns [r*Q,(r+1)*Q)); index replicated",
+        "sharding": "regions split across ranks (counter-based stream, rank r owns [r*Q,(r+1)*Q)); index replicated; N>1: the job's "
+                    "accumulators (root hit flags, line rank-space keys) are exchanged over NCCL (all-to-all + fold kernel + all-gather) "
+                    "and every rank emits the byte ranges of the whole N*Q-region job",
     }
 
 
@@ -227,10 +229,19 @@ def run_gpu(args, rank, world, local_rank):
     stream = torch.cuda.ExternalStream(idx.cuda_stream, device=dev)
     F_DEV = _lib.F_PAIRS_ON_DEVICE | _lib.F_NO_HOST_COPY
 
+    combiner = None
+    if world > 1:
+        from gffx_b200.shard import Combiner
+
+        combiner = Combiner(idx)  # exchanges the job's accumulators over NCCL before the finish step (gffx_b200/shard.py)
+
     def step(sets, flags, acc=None):
         for (name, mode, inv), regs in zip(PASSES, sets):
             # copy=False: the byte ranges stay in the result's page-locked buffer (what a Rust caller of the C ABI reads too)
-            r = idx.intersect(regs, mode, inv, False, None, flags=flags, copy=False)
+            if world == 1:
+                r = idx.intersect(regs, mode, inv, False, None, flags=flags, copy=False)
+            else:  # every rank joins its own Q regions; after the exchange each rank holds the ranges of the world's N*Q regions
+                r = idx.shard_intersect(regs, mode, inv, False, None, combine=combiner, flags=flags, copy=False)
             if acc is not None:
                 a = acc.setdefault(name, {"calls": 0, "pairs": 0, "ranges": 0, "roots": 0, "launches": 0, "kernel_ms": 0.0, "stage_ms": [0.0] * 12})
                 a["calls"] += 1

@@ -126,7 +126,7 @@ SIGNATURES = {
     "gffx_index_id_string": (vp, vp, C.c_uint32, u32p),
     "gffx_index_chrom_string": (vp, vp, C.c_uint32, u32p),
     "gffx_counts_write": (C.c_int, vp, C.c_char_p),
-    "gffx_shard_begin": (C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_uint32),
+    "gffx_shard_begin": (C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_uint32, C.c_uint64, C.c_uint32),
     "gffx_shard_add": (C.c_int, vp, vp, vp, vp, C.c_uint64, C.c_uint32, u64p),
     "gffx_shard_finish": (C.c_int, vp, C.POINTER(vp)),
     "gffx_job_buffer": (C.c_int, vp, vp, C.c_uint32, C.POINTER(vp), u64p, C.POINTER(C.c_int)),

@@ -281,14 +281,17 @@ class TreeIndexData:
             k += 1
 
     def shard_intersect(self, regions, mode: OverlapMode = OverlapMode.Overlap, invert: bool = False, entire_group: bool = False,
-                        types: Optional[str] = None, *, combine=None, batches: int = 1, flags: int = 0, copy: bool = True) -> Result:
+                        types: Optional[str] = None, *, combine=None, batches: int = 1, want_pairs: bool = False, flags: int = 0,
+                        copy: bool = True) -> Result:
         """The same result as intersect() over the union of every shard's regions: begin, add this shard's regions (in
         `batches` pieces), `combine(buffers)` exchanges the accumulators (gffx_b200.shard.Combiner; None = single shard),
-        finish.  Result.n_pairs counts THIS shard's pairs."""
+        finish.  Result.n_pairs / pairs are THIS shard's."""
         keep: list = []
         pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
+        flags |= _lib.F_WANT_PAIRS if want_pairs else 0
+        announce = n if flags & (_lib.F_WANT_PAIRS | _lib.F_PAIRS_ON_DEVICE) else 0
         _check(lib.gffx_shard_begin(self._h, int(mode), int(bool(invert)), int(bool(entire_group)),
-                                    types.encode() if types is not None else None, flags))
+                                    types.encode() if types is not None else None, flags, announce, max(1, batches) + 1))
         step = max(1, (n + max(1, batches) - 1) // max(1, batches))
         for b0 in range(0, n, step):
             m = min(step, n - b0)

@@ -188,10 +188,11 @@ int gffx_intersect(gffx_index* idx, const uint32_t* chr, const uint32_t* start, 
     });
 }
 
-int gffx_shard_begin(gffx_index* idx, int mode, int invert, int entire_group, const char* types_csv, uint32_t flags) {
+int gffx_shard_begin(gffx_index* idx, int mode, int invert, int entire_group, const char* types_csv, uint32_t flags, uint64_t n_expected,
+                     uint32_t batches_expected) {
     return guard([&] {
         need(idx, "idx");
-        idx->engine()->shard_begin(mode, invert != 0, entire_group != 0, types_csv, flags);
+        idx->engine()->shard_begin(mode, invert != 0, entire_group != 0, types_csv, flags, n_expected, batches_expected);
     });
 }
 int gffx_shard_add(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,

@@ -742,9 +742,12 @@ int cuda_device_count() {
     return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
 }
 // ---- shards ---------------------------------------------------------------------------------------
-void Engine::shard_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags) {
-    if (flags & (2u | 8u)) throw Err(E_ARG, "a sharded / batched intersect job counts the pairs but does not materialise them (use gffx_query_features per batch)");
-    impl_->ix_begin(mode, invert, entire_group, types_csv, flags, false, 0, 1);
+void Engine::shard_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags, uint64_t n_expected,
+                         uint32_t batches_expected) {
+    if ((flags & (2u | 8u)) && n_expected == 0)
+        throw Err(E_ARG, "a batched intersect job materialises its pairs only when the number of regions is announced at begin (n_expected)");
+    if (n_expected >= (1ull << 31)) throw Err(E_ARG, "n_expected must stay below 2^31 (announce 0 for a streaming job)");
+    impl_->ix_begin(mode, invert, entire_group, types_csv, flags, false, n_expected, std::max<uint32_t>(batches_expected, 1));
 }
 void Engine::shard_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags, uint64_t* n_pairs_total) {
     EngineImpl* E = impl_.get();

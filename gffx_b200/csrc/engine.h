@@ -83,7 +83,8 @@ class Engine {
 
     // The same pipeline in three steps, for jobs whose regions arrive in batches or are spread over several GPUs: begin,
     // any number of adds (accumulate), [combine the accumulators of the shards: shard_buffer + fold], finish.
-    void shard_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags);
+    void shard_begin(int mode, bool invert, bool entire_group, const char* types_csv, uint32_t flags, uint64_t n_expected,
+                     uint32_t batches_expected);
     void shard_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags, uint64_t* n_pairs_total);
     void shard_finish(IntersectResult* out);
     // accumulator k of the running intersect job (which = 0) or depth / coverage job (which = 1): device pointer, element

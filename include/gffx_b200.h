@@ -190,12 +190,15 @@ int gffx_counts_write(gffx_counts* st, const char* out_path);
  * [combine], multi-GPU only: for every accumulator k reported by gffx_job_buffer, exchange the shards' copies and
  * reduce them element-wise with the reported op (gffx_fold is the reduction kernel; gffx_b200/shard.py drives it over
  * torch.distributed: all-to-all of 1/W slices, fold, all-gather).  Every shard then finishes with the job's global
- * state and produces the complete result.  Pairs are counted, not materialised, by a sharded job.
+ * state and produces the complete result.  The pairs of a shard's own regions are materialised (GFFX_F_WANT_PAIRS /
+ * GFFX_F_PAIRS_ON_DEVICE) only when the job announces its size: n_expected regions in at most batches_expected adds
+ * (the bucketed batches are then kept on the device); n_expected = 0 is a streaming job that only counts them.
  * ------------------------------------------------------------------------------------------ */
 typedef enum {
     GFFX_RED_MAX_U8 = 0, GFFX_RED_MAX_U64 = 1, GFFX_RED_MIN_U64 = 2, GFFX_RED_SUM_U32 = 3, GFFX_RED_SUM_I32 = 4, GFFX_RED_OR_U64 = 5
 } gffx_reduce_op;
-int gffx_shard_begin(gffx_index* idx, int mode, int invert, int entire_group, const char* types_csv, uint32_t flags);
+int gffx_shard_begin(gffx_index* idx, int mode, int invert, int entire_group, const char* types_csv, uint32_t flags,
+                     uint64_t n_expected, uint32_t batches_expected);
 /* n_pairs_total (may be NULL): pairs counted so far by this shard.  The arrays may be reused when the call returns. */
 int gffx_shard_add(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                    uint64_t* n_pairs_total);

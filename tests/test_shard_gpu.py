@@ -101,12 +101,26 @@ def test_two_shards_depth_coverage(quirk, kind):
     assert rows.to_tsv() == want
 
 
-def test_sharded_job_refuses_pairs(quirk, gffx):
+def test_batched_job_with_pairs(quirk):
+    """a job that announces its size keeps the bucketed batches and materialises the pairs like one call does"""
+    from tests._oracle import sorted_pairs
+
+    idx, o = quirk
+    regs = mixed_regions(idx, 77, 3000)
+    for mode, invert in MODES:
+        r = idx.shard_intersect(regs, mode, invert, batches=3, want_pairs=True)
+        want = o.query_features(regs, mode, invert)
+        got = r.pairs if r.pairs is not None else np.zeros((0, 3), dtype=np.uint32)
+        assert r.n_pairs == want.shape[0]
+        assert np.array_equal(sorted_pairs(got), sorted_pairs(want))
+
+
+def test_streaming_job_refuses_pairs(quirk, gffx):
     idx, _ = quirk
     from gffx_b200 import _lib
 
     with pytest.raises(gffx.GffxError):
-        idx.shard_intersect(idx.synth_regions(1, 10, 100), 2, flags=_lib.F_WANT_PAIRS)
+        gffx.api._check(_lib.lib.gffx_shard_begin(idx._h, 2, 0, 0, None, _lib.F_WANT_PAIRS, 0, 1))
 
 
 def test_two_gpus_nccl(synth_quirk_gff):
