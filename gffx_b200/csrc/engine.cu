@@ -42,7 +42,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
-                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
                     &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit,
                     &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
@@ -61,7 +61,7 @@ EngineImpl::~EngineImpl() {
     if (st) cudaStreamSynchronize(st);
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
-                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
                     &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit,
                     &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
@@ -504,6 +504,58 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 3], st));
 }
 
+// the rank-space scans of the line filter (filter.cuh): PMX / SMN / NS / NE from the scattered region keys
+uint32_t EngineImpl::ix_scans(FilterScans* Pout) {
+    typedef unsigned long long ull;
+    const IxJob& jb = job;
+    const int mode = jb.mode;
+    const uint64_t ns = f_slots;
+    uint32_t launches = 0;
+    d_scan_scratch.ensure(scan_scratch_elems(LA.n / LINE_THREADS + 1) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
+    FilterArrays F{d_A.as<ull>(), d_B.as<ull>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
+    ull* scr = d_scan_scratch.as<ull>();
+    *Pout = FilterScans{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>()};
+    if (mode == 0 || mode == 2)
+        launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
+                                                                                     OpMax(), 0ull, scr, nullptr, st);
+    if (mode == 1) {
+        launches += device_scan<ull, OpMin, PtrLoad<ull>, PtrStore<ull>, true, true>(PtrLoad<ull>{F.B}, PtrStore<ull>{d_SMN.as<ull>()}, ns,
+                                                                                    OpMin(), ~0ull, scr, nullptr, st);
+        fill_u64_kernel<<<1, 32, 0, st>>>(d_SMN.as<ull>() + ns, 1, ~0ull);  // SMN[iS+1] may index one past the last slot
+        launches++;
+    }
+    if (mode == 2) {
+        launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
+            MarkLoad{F.Ms}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
+        launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
+            MarkLoad{F.Me}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
+    }
+    return launches;
+}
+
+// No more batches: the shard-local half of the finish step.  Afterwards the job's state that other shards can add to is
+// two byte-flag arrays — which roots were hit, which lines match some region — both combined by MAX.
+void EngineImpl::ix_seal() {
+    IxJob& jb = job;
+    if (!jb.active) throw Err(E_STATE, "no intersect job is open");
+    if (jb.sealed) return;
+    GFFX_CUDA(cudaSetDevice(dev));
+    jb.sealed = true;
+    if (!jb.run_filter) return;
+    d_match.ensure(std::max<uint64_t>(LA.n, 1));
+    if (jb.nothing || jb.n_total == 0) {
+        GFFX_CUDA(cudaMemsetAsync(d_match.p, 0, std::max<uint64_t>(LA.n, 1), st));
+        return;
+    }
+    FilterScans P{};
+    jb.launches += ix_scans(&P);
+    const unsigned tiles = (unsigned)((LA.n + LINE_THREADS - 1) / LINE_THREADS);
+    if (jb.mode == 0) match_lines_kernel<0><<<tiles, LINE_THREADS, 0, st>>>(LA, P, d_match.as<uint8_t>());
+    else if (jb.mode == 1) match_lines_kernel<1><<<tiles, LINE_THREADS, 0, st>>>(LA, P, d_match.as<uint8_t>());
+    else match_lines_kernel<2><<<tiles, LINE_THREADS, 0, st>>>(LA, P, d_match.as<uint8_t>());
+    jb.launches++;
+}
+
 void EngineImpl::ix_finish(IntersectResult* out) {
     IxJob& jb = job;
     if (!jb.active) throw Err(E_STATE, "intersect finish without a job");
@@ -512,7 +564,8 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     *out = IntersectResult();
     out->n_queries = jb.n_total;
     const int mode = jb.mode;
-    const bool nothing = jb.nothing || jb.n_total == 0;
+    // a sealed job may hold other shards' flags even when this shard added no regions
+    const bool nothing = jb.nothing || (jb.n_total == 0 && !jb.sealed);
     uint32_t launches = jb.launches;
     unsigned long long* small = d_small.as<unsigned long long>();  // [0] n_pairs [1..3] merge counts [4] bytes_out [5] n_emit (u64); u32 view: [12] err [13] n_warn
     uint32_t* small32 = d_small.as<uint32_t>();
@@ -538,35 +591,18 @@ void EngineImpl::ix_finish(IntersectResult* out) {
 
     // ---- line filter: rank-space scans, per-line decision, ordered compaction --------------------
     if (jb.run_filter && !nothing) {
-        typedef unsigned long long ull;
-        const uint64_t ns = f_slots;
-        FilterArrays F{d_A.as<ull>(), d_B.as<ull>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
-        ull* scr = d_scan_scratch.as<ull>();
-        FilterScans P{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>()};
-        if (mode == 0 || mode == 2)
-            launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
-                                                                                         OpMax(), 0ull, scr, nullptr, st);
-        if (mode == 1) {
-            launches += device_scan<ull, OpMin, PtrLoad<ull>, PtrStore<ull>, true, true>(PtrLoad<ull>{F.B}, PtrStore<ull>{d_SMN.as<ull>()}, ns,
-                                                                                        OpMin(), ~0ull, scr, nullptr, st);
-            fill_u64_kernel<<<1, 32, 0, st>>>(d_SMN.as<ull>() + ns, 1, ~0ull);  // SMN[iS+1] may index one past the last slot
-            launches++;
-        }
-        if (mode == 2) {
-            launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
-                MarkLoad{F.Ms}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
-            launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
-                MarkLoad{F.Me}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
-        }
+        FilterScans P{};
+        if (!jb.sealed) launches += ix_scans(&P);
         GFFX_CUDA(cudaEventRecord(ev[6], st));
-
         const uint64_t n_emit_tiles = (LA.n + LINE_THREADS - 1) / LINE_THREADS;
         d_tile_count.ensure(n_emit_tiles * 4);
         d_tile_off.ensure(n_emit_tiles * 8);
         const uint8_t* sel = d_blk_sel.as<uint8_t>();
         const uint8_t* ta = d_type_allow.as<uint8_t>();
         const bool ht = jb.have_types;
-        if (mode == 0) eval_lines_kernel<0><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        if (jb.sealed)  // the per-line match flags exist already (and may hold the other shards' matches too)
+            keep_lines_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, d_match.as<uint8_t>(), sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+        else if (mode == 0) eval_lines_kernel<0><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         else if (mode == 1) eval_lines_kernel<1><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         else eval_lines_kernel<2><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         launches++;
@@ -757,7 +793,8 @@ void Engine::shard_add(const uint32_t* chr, const uint32_t* start, const uint32_
     const uint32_t *dc, *ds, *de;
     E->stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
     E->ix_add(dc, ds, de, n);
-    // the caller's arrays (host or device) are free again when this returns
+    if ((flags & 1u) && !n_pairs_total) return;  // device input, no count wanted: stays asynchronous (gffx.h: arrays live until finish / sync)
+    // the caller's arrays are free again when this returns
     GFFX_CUDA(cudaMemcpyAsync(E->h_small, E->d_small.p, 64, cudaMemcpyDeviceToHost, E->st));
     GFFX_CUDA(cudaStreamSynchronize(E->st));
     GFFX_CUDA(cudaGetLastError());
@@ -772,18 +809,13 @@ void Engine::sync() {
 bool Engine::shard_buffer(int which, uint32_t k, void** dptr, uint64_t* n_elems, int* op) {
     EngineImpl* E = impl_.get();
     if (which == 1) return counts_buffer_impl(E, k, dptr, n_elems, op);
+    E->ix_seal();
     const IxJob& jb = E->job;
-    if (!jb.active) throw Err(E_STATE, "no intersect job is open");
     struct B { void* p; uint64_t n; int op; };
     std::vector<B> v;
     if (!jb.nothing) {
-        v.push_back({E->d_wj_hit.p, E->wj_n_ent, RED_MAX_U8});  // which roots were hit -> selected blocks, warn list
-        if (jb.run_filter) {                                    // the regions as seen from the line rank space (filter.cuh)
-            const uint64_t ns = E->f_slots;
-            if (jb.mode == 0 || jb.mode == 2) v.push_back({E->d_A.p, ns, RED_MAX_U64});
-            if (jb.mode == 1) v.push_back({E->d_B.p, ns, RED_MIN_U64});
-            if (jb.mode == 2) { v.push_back({E->d_Ms.p, 2 * ns, RED_MAX_U8}); v.push_back({E->d_Me.p, 2 * ns, RED_MAX_U8}); }
-        }
+        v.push_back({E->d_wj_hit.p, E->wj_n_ent, RED_MAX_U8});                      // which roots were hit -> selected blocks, warn list
+        if (jb.run_filter) v.push_back({E->d_match.p, E->LA.n, RED_MAX_U8});       // which lines match some region (filter.cuh)
     }
     if (k >= v.size()) return false;
     *dptr = v[k].p; *n_elems = v[k].n; *op = v[k].op;

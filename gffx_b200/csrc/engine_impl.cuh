@@ -83,7 +83,7 @@ struct IxJob {  // state of one intersect job between ix_begin and ix_finish
     bool active = false;
     int mode = 2;
     bool invert = false, entire_group = false, join_only = false, match_only = true, run_filter = false, have_types = false;
-    bool pairs_dev = false, want_pairs_host = false, no_host = false, nothing = false;
+    bool pairs_dev = false, want_pairs_host = false, no_host = false, nothing = false, sealed = false;
     uint64_t n_total = 0, retained = 0;
     unsigned long long pair_cap = 0;
     uint32_t launches = 0;
@@ -120,7 +120,7 @@ class EngineImpl {
     uint32_t f_slots = 0;
     RankSpace FR{};
     LineArrays LA{};
-    DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_type_allow;
+    DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_match, d_type_allow;
 
     // ---- window grid + partition scratch (partition.cuh) --------------------------------------
     DBuf d_win0, d_poff, d_pmat, d_pscan, d_pscratch, d_bchr, d_bse;
@@ -150,6 +150,8 @@ class EngineImpl {
                   uint32_t n_chunks);
     void ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n);
     void ix_finish(IntersectResult* out);
+    void ix_seal();
+    uint32_t ix_scans(FilterScans* P);
     // stage the regions on the device; returns device pointers (either the caller's or the staging buffers)
     void stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                        const uint32_t** dc, const uint32_t** ds, const uint32_t** de);

@@ -196,6 +196,35 @@ __global__ void __launch_bounds__(LINE_THREADS)
     if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
 }
 
+// The same decision in two steps, for jobs spread over several GPUs: "does any region match this line" is an OR over the
+// regions, hence over the shards, and so is "was this root hit".  Each shard evaluates its own regions (match_lines), the
+// byte flags are MAX-reduced across the shards, and keep_lines applies the block selection and the type filter.
+template <int MODE>
+__global__ void __launch_bounds__(LINE_THREADS) match_lines_kernel(LineArrays L, FilterScans P, uint8_t* __restrict__ match) {
+    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
+    if (i < L.n) match[i] = ((L.flags[i] & 1) && line_matches<MODE>(L, P, i)) ? 1 : 0;
+}
+
+static __global__ void __launch_bounds__(LINE_THREADS)
+    keep_lines_kernel(LineArrays L, const uint8_t* __restrict__ match, const uint8_t* __restrict__ blk_sel,
+                      const uint8_t* __restrict__ type_allow, bool have_types, uint8_t* __restrict__ keep, uint32_t* __restrict__ tile_count) {
+    __shared__ uint32_t sm[LINE_THREADS / 32 + 1];
+    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
+    uint32_t k = 0;
+    if (i < L.n) {
+        bool ok = match[i] && blk_sel[L.blk[i]];
+        if (ok && have_types) {
+            const uint32_t t = L.type_id[i];
+            ok = t != 0xFFFFFFFFu && type_allow[t];
+        }
+        k = ok ? 1u : 0u;
+        keep[i] = (uint8_t)k;
+    }
+    uint32_t tot;
+    block_scan_excl(k, OpSum(), 0u, sm, &tot);
+    if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
+}
+
 // pass 2: order-preserving compaction of (offset, offset+len)
 static __global__ void __launch_bounds__(LINE_THREADS)
     emit_ranges_kernel(LineArrays L, const uint8_t* __restrict__ keep, const uint64_t* __restrict__ tile_off,

@@ -4,10 +4,12 @@ the finish step — after which every rank holds the complete result.
 
 Why accumulators and not results: the reference tests every line against ALL regions of the line's sequence
 (src/commands/intersect.rs:621-633) inside blocks selected by ANY region (:598-617), so the union of per-shard outputs is
-not the output; the OR of "root hit" flags and the MAX / MIN of the rank-space keys (filter.cuh) is.  depth's histograms
-add, coverage's bitmap ORs and its word difference array adds (counts.cuh).
+not the output; but "was this root hit by any region" and "does any region match this line" are ORs over the regions,
+hence over the shards: a sealed intersect job (gffx_job_buffer) exposes exactly these two byte-flag arrays, ~1 byte per
+root and per line.  depth's histograms add, coverage's bitmap ORs and its word difference array adds (counts.cuh).
 
-The exchange of one accumulator of n elements over W ranks: all-to-all of the W slices (each rank receives slice r of every
+Byte flags (MAX) and 32-bit counters (SUM) go through NCCL's all-reduce.  The other accumulators (unsigned 64-bit MAX /
+MIN keys, bitmaps combined by OR) have no NCCL reduction: all-to-all of the W slices (each rank receives slice r of every
 rank), one fold kernel over the W copies (gffx_fold), all-gather of the folded slices: 2 (W-1)/W n elements per rank over
 NVLink instead of the (W-1) n of a plain all-gather; NCCL has no bitwise-OR / unsigned-64 MIN reduction, which is why the
 reduction is our own kernel.  With the gloo backend (CPU tests) the same protocol runs on host arrays with a numpy fold.
@@ -116,6 +118,15 @@ class Combiner:
                 es = np.dtype(OPS[op][0]).itemsize
                 seg = -(-n // W)
                 t = torch.as_tensor(_DevView(ptr, n * es), device=self.stream.device)
+                if op == 0:      # byte flags: NCCL's own MAX
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+                    self.bytes_exchanged += 2 * (W - 1) * n // W
+                    continue
+                if op in (3, 4):  # 32-bit sums (wrap-around addition is the same for signed and unsigned)
+                    dist.all_reduce(t.view(torch.int32), op=dist.ReduceOp.SUM, group=self.group)
+                    self.bytes_exchanged += 2 * (W - 1) * n * 4 // W
+                    continue
+                # unsigned 64-bit MAX / MIN and bitwise OR: no NCCL reduction exists -> slices, our fold kernel, gather
                 send = self._buf("send", W * seg * es, t.device)
                 recv = self._buf("recv", W * seg * es, t.device)
                 send[: n * es].copy_(t)
@@ -129,7 +140,7 @@ class Combiner:
                 dist.all_gather_into_tensor(send, mine, group=self.group)
                 t.copy_(send[: n * es])
                 self.bytes_exchanged += 2 * (W - 1) * seg * es
-        self.stream.synchronize()
+        # no host synchronisation: the finish step is queued on the same (engine) stream
 
 
 def merge_count_rows(rows_per_shard: List[dict], kind: int) -> dict:
