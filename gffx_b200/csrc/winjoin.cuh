@@ -80,7 +80,8 @@ struct WjSlice {
     uint4 run[WJ_RUN_CAP];
     uint32_t boff[WJ_BINS_MAX + 1];
     uint32_t first[WJ_BINS_MAX + 1];
-    uint32_t lhit[WJ_LIST_CAP / 32], rhit[WJ_RUN_CAP / 32];
+    uint8_t lhit[WJ_LIST_CAP], rhit[WJ_RUN_CAP];   // hit flags of the slice members: plain byte stores, no atomics
+    uint32_t fits;   // every list member of the window is in the slice
     uint32_t w_first, w_last, lo, l0, nlist, j0, nrun;
 };
 
@@ -149,14 +150,16 @@ __global__ void __launch_bounds__(WJ_THREADS)
             const uint32_t l0 = __ldg(C.boff + row), l1 = __ldg(C.boff + row + nb);
             const uint32_t j0 = __ldg(C.first + row), j1 = __ldg(C.first + row + nb);
             S.l0 = l0; S.nlist = min(l1 - l0, (uint32_t)WJ_LIST_CAP);
+            S.fits = (l1 - l0 <= (uint32_t)WJ_LIST_CAP) ? 1u : 0u;
             S.j0 = j0; S.nrun = min(min(j1 - j0 + 8u, (uint32_t)WJ_RUN_CAP), C.n_ent - j0);
         }
         for (uint32_t i = threadIdx.x; i <= nb; i += WJ_THREADS) {
             S.boff[i] = __ldg(C.boff + row + i);
             S.first[i] = __ldg(C.first + row + i);
         }
-        if (threadIdx.x < WJ_LIST_CAP / 32) S.lhit[threadIdx.x] = 0;
-        if (threadIdx.x < WJ_RUN_CAP / 32) S.rhit[threadIdx.x] = 0;
+        static_assert(WJ_LIST_CAP / 4 <= WJ_THREADS && WJ_RUN_CAP / 4 <= WJ_THREADS, "one word of hit flags per thread");
+        if (threadIdx.x < WJ_LIST_CAP / 4) reinterpret_cast<uint32_t*>(S.lhit)[threadIdx.x] = 0;
+        if (threadIdx.x < WJ_RUN_CAP / 4) reinterpret_cast<uint32_t*>(S.rhit)[threadIdx.x] = 0;
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < S.nlist; i += WJ_THREADS) S.list[i] = __ldg(C.list4 + S.l0 + i);
         for (uint32_t i = threadIdx.x; i < S.nrun; i += WJ_THREADS) S.run[i] = __ldg(C.ent4 + S.j0 + i);
@@ -173,15 +176,49 @@ __global__ void __launch_bounds__(WJ_THREADS)
             if (b > nb - 1) b = nb - 1;
             bin[k] = b;
             uint32_t mk = 0;
-            wj_visit<MODE, INVERT>(C, S, b, s[k], e[k], [&](const uint4& v, uint32_t bit, uint32_t i, bool in_list) {
-                mk |= bit;
-                cnt++;
-                if (in_list ? i < S.nlist : i < S.nrun) {
-                    uint32_t* h = (in_list ? S.lhit : S.rhit) + (i >> 5);
-                    const uint32_t hb = 1u << (i & 31);
-                    if (!(*h & hb)) atomicOr(h, hb);
-                } else if (!ent_hit[v.w]) ent_hit[v.w] = 1;
-            });
+            const uint32_t rs = s[k], re = e[k];
+            const uint32_t o0 = S.boff[b], nL = S.boff[b + 1] - o0;
+            if (S.fits && nL <= 16u) {
+                // the common case, branch-free: the first four list members predicated, then the (rare) rest
+                const uint32_t il = o0 - S.l0;
+#pragma unroll
+                for (uint32_t t = 0; t < 4; t++) {
+                    const bool ok = t < nL;
+                    const uint4 v = S.list[ok ? il + t : 0u];
+                    if (ok && v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) { mk |= 1u << t; S.lhit[il + t] = 1; }
+                }
+                for (uint32_t t = 4; t < nL; t++) {
+                    const uint4 v = S.list[il + t];
+                    if (v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) { mk |= 1u << t; S.lhit[il + t] = 1; }
+                }
+            } else {
+                uint32_t bit = 1u;
+                for (uint32_t a = o0; a < o0 + nL; a++, bit <<= 1) {
+                    const uint32_t i = a - S.l0;
+                    const uint4 v = i < S.nlist ? S.list[i] : __ldg(C.list4 + a);
+                    if (v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) {
+                        mk |= (bit & 0xFFFFu) ? bit : 0x80000000u;
+                        if (bit & 0xFFFF0000u || bit == 0) cnt++;   // beyond the position bits: counted here, not by the popcount below
+                        if (i < S.nlist) S.lhit[i] = 1;
+                        else if (!ent_hit[v.w]) ent_hit[v.w] = 1;
+                    }
+                }
+            }
+            {
+                uint32_t bit = 1u << 16;
+                for (uint32_t j = S.first[b + 1];; j++, bit <<= 1) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
+                    const uint32_t i = j - S.j0;
+                    const uint4 v = i < S.nrun ? S.run[i] : __ldg(C.ent4 + j);
+                    if (v.x >= re) break;
+                    if (v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) {
+                        mk |= (bit & 0x7FFF0000u) ? bit : 0x80000000u;
+                        if (!(bit & 0x7FFF0000u)) cnt++;
+                        if (i < S.nrun) S.rhit[i] = 1;
+                        else if (!ent_hit[j]) ent_hit[j] = 1;
+                    }
+                }
+            }
+            cnt += __popc(mk & 0x7FFFFFFFu);
             mask[k] = mk;
         }
         uint32_t tot;
@@ -189,12 +226,12 @@ __global__ void __launch_bounds__(WJ_THREADS)
         if (tot != 0) {   // uniform
             // hit flags of the slice: one idempotent byte store per hit root and CTA
             for (uint32_t i = threadIdx.x; i < S.nlist; i += WJ_THREADS)
-                if ((S.lhit[i >> 5] >> (i & 31)) & 1u) {
+                if (S.lhit[i]) {
                     uint8_t* h = ent_hit + S.list[i].w;
                     if (!*h) *h = 1;
                 }
             for (uint32_t i = threadIdx.x; i < S.nrun; i += WJ_THREADS)
-                if ((S.rhit[i >> 5] >> (i & 31)) & 1u) {
+                if (S.rhit[i]) {
                     uint8_t* h = ent_hit + S.j0 + i;
                     if (!*h) *h = 1;
                 }
