@@ -359,6 +359,109 @@ def run_gpu(args, rank, world, local_rank):
     return 0
 
 
+# ---------------------------------------------------------------------------------------------------
+# depth / coverage (BASELINE.json configs[3]): --workload depth|coverage.  One step = one whole job over Q read
+# intervals of 150 bases (regions -> histograms / bitmap, scans, per-ID rows).  Not the default line of the contract
+# (that is the intersect sweep); run by hand and recorded under profiles/.
+# ---------------------------------------------------------------------------------------------------
+def run_counts(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    import gffx_b200 as g
+
+    kind = 0 if args.workload == "depth" else 1
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    if rank == 0:
+        ensure_workload(args.genes, g.build_index)
+    barrier()
+    gff = os.path.join(workload_dir(args.genes), "hs_synth.gff")
+    idx = g.TreeIndexData.load_tree_index(gff, device=local_rank)
+    Q = args.regions
+    reads = idx.synth_regions_device(20260010, Q, 150, first=rank * Q, device=dev)
+    combiner = None
+    if world > 1:
+        from gffx_b200.shard import Combiner
+
+        combiner = Combiner(idx)
+    fn = idx.depth if kind == 0 else idx.coverage
+    stream = torch.cuda.ExternalStream(idx.cuda_stream, device=dev)
+    for _ in range(args.warmup):
+        rows = fn(reads, combine=combiner)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    kms, launches = 0.0, 0
+    for _ in range(args.steps):
+        rows = fn(reads, combine=combiner)
+        kms += rows.kernel_ms
+        launches += rows.launches
+    ev1.record(stream)
+    barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop(t0, t1) if sampler else None
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    # end to end: pinned host reads in, rows out
+    e2e = None
+    if args.e2e_steps > 0:
+        host = tuple(torch.empty(Q, dtype=torch.int32, pin_memory=True) for _ in range(3))
+        idx.synth_regions(20260010, Q, 150, first=rank * Q, out=host)
+        fn(host, combine=combiner)
+        barrier()
+        te0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            r2 = fn(host, combine=combiner)
+        torch.cuda.synchronize()
+        te = torch.tensor([time.perf_counter() - te0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_s = float(te.item())
+        e2e = {"value": world * Q * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 12 * Q,
+               "d2h_bytes_per_step": int(r2.id_idx.shape[0]) * 24, "steps": args.e2e_steps, "ms_per_step": e2e_s / args.e2e_steps * 1e3}
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    n_rows = int(rows.id_idx.shape[0])
+    # B = 12*Q + 16*L + 24*F_out per job, over the job's kernels (event-timed inside the library)
+    nbytes = 12 * Q + 16 * idx.n_lines + 24 * n_rows
+    ach = nbytes * args.steps / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": world * Q * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u32", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: synthetic human-like GFF3 ({args.genes} genes, {idx.n_lines} lines) x {Q} 150-base read intervals per GPU per step",
+                   "rows": n_rows, "l2": "inputs larger than L2 (12 B x Q)"},
+        "roofline": {"bound": "hbm", "kernel": f"{args.workload} job (scatter + scans + rows)", "achieved": ach, "peak": peak, "unit": "GB/s",
+                     "frac": ach / peak, "traffic": None, "kernel_ms_per_step": kms / args.steps, "algorithmic_bytes_per_step": nbytes},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def cpu_baseline(args, idx, gff):
     """rank 0, N=1 only: the oracle (C++ restatement) on a bounded sample of the same workload, all host threads"""
     from tests import _oracle
@@ -387,12 +490,16 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the in-line cpu_baseline sample")
     ap.add_argument("--ref-seconds", type=float, default=150.0, help="target total CPU time of --impl reference")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="intersect", choices=["intersect", "depth", "coverage"],
+                    help="intersect = the contract's line (configs[1]); depth / coverage = configs[3], reported by hand")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: W >= 3
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
         return run_reference(args, rank, world)
+    if args.workload != "intersect":
+        return run_counts(args, rank, world, local_rank)
     return run_gpu(args, rank, world, local_rank)
 
 

@@ -331,7 +331,7 @@ class TreeIndexData:
             k = nr.value
 
             def arr(p, dt):
-                return np.ctypeslib.as_array(p, shape=(k,)).astype(dt, copy=True) if k else np.zeros(0, dtype=dt)
+                return np.ctypeslib.as_array(p, shape=(k,)).copy() if k else np.zeros(0, dtype=dt)
 
             rows = CountRows(arr(pid, np.uint32), arr(pch, np.uint32), arr(pst, np.uint32), arr(pen, np.uint32), arr(pv, np.uint64),
                              lib.gffx_counts_kernel_ms(st), lib.gffx_counts_launches(st), kind, self)

@@ -150,23 +150,58 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     return D;
 }
 
+// one batch of device-resident regions: K0 partition + the scatter kernel; asynchronous on the engine's stream
+static void counts_add_device(EngineImpl* E, CountsState* C, const CountsDev& D, const uint32_t* dc, const uint32_t* ds, const uint32_t* de,
+                              uint64_t n, uint32_t* oc, uint2* ose) {
+    const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
+    C->launches += E->partition_into(dc, ds, de, n, oc, ose, E->d_poff.as<uint32_t>());
+    const uint32_t ks = E->WG.shift > 8 ? E->WG.shift - 8 : 0;
+    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, oc, ose, n, ks, C->d_err.as<uint32_t>());
+    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, oc, ose, n, ks, C->d_err.as<uint32_t>());
+    C->launches += 1;
+}
+
 void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags) {
     CountsState* C = E->counts;
     if (!C || !C->active) throw Err(E_STATE, "gffx_counts_add without gffx_counts_begin");
     if (n == 0) return;
     if (!chr || !start || !end) throw Err(E_ARG, "NULL region arrays");
+    if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
     if (C->n_regions + n >= (1ull << 32)) throw Err(E_ARG, "more than 2^32-1 regions in one depth/coverage job (32-bit histogram slots)");
     GFFX_CUDA(cudaSetDevice(E->dev));
-    const uint32_t *dc, *ds, *de;
-    E->stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
     const CountsDev D = make_dev(E, C);
-    const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
+    const bool dev_in = flags & 1u;  // GFFX_F_DEVICE_INPUT
+    // host input: chunks of the copy cross PCIe while the previous chunk is partitioned and scattered
+    uint64_t chunk = n;
+    if (!dev_in && n >= (1u << 22)) chunk = ((n + 7) / 8 + PART_TILE - 1) / PART_TILE * PART_TILE;
+    const uint32_t n_chunks = (uint32_t)((n + chunk - 1) / chunk);
+    E->d_bchr.ensure(chunk * 4 + 16);
+    E->d_bse.ensure(chunk * 8 + 32);
     GFFX_CUDA(cudaEventRecord(C->ev0, E->st));
-    const uint32_t* bc = nullptr;  // K0: window-bucketed regions keep every look-up below in L1
-    const uint2* bse = nullptr;
-    C->launches += E->partition(dc, ds, de, n, &bc, &bse);
-    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, C->d_err.as<uint32_t>());
-    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, bc, bse, n, E->WG.shift > 8 ? E->WG.shift - 8 : 0, C->d_err.as<uint32_t>());
+    if (dev_in) {
+        counts_add_device(E, C, D, chr, start, end, n, E->d_bchr.as<uint32_t>(), E->d_bse.as<uint2>());
+    } else {
+        const uint32_t* src[3] = {chr, start, end};
+        for (int k = 0; k < 3; k++) E->d_q[k].ensure(n * 4);
+        while (E->ev_copy.size() < n_chunks) {
+            cudaEvent_t e;
+            GFFX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            E->ev_copy.push_back(e);
+        }
+        for (uint32_t c = 0; c < n_chunks; c++) {
+            const uint64_t o = (uint64_t)c * chunk, m = std::min<uint64_t>(chunk, n - o);
+            for (int k = 0; k < 3; k++)
+                GFFX_CUDA(cudaMemcpyAsync(E->d_q[k].as<uint32_t>() + o, src[k] + o, m * 4, cudaMemcpyHostToDevice, E->st_copy));
+            GFFX_CUDA(cudaEventRecord(E->ev_copy[c], E->st_copy));
+        }
+        for (uint32_t c = 0; c < n_chunks; c++) {
+            const uint64_t o = (uint64_t)c * chunk, m = std::min<uint64_t>(chunk, n - o);
+            GFFX_CUDA(cudaStreamWaitEvent(E->st, E->ev_copy[c], 0));
+            // the bucketed form of a chunk is scratch: the next chunk's partition overwrites it (stream order)
+            counts_add_device(E, C, D, E->d_q[0].as<uint32_t>() + o, E->d_q[1].as<uint32_t>() + o, E->d_q[2].as<uint32_t>() + o, m,
+                              E->d_bchr.as<uint32_t>(), E->d_bse.as<uint2>());
+        }
+    }
     GFFX_CUDA(cudaEventRecord(C->ev1, E->st));
     GFFX_CUDA(cudaMemcpyAsync(E->h_small, C->d_err.p, 4, cudaMemcpyDeviceToHost, E->st));
     GFFX_CUDA(cudaStreamSynchronize(E->st));
@@ -174,7 +209,6 @@ void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, 
     float ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, C->ev0, C->ev1));
     C->ms += ms;
-    C->launches += 1;
     C->n_regions += n;
     if (*(uint32_t*)E->h_small) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
 }

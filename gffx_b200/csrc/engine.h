@@ -25,6 +25,8 @@ template <class T> class HostBlob {
     const T* data() const { return (const T*)p_; }
     size_t size() const { return n_; }
     bool empty() const { return n_ == 0; }
+    T& operator[](size_t i) { return ((T*)p_)[i]; }
+    const T& operator[](size_t i) const { return ((const T*)p_)[i]; }
    private:
     void* p_ = nullptr;
     size_t cap_ = 0, n_ = 0;
@@ -55,9 +57,11 @@ struct IntersectResult {
     uint32_t launches = 0;
 };
 
-struct CountRows {
-    std::vector<uint32_t> id_idx, chrom_idx, start, end;
-    std::vector<uint64_t> value;
+
+
+struct CountRows {  // parallel arrays in page-locked memory
+    HostBlob<uint32_t> id_idx, chrom_idx, start, end;
+    HostBlob<uint64_t> value;
 };
 
 // how the shards' copies of an accumulator combine (gffx_reduce_op of the C ABI)
