@@ -43,7 +43,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off,
                     &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
@@ -62,7 +62,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off,
                     &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
@@ -176,7 +176,7 @@ void EngineImpl::build_join() {
     const std::vector<uint32_t>& jwin0 = h_win0;
     const uint32_t jshift = WG.shift;
     WinBinsHost bh;
-    uint32_t max_sub = 9;  // GFFX_WJ_SUB=0..9: coarser bins (tests: long lists, slices beyond the shared-memory capacity)
+    uint32_t max_sub = 7;  // GFFX_WJ_SUB=0..9; 2^7 bins per window: a 4096-region tile sorted by bin has >= 32 regions per bin
     if (const char* e = getenv("GFFX_WJ_SUB")) max_sub = (uint32_t)std::min(9, std::max(0, atoi(e)));
     build_win_bins((uint32_t)n_seqs, items, jwin0, jshift, max_sub, 1ull << 27, &bh);
     std::vector<uint4> ent4(bh.n_entries()), list4(std::max<size_t>(bh.list.size(), 1));
@@ -194,6 +194,8 @@ void EngineImpl::build_join() {
     upload(d_wj_blk, wblk, st);
     wj_n_ent = (uint32_t)bh.n_entries();
     d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));
+    d_wj_cnt.ensure(std::max<uint32_t>(wj_n_ent, 1) * 8ull);
+    d_wj_off.ensure(((uint64_t)wj_n_ent + 1) * 8);
     GFFX_CUDA(cudaStreamSynchronize(st));
     WC = WinBins{};
     WC.win_seq = d_wj_winseq.as<uint32_t>();
@@ -374,22 +376,37 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
 }
 
 template <int MODE, bool INV>
-static void launch_wj(EngineImpl* E, bool emit, const uint32_t* poff, const uint32_t* c, const uint2* se, uint64_t n, unsigned tiles,
-                      unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
-    if (emit)
-        wj_join_kernel<MODE, INV, true><<<tiles, WJ_THREADS, 0, E->st>>>(E->WC, poff, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, E->d_pairs.as<uint32_t>(), cap, err);
-    else
-        wj_join_kernel<MODE, INV, false><<<tiles, WJ_THREADS, 0, E->st>>>(E->WC, poff, c, se, n, E->d_wj_hit.as<uint8_t>(), n_pairs, nullptr, 0, err);
-}
-static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool emit, const uint32_t* poff, const uint32_t* c, const uint2* se, uint64_t n,
-                           unsigned tiles, unsigned long long* n_pairs, unsigned long long cap, uint32_t* err) {
-    switch (mode * 2 + (invert ? 1 : 0)) {
-        case 0: launch_wj<0, false>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
-        case 1: launch_wj<0, true>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
-        case 2: launch_wj<1, false>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
-        case 3: launch_wj<1, true>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
-        default: launch_wj<2, false>(E, emit, poff, c, se, n, tiles, n_pairs, cap, err); break;
+static void launch_wj(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
+    static bool attr_set = false;   // per instantiation: the kernel's dynamic shared memory is above the 48 KB default
+    if (!attr_set) {
+        GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WjSmem)));
+        attr_set = true;
     }
+    wj_count_kernel<MODE, INV><<<tiles, WJ_THREADS, sizeof(WjSmem), E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(),
+                                                                            E->d_wj_cnt.as<unsigned long long>(), n_pairs, err);
+}
+static void launch_wj_mode(EngineImpl* E, int mode, bool invert, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles,
+                           unsigned long long* n_pairs, uint32_t* err) {
+    switch (mode * 2 + (invert ? 1 : 0)) {
+        case 0: launch_wj<0, false>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 1: launch_wj<0, true>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 2: launch_wj<1, false>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 3: launch_wj<1, true>(E, poff, se, n, tiles, n_pairs, err); break;
+        default: launch_wj<2, false>(E, poff, se, n, tiles, n_pairs, err); break;
+    }
+}
+
+// K1b: per-root counters -> first-pair offsets -> the pair array (winjoin.cuh); nothing is written when the total exceeds `cap`
+uint32_t EngineImpl::expand_pairs(unsigned long long cap) {
+    typedef unsigned long long ull;
+    d_scan_scratch.ensure(scan_scratch_elems((uint64_t)wj_n_ent + 1) * 8);
+    uint32_t launches = device_scan<ull, OpSum, WjCntLoad, PtrStore<ull>, false, false>(
+        WjCntLoad{d_wj_cnt.as<ull>(), wj_n_ent}, PtrStore<ull>{d_wj_off.as<ull>()}, (uint64_t)wj_n_ent + 1, OpSum(), 0ull,
+        d_scan_scratch.as<ull>(), nullptr, st);
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    wj_expand_kernel<<<(unsigned)sms * 8, WJ_EXP_THREADS, 0, st>>>(d_wj_off.as<ull>(), WC.ent4, wj_n_ent, d_pairs.as<uint32_t>(), cap);
+    return launches + 1;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -426,7 +443,10 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
     d_poff.ensure((size_t)std::max<uint32_t>(n_chunks, 1) * (WG.n_win + 2) * 4);
     GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 256, st));
     GFFX_CUDA(cudaEventRecord(ev[0], st));
-    if (wj_n_ent) GFFX_CUDA(cudaMemsetAsync(d_wj_hit.p, 0, wj_n_ent, st));
+    if (wj_n_ent) {
+        GFFX_CUDA(cudaMemsetAsync(d_wj_hit.p, 0, wj_n_ent, st));
+        GFFX_CUDA(cudaMemsetAsync(d_wj_cnt.p, 0, wj_n_ent * 8ull, st));
+    }
     if (jb.run_filter) {
         if (jb.have_types) {  // -T: comma-split, trimmed, non-empty tokens (intersect.rs:252-259)
             std::vector<uint8_t> allow(std::max<size_t>(H->types.size(), 1), 0);
@@ -485,11 +505,11 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
     jb.launches += partition_into(dc, ds, de, n, oc, ose, poff);
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 1], st));
     if (jb.pairs_dev && jb.pair_cap == 0) {
-        d_pairs.ensure(std::max<uint64_t>(2 * std::max<uint64_t>(jb.retained, n), 1024) * 12);  // grow-only; a larger result re-runs the join
+        d_pairs.ensure(std::max<uint64_t>(2 * std::max<uint64_t>(jb.retained, n), 1024) * 12);  // grow-only; a larger result re-runs the expansion
         jb.pair_cap = d_pairs.cap / 12;
     }
     const unsigned tiles = (unsigned)((n + WJ_TILE - 1) / WJ_TILE);
-    launch_wj_mode(this, jb.mode, jb.invert, jb.pairs_dev, poff, oc, ose, n, tiles, small, jb.pair_cap, small32 + 12);
+    launch_wj_mode(this, jb.mode, jb.invert, poff, ose, n, tiles, small, small32 + 12);
     jb.launches++;
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 2], st));
     if (jb.run_filter) {
@@ -619,6 +639,11 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     }
     GFFX_CUDA(cudaEventRecord(ev[7], st));
 
+    // ---- pairs: the run-length expansion of the per-root hit counters (K1b) ----------------------
+    GFFX_CUDA(cudaEventRecord(ev[8], st));
+    if (jb.pairs_dev && !nothing && jb.n_total) launches += expand_pairs(jb.pair_cap);
+    GFFX_CUDA(cudaEventRecord(ev[9], st));
+
     // ---- results -----------------------------------------------------------------------------
     GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
     GFFX_CUDA(cudaStreamSynchronize(st));
@@ -631,17 +656,9 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     if (hs32[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
     out->n_pairs = hs[0];
     if (jb.pairs_dev && out->n_pairs > jb.pair_cap) {
-        // the pair buffer was too small for this result: grow it to the exact size and run the join again over the
-        // retained bucketed batches (hit flags are idempotent; only the pair counter restarts)
-        if (!jb.retained) throw Err(E_STATE, "pair buffer overflow in a streaming job");
+        // the pair buffer was too small for this result: grow it to the exact size and expand again (the counters are intact)
         d_pairs.ensure(out->n_pairs * 12);
-        GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 8, st));
-        for (size_t k = 0; k < jb.chunks.size(); k++) {
-            const IxChunk& ck = jb.chunks[k];
-            launch_wj_mode(this, mode, jb.invert, true, d_poff.as<uint32_t>() + k * (WG.n_win + 2), d_bchr.as<uint32_t>() + ck.off,
-                           d_bse.as<uint2>() + ck.off, ck.n, (unsigned)((ck.n + WJ_TILE - 1) / WJ_TILE), small, d_pairs.cap / 12, small32 + 12);
-            launches++;
-        }
+        launches += expand_pairs(d_pairs.cap / 12);
         GFFX_CUDA(cudaStreamSynchronize(st));
         GFFX_CUDA(cudaGetLastError());
     }
@@ -678,14 +695,15 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         GFFX_CUDA(cudaEventElapsedTime(&ms, ev_chunk[4 * k + 2], ev_chunk[4 * k + 3]));
         out->stage_ms[4] += ms;
     }
-    if (jb.pairs_dev) out->stage_ms[7] = out->stage_ms[0];
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[8], ev[9]));
+    out->stage_ms[7] = ms;  // offsets scan + pair expansion
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[3], ev[4]));
     out->stage_ms[3] = ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[4], ev[6]));
     out->stage_ms[5] = ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[6], ev[7]));
     out->stage_ms[6] = ms;
-    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[7]));
+    GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[9]));
     out->kernel_ms = ms;
     out->launches = launches;
 }

@@ -106,7 +106,7 @@ class EngineImpl {
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
 
     // ---- window-addressed root join (winjoin.cuh): what intersect uses -------------------------
-    DBuf d_wj_win0, d_wj_winseq, d_wj_ent4, d_wj_list4, d_wj_fid, d_wj_first, d_wj_boff, d_wj_blk, d_wj_hit;
+    DBuf d_wj_win0, d_wj_winseq, d_wj_ent4, d_wj_list4, d_wj_fid, d_wj_first, d_wj_boff, d_wj_blk, d_wj_hit, d_wj_cnt, d_wj_off;
     WinBins WC{};
     uint32_t wj_n_ent = 0;
 
@@ -130,7 +130,7 @@ class EngineImpl {
     // ---- per-call scratch --------------------------------------------------------------------
     DBuf d_q[3], d_tile_count, d_tile_off, d_scan_scratch, d_pairs, d_ranges, d_small, d_warn;
     void* h_small = nullptr;  // pinned, 256 B
-    cudaEvent_t ev[12];  // [0..7] stage boundaries of one intersect call, [8],[9] around the join emit kernel alone, [10] end of the partition pass
+    cudaEvent_t ev[12];  // [0..7] stage boundaries of one intersect call, [8],[9] around the pair expansion (K1b), [10] end of the partition pass
 
     IxJob job;
     std::vector<cudaEvent_t> ev_chunk, ev_copy;  // 4 timing events per batch of a job; one copy-done event per chunk
@@ -152,6 +152,7 @@ class EngineImpl {
     void ix_finish(IntersectResult* out);
     void ix_seal();
     uint32_t ix_scans(FilterScans* P);
+    uint32_t expand_pairs(unsigned long long cap);  // K1b: offsets scan + wj_expand_kernel into d_pairs
     // stage the regions on the device; returns device pointers (either the caller's or the staging buffers)
     void stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                        const uint32_t** dc, const uint32_t** ds, const uint32_t** de);

@@ -10,10 +10,10 @@
 
 namespace gffx {
 
-constexpr int WJ_THREADS = 256;
-constexpr int WJ_QPT = 4;  // consecutive bucketed regions per thread: one 16 B load of chr, two of (start,end)
+constexpr int WJ_THREADS = 512;
+constexpr int WJ_QPT = 8;            // regions per thread
 constexpr int WJ_TILE = WJ_THREADS * WJ_QPT;
-constexpr int WJ_STAGE_PAIRS = 1792;  // 21 KB of shared memory (5 CTAs per SM with the 20 KB window slice)
+constexpr int WJ_WARPS = WJ_THREADS / 32;
 
 // mode test of src/commands/intersect.rs:145-158 and the XOR of :161
 template <int MODE, bool INVERT> __device__ __forceinline__ bool wj_keep(uint32_t s, uint32_t e, uint32_t rs, uint32_t re) {
@@ -21,45 +21,33 @@ template <int MODE, bool INVERT> __device__ __forceinline__ bool wj_keep(uint32_
     return INVERT != keep;
 }
 
-// thread t loads tile elements t*4 .. t*4+3 (one 16 B load of chr, two of (start,end)); returns how many exist
-__device__ __forceinline__ int wj_load(const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n, uint64_t q0,
-                                       uint32_t (&c)[WJ_QPT], uint32_t (&s)[WJ_QPT], uint32_t (&e)[WJ_QPT]) {
-    if (q0 >= n) return 0;
-    if (q0 + WJ_QPT <= n) {
-        const uint4 cc = __ldcs(reinterpret_cast<const uint4*>(chr + q0));
-        const uint4 a = __ldcs(reinterpret_cast<const uint4*>(se + q0));
-        const uint4 b = __ldcs(reinterpret_cast<const uint4*>(se + q0) + 1);
-        c[0] = cc.x; c[1] = cc.y; c[2] = cc.z; c[3] = cc.w;
-        s[0] = a.x; e[0] = a.y; s[1] = a.z; e[1] = a.w;
-        s[2] = b.x; e[2] = b.y; s[3] = b.z; e[3] = b.w;
-        return WJ_QPT;
-    }
-    int m = 0;
-#pragma unroll
-    for (int k = 0; k < WJ_QPT; k++)
-        if (q0 + k < n) {
-            const uint2 v = se[q0 + k];
-            c[k] = chr[q0 + k]; s[k] = v.x; e[k] = v.y;
-            m = k + 1;
-        }
-    return m;
-}
-
 // ------------------------------------------------------------------------------------------------
-// K1, bin lists in shared memory.
+// K1 = wj_count_kernel (regions -> hits per root) + wj_expand_kernel (hits per root -> the pair array).
+//
+// What query_features returns per hit is (iv.root_fid, iv.start, iv.end) (src/commands/intersect.rs:162): the pair
+// names the ROOT only, so the result is the multiset { root r, once per region that hits r }.  The join therefore
+// counts, per root, the regions that pass the tests of tree.rs:110 and intersect.rs:145-161, and the pair array is
+// the run-length expansion of those counts (cnt[r] copies of r's 12-byte record, roots in start order per sequence —
+// the reference's own order is hash-map order per chromosome, nothing downstream depends on it).
 //
 // Index (winjoin_build.h, WinBinsHost): every window of the partition grid is cut into 2^sub bins; a bin owns the list
 // of the intervals overlapping it, and `first` points into the sequence's start-sorted interval array.  The intervals
 // that overlap a region starting in bin b are the members of b's list that pass the test, then the run of the sorted
 // array from first[b+1] while start < re.  Long genes, nested genes and chromosome-spanning roots cost nothing
-// extra: no running max-end to back-track over (r01h/r01i profiles: 400-900 instructions per region went into
-// candidates that an earlier long gene dragged in, or into probing one chain per nesting level).
+// extra: no running max-end to back-track over (r01h/r01i profiles).
 //
 // After K0 the bucketed regions of one window are CONTIGUOUS, so a tile of WJ_TILE regions lies in one window
-// (rarely a few: the sum over all tiles of extra windows is <= n_win).  The CTA copies the window's slice — bin
-// offsets, `first`, the list members and the run, as 16-byte (start,end,fid,id) records — into shared memory once,
-// and every region resolves with shared-memory reads only; whatever exceeds the slice capacity is read from global
-// memory, so the result is the same set for any input.
+// (rarely a few: the sum over all tiles of extra windows is <= n_win).  Per (tile, window) the CTA
+//   1. copies the window's slice — bin offsets, `first`, the list members and the run, as 16-byte
+//      (start,end,fid,id) records — into shared memory; whatever exceeds the slice capacity is read from global
+//      memory, so the result is the same for any input;
+//   2. counting-sorts its regions by bin in shared memory (one shared atomic per region, one scan of <= 512 counters);
+//   3. hands the bins to its warps: the <= 32 regions of a round all lie in ONE bin, so the candidate loops are
+//      uniform across the warp — one broadcast 16-byte shared load per candidate, the per-lane test, one ballot, and
+//      lane 0 adds the popcount to the candidate's counter.  No lane divergence, no per-hit stores (r01k / s17
+//      profiles of the per-region-thread versions: 480-490 instructions per region in divergent candidate loops and
+//      per-pair bookkeeping; this form: a few instructions per region plus the sort);
+//   4. adds the non-zero slot counters to the global per-root counters (one 64-bit atomic per hit root and CTA).
 constexpr int WJ_BINS_MAX = 512;    // bins per window (sub <= 9)
 constexpr int WJ_LIST_CAP = 768;    // list members of the window held in shared memory (12 KB)
 constexpr int WJ_RUN_CAP = 256;     // start-sorted intervals from the window's first held in shared memory (4 KB)
@@ -75,64 +63,53 @@ struct WinBins {
     uint32_t shift, sub, n_win, n_ent;
 };
 
-struct WjSlice {
+struct WjSmem {
+    uint2 sorted[WJ_TILE];                         // the (tile, window) regions ordered by bin
     uint4 list[WJ_LIST_CAP];
     uint4 run[WJ_RUN_CAP];
-    uint32_t boff[WJ_BINS_MAX + 1];
-    uint32_t first[WJ_BINS_MAX + 1];
-    uint8_t lhit[WJ_LIST_CAP], rhit[WJ_RUN_CAP];   // hit flags of the slice members: plain byte stores, no atomics
-    uint32_t fits;   // every list member of the window is in the slice
-    uint32_t w_first, w_last, lo, l0, nlist, j0, nrun;
+    uint2 bf[WJ_BINS_MAX + 1];                     // (boff - l0, first - j0): slice-local indices
+    uint32_t hist[WJ_BINS_MAX + 1];                // regions per bin -> first sorted position of the bin
+    uint32_t lcnt[WJ_LIST_CAP], rcnt[WJ_RUN_CAP];  // hits per slice member
+    uint32_t scan[WJ_WARPS + 1];
+    uint32_t tot;
+    uint32_t w_first, w_last;
 };
 
-// visits, in order, the intervals with start < re && end > rs that pass the mode test: f(record, bit) where bit is the
-// position code of the hit (list member i < 16 -> bit i, run member i < 15 -> bit 16+i, else bit 31 = "does not fit")
-template <int MODE, bool INVERT, class F>
-__device__ __forceinline__ void wj_visit(const WinBins& C, const WjSlice& S, uint32_t b, uint32_t rs, uint32_t re, F&& f) {
-    const uint32_t o0 = S.boff[b], o1 = S.boff[b + 1];
-    uint32_t bit = 1u;
-    for (uint32_t a = o0; a < o1; a++, bit <<= 1) {
-        const uint32_t i = a - S.l0;
-        const uint4 v = i < S.nlist ? S.list[i] : __ldg(C.list4 + a);
-        if (v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) f(v, (bit & 0xFFFFu) ? bit : 0x80000000u, i, true);
-    }
-    bit = 1u << 16;
-    for (uint32_t j = S.first[b + 1];; j++, bit <<= 1) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
-        const uint32_t i = j - S.j0;
-        const uint4 v = i < S.nrun ? S.run[i] : __ldg(C.ent4 + j);
-        if (v.x >= re) break;
-        if (v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) f(v, (bit & 0x7FFF0000u) ? bit : 0x80000000u, i, false);
-    }
-}
-
-// EMIT = false: pair count + per-entry hit flags only (the CLI path needs no pairs).
-// EMIT = true : also writes the pairs; a (tile, window) whose claimed range does not fit `cap` writes nothing (the
-//               host grows the buffer to the reported total and runs the kernel again).
-template <int MODE, bool INVERT, bool EMIT>
-__global__ void __launch_bounds__(WJ_THREADS)
-    wj_join_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint32_t* __restrict__ chr, const uint2* __restrict__ qse,
-                   uint64_t n, uint8_t* ent_hit, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ pairs,
-                   unsigned long long cap, uint32_t* __restrict__ err) {
-    __shared__ WjSlice S;
-    __shared__ __align__(16) uint32_t stage[EMIT ? WJ_STAGE_PAIRS * 3 : 4];
-    __shared__ uint32_t sm[WJ_THREADS / 32 + 1];
-    __shared__ unsigned long long sbase;
+template <int MODE, bool INVERT>
+__global__ void __launch_bounds__(WJ_THREADS, 2)
+    wj_count_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint2* __restrict__ qse, uint64_t n, uint8_t* ent_hit,
+                    unsigned long long* ent_cnt, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ err) {
+    extern __shared__ __align__(16) unsigned char wj_dyn[];
+    WjSmem& S = *reinterpret_cast<WjSmem*>(wj_dyn);
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t tile0 = blockIdx.x * (uint32_t)WJ_TILE;
     const uint32_t m = (uint32_t)min((uint64_t)WJ_TILE, n - tile0);
     const uint32_t n_win = C.n_win, nb = 1u << C.sub, bsh = C.shift - C.sub;
-    uint32_t c[WJ_QPT], s[WJ_QPT], e[WJ_QPT];
-    const uint32_t q0 = tile0 + threadIdx.x * WJ_QPT;
-    wj_load(chr, qse, n, q0, c, s, e);
+    // thread t holds the tile elements 2 * (k * THREADS + t) and the next one, k < QPT / 2: 16-byte loads, a warp on 512 contiguous bytes
+    uint32_t s[WJ_QPT], e[WJ_QPT];
+    const bool al16 = (reinterpret_cast<uintptr_t>(qse) & 15u) == 0;   // a batch appended at an odd offset is only 8-byte aligned
+#pragma unroll
+    for (int k = 0; k < WJ_QPT / 2; k++) {
+        const uint32_t i = 2u * ((uint32_t)k * WJ_THREADS + tid);
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (i + 1 < m && al16) v = __ldcs(reinterpret_cast<const uint4*>(qse + tile0 + i));
+        else if (i < m) {
+            const uint2 u = __ldcs(qse + tile0 + i);
+            v.x = u.x; v.y = u.y;
+            if (i + 1 < m) { const uint2 u1 = __ldcs(qse + tile0 + i + 1); v.z = u1.x; v.w = u1.y; }
+        }
+        s[2 * k] = v.x; e[2 * k] = v.y; s[2 * k + 1] = v.z; e[2 * k + 1] = v.w;
+    }
     // windows of the tile's first and last region: (number of window offsets <= position) - 1; poff has n_win + 2 cells
     {
         int nf = 0, nl = 0;
         for (uint32_t i0 = 0; i0 < n_win + 2; i0 += WJ_THREADS) {
-            const uint32_t i = i0 + threadIdx.x;
+            const uint32_t i = i0 + tid;
             const uint32_t o = i < n_win + 2 ? __ldg(poff + i) : 0xFFFFFFFFu;
             nf += __syncthreads_count(o <= tile0);
             nl += __syncthreads_count(o <= tile0 + m - 1);
         }
-        if (threadIdx.x == 0) { S.w_first = (uint32_t)nf - 1u; S.w_last = (uint32_t)nl - 1u; }
+        if (tid == 0) { S.w_first = (uint32_t)nf - 1u; S.w_last = (uint32_t)nl - 1u; }
     }
     __syncthreads();
     const uint32_t w_first = S.w_first, w_last = S.w_last;
@@ -140,153 +117,177 @@ __global__ void __launch_bounds__(WJ_THREADS)
         const uint32_t p_lo = max(__ldg(poff + w), tile0), p_hi = min(__ldg(poff + w + 1), tile0 + m);
         if (p_lo >= p_hi) continue;   // empty window (uniform)
         if (w >= n_win) {             // bucket of the regions whose sequence number is out of range
-            if (threadIdx.x == 0) *err = 1;
+            if (tid == 0) *err = 1;
             continue;
         }
+        // ---- 1. the window's slice -----------------------------------------------------------------
         const size_t row = (size_t)w * (nb + 1);
-        if (threadIdx.x == 0) {
-            const uint32_t cw = __ldg(C.win_seq + w);
-            S.lo = (w - __ldg(C.win0 + cw)) << C.shift;
-            const uint32_t l0 = __ldg(C.boff + row), l1 = __ldg(C.boff + row + nb);
-            const uint32_t j0 = __ldg(C.first + row), j1 = __ldg(C.first + row + nb);
-            S.l0 = l0; S.nlist = min(l1 - l0, (uint32_t)WJ_LIST_CAP);
-            S.fits = (l1 - l0 <= (uint32_t)WJ_LIST_CAP) ? 1u : 0u;
-            S.j0 = j0; S.nrun = min(min(j1 - j0 + 8u, (uint32_t)WJ_RUN_CAP), C.n_ent - j0);
+        const uint32_t lo = (w - __ldg(C.win0 + __ldg(C.win_seq + w))) << C.shift;
+        const uint32_t l0 = __ldg(C.boff + row), j0 = __ldg(C.first + row);
+        const uint32_t nlist = min(__ldg(C.boff + row + nb) - l0, (uint32_t)WJ_LIST_CAP);
+        const uint32_t nrun = min(min(__ldg(C.first + row + nb) - j0 + 8u, (uint32_t)WJ_RUN_CAP), C.n_ent - j0);
+        for (uint32_t i = tid; i <= nb; i += WJ_THREADS) {
+            S.bf[i] = make_uint2(__ldg(C.boff + row + i) - l0, __ldg(C.first + row + i) - j0);
+            S.hist[i] = 0;
         }
-        for (uint32_t i = threadIdx.x; i <= nb; i += WJ_THREADS) {
-            S.boff[i] = __ldg(C.boff + row + i);
-            S.first[i] = __ldg(C.first + row + i);
-        }
-        static_assert(WJ_LIST_CAP / 4 <= WJ_THREADS && WJ_RUN_CAP / 4 <= WJ_THREADS, "one word of hit flags per thread");
-        if (threadIdx.x < WJ_LIST_CAP / 4) reinterpret_cast<uint32_t*>(S.lhit)[threadIdx.x] = 0;
-        if (threadIdx.x < WJ_RUN_CAP / 4) reinterpret_cast<uint32_t*>(S.rhit)[threadIdx.x] = 0;
+        for (uint32_t i = tid; i < nlist; i += WJ_THREADS) { S.list[i] = __ldg(C.list4 + l0 + i); S.lcnt[i] = 0; }
+        for (uint32_t i = tid; i < nrun; i += WJ_THREADS) { S.run[i] = __ldg(C.ent4 + j0 + i); S.rcnt[i] = 0; }
+        if (tid == 0) S.tot = 0;
         __syncthreads();
-        for (uint32_t i = threadIdx.x; i < S.nlist; i += WJ_THREADS) S.list[i] = __ldg(C.list4 + S.l0 + i);
-        for (uint32_t i = threadIdx.x; i < S.nrun; i += WJ_THREADS) S.run[i] = __ldg(C.ent4 + S.j0 + i);
-        __syncthreads();
-        const uint32_t lo = S.lo;
-        uint32_t cnt = 0;
-        uint32_t mask[WJ_QPT], bin[WJ_QPT];
+        // ---- 2. counting sort of the window's regions by bin ----------------------------------------
+        uint32_t rank[WJ_QPT];
 #pragma unroll
         for (int k = 0; k < WJ_QPT; k++) {
-            mask[k] = 0;
-            const uint32_t q = q0 + k;
-            if (q < p_lo || q >= p_hi) continue;
-            uint32_t b = (s[k] - lo) >> bsh;
-            if (b > nb - 1) b = nb - 1;
-            bin[k] = b;
-            uint32_t mk = 0;
-            const uint32_t rs = s[k], re = e[k];
-            const uint32_t o0 = S.boff[b], nL = S.boff[b + 1] - o0;
-            if (S.fits && nL <= 16u) {
-                // the common case, branch-free: the first four list members predicated, then the (rare) rest
-                const uint32_t il = o0 - S.l0;
-#pragma unroll
-                for (uint32_t t = 0; t < 4; t++) {
-                    const bool ok = t < nL;
-                    const uint4 v = S.list[ok ? il + t : 0u];
-                    if (ok && v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) { mk |= 1u << t; S.lhit[il + t] = 1; }
-                }
-                for (uint32_t t = 4; t < nL; t++) {
-                    const uint4 v = S.list[il + t];
-                    if (v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) { mk |= 1u << t; S.lhit[il + t] = 1; }
-                }
-            } else {
-                uint32_t bit = 1u;
-                for (uint32_t a = o0; a < o0 + nL; a++, bit <<= 1) {
-                    const uint32_t i = a - S.l0;
-                    const uint4 v = i < S.nlist ? S.list[i] : __ldg(C.list4 + a);
-                    if (v.x < re && v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) {
-                        mk |= (bit & 0xFFFFu) ? bit : 0x80000000u;
-                        if (bit & 0xFFFF0000u || bit == 0) cnt++;   // beyond the position bits: counted here, not by the popcount below
-                        if (i < S.nlist) S.lhit[i] = 1;
-                        else if (!ent_hit[v.w]) ent_hit[v.w] = 1;
-                    }
-                }
-            }
-            {
-                uint32_t bit = 1u << 16;
-                for (uint32_t j = S.first[b + 1];; j++, bit <<= 1) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
-                    const uint32_t i = j - S.j0;
-                    const uint4 v = i < S.nrun ? S.run[i] : __ldg(C.ent4 + j);
-                    if (v.x >= re) break;
-                    if (v.y > rs && wj_keep<MODE, INVERT>(v.x, v.y, rs, re)) {
-                        mk |= (bit & 0x7FFF0000u) ? bit : 0x80000000u;
-                        if (!(bit & 0x7FFF0000u)) cnt++;
-                        if (i < S.nrun) S.rhit[i] = 1;
-                        else if (!ent_hit[j]) ent_hit[j] = 1;
-                    }
-                }
-            }
-            cnt += __popc(mk & 0x7FFFFFFFu);
-            mask[k] = mk;
+            const uint32_t q = tile0 + 2u * ((uint32_t)(k >> 1) * WJ_THREADS + tid) + (uint32_t)(k & 1);
+            rank[k] = 0xFFFFFFFFu;
+            if (q >= p_lo && q < p_hi) rank[k] = atomicAdd(&S.hist[min((s[k] - lo) >> bsh, nb - 1)], 1u);
         }
-        uint32_t tot;
-        const uint32_t pos = block_scan_excl(cnt, OpSum(), 0u, sm, &tot);
-        if (tot != 0) {   // uniform
-            // hit flags of the slice: one idempotent byte store per hit root and CTA
-            for (uint32_t i = threadIdx.x; i < S.nlist; i += WJ_THREADS)
-                if (S.lhit[i]) {
-                    uint8_t* h = ent_hit + S.list[i].w;
-                    if (!*h) *h = 1;
-                }
-            for (uint32_t i = threadIdx.x; i < S.nrun; i += WJ_THREADS)
-                if (S.rhit[i]) {
-                    uint8_t* h = ent_hit + S.j0 + i;
-                    if (!*h) *h = 1;
-                }
-            if (threadIdx.x == 0) sbase = atomicAdd(n_pairs, (unsigned long long)tot);
-            if (EMIT) {
-                __syncthreads();
-                const unsigned long long gbase = sbase;
-                if (gbase + tot <= cap) {
-                    const bool staged = tot <= WJ_STAGE_PAIRS;
-                    uint32_t* dst = staged ? stage + 3 * pos : pairs + 3 * (gbase + pos);
+        __syncthreads();
+        {
+            static_assert(WJ_BINS_MAX <= WJ_THREADS, "one bin counter per thread");
+            const uint32_t v = tid < nb ? S.hist[tid] : 0u;
+            uint32_t tot;
+            const uint32_t ex = block_scan_excl(v, OpSum(), 0u, S.scan, &tot);
+            if (tid < nb) S.hist[tid] = ex;   // every thread read its counter before the scan's first barrier
+            if (tid == 0) S.hist[nb] = tot;
+        }
+        __syncthreads();
 #pragma unroll
-                    for (int k = 0; k < WJ_QPT; k++) {
-                        const uint32_t mk = mask[k];
-                        if (!mk) continue;
-                        if (mk & 0x80000000u) {   // more hits than position bits: the same walk again
-                            wj_visit<MODE, INVERT>(C, S, bin[k], s[k], e[k], [&](const uint4& v, uint32_t, uint32_t, bool) {
-                                dst[0] = v.z; dst[1] = v.x; dst[2] = v.y;
-                                dst += 3;
-                            });
-                            continue;
-                        }
-                        const uint32_t o0 = S.boff[bin[k]], f1 = S.first[bin[k] + 1];
-                        for (uint32_t mm = mk & 0xFFFFu; mm; mm &= mm - 1) {
-                            const uint32_t a = o0 + (uint32_t)__ffs(mm) - 1u, i = a - S.l0;
-                            const uint4 v = i < S.nlist ? S.list[i] : __ldg(C.list4 + a);
-                            dst[0] = v.z; dst[1] = v.x; dst[2] = v.y;
-                            dst += 3;
-                        }
-                        for (uint32_t mm = mk >> 16; mm; mm &= mm - 1) {
-                            const uint32_t j = f1 + (uint32_t)__ffs(mm) - 1u, i = j - S.j0;
-                            const uint4 v = i < S.nrun ? S.run[i] : __ldg(C.ent4 + j);
-                            dst[0] = v.z; dst[1] = v.x; dst[2] = v.y;
-                            dst += 3;
+        for (int k = 0; k < WJ_QPT; k++)
+            if (rank[k] != 0xFFFFFFFFu) S.sorted[S.hist[min((s[k] - lo) >> bsh, nb - 1)] + rank[k]] = make_uint2(s[k], e[k]);
+        __syncthreads();
+        // ---- 3. probe: one bin per warp at a time, 32 of its regions per round, candidates in lock step ----------
+        uint32_t wtot = 0;   // uniform across the warp
+        for (uint32_t b = warp; b < nb; b += WJ_WARPS) {
+            const uint32_t p0 = S.hist[b], p1 = S.hist[b + 1];
+            if (p0 == p1) continue;
+            const uint2 b0 = S.bf[b], b1 = S.bf[b + 1];
+            for (uint32_t pp = p0; pp < p1; pp += 32) {
+                // a lane without a region holds (rs, re) = (max, 0): no interval has start < 0
+                const uint2 r = pp + lane < p1 ? S.sorted[pp + lane] : make_uint2(0xFFFFFFFFu, 0u);
+                for (uint32_t i = b0.x; i < b1.x; i++) {
+                    const bool in = i < nlist;
+                    const uint4 v = in ? S.list[i] : __ldg(C.list4 + l0 + i);
+                    const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                    const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                    if (nh) {
+                        wtot += nh;
+                        if (lane == 0) {
+                            if (in) atomicAdd(&S.lcnt[i], nh);
+                            else { atomicAdd(ent_cnt + v.w, (unsigned long long)nh); ent_hit[v.w] = 1; }
                         }
                     }
-                    if (staged) {
-                        __syncthreads();
-                        // 3*tot words to pairs + 3*gbase: scalar head up to 16-byte alignment, 16-byte body, scalar tail
-                        uint32_t* g = pairs + 3 * gbase;
-                        const uint32_t nwords = 3 * tot;
-                        const uint32_t head = min(nwords, (uint32_t)((4u - ((uint32_t)(3ull * gbase) & 3u)) & 3u));
-                        if (threadIdx.x < head) __stcs(g + threadIdx.x, stage[threadIdx.x]);
-                        const uint32_t nvec = (nwords - head) >> 2;
-                        uint4* gv = reinterpret_cast<uint4*>(g + head);
-                        for (uint32_t i = threadIdx.x; i < nvec; i += WJ_THREADS) {
-                            const uint32_t* sp = stage + head + 4 * i;   // shared reads are word-aligned only
-                            __stcs(gv + i, make_uint4(sp[0], sp[1], sp[2], sp[3]));
+                }
+                const uint32_t re_max = __reduce_max_sync(0xffffffffu, r.y);
+                for (uint32_t i = b1.y;; i++) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
+                    const bool in = i < nrun;
+                    const uint4 v = in ? S.run[i] : __ldg(C.ent4 + j0 + i);
+                    if (v.x >= re_max) break;
+                    const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                    const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                    if (nh) {
+                        wtot += nh;
+                        if (lane == 0) {
+                            if (in) atomicAdd(&S.rcnt[i], nh);
+                            else { atomicAdd(ent_cnt + j0 + i, (unsigned long long)nh); ent_hit[j0 + i] = 1; }
                         }
-                        const uint32_t done = head + 4 * nvec;
-                        if (threadIdx.x < nwords - done) __stcs(g + done + threadIdx.x, stage[done + threadIdx.x]);
                     }
                 }
             }
         }
-        __syncthreads();  // the slice, the stage and sbase are reused by the next window of this tile
+        if (lane == 0 && wtot) atomicAdd(&S.tot, wtot);
+        __syncthreads();
+        // ---- 4. slot counters -> per-root counters and hit flags ---------------------------------------------
+        for (uint32_t i = tid; i < nlist; i += WJ_THREADS) {
+            const uint32_t c = S.lcnt[i];
+            if (c) {
+                const uint32_t id = S.list[i].w;
+                atomicAdd(ent_cnt + id, (unsigned long long)c);
+                if (!ent_hit[id]) ent_hit[id] = 1;
+            }
+        }
+        for (uint32_t i = tid; i < nrun; i += WJ_THREADS) {
+            const uint32_t c = S.rcnt[i];
+            if (c) {
+                atomicAdd(ent_cnt + j0 + i, (unsigned long long)c);
+                if (!ent_hit[j0 + i]) ent_hit[j0 + i] = 1;
+            }
+        }
+        if (tid == 0 && S.tot) atomicAdd(n_pairs, (unsigned long long)S.tot);
+        __syncthreads();  // the slice and the sorted tile are reused by the next window of this tile
+    }
+}
+
+// element i of the scan that turns the per-root counters into first-pair offsets: n_ent counters, then one 0
+struct WjCntLoad {
+    const unsigned long long* cnt;
+    uint32_t n_ent;
+    __device__ unsigned long long operator()(uint64_t i) const { return i < n_ent ? cnt[i] : 0ull; }
+};
+
+// K1b: pairs[off[j] .. off[j+1]) = cnt[j] copies of (root_fid, start, end) of sorted interval j.  Output-centric: a
+// warp owns WJ_EXP_CHUNK consecutive pairs, finds the interval of its first pair by binary search over `off`
+// (n_ent + 1 ascending offsets, off[n_ent] = total) and walks forward, skipping the intervals nobody hit 32 at a
+// time; the stores are 16-byte st.cs (the 12-byte record repeats with period three vectors), so a root with
+// millions of hits (a chromosome-spanning `region` root) is spread over as many warps as its bytes need.
+constexpr int WJ_EXP_THREADS = 256;
+constexpr uint32_t WJ_EXP_CHUNK = 2048;   // pairs per warp and step: 24 KB
+
+static __global__ void __launch_bounds__(WJ_EXP_THREADS)
+    wj_expand_kernel(const unsigned long long* __restrict__ off, const uint4* __restrict__ ent4, uint32_t n_ent, uint32_t* __restrict__ pairs,
+                     unsigned long long cap) {
+    const unsigned long long total = off[n_ent];
+    if (total > cap) return;   // the host grows the buffer and launches again
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t n_warps = (uint64_t)gridDim.x * (WJ_EXP_THREADS / 32);
+    for (uint64_t chunk = (uint64_t)blockIdx.x * (WJ_EXP_THREADS / 32) + (threadIdx.x >> 5); chunk * WJ_EXP_CHUNK < total; chunk += n_warps) {
+        const unsigned long long p0 = chunk * WJ_EXP_CHUNK, p1 = min(p0 + WJ_EXP_CHUNK, total);
+        uint32_t lo = 0, hi = n_ent;   // off[lo] <= p0 < off[hi]
+        while (hi - lo > 1) {
+            const uint32_t mid = lo + ((hi - lo) >> 1);
+            if (__ldg(off + mid) <= p0) lo = mid;
+            else hi = mid;
+        }
+        uint32_t j = lo;   // off[j] <= p0 < off[j + 1]
+        unsigned long long p = p0;
+        while (true) {
+            const unsigned long long pe = min((unsigned long long)__ldg(off + j + 1), p1);   // this interval's pairs in the chunk: [p, pe)
+            const uint4 v = __ldg(ent4 + j);
+            const uint32_t c0 = v.z, c1 = v.x, c2 = v.y;   // word w of the pair array holds component w % 3
+            const unsigned long long w0 = 3ull * p, w1 = 3ull * pe;
+            unsigned long long wa = min((w0 + 3ull) & ~3ull, w1);   // first 16-byte boundary at or after w0
+            if (w0 + lane < wa) {
+                const uint32_t k = (uint32_t)((w0 + lane) % 3ull);
+                __stcs(pairs + w0 + lane, k == 0 ? c0 : k == 1 ? c1 : c2);
+            }
+            const unsigned long long wb = wa + ((w1 - wa) & ~3ull);   // end of the whole vectors
+            if (wa < wb) {
+                uint32_t k = (uint32_t)((wa + 4ull * lane) % 3ull);
+                uint4* g = reinterpret_cast<uint4*>(pairs + wa);
+                const uint64_t nv = (wb - wa) >> 2;
+                for (uint64_t u = lane; u < nv; u += 32) {
+                    // components k, k+1, k+2, k (mod 3); the next vector of this lane is 128 words on: k advances by 128 % 3 = 2
+                    const uint4 x = k == 0 ? make_uint4(c0, c1, c2, c0) : k == 1 ? make_uint4(c1, c2, c0, c1) : make_uint4(c2, c0, c1, c2);
+                    __stcs(g + u, x);
+                    k = k >= 1 ? k - 1 : 2;
+                }
+            }
+            if (wb + lane < w1) {
+                const uint32_t k = (uint32_t)((wb + lane) % 3ull);
+                __stcs(pairs + wb + lane, k == 0 ? c0 : k == 1 ? c1 : c2);
+            }
+            p = pe;
+            if (p >= p1) break;
+            // next interval with pairs: the first j' > j with off[j' + 1] > p (it exists: p < total = off[n_ent])
+            j++;
+            while (true) {
+                const uint32_t jj = j + lane;
+                const bool has = jj < n_ent && __ldg(off + jj + 1) > p;
+                const uint32_t bal = __ballot_sync(0xffffffffu, has);
+                if (bal) { j += (uint32_t)__ffs(bal) - 1u; break; }
+                j += 32;
+            }
+        }
     }
 }
 
