@@ -14,6 +14,7 @@
 #pragma once
 #include "filter.cuh"
 #include "join.cuh"
+#include "tilesort.cuh"
 
 namespace gffx {
 

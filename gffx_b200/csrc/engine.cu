@@ -176,7 +176,7 @@ void EngineImpl::build_join() {
     const std::vector<uint32_t>& jwin0 = h_win0;
     const uint32_t jshift = WG.shift;
     WinBinsHost bh;
-    uint32_t max_sub = 7;  // GFFX_WJ_SUB=0..9; 2^7 bins per window: a 4096-region tile sorted by bin has >= 32 regions per bin
+    uint32_t max_sub = 6;  // GFFX_WJ_SUB=0..9; 2^6 bins per window: a 4096-region tile sorted by bin has ~64 regions per bin (measured best of 5/6/7)
     if (const char* e = getenv("GFFX_WJ_SUB")) max_sub = (uint32_t)std::min(9, std::max(0, atoi(e)));
     build_win_bins((uint32_t)n_seqs, items, jwin0, jshift, max_sub, 1ull << 27, &bh);
     std::vector<uint4> ent4(bh.n_entries()), list4(std::max<size_t>(bh.list.size(), 1));
@@ -375,24 +375,32 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
     *dc = d_q[0].as<uint32_t>(); *ds = d_q[1].as<uint32_t>(); *de = d_q[2].as<uint32_t>();
 }
 
-template <int MODE, bool INV>
+template <int MODE, bool INV, bool FILT>
 static void launch_wj(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
-    static bool attr_set = false;   // per instantiation: the kernel's dynamic shared memory is above the 48 KB default
+    static bool attr_set = false;   // per instantiation: the kernel's dynamic shared memory on top of its static 26 KB exceeds the 48 KB default
     if (!attr_set) {
-        GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WjSmem)));
+        GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, FILT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
         attr_set = true;
     }
-    wj_count_kernel<MODE, INV><<<tiles, WJ_THREADS, sizeof(WjSmem), E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(),
-                                                                            E->d_wj_cnt.as<unsigned long long>(), n_pairs, err);
+    typedef unsigned long long ull;
+    FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>()};
+    wj_count_kernel<MODE, INV, FILT><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(), E->d_wj_cnt.as<ull>(),
+                                                                                n_pairs, err, E->FR, F);
 }
-static void launch_wj_mode(EngineImpl* E, int mode, bool invert, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles,
+// `filt`: the line filter's rank-space scatter (K3a) rides on the same pass
+static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool filt, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles,
                            unsigned long long* n_pairs, uint32_t* err) {
-    switch (mode * 2 + (invert ? 1 : 0)) {
-        case 0: launch_wj<0, false>(E, poff, se, n, tiles, n_pairs, err); break;
-        case 1: launch_wj<0, true>(E, poff, se, n, tiles, n_pairs, err); break;
-        case 2: launch_wj<1, false>(E, poff, se, n, tiles, n_pairs, err); break;
-        case 3: launch_wj<1, true>(E, poff, se, n, tiles, n_pairs, err); break;
-        default: launch_wj<2, false>(E, poff, se, n, tiles, n_pairs, err); break;
+    switch ((mode * 2 + (invert ? 1 : 0)) * 2 + (filt ? 1 : 0)) {
+        case 0: launch_wj<0, false, false>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 1: launch_wj<0, false, true>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 2: launch_wj<0, true, false>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 3: launch_wj<0, true, true>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 4: launch_wj<1, false, false>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 5: launch_wj<1, false, true>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 6: launch_wj<1, true, false>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 7: launch_wj<1, true, true>(E, poff, se, n, tiles, n_pairs, err); break;
+        case 8: launch_wj<2, false, false>(E, poff, se, n, tiles, n_pairs, err); break;
+        default: launch_wj<2, false, true>(E, poff, se, n, tiles, n_pairs, err); break;
     }
 }
 
@@ -509,18 +517,9 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
         jb.pair_cap = d_pairs.cap / 12;
     }
     const unsigned tiles = (unsigned)((n + WJ_TILE - 1) / WJ_TILE);
-    launch_wj_mode(this, jb.mode, jb.invert, poff, ose, n, tiles, small, small32 + 12);
+    launch_wj_mode(this, jb.mode, jb.invert, jb.run_filter, poff, ose, n, tiles, small, small32 + 12);   // K1 (+ K3a when the line filter runs)
     jb.launches++;
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 2], st));
-    if (jb.run_filter) {
-        FilterArrays F{d_A.as<unsigned long long>(), d_B.as<unsigned long long>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
-        const unsigned sblocks = (unsigned)((n + (uint64_t)FILT_THREADS * FILT_QPT - 1) / ((uint64_t)FILT_THREADS * FILT_QPT));
-        const uint32_t ks = WG.shift > 8 ? WG.shift - 8 : 0;
-        if (jb.mode == 0) scatter_regions_kernel<0><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, oc, ose, n, ks);
-        else if (jb.mode == 1) scatter_regions_kernel<1><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, oc, ose, n, ks);
-        else scatter_regions_kernel<2><<<sblocks, FILT_THREADS, 0, st>>>(FR, F, oc, ose, n, ks);
-        jb.launches++;
-    }
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 3], st));
 }
 

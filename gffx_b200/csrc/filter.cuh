@@ -23,7 +23,6 @@
 // plain (unsegmented) scan serve all sequences.
 #pragma once
 #include "scan.cuh"
-#include "tilesort.cuh"
 
 namespace gffx {
 
@@ -76,52 +75,23 @@ struct FilterArrays {
     uint8_t* Me;            // 2*n_slots
 };
 
-// one streaming pass over the regions (12 B read per region, 1-3 scattered L2 updates)
+// one region (qs, qe) of sequence `seq` onto the rank space: 1-3 scattered L2 updates
 template <int MODE>
-__global__ void __launch_bounds__(FILT_THREADS)
-    scatter_regions_kernel(RankSpace R, FilterArrays F, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n,
-                           uint32_t key_shift) {
-    __shared__ TileSortSmem<FILT_THREADS, FILT_QPT> ts;
-    const uint64_t tile0 = (uint64_t)blockIdx.x * FILT_THREADS * FILT_QPT;
-    const uint32_t tm = (uint32_t)min((uint64_t)FILT_THREADS * FILT_QPT, n - tile0);
-    const uint64_t q0 = tile0 + (uint64_t)threadIdx.x * FILT_QPT;
-    uint32_t c[FILT_QPT], s[FILT_QPT], e[FILT_QPT];
-    bool valid[FILT_QPT];
-    int m = 0;
-    if (q0 + FILT_QPT <= n) {
-        const uint4 a = __ldcs(reinterpret_cast<const uint4*>(chr + q0));
-        const uint4 b = __ldcs(reinterpret_cast<const uint4*>(se + q0));
-        const uint4 d = __ldcs(reinterpret_cast<const uint4*>(se + q0) + 1);
-        c[0] = a.x; c[1] = a.y; c[2] = a.z; c[3] = a.w;
-        s[0] = b.x; e[0] = b.y; s[1] = b.z; e[1] = b.w;
-        s[2] = d.x; e[2] = d.y; s[3] = d.z; e[3] = d.w;
-        m = FILT_QPT;
+__device__ __forceinline__ void scatter_region(const RankSpace& R, const RankSeq& S, const FilterArrays& F, uint32_t seq, uint32_t qs, uint32_t qe) {
+    bool eq;
+    const uint32_t lb = rank_lb(R, S, qs, &eq);
+    const uint32_t slot = S.slot0 + lb;
+    if (MODE == 0) {
+        atomicMax(F.A + slot, ((unsigned long long)seq << TAG_MAX_SHIFT) | ((unsigned long long)qe + 1ull));
+    } else if (MODE == 1) {
+        atomicMin(F.B + slot + (eq ? 1u : 0u), ((unsigned long long)seq << TAG_MIN_SHIFT) | (unsigned long long)qe);
     } else {
-        for (int k = 0; k < FILT_QPT; k++)
-            if (q0 + k < n) { const uint2 v = se[q0 + k]; c[k] = chr[q0 + k]; s[k] = v.x; e[k] = v.y; m = k + 1; }
-    }
-    // a warp's 32 regions next to each other on the genome: the rank look-ups below share their cache lines
-    tile_sort<FILT_THREADS, FILT_QPT>(ts, key_shift, tm, m, c, s, e, valid);
-#pragma unroll
-    for (int k = 0; k < FILT_QPT; k++) {
-        if (!valid[k] || c[k] >= R.n_seqs) continue;
-        const RankSeq S = load_rank_seq(R, c[k]);
-        if (!S.canon || S.cnt == 0) continue;  // no line of this sequence can ever match
-        bool eq;
-        const uint32_t lb = rank_lb(R, S, s[k], &eq);
-        const uint32_t slot = S.slot0 + lb;
-        if (MODE == 0) {
-            atomicMax(F.A + slot, ((unsigned long long)c[k] << TAG_MAX_SHIFT) | ((unsigned long long)e[k] + 1ull));
-        } else if (MODE == 1) {
-            atomicMin(F.B + slot + (eq ? 1u : 0u), ((unsigned long long)c[k] << TAG_MIN_SHIFT) | (unsigned long long)e[k]);
-        } else {
-            atomicMax(F.A + slot, ((unsigned long long)c[k] << TAG_MAX_SHIFT) | ((unsigned long long)e[k] + 1ull));
-            F.Ms[2ull * slot + (eq ? 1u : 0u)] = 1;
-            if (s[k] > e[k]) {
-                bool eq2;
-                const uint32_t lb2 = rank_lb(R, S, e[k], &eq2);
-                F.Me[2ull * (S.slot0 + lb2) + (eq2 ? 1u : 0u)] = 1;
-            }
+        atomicMax(F.A + slot, ((unsigned long long)seq << TAG_MAX_SHIFT) | ((unsigned long long)qe + 1ull));
+        F.Ms[2ull * slot + (eq ? 1u : 0u)] = 1;
+        if (qs > qe) {
+            bool eq2;
+            const uint32_t lb2 = rank_lb(R, S, qe, &eq2);
+            F.Me[2ull * (S.slot0 + lb2) + (eq2 ? 1u : 0u)] = 1;
         }
     }
 }

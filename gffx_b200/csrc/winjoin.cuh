@@ -7,6 +7,7 @@
 // test of intersect.rs:145-163.
 #pragma once
 #include "scan.cuh"
+#include "filter.cuh"
 
 namespace gffx {
 
@@ -63,8 +64,7 @@ struct WinBins {
     uint32_t shift, sub, n_win, n_ent;
 };
 
-struct WjSmem {
-    uint2 sorted[WJ_TILE];                         // the (tile, window) regions ordered by bin
+struct WjSmem {   // static shared memory (26 KB); the sorted tile (WJ_DYN_SMEM bytes) is the dynamic part
     uint4 list[WJ_LIST_CAP];
     uint4 run[WJ_RUN_CAP];
     uint2 bf[WJ_BINS_MAX + 1];                     // (boff - l0, first - j0): slice-local indices
@@ -73,14 +73,28 @@ struct WjSmem {
     uint32_t scan[WJ_WARPS + 1];
     uint32_t tot;
     uint32_t w_first, w_last;
+    uint32_t next_bin;                             // bins are handed to the warps in arrival order
+    uint32_t sent;                                 // slice-local index of the sequence's sentinel if the run holds it, else 0xFFFFFFFF
 };
+constexpr size_t WJ_DYN_SMEM = (size_t)WJ_TILE * sizeof(uint2);   // the (tile, window) regions ordered by bin
 
-template <int MODE, bool INVERT>
-__global__ void __launch_bounds__(WJ_THREADS, 2)
+#ifndef WJ_MIN_CTAS
+#define WJ_MIN_CTAS 3     // 40 registers: the join alone fits without spills
+#endif
+#ifndef WJ_MIN_CTAS_FILT
+#define WJ_MIN_CTAS_FILT 2
+#endif
+// FILT: the same pass also scatters every region onto the line filter's rank space (K3a, filter.cuh: scatter_region) —
+// the regions are in shared memory already, and a round's 32 regions start inside one bin, so their rank look-ups
+// walk the same few cache lines.  (As its own kernel, with its own load and tile sort, K3a took 120-135 us per 10 M
+// regions, L1-bound on those look-ups: profiles/r01k.)
+template <int MODE, bool INVERT, bool FILT>
+__global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_CTAS)
     wj_count_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint2* __restrict__ qse, uint64_t n, uint8_t* ent_hit,
-                    unsigned long long* ent_cnt, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ err) {
-    extern __shared__ __align__(16) unsigned char wj_dyn[];
-    WjSmem& S = *reinterpret_cast<WjSmem*>(wj_dyn);
+                    unsigned long long* ent_cnt, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ err, RankSpace R,
+                    FilterArrays F) {
+    extern __shared__ __align__(16) uint2 wj_sorted[];
+    __shared__ WjSmem S;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t tile0 = blockIdx.x * (uint32_t)WJ_TILE;
     const uint32_t m = (uint32_t)min((uint64_t)WJ_TILE, n - tile0);
@@ -109,7 +123,7 @@ __global__ void __launch_bounds__(WJ_THREADS, 2)
             nf += __syncthreads_count(o <= tile0);
             nl += __syncthreads_count(o <= tile0 + m - 1);
         }
-        if (tid == 0) { S.w_first = (uint32_t)nf - 1u; S.w_last = (uint32_t)nl - 1u; }
+        if (tid == 0) { S.w_first = (uint32_t)nf - 1u; S.w_last = (uint32_t)nl - 1u; S.sent = 0xFFFFFFFFu; }
     }
     __syncthreads();
     const uint32_t w_first = S.w_first, w_last = S.w_last;
@@ -122,7 +136,14 @@ __global__ void __launch_bounds__(WJ_THREADS, 2)
         }
         // ---- 1. the window's slice -----------------------------------------------------------------
         const size_t row = (size_t)w * (nb + 1);
-        const uint32_t lo = (w - __ldg(C.win0 + __ldg(C.win_seq + w))) << C.shift;
+        const uint32_t seq = __ldg(C.win_seq + w);
+        const uint32_t lo = (w - __ldg(C.win0 + seq)) << C.shift;
+        RankSeq RS{};
+        bool filt = false;   // no line of a sequence without rank space can ever match
+        if (FILT) {
+            RS = load_rank_seq(R, seq);
+            filt = RS.canon && RS.cnt != 0;
+        }
         const uint32_t l0 = __ldg(C.boff + row), j0 = __ldg(C.first + row);
         const uint32_t nlist = min(__ldg(C.boff + row + nb) - l0, (uint32_t)WJ_LIST_CAP);
         const uint32_t nrun = min(min(__ldg(C.first + row + nb) - j0 + 8u, (uint32_t)WJ_RUN_CAP), C.n_ent - j0);
@@ -131,8 +152,12 @@ __global__ void __launch_bounds__(WJ_THREADS, 2)
             S.hist[i] = 0;
         }
         for (uint32_t i = tid; i < nlist; i += WJ_THREADS) { S.list[i] = __ldg(C.list4 + l0 + i); S.lcnt[i] = 0; }
-        for (uint32_t i = tid; i < nrun; i += WJ_THREADS) { S.run[i] = __ldg(C.ent4 + j0 + i); S.rcnt[i] = 0; }
-        if (tid == 0) S.tot = 0;
+        for (uint32_t i = tid; i < nrun; i += WJ_THREADS) {
+            const uint4 v = __ldg(C.ent4 + j0 + i);
+            S.run[i] = v; S.rcnt[i] = 0;
+            if (v.x == 0xFFFFFFFFu) atomicMin(&S.sent, i);   // what follows the sentinel belongs to the next sequence
+        }
+        if (tid == 0) { S.tot = 0; S.next_bin = 0; }
         __syncthreads();
         // ---- 2. counting sort of the window's regions by bin ----------------------------------------
         uint32_t rank[WJ_QPT];
@@ -154,48 +179,92 @@ __global__ void __launch_bounds__(WJ_THREADS, 2)
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < WJ_QPT; k++)
-            if (rank[k] != 0xFFFFFFFFu) S.sorted[S.hist[min((s[k] - lo) >> bsh, nb - 1)] + rank[k]] = make_uint2(s[k], e[k]);
+            if (rank[k] != 0xFFFFFFFFu) wj_sorted[S.hist[min((s[k] - lo) >> bsh, nb - 1)] + rank[k]] = make_uint2(s[k], e[k]);
         __syncthreads();
         // ---- 3. probe: one bin per warp at a time, 32 of its regions per round, candidates in lock step ----------
-        uint32_t wtot = 0;   // uniform across the warp
+        const bool list_full = __ldg(C.boff + row + nb) - l0 <= (uint32_t)WJ_LIST_CAP;   // every list member of the window is in shared memory
+        const uint32_t run_end = S.sent == 0xFFFFFFFFu ? nrun : min(nrun, S.sent + 1u);   // the shared-memory run is ascending in start up to here
+        uint32_t mytot = 0;   // this lane's part of the (tile, window) hit total
+        // the general walks: any list length, members beyond the shared-memory slice read from global memory
+        auto walk_list = [&](const uint2 r, uint32_t i0, uint32_t i1) {
+            for (uint32_t i = i0; i < i1; i++) {
+                const bool in = i < nlist;
+                const uint4 v = in ? S.list[i] : __ldg(C.list4 + l0 + i);
+                const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                if (nh && lane == 0) {
+                    mytot += nh;
+                    if (in) atomicAdd(&S.lcnt[i], nh);
+                    else { atomicAdd(ent_cnt + v.w, (unsigned long long)nh); ent_hit[v.w] = 1; }
+                }
+            }
+        };
+        auto walk_run = [&](const uint2 r, uint32_t i0, uint32_t re_max) {
+            for (uint32_t i = i0;; i++) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
+                const bool in = i < nrun;
+                const uint4 v = in ? S.run[i] : __ldg(C.ent4 + j0 + i);
+                if (v.x >= re_max) break;
+                const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                if (nh && lane == 0) {
+                    mytot += nh;
+                    if (in) atomicAdd(&S.rcnt[i], nh);
+                    else { atomicAdd(ent_cnt + j0 + i, (unsigned long long)nh); ent_hit[j0 + i] = 1; }
+                }
+            }
+        };
+#ifndef WJ_STATIC_BINS
+        for (;;) {
+            uint32_t b = 0;
+            if (lane == 0) b = atomicAdd(&S.next_bin, 1u);   // per-bin work varies (regions x candidates): no warp waits at the barrier for long
+            b = __shfl_sync(0xffffffffu, b, 0);
+            if (b >= nb) break;
+#else
         for (uint32_t b = warp; b < nb; b += WJ_WARPS) {
+#endif
             const uint32_t p0 = S.hist[b], p1 = S.hist[b + 1];
             if (p0 == p1) continue;
             const uint2 b0 = S.bf[b], b1 = S.bf[b + 1];
+            const uint32_t nL = b1.x - b0.x;
+            const bool lean_list = list_full && nL <= 32u;
+            // lean form: lane t keeps the hits of the bin's list member t and run member t in registers
+            uint32_t lacc = 0, racc = 0;
+            // within 32 run members of the bin's first one the start reaches the round's largest region end
+            const uint32_t jl = min(b1.y + 31u, run_end - 1u);
+            const uint32_t run_reach = (run_end && b1.y < run_end) ? S.run[jl].x : 0u;
             for (uint32_t pp = p0; pp < p1; pp += 32) {
                 // a lane without a region holds (rs, re) = (max, 0): no interval has start < 0
-                const uint2 r = pp + lane < p1 ? S.sorted[pp + lane] : make_uint2(0xFFFFFFFFu, 0u);
-                for (uint32_t i = b0.x; i < b1.x; i++) {
-                    const bool in = i < nlist;
-                    const uint4 v = in ? S.list[i] : __ldg(C.list4 + l0 + i);
-                    const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
-                    const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
-                    if (nh) {
-                        wtot += nh;
-                        if (lane == 0) {
-                            if (in) atomicAdd(&S.lcnt[i], nh);
-                            else { atomicAdd(ent_cnt + v.w, (unsigned long long)nh); ent_hit[v.w] = 1; }
-                        }
+                const uint2 r = pp + lane < p1 ? wj_sorted[pp + lane] : make_uint2(0xFFFFFFFFu, 0u);
+                if (FILT && filt && pp + lane < p1) scatter_region<MODE>(R, RS, F, seq, r.x, r.y);
+                if (lean_list) {
+                    for (uint32_t t = 0; t < nL; t++) {
+                        const uint4 v = S.list[b0.x + t];
+                        const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                        const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                        if (lane == t) lacc += nh;
                     }
+                } else {
+                    walk_list(r, b0.x, b1.x);
                 }
                 const uint32_t re_max = __reduce_max_sync(0xffffffffu, r.y);
-                for (uint32_t i = b1.y;; i++) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
-                    const bool in = i < nrun;
-                    const uint4 v = in ? S.run[i] : __ldg(C.ent4 + j0 + i);
-                    if (v.x >= re_max) break;
-                    const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
-                    const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
-                    if (nh) {
-                        wtot += nh;
-                        if (lane == 0) {
-                            if (in) atomicAdd(&S.rcnt[i], nh);
-                            else { atomicAdd(ent_cnt + j0 + i, (unsigned long long)nh); ent_hit[j0 + i] = 1; }
-                        }
+                if (run_reach >= re_max && re_max != 0u) {
+                    for (uint32_t t = 0;; t++) {
+                        const uint4 v = S.run[b1.y + t];
+                        if (v.x >= re_max) break;
+                        const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                        const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                        if (lane == t) racc += nh;
                     }
+                } else {
+                    walk_run(r, b1.y, re_max);
                 }
             }
+            if (lacc) atomicAdd(&S.lcnt[b0.x + lane], lacc);
+            if (racc) atomicAdd(&S.rcnt[b1.y + lane], racc);
+            mytot += lacc + racc;
         }
-        if (lane == 0 && wtot) atomicAdd(&S.tot, wtot);
+        mytot = __reduce_add_sync(0xffffffffu, mytot);
+        if (lane == 0 && mytot) atomicAdd(&S.tot, mytot);
         __syncthreads();
         // ---- 4. slot counters -> per-root counters and hit flags ---------------------------------------------
         for (uint32_t i = tid; i < nlist; i += WJ_THREADS) {
@@ -213,7 +282,10 @@ __global__ void __launch_bounds__(WJ_THREADS, 2)
                 if (!ent_hit[j0 + i]) ent_hit[j0 + i] = 1;
             }
         }
-        if (tid == 0 && S.tot) atomicAdd(n_pairs, (unsigned long long)S.tot);
+        if (tid == 0) {
+            if (S.tot) atomicAdd(n_pairs, (unsigned long long)S.tot);
+            S.sent = 0xFFFFFFFFu;
+        }
         __syncthreads();  // the slice and the sorted tile are reused by the next window of this tile
     }
 }
@@ -240,8 +312,11 @@ static __global__ void __launch_bounds__(WJ_EXP_THREADS)
     if (total > cap) return;   // the host grows the buffer and launches again
     const uint32_t lane = threadIdx.x & 31u;
     const uint64_t n_warps = (uint64_t)gridDim.x * (WJ_EXP_THREADS / 32);
-    for (uint64_t chunk = (uint64_t)blockIdx.x * (WJ_EXP_THREADS / 32) + (threadIdx.x >> 5); chunk * WJ_EXP_CHUNK < total; chunk += n_warps) {
-        const unsigned long long p0 = chunk * WJ_EXP_CHUNK, p1 = min(p0 + WJ_EXP_CHUNK, total);
+    // pairs per warp and step: the whole grid gets work even for a small result (the walk over the intervals of a chunk
+    // is a chain of dependent loads), at most WJ_EXP_CHUNK
+    const unsigned long long per = min((unsigned long long)WJ_EXP_CHUNK, max(32ull, (total + n_warps - 1) / n_warps));
+    for (uint64_t chunk = (uint64_t)blockIdx.x * (WJ_EXP_THREADS / 32) + (threadIdx.x >> 5); chunk * per < total; chunk += n_warps) {
+        const unsigned long long p0 = chunk * per, p1 = min(p0 + per, total);
         uint32_t lo = 0, hi = n_ent;   // off[lo] <= p0 < off[hi]
         while (hi - lo > 1) {
             const uint32_t mid = lo + ((hi - lo) >> 1);
