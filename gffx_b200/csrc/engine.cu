@@ -44,7 +44,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
                     &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off,
-                    &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
+                    &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
     build_windows();
@@ -63,7 +63,7 @@ EngineImpl::~EngineImpl() {
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
                     &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off,
-                    &d_win0, &d_poff, &d_pmat, &d_pscan, &d_pscratch, &d_bchr, &d_bse,
+                    &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
     dj.release();
@@ -100,6 +100,9 @@ void EngineImpl::build_windows() {
     WG.shift = shift;
     WG.n_win = h_win0[n_seqs];
     d_poff.ensure(((size_t)WG.n_win + 2) * 4);
+    d_ptot.ensure((size_t)PART_NB_MAX * 4);   // window totals: zero between partition passes (part_offsets_kernel clears them)
+    d_pcur.ensure((size_t)PART_NB_MAX * 4);
+    GFFX_CUDA(cudaMemsetAsync(d_ptot.p, 0, (size_t)PART_NB_MAX * 4, st));
     GFFX_CUDA(cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PART_SCATTER_SMEM));
     GFFX_CUDA(cudaStreamSynchronize(st));
 }
@@ -116,26 +119,18 @@ uint32_t EngineImpl::partition(const uint32_t* dc, const uint32_t* ds, const uin
     return launches;
 }
 
-// the same pass with caller-chosen outputs: `oc`/`ose` take the n bucketed regions, `poff` the n_win + 2 window offsets.
-// The count matrix and its scan are scratch that the NEXT call on the stream reuses (stream order keeps that safe).
+// the same pass with caller-chosen outputs: `ose` (and `oc` unless NULL) take the n bucketed regions, `poff` the n_win + 2
+// window offsets.  The window totals and cursors are scratch that the NEXT call on the stream reuses (stream order keeps that safe).
 uint32_t EngineImpl::partition_into(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, uint32_t* oc, uint2* ose,
                                     uint32_t* poff) {
     if (n == 0) return 0;
     if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
     const uint32_t nb = WG.n_win + 1;
     const unsigned tiles = (unsigned)((n + PART_TILE - 1) / PART_TILE);
-    const uint64_t cells = (uint64_t)nb * tiles;
-    d_pmat.ensure(cells * 4);
-    d_pscan.ensure(cells * 4);
-    d_pscratch.ensure(scan_scratch_elems(cells) * 4);
-    part_count_kernel<<<tiles, PART_THREADS, 0, st>>>(WG, dc, ds, (uint32_t)n, tiles, d_pmat.as<uint32_t>());
-    uint32_t launches = 1;
-    launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, false>(
-        PtrLoad<uint32_t>{d_pmat.as<uint32_t>()}, PtrStore<uint32_t>{d_pscan.as<uint32_t>()}, cells, OpSum(), 0u, d_pscratch.as<uint32_t>(), nullptr, st);
-    part_scatter_kernel<<<tiles, PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, tiles, d_pmat.as<uint32_t>(), d_pscan.as<uint32_t>(),
-                                                                       oc, ose);
-    part_offsets_kernel<<<(nb + 1 + 255) / 256, 256, 0, st>>>(d_pscan.as<uint32_t>(), nb, tiles, (uint32_t)n, poff);
-    return launches + 2;
+    part_count_kernel<<<(tiles + PART_COUNT_TILES - 1) / PART_COUNT_TILES, PART_THREADS, 0, st>>>(WG, dc, ds, (uint32_t)n, d_ptot.as<uint32_t>());
+    part_offsets_kernel<<<1, PART_NB_MAX, 0, st>>>(d_ptot.as<uint32_t>(), nb, (uint32_t)n, poff, d_pcur.as<uint32_t>());
+    part_scatter_kernel<<<tiles, PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, d_pcur.as<uint32_t>(), oc, ose);
+    return 3;
 }
 
 // Join index over the root intervals (see join_build.h / join.cuh).
@@ -445,7 +440,6 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
         ev_chunk.push_back(e);
     }
     if (n_retained) {  // the bucketed form of every batch is kept (a too-small pair buffer re-runs the join)
-        d_bchr.ensure(n_retained * 4 + 16);
         d_bse.ensure(n_retained * 8 + 32);
     }
     d_poff.ensure((size_t)std::max<uint32_t>(n_chunks, 1) * (WG.n_win + 2) * 4);
@@ -498,10 +492,9 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
         if (jb.n_total + n > jb.retained) throw Err(E_STATE, "more regions than announced at the job's begin");
         if ((size_t)(slot + 1) * (WG.n_win + 2) * 4 > d_poff.cap) throw Err(E_STATE, "more batches than announced at the job's begin");
     } else {
-        d_bchr.ensure(n * 4 + 16);
         d_bse.ensure(n * 8 + 32);
     }
-    uint32_t* oc = d_bchr.as<uint32_t>() + ck.off;
+    uint32_t* oc = nullptr;   // the join and the rank-space scatter take the sequence from the window
     uint2* ose = d_bse.as<uint2>() + ck.off;
     uint32_t* poff = d_poff.as<uint32_t>() + (jb.retained ? (size_t)slot * (WG.n_win + 2) : 0);
     jb.n_total += n;

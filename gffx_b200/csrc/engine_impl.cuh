@@ -123,7 +123,7 @@ class EngineImpl {
     DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_match, d_type_allow;
 
     // ---- window grid + partition scratch (partition.cuh) --------------------------------------
-    DBuf d_win0, d_poff, d_pmat, d_pscan, d_pscratch, d_bchr, d_bse;
+    DBuf d_win0, d_poff, d_ptot, d_pcur, d_bchr, d_bse;
     std::vector<uint32_t> h_win0;
     WinGrid WG{};
 

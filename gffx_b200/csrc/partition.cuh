@@ -16,12 +16,16 @@
 // shared memory first and stored run by run with consecutive lanes on consecutive addresses, and the window
 // count is kept small enough (<= 511) for the runs to be whole 32-byte sectors; the kernels that need finer
 // locality than a window sort their own tile again in shared memory (tilesort.cuh).
-//   part_count_kernel    tile of 4096 regions: shared-memory histogram over the windows -> column `tile`
-//                        of a window-major count matrix
-//   device_scan          exclusive scan of the matrix = first output position of every (window, tile)
-//   part_scatter_kernel  ranks from a second shared histogram pass, tile sorted in shared memory, runs
-//                        stored coalesced: (start,end) pairs and the sequence numbers
-// The order inside a (tile, window) run is the arrival order of the atomics, i.e. arbitrary.
+//   part_count_kernel    tile of 4096 regions: shared-memory histogram over the windows, added to the global window totals
+//   part_offsets_kernel  one CTA: exclusive scan of the <= 512 totals = first bucketed position of every window (`poff`)
+//                        and the windows' write cursors
+//   part_scatter_kernel  the tile again: ranks from the shared histogram, one atomicAdd per (tile, window) on the
+//                        window's cursor claims the run's place, tile sorted in shared memory, runs stored coalesced
+//                        as (start,end) pairs (+ the sequence numbers where a consumer wants them)
+// The order of the runs inside a window is the arrival order of the tiles, the order inside a run that of the shared
+// atomics: arbitrary, and nothing downstream depends on it (the join counts, the filters take max/min/or).
+// (Until r01l the runs were placed by a window x tile count matrix and its device-wide scan: three more launches, 10 MB of
+// strided matrix traffic per 10 M regions.)
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
@@ -33,7 +37,6 @@ constexpr int PART_TILE = 4096;             // regions per CTA
 constexpr int PART_UNROLL = 4;              // independent loads in flight per thread
 constexpr uint32_t PART_MAX_WINDOWS = 511;  // + 1 bucket for regions whose sequence number is out of range
 constexpr uint32_t PART_NB_MAX = PART_MAX_WINDOWS + 1;
-constexpr size_t PART_SCATTER_SMEM = (size_t)PART_TILE * 14 + (size_t)PART_NB_MAX * 12;
 
 struct WinGrid {
     const uint32_t* win0;  // n_seqs + 1: windows of sequence s are [win0[s], win0[s+1])
@@ -47,100 +50,162 @@ __device__ __forceinline__ uint32_t window_of(const WinGrid& G, uint32_t c, uint
     return w0 + (b < nw ? b : nw - 1);
 }
 
-static __global__ void __launch_bounds__(PART_THREADS)
-    part_count_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, uint32_t n, uint32_t n_tiles,
-                      uint32_t* __restrict__ counts) {
-    __shared__ uint32_t sh[PART_NB_MAX];
-    const uint32_t nb = G.n_win + 1;
-    const uint32_t base = blockIdx.x * (uint32_t)PART_TILE;
-    const uint32_t end = min(n, base + (uint32_t)PART_TILE);
-    for (uint32_t i = threadIdx.x; i < nb; i += PART_THREADS) sh[i] = 0;
-    __syncthreads();
-    for (uint32_t i0 = base + threadIdx.x; i0 < end; i0 += PART_THREADS * PART_UNROLL) {
-        uint32_t c[PART_UNROLL], s[PART_UNROLL];
+// thread t of a tile holds elements 4 * (k * THREADS + t) .. + 3, k < PART_TILE / (4 * THREADS): 16-byte loads when the arrays allow
+constexpr int PART_VEC = PART_TILE / (4 * PART_THREADS);
+__device__ __forceinline__ void part_load4(const uint32_t* __restrict__ a, uint32_t i, uint32_t end, bool al16, uint32_t (&v)[4]) {
+    if (al16 && i + 4 <= end) {
+        const uint4 x = __ldcs(reinterpret_cast<const uint4*>(a + i));
+        v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+    } else {
 #pragma unroll
-        for (int k = 0; k < PART_UNROLL; k++) {
-            const uint32_t i = i0 + k * PART_THREADS;
-            if (i < end) { c[k] = __ldg(chr + i); s[k] = __ldg(qs + i); }
-        }
-#pragma unroll
-        for (int k = 0; k < PART_UNROLL; k++)
-            if (i0 + k * PART_THREADS < end) atomicAdd(&sh[window_of(G, c[k], s[k])], 1u);
+        for (int j = 0; j < 4; j++) v[j] = i + j < end ? __ldcs(a + i + j) : 0u;
     }
-    __syncthreads();
-    for (uint32_t i = threadIdx.x; i < nb; i += PART_THREADS) counts[(uint64_t)i * n_tiles + blockIdx.x] = sh[i];
 }
 
+// the windows of a sequence from a shared-memory copy of win0 (n_seqs + 1 <= PART_NB_MAX cells: every sequence has a window)
+__device__ __forceinline__ uint32_t window_of_s(const uint32_t* s_win0, uint32_t n_seqs, uint32_t n_win, uint32_t shift, uint32_t c, uint32_t s) {
+    if (c >= n_seqs) return n_win;
+    const uint32_t w0 = s_win0[c], nw = s_win0[c + 1] - w0;
+    const uint32_t b = s >> shift;
+    return w0 + (b < nw ? b : nw - 1);
+}
+
+constexpr int PART_COUNT_TILES = 4;   // tiles per CTA of the count pass: fewer global atomics on the window totals
+
 static __global__ void __launch_bounds__(PART_THREADS)
+    part_count_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, uint32_t n, uint32_t* __restrict__ tot) {
+    __shared__ uint32_t sh[PART_NB_MAX];
+    __shared__ uint32_t s_win0[PART_NB_MAX + 1];
+    const uint32_t nb = G.n_win + 1;
+    const bool al16 = ((reinterpret_cast<uintptr_t>(chr) | reinterpret_cast<uintptr_t>(qs)) & 15u) == 0;
+    for (uint32_t i = threadIdx.x; i < nb; i += PART_THREADS) sh[i] = 0;
+    for (uint32_t i = threadIdx.x; i <= G.n_seqs; i += PART_THREADS) s_win0[i] = __ldg(G.win0 + i);
+    __syncthreads();
+    for (int t = 0; t < PART_COUNT_TILES; t++) {
+        const uint64_t base64 = ((uint64_t)blockIdx.x * PART_COUNT_TILES + t) * PART_TILE;
+        if (base64 >= n) break;
+        const uint32_t base = (uint32_t)base64;
+        const uint32_t end = min(n, base + (uint32_t)PART_TILE);
+        uint32_t c[PART_VEC][4], s[PART_VEC][4];
+#pragma unroll
+        for (int k = 0; k < PART_VEC; k++) {
+            const uint32_t i = base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
+            part_load4(chr, i, end, al16, c[k]);
+            part_load4(qs, i, end, al16, s[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < PART_VEC; k++)
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x) + j < end)
+                    atomicAdd(&sh[window_of_s(s_win0, G.n_seqs, G.n_win, G.shift, c[k][j], s[k][j])], 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < nb; i += PART_THREADS)
+        if (sh[i]) atomicAdd(tot + i, sh[i]);
+}
+
+// one CTA of PART_NB_MAX threads: poff[w] = cursor[w] = first bucketed position of window w, poff[nb] = n; the totals are
+// zeroed for the next partition pass on the stream
+static __global__ void __launch_bounds__(PART_NB_MAX) part_offsets_kernel(uint32_t* __restrict__ tot, uint32_t nb, uint32_t n,
+                                                                         uint32_t* __restrict__ poff, uint32_t* __restrict__ cursor) {
+    __shared__ uint32_t warp_tot[PART_NB_MAX / 32];
+    const uint32_t w = threadIdx.x, lane = w & 31u;
+    const uint32_t v = w < nb ? tot[w] : 0u;
+    uint32_t x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= (uint32_t)d) x += o;
+    }
+    if (lane == 31) warp_tot[w >> 5] = x;
+    __syncthreads();
+    uint32_t pre = 0;
+    for (uint32_t k = 0; k < (w >> 5); k++) pre += warp_tot[k];
+    const uint32_t ex = pre + x - v;
+    if (w < nb) { poff[w] = ex; cursor[w] = ex; tot[w] = 0; }
+    if (w == 0) poff[nb] = n;
+}
+
+constexpr size_t PART_SCATTER_SMEM = (size_t)PART_TILE * 14 + (size_t)PART_NB_MAX * 8;
+
+// oc == nullptr: the consumer does not need the sequence numbers (a window lies in one sequence)
+static __global__ void __launch_bounds__(PART_THREADS, 2)
     part_scatter_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
-                        uint32_t n, uint32_t n_tiles, const uint32_t* __restrict__ counts, const uint32_t* __restrict__ scanned,
-                        uint32_t* __restrict__ oc, uint2* __restrict__ ose) {
-    extern __shared__ uint32_t part_dyn[];  // PART_SCATTER_SMEM bytes
-    uint32_t* s_c = part_dyn;
-    uint32_t* s_s = s_c + PART_TILE;
-    uint32_t* s_e = s_s + PART_TILE;
-    uint16_t* s_w = reinterpret_cast<uint16_t*>(s_e + PART_TILE);
-    uint32_t* s_loff = s_e + PART_TILE + PART_TILE / 2;
-    uint32_t* s_goff = s_loff + PART_NB_MAX;
-    uint32_t* s_cur = s_goff + PART_NB_MAX;
+                        uint32_t n, uint32_t* __restrict__ cursor, uint32_t* __restrict__ oc, uint2* __restrict__ ose) {
+    extern __shared__ __align__(16) uint32_t part_dyn[];  // PART_SCATTER_SMEM bytes
+    uint2* s_se = reinterpret_cast<uint2*>(part_dyn);                  // the tile sorted by window
+    uint32_t* s_c = part_dyn + 2 * PART_TILE;
+    uint16_t* s_w = reinterpret_cast<uint16_t*>(s_c + PART_TILE);
+    uint32_t* s_hist = s_c + PART_TILE + PART_TILE / 2;                // regions per window -> first sorted position
+    uint32_t* s_delta = s_hist + PART_NB_MAX;                          // global position minus sorted position of the window's run
     __shared__ uint32_t s_warp[PART_THREADS / 32];
+    __shared__ uint32_t s_win0[PART_NB_MAX + 1];
     const uint32_t nb = G.n_win + 1;
     const uint32_t base = blockIdx.x * (uint32_t)PART_TILE;
     const uint32_t end = min(n, base + (uint32_t)PART_TILE);
-    // local offsets of the windows inside the sorted tile: exclusive scan of this tile's column (2 windows per thread)
-    {
-        const uint32_t w0 = 2 * threadIdx.x, w1 = w0 + 1;
-        const uint32_t c0 = w0 < nb ? __ldg(counts + (uint64_t)w0 * n_tiles + blockIdx.x) : 0u;
-        const uint32_t c1 = w1 < nb ? __ldg(counts + (uint64_t)w1 * n_tiles + blockIdx.x) : 0u;
-        if (w0 < nb) s_goff[w0] = __ldg(scanned + (uint64_t)w0 * n_tiles + blockIdx.x);
-        if (w1 < nb) s_goff[w1] = __ldg(scanned + (uint64_t)w1 * n_tiles + blockIdx.x);
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        uint32_t x = c0 + c1;
+    const bool al16 = ((reinterpret_cast<uintptr_t>(chr) | reinterpret_cast<uintptr_t>(qs) | reinterpret_cast<uintptr_t>(qe)) & 15u) == 0;
+    static_assert(PART_NB_MAX == PART_THREADS, "one window per thread");
+    s_hist[threadIdx.x] = 0;
+    for (uint32_t i = threadIdx.x; i <= G.n_seqs; i += PART_THREADS) s_win0[i] = __ldg(G.win0 + i);
+    uint32_t c[PART_VEC][4], s[PART_VEC][4], e[PART_VEC][4];
+#pragma unroll
+    for (int k = 0; k < PART_VEC; k++) {
+        const uint32_t i = base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
+        part_load4(chr, i, end, al16, c[k]);
+        part_load4(qs, i, end, al16, s[k]);
+        part_load4(qe, i, end, al16, e[k]);
+    }
+    __syncthreads();
+    uint32_t wr[PART_VEC][4];   // window << 12 | rank inside the tile's run of that window
+#pragma unroll
+    for (int k = 0; k < PART_VEC; k++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            wr[k][j] = 0xFFFFFFFFu;
+            if (base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x) + j < end) {
+                const uint32_t w = window_of_s(s_win0, G.n_seqs, G.n_win, G.shift, c[k][j], s[k][j]);
+                wr[k][j] = (w << 12) | atomicAdd(&s_hist[w], 1u);
+            }
+        }
+    static_assert(PART_TILE <= 4096, "12 bits of rank");
+    __syncthreads();
+    {   // exclusive scan of the histogram; every window with regions claims its run on the window's cursor
+        const uint32_t w = threadIdx.x, lane = w & 31u;
+        const uint32_t v = s_hist[w];
+        uint32_t x = v;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const uint32_t o = __shfl_up_sync(0xffffffffu, x, d);
-            if (lane >= d) x += o;
+            if (lane >= (uint32_t)d) x += o;
         }
-        if (lane == 31) s_warp[warp] = x;
+        if (lane == 31) s_warp[w >> 5] = x;
+        const uint32_t g = (v && w < nb) ? atomicAdd(cursor + w, v) : 0u;
         __syncthreads();
         uint32_t pre = 0;
-        for (int k = 0; k < warp; k++) pre += s_warp[k];
-        const uint32_t ex = pre + x - (c0 + c1);
-        if (w0 < nb) { s_loff[w0] = ex; s_cur[w0] = ex; }
-        if (w1 < nb) { s_loff[w1] = ex + c0; s_cur[w1] = ex + c0; }
+        for (uint32_t k = 0; k < (w >> 5); k++) pre += s_warp[k];
+        const uint32_t ex = pre + x - v;
+        s_hist[w] = ex;
+        s_delta[w] = g - ex;
     }
     __syncthreads();
-    for (uint32_t i0 = base + threadIdx.x; i0 < end; i0 += PART_THREADS * PART_UNROLL) {
-        uint32_t c[PART_UNROLL], s[PART_UNROLL], e[PART_UNROLL];
 #pragma unroll
-        for (int k = 0; k < PART_UNROLL; k++) {
-            const uint32_t i = i0 + k * PART_THREADS;
-            if (i < end) { c[k] = __ldcs(chr + i); s[k] = __ldcs(qs + i); e[k] = __ldcs(qe + i); }
-        }
+    for (int k = 0; k < PART_VEC; k++)
 #pragma unroll
-        for (int k = 0; k < PART_UNROLL; k++)
-            if (i0 + k * PART_THREADS < end) {
-                const uint32_t w = window_of(G, c[k], s[k]);
-                const uint32_t lp = atomicAdd(&s_cur[w], 1u);
-                s_c[lp] = c[k]; s_s[lp] = s[k]; s_e[lp] = e[k]; s_w[lp] = (uint16_t)w;
+        for (int j = 0; j < 4; j++)
+            if (wr[k][j] != 0xFFFFFFFFu) {
+                const uint32_t w = wr[k][j] >> 12, lp = s_hist[w] + (wr[k][j] & 0xFFFu);
+                s_se[lp] = make_uint2(s[k][j], e[k][j]);
+                s_w[lp] = (uint16_t)w;
+                if (oc) s_c[lp] = c[k][j];
             }
-    }
     __syncthreads();
     const uint32_t cnt = end - base;
     for (uint32_t i = threadIdx.x; i < cnt; i += PART_THREADS) {
-        const uint32_t w = s_w[i];
-        const uint32_t g = s_goff[w] + (i - s_loff[w]);
-        ose[g] = make_uint2(s_s[i], s_e[i]);
-        oc[g] = s_c[i];
+        const uint32_t g = i + s_delta[s_w[i]];
+        ose[g] = s_se[i];
+        if (oc) oc[g] = s_c[i];
     }
-}
-
-// first bucketed position of every window: off[w] = scanned[w][0], off[nb] = n
-static __global__ void part_offsets_kernel(const uint32_t* __restrict__ scanned, uint32_t nb, uint32_t n_tiles, uint32_t n,
-                                           uint32_t* __restrict__ off) {
-    const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
-    if (w < nb) off[w] = scanned[(uint64_t)w * n_tiles];
-    else if (w == nb) off[w] = n;
 }
 
 }  // namespace gffx

@@ -82,7 +82,7 @@ constexpr size_t WJ_DYN_SMEM = (size_t)WJ_TILE * sizeof(uint2);   // the (tile, 
 #define WJ_MIN_CTAS 3     // 40 registers: the join alone fits without spills
 #endif
 #ifndef WJ_MIN_CTAS_FILT
-#define WJ_MIN_CTAS_FILT 2
+#define WJ_MIN_CTAS_FILT 3   // 96 bytes of spills, still faster than 2 CTAs (measured)
 #endif
 // FILT: the same pass also scatters every region onto the line filter's rank space (K3a, filter.cuh: scatter_region) —
 // the regions are in shared memory already, and a round's 32 regions start inside one bin, so their rank look-ups
