@@ -171,7 +171,7 @@ void EngineImpl::build_join() {
     const std::vector<uint32_t>& jwin0 = h_win0;
     const uint32_t jshift = WG.shift;
     WinBinsHost bh;
-    uint32_t max_sub = 6;  // GFFX_WJ_SUB=0..9; 2^6 bins per window: a 4096-region tile sorted by bin has ~64 regions per bin (measured best of 5/6/7)
+    uint32_t max_sub = 7;  // GFFX_WJ_SUB=0..9; 2^7 bins per window (~65 kb at human scale): 6, 7 and 8 measure the same on the bench
     if (const char* e = getenv("GFFX_WJ_SUB")) max_sub = (uint32_t)std::min(9, std::max(0, atoi(e)));
     build_win_bins((uint32_t)n_seqs, items, jwin0, jshift, max_sub, 1ull << 27, &bh);
     std::vector<uint4> ent4(bh.n_entries()), list4(std::max<size_t>(bh.list.size(), 1));

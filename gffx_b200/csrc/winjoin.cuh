@@ -43,11 +43,13 @@ template <int MODE, bool INVERT> __device__ __forceinline__ bool wj_keep(uint32_
 //      (start,end,fid,id) records — into shared memory; whatever exceeds the slice capacity is read from global
 //      memory, so the result is the same for any input;
 //   2. counting-sorts its regions by bin in shared memory (one shared atomic per region, one scan of <= 512 counters);
-//   3. hands the bins to its warps: the <= 32 regions of a round all lie in ONE bin, so the candidate loops are
-//      uniform across the warp — one broadcast 16-byte shared load per candidate, the per-lane test, one ballot, and
-//      lane 0 adds the popcount to the candidate's counter.  No lane divergence, no per-hit stores (r01k / s17
-//      profiles of the per-region-thread versions: 480-490 instructions per region in divergent candidate loops and
-//      per-pair bookkeeping; this form: a few instructions per region plus the sort);
+//   3. hands rounds of 32 consecutive sorted regions to its warps: the regions of a round start in the same bin or the
+//      next few, so ONE candidate set serves the round (the list of the round's first bin, then the run while start <
+//      the round's largest region end) and the candidate loops are uniform across the warp — one broadcast 16-byte
+//      shared load per candidate, the exact per-lane test, one ballot, and lane t keeps the popcount of candidate t in a
+//      register until the round ends.  No lane divergence, no per-hit stores (r01k / s17 profiles of the
+//      per-region-thread versions: 480-490 instructions per region in divergent candidate loops and per-pair
+//      bookkeeping);
 //   4. adds the non-zero slot counters to the global per-root counters (one 64-bit atomic per hit root and CTA).
 constexpr int WJ_BINS_MAX = 512;    // bins per window (sub <= 9)
 constexpr int WJ_LIST_CAP = 768;    // list members of the window held in shared memory (12 KB)
@@ -73,7 +75,7 @@ struct WjSmem {   // static shared memory (26 KB); the sorted tile (WJ_DYN_SMEM 
     uint32_t scan[WJ_WARPS + 1];
     uint32_t tot;
     uint32_t w_first, w_last;
-    uint32_t next_bin;                             // bins are handed to the warps in arrival order
+    uint32_t next_round;                           // rounds are handed to the warps in arrival order
     uint32_t sent;                                 // slice-local index of the sequence's sentinel if the run holds it, else 0xFFFFFFFF
 };
 constexpr size_t WJ_DYN_SMEM = (size_t)WJ_TILE * sizeof(uint2);   // the (tile, window) regions ordered by bin
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
             S.run[i] = v; S.rcnt[i] = 0;
             if (v.x == 0xFFFFFFFFu) atomicMin(&S.sent, i);   // what follows the sentinel belongs to the next sequence
         }
-        if (tid == 0) { S.tot = 0; S.next_bin = 0; }
+        if (tid == 0) { S.tot = 0; S.next_round = 0; }
         __syncthreads();
         // ---- 2. counting sort of the window's regions by bin ----------------------------------------
         uint32_t rank[WJ_QPT];
@@ -213,51 +215,50 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
                 }
             }
         };
-#ifndef WJ_STATIC_BINS
+        // A round = 32 consecutive positions of the sorted tile.  Its regions start in bins b_first <= b: an interval that hits one
+        // of them either overlaps bin b_first (it starts before that bin's end and ends after the region's start, which is
+        // not before the bin's start) or starts later, at or after the bin's end — so the candidates of the whole round are
+        // the list of b_first and the run from first[b_first + 1] while start < the round's largest region end.  The test
+        // per candidate and lane is the exact one, so a candidate too many costs a compare, never a wrong count.
+        const uint32_t m_seg = p_hi - p_lo, n_rounds = (m_seg + 31u) >> 5;
         for (;;) {
-            uint32_t b = 0;
-            if (lane == 0) b = atomicAdd(&S.next_bin, 1u);   // per-bin work varies (regions x candidates): no warp waits at the barrier for long
-            b = __shfl_sync(0xffffffffu, b, 0);
-            if (b >= nb) break;
-#else
-        for (uint32_t b = warp; b < nb; b += WJ_WARPS) {
-#endif
-            const uint32_t p0 = S.hist[b], p1 = S.hist[b + 1];
-            if (p0 == p1) continue;
+            uint32_t rd = 0;
+            if (lane == 0) rd = atomicAdd(&S.next_round, 1u);   // rounds go to the warps in arrival order: no warp waits long at the barrier
+            rd = __shfl_sync(0xffffffffu, rd, 0);
+            if (rd >= n_rounds) break;
+            const bool have = rd * 32u + lane < m_seg;
+            // a lane without a region holds (rs, re) = (max, 0): no interval has start < 0
+            const uint2 r = have ? wj_sorted[rd * 32u + lane] : make_uint2(0xFFFFFFFFu, 0u);
+            if (FILT && filt && have) scatter_region<MODE>(R, RS, F, seq, r.x, r.y);
+            const uint32_t b = __shfl_sync(0xffffffffu, min((r.x - lo) >> bsh, nb - 1), 0);   // lane 0 always has a region, the smallest bin
             const uint2 b0 = S.bf[b], b1 = S.bf[b + 1];
             const uint32_t nL = b1.x - b0.x;
-            const bool lean_list = list_full && nL <= 32u;
             // lean form: lane t keeps the hits of the bin's list member t and run member t in registers
             uint32_t lacc = 0, racc = 0;
-            // within 32 run members of the bin's first one the start reaches the round's largest region end
+            if (list_full && nL <= 32u) {
+                for (uint32_t t = 0; t < nL; t++) {
+                    const uint4 v = S.list[b0.x + t];
+                    const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                    const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                    if (lane == t) lacc += nh;
+                }
+            } else {
+                walk_list(r, b0.x, b1.x);
+            }
+            const uint32_t re_max = __reduce_max_sync(0xffffffffu, r.y);
+            // within 32 run members of the first one the start reaches the round's largest region end, all in shared memory
             const uint32_t jl = min(b1.y + 31u, run_end - 1u);
             const uint32_t run_reach = (run_end && b1.y < run_end) ? S.run[jl].x : 0u;
-            for (uint32_t pp = p0; pp < p1; pp += 32) {
-                // a lane without a region holds (rs, re) = (max, 0): no interval has start < 0
-                const uint2 r = pp + lane < p1 ? wj_sorted[pp + lane] : make_uint2(0xFFFFFFFFu, 0u);
-                if (FILT && filt && pp + lane < p1) scatter_region<MODE>(R, RS, F, seq, r.x, r.y);
-                if (lean_list) {
-                    for (uint32_t t = 0; t < nL; t++) {
-                        const uint4 v = S.list[b0.x + t];
-                        const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
-                        const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
-                        if (lane == t) lacc += nh;
-                    }
-                } else {
-                    walk_list(r, b0.x, b1.x);
+            if (run_reach >= re_max) {
+                for (uint32_t t = 0;; t++) {
+                    const uint4 v = S.run[b1.y + t];
+                    if (v.x >= re_max) break;
+                    const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+                    const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+                    if (lane == t) racc += nh;
                 }
-                const uint32_t re_max = __reduce_max_sync(0xffffffffu, r.y);
-                if (run_reach >= re_max && re_max != 0u) {
-                    for (uint32_t t = 0;; t++) {
-                        const uint4 v = S.run[b1.y + t];
-                        if (v.x >= re_max) break;
-                        const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
-                        const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
-                        if (lane == t) racc += nh;
-                    }
-                } else {
-                    walk_run(r, b1.y, re_max);
-                }
+            } else {
+                walk_run(r, b1.y, re_max);
             }
             if (lacc) atomicAdd(&S.lcnt[b0.x + lane], lacc);
             if (racc) atomicAdd(&S.rcnt[b1.y + lane], racc);

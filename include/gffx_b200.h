@@ -118,7 +118,10 @@ void gffx_free(void* p);
 /* ------------------------------------------------------------------------------------------
  * Root-level join: replaces query_features (src/commands/intersect.rs:105-169) and the
  * IntervalTree::query_interval calls under it (src/utils/tree.rs:98-121).
- * Pairs come back in query order (the reference's order is hash-map order: unspecified).
+ * A pair names the root only — (iv.root_fid, iv.start, iv.end), intersect.rs:162 — so the result is the multiset
+ * "root r, once per region that hits r".  Pairs come back grouped by root, roots in (sequence, start, end) order; the
+ * reference's order (chromosomes in hash-map order, regions in BED order) is not reproduced, nothing downstream of
+ * query_features depends on it (intersect.rs:598-617 only dedups the roots).
  * ------------------------------------------------------------------------------------------ */
 int gffx_query_features(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n,
                         int mode, int invert, uint32_t flags, gffx_result** out);
@@ -150,9 +153,9 @@ const uint32_t* gffx_result_warn_fids(const gffx_result* r);
 /* device time of the call's kernels in ms (CUDA events on the engine's stream) and launch count */
 double gffx_result_kernel_ms(const gffx_result* r);
 uint32_t gffx_result_launches(const gffx_result* r);
-/* per-stage device ms: 0 join count kernel, 1 tile-offset scan, 2 join emit kernel, 3 root/block select + merge,
- * 4 region scatter onto the line rank space, 5 rank scans, 6 line filter + compaction, 7 the join emit kernel alone
- * (stage 2 also holds the host read-back of the pair count), 8 the window partition pass (hist + scan + scatter);
+/* per-stage device ms: 0 root join (hits per root) with the region scatter onto the line rank space fused in,
+ * 3 root/block select + merge, 4 (unused since the scatter rides on stage 0), 5 rank scans, 6 line filter + compaction,
+ * 7 pair offsets scan + pair expansion, 8 the window partition pass (totals + offsets + scatter);
  * stages that did not run report 0 */
 double gffx_result_stage_ms(const gffx_result* r, int stage);
 void gffx_result_free(gffx_result* r);
