@@ -340,6 +340,22 @@ def run_gpu(args, rank, world, local_rank):
         except (OSError, ValueError):
             pass
 
+    # ---- record emission (K8, not part of the timed step): the text of the overlap pass's ranges gathered on the device ----
+    emit = None
+    if world == 1 and not getattr(args, "no_emit", False):
+        name, mode, inv = PASSES[0]
+        r = idx.intersect(dev_sets[0], mode, inv, False, None, flags=F_DEV, copy=False)
+        nr = r.n_ranges
+        best, nbytes = None, 0
+        for _ in range(4):
+            _, nbytes = idx.gather_text(None, nr, device=True)
+            best = idx.gather_ms if best is None else min(best, idx.gather_ms)
+        r.close()
+        if best and nbytes:
+            gbs = 2.0 * nbytes / (best * 1e-3) / 1e9
+            emit = {"kernel": "gather_text_kernel", "pass": name, "ranges": int(nr), "bytes_out": int(nbytes), "ms": best, "scan_ms": idx.gather_scan_ms,
+                    "algorithmic_bytes": 2 * int(nbytes), "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak}
+
     h2d = len(PASSES) * 12 * Q
     d2h = int(16 * ranges_e2e / world / e2e_steps) + 64 * len(PASSES)
     e2e_val = world * len(PASSES) * Q * e2e_steps / e2e_s
@@ -355,6 +371,8 @@ def run_gpu(args, rank, world, local_rank):
                 "ms_per_step": e2e_s / e2e_steps * 1e3, "api": "gffx_intersect (C ABI) with pinned host region arrays; byte ranges copied back"},
         "gpu_launches": int(launches_total),
     }
+    if emit:
+        line["emit"] = emit
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args, idx, gff)
     print(json.dumps(line), flush=True)

@@ -117,6 +117,9 @@ SIGNATURES = {
     "gffx_result_stage_ms": (C.c_double, vp, C.c_int),
     "gffx_result_free": (None, vp),
     "gffx_write_ranges": (C.c_int, vp, vp, C.c_uint64, C.c_char_p),
+    "gffx_gather_text": (C.c_int, vp, vp, C.c_uint64, C.c_uint32, C.POINTER(vp), C.POINTER(C.c_uint64)),
+    "gffx_gather_kernel_ms": (C.c_double, vp, C.c_int),
+    "gffx_write_text": (C.c_int, vp, C.c_uint64, C.c_char_p),
     "gffx_counts_begin": (C.c_int, vp, C.c_int, C.POINTER(vp)),
     "gffx_counts_add": (C.c_int, vp, vp, vp, vp, C.c_uint64, C.c_uint32),
     "gffx_counts_finish": (C.c_int, vp, u64p, C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u64p)),

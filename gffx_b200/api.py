@@ -309,6 +309,22 @@ class TreeIndexData:
         r = np.ascontiguousarray(ranges, dtype=np.uint64)
         _check(lib.gffx_write_ranges(self._h, r.ctypes.data, r.shape[0], str(out_path).encode() if out_path else None))
 
+    def gather_text(self, ranges: Optional[np.ndarray] = None, n_ranges: Optional[int] = None, device: bool = False):
+        """Record emission on the device (K8, gather.cuh): the bytes write_ranges would write, gathered from the HBM-resident
+        GFF into one buffer.  ranges=None: the ranges of the last intersect on this handle (pass its n_ranges).
+        Returns bytes (device=False) or (device_pointer, n_bytes); `gather_ms` / `gather_scan_ms` hold the device times."""
+        text, nb = C.c_void_p(), C.c_uint64()
+        if ranges is None:
+            _check(lib.gffx_gather_text(self._h, None, int(n_ranges or 0), _lib.F_NO_HOST_COPY if device else 0, C.byref(text), C.byref(nb)))
+        else:
+            r = np.ascontiguousarray(ranges, dtype=np.uint64)
+            _check(lib.gffx_gather_text(self._h, r.ctypes.data, r.shape[0], _lib.F_NO_HOST_COPY if device else 0, C.byref(text), C.byref(nb)))
+        self.gather_ms = lib.gffx_gather_kernel_ms(self._h, 0)
+        self.gather_scan_ms = lib.gffx_gather_kernel_ms(self._h, 1)
+        if device:
+            return text.value, nb.value
+        return C.string_at(text.value, nb.value) if nb.value else b""
+
     def _counts(self, kind: int, regions, batches: int = 1, combine=None):
         st = C.c_void_p()
         _check(lib.gffx_counts_begin(self._h, kind, C.byref(st)))

@@ -257,6 +257,23 @@ int gffx_write_ranges(const gffx_index* idx, const uint64_t* ranges, uint64_t n_
     });
 }
 
+int gffx_gather_text(gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, uint32_t flags, const uint8_t** text, uint64_t* n_bytes) {
+    return guard([&] {
+        need(idx, "idx"); need(text, "text"); need(n_bytes, "n_bytes");
+        idx->engine()->gather_text(ranges, n_ranges, flags, text, n_bytes);
+    });
+}
+double gffx_gather_kernel_ms(const gffx_index* idx, int part) {
+    if (!idx) return 0;
+    return part == 0 ? const_cast<gffx_index*>(idx)->engine()->gather_kernel_ms() : const_cast<gffx_index*>(idx)->engine()->gather_scan_ms();
+}
+int gffx_write_text(const uint8_t* text, uint64_t n_bytes, const char* out_path) {
+    return guard([&] {
+        if (n_bytes) need(text, "text");
+        write_text_to(text, n_bytes, out_path);
+    });
+}
+
 int gffx_counts_begin(gffx_index* idx, int kind, gffx_counts** out) {
     return guard([&] {
         need(idx, "idx"); need(out, "out");
@@ -366,7 +383,14 @@ int gffx_intersect_run(const gffx_intersect_args* a) {
         for (uint32_t fid : res.warn_fids) fprintf(stderr, "[WARN] skipped fid=%u due to sentinel start offset\n", fid);
         const HostIndex& H = idx->host();
         if (!H.gff) throw Err(E_IO, std::string("Cannot open GFF: \"") + a->input + "\"");
-        write_ranges_to(H.gff, H.gff_len, res.ranges.data(), res.n_ranges, a->output);
+        if (getenv("GFFX_HOST_EMIT")) {   // the reference's way: one slice per range from the mapped file
+            write_ranges_to(H.gff, H.gff_len, res.ranges.data(), res.n_ranges, a->output);
+        } else {                          // K8: gathered on the device, one write
+            const uint8_t* text = nullptr;
+            uint64_t nb = 0;
+            idx->engine()->gather_text(nullptr, res.n_ranges, 0, &text, &nb);
+            write_text_to(text, nb, a->output);
+        }
         if (a->verbose)
             fprintf(stderr, "[INFO] gpu intersect: %llu regions, %llu pairs, %llu roots, %llu ranges, %.3f ms on device\n",
                     (unsigned long long)res.n_queries, (unsigned long long)res.n_pairs, (unsigned long long)res.n_roots,

@@ -43,7 +43,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
@@ -62,7 +62,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
@@ -72,6 +72,7 @@ EngineImpl::~EngineImpl() {
     for (auto& x : ev) cudaEventDestroy(x);
     for (auto& x : ev_chunk) cudaEventDestroy(x);
     for (auto& x : ev_copy) cudaEventDestroy(x);
+    for (auto& x : ev_gather) if (x) cudaEventDestroy(x);
     if (st_copy) cudaStreamDestroy(st_copy);
     if (st) cudaStreamDestroy(st);
 }
@@ -668,6 +669,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         if (jb.match_only) { out->n_ranges = hs[5]; out->bytes_out = hs[4]; }
         else { out->n_ranges = hs[1]; out->bytes_out = hs[3]; }
     }
+    last_n_ranges = out->n_ranges;
     if (out->n_ranges && !jb.no_host) {
         out->ranges.resize(out->n_ranges * 2);
         GFFX_CUDA(cudaMemcpyAsync(out->ranges.data(), d_ranges.p, out->n_ranges * 16, cudaMemcpyDeviceToHost, st));
@@ -862,6 +864,73 @@ void Engine::fold(void* dst, const void* src, uint32_t rows, uint64_t stride, ui
     }
     GFFX_CUDA(cudaGetLastError());
 }
+
+// ------------------------------------------------------------------------------------------------
+// K8: record emission on the device (gather.cuh)
+void EngineImpl::gather_text(const uint64_t* ranges, uint64_t n_ranges, uint32_t flags, const uint8_t** text, uint64_t* n_bytes) {
+    typedef unsigned long long ull;
+    GFFX_CUDA(cudaSetDevice(dev));
+    *text = nullptr; *n_bytes = 0;
+    gather_ms = 0; gather_launches = 0;
+    if (!H->gff) throw Err(E_STATE, "index was opened without the GFF text");
+    if (!text_resident) {   // once per index: the GFF text goes to HBM (+ 8 bytes of padding for the copy's look-ahead word)
+        d_text.ensure(H->gff_len + 16);
+        GFFX_CUDA(cudaMemsetAsync((uint8_t*)d_text.p + H->gff_len, 0, 16, st));
+        if (H->gff_len) GFFX_CUDA(cudaMemcpyAsync(d_text.p, H->gff, H->gff_len, cudaMemcpyHostToDevice, st));
+        text_resident = true;
+    }
+    const ulonglong2* dr;
+    if (ranges) {
+        d_text_ranges.ensure(std::max<uint64_t>(n_ranges, 1) * 16);
+        if (n_ranges) GFFX_CUDA(cudaMemcpyAsync(d_text_ranges.p, ranges, n_ranges * 16, cudaMemcpyHostToDevice, st));
+        dr = d_text_ranges.as<ulonglong2>();
+    } else {
+        if (n_ranges != last_n_ranges) throw Err(E_STATE, "the ranges of that result are no longer on the device: pass them explicitly");
+        dr = d_ranges.as<ulonglong2>();
+    }
+    if (n_ranges == 0) return;
+    if (!ev_gather[0])
+        for (auto& e : ev_gather) GFFX_CUDA(cudaEventCreate(&e));
+    GFFX_CUDA(cudaEventRecord(ev_gather[0], st));
+    d_text_off.ensure((n_ranges + 1) * 8);
+    d_scan_scratch.ensure(scan_scratch_elems(n_ranges + 1) * 8);
+    gather_launches += device_scan<ull, OpSum, RangeLenLoad, PtrStore<ull>, false, false>(
+        RangeLenLoad{dr, n_ranges, H->gff_len}, PtrStore<ull>{d_text_off.as<ull>()}, n_ranges + 1, OpSum(), 0ull, d_scan_scratch.as<ull>(),
+        (ull*)((uint8_t*)d_small.p + 128), st);
+    GFFX_CUDA(cudaEventRecord(ev_gather[1], st));
+    GFFX_CUDA(cudaMemcpyAsync((uint8_t*)h_small + 128, (uint8_t*)d_small.p + 128, 8, cudaMemcpyDeviceToHost, st));
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    const uint64_t total = *(const uint64_t*)((const uint8_t*)h_small + 128);
+    *n_bytes = total;
+    if (total == 0) return;
+    d_text_out.ensure(total + 16);
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    GFFX_CUDA(cudaEventRecord(ev_gather[2], st));
+    gather_text_kernel<<<(unsigned)sms * 8, GATHER_THREADS, 0, st>>>(d_text.as<uint8_t>(), dr, d_text_off.as<ull>(), n_ranges, d_text_out.as<uint8_t>());
+    gather_launches++;
+    GFFX_CUDA(cudaEventRecord(ev_gather[3], st));
+    if (flags & 4u) {
+        *text = d_text_out.as<uint8_t>();
+    } else {
+        h_text_out.resize(total);
+        GFFX_CUDA(cudaMemcpyAsync(h_text_out.data(), d_text_out.p, total, cudaMemcpyDeviceToHost, st));
+        *text = h_text_out.data();
+    }
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    GFFX_CUDA(cudaGetLastError());
+    float ms0, ms1;   // the offsets scan and the gather kernel, without the host round trip for the output size between them
+    GFFX_CUDA(cudaEventElapsedTime(&ms0, ev_gather[0], ev_gather[1]));
+    GFFX_CUDA(cudaEventElapsedTime(&ms1, ev_gather[2], ev_gather[3]));
+    gather_scan_ms = ms0;
+    gather_ms = ms1;
+}
+void Engine::gather_text(const uint64_t* ranges, uint64_t n_ranges, uint32_t flags, const uint8_t** text, uint64_t* n_bytes) {
+    impl_->gather_text(ranges, n_ranges, flags, text, n_bytes);
+}
+double Engine::gather_kernel_ms() const { return impl_->gather_ms; }
+double Engine::gather_scan_ms() const { return impl_->gather_scan_ms; }
+uint32_t Engine::gather_launches() const { return impl_->gather_launches; }
 
 void Engine::counts_begin(int kind) { counts_begin_impl(impl_.get(), kind); }
 void Engine::counts_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags) {

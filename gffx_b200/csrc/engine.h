@@ -105,6 +105,14 @@ class Engine {
     double counts_kernel_ms() const;
     uint32_t counts_launches() const;
 
+    // record emission on the device (gather.cuh): the text of the byte ranges — `ranges` (host, n_ranges x (start,end)) or,
+    // when NULL, the ranges of the last finished intersect still on the device — gathered from the HBM-resident GFF.
+    // flags & 4 (NO_HOST_COPY): *text is a device pointer; else a page-locked host copy.  Both live until the next call.
+    void gather_text(const uint64_t* ranges, uint64_t n_ranges, uint32_t flags, const uint8_t** text, uint64_t* n_bytes);
+    double gather_kernel_ms() const;   // gather_text_kernel alone (CUDA events)
+    double gather_scan_ms() const;     // the offsets scan before it
+    uint32_t gather_launches() const;
+
     void synth_regions_device(uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* d_chr, uint32_t* d_start,
                               uint32_t* d_end);
 

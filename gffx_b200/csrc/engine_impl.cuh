@@ -6,6 +6,7 @@
 #include "join.cuh"
 #include "join_build.h"
 #include "partition.cuh"
+#include "gather.cuh"
 #include "winjoin.cuh"
 #include "winjoin_build.h"
 
@@ -152,7 +153,16 @@ class EngineImpl {
     void ix_finish(IntersectResult* out);
     void ix_seal();
     uint32_t ix_scans(FilterScans* P);
-    uint32_t expand_pairs(unsigned long long cap);  // K1b: offsets scan + wj_expand_kernel into d_pairs
+    uint32_t expand_pairs(unsigned long long cap);
+    // K8 (gather.cuh): the text of `n_ranges` byte ranges gathered on the device; ranges == nullptr: those of the last intersect
+    void gather_text(const uint64_t* ranges, uint64_t n_ranges, uint32_t flags, const uint8_t** text, uint64_t* n_bytes);
+    DBuf d_text, d_text_off, d_text_out, d_text_ranges;
+    bool text_resident = false;
+    uint64_t last_n_ranges = 0;      // ranges of the last finished intersect still in d_ranges
+    HostBlob<uint8_t> h_text_out;    // page-locked copy of the last gathered text
+    double gather_ms = 0, gather_scan_ms = 0;   // gather_text_kernel alone; its offsets scan
+    cudaEvent_t ev_gather[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t gather_launches = 0;  // K1b: offsets scan + wj_expand_kernel into d_pairs
     // stage the regions on the device; returns device pointers (either the caller's or the staging buffers)
     void stage_queries(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                        const uint32_t** dc, const uint32_t** ds, const uint32_t** de);

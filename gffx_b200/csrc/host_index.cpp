@@ -558,4 +558,19 @@ void write_ranges_to(const uint8_t* text, uint64_t text_len, const uint64_t* ran
     if (out_path) ::close(fd);
 }
 
+void write_text_to(const uint8_t* text, uint64_t n, const char* out_path) {
+    int fd = out_path ? ::open(out_path, O_WRONLY | O_CREAT | O_TRUNC, 0644) : 1;
+    if (fd < 0) throw Err(E_IO, std::string("cannot create output file ") + out_path);
+    uint64_t done = 0;
+    while (done < n) {
+        const ssize_t w = ::write(fd, text + done, (size_t)std::min<uint64_t>(n - done, 1ull << 30));
+        if (w < 0) {
+            if (out_path) ::close(fd);
+            throw Err(E_IO, "write failed");
+        }
+        done += (uint64_t)w;
+    }
+    if (out_path) ::close(fd);
+}
+
 }  // namespace gffx

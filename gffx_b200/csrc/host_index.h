@@ -106,5 +106,6 @@ void parse_region_arg(const std::string& region, const std::unordered_map<std::s
 
 // Writes the byte ranges of `text` in order with writev batches (intersect.rs:385-429, common.rs:231-278)
 void write_ranges_to(const uint8_t* text, uint64_t text_len, const uint64_t* ranges, uint64_t n, const char* out_path);
+void write_text_to(const uint8_t* text, uint64_t n, const char* out_path);
 
 }  // namespace gffx

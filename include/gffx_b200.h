@@ -164,6 +164,19 @@ void gffx_result_free(gffx_result* r);
  * common.rs:231-278). out_path NULL = stdout. */
 int gffx_write_ranges(const gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, const char* out_path);
 
+/* Record emission on the device: the same bytes the write_vectored loops above produce — the
+ * concatenation of text[start,end) over the ranges, skipping start >= end and end > file length — gathered from the
+ * HBM-resident GFF text (uploaded on first use) into ONE buffer, so the host issues a single write.
+ * ranges: n_ranges x (start,end) u64 on the host, or NULL = the ranges of this handle's last finished intersect, still
+ * on the device (n_ranges must then be that result's gffx_result_n_ranges).
+ * flags & GFFX_F_NO_HOST_COPY: *text is a device pointer, else a page-locked host copy; both stay valid until the
+ * handle's next gather.  gffx_gather_kernel_ms: device time of the gather kernel alone / of its offsets scan. */
+int gffx_gather_text(gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, uint32_t flags, const uint8_t** text,
+                     uint64_t* n_bytes);
+double gffx_gather_kernel_ms(const gffx_index* idx, int part /* 0 gather kernel, 1 offsets scan */);
+/* one write(2) loop over a gathered buffer; out_path NULL = stdout */
+int gffx_write_text(const uint8_t* text, uint64_t n_bytes, const char* out_path);
+
 /* ------------------------------------------------------------------------------------------
  * depth / coverage: replace compute_hit_depth + compute_root_depth (src/commands/depth.rs:121-293)
  * and collect_by_root_* + finalize_compute_breadth (src/commands/coverage.rs:208-450).
