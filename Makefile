@@ -10,7 +10,7 @@ OBJ := build/obj
 LIB := gffx_b200/lib/libgffx_b200.so
 BIN := gffx_b200/bin/gffx-b200
 
-CU_SRCS := $(SRC)/engine.cu $(SRC)/counts.cu
+CU_SRCS := $(SRC)/engine.cu $(SRC)/counts.cu $(SRC)/bedparse.cu
 CPP_SRCS := $(SRC)/util.cpp $(SRC)/join_build.cpp $(SRC)/winjoin_build.cpp $(SRC)/counts_index.cpp $(SRC)/host_index.cpp $(SRC)/index_builder.cpp $(SRC)/synth.cpp $(SRC)/capi.cpp
 CU_OBJS := $(patsubst $(SRC)/%.cu,$(OBJ)/%.cu.o,$(CU_SRCS))
 CPP_OBJS := $(patsubst $(SRC)/%.cpp,$(OBJ)/%.o,$(CPP_SRCS))

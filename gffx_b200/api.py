@@ -238,6 +238,29 @@ class TreeIndexData:
         """BED dialect of depth/coverage: src/commands/depth.rs:449-495, src/commands/coverage.rs:222-255"""
         return self._parse(lib.gffx_parse_bed_counts, bed_path)
 
+    def parse_bed_device(self, bed_path, dialect: int = 0, device: int = 0):
+        """The same dialects parsed on the device (K9, bedparse.cuh): dialect 0 = parse_bed_file, 1 = depth / coverage.  Returns three
+        torch int32 CUDA tensors (views of engine-owned memory, valid until the next parse on this handle) — pass them as regions."""
+        import torch
+
+        ps = [C.c_void_p() for _ in range(3)]
+        n = C.c_uint64()
+        _check(lib.gffx_parse_bed_device(self._h, str(bed_path).encode(), int(dialect), C.byref(ps[0]), C.byref(ps[1]), C.byref(ps[2]), C.byref(n)))
+        self.bed_parse_ms = lib.gffx_bed_parse_stat(self._h, 0)
+        self.bed_host_lines = int(lib.gffx_bed_parse_stat(self._h, 2))
+        self.bed_bytes = int(lib.gffx_bed_parse_stat(self._h, 3))
+        dev = torch.device("cuda", int(device))   # the device this handle was opened on
+        if n.value == 0:
+            return tuple(torch.empty(0, dtype=torch.int32, device=dev) for _ in range(3))
+        out = []
+        for p in ps:
+            class _Mem:   # __cuda_array_interface__ view of engine-owned device memory
+                pass
+            m = _Mem()
+            m.__cuda_array_interface__ = {"shape": (n.value,), "typestr": "<i4", "data": (p.value, False), "version": 2}
+            out.append(torch.as_tensor(m, device=dev))
+        return tuple(out)
+
     def parse_region(self, region: str):
         """src/commands/intersect.rs:172-198"""
         c, s, e = C.c_uint32(), C.c_uint32(), C.c_uint32()

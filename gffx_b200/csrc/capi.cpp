@@ -151,6 +151,14 @@ int gffx_parse_bed_intersect(const gffx_index* idx, const char* bed_path, uint32
         *n = R.size();
     });
 }
+int gffx_parse_bed_device(gffx_index* idx, const char* bed_path, int dialect, const uint32_t** d_chr, const uint32_t** d_start,
+                          const uint32_t** d_end, uint64_t* n) {
+    return guard([&] {
+        need(idx, "idx"); need(bed_path, "bed_path"); need(d_chr, "d_chr"); need(d_start, "d_start"); need(d_end, "d_end"); need(n, "n");
+        idx->engine()->parse_bed_device(bed_path, dialect, d_chr, d_start, d_end, n);
+    });
+}
+double gffx_bed_parse_stat(const gffx_index* idx, int what) { return idx ? const_cast<gffx_index*>(idx)->engine()->bed_parse_stat(what) : 0; }
 int gffx_parse_bed_counts(const gffx_index* idx, const char* bed_path, uint32_t** chr, uint32_t** start, uint32_t** end, uint64_t* n) {
     return guard([&] {
         need(idx, "idx"); need(bed_path, "bed_path"); need(chr, "chr"); need(start, "start"); need(end, "end"); need(n, "n");
@@ -370,16 +378,24 @@ int gffx_intersect_run(const gffx_intersect_args* a) {
         if (int rc = gffx_index_open(a->input, a->device, &idx)) throw Err(rc, g_err);
         std::unique_ptr<gffx_index> hold(idx);
         Regions R;
-        if (a->bed) parse_bed_intersect(a->bed, idx->host().seq_num, &R);
-        else {
-            uint32_t c, s, e;
-            parse_region_arg(a->region, idx->host().seq_num, &c, &s, &e);
-            R.chr.push_back(c); R.start.push_back(s); R.end.push_back(e);
+        const uint32_t *qc = nullptr, *qs = nullptr, *qe = nullptr;
+        uint64_t nq = 0;
+        uint32_t qflags = 0;
+        if (a->bed && !getenv("GFFX_HOST_BED")) {   // K9: the BED text is parsed on the device, the regions stay there
+            idx->engine()->parse_bed_device(a->bed, 0, &qc, &qs, &qe, &nq);
+            qflags = GFFX_F_DEVICE_INPUT;
+        } else {
+            if (a->bed) parse_bed_intersect(a->bed, idx->host().seq_num, &R);
+            else {
+                uint32_t c, s, e;
+                parse_region_arg(a->region, idx->host().seq_num, &c, &s, &e);
+                R.chr.push_back(c); R.start.push_back(s); R.end.push_back(e);
+            }
+            qc = R.chr.data(); qs = R.start.data(); qe = R.end.data(); nq = R.size();
         }
-        if (a->verbose) fprintf(stderr, "[DEBUG] Starting query_features with %zu regions\n", R.size());
+        if (a->verbose) fprintf(stderr, "[DEBUG] Starting query_features with %llu regions\n", (unsigned long long)nq);
         IntersectResult res;
-        idx->engine()->intersect(R.chr.data(), R.start.data(), R.end.data(), R.size(), a->mode, a->invert != 0, a->entire_group != 0, a->types, 0,
-                            false, &res);
+        idx->engine()->intersect(qc, qs, qe, nq, a->mode, a->invert != 0, a->entire_group != 0, a->types, qflags, false, &res);
         for (uint32_t fid : res.warn_fids) fprintf(stderr, "[WARN] skipped fid=%u due to sentinel start offset\n", fid);
         const HostIndex& H = idx->host();
         if (!H.gff) throw Err(E_IO, std::string("Cannot open GFF: \"") + a->input + "\"");
@@ -413,14 +429,23 @@ static int counts_run(const gffx_counts_args* a, int kind) {
         std::unique_ptr<gffx_index> hold(idx);
         if (!idx->host().gff) throw Err(E_IO, std::string("Cannot open GFF file: \"") + a->input + "\"");
         Regions R;
-        parse_bed_counts(src, idx->host().seq_num, a->threads > 0 ? a->threads : host_threads(), &R);
+        const uint32_t *qc = nullptr, *qs = nullptr, *qe = nullptr;
+        uint64_t nq = 0;
+        uint32_t qflags = 0;
+        if (!getenv("GFFX_HOST_BED")) {   // K9: parsed on the device, the regions stay there
+            idx->engine()->parse_bed_device(src, 1, &qc, &qs, &qe, &nq);
+            qflags = GFFX_F_DEVICE_INPUT;
+        } else {
+            parse_bed_counts(src, idx->host().seq_num, a->threads > 0 ? a->threads : host_threads(), &R);
+            qc = R.chr.data(); qs = R.start.data(); qe = R.end.data(); nq = R.size();
+        }
         gffx_counts* st = nullptr;
         if (int rc = gffx_counts_begin(idx, kind, &st)) throw Err(rc, g_err);
         std::unique_ptr<gffx_counts> hold2(st);
-        if (int rc = gffx_counts_add(st, R.chr.data(), R.start.data(), R.end.data(), R.size(), 0)) throw Err(rc, g_err);
+        if (int rc = gffx_counts_add(st, qc, qs, qe, nq, qflags)) throw Err(rc, g_err);
         if (int rc = gffx_counts_write(st, a->output)) throw Err(rc, g_err);
         if (a->verbose)
-            fprintf(stderr, "[INFO] gpu %s: %zu regions, %.3f ms on device\n", kind ? "coverage" : "depth", R.size(), gffx_counts_kernel_ms(st));
+            fprintf(stderr, "[INFO] gpu %s: %llu regions, %.3f ms on device\n", kind ? "coverage" : "depth", (unsigned long long)nq, gffx_counts_kernel_ms(st));
     });
 }
 int gffx_depth_run(const gffx_counts_args* a) { return counts_run(a, 0); }

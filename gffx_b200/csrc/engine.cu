@@ -43,7 +43,9 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
+                    &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
@@ -62,7 +64,9 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges,
+                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
+                    &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
@@ -73,6 +77,7 @@ EngineImpl::~EngineImpl() {
     for (auto& x : ev_chunk) cudaEventDestroy(x);
     for (auto& x : ev_copy) cudaEventDestroy(x);
     for (auto& x : ev_gather) if (x) cudaEventDestroy(x);
+    for (auto& x : ev_bed) if (x) cudaEventDestroy(x);
     if (st_copy) cudaStreamDestroy(st_copy);
     if (st) cudaStreamDestroy(st);
 }
@@ -931,6 +936,22 @@ void Engine::gather_text(const uint64_t* ranges, uint64_t n_ranges, uint32_t fla
 double Engine::gather_kernel_ms() const { return impl_->gather_ms; }
 double Engine::gather_scan_ms() const { return impl_->gather_scan_ms; }
 uint32_t Engine::gather_launches() const { return impl_->gather_launches; }
+
+void bed_parse_device_impl(EngineImpl* E, const std::string& path, int dialect, const uint32_t** dc, const uint32_t** ds, const uint32_t** de,
+                           uint64_t* n_out);   // bedparse.cu
+void Engine::parse_bed_device(const std::string& path, int dialect, const uint32_t** d_chr, const uint32_t** d_start, const uint32_t** d_end,
+                              uint64_t* n) {
+    bed_parse_device_impl(impl_.get(), path, dialect, d_chr, d_start, d_end, n);
+}
+double Engine::bed_parse_stat(int what) const {
+    switch (what) {
+        case 0: return impl_->bed_ms;
+        case 1: return (double)impl_->bed_launches;
+        case 2: return (double)impl_->bed_host_lines;
+        case 3: return (double)impl_->bed_bytes;
+        default: return 0;
+    }
+}
 
 void Engine::counts_begin(int kind) { counts_begin_impl(impl_.get(), kind); }
 void Engine::counts_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags) {

@@ -113,6 +113,13 @@ class Engine {
     double gather_scan_ms() const;     // the offsets scan before it
     uint32_t gather_launches() const;
 
+    // BED text parsed on the device (bedparse.cuh): dialect 0 = intersect (parse_bed_file), 1 = depth / coverage.  The arrays are
+    // device pointers owned by the engine until its next parse; pass them on with GFFX_F_DEVICE_INPUT.
+    void parse_bed_device(const std::string& path, int dialect, const uint32_t** d_chr, const uint32_t** d_start, const uint32_t** d_end,
+                          uint64_t* n);
+    // 0 kernel ms, 1 launches, 2 lines decided by the host's per-line functions, 3 bytes of text
+    double bed_parse_stat(int what) const;
+
     void synth_regions_device(uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* d_chr, uint32_t* d_start,
                               uint32_t* d_end);
 

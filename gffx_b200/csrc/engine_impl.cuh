@@ -6,6 +6,7 @@
 #include "join.cuh"
 #include "join_build.h"
 #include "partition.cuh"
+#include "bedparse.cuh"
 #include "gather.cuh"
 #include "winjoin.cuh"
 #include "winjoin_build.h"
@@ -160,6 +161,16 @@ class EngineImpl {
     bool text_resident = false;
     uint64_t last_n_ranges = 0;      // ranges of the last finished intersect still in d_ranges
     HostBlob<uint8_t> h_text_out;    // page-locked copy of the last gathered text
+    // K9 (bedparse.cuh / bedparse.cu): BED text -> device-resident regions
+    DBuf d_bed_text, d_bed_tiles, d_bed_tfirst, d_bed_lstart, d_bed_status, d_bed_line[3], d_bed_flag, d_bed_pos, d_bed_out[3];
+    DBuf d_bed_nhash, d_bed_nid, d_bed_noff, d_bed_nlen, d_bed_nblob;
+    BedNames bed_names{};
+    bool bed_names_built = false;
+    cudaEvent_t ev_bed[4] = {nullptr, nullptr, nullptr, nullptr};
+    double bed_ms = 0;            // device time of the parse kernels
+    uint32_t bed_launches = 0;
+    uint64_t bed_host_lines = 0;  // lines the kernel left to the host's exact per-line functions
+    uint64_t bed_bytes = 0;
     double gather_ms = 0, gather_scan_ms = 0;   // gather_text_kernel alone; its offsets scan
     cudaEvent_t ev_gather[4] = {nullptr, nullptr, nullptr, nullptr};
     uint32_t gather_launches = 0;  // K1b: offsets scan + wj_expand_kernel into d_pairs

@@ -376,58 +376,61 @@ void HostIndex::build_lines(int threads) {
 // ------------------------------------------------------------------------------------------
 // BED parsing
 // ------------------------------------------------------------------------------------------
+// one line [line, q) of the intersect dialect (q = its '\n' or the end of the file): false = skipped, throws where the
+// reference aborts (intersect.rs:215, :223-224)
+bool bed_intersect_line(const uint8_t* line, const uint8_t* q, const std::unordered_map<std::string, uint32_t>& seq_num, const std::string& path,
+                        std::string& scratch, uint32_t* chr, uint32_t* s, uint32_t* e) {
+    if (q == line || line[0] == '#') return false;
+    if (!utf8_ok(line, (size_t)(q - line))) throw Err(E_FORMAT, "invalid utf-8 sequence in BED file " + path);
+    const uint8_t* f[3];
+    size_t fl[3];
+    int nf = 0;
+    const uint8_t* c = line;
+    while (nf < 3) {  // split_ascii_whitespace
+        while (c < q && ascii_ws(*c)) c++;
+        if (c >= q) break;
+        const uint8_t* st = c;
+        while (c < q && !ascii_ws(*c)) c++;
+        f[nf] = st;
+        fl[nf] = (size_t)(c - st);
+        nf++;
+    }
+    if (nf < 3) return false;
+    if (scratch.size() != fl[0] || memcmp(scratch.data(), f[0], fl[0]) != 0 || *chr == NONE32 - 1) {
+        scratch.assign((const char*)f[0], fl[0]);
+        auto it = seq_num.find(scratch);
+        *chr = it == seq_num.end() ? NONE32 : it->second;
+    }
+    if (*chr == NONE32) return false;  // unknown chromosome: skipped BEFORE the numbers are looked at
+    if (!parse_u32_strict(f[1], fl[1], s))
+        throw Err(E_FORMAT, "BED " + path + ": cannot parse start '" + std::string((const char*)f[1], fl[1]) + "' as u32");
+    if (!parse_u32_strict(f[2], fl[2], e))
+        throw Err(E_FORMAT, "BED " + path + ": cannot parse end '" + std::string((const char*)f[2], fl[2]) + "' as u32");
+    return true;
+}
+
 void parse_bed_intersect(const std::string& path, const std::unordered_map<std::string, uint32_t>& seq_num, Regions* out) {
     Mapped m;
     m.open(path);
     const uint8_t* p = m.data();
     const uint8_t* end = p + m.size();
-    std::string name, last_name;
-    uint32_t last_chr = NONE32;
-    bool have_last = false;
+    std::string last_name;            // the previous line's chromosome name and number: BED files come in runs
+    uint32_t chr = NONE32 - 1;        // "nothing looked up yet"
     while (p < end) {
         const uint8_t* nl = find_byte(p, end, '\n');
         const uint8_t* q = nl ? nl : end;
         const uint8_t* line = p;
         p = q + 1;
-        if (q == line || line[0] == '#') continue;
-        if (!utf8_ok(line, (size_t)(q - line))) throw Err(E_FORMAT, "invalid utf-8 sequence in BED file " + path);
-        const uint8_t* f[3];
-        size_t fl[3];
-        int nf = 0;
-        const uint8_t* c = line;
-        while (nf < 3) {  // split_ascii_whitespace
-            while (c < q && ascii_ws(*c)) c++;
-            if (c >= q) break;
-            const uint8_t* s = c;
-            while (c < q && !ascii_ws(*c)) c++;
-            f[nf] = s;
-            fl[nf] = (size_t)(c - s);
-            nf++;
-        }
-        if (nf < 3) continue;
-        uint32_t chr;
-        if (have_last && last_name.size() == fl[0] && memcmp(last_name.data(), f[0], fl[0]) == 0) {
-            chr = last_chr;
-        } else {
-            last_name.assign((const char*)f[0], fl[0]);
-            auto it = seq_num.find(last_name);
-            last_chr = it == seq_num.end() ? NONE32 : it->second;
-            have_last = true;
-            chr = last_chr;
-        }
-        if (chr == NONE32) continue;  // unknown chromosome: skipped BEFORE the numbers are looked at
         uint32_t s, e;
-        if (!parse_u32_strict(f[1], fl[1], &s))
-            throw Err(E_FORMAT, "BED " + path + ": cannot parse start '" + std::string((const char*)f[1], fl[1]) + "' as u32");
-        if (!parse_u32_strict(f[2], fl[2], &e))
-            throw Err(E_FORMAT, "BED " + path + ": cannot parse end '" + std::string((const char*)f[2], fl[2]) + "' as u32");
-        out->chr.push_back(chr);
-        out->start.push_back(s);
-        out->end.push_back(e);
+        if (bed_intersect_line(line, q, seq_num, path, last_name, &chr, &s, &e)) {
+            out->chr.push_back(chr);
+            out->start.push_back(s);
+            out->end.push_back(e);
+        }
     }
 }
 
-static bool bed_counts_line(const uint8_t* line, const uint8_t* q, const std::unordered_map<std::string, uint32_t>& seq_num,
+bool bed_counts_line(const uint8_t* line, const uint8_t* q, const std::unordered_map<std::string, uint32_t>& seq_num,
                             std::string& scratch, uint32_t* chr, uint32_t* s, uint32_t* e) {
     if (q == line || line[0] == '#') return false;
     const uint8_t* f[3];

@@ -106,6 +106,13 @@ void parse_region_arg(const std::string& region, const std::unordered_map<std::s
 
 // Writes the byte ranges of `text` in order with writev batches (intersect.rs:385-429, common.rs:231-278)
 void write_ranges_to(const uint8_t* text, uint64_t text_len, const uint64_t* ranges, uint64_t n, const char* out_path);
+// the exact per-line deciders of the two BED dialects; the device parser (bedparse.cuh) hands them the
+// lines it does not decide itself.  `chr` / `scratch` of the intersect form cache the previous line's name look-up
+// (start with *chr = NONE32 - 1).
+bool bed_intersect_line(const uint8_t* line, const uint8_t* q, const std::unordered_map<std::string, uint32_t>& seq_num, const std::string& path,
+                        std::string& scratch, uint32_t* chr, uint32_t* s, uint32_t* e);
+bool bed_counts_line(const uint8_t* line, const uint8_t* q, const std::unordered_map<std::string, uint32_t>& seq_num, std::string& scratch,
+                     uint32_t* chr, uint32_t* s, uint32_t* e);
 void write_text_to(const uint8_t* text, uint64_t n, const char* out_path);
 
 }  // namespace gffx

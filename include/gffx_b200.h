@@ -111,6 +111,14 @@ int gffx_parse_bed_intersect(const gffx_index* idx, const char* bed_path, uint32
                              uint64_t* n);
 int gffx_parse_bed_counts(const gffx_index* idx, const char* bed_path, uint32_t** chr, uint32_t** start, uint32_t** end,
                           uint64_t* n);
+/* The same two dialects parsed on the device (bedparse.cuh): the file's text goes to HBM, one thread per
+ * line decides the plain lines, the host's exact per-line functions the rest (non-ASCII, signs, overlong numbers...), so
+ * the result — and dialect 0's abort on a bad number — is that of the host parsers above.  dialect: 0 intersect, 1 counts.
+ * The arrays are DEVICE pointers owned by the handle until its next parse: pass them to gffx_intersect / gffx_counts_add
+ * with GFFX_F_DEVICE_INPUT.  gffx_bed_parse_stat: 0 kernel ms, 1 launches, 2 lines left to the host, 3 bytes of text. */
+int gffx_parse_bed_device(gffx_index* idx, const char* bed_path, int dialect, const uint32_t** d_chr, const uint32_t** d_start,
+                          const uint32_t** d_end, uint64_t* n);
+double gffx_bed_parse_stat(const gffx_index* idx, int what);
 /* parse_region, src/commands/intersect.rs:172-198 */
 int gffx_parse_region(const gffx_index* idx, const char* region, uint32_t* chr, uint32_t* start, uint32_t* end);
 void gffx_free(void* p);
