@@ -356,6 +356,32 @@ def run_gpu(args, rank, world, local_rank):
             emit = {"kernel": "gather_text_kernel", "pass": name, "ranges": int(nr), "bytes_out": int(nbytes), "ms": best, "scan_ms": idx.gather_scan_ms,
                     "algorithmic_bytes": 2 * int(nbytes), "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak}
 
+    # ---- BED text parsing on the device (K9, not part of the timed step): a 3-column BED of the first pass's regions ----
+    bed_parse = None
+    if world == 1 and not getattr(args, "no_emit", False):
+        import pandas as pd
+        n_bed = min(Q, 10_000_000)
+        names = np.array(idx.num_to_seqid, dtype=object)
+        h = host_sets[0]
+        bed_path = os.path.join(workload_dir(args.genes), f"bench_{n_bed}.bed")
+        if not os.path.exists(bed_path):
+            pd.DataFrame({"c": names[h[0][:n_bed].numpy()], "s": h[1][:n_bed].numpy(), "e": h[2][:n_bed].numpy()}).to_csv(
+                bed_path, sep="\t", header=False, index=False)
+        best = None
+        for _ in range(3):
+            t = idx.parse_bed_device(bed_path, 0, device=local_rank)
+            best = idx.bed_parse_ms if best is None else min(best, idx.bed_parse_ms)
+        n_parsed = int(t[0].numel())
+        t0 = time.perf_counter()
+        hp = idx.parse_bed_file(bed_path)
+        host_ms = (time.perf_counter() - t0) * 1e3
+        nbytes = idx.bed_bytes + 12 * n_parsed
+        bed_parse = {"kernels": "bed_count_nl + bed_line_starts + bed_parse_lines + scan + bed_compact", "lines": n_parsed, "text_bytes": idx.bed_bytes,
+                     "host_decided_lines": idx.bed_host_lines, "ms": best, "lines_per_sec": n_parsed / (best * 1e-3),
+                     "algorithmic_bytes": nbytes, "achieved": nbytes / (best * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": nbytes / (best * 1e-3) / 1e9 / peak, "host_parser_ms_1_thread": host_ms, "same_as_host": bool(
+                         len(hp[0]) == n_parsed and np.array_equal(hp[1], t[1].cpu().numpy().view(np.uint32)))}
+
     h2d = len(PASSES) * 12 * Q
     d2h = int(16 * ranges_e2e / world / e2e_steps) + 64 * len(PASSES)
     e2e_val = world * len(PASSES) * Q * e2e_steps / e2e_s
@@ -373,6 +399,8 @@ def run_gpu(args, rank, world, local_rank):
     }
     if emit:
         line["emit"] = emit
+    if bed_parse:
+        line["bed_parse"] = bed_parse
     if world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args, idx, gff)
     print(json.dumps(line), flush=True)
