@@ -384,7 +384,7 @@ static void launch_wj(EngineImpl* E, const uint32_t* poff, const uint2* se, uint
         attr_set = true;
     }
     typedef unsigned long long ull;
-    FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>()};
+    FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48};
     wj_count_kernel<MODE, INV, FILT><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(), E->d_wj_cnt.as<ull>(),
                                                                                 n_pairs, err, E->FR, F);
 }
@@ -530,9 +530,9 @@ uint32_t EngineImpl::ix_scans(FilterScans* Pout) {
     const uint64_t ns = f_slots;
     uint32_t launches = 0;
     d_scan_scratch.ensure(scan_scratch_elems(LA.n / LINE_THREADS + 1) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
-    FilterArrays F{d_A.as<ull>(), d_B.as<ull>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>()};
+    FilterArrays F{d_A.as<ull>(), d_B.as<ull>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>(), d_small.as<uint32_t>() + 48};
     ull* scr = d_scan_scratch.as<ull>();
-    *Pout = FilterScans{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>()};
+    *Pout = FilterScans{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>(), F.any_inv};
     if (mode == 0 || mode == 2)
         launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
                                                                                      OpMax(), 0ull, scr, nullptr, st);
@@ -546,7 +546,7 @@ uint32_t EngineImpl::ix_scans(FilterScans* Pout) {
         launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
             MarkLoad{F.Ms}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
         launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
-            MarkLoad{F.Me}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
+            MarkLoad{F.Me}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, F.any_inv);
     }
     return launches;
 }

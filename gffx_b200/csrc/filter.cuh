@@ -73,6 +73,7 @@ struct FilterArrays {
     unsigned long long* B;  // n_slots
     uint8_t* Ms;            // 2*n_slots
     uint8_t* Me;            // 2*n_slots
+    uint32_t* any_inv;      // set when some region has qs > qe: only then Me holds marks and NE is scanned / consulted
 };
 
 // one region (qs, qe) of sequence `seq` onto the rank space: 1-3 scattered L2 updates
@@ -92,6 +93,7 @@ __device__ __forceinline__ void scatter_region(const RankSpace& R, const RankSeq
             bool eq2;
             const uint32_t lb2 = rank_lb(R, S, qe, &eq2);
             F.Me[2ull * (S.slot0 + lb2) + (eq2 ? 1u : 0u)] = 1;
+            *F.any_inv = 1u;
         }
     }
 }
@@ -115,6 +117,7 @@ struct FilterScans {
     const unsigned long long* SMN;  // inclusive suffix min of B
     const uint32_t* NS;             // next marked cell >= c in Ms
     const uint32_t* NE;             // same for Me
+    const uint32_t* ne_on;          // FilterArrays::any_inv: 0 = no mark in Me, NE was not scanned
 };
 
 template <int MODE>
@@ -135,7 +138,7 @@ __device__ __forceinline__ bool line_matches(const LineArrays& L, const FilterSc
         if (S <= E) {
             const uint32_t c0 = 2u * iS + 1u, c1 = 2u * iE + 1u;
             if (P.NS[c0] <= c1) return true;  // S<=qs<=E
-            if (P.NE[c0] <= c1) return true;  // S<=qe<=E
+            if (*P.ne_on && P.NE[c0] <= c1) return true;  // S<=qe<=E
         }
         return false;
     }

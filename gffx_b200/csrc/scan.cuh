@@ -81,8 +81,10 @@ template <class T, class Op> __device__ __forceinline__ T block_scan_excl(T v, O
 // Load(i) -> T gives element i; REVERSE scans from the high end (suffix scan).  Element j of the
 // scan order is array index (REVERSE ? n-1-j : j).
 template <class T, class Op, class Load, bool REVERSE>
-__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(Load load, uint64_t n, Op op, T identity, T* __restrict__ agg) {
+__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(Load load, uint64_t n, Op op, T identity, T* __restrict__ agg,
+                                                                   const uint32_t* __restrict__ gate) {
     __shared__ T sm[SCAN_THREADS / 32 + 1];
+    if (gate && *gate == 0) return;   // the whole scan is switched off by a device-side flag (uniform)
     const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
     T acc = identity;
 #pragma unroll
@@ -98,8 +100,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(Load load, ui
 
 // single CTA: in-place exclusive scan of `agg[0..m)`; writes the grand total to agg[m]
 template <class T, class Op>
-__global__ void __launch_bounds__(1024) scan_agg_kernel(T* __restrict__ agg, uint32_t m, Op op, T identity) {
+__global__ void __launch_bounds__(1024) scan_agg_kernel(T* __restrict__ agg, uint32_t m, Op op, T identity, const uint32_t* __restrict__ gate) {
     __shared__ T sm[1024 / 32 + 1];
+    if (gate && *gate == 0) return;
     T carry = identity;
     for (uint32_t base = 0; base < m; base += 1024) {
         uint32_t i = base + threadIdx.x;
@@ -115,8 +118,9 @@ __global__ void __launch_bounds__(1024) scan_agg_kernel(T* __restrict__ agg, uin
 
 template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE>
 __global__ void __launch_bounds__(SCAN_THREADS)
-    scan_apply_kernel(Load load, Store store, uint64_t n, Op op, T identity, const T* __restrict__ agg) {
+    scan_apply_kernel(Load load, Store store, uint64_t n, Op op, T identity, const T* __restrict__ agg, const uint32_t* __restrict__ gate) {
     __shared__ T sm[SCAN_THREADS / 32 + 1];
+    if (gate && *gate == 0) return;
     // thread t owns SCAN_ITEMS consecutive elements of the scan order -> blocked arrangement
     const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
     T v[SCAN_ITEMS];
@@ -164,25 +168,26 @@ template <class T> struct PtrStore {
 };
 
 // Scans n elements; `scratch` holds scan_scratch_elems(n) Ts.  If total_out != nullptr the grand
-// total (device pointer) is written there.  Returns the number of kernels launched.
+// total (device pointer) is written there.  gate != nullptr: a device-side word; when it is 0 the kernels return at once
+// and nothing is written (the consumer checks the same word).  Returns the number of kernels launched.
 template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE>
-int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratch, T* total_out, cudaStream_t st) {
+int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratch, T* total_out, cudaStream_t st, const uint32_t* gate = nullptr) {
     int launches = 0;
     uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (tiles == 0) tiles = 1;
     T* agg = scratch;
-    scan_reduce_kernel<T, Op, Load, REVERSE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, n, op, identity, agg);
+    scan_reduce_kernel<T, Op, Load, REVERSE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, n, op, identity, agg, gate);
     launches++;
     if (tiles <= 1024 * 64) {
-        scan_agg_kernel<T, Op><<<1, 1024, 0, st>>>(agg, (uint32_t)tiles, op, identity);
+        scan_agg_kernel<T, Op><<<1, 1024, 0, st>>>(agg, (uint32_t)tiles, op, identity, gate);
         launches++;
     } else {
         // scan the aggregates with the same machinery (exclusive, forward), in place
         T* next = agg + tiles + 1;
         launches += device_scan<T, Op, PtrLoad<T>, PtrStore<T>, false, false>(PtrLoad<T>{agg}, PtrStore<T>{agg}, tiles, op, identity,
-                                                                             next, agg + tiles, st);
+                                                                             next, agg + tiles, st, gate);
     }
-    scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg);
+    scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate);
     launches++;
     if (total_out) {
         cudaMemcpyAsync(total_out, agg + tiles, sizeof(T), cudaMemcpyDeviceToDevice, st);

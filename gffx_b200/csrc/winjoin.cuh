@@ -73,7 +73,7 @@ struct WjSmem {   // static shared memory (26 KB); the sorted tile (WJ_DYN_SMEM 
     uint32_t hist[WJ_BINS_MAX + 1];                // regions per bin -> first sorted position of the bin
     uint32_t lcnt[WJ_LIST_CAP], rcnt[WJ_RUN_CAP];  // hits per slice member
     uint32_t scan[WJ_WARPS + 1];
-    uint32_t tot;
+    unsigned long long tot;                        // hits of the (tile, window): 64-bit, a region may hit every interval of a huge index
     uint32_t w_first, w_last;
     uint32_t next_round;                           // rounds are handed to the warps in arrival order
     uint32_t sent;                                 // slice-local index of the sequence's sentinel if the run holds it, else 0xFFFFFFFF
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
         // ---- 3. probe: one bin per warp at a time, 32 of its regions per round, candidates in lock step ----------
         const bool list_full = __ldg(C.boff + row + nb) - l0 <= (uint32_t)WJ_LIST_CAP;   // every list member of the window is in shared memory
         const uint32_t run_end = S.sent == 0xFFFFFFFFu ? nrun : min(nrun, S.sent + 1u);   // the shared-memory run is ascending in start up to here
-        uint32_t mytot = 0;   // this lane's part of the (tile, window) hit total
+        unsigned long long mytot = 0;   // this lane's part of the (tile, window) hit total
         // the general walks: any list length, members beyond the shared-memory slice read from global memory
         auto walk_list = [&](const uint2 r, uint32_t i0, uint32_t i1) {
             for (uint32_t i = i0; i < i1; i++) {
@@ -264,7 +264,8 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
             if (racc) atomicAdd(&S.rcnt[b1.y + lane], racc);
             mytot += lacc + racc;
         }
-        mytot = __reduce_add_sync(0xffffffffu, mytot);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) mytot += __shfl_xor_sync(0xffffffffu, mytot, d);
         if (lane == 0 && mytot) atomicAdd(&S.tot, mytot);
         __syncthreads();
         // ---- 4. slot counters -> per-root counters and hit flags ---------------------------------------------
@@ -284,7 +285,7 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
             }
         }
         if (tid == 0) {
-            if (S.tot) atomicAdd(n_pairs, (unsigned long long)S.tot);
+            if (S.tot) atomicAdd(n_pairs, S.tot);
             S.sent = 0xFFFFFFFFu;
         }
         __syncthreads();  // the slice and the sorted tile are reused by the next window of this tile

@@ -172,3 +172,34 @@ def test_join_coarse_bins_overflow_the_slice(gffx, synth_quirk_gff, sub, monkeyp
                 assert np.array_equal(ri.ranges, want_ranges)
     finally:
         idx.close()
+
+
+def test_pair_buffer_grows_when_the_result_outruns_the_first_guess(quirk):
+    """Chromosome-wide regions hit every root of their sequence: far more than the 2 pairs per region the pair buffer is
+    first sized for, so the expansion (K1b) runs again into a buffer of the exact size.  Same multiset as the oracle."""
+    idx, o, _ = quirk
+    n_seq = len(idx.num_to_seqid)
+    chr_ = np.arange(200, dtype=np.uint32) % n_seq
+    regs = (chr_, np.zeros(200, dtype=np.uint32), np.full(200, 0xFFFFFFF0, dtype=np.uint32))
+    for mode, invert in [(2, False), (0, False), (1, True)]:
+        r = idx.query_features(regs, mode, invert)
+        want = o.query_features(regs, mode, invert)
+        assert r.n_pairs == want.shape[0]
+        if mode != 1:
+            assert r.n_pairs > 20 * 200
+        got = r.pairs if r.pairs is not None else np.zeros((0, 3), dtype=np.uint32)
+        assert np.array_equal(sorted_pairs(got), sorted_pairs(want))
+
+
+def test_pairs_come_back_grouped_by_root_in_start_order(quirk):
+    """The documented order of the pair array (include/gffx_b200.h): grouped by root, roots by (sequence, start, end)."""
+    idx, _, _ = quirk
+    regs = mixed_regions(idx, 4242, 3000)
+    r = idx.query_features(regs, 2, False)
+    p = r.pairs
+    assert p is not None and len(p) > 0
+    change = np.flatnonzero(np.any(p[1:] != p[:-1], axis=1)) + 1
+    heads = p[np.concatenate([[0], change])]
+    assert len(np.unique(heads, axis=0)) == len(heads)          # every root's copies are contiguous
+    r2 = idx.query_features(regs, 2, False)
+    assert np.array_equal(p, r2.pairs)                            # and the order is reproducible
