@@ -376,17 +376,23 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
     *dc = d_q[0].as<uint32_t>(); *ds = d_q[1].as<uint32_t>(); *de = d_q[2].as<uint32_t>();
 }
 
-template <int MODE, bool INV, bool FILT>
-static void launch_wj(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
+template <int MODE, bool INV, bool FILT, bool SMALL>
+static void launch_wj2(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
     static bool attr_set = false;   // per instantiation: the kernel's dynamic shared memory on top of its static 26 KB exceeds the 48 KB default
     if (!attr_set) {
-        GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, FILT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+        GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, FILT, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
         attr_set = true;
     }
     typedef unsigned long long ull;
     FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48};
-    wj_count_kernel<MODE, INV, FILT><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(), E->d_wj_cnt.as<ull>(),
-                                                                                n_pairs, err, E->FR, F);
+    wj_count_kernel<MODE, INV, FILT, SMALL><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(),
+                                                                                       E->d_wj_cnt.as<ull>(), n_pairs, err, E->FR, F);
+}
+template <int MODE, bool INV, bool FILT>
+static void launch_wj(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
+    // fewer than ~64 regions per window on average: most (tile, window) segments are small
+    if (n < 64ull * std::max<uint32_t>(E->WC.n_win, 1)) launch_wj2<MODE, INV, FILT, true>(E, poff, se, n, tiles, n_pairs, err);
+    else launch_wj2<MODE, INV, FILT, false>(E, poff, se, n, tiles, n_pairs, err);
 }
 // `filt`: the line filter's rank-space scatter (K3a) rides on the same pass
 static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool filt, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles,

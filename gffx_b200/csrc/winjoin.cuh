@@ -80,6 +80,48 @@ struct WjSmem {   // static shared memory (26 KB); the sorted tile (WJ_DYN_SMEM 
 };
 constexpr size_t WJ_DYN_SMEM = (size_t)WJ_TILE * sizeof(uint2);   // the (tile, window) regions ordered by bin
 
+// A (tile, window) segment of at most 32 regions — a small job, or the edge of a tile — is not worth a slice in shared memory:
+// one warp resolves it as a single round straight from the global index (the same candidate rule as the rounds below: the
+// list of the smallest bin among its regions, then the run while start < the largest region end).  Warps take such
+// segments side by side, so a 10 k-region job no longer walks the windows one after the other with CTA-wide barriers
+// (4.3 ms for 1000 regions before, profiles/host_overhead.py).
+template <int MODE, bool INVERT, bool FILT>
+__device__ __noinline__ void wj_small_segment(const WinBins& C, uint32_t w, const uint2* __restrict__ qse, uint32_t p_lo, uint32_t m_seg, uint32_t lane,
+                                              uint8_t* ent_hit, unsigned long long* ent_cnt, unsigned long long* n_pairs, const RankSpace& R,
+                                              const FilterArrays& F) {
+    const uint32_t nb = 1u << C.sub, bsh = C.shift - C.sub;
+    const size_t row = (size_t)w * (nb + 1);
+    const uint32_t seq = __ldg(C.win_seq + w);
+    const uint32_t lo = (w - __ldg(C.win0 + seq)) << C.shift;
+    const bool have = lane < m_seg;
+    const uint2 r = have ? qse[p_lo + lane] : make_uint2(0xFFFFFFFFu, 0u);
+    if (FILT) {
+        const RankSeq RS = load_rank_seq(R, seq);
+        if (RS.canon && RS.cnt != 0 && have) scatter_region<MODE>(R, RS, F, seq, r.x, r.y);
+    }
+    const uint32_t b = __reduce_min_sync(0xffffffffu, have ? min((r.x - lo) >> bsh, nb - 1) : 0xFFFFFFFFu);
+    const uint32_t o0 = __ldg(C.boff + row + b), o1 = __ldg(C.boff + row + b + 1);
+    unsigned long long tot = 0;
+    for (uint32_t i = o0; i < o1; i++) {
+        const uint4 v = __ldg(C.list4 + i);
+        const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+        const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+        if (nh && lane == 0) { atomicAdd(ent_cnt + v.w, (unsigned long long)nh); ent_hit[v.w] = 1; }
+        tot += nh;
+    }
+    const uint32_t re_max = __reduce_max_sync(0xffffffffu, r.y);
+    for (uint32_t j = __ldg(C.first + row + b + 1);; j++) {   // the sequence's sentinel (start 0xFFFFFFFF) ends it at the latest
+        const uint4 v = __ldg(C.ent4 + j);
+        if (v.x >= re_max) break;
+        const bool hit = v.x < r.y && v.y > r.x && wj_keep<MODE, INVERT>(v.x, v.y, r.x, r.y);
+        const uint32_t nh = __popc(__ballot_sync(0xffffffffu, hit));
+        if (nh && lane == 0) { atomicAdd(ent_cnt + j, (unsigned long long)nh); ent_hit[j] = 1; }
+        tot += nh;
+    }
+    if (lane == 0 && tot) atomicAdd(n_pairs, tot);
+}
+constexpr uint32_t WJ_SMALL_SEG = 32;
+
 #ifndef WJ_MIN_CTAS
 #define WJ_MIN_CTAS 3     // 40 registers: the join alone fits without spills
 #endif
@@ -90,7 +132,8 @@ constexpr size_t WJ_DYN_SMEM = (size_t)WJ_TILE * sizeof(uint2);   // the (tile, 
 // the regions are in shared memory already, and a round's 32 regions start inside one bin, so their rank look-ups
 // walk the same few cache lines.  (As its own kernel, with its own load and tile sort, K3a took 120-135 us per 10 M
 // regions, L1-bound on those look-ups: profiles/r01k.)
-template <int MODE, bool INVERT, bool FILT>
+// SMALL: few regions per window (a small job): segments of <= 32 regions go to wj_small_segment, one warp each.
+template <int MODE, bool INVERT, bool FILT, bool SMALL>
 __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_CTAS)
     wj_count_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint2* __restrict__ qse, uint64_t n, uint8_t* ent_hit,
                     unsigned long long* ent_cnt, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ err, RankSpace R,
@@ -129,6 +172,11 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
     }
     __syncthreads();
     const uint32_t w_first = S.w_first, w_last = S.w_last;
+    // small segments first, one warp each
+    for (uint32_t w = w_first + warp; SMALL && w <= w_last && w < n_win; w += WJ_WARPS) {
+        const uint32_t p_lo = max(__ldg(poff + w), tile0), p_hi = min(__ldg(poff + w + 1), tile0 + m);
+        if (p_lo < p_hi && p_hi - p_lo <= WJ_SMALL_SEG) wj_small_segment<MODE, INVERT, FILT>(C, w, qse, p_lo, p_hi - p_lo, lane, ent_hit, ent_cnt, n_pairs, R, F);
+    }
     for (uint32_t w = w_first; w <= w_last; w++) {
         const uint32_t p_lo = max(__ldg(poff + w), tile0), p_hi = min(__ldg(poff + w + 1), tile0 + m);
         if (p_lo >= p_hi) continue;   // empty window (uniform)
@@ -136,6 +184,7 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
             if (tid == 0) *err = 1;
             continue;
         }
+        if (SMALL && p_hi - p_lo <= WJ_SMALL_SEG) continue;   // done above
         // ---- 1. the window's slice -----------------------------------------------------------------
         const size_t row = (size_t)w * (nb + 1);
         const uint32_t seq = __ldg(C.win_seq + w);
