@@ -385,7 +385,8 @@ static void launch_wj2(EngineImpl* E, const uint32_t* poff, const uint2* se, uin
     }
     typedef unsigned long long ull;
     FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48};
-    wj_count_kernel<MODE, INV, FILT, SMALL><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(),
+    const dim3 grid(tiles, SMALL ? 16u : 1u);   // SMALL: 16 CTAs share a tile's small segments
+    wj_count_kernel<MODE, INV, FILT, SMALL><<<grid, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(),
                                                                                        E->d_wj_cnt.as<ull>(), n_pairs, err, E->FR, F);
 }
 template <int MODE, bool INV, bool FILT>

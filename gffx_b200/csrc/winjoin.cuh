@@ -172,11 +172,12 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
     }
     __syncthreads();
     const uint32_t w_first = S.w_first, w_last = S.w_last;
-    // small segments first, one warp each
-    for (uint32_t w = w_first + warp; SMALL && w <= w_last && w < n_win; w += WJ_WARPS) {
+    // small segments first, one warp each; a SMALL launch spreads them over gridDim.y CTAs per tile, of which only y = 0 goes on
+    for (uint32_t w = w_first + warp + WJ_WARPS * blockIdx.y; SMALL && w <= w_last && w < n_win; w += WJ_WARPS * gridDim.y) {
         const uint32_t p_lo = max(__ldg(poff + w), tile0), p_hi = min(__ldg(poff + w + 1), tile0 + m);
         if (p_lo < p_hi && p_hi - p_lo <= WJ_SMALL_SEG) wj_small_segment<MODE, INVERT, FILT>(C, w, qse, p_lo, p_hi - p_lo, lane, ent_hit, ent_cnt, n_pairs, R, F);
     }
+    if (SMALL && blockIdx.y != 0) return;
     for (uint32_t w = w_first; w <= w_last; w++) {
         const uint32_t p_lo = max(__ldg(poff + w), tile0), p_hi = min(__ldg(poff + w + 1), tile0 + m);
         if (p_lo >= p_hi) continue;   // empty window (uniform)
