@@ -2,6 +2,9 @@
 #include <algorithm>
 #include <numeric>
 #include <mutex>
+#include <atomic>
+#include <functional>
+#include <thread>
 #include "engine_impl.cuh"
 #include "synth_common.h"
 
@@ -49,10 +52,16 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
-    build_windows();
-    build_join();
-    build_blocks();
-    build_lines();
+    {
+        PhaseTimer t("engine: windows + join index");
+        build_windows();
+        build_join();
+        build_blocks();
+    }
+    {
+        PhaseTimer t("engine: lines + rank space");
+        build_lines();
+    }
     d_small.ensure(256);
     d_warn.ensure(WARN_CAP * 4);
     GFFX_CUDA(cudaStreamSynchronize(st));
@@ -227,17 +236,40 @@ void EngineImpl::build_blocks() {
 void EngineImpl::build_lines() {
     const LineTable& L = H->lines;
     const size_t n = L.size(), n_seqs = H->seq_names.size();
-    // per sequence: sorted distinct S/E of usable lines
+    // per sequence: sorted distinct S/E of usable lines (host threads: sequences are sorted side by side, longest first)
+    const size_t T = (size_t)std::max(1, H->n_threads);
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
+        if (n_jobs <= 1 || T <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
+        std::vector<std::thread> th;
+        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
+        for (auto& t : th) t.join();
+    };
     std::vector<std::vector<uint32_t>> xs(n_seqs);
-    for (size_t i = 0; i < n; i++)
-        if (L.flags[i] & LN_I_OK) { xs[L.iseq[i]].push_back(L.S[i]); xs[L.iseq[i]].push_back(L.E[i]); }
+    {
+        PhaseTimer t("  rank space: coordinate sets (sort)");
+        std::vector<size_t> cnt(n_seqs, 0);
+        for (size_t i = 0; i < n; i++)
+            if (L.flags[i] & LN_I_OK) cnt[L.iseq[i]] += 2;
+        for (size_t s = 0; s < n_seqs; s++) xs[s].reserve(cnt[s]);
+        for (size_t i = 0; i < n; i++)
+            if (L.flags[i] & LN_I_OK) { xs[L.iseq[i]].push_back(L.S[i]); xs[L.iseq[i]].push_back(L.E[i]); }
+        std::vector<uint32_t> order(n_seqs);
+        for (size_t s = 0; s < n_seqs; s++) order[s] = (uint32_t)s;
+        std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return xs[a].size() > xs[b].size(); });
+        std::atomic<size_t> next{0};
+        run_parallel(std::min(T, n_seqs), [&](size_t) {
+            for (size_t k; (k = next.fetch_add(1)) < n_seqs;) {
+                auto& v = xs[order[k]];
+                std::sort(v.begin(), v.end());
+                v.erase(std::unique(v.begin(), v.end()), v.end());
+            }
+        });
+    }
     std::vector<RankSeq> seqs(n_seqs);
     std::vector<uint32_t> X, dir;
     uint32_t slot = 0;
     for (size_t s = 0; s < n_seqs; s++) {
         auto& v = xs[s];
-        std::sort(v.begin(), v.end());
-        v.erase(std::unique(v.begin(), v.end()), v.end());
         RankSeq& r = seqs[s];
         r.x0 = (uint32_t)X.size();
         r.cnt = (uint32_t)v.size();
@@ -262,13 +294,20 @@ void EngineImpl::build_lines() {
     }
     f_slots = slot;
     std::vector<uint32_t> iS(n, 0), iE(n, 0);
-    for (size_t i = 0; i < n; i++)
-        if (L.flags[i] & LN_I_OK) {
-            const auto& v = xs[L.iseq[i]];
-            const RankSeq& r = seqs[L.iseq[i]];
-            iS[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.S[i]) - v.begin());
-            iE[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.E[i]) - v.begin());
-        }
+    const size_t n_chunks = n >= (1u << 16) ? T : 1;
+    PhaseTimer* t_rank = new PhaseTimer("  rank space: line ranks");
+    run_parallel(n_chunks, [&](size_t c) {
+        const size_t i0 = n * c / n_chunks, i1 = n * (c + 1) / n_chunks;
+        for (size_t i = i0; i < i1; i++)
+            if (L.flags[i] & LN_I_OK) {
+                const auto& v = xs[L.iseq[i]];
+                const RankSeq& r = seqs[L.iseq[i]];
+                iS[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.S[i]) - v.begin());
+                iE[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.E[i]) - v.begin());
+            }
+    });
+    delete t_rank;
+    PhaseTimer t_up("  line table upload");
     upload(d_ln_flags, L.flags, st);
     upload(d_ln_blk, L.blk, st);
     upload(d_ln_type, L.type_id, st);

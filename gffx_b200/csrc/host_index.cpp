@@ -1,4 +1,5 @@
 #include "host_index.h"
+#include <functional>
 #include <algorithm>
 #include <thread>
 #include <fcntl.h>
@@ -134,6 +135,8 @@ void load_gof_file(const std::string& path, std::vector<uint32_t>* fid, std::vec
 // ------------------------------------------------------------------------------------------
 void HostIndex::open(const std::string& path, int threads) {
     gff_path = path;
+    PhaseTimer t_all("host index (total)");
+    PhaseTimer* t_files = new PhaseTimer("  index files");
     load_sqs_file(path + ".sqs", &seq_names);
     uint32_t n_trees = 0;
     load_trees_flat(path + ".rit", path + ".rix", &roots, &n_trees);
@@ -144,6 +147,7 @@ void HostIndex::open(const std::string& path, int threads) {
         gff = gff_map.data();
         gff_len = gff_map.size();
     }
+    delete t_files;
     finish(gfid, gs, ge, threads);
 }
 
@@ -217,6 +221,7 @@ struct Part {  // lines of a contiguous range of blocks
     LineTable t;
     std::vector<uint64_t> id_off;  // absolute offset of the ID string (d_ok lines)
     std::vector<uint32_t> id_len;
+    std::vector<uint64_t> id_hash; // FNV-1a of the ID string (d_ok lines): the dictionary is built from these, in parallel
     LocalDict types, chroms;
     std::vector<uint64_t> blk_nlines;
     std::vector<uint8_t> blk_utf8;
@@ -239,12 +244,14 @@ inline bool find_id(const uint8_t* a, size_t n, size_t* vs, size_t* vn) {
 }  // namespace
 
 void HostIndex::build_lines(int threads) {
+    PhaseTimer t_lines("  GFF line table (host scan)");
     const size_t nb = blocks.size();
     blk_utf8.assign(nb, 0);
     blk_line0.assign(nb + 1, 0);
     lines = LineTable();
     if (!gff || gff_len == 0 || nb == 0) return;
     if (threads < 1) threads = 1;
+    n_threads = threads;
     size_t nparts = std::min<size_t>((size_t)threads, std::max<size_t>(1, nb / 64));
     std::vector<Part> parts(nparts);
     // split blocks so that each part scans about the same number of bytes
@@ -320,11 +327,16 @@ void HostIndex::build_lines(int threads) {
                     t.S.push_back(S); t.E.push_back(E); t.iseq.push_back(iseq); t.type_id.push_back(ty);
                     t.fs.push_back(fs); t.fe.push_back(fe); t.chrom.push_back(chrom);
                     if (fl & LN_D_OK) {
-                        P.id_off.push_back((uint64_t)(tab[7] + 1 + ivs - gff));
+                        const uint8_t* ids0 = tab[7] + 1 + ivs;
+                        uint64_t h = 1469598103934665603ull;
+                        for (size_t z = 0; z < ivn; z++) { h ^= ids0[z]; h *= 1099511628211ull; }
+                        P.id_off.push_back((uint64_t)(ids0 - gff));
                         P.id_len.push_back((uint32_t)ivn);
+                        P.id_hash.push_back(h);
                     } else {
                         P.id_off.push_back(0);
                         P.id_len.push_back(0);
+                        P.id_hash.push_back(0);
                     }
                     nl_count++;
                 }
@@ -333,42 +345,99 @@ void HostIndex::build_lines(int threads) {
             P.blk_nlines[b - b0] = nl_count;
         }
     };
-    if (nparts == 1) work(0);
-    else {
-        std::vector<std::thread> th;
-        for (size_t i = 0; i < nparts; i++) th.emplace_back(work, i);
-        for (auto& t : th) t.join();
+    {
+        PhaseTimer t_scan("    parallel scan");
+        if (nparts == 1) work(0);
+        else {
+            std::vector<std::thread> th;
+            for (size_t i = 0; i < nparts; i++) th.emplace_back(work, i);
+            for (auto& t : th) t.join();
+        }
     }
-    // concatenate, remapping the per-part dictionaries; intern IDs serially (dictionary order = file order)
-    size_t total = 0;
-    for (auto& P : parts) total += P.t.size();
+    PhaseTimer t_merge("    merge + ID dictionary");
+    // concatenate (every part copies its own slice, in parallel), remapping the per-part type / chromosome dictionaries
+    std::vector<size_t> base(nparts + 1, 0);
+    for (size_t pi = 0; pi < nparts; pi++) base[pi + 1] = base[pi] + parts[pi].t.size();
+    const size_t total = base[nparts];
     LineTable& L = lines;
-    L.off.reserve(total); L.len.reserve(total); L.blk.reserve(total); L.flags.reserve(total);
-    L.S.reserve(total); L.E.reserve(total); L.iseq.reserve(total); L.type_id.reserve(total);
-    L.fs.reserve(total); L.fe.reserve(total); L.id.reserve(total); L.chrom.reserve(total);
-    ids.map.reserve(total);
-    for (size_t pi = 0; pi < nparts; pi++) {
+    L.off.resize(total); L.len.resize(total); L.blk.resize(total); L.flags.resize(total);
+    L.S.resize(total); L.E.resize(total); L.iseq.resize(total); L.type_id.resize(total);
+    L.fs.resize(total); L.fe.resize(total); L.id.assign(total, NONE32); L.chrom.resize(total);
+    std::vector<uint64_t> g_hash(total), g_off(total);
+    std::vector<uint32_t> g_len(total);
+    std::vector<std::vector<uint32_t>> tmaps(nparts), cmaps(nparts);
+    for (size_t pi = 0; pi < nparts; pi++) {   // dictionary order = file order: parts in turn
         Part& P = parts[pi];
-        std::vector<uint32_t> tmap(P.types.items.size()), cmap(P.chroms.items.size());
-        for (size_t i = 0; i < tmap.size(); i++) tmap[i] = types.intern(P.types.items[i]);
-        for (size_t i = 0; i < cmap.size(); i++) cmap[i] = chroms.intern(P.chroms.items[i]);
+        tmaps[pi].resize(P.types.items.size());
+        cmaps[pi].resize(P.chroms.items.size());
+        for (size_t i = 0; i < tmaps[pi].size(); i++) tmaps[pi][i] = types.intern(P.types.items[i]);
+        for (size_t i = 0; i < cmaps[pi].size(); i++) cmaps[pi][i] = chroms.intern(P.chroms.items[i]);
         for (size_t b = cut[pi]; b < cut[pi + 1]; b++) {
             blk_utf8[b] = P.blk_utf8[b - cut[pi]];
             blk_line0[b + 1] = P.blk_nlines[b - cut[pi]];
         }
+    }
+    auto copy_part = [&](size_t pi) {
+        Part& P = parts[pi];
         const LineTable& t = P.t;
-        for (size_t i = 0; i < t.size(); i++) {
-            L.off.push_back(t.off[i]); L.len.push_back(t.len[i]); L.blk.push_back(t.blk[i]); L.flags.push_back(t.flags[i]);
-            L.S.push_back(t.S[i]); L.E.push_back(t.E[i]); L.iseq.push_back(t.iseq[i]);
-            L.type_id.push_back(t.type_id[i] == NONE32 ? NONE32 : tmap[t.type_id[i]]);
-            L.fs.push_back(t.fs[i]); L.fe.push_back(t.fe[i]);
-            L.chrom.push_back(t.chrom[i] == NONE32 ? NONE32 : cmap[t.chrom[i]]);
-            if (t.flags[i] & LN_D_OK)
-                L.id.push_back(ids.intern(std::string_view((const char*)gff + P.id_off[i], P.id_len[i])));
-            else
-                L.id.push_back(NONE32);
+        const size_t o = base[pi], m = t.size();
+        if (m) {
+            memcpy(&L.off[o], t.off.data(), m * 8); memcpy(&L.len[o], t.len.data(), m * 4); memcpy(&L.blk[o], t.blk.data(), m * 4);
+            memcpy(&L.flags[o], t.flags.data(), m); memcpy(&L.S[o], t.S.data(), m * 4); memcpy(&L.E[o], t.E.data(), m * 4);
+            memcpy(&L.iseq[o], t.iseq.data(), m * 4); memcpy(&L.fs[o], t.fs.data(), m * 4); memcpy(&L.fe[o], t.fe.data(), m * 4);
+            memcpy(&g_hash[o], P.id_hash.data(), m * 8); memcpy(&g_off[o], P.id_off.data(), m * 8); memcpy(&g_len[o], P.id_len.data(), m * 4);
+        }
+        for (size_t i = 0; i < m; i++) {
+            L.type_id[o + i] = t.type_id[i] == NONE32 ? NONE32 : tmaps[pi][t.type_id[i]];
+            L.chrom[o + i] = t.chrom[i] == NONE32 ? NONE32 : cmaps[pi][t.chrom[i]];
         }
         P = Part();
+    };
+    // ID dictionary: the lines are cut into `nshard` shards by hash; every shard finds, for each of its lines, the FIRST line
+    // with the same ID (its own open-addressing table over line numbers, lines visited in file order); an ID's number is then
+    // the rank of its first line among all first lines = order of first appearance, as a serial intern loop would number them
+    const size_t nshard = std::max<size_t>(1, std::min<size_t>((size_t)threads, 64));
+    std::vector<uint32_t> first(total, NONE32);
+    auto dedup_shard = [&](size_t sh) {
+        size_t cnt = 0;
+        for (size_t i = 0; i < total; i++)
+            if ((L.flags[i] & LN_D_OK) && (g_hash[i] >> 32) % nshard == sh) cnt++;
+        size_t cap = 16;
+        while (cap < 2 * cnt + 2) cap <<= 1;
+        std::vector<uint32_t> tab(cap, 0);   // line number + 1
+        const size_t mask = cap - 1;
+        for (size_t i = 0; i < total; i++) {
+            if (!(L.flags[i] & LN_D_OK)) continue;
+            const uint64_t h = g_hash[i];
+            if ((h >> 32) % nshard != sh) continue;
+            size_t k = (size_t)h & mask;
+            for (;; k = (k + 1) & mask) {
+                if (tab[k] == 0) { tab[k] = (uint32_t)i + 1; first[i] = (uint32_t)i; break; }
+                const size_t j = tab[k] - 1;
+                if (g_hash[j] == h && g_len[j] == g_len[i] && memcmp(gff + g_off[j], gff + g_off[i], g_len[i]) == 0) { first[i] = (uint32_t)j; break; }
+            }
+        }
+    };
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
+        if (n_jobs <= 1 || threads <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
+        std::vector<std::thread> th;
+        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
+        for (auto& t : th) t.join();
+    };
+    if (total >= (1ull << 32) - 1) throw Err(E_FORMAT, "more than 2^32-2 GFF lines inside blocks");
+    run_parallel(nparts, copy_part);
+    run_parallel(nshard, dedup_shard);
+    ids = IdTable();
+    ids.base = gff;
+    for (size_t i = 0; i < total; i++) {   // first[i] <= i: one forward pass numbers the IDs and fills the column
+        if (first[i] == NONE32) continue;
+        if (first[i] == (uint32_t)i) {
+            L.id[i] = (uint32_t)ids.off.size();
+            ids.off.push_back(g_off[i]);
+            ids.len.push_back(g_len[i]);
+        } else {
+            L.id[i] = L.id[first[i]];
+        }
     }
     for (size_t b = 0; b < nb; b++) blk_line0[b + 1] += blk_line0[b];
 }

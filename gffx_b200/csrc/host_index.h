@@ -49,6 +49,16 @@ struct StringPool {  // append-only dictionary: string -> dense index
     size_t size() const { return keys.size(); }
 };
 
+// ID dictionary of the depth / coverage view: index = order of first appearance in the GFF; the strings stay where they are,
+// in the GFF text (mapped file or the caller's buffer, both outlive the index)
+struct IdTable {
+    const uint8_t* base = nullptr;
+    std::vector<uint64_t> off;
+    std::vector<uint32_t> len;
+    size_t size() const { return off.size(); }
+    std::string_view get(uint32_t i) const { return std::string_view((const char*)base + off[i], len[i]); }
+};
+
 struct HostIndex {
     std::string gff_path;
     std::vector<std::string> seq_names;                     // num_to_seqid
@@ -62,7 +72,9 @@ struct HostIndex {
     const uint8_t* gff = nullptr;
     uint64_t gff_len = 0;
     LineTable lines;
-    StringPool types, ids, chroms;
+    StringPool types, chroms;
+    IdTable ids;
+    int n_threads = 1;   // host threads the loaders were given (the engine's load-time builders use as many)
 
     // load .sqs/.rix/.rit/.gof beside `path` and (when the text is there) build the line table
     void open(const std::string& path, int threads);

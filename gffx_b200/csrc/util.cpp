@@ -4,7 +4,15 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <chrono>
+#include <cstdlib>
+
 namespace gffx {
+
+double PhaseTimer::now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+PhaseTimer::PhaseTimer(const char* w) : what(w), t0(0), on(getenv("GFFX_TIMING") != nullptr) { if (on) t0 = now(); }
+PhaseTimer::~PhaseTimer() { if (on) fprintf(stderr, "[gffx timing] %-28s %8.1f ms\n", what, (now() - t0) * 1e3); }
+
 
 Mapped::~Mapped() {
     if (p_) munmap((void*)p_, n_);

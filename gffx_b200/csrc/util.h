@@ -48,6 +48,16 @@ std::string_view trim_unicode(std::string_view s);           // str::trim
 bool parse_u32_strict(const uint8_t* s, size_t n, uint32_t* out);   // digits only, checked (intersect.rs:526-538)
 bool parse_u32_rust(std::string_view s, uint32_t* out);              // str::parse::<u32> ('+' allowed)
 
+// GFFX_TIMING=1: wall time of the load phases on stderr (profiles/load_time.py)
+struct PhaseTimer {
+    const char* what;
+    double t0;
+    bool on;
+    static double now();
+    explicit PhaseTimer(const char* w);
+    ~PhaseTimer();
+};
+
 inline const uint8_t* find_byte(const uint8_t* p, const uint8_t* end, uint8_t c) {
     return p < end ? (const uint8_t*)memchr(p, c, (size_t)(end - p)) : nullptr;
 }
