@@ -43,6 +43,12 @@ class IndexDesc(C.Structure):
     ]
 
 
+class ResultInfo(C.Structure):   # gffx_result_info
+    _fields_ = [(n, C.c_uint64) for n in ("n_queries", "n_pairs", "n_roots", "n_ranges", "bytes_out", "n_warn")] + [
+        ("pairs", u32p), ("pairs_device", vp), ("ranges", u64p), ("warn_fids", u32p),
+        ("kernel_ms", C.c_double), ("stage_ms", C.c_double * 12), ("launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+
 class IntersectArgs(C.Structure):
     _fields_ = [
         ("input", C.c_char_p),
@@ -117,6 +123,7 @@ SIGNATURES = {
     "gffx_result_kernel_ms": (C.c_double, vp),
     "gffx_result_launches": (C.c_uint32, vp),
     "gffx_result_stage_ms": (C.c_double, vp, C.c_int),
+    "gffx_result_get_info": (C.c_int, vp, vp),
     "gffx_result_free": (None, vp),
     "gffx_write_ranges": (C.c_int, vp, vp, C.c_uint64, C.c_char_p),
     "gffx_gather_text": (C.c_int, vp, vp, C.c_uint64, C.c_uint32, C.POINTER(vp), C.POINTER(C.c_uint64)),

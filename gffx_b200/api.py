@@ -103,30 +103,25 @@ def _take_result(h, copy: bool = True) -> Result:
     done = False
     try:
         r = Result()
-        r.n_queries = lib.gffx_result_n_queries(h)
-        r.n_pairs = lib.gffx_result_n_pairs(h)
-        p = lib.gffx_result_pairs(h)
-        if p and r.n_pairs:
-            r.pairs = np.ctypeslib.as_array(p, shape=(r.n_pairs, 3))
+        info = _lib.ResultInfo()
+        _check(lib.gffx_result_get_info(h, C.byref(info)))   # one call for the whole summary
+        r.n_queries, r.n_pairs, r.n_roots, r.n_ranges, r.bytes_out = info.n_queries, info.n_pairs, info.n_roots, info.n_ranges, info.bytes_out
+        if info.pairs and r.n_pairs:
+            r.pairs = np.ctypeslib.as_array(info.pairs, shape=(r.n_pairs, 3))
             if copy:
                 r.pairs = r.pairs.copy()
-        r.pairs_device_ptr = lib.gffx_result_pairs_device(h) or 0
-        r.n_roots = lib.gffx_result_n_roots(h)
-        r.n_ranges = lib.gffx_result_n_ranges(h)
-        q = lib.gffx_result_ranges(h)
-        if q and r.n_ranges:
-            r.ranges = np.ctypeslib.as_array(q, shape=(r.n_ranges, 2))
+        r.pairs_device_ptr = info.pairs_device or 0
+        if info.ranges and r.n_ranges:
+            r.ranges = np.ctypeslib.as_array(info.ranges, shape=(r.n_ranges, 2))
             if copy:
                 r.ranges = r.ranges.copy()
         elif r.n_ranges == 0:
             r.ranges = np.zeros((0, 2), dtype=np.uint64)
-        r.bytes_out = lib.gffx_result_bytes_out(h)
-        nw = lib.gffx_result_n_warn(h)
-        if nw:
-            r.warn_fids = list(np.ctypeslib.as_array(lib.gffx_result_warn_fids(h), shape=(nw,)))
-        r.kernel_ms = lib.gffx_result_kernel_ms(h)
-        r.stage_ms = tuple(lib.gffx_result_stage_ms(h, k) for k in range(12))
-        r.launches = lib.gffx_result_launches(h)
+        if info.n_warn:
+            r.warn_fids = list(np.ctypeslib.as_array(info.warn_fids, shape=(info.n_warn,)))
+        r.kernel_ms = info.kernel_ms
+        r.stage_ms = tuple(info.stage_ms)
+        r.launches = info.launches
         if not copy:
             r._h = h
             done = True

@@ -253,6 +253,18 @@ const uint32_t* gffx_result_warn_fids(const gffx_result* r) { return r && !r->r.
 double gffx_result_kernel_ms(const gffx_result* r) { return r ? r->r.kernel_ms : 0; }
 uint32_t gffx_result_launches(const gffx_result* r) { return r ? r->r.launches : 0; }
 double gffx_result_stage_ms(const gffx_result* r, int stage) { return (r && stage >= 0 && stage < 12) ? r->r.stage_ms[stage] : 0; }
+int gffx_result_get_info(const gffx_result* r, gffx_result_info* out) {
+    if (!r || !out) return GFFX_E_ARG;
+    const auto& R = r->r;
+    out->n_queries = R.n_queries; out->n_pairs = R.n_pairs; out->n_roots = R.n_roots; out->n_ranges = R.n_ranges;
+    out->bytes_out = R.bytes_out; out->n_warn = R.warn_fids.size();
+    out->pairs = gffx_result_pairs(r); out->pairs_device = gffx_result_pairs_device(r);
+    out->ranges = gffx_result_ranges(r); out->warn_fids = gffx_result_warn_fids(r);
+    out->kernel_ms = R.kernel_ms;
+    for (int k = 0; k < 12; k++) out->stage_ms[k] = R.stage_ms[k];
+    out->launches = R.launches; out->reserved = 0;
+    return GFFX_OK;
+}
 void gffx_result_free(gffx_result* r) { delete r; }
 
 int gffx_write_ranges(const gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, const char* out_path) {

@@ -166,6 +166,19 @@ uint32_t gffx_result_launches(const gffx_result* r);
  * 7 pair offsets scan + pair expansion, 8 the window partition pass (totals + offsets + scatter);
  * stages that did not run report 0 */
 double gffx_result_stage_ms(const gffx_result* r, int stage);
+/* everything above in one call (the accessors stay): what run() reads after the join, src/commands/intersect.rs:596-654 */
+typedef struct gffx_result_info {
+    uint64_t n_queries, n_pairs, n_roots, n_ranges, bytes_out, n_warn;
+    const uint32_t* pairs;        /* as gffx_result_pairs */
+    const uint32_t* pairs_device; /* as gffx_result_pairs_device */
+    const uint64_t* ranges;       /* as gffx_result_ranges */
+    const uint32_t* warn_fids;    /* as gffx_result_warn_fids */
+    double kernel_ms;
+    double stage_ms[12];
+    uint32_t launches;
+    uint32_t reserved;
+} gffx_result_info;
+int gffx_result_get_info(const gffx_result* r, gffx_result_info* out);
 void gffx_result_free(gffx_result* r);
 
 /* Write the selected byte ranges of the GFF (write_vectored loops of intersect.rs:385-429 and
