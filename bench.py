@@ -333,6 +333,13 @@ def run_gpu(args, rank, world, local_rank):
                 "algorithmic_bytes_per_launch": dom["bytes"] / max(1, dom["launches"]), "share_of_step": dom["ms"] / stage_sum,
                 "kernels": {n: {"ms_per_step": k["ms"] / args.steps, "share": k["ms"] / stage_sum,
                                 "GBps": (k["bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else 0.0)} for n, k in per_kernel.items()}}
+    # the whole pass against the same roof: every algorithmic byte of SURVEY.md 8(d) for a5 + a7 (each credited once)
+    # over the pass's whole kernel span, partition and scans included
+    pass_bytes = sum(k["bytes"] for k in per_kernel.values())
+    pass_ms = sum(a["kernel_ms"] for a in acc.values())
+    if pass_ms > 0:
+        roofline["whole_pass"] = {"algorithmic_bytes_per_step": pass_bytes / args.steps, "ms_per_step": pass_ms / args.steps,
+                                  "achieved": pass_bytes / (pass_ms * 1e-3) / 1e9, "frac": pass_bytes / (pass_ms * 1e-3) / 1e9 / peak}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:

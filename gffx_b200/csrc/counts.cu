@@ -51,6 +51,7 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     cudaStream_t st = E->st;
     upload(C->d_rank, h.rank, st);
     upload(C->d_cov, h.cov, st);
+    h.X.insert(h.X.end(), 8, 0u);   // rank_lb (filter.cuh) reads up to 4 entries past a bin
     upload(C->d_X, h.X, st);
     upload(C->d_dir, h.dir, st);
     upload(C->d_u_space, h.u_space, st);

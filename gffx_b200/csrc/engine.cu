@@ -293,6 +293,7 @@ void EngineImpl::build_lines() {
         X.insert(X.end(), v.begin(), v.end());
     }
     f_slots = slot;
+    X.insert(X.end(), 8, 0u);   // rank_lb (filter.cuh) reads up to 4 entries past a bin
     std::vector<uint32_t> iS(n, 0), iE(n, 0);
     const size_t n_chunks = n >= (1u << 16) ? T : 1;
     PhaseTimer* t_rank = new PhaseTimer("  rank space: line ranks");

@@ -49,9 +49,20 @@ __device__ __forceinline__ uint32_t rank_lb(const RankSpace& R, const RankSeq& S
         uint32_t mid = (lo + hi) >> 1;
         if (__ldg(X + mid) < v) lo = mid + 1; else hi = mid;
     }
-    while (lo < hi && __ldg(X + lo) < v) lo++;
-    if (lo < S.cnt && __ldg(X + lo) == v) *eq = true;
-    return lo;
+    // at most 4 values left: five independent loads (the array is padded by 8 entries) instead of a chain of dependent ones;
+    // the values are sorted and distinct, those past `hi` belong to later bins (> v), those past cnt to the next sequence
+    uint32_t x[5];
+#pragma unroll
+    for (int k = 0; k < 5; k++) x[k] = __ldg(X + lo + k);
+    uint32_t c = 0;
+    bool e = false;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        if (k < 4) c += (lo + k < hi && x[k] < v) ? 1u : 0u;
+        e |= lo + k < S.cnt && x[k] == v;
+    }
+    *eq = e;
+    return lo + c;
 }
 
 __device__ __forceinline__ RankSeq load_rank_seq(const RankSpace& R, uint32_t seq) {
