@@ -131,9 +131,18 @@ struct FilterScans {
     const uint32_t* ne_on;          // FilterArrays::any_inv: 0 = no mark in Me, NE was not scanned
 };
 
+// The per-line decision in two rounds of independent loads (a thread is latency bound here: one line, a handful of loads):
+// round 1 = the line's own columns, round 2 = the scan cells they point at; nothing is loaded behind a branch.
+struct LineCols {
+    uint32_t seq, S, E, iS, iE;
+};
+__device__ __forceinline__ LineCols load_line_cols(const LineArrays& L, uint64_t i) {
+    return LineCols{L.iseq[i], L.S[i], L.E[i], L.iS[i], L.iE[i]};
+}
+
 template <int MODE>
-__device__ __forceinline__ bool line_matches(const LineArrays& L, const FilterScans& P, uint64_t i) {
-    const uint32_t seq = L.iseq[i], S = L.S[i], E = L.E[i], iS = L.iS[i], iE = L.iE[i];
+__device__ __forceinline__ bool line_matches(const LineCols& c, const FilterScans& P) {
+    const uint32_t seq = c.seq, S = c.S, E = c.E, iS = c.iS, iE = c.iE;
     if (MODE == 0) {
         const unsigned long long k = P.PMX[iS];
         return (k >> TAG_MAX_SHIFT) == seq && (k & ((1ull << TAG_MAX_SHIFT) - 1)) >= (unsigned long long)E + 1ull;
@@ -142,14 +151,15 @@ __device__ __forceinline__ bool line_matches(const LineArrays& L, const FilterSc
         return (k >> TAG_MIN_SHIFT) == seq && (uint32_t)k <= E;
     } else {
         const unsigned long long mask = (1ull << TAG_MAX_SHIFT) - 1;
-        const unsigned long long k1 = P.PMX[iS];
+        const uint32_t c0 = 2u * iS + 1u, c1 = 2u * iE + 1u;
+        const unsigned long long k1 = P.PMX[iS], k2 = P.PMX[iE];
+        const uint32_t ns = P.NS[c0];
+        const bool ne_on = *P.ne_on != 0u;
         if ((k1 >> TAG_MAX_SHIFT) == seq && (k1 & mask) >= (unsigned long long)S + 1ull) return true;  // qs<=S<=qe
-        const unsigned long long k2 = P.PMX[iE];
         if ((k2 >> TAG_MAX_SHIFT) == seq && (k2 & mask) >= (unsigned long long)E + 1ull) return true;  // qs<=E<=qe
         if (S <= E) {
-            const uint32_t c0 = 2u * iS + 1u, c1 = 2u * iE + 1u;
-            if (P.NS[c0] <= c1) return true;  // S<=qs<=E
-            if (*P.ne_on && P.NE[c0] <= c1) return true;  // S<=qe<=E
+            if (ns <= c1) return true;  // S<=qs<=E
+            if (ne_on && P.NE[c0] <= c1) return true;  // S<=qe<=E
         }
         return false;
     }
@@ -166,13 +176,14 @@ __global__ void __launch_bounds__(LINE_THREADS)
     const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
     uint32_t k = 0;
     if (i < L.n) {
-        bool ok = (L.flags[i] & 1) && blk_sel[L.blk[i]];
-        if (ok && have_types) {
-            const uint32_t t = L.type_id[i];
-            ok = t != 0xFFFFFFFFu && type_allow[t];
-        }
-        if (ok) ok = line_matches<MODE>(L, P, i);
-        k = ok ? 1u : 0u;
+        const uint8_t fl = L.flags[i];
+        const uint32_t blk = L.blk[i];
+        const uint32_t t = have_types ? L.type_id[i] : 0u;
+        const LineCols c = load_line_cols(L, i);
+        bool ok = (fl & 1) && blk_sel[blk];
+        if (have_types) ok = ok && t != 0xFFFFFFFFu && type_allow[t];
+        const bool mt = line_matches<MODE>(c, P);   // iS / iE are 0 (a valid slot) for a line without usable coordinates
+        k = ok && mt ? 1u : 0u;
         keep[i] = (uint8_t)k;
     }
     uint32_t tot;
@@ -186,7 +197,11 @@ __global__ void __launch_bounds__(LINE_THREADS)
 template <int MODE>
 __global__ void __launch_bounds__(LINE_THREADS) match_lines_kernel(LineArrays L, FilterScans P, uint8_t* __restrict__ match) {
     const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
-    if (i < L.n) match[i] = ((L.flags[i] & 1) && line_matches<MODE>(L, P, i)) ? 1 : 0;
+    if (i < L.n) {
+        const uint8_t fl = L.flags[i];
+        const LineCols c = load_line_cols(L, i);
+        match[i] = ((fl & 1) && line_matches<MODE>(c, P)) ? 1 : 0;
+    }
 }
 
 static __global__ void __launch_bounds__(LINE_THREADS)
@@ -216,15 +231,15 @@ static __global__ void __launch_bounds__(LINE_THREADS)
     __shared__ uint32_t sm[LINE_THREADS / 32 + 1];
     __shared__ unsigned long long sb[LINE_THREADS / 32 + 1];
     const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
+    // offset and length are loaded beside the flag, not behind it: one round of loads, then the scan
     const uint32_t k = (i < L.n && keep[i]) ? 1u : 0u;
+    const uint64_t o = i < L.n ? L.off[i] : 0ull;
+    unsigned long long len = i < L.n ? L.len[i] : 0u;
+    const uint64_t t0 = tile_off[blockIdx.x];
     uint32_t tot;
     const uint32_t pos = block_scan_excl(k, OpSum(), 0u, sm, &tot);
-    unsigned long long len = 0;
-    if (k) {
-        const uint64_t o = L.off[i];
-        len = L.len[i];
-        ranges[tile_off[blockIdx.x] + pos] = make_ulonglong2(o, o + len);
-    }
+    if (k) ranges[t0 + pos] = make_ulonglong2(o, o + len);
+    else len = 0;
     unsigned long long btot;
     block_scan_excl(len, OpSum(), 0ull, sb, &btot);
     if (threadIdx.x == 0 && btot) atomicAdd(bytes_out, btot);

@@ -324,14 +324,14 @@ __global__ void __launch_bounds__(WJ_THREADS, FILT ? WJ_MIN_CTAS_FILT : WJ_MIN_C
             if (c) {
                 const uint32_t id = S.list[i].w;
                 atomicAdd(ent_cnt + id, (unsigned long long)c);
-                if (!ent_hit[id]) ent_hit[id] = 1;
+                ent_hit[id] = 1;   // a plain byte store: testing the flag first would stall on the load
             }
         }
         for (uint32_t i = tid; i < nrun; i += WJ_THREADS) {
             const uint32_t c = S.rcnt[i];
             if (c) {
                 atomicAdd(ent_cnt + j0 + i, (unsigned long long)c);
-                if (!ent_hit[j0 + i]) ent_hit[j0 + i] = 1;
+                ent_hit[j0 + i] = 1;
             }
         }
         if (tid == 0) {
