@@ -45,7 +45,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
-                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
+                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
                     &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
@@ -61,6 +61,9 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     {
         PhaseTimer t("engine: lines + rank space");
         build_lines();
+        // roots hit | lines matched: one allocation, so that a sharded job has ONE flag array to exchange (match_flags())
+        d_wj_hit.ensure(flag_bytes());
+        GFFX_CUDA(cudaMemsetAsync(d_wj_hit.p, 0, flag_bytes(), st));
     }
     d_small.ensure(256);
     d_warn.ensure(WARN_CAP * 4);
@@ -72,7 +75,7 @@ EngineImpl::~EngineImpl() {
     if (st) cudaStreamSynchronize(st);
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
-                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_match, &d_type_allow,
+                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
                     &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
@@ -203,7 +206,7 @@ void EngineImpl::build_join() {
     upload(d_wj_boff, bh.boff, st);
     upload(d_wj_blk, wblk, st);
     wj_n_ent = (uint32_t)bh.n_entries();
-    d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));
+    d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));   // grown to flag_bytes() once the line table is known (constructor)
     d_wj_cnt.ensure(std::max<uint32_t>(wj_n_ent, 1) * 8ull);
     d_wj_off.ensure(((uint64_t)wj_n_ent + 1) * 8);
     GFFX_CUDA(cudaStreamSynchronize(st));
@@ -607,17 +610,16 @@ void EngineImpl::ix_seal() {
     GFFX_CUDA(cudaSetDevice(dev));
     jb.sealed = true;
     if (!jb.run_filter) return;
-    d_match.ensure(std::max<uint64_t>(LA.n, 1));
     if (jb.nothing || jb.n_total == 0) {
-        GFFX_CUDA(cudaMemsetAsync(d_match.p, 0, std::max<uint64_t>(LA.n, 1), st));
+        GFFX_CUDA(cudaMemsetAsync(match_flags(), 0, std::max<uint64_t>(LA.n, 1), st));
         return;
     }
     FilterScans P{};
     jb.launches += ix_scans(&P);
     const unsigned tiles = (unsigned)((LA.n + LINE_THREADS - 1) / LINE_THREADS);
-    if (jb.mode == 0) match_lines_kernel<0><<<tiles, LINE_THREADS, 0, st>>>(LA, P, d_match.as<uint8_t>());
-    else if (jb.mode == 1) match_lines_kernel<1><<<tiles, LINE_THREADS, 0, st>>>(LA, P, d_match.as<uint8_t>());
-    else match_lines_kernel<2><<<tiles, LINE_THREADS, 0, st>>>(LA, P, d_match.as<uint8_t>());
+    if (jb.mode == 0) match_lines_kernel<0><<<tiles, LINE_THREADS, 0, st>>>(LA, P, match_flags());
+    else if (jb.mode == 1) match_lines_kernel<1><<<tiles, LINE_THREADS, 0, st>>>(LA, P, match_flags());
+    else match_lines_kernel<2><<<tiles, LINE_THREADS, 0, st>>>(LA, P, match_flags());
     jb.launches++;
 }
 
@@ -666,7 +668,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         const uint8_t* ta = d_type_allow.as<uint8_t>();
         const bool ht = jb.have_types;
         if (jb.sealed)  // the per-line match flags exist already (and may hold the other shards' matches too)
-            keep_lines_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, d_match.as<uint8_t>(), sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
+            keep_lines_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, match_flags(), sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         else if (mode == 0) eval_lines_kernel<0><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         else if (mode == 1) eval_lines_kernel<1><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         else eval_lines_kernel<2><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
@@ -878,8 +880,9 @@ bool Engine::shard_buffer(int which, uint32_t k, void** dptr, uint64_t* n_elems,
     struct B { void* p; uint64_t n; int op; };
     std::vector<B> v;
     if (!jb.nothing) {
-        v.push_back({E->d_wj_hit.p, E->wj_n_ent, RED_MAX_U8});                      // which roots were hit -> selected blocks, warn list
-        if (jb.run_filter) v.push_back({E->d_match.p, E->LA.n, RED_MAX_U8});       // which lines match some region (filter.cuh)
+        // byte flags, MAX: which roots were hit (-> selected blocks, warn list) and, behind them in the same allocation, which
+        // lines match some region (filter.cuh); the padding between the two stays 0
+        v.push_back({E->d_wj_hit.p, jb.run_filter ? E->flag_bytes() : (uint64_t)E->wj_n_ent, RED_MAX_U8});
     }
     if (k >= v.size()) return false;
     *dptr = v[k].p; *n_elems = v[k].n; *op = v[k].op;

@@ -122,7 +122,11 @@ class EngineImpl {
     uint32_t f_slots = 0;
     RankSpace FR{};
     LineArrays LA{};
-    DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_match, d_type_allow;
+    // per-line match flags of a sealed (sharded) job live behind the per-root hit flags in d_wj_hit
+    uint64_t match_off() const { return ((uint64_t)wj_n_ent + 255u) & ~255ull; }
+    uint64_t flag_bytes() const { return match_off() + std::max<uint64_t>(LA.n, 1); }
+    uint8_t* match_flags() const { return d_wj_hit.as<uint8_t>() + match_off(); }
+    DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_type_allow;
 
     // ---- window grid + partition scratch (partition.cuh) --------------------------------------
     DBuf d_win0, d_poff, d_ptot, d_pcur, d_bchr, d_bse;

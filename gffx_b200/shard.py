@@ -91,6 +91,7 @@ class Combiner:
         self.stream = torch.cuda.ExternalStream(idx.cuda_stream)
         self.bytes_exchanged = 0
         self._scratch = {}
+        self._views = {}
 
     def _buf(self, name, nbytes, device):
         import torch
@@ -117,7 +118,9 @@ class Combiner:
                     continue
                 es = np.dtype(OPS[op][0]).itemsize
                 seg = -(-n // W)
-                t = torch.as_tensor(_DevView(ptr, n * es), device=self.stream.device)
+                t = self._views.get((ptr, n * es))   # the engine's accumulators keep their addresses from job to job
+                if t is None:
+                    t = self._views[(ptr, n * es)] = torch.as_tensor(_DevView(ptr, n * es), device=self.stream.device)
                 if op == 0:      # byte flags: NCCL's own MAX
                     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
                     self.bytes_exchanged += 2 * (W - 1) * n // W
