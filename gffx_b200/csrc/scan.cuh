@@ -1,8 +1,9 @@
 // scan.cuh — device-wide scans used by the join (tile offsets), the rank-space post-passes
 // (prefix-max, suffix-min, next-set) and the order-preserving compactions.
 //
-// Scheme: reduce-then-scan in three launches (tile reduce -> scan of tile aggregates, recursive
-// above one tile of aggregates -> tile rescan with carry-in).  Warp shuffles inside a warp, one
+// Scheme: reduce-then-scan (tile reduce -> scan of tile aggregates, recursive above one tile of
+// aggregates -> tile rescan with carry-in); up to SCAN_FOLD_TILES tiles the middle step is folded
+// into the rescan (two launches).  Warp shuffles inside a warp, one
 // shared-memory pass across the warps of a CTA.  No spin-waits between CTAs, so nothing here can
 // hang a device.  Every array these run over is small next to the query stream (<= a few
 // hundred MB); the streaming kernels do their own block scans in registers/shared memory.
@@ -15,6 +16,7 @@ namespace gffx {
 constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+constexpr uint64_t SCAN_FOLD_TILES = 8192;   // up to here (16.8 M elements) the rescan kernel folds the tile totals itself
 
 struct OpSum {
     template <class T> __host__ __device__ T operator()(T a, T b) const { return a + b; }
@@ -118,9 +120,22 @@ __global__ void __launch_bounds__(1024) scan_agg_kernel(T* __restrict__ agg, uin
 
 template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE>
 __global__ void __launch_bounds__(SCAN_THREADS)
-    scan_apply_kernel(Load load, Store store, uint64_t n, Op op, T identity, const T* __restrict__ agg, const uint32_t* __restrict__ gate) {
+    scan_apply_kernel(Load load, Store store, uint64_t n, Op op, T identity, const T* __restrict__ agg, const uint32_t* __restrict__ gate,
+                      bool fold, T* __restrict__ total_out) {
     __shared__ T sm[SCAN_THREADS / 32 + 1];
     if (gate && *gate == 0) return;
+    // fold: agg holds the tiles' raw totals and this CTA combines its predecessors' itself (a few loads per thread while the
+    // tile count is small) - the single-CTA pass over the aggregates and its launch are skipped
+    T carry = identity;
+    if (fold) {
+        for (uint32_t j = threadIdx.x; j < blockIdx.x; j += SCAN_THREADS) carry = op(carry, agg[j]);
+        T ctot;
+        block_scan_excl(carry, op, identity, sm, &ctot);
+        carry = ctot;
+        __syncthreads();   // sm is used again below
+    } else {
+        carry = agg[blockIdx.x];
+    }
     // thread t owns SCAN_ITEMS consecutive elements of the scan order -> blocked arrangement
     const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
     T v[SCAN_ITEMS];
@@ -133,7 +148,8 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     }
     T tot;
     T ex = block_scan_excl(acc, op, identity, sm, &tot);
-    T run = op(agg[blockIdx.x], ex);
+    T run = op(carry, ex);
+    if (fold && total_out && blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *total_out = op(carry, tot);
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
         uint64_t j = base + k;
@@ -178,6 +194,11 @@ int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratc
     T* agg = scratch;
     scan_reduce_kernel<T, Op, Load, REVERSE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, n, op, identity, agg, gate);
     launches++;
+    if (tiles <= SCAN_FOLD_TILES) {   // two launches: the rescan folds the raw tile totals itself and writes the grand total
+        scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate,
+                                                                                                            true, total_out);
+        return launches + 1;
+    }
     if (tiles <= 1024 * 64) {
         scan_agg_kernel<T, Op><<<1, 1024, 0, st>>>(agg, (uint32_t)tiles, op, identity, gate);
         launches++;
@@ -187,7 +208,8 @@ int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratc
         launches += device_scan<T, Op, PtrLoad<T>, PtrStore<T>, false, false>(PtrLoad<T>{agg}, PtrStore<T>{agg}, tiles, op, identity,
                                                                              next, agg + tiles, st, gate);
     }
-    scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate);
+    scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate,
+                                                                                                        false, nullptr);
     launches++;
     if (total_out) {
         cudaMemcpyAsync(total_out, agg + tiles, sizeof(T), cudaMemcpyDeviceToDevice, st);
