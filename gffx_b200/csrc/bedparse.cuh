@@ -119,24 +119,14 @@ __device__ __forceinline__ bool bed_plain_u32(const uint8_t* s, uint32_t n, uint
     return true;
 }
 
-// DIALECT 0: intersect (parse_bed_file), 1: depth / coverage
+// one line [L, L + len) without its '\n': status and, for a kept line, its region.  L may point into shared or global memory
+// (the caller instantiates both, so every byte load is of a known address space)
 template <int DIALECT>
-static __global__ void __launch_bounds__(BED_THREADS)
-    bed_parse_lines_kernel(const uint8_t* __restrict__ text, uint64_t n, const uint64_t* __restrict__ line_start, uint64_t n_lines, BedNames T,
-                           uint8_t* __restrict__ status, uint32_t* __restrict__ oc, uint32_t* __restrict__ os, uint32_t* __restrict__ oe,
-                           uint32_t* __restrict__ n_flag, uint32_t* __restrict__ flag_list) {
-    const uint64_t k = (uint64_t)blockIdx.x * BED_THREADS + threadIdx.x;
-    if (k >= n_lines) return;
-    const uint64_t p = line_start[k];
-    // q: the line's '\n', or the end of the text for an unterminated last line
-    const uint64_t q = k + 1 < n_lines ? line_start[k + 1] - 1 : (text[n - 1] == 10 ? n - 1 : n);
+__device__ __forceinline__ uint8_t bed_parse_one(const uint8_t* __restrict__ L, uint32_t len, const BedNames& T, uint32_t* pc, uint32_t* ps,
+                                                 uint32_t* pe) {
     uint8_t st = BED_SKIP;
     uint32_t c = 0, s = 0, e = 0;
-    const uint8_t* L = text + p;
-    const uint32_t len = (uint32_t)min(q - p, (uint64_t)0x7FFFFFFF);
-    if (q - p > 4096) {
-        st = BED_HOST;   // a line this long is not a plain BED line
-    } else if (len != 0 && L[0] != '#') {
+    if (len != 0 && L[0] != '#') {
         bool ascii = true;
         for (uint32_t j = 0; j < len; j++) ascii = ascii && L[j] < 0x80;
         uint32_t f0[3] = {0, 0, 0}, f1[3] = {0, 0, 0};
@@ -174,6 +164,39 @@ static __global__ void __launch_bounds__(BED_THREADS)
             }
         }
     }
+    *pc = c; *ps = s; *pe = e;
+    return st;
+}
+
+constexpr uint32_t BED_STAGE = 16384;   // bytes of text a CTA stages in shared memory (256 lines of a plain BED are ~6 KB)
+
+// DIALECT 0: intersect (parse_bed_file), 1: depth / coverage.  text must be readable up to n + 16 (the staging copy is 16-byte wide).
+template <int DIALECT>
+static __global__ void __launch_bounds__(BED_THREADS)
+    bed_parse_lines_kernel(const uint8_t* __restrict__ text, uint64_t n, const uint64_t* __restrict__ line_start, uint64_t n_lines, BedNames T,
+                           uint8_t* __restrict__ status, uint32_t* __restrict__ oc, uint32_t* __restrict__ os, uint32_t* __restrict__ oe,
+                           uint32_t* __restrict__ n_flag, uint32_t* __restrict__ flag_list) {
+    __shared__ __align__(16) uint8_t buf[BED_STAGE + 16];
+    const uint64_t k0 = (uint64_t)blockIdx.x * BED_THREADS, k = k0 + threadIdx.x;
+    const uint64_t k1 = min(k0 + BED_THREADS, n_lines);
+    // the CTA's lines are one contiguous span of the text: copied once with 16-byte loads, parsed from shared memory
+    const uint64_t p_lo = line_start[k0], p_hi = k1 < n_lines ? line_start[k1] : n;
+    const uint64_t a0 = p_lo & ~15ull;
+    const bool staged = p_hi - a0 <= BED_STAGE;   // uniform
+    if (staged)
+        for (uint64_t o = (uint64_t)threadIdx.x * 16; a0 + o < p_hi; o += (uint64_t)BED_THREADS * 16)
+            *reinterpret_cast<uint4*>(buf + o) = *reinterpret_cast<const uint4*>(text + a0 + o);
+    __syncthreads();
+    if (k >= n_lines) return;
+    const uint64_t p = k == k0 ? p_lo : line_start[k];
+    // q: the line's '\n', or the end of the text for an unterminated last line
+    const uint64_t q = k + 1 < n_lines ? line_start[k + 1] - 1 : (text[n - 1] == 10 ? n - 1 : n);
+    uint8_t st;
+    uint32_t c = 0, s = 0, e = 0;
+    const uint32_t len = (uint32_t)min(q - p, (uint64_t)0x7FFFFFFF);
+    if (q - p > 4096) st = BED_HOST;   // a line this long is not a plain BED line
+    else if (staged) st = bed_parse_one<DIALECT>(buf + (p - a0), len, T, &c, &s, &e);
+    else st = bed_parse_one<DIALECT>(text + p, len, T, &c, &s, &e);
     status[k] = st;
     oc[k] = c; os[k] = s; oe[k] = e;
     if (st == BED_HOST) flag_list[atomicAdd(n_flag, 1u)] = (uint32_t)k;
