@@ -138,3 +138,32 @@ def test_index_builder_errors(gffx, tmp_path):
         gffx.build_index(str(p))
     with pytest.raises(gffx.GffxError):
         gffx.build_index(str(tmp_path / "missing.gff"))
+
+
+def test_id_dictionary_is_numbered_by_first_appearance(gffx, synth_plain_gff):
+    """The depth / coverage view numbers the ID attribute values in order of first appearance in the GFF (the order a serial
+    scan interns them in); the loader builds that dictionary on all host threads from per-line hashes."""
+    idx = gffx.TreeIndexData.load_tree_index(synth_plain_gff, device=-1)
+    seen, order = set(), []
+    with open(synth_plain_gff, "rb") as f:
+        for line in f:
+            if line.startswith(b"#"):
+                continue
+            cols = line.rstrip(b"\r\n").split(b"\t")
+            if len(cols) < 9:
+                continue
+            # `region` lines are skipped at index build: the one in front of the first root lies in no block; the later ones
+            # sit in the tail of the preceding root's block and count
+            if not seen and cols[2] == b"region":
+                continue
+            for kv in cols[8].split(b";"):
+                if kv.startswith(b"ID="):
+                    v = kv[3:]
+                    if v not in seen:
+                        seen.add(v)
+                        order.append(v)
+                    break
+    assert idx.n_ids == len(order)
+    assert len(order) < idx.n_lines   # multi-line CDS features share one ID: the dictionary really dedups
+    got = [idx.id_string(i) for i in range(idx.n_ids)]
+    assert got == order

@@ -203,3 +203,38 @@ def test_pairs_come_back_grouped_by_root_in_start_order(quirk):
     assert len(np.unique(heads, axis=0)) == len(heads)          # every root's copies are contiguous
     r2 = idx.query_features(regs, 2, False)
     assert np.array_equal(p, r2.pairs)                            # and the order is reproducible
+
+
+def test_result_summary_in_one_call_equals_the_accessors(quirk):
+    """gffx_result_get_info fills one struct with what the gffx_result_* accessors return one by one."""
+    import ctypes as C
+
+    from gffx_b200 import _lib
+
+    idx, _, _ = quirk
+    regs = mixed_regions(idx, 99, 2000)
+    keep = []
+    h = C.c_void_p()
+    arrs = [np.ascontiguousarray(a, dtype=np.uint32) for a in regs]
+    rc = _lib.lib.gffx_intersect(idx._h, arrs[0].ctypes.data, arrs[1].ctypes.data, arrs[2].ctypes.data, len(arrs[0]), 2, 0, 0, None,
+                                 _lib.F_WANT_PAIRS, C.byref(h))
+    assert rc == 0, _lib.last_error()
+    try:
+        info = _lib.ResultInfo()
+        assert _lib.lib.gffx_result_get_info(h, C.byref(info)) == 0
+        L = _lib.lib
+        assert info.n_queries == L.gffx_result_n_queries(h) == len(arrs[0])
+        assert info.n_pairs == L.gffx_result_n_pairs(h) > 0
+        assert info.n_roots == L.gffx_result_n_roots(h)
+        assert info.n_ranges == L.gffx_result_n_ranges(h) > 0
+        assert info.bytes_out == L.gffx_result_bytes_out(h)
+        assert info.n_warn == L.gffx_result_n_warn(h)
+        assert C.cast(info.pairs, C.c_void_p).value == C.cast(L.gffx_result_pairs(h), C.c_void_p).value
+        assert C.cast(info.ranges, C.c_void_p).value == C.cast(L.gffx_result_ranges(h), C.c_void_p).value
+        assert (info.pairs_device or 0) == (L.gffx_result_pairs_device(h) or 0)
+        assert info.kernel_ms == L.gffx_result_kernel_ms(h) > 0
+        assert info.launches == L.gffx_result_launches(h) > 0
+        assert [info.stage_ms[k] for k in range(12)] == [L.gffx_result_stage_ms(h, k) for k in range(12)]
+        assert _lib.lib.gffx_result_get_info(h, None) != 0
+    finally:
+        _lib.lib.gffx_result_free(h)
