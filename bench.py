@@ -172,7 +172,7 @@ def workload_config(args, idx, q):
         "regions_per_pass_per_gpu": q, "passes_per_step": len(PASSES), "region_len": REGION_LEN, "n_roots": idx.n_roots,
         "n_lines": idx.n_lines, "pairs": "materialised in HBM", "l2": "inputs larger than L2: 4 x 12 B x Q region sets rotate (no flush needed)",
         "sharding": "regions split across ranks (counter-based stream, rank r owns [r*Q,(r+1)*Q)); index replicated; N>1: the job's "
-                    "accumulators (root hit flags, line rank-space keys) are exchanged over NCCL (all-to-all + fold kernel + all-gather) "
+                    "byte flags (roots hit | lines matched, one array) are combined by one NCCL all-reduce(MAX) per pass "
                     "and every rank emits the byte ranges of the whole N*Q-region job",
     }
 
