@@ -452,8 +452,9 @@ def run_counts(args, rank, world, local_rank):
         combiner = Combiner(idx)
     fn = idx.depth if kind == 0 else idx.coverage
     stream = torch.cuda.ExternalStream(idx.cuda_stream, device=dev)
+    # copy=False: the rows stay in the job's page-locked buffers (what a caller of the C ABI reads too)
     for _ in range(args.warmup):
-        rows = fn(reads, combine=combiner)
+        fn(reads, combine=combiner, copy=False).close()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -461,9 +462,11 @@ def run_counts(args, rank, world, local_rank):
     ev0.record(stream)
     kms, launches = 0.0, 0
     for _ in range(args.steps):
-        rows = fn(reads, combine=combiner)
+        rows = fn(reads, combine=combiner, copy=False)
         kms += rows.kernel_ms
         launches += rows.launches
+        n_rows = int(rows.id_idx.shape[0])
+        rows.close()
     ev1.record(stream)
     barrier()
     t1 = time.perf_counter()
@@ -477,18 +480,20 @@ def run_counts(args, rank, world, local_rank):
     if args.e2e_steps > 0:
         host = tuple(torch.empty(Q, dtype=torch.int32, pin_memory=True) for _ in range(3))
         idx.synth_regions(20260010, Q, 150, first=rank * Q, out=host)
-        fn(host, combine=combiner)
+        fn(host, combine=combiner, copy=False).close()
         barrier()
         te0 = time.perf_counter()
         for _ in range(args.e2e_steps):
-            r2 = fn(host, combine=combiner)
+            r2 = fn(host, combine=combiner, copy=False)
+            n_rows_e2e = int(r2.id_idx.shape[0])
+            r2.close()
         torch.cuda.synchronize()
         te = torch.tensor([time.perf_counter() - te0], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e_s = float(te.item())
         e2e = {"value": world * Q * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 12 * Q,
-               "d2h_bytes_per_step": int(r2.id_idx.shape[0]) * 24, "steps": args.e2e_steps, "ms_per_step": e2e_s / args.e2e_steps * 1e3}
+               "d2h_bytes_per_step": n_rows_e2e * 24, "steps": args.e2e_steps, "ms_per_step": e2e_s / args.e2e_steps * 1e3}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -499,7 +504,6 @@ def run_counts(args, rank, world, local_rank):
     except (OSError, ValueError):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    n_rows = int(rows.id_idx.shape[0])
     # B = 12*Q + 16*L + 24*F_out per job, over the job's kernels (event-timed inside the library)
     nbytes = 12 * Q + 16 * idx.n_lines + 24 * n_rows
     ach = nbytes * args.steps / (kms * 1e-3) / 1e9 if kms > 0 else 0.0

@@ -343,9 +343,10 @@ class TreeIndexData:
             return text.value, nb.value
         return C.string_at(text.value, nb.value) if nb.value else b""
 
-    def _counts(self, kind: int, regions, batches: int = 1, combine=None):
+    def _counts(self, kind: int, regions, batches: int = 1, combine=None, copy: bool = True):
         st = C.c_void_p()
         _check(lib.gffx_counts_begin(self._h, kind, C.byref(st)))
+        done = False
         try:
             keep: list = []
             pc, ps, pe, n, f = _as_region_ptrs(regions, keep)
@@ -365,21 +366,29 @@ class TreeIndexData:
             k = nr.value
 
             def arr(p, dt):
-                return np.ctypeslib.as_array(p, shape=(k,)).copy() if k else np.zeros(0, dtype=dt)
+                if not k:
+                    return np.zeros(0, dtype=dt)
+                a = np.ctypeslib.as_array(p, shape=(k,))
+                return a.copy() if copy else a
 
             rows = CountRows(arr(pid, np.uint32), arr(pch, np.uint32), arr(pst, np.uint32), arr(pen, np.uint32), arr(pv, np.uint64),
                              lib.gffx_counts_kernel_ms(st), lib.gffx_counts_launches(st), kind, self)
+            if not copy:   # the arrays are views of the job's page-locked row buffers: the job lives until rows.close()
+                rows._st = st
+                done = True
             return rows
         finally:
-            lib.gffx_counts_free(st)
+            if not done:
+                lib.gffx_counts_free(st)
 
-    def depth(self, regions, batches: int = 1, combine=None) -> "CountRows":
-        """compute_hit_depth over all batches, src/commands/depth.rs:222-293,429-512"""
-        return self._counts(0, regions, batches, combine)
+    def depth(self, regions, batches: int = 1, combine=None, copy: bool = True) -> "CountRows":
+        """compute_hit_depth over all batches, src/commands/depth.rs:222-293,429-512.  copy=False: the row arrays are views
+        of library-owned page-locked memory, valid until CountRows.close()."""
+        return self._counts(0, regions, batches, combine, copy)
 
-    def coverage(self, regions, batches: int = 1, combine=None) -> "CountRows":
+    def coverage(self, regions, batches: int = 1, combine=None, copy: bool = True) -> "CountRows":
         """collect_by_root + finalize_compute_breadth, src/commands/coverage.rs:208-450"""
-        return self._counts(1, regions, batches, combine)
+        return self._counts(1, regions, batches, combine, copy)
 
     def id_string(self, i: int) -> bytes:
         n = C.c_uint32()
@@ -424,6 +433,20 @@ class CountRows:
     launches: int
     kind: int
     index: "TreeIndexData"
+    _st: object = None   # the C job handle while the arrays are zero-copy views (copy=False)
+
+    def close(self):
+        """release the library-owned row buffers behind zero-copy arrays (they must not be used afterwards)"""
+        if self._st is not None:
+            st, self._st = self._st, None
+            self.id_idx = self.chrom_idx = self.start = self.end = self.value = None
+            lib.gffx_counts_free(st)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def to_tsv(self, sort_rows: bool = True) -> bytes:
         """The reference's TSV (write_depth_results / write_breadth_results); rows sorted bytewise when asked,
