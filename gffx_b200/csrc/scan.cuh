@@ -136,26 +136,43 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     } else {
         carry = agg[blockIdx.x];
     }
-    // thread t owns SCAN_ITEMS consecutive elements of the scan order -> blocked arrangement
-    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)threadIdx.x * SCAN_ITEMS;
+    // striped arrangement: element k * 32 + lane of the warp's 256 -> every load and store of a warp is one contiguous run
+    // (a blocked arrangement, 64 bytes per thread, costs four times the L1 wavefronts); the price is one warp scan per k
+    // instead of one per thread, a few dozen shuffles that nothing here waits for
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint64_t wbase = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)warp * (32 * SCAN_ITEMS) + lane;
     T v[SCAN_ITEMS];
-    T acc = identity;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
-        uint64_t j = base + k;
+        const uint64_t j = wbase + 32u * k;
         v[k] = j < n ? load(REVERSE ? n - 1 - j : j) : identity;
-        acc = op(acc, v[k]);
     }
-    T tot;
-    T ex = block_scan_excl(acc, op, identity, sm, &tot);
-    T run = op(carry, ex);
+    T run = identity;   // this warp's elements before row k, combined
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const T inc = warp_scan_incl(v[k], op);
+        const T row = shfl_idx_any(inc, 31);
+        T ex = shfl_up_any(inc, 1);
+        if (lane == 0) ex = identity;
+        v[k] = op(run, INCLUSIVE ? inc : ex);   // prefix inside the warp's 256 elements
+        run = op(run, row);
+    }
+    // exclusive scan of the warps' totals
+    if (lane == 0) sm[warp] = run;
+    __syncthreads();
+    T wpre = identity, tot = identity;
+#pragma unroll
+    for (int w = 0; w < SCAN_THREADS / 32; w++) {
+        const T x = sm[w];
+        if (w < (int)warp) wpre = op(wpre, x);
+        tot = op(tot, x);
+    }
+    const T pre = op(carry, wpre);
     if (fold && total_out && blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *total_out = op(carry, tot);
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; k++) {
-        uint64_t j = base + k;
-        T inc = op(run, v[k]);
-        if (j < n) store(REVERSE ? n - 1 - j : j, INCLUSIVE ? inc : run);
-        run = inc;
+        const uint64_t j = wbase + 32u * k;
+        if (j < n) store(REVERSE ? n - 1 - j : j, op(pre, v[k]));
     }
 }
 
