@@ -661,9 +661,8 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         FilterScans P{};
         if (!jb.sealed) launches += ix_scans(&P);
         GFFX_CUDA(cudaEventRecord(ev[6], st));
-        const uint64_t n_emit_tiles = (LA.n + LINE_THREADS - 1) / LINE_THREADS;
+        const uint64_t n_emit_tiles = (LA.n + LINE_TILE - 1) / LINE_TILE;
         d_tile_count.ensure(n_emit_tiles * 4);
-        d_tile_off.ensure(n_emit_tiles * 8);
         const uint8_t* sel = d_blk_sel.as<uint8_t>();
         const uint8_t* ta = d_type_allow.as<uint8_t>();
         const bool ht = jb.have_types;
@@ -673,13 +672,10 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         else if (mode == 1) eval_lines_kernel<1><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         else eval_lines_kernel<2><<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, P, sel, ta, ht, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>());
         launches++;
-        launches += device_scan<uint64_t, OpSum, TileCountLoad, PtrStore<uint64_t>, false, false>(
-            TileCountLoad{d_tile_count.as<uint32_t>()}, PtrStore<uint64_t>{d_tile_off.as<uint64_t>()}, n_emit_tiles, OpSum(), 0ull,
-            d_scan_scratch.as<uint64_t>(), (uint64_t*)(small + 5), st);
         // the compacted list can never exceed the number of lines
         d_ranges.ensure(std::max<uint64_t>(LA.n, n_blocks) * 16);
-        emit_ranges_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, d_keep.as<uint8_t>(), d_tile_off.as<uint64_t>(),
-                                                                          d_ranges.as<ulonglong2>(), small + 4);
+        emit_ranges_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>(),
+                                                                          d_ranges.as<ulonglong2>(), small + 4, small + 5);
         launches++;
     } else {
         GFFX_CUDA(cudaEventRecord(ev[6], st));

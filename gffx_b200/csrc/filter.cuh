@@ -166,25 +166,57 @@ __device__ __forceinline__ bool line_matches(const LineCols& c, const FilterScan
 }
 
 constexpr int LINE_THREADS = 256;
+constexpr int LINE_ITEMS = 4;                            // consecutive lines per thread: 16-byte loads of the 4-byte columns
+constexpr int LINE_TILE = LINE_THREADS * LINE_ITEMS;     // lines per CTA of the decision / compaction kernels
 
-// pass 1: per-line decision -> keep flag (byte) + per-CTA count
+// four consecutive elements of a column, i a multiple of 4 (the arrays are cudaMalloc'ed: 16-byte aligned)
+__device__ __forceinline__ void load4(const uint32_t* __restrict__ a, uint64_t i, uint64_t n, uint32_t (&v)[4]) {
+    if (i + 4 <= n) {
+        const uint4 x = *reinterpret_cast<const uint4*>(a + i);
+        v[0] = x.x; v[1] = x.y; v[2] = x.z; v[3] = x.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) v[j] = i + j < n ? a[i + j] : 0u;
+    }
+}
+__device__ __forceinline__ uint32_t load4b(const uint8_t* __restrict__ a, uint64_t i, uint64_t n) {   // four bytes, byte j in bits 8j..
+    if (i + 4 <= n) return *reinterpret_cast<const uint32_t*>(a + i);
+    uint32_t w = 0;
+    for (int j = 0; j < 4; j++)
+        if (i + j < n) w |= (uint32_t)a[i + j] << (8 * j);
+    return w;
+}
+__device__ __forceinline__ void store4b(uint8_t* __restrict__ a, uint64_t i, uint64_t n, uint32_t w) {
+    if (i + 4 <= n) { *reinterpret_cast<uint32_t*>(a + i) = w; return; }
+    for (int j = 0; j < 4; j++)
+        if (i + j < n) a[i + j] = (uint8_t)(w >> (8 * j));
+}
+
+// pass 1: per-line decision -> keep flag (byte) + per-CTA count.  A thread decides 4 consecutive lines: the columns come in
+// as 16-byte loads, the scan cells they point at as four independent gathers.
 template <int MODE>
 __global__ void __launch_bounds__(LINE_THREADS)
     eval_lines_kernel(LineArrays L, FilterScans P, const uint8_t* __restrict__ blk_sel, const uint8_t* __restrict__ type_allow,
                       bool have_types, uint8_t* __restrict__ keep, uint32_t* __restrict__ tile_count) {
     __shared__ uint32_t sm[LINE_THREADS / 32 + 1];
-    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
+    const uint64_t i = ((uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x) * LINE_ITEMS;
     uint32_t k = 0;
     if (i < L.n) {
-        const uint8_t fl = L.flags[i];
-        const uint32_t blk = L.blk[i];
-        const uint32_t t = have_types ? L.type_id[i] : 0u;
-        const LineCols c = load_line_cols(L, i);
-        bool ok = (fl & 1) && blk_sel[blk];
-        if (have_types) ok = ok && t != 0xFFFFFFFFu && type_allow[t];
-        const bool mt = line_matches<MODE>(c, P);   // iS / iE are 0 (a valid slot) for a line without usable coordinates
-        k = ok && mt ? 1u : 0u;
-        keep[i] = (uint8_t)k;
+        const uint32_t fl = load4b(L.flags, i, L.n);
+        uint32_t blk[4], ty[4] = {0, 0, 0, 0}, seq[4], S[4], E[4], iS[4], iE[4];
+        load4(L.blk, i, L.n, blk);
+        if (have_types) load4(L.type_id, i, L.n, ty);
+        load4(L.iseq, i, L.n, seq); load4(L.S, i, L.n, S); load4(L.E, i, L.n, E); load4(L.iS, i, L.n, iS); load4(L.iE, i, L.n, iE);
+        uint32_t w = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (i + j >= L.n) break;   // padded entries are 0: valid indices, but not lines
+            bool ok = ((fl >> (8 * j)) & 1u) && blk_sel[blk[j]];
+            if (have_types) ok = ok && ty[j] != 0xFFFFFFFFu && type_allow[ty[j]];
+            const bool mt = line_matches<MODE>(LineCols{seq[j], S[j], E[j], iS[j], iE[j]}, P);   // iS / iE are 0 (a valid slot) without usable coordinates
+            if (ok && mt) { w |= 1u << (8 * j); k++; }
+        }
+        store4b(keep, i, L.n, w);
     }
     uint32_t tot;
     block_scan_excl(k, OpSum(), 0u, sm, &tot);
@@ -208,41 +240,74 @@ static __global__ void __launch_bounds__(LINE_THREADS)
     keep_lines_kernel(LineArrays L, const uint8_t* __restrict__ match, const uint8_t* __restrict__ blk_sel,
                       const uint8_t* __restrict__ type_allow, bool have_types, uint8_t* __restrict__ keep, uint32_t* __restrict__ tile_count) {
     __shared__ uint32_t sm[LINE_THREADS / 32 + 1];
-    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
+    const uint64_t i = ((uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x) * LINE_ITEMS;
     uint32_t k = 0;
     if (i < L.n) {
-        bool ok = match[i] && blk_sel[L.blk[i]];
-        if (ok && have_types) {
-            const uint32_t t = L.type_id[i];
-            ok = t != 0xFFFFFFFFu && type_allow[t];
+        const uint32_t mt = load4b(match, i, L.n);
+        uint32_t blk[4], ty[4] = {0, 0, 0, 0};
+        load4(L.blk, i, L.n, blk);
+        if (have_types) load4(L.type_id, i, L.n, ty);
+        uint32_t w = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (i + j >= L.n) break;
+            bool ok = ((mt >> (8 * j)) & 0xFFu) && blk_sel[blk[j]];
+            if (have_types) ok = ok && ty[j] != 0xFFFFFFFFu && type_allow[ty[j]];
+            if (ok) { w |= 1u << (8 * j); k++; }
         }
-        k = ok ? 1u : 0u;
-        keep[i] = (uint8_t)k;
+        store4b(keep, i, L.n, w);
     }
     uint32_t tot;
     block_scan_excl(k, OpSum(), 0u, sm, &tot);
     if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
 }
 
-// pass 2: order-preserving compaction of (offset, offset+len)
+// pass 2: order-preserving compaction of (offset, offset+len).  The CTA adds up its predecessors' counts itself (<= a few
+// thousand tiles of 1024 lines: a dozen loads per thread), so no scan pass runs between the two kernels; the last CTA
+// reports the number of ranges.
 static __global__ void __launch_bounds__(LINE_THREADS)
-    emit_ranges_kernel(LineArrays L, const uint8_t* __restrict__ keep, const uint64_t* __restrict__ tile_off,
-                       ulonglong2* __restrict__ ranges, unsigned long long* __restrict__ bytes_out) {
-    __shared__ uint32_t sm[LINE_THREADS / 32 + 1];
+    emit_ranges_kernel(LineArrays L, const uint8_t* __restrict__ keep, const uint32_t* __restrict__ tile_count,
+                       ulonglong2* __restrict__ ranges, unsigned long long* __restrict__ bytes_out, unsigned long long* __restrict__ n_out) {
     __shared__ unsigned long long sb[LINE_THREADS / 32 + 1];
-    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
-    // offset and length are loaded beside the flag, not behind it: one round of loads, then the scan
-    const uint32_t k = (i < L.n && keep[i]) ? 1u : 0u;
-    const uint64_t o = i < L.n ? L.off[i] : 0ull;
-    unsigned long long len = i < L.n ? L.len[i] : 0u;
-    const uint64_t t0 = tile_off[blockIdx.x];
-    uint32_t tot;
-    const uint32_t pos = block_scan_excl(k, OpSum(), 0u, sm, &tot);
-    if (k) ranges[t0 + pos] = make_ulonglong2(o, o + len);
-    else len = 0;
+    const uint64_t i = ((uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x) * LINE_ITEMS;
+    // offset, length and flag of the thread's 4 lines: loaded side by side, before anything is decided
+    uint32_t kw = 0, len[4] = {0, 0, 0, 0};
+    unsigned long long off[4] = {0, 0, 0, 0};
+    if (i < L.n) {
+        kw = load4b(keep, i, L.n);
+        load4(L.len, i, L.n, len);
+        if (i + 4 <= L.n) {
+            const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(L.off + i), b = *reinterpret_cast<const ulonglong2*>(L.off + i + 2);
+            off[0] = a.x; off[1] = a.y; off[2] = b.x; off[3] = b.y;
+        } else {
+            for (int j = 0; j < 4; j++)
+                if (i + j < L.n) off[j] = L.off[i + j];
+        }
+    }
+    unsigned long long before = 0;   // ranges of the tiles in front of this one
+    for (uint32_t t = threadIdx.x; t < blockIdx.x; t += LINE_THREADS) before += tile_count[t];
+    // one block scan over (count, bytes) packed per thread: count < 2^11 per CTA, bytes < 2^53
+    uint32_t k = 0;
+    unsigned long long bytes = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        if ((kw >> (8 * j)) & 0xFFu) { k++; bytes += len[j]; }
+    unsigned long long tb;
+    block_scan_excl(before, OpSum(), 0ull, sb, &tb);
+    const unsigned long long t0 = tb;
+    __syncthreads();
+    unsigned long long tot;
+    unsigned long long pos = t0 + block_scan_excl((unsigned long long)k, OpSum(), 0ull, sb, &tot);
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        if ((kw >> (8 * j)) & 0xFFu) ranges[pos++] = make_ulonglong2(off[j], off[j] + len[j]);
     unsigned long long btot;
-    block_scan_excl(len, OpSum(), 0ull, sb, &btot);
-    if (threadIdx.x == 0 && btot) atomicAdd(bytes_out, btot);
+    block_scan_excl(bytes, OpSum(), 0ull, sb, &btot);
+    if (threadIdx.x == 0) {
+        if (btot) atomicAdd(bytes_out, btot);
+        if (blockIdx.x == gridDim.x - 1) *n_out = t0 + tot;
+    }
 }
 
 // number of selected blocks with a usable start (what merge_blocks_kernel reports as out_counts[1]) when no
