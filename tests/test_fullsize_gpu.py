@@ -118,3 +118,35 @@ def test_sample_of_the_full_stream_matches_the_oracle_on_the_full_index(full):
             w_ranges, w_pairs, _ = o.intersect(regs, mode, invert, False, None)
             assert w_pairs == r.n_pairs
             assert np.array_equal(r.ranges, w_ranges)
+
+
+def _by_id(rows):
+    return dict(zip(rows.id_idx.tolist(), rows.value.tolist()))
+
+
+def test_depth_adds_over_read_chunks_and_coverage_is_idempotent(full):
+    """depth is a sum over the reads (linearity), breadth a union (reading the same reads twice changes nothing); a job fed in
+    batches equals the job fed at once — 10 M 150-base reads against the full index."""
+    import torch
+
+    idx, _, _ = full
+    reads = idx.synth_regions_device(20260010, Q, 150, device=torch.device("cuda", 0))
+    h = Q // 2
+    lo = tuple(t[:h].contiguous() for t in reads)
+    hi = tuple(t[h:].contiguous() for t in reads)
+    whole, a, b = idx.depth(reads), idx.depth(lo), idx.depth(hi)
+    dw, da, db = _by_id(whole), _by_id(a), _by_id(b)
+    assert len(dw) > 100000 and sum(dw.values()) > Q // 2
+    assert set(dw) == set(da) | set(db)
+    assert all(dw[k] == da.get(k, 0) + db.get(k, 0) for k in dw)
+    batched = idx.depth(reads, batches=4)
+    for f in ("id_idx", "chrom_idx", "start", "end", "value"):
+        assert np.array_equal(getattr(batched, f), getattr(whole, f))
+    cov = idx.coverage(reads)
+    twice = idx.coverage(tuple(torch.cat([t, t]) for t in reads))
+    for f in ("id_idx", "chrom_idx", "start", "end", "value"):
+        assert np.array_equal(getattr(cov, f), getattr(twice, f))
+    length = np.maximum(cov.end.astype(np.int64) - cov.start.astype(np.int64), 0)
+    assert np.all(cov.value.astype(np.int64) <= length)
+    ca, cw = _by_id(idx.coverage(lo)), _by_id(cov)
+    assert all(ca[k] <= cw.get(k, 0) for k in ca)   # more reads never cover less
