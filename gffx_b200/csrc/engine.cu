@@ -674,7 +674,17 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         launches++;
         // the compacted list can never exceed the number of lines
         d_ranges.ensure(std::max<uint64_t>(LA.n, n_blocks) * 16);
-        emit_ranges_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>(),
+        const unsigned long long* tile_off = nullptr;
+        static const bool force_scan = getenv("GFFX_EMIT_SCAN") != nullptr;   // test hook for the large-table path
+        if (n_emit_tiles > LINE_FOLD_TILES || force_scan) {   // a very large line table: offsets by a scan pass instead
+            d_tile_off.ensure(n_emit_tiles * 8);
+            d_scan_scratch.ensure(scan_scratch_elems(n_emit_tiles) * 8);
+            launches += device_scan<uint64_t, OpSum, TileCountLoad, PtrStore<uint64_t>, false, false>(
+                TileCountLoad{d_tile_count.as<uint32_t>()}, PtrStore<uint64_t>{d_tile_off.as<uint64_t>()}, n_emit_tiles, OpSum(), 0ull,
+                d_scan_scratch.as<uint64_t>(), nullptr, st);
+            tile_off = d_tile_off.as<unsigned long long>();
+        }
+        emit_ranges_kernel<<<(unsigned)n_emit_tiles, LINE_THREADS, 0, st>>>(LA, d_keep.as<uint8_t>(), d_tile_count.as<uint32_t>(), tile_off,
                                                                           d_ranges.as<ulonglong2>(), small + 4, small + 5);
         launches++;
     } else {

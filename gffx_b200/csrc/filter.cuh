@@ -168,6 +168,7 @@ __device__ __forceinline__ bool line_matches(const LineCols& c, const FilterScan
 constexpr int LINE_THREADS = 256;
 constexpr int LINE_ITEMS = 4;                            // consecutive lines per thread: 16-byte loads of the 4-byte columns
 constexpr int LINE_TILE = LINE_THREADS * LINE_ITEMS;     // lines per CTA of the decision / compaction kernels
+constexpr uint64_t LINE_FOLD_TILES = 16384;              // up to 16.8 M lines the compaction CTAs add up the tile counts themselves
 
 // four consecutive elements of a column, i a multiple of 4 (the arrays are cudaMalloc'ed: 16-byte aligned)
 __device__ __forceinline__ void load4(const uint32_t* __restrict__ a, uint64_t i, uint64_t n, uint32_t (&v)[4]) {
@@ -267,7 +268,8 @@ static __global__ void __launch_bounds__(LINE_THREADS)
 // reports the number of ranges.
 static __global__ void __launch_bounds__(LINE_THREADS)
     emit_ranges_kernel(LineArrays L, const uint8_t* __restrict__ keep, const uint32_t* __restrict__ tile_count,
-                       ulonglong2* __restrict__ ranges, unsigned long long* __restrict__ bytes_out, unsigned long long* __restrict__ n_out) {
+                       const unsigned long long* __restrict__ tile_off, ulonglong2* __restrict__ ranges, unsigned long long* __restrict__ bytes_out,
+                       unsigned long long* __restrict__ n_out) {
     __shared__ unsigned long long sb[LINE_THREADS / 32 + 1];
     const uint64_t i = ((uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x) * LINE_ITEMS;
     // offset, length and flag of the thread's 4 lines: loaded side by side, before anything is decided
@@ -284,8 +286,11 @@ static __global__ void __launch_bounds__(LINE_THREADS)
                 if (i + j < L.n) off[j] = L.off[i + j];
         }
     }
-    unsigned long long before = 0;   // ranges of the tiles in front of this one
-    for (uint32_t t = threadIdx.x; t < blockIdx.x; t += LINE_THREADS) before += tile_count[t];
+    // ranges of the tiles in front of this one: added up here, or (tile_off != nullptr: a line table of > LINE_FOLD_TILES tiles,
+    // where adding up would be quadratic) taken from a scan the host ran in between
+    unsigned long long before = 0;
+    if (tile_off) before = threadIdx.x == 0 ? tile_off[blockIdx.x] : 0ull;
+    else for (uint32_t t = threadIdx.x; t < blockIdx.x; t += LINE_THREADS) before += tile_count[t];
     // one block scan over (count, bytes) packed per thread: count < 2^11 per CTA, bytes < 2^53
     uint32_t k = 0;
     unsigned long long bytes = 0;

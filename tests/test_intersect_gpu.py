@@ -238,3 +238,31 @@ def test_result_summary_in_one_call_equals_the_accessors(quirk):
         assert _lib.lib.gffx_result_get_info(h, None) != 0
     finally:
         _lib.lib.gffx_result_free(h)
+
+
+def test_compaction_offsets_by_scan_for_very_large_line_tables(gffx, synth_quirk_gff):
+    """Past 16.8 M lines the compaction kernel takes its tile offsets from a scan pass instead of adding up the tile counts
+    itself; GFFX_EMIT_SCAN forces that path on a small table (read once per process: run in a child).  Same ranges."""
+    import subprocess
+    import sys
+
+    code = (
+        "import os, sys, numpy as np\n"
+        "sys.path.insert(0, os.getcwd())\n"
+        "import gffx_b200 as g\n"
+        "from tests._oracle import Oracle\n"
+        "from tests.test_intersect_gpu import mixed_regions\n"
+        f"gff = {synth_quirk_gff!r}\n"
+        "idx = g.TreeIndexData.load_tree_index(gff, device=0)\n"
+        "regs = mixed_regions(idx, 31, 3000)\n"
+        "with Oracle(gff) as o:\n"
+        "    for mode, inv in [(2, False), (0, False), (1, True)]:\n"
+        "        r = idx.intersect(regs, mode, inv, False, None)\n"
+        "        want, n_pairs, _ = o.intersect(regs, mode, inv, False, None)\n"
+        "        assert r.n_pairs == n_pairs and np.array_equal(r.ranges, want), (mode, inv)\n"
+        "print('ok')\n"
+    )
+    env = dict(os.environ, GFFX_EMIT_SCAN="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300,
+                         cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stderr[-2000:]
