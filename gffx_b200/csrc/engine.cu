@@ -616,7 +616,7 @@ void EngineImpl::ix_seal() {
     }
     FilterScans P{};
     jb.launches += ix_scans(&P);
-    const unsigned tiles = (unsigned)((LA.n + LINE_THREADS - 1) / LINE_THREADS);
+    const unsigned tiles = (unsigned)((LA.n + LINE_TILE - 1) / LINE_TILE);
     if (jb.mode == 0) match_lines_kernel<0><<<tiles, LINE_THREADS, 0, st>>>(LA, P, match_flags());
     else if (jb.mode == 1) match_lines_kernel<1><<<tiles, LINE_THREADS, 0, st>>>(LA, P, match_flags());
     else match_lines_kernel<2><<<tiles, LINE_THREADS, 0, st>>>(LA, P, match_flags());

@@ -136,9 +136,6 @@ struct FilterScans {
 struct LineCols {
     uint32_t seq, S, E, iS, iE;
 };
-__device__ __forceinline__ LineCols load_line_cols(const LineArrays& L, uint64_t i) {
-    return LineCols{L.iseq[i], L.S[i], L.E[i], L.iS[i], L.iE[i]};
-}
 
 template <int MODE>
 __device__ __forceinline__ bool line_matches(const LineCols& c, const FilterScans& P) {
@@ -229,12 +226,19 @@ __global__ void __launch_bounds__(LINE_THREADS)
 // byte flags are MAX-reduced across the shards, and keep_lines applies the block selection and the type filter.
 template <int MODE>
 __global__ void __launch_bounds__(LINE_THREADS) match_lines_kernel(LineArrays L, FilterScans P, uint8_t* __restrict__ match) {
-    const uint64_t i = (uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x;
-    if (i < L.n) {
-        const uint8_t fl = L.flags[i];
-        const LineCols c = load_line_cols(L, i);
-        match[i] = ((fl & 1) && line_matches<MODE>(c, P)) ? 1 : 0;
+    const uint64_t i = ((uint64_t)blockIdx.x * LINE_THREADS + threadIdx.x) * LINE_ITEMS;
+    if (i >= L.n) return;
+    const uint32_t fl = load4b(L.flags, i, L.n);
+    uint32_t seq[4], S[4], E[4], iS[4], iE[4];
+    load4(L.iseq, i, L.n, seq); load4(L.S, i, L.n, S); load4(L.E, i, L.n, E); load4(L.iS, i, L.n, iS); load4(L.iE, i, L.n, iE);
+    uint32_t w = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        if (i + j >= L.n) break;
+        const bool mt = line_matches<MODE>(LineCols{seq[j], S[j], E[j], iS[j], iE[j]}, P);
+        if (((fl >> (8 * j)) & 1u) && mt) w |= 1u << (8 * j);
     }
+    store4b(match, i, L.n, w);
 }
 
 static __global__ void __launch_bounds__(LINE_THREADS)
