@@ -70,7 +70,10 @@ __device__ __forceinline__ uint32_t window_of_s(const uint32_t* s_win0, uint32_t
     return w0 + (b < nw ? b : nw - 1);
 }
 
-constexpr int PART_COUNT_TILES = 4;   // tiles per CTA of the count pass: fewer global atomics on the window totals
+#ifndef GFFX_PART_COUNT_TILES
+#define GFFX_PART_COUNT_TILES 2
+#endif
+constexpr int PART_COUNT_TILES = GFFX_PART_COUNT_TILES;   // tiles per CTA of the count pass: fewer global atomics on the window totals
 
 static __global__ void __launch_bounds__(PART_THREADS)
     part_count_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, uint32_t n, uint32_t* __restrict__ tot) {
