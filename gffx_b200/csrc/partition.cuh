@@ -32,7 +32,7 @@
 
 namespace gffx {
 
-constexpr int PART_THREADS = 512;           // 3 CTAs of 70 KB per SM: 512 threads each keep 1536 threads in flight
+constexpr int PART_THREADS = 512;           // the scatter kernel runs 2 CTAs of 61 KB shared memory per SM (51 registers per thread)
 constexpr int PART_TILE = 4096;             // regions per CTA
 constexpr int PART_UNROLL = 4;              // independent loads in flight per thread
 constexpr uint32_t PART_MAX_WINDOWS = 511;  // + 1 bucket for regions whose sequence number is out of range
