@@ -170,7 +170,11 @@ def workload_config(args, idx, q):
         "workload": f"intersect --bed: synthetic human-like GFF3 ({args.genes} genes, {idx.n_lines} lines, seed {GFF_SEED}) x {q} "
                     f"20 kb BED regions per pass per GPU; step = overlap | --contained | --contains-region | --contained --invert",
         "regions_per_pass_per_gpu": q, "passes_per_step": len(PASSES), "region_len": REGION_LEN, "n_roots": idx.n_roots,
-        "n_lines": idx.n_lines, "pairs": "materialised in HBM", "l2": "inputs larger than L2: 4 x 12 B x Q region sets rotate (no flush needed)",
+        "n_lines": idx.n_lines, "pairs": "materialised in HBM",
+        "timing": "value / ms_per_step: K steps between two CUDA events on the engine's stream, calls without per-stage events; "
+                  "roofline / per_pass: the same K steps repeated with GFFX_F_STAGE_TIMES (per-stage CUDA events inside every call, "
+                  "~40 us per call; roofline.staged_run_ms_per_step is that run's step time)",
+        "l2": "inputs larger than L2: 4 x 12 B x Q region sets rotate (no flush needed)",
         "sharding": "regions split across ranks (counter-based stream, rank r owns [r*Q,(r+1)*Q)); index replicated; N>1: the job's "
                     "byte flags (roots hit | lines matched, one array) are combined by one NCCL all-reduce(MAX) per pass "
                     "and every rank emits the byte ranges of the whole N*Q-region job",
@@ -261,14 +265,14 @@ def run_gpu(args, rank, world, local_rank):
     # ---- device-resident arm: K steps between two events on the engine's stream --------------------
     for _ in range(args.warmup):
         step(dev_sets, F_DEV)
-    acc = {}
+    tally = {}   # pairs / ranges / launches of the timed steps (no per-stage events inside them: what a caller of the ABI runs)
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record(stream)
     for _ in range(args.steps):
-        step(dev_sets, F_DEV, acc)
+        step(dev_sets, F_DEV, tally)
     ev1.record(stream)
     barrier()
     t1 = time.perf_counter()
@@ -277,6 +281,16 @@ def run_gpu(args, rank, world, local_rank):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
+    # the same K steps once more with GFFX_F_STAGE_TIMES: the per-stage CUDA events behind `roofline` (a dozen events and
+    # their read-back cost ~40 us per call, which is why the timed steps above run without them)
+    acc = {}
+    evs0, evs1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    evs0.record(stream)
+    for _ in range(args.steps):
+        step(dev_sets, F_DEV | _lib.F_STAGE_TIMES, acc)
+    evs1.record(stream)
+    torch.cuda.synchronize()
+    ms_staged = evs0.elapsed_time(evs1)
 
     # ---- end-to-end arm: the same calls with pinned HOST inputs and the byte ranges read back -------
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
@@ -293,7 +307,7 @@ def run_gpu(args, rank, world, local_rank):
     e2e_s = float(te.item())
 
     # ---- totals over ranks --------------------------------------------------------------------------
-    tot = torch.tensor([sum(a["pairs"] for a in acc.values()), sum(a["launches"] for a in acc.values()),
+    tot = torch.tensor([sum(a["pairs"] for a in tally.values()), sum(a["launches"] for a in tally.values()),
                         sum(a["ranges"] for a in acc_e.values())], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
@@ -338,6 +352,7 @@ def run_gpu(args, rank, world, local_rank):
     pass_bytes = sum(k["bytes"] for k in per_kernel.values())
     pass_ms = sum(a["kernel_ms"] for a in acc.values())
     if pass_ms > 0:
+        roofline["staged_run_ms_per_step"] = ms_staged / args.steps
         roofline["whole_pass"] = {"algorithmic_bytes_per_step": pass_bytes / args.steps, "ms_per_step": pass_ms / args.steps,
                                   "achieved": pass_bytes / (pass_ms * 1e-3) / 1e9, "frac": pass_bytes / (pass_ms * 1e-3) / 1e9 / peak}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
@@ -398,7 +413,8 @@ def run_gpu(args, rank, world, local_rank):
         "data": "synthetic", "config": workload_config(args, idx, Q),
         "pairs_per_sec": pairs_total / (ms_total * 1e-3), "pairs_per_step": pairs_total / args.steps,
         "per_pass": {n: {"ms": a["kernel_ms"] / a["calls"], "pairs": a["pairs"] // a["calls"], "ranges": a["ranges"] // a["calls"],
-                         "roots": a["roots"] // a["calls"], "launches": a["launches"] // a["calls"]} for n, a in acc.items()},
+                         "roots": a["roots"] // a["calls"], "launches": a["launches"] // a["calls"],
+                         "ms_without_stage_events": tally[n]["kernel_ms"] / tally[n]["calls"]} for n, a in acc.items()},
         "roofline": roofline, "clocks": clocks,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "ms_per_step": e2e_s / e2e_steps * 1e3, "api": "gffx_intersect (C ABI) with pinned host region arrays; byte ranges copied back"},

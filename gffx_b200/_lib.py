@@ -159,6 +159,7 @@ F_DEVICE_INPUT = 1
 F_WANT_PAIRS = 2
 F_NO_HOST_COPY = 4
 F_PAIRS_ON_DEVICE = 8
+F_STAGE_TIMES = 16
 
 
 def last_error() -> str:

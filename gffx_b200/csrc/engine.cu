@@ -484,6 +484,7 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
     jb.want_pairs_host = flags & 2u;
     jb.pairs_dev = (flags & 8u) || jb.want_pairs_host;
     jb.no_host = flags & 4u;
+    jb.stage_events = flags & 16u;
     jb.match_only = !entire_group || types_csv != nullptr;  // intersect.rs:619
     jb.nothing = (mode == 2 && invert) || wj_n_ent == 0;    // -I with overlap selects nothing (intersect.rs:161)
     jb.run_filter = !jb.nothing && !join_only && jb.match_only && LA.n > 0;
@@ -540,7 +541,7 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
     if (n == 0) return;
     if (jb.n_total + n >= (1ull << 40)) throw Err(E_ARG, "too many regions in one job");
     const uint32_t slot = (uint32_t)jb.chunks.size();
-    const bool timed = 4 * (size_t)slot + 3 < ev_chunk.size();
+    const bool timed = jb.stage_events && 4 * (size_t)slot + 3 < ev_chunk.size();
     IxChunk ck;
     ck.n = n;
     ck.off = jb.retained ? jb.n_total : 0;
@@ -636,7 +637,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     uint32_t launches = jb.launches;
     unsigned long long* small = d_small.as<unsigned long long>();  // [0] n_pairs [1..3] merge counts [4] bytes_out [5] n_emit (u64); u32 view: [12] err [13] n_warn
     uint32_t* small32 = d_small.as<uint32_t>();
-    GFFX_CUDA(cudaEventRecord(ev[3], st));
+    if (jb.stage_events) GFFX_CUDA(cudaEventRecord(ev[3], st));
 
     // ---- root -> block selection, merged ranges (-e) --------------------------------------------
     if (n_blocks) GFFX_CUDA(cudaMemsetAsync(d_blk_sel.p, 0, n_blocks, st));
@@ -654,13 +655,13 @@ void EngineImpl::ix_finish(IntersectResult* out) {
             launches++;
         }
     }
-    GFFX_CUDA(cudaEventRecord(ev[4], st));
+    if (jb.stage_events) GFFX_CUDA(cudaEventRecord(ev[4], st));
 
     // ---- line filter: rank-space scans, per-line decision, ordered compaction --------------------
     if (jb.run_filter && !nothing) {
         FilterScans P{};
         if (!jb.sealed) launches += ix_scans(&P);
-        GFFX_CUDA(cudaEventRecord(ev[6], st));
+        if (jb.stage_events) GFFX_CUDA(cudaEventRecord(ev[6], st));
         const uint64_t n_emit_tiles = (LA.n + LINE_TILE - 1) / LINE_TILE;
         d_tile_count.ensure(n_emit_tiles * 4);
         const uint8_t* sel = d_blk_sel.as<uint8_t>();
@@ -688,12 +689,12 @@ void EngineImpl::ix_finish(IntersectResult* out) {
                                                                           d_ranges.as<ulonglong2>(), small + 4, small + 5);
         launches++;
     } else {
-        GFFX_CUDA(cudaEventRecord(ev[6], st));
+        if (jb.stage_events) GFFX_CUDA(cudaEventRecord(ev[6], st));
     }
-    GFFX_CUDA(cudaEventRecord(ev[7], st));
+    if (jb.stage_events) GFFX_CUDA(cudaEventRecord(ev[7], st));
 
     // ---- pairs: the run-length expansion of the per-root hit counters (K1b) ----------------------
-    GFFX_CUDA(cudaEventRecord(ev[8], st));
+    if (jb.stage_events) GFFX_CUDA(cudaEventRecord(ev[8], st));
     if (jb.pairs_dev && !nothing && jb.n_total) launches += expand_pairs(jb.pair_cap);
     GFFX_CUDA(cudaEventRecord(ev[9], st));
 
@@ -741,7 +742,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     GFFX_CUDA(cudaStreamSynchronize(st));
     // per-stage device time: the batches' partition / join / scatter intervals add up; the rest is measured once
     float ms;
-    for (size_t k = 0; k < jb.chunks.size() && 4 * k + 3 < ev_chunk.size() && !jb.nothing; k++) {
+    for (size_t k = 0; jb.stage_events && k < jb.chunks.size() && 4 * k + 3 < ev_chunk.size() && !jb.nothing; k++) {
         GFFX_CUDA(cudaEventElapsedTime(&ms, ev_chunk[4 * k], ev_chunk[4 * k + 1]));
         out->stage_ms[8] += ms;
         GFFX_CUDA(cudaEventElapsedTime(&ms, ev_chunk[4 * k + 1], ev_chunk[4 * k + 2]));
@@ -749,6 +750,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         GFFX_CUDA(cudaEventElapsedTime(&ms, ev_chunk[4 * k + 2], ev_chunk[4 * k + 3]));
         out->stage_ms[4] += ms;
     }
+    if (jb.stage_events) {
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[8], ev[9]));
     out->stage_ms[7] = ms;  // offsets scan + pair expansion
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[3], ev[4]));
@@ -757,6 +759,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     out->stage_ms[5] = ms;
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[6], ev[7]));
     out->stage_ms[6] = ms;
+    }
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[9]));
     out->kernel_ms = ms;
     out->launches = launches;

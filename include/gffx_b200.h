@@ -40,7 +40,8 @@ enum {
     GFFX_F_DEVICE_INPUT = 1u << 0, /* chr/start/end are device pointers on the handle's GPU (HBM-resident queries) */
     GFFX_F_WANT_PAIRS = 1u << 1,   /* materialise the (root_fid,start,end) pairs and copy them to the host         */
     GFFX_F_NO_HOST_COPY = 1u << 2, /* leave pairs / ranges on the device (bench: kernel-only timing)               */
-    GFFX_F_PAIRS_ON_DEVICE = 1u << 3 /* materialise pairs in HBM but do not copy them to the host                  */
+    GFFX_F_PAIRS_ON_DEVICE = 1u << 3, /* materialise pairs in HBM but do not copy them to the host                 */
+    GFFX_F_STAGE_TIMES = 1u << 4   /* fill gffx_result_stage_ms: a dozen CUDA events inside the call, ~40 us of it  */
 };
 
 typedef struct gffx_index gffx_index;     /* device-resident index: TreeIndexData + GofMap + GFF line table */
@@ -161,7 +162,7 @@ const uint32_t* gffx_result_warn_fids(const gffx_result* r);
 /* device time of the call's kernels in ms (CUDA events on the engine's stream) and launch count */
 double gffx_result_kernel_ms(const gffx_result* r);
 uint32_t gffx_result_launches(const gffx_result* r);
-/* per-stage device ms: 0 root join (hits per root) with the region scatter onto the line rank space fused in,
+/* per-stage device ms (all 0 unless the call carried GFFX_F_STAGE_TIMES; gffx_result_kernel_ms is always there): 0 root join (hits per root) with the region scatter onto the line rank space fused in,
  * 3 root/block select + merge, 4 (unused since the scatter rides on stage 0), 5 rank scans, 6 line filter + compaction,
  * 7 pair offsets scan + pair expansion, 8 the window partition pass (totals + offsets + scatter);
  * stages that did not run report 0 */

@@ -8,7 +8,7 @@ from bench import ensure_workload, workload_dir
 gff = ensure_workload(60000, g.build_index)
 idx = g.TreeIndexData.load_tree_index(gff, device=0)
 dev = torch.device("cuda", 0)
-F = _lib.F_PAIRS_ON_DEVICE | _lib.F_NO_HOST_COPY
+F = _lib.F_PAIRS_ON_DEVICE | _lib.F_NO_HOST_COPY | (_lib.F_STAGE_TIMES if os.environ.get("STAGES") else 0)
 for n in (1000, 10_000_000):
     regs = idx.synth_regions_device(5, n, 20000, device=dev)
     for _ in range(5):

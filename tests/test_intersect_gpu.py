@@ -217,7 +217,7 @@ def test_result_summary_in_one_call_equals_the_accessors(quirk):
     h = C.c_void_p()
     arrs = [np.ascontiguousarray(a, dtype=np.uint32) for a in regs]
     rc = _lib.lib.gffx_intersect(idx._h, arrs[0].ctypes.data, arrs[1].ctypes.data, arrs[2].ctypes.data, len(arrs[0]), 2, 0, 0, None,
-                                 _lib.F_WANT_PAIRS, C.byref(h))
+                                 _lib.F_WANT_PAIRS | _lib.F_STAGE_TIMES, C.byref(h))
     assert rc == 0, _lib.last_error()
     try:
         info = _lib.ResultInfo()
@@ -235,6 +235,9 @@ def test_result_summary_in_one_call_equals_the_accessors(quirk):
         assert info.kernel_ms == L.gffx_result_kernel_ms(h) > 0
         assert info.launches == L.gffx_result_launches(h) > 0
         assert [info.stage_ms[k] for k in range(12)] == [L.gffx_result_stage_ms(h, k) for k in range(12)]
+        assert info.stage_ms[0] > 0 and info.stage_ms[8] > 0   # GFFX_F_STAGE_TIMES was asked for
+        plain = idx.intersect(regs, 2, False, False, None)
+        assert plain.kernel_ms > 0 and not any(plain.stage_ms)   # without the flag only the call's whole span is timed
         assert _lib.lib.gffx_result_get_info(h, None) != 0
     finally:
         _lib.lib.gffx_result_free(h)
