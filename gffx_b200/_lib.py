@@ -148,6 +148,8 @@ SIGNATURES = {
     "gffx_depth_run": (C.c_int, C.POINTER(CountsArgs)),
     "gffx_coverage_run": (C.c_int, C.POINTER(CountsArgs)),
     "gffx_synth_gff": (C.c_int, C.c_char_p, C.c_uint64, C.c_uint32, C.c_int, u64p),
+    "gffx_synth_gff_scaffolds": (C.c_int, C.c_char_p, C.c_uint64, C.c_uint32, C.c_int, C.c_uint32, u64p),
+    "gffx_index_vseq": (C.c_int, vp, C.c_uint32, u32p, u32p, u32p, u32p),
     "gffx_synth_regions_host": (C.c_int, vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, vp, vp, vp),
     "gffx_synth_regions_device": (C.c_int, vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, vp, vp, vp),
 }

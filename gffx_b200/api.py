@@ -198,6 +198,12 @@ class TreeIndexData:
         return {n: lib.gffx_index_seq_num(self._h, n.encode()) for n in self.num_to_seqid}
 
     n_seqs = property(lambda self: lib.gffx_index_n_seqs(self._h))
+
+    def vseq(self, seq: int):
+        """(virtual sequence, base, clamp, number of virtual sequences) of sequence `seq` (gffx_index_vseq)"""
+        v, b, c, n = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _check(lib.gffx_index_vseq(self._h, int(seq), C.byref(v), C.byref(b), C.byref(c), C.byref(n)))
+        return v.value, b.value, c.value, n.value
     n_roots = property(lambda self: lib.gffx_index_n_roots(self._h))
     n_blocks = property(lambda self: lib.gffx_index_n_blocks(self._h))
     n_lines = property(lambda self: lib.gffx_index_n_lines(self._h))
@@ -473,9 +479,13 @@ def build_index(gff_path: str, attribute: str = "gene_name", skip_types: Optiona
     _check(lib.gffx_index_build(str(gff_path).encode(), attribute.encode(), skip_types.encode() if skip_types is not None else None))
 
 
-def synth_gff(path: str, seed: int = 20260001, n_genes: int = 60000, quirks: bool = False) -> int:
+def synth_gff(path: str, seed: int = 20260001, n_genes: int = 60000, quirks: bool = False, n_scaffolds: int = 0) -> int:
+    """human-like synthetic GFF3 (24 chromosomes); n_scaffolds > 0 appends that many small unplaced scaffolds"""
     n = C.c_uint64()
-    _check(lib.gffx_synth_gff(str(path).encode(), seed, n_genes, int(quirks), C.byref(n)))
+    if n_scaffolds:
+        _check(lib.gffx_synth_gff_scaffolds(str(path).encode(), seed, n_genes, int(quirks), int(n_scaffolds), C.byref(n)))
+    else:
+        _check(lib.gffx_synth_gff(str(path).encode(), seed, n_genes, int(quirks), C.byref(n)))
     return n.value
 
 

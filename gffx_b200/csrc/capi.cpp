@@ -471,6 +471,24 @@ int gffx_synth_gff(const char* path, uint64_t seed, uint32_t n_genes, int quirks
         if (n_lines) *n_lines = n;
     });
 }
+int gffx_synth_gff_scaffolds(const char* path, uint64_t seed, uint32_t n_genes, int quirks, uint32_t n_scaffolds, uint64_t* n_lines) {
+    return guard([&] {
+        need(path, "path");
+        uint64_t n = synth_gff_file(path, seed, n_genes, quirks != 0, n_scaffolds);
+        if (n_lines) *n_lines = n;
+    });
+}
+int gffx_index_vseq(const gffx_index* idx, uint32_t seq, uint32_t* vseq, uint32_t* base, uint32_t* clamp, uint32_t* n_vseqs) {
+    return guard([&] {
+        need(idx, "idx");
+        const VSeqMap& V = idx->host().vmap;
+        if (seq >= V.seq.size()) throw Err(E_ARG, "sequence number out of range");
+        if (vseq) *vseq = V.seq[seq].vseq;
+        if (base) *base = V.seq[seq].base;
+        if (clamp) *clamp = V.seq[seq].clamp;
+        if (n_vseqs) *n_vseqs = (uint32_t)V.n_vseqs();
+    });
+}
 int gffx_synth_regions_host(const gffx_index* idx, uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* chr,
                             uint32_t* start, uint32_t* end) {
     return guard([&] {

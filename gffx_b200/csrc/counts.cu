@@ -11,7 +11,7 @@ struct CountsState {
     bool built = false;
     CountsIndexHost host;  // scalars are read after the upload; the big vectors are released
     DBuf d_rank, d_cov, d_X, d_dir;
-    DBuf d_u_space, d_u_chrom, d_u_blk, d_u_line0, d_u_seg0, d_l_fs, d_l_fe, d_l_sfs, d_l_sfe, d_g_s, d_g_e, d_g_ss, d_g_se;
+    DBuf d_u_space, d_u_chrom, d_u_blk, d_u_base, d_irr_base, d_u_line0, d_u_seg0, d_l_fs, d_l_fe, d_l_sfs, d_l_sfe, d_g_s, d_g_e, d_g_ss, d_g_se;
     DBuf d_id_unit0, d_id_units, d_irr_grp, d_irr_pos, d_grp_off, d_grp_seq, d_grp_s, d_grp_e, d_blk_space;
     DJoin gaps, irr;
     // ---- accumulators of the running job ----
@@ -25,7 +25,7 @@ struct CountsState {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 
     std::vector<DBuf*> all() {
-        return {&d_rank, &d_cov, &d_X, &d_dir, &d_u_space, &d_u_chrom, &d_u_blk, &d_u_line0, &d_u_seg0, &d_l_fs, &d_l_fe, &d_l_sfs,
+        return {&d_rank, &d_cov, &d_X, &d_dir, &d_u_space, &d_u_chrom, &d_u_blk, &d_u_base, &d_irr_base, &d_u_line0, &d_u_seg0, &d_l_fs, &d_l_fe, &d_l_sfs,
                 &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
                 &d_grp_s, &d_grp_e, &d_blk_space, &d_Hs, &d_He, &d_G, &d_S, &d_E, &d_bits, &d_diff, &d_P, &d_routed, &d_scratch, &d_err,
                 &r_chrom, &r_start, &r_end, &r_value, &r_flag, &r_pos, &o_id, &o_chrom, &o_start, &o_end, &o_value};
@@ -57,6 +57,8 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     upload(C->d_u_space, h.u_space, st);
     upload(C->d_u_chrom, h.u_chrom, st);
     upload(C->d_u_blk, h.u_blk, st);
+    upload(C->d_u_base, h.u_base, st);
+    upload(C->d_irr_base, h.irr_base, st);
     upload(C->d_u_line0, h.u_line0, st);
     upload(C->d_u_seg0, h.u_seg0, st);
     upload(C->d_l_fs, h.l_fs, st);
@@ -83,7 +85,7 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     GFFX_CUDA(cudaEventCreate(&C->ev0));
     GFFX_CUDA(cudaEventCreate(&C->ev1));
     // keep the scalars, drop the bulk
-    for (auto* v : {&h.X, &h.dir, &h.u_space, &h.u_chrom, &h.u_blk, &h.u_line0, &h.u_seg0, &h.l_fs, &h.l_fe, &h.l_sfs, &h.l_sfe, &h.g_s,
+    for (auto* v : {&h.X, &h.dir, &h.u_space, &h.u_chrom, &h.u_blk, &h.u_base, &h.irr_base, &h.u_line0, &h.u_seg0, &h.l_fs, &h.l_fe, &h.l_sfs, &h.l_sfe, &h.g_s,
                     &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space})
         std::vector<uint32_t>().swap(*v);
     h.gaps = JoinHost();
@@ -134,6 +136,8 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.JI = C->irr.J;
     D.irr_grp = C->d_irr_grp.as<uint32_t>();
     D.irr_pos = C->d_irr_pos.as<uint32_t>();
+    D.irr_base = C->d_irr_base.as<uint32_t>();
+    D.ent_base = E->d_ent_base.as<uint32_t>();
     D.grp_off = C->d_grp_off.as<uint32_t>();
     D.grp_seq = C->d_grp_seq.as<uint32_t>();
     D.grp_s = C->d_grp_s.as<uint32_t>();
@@ -141,7 +145,7 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.JR = E->J;
     D.ent_blk = E->d_ent_blk.as<uint32_t>();
     D.blk_space = C->d_blk_space.as<uint32_t>();
-    D.n_seqs = (uint32_t)E->H->seq_names.size();
+    D.n_seqs = (uint32_t)E->H->vmap.n_vseqs();   // the bucketed regions carry virtual sequence numbers (0xFFFFFFFF: unknown sequence)
     D.Hs = C->d_Hs.as<uint32_t>();
     D.He = C->d_He.as<uint32_t>();
     D.G = C->d_G.as<uint32_t>();
@@ -232,7 +236,7 @@ void counts_finish_impl(EngineImpl* E, CountRows* rows) {
     GFFX_CUDA(cudaEventRecord(C->ev0, st));
     CountsFin F{};
     F.id_unit0 = C->d_id_unit0.as<uint32_t>(); F.id_units = C->d_id_units.as<uint32_t>();
-    F.u_space = C->d_u_space.as<uint32_t>(); F.u_chrom = C->d_u_chrom.as<uint32_t>(); F.u_blk = C->d_u_blk.as<uint32_t>();
+    F.u_space = C->d_u_space.as<uint32_t>(); F.u_chrom = C->d_u_chrom.as<uint32_t>(); F.u_blk = C->d_u_blk.as<uint32_t>(); F.u_base = C->d_u_base.as<uint32_t>();
     F.u_line0 = C->d_u_line0.as<uint32_t>(); F.u_seg0 = C->d_u_seg0.as<uint32_t>();
     F.l_fs = C->d_l_fs.as<uint32_t>(); F.l_fe = C->d_l_fe.as<uint32_t>(); F.l_sfs = C->d_l_sfs.as<uint32_t>(); F.l_sfe = C->d_l_sfe.as<uint32_t>();
     F.g_s = C->d_g_s.as<uint32_t>(); F.g_e = C->d_g_e.as<uint32_t>(); F.g_ss = C->d_g_ss.as<uint32_t>(); F.g_se = C->d_g_se.as<uint32_t>();

@@ -30,6 +30,8 @@ struct CountsDev {
     JoinIndex JI;           // tree intervals of irregular blocks, seq = sequence, payload = private space
     const uint32_t* irr_grp;
     const uint32_t* irr_pos;
+    const uint32_t* irr_base;   // per JI entry: base of its sequence on the virtual sequence (a private space keeps the lines' own coordinates)
+    const uint32_t* ent_base;   // the same per JR entry
     const uint32_t* grp_off;
     const uint32_t* grp_seq;
     const uint32_t* grp_s;
@@ -118,7 +120,8 @@ __global__ void __launch_bounds__(JOIN_THREADS)
                     for (uint32_t m = m0; m < m1; m++)
                         if (__ldg(D.grp_seq + m) == c && __ldg(D.grp_s + m) < re && __ldg(D.grp_e + m) > rs) return;
                 }
-                depth_space_update(D, __ldg(D.JI.ent_fid + j), rs, re);
+                const uint32_t vb = __ldg(D.irr_base + j);
+                depth_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
             });
         } else {
             cov_space_update(D, c, rs, re);
@@ -127,7 +130,10 @@ __global__ void __launch_bounds__(JOIN_THREADS)
                 if (blk == 0xFFFFFFFFu) return;
                 if (!D.blk_routed[blk]) D.blk_routed[blk] = 1;
                 const uint32_t sp = __ldg(D.blk_space + blk);
-                if (sp != 0xFFFFFFFFu) cov_space_update(D, sp, rs, re);  // OR / +-1 updates tolerate repeats: no dedup needed
+                if (sp != 0xFFFFFFFFu) {   // OR / +-1 updates tolerate repeats: no dedup needed
+                    const uint32_t vb = __ldg(D.ent_base + j);
+                    cov_space_update(D, sp, rs - vb, re - vb);
+                }
             });
         }
     }
@@ -155,6 +161,7 @@ struct CountsFin {
     const uint32_t* u_space;
     const uint32_t* u_chrom;
     const uint32_t* u_blk;
+    const uint32_t* u_base;
     const uint32_t* u_line0;
     const uint32_t* u_seg0;
     const uint32_t* l_fs;
@@ -201,6 +208,7 @@ __global__ void __launch_bounds__(256) counts_rows_kernel(CountsFin F, RowArrays
     for (uint32_t k = F.id_unit0[id]; k < F.id_unit0[id + 1]; k++) {
         const uint32_t u = F.id_units[k];
         const uint32_t s0 = F.u_seg0[u], s1 = F.u_seg0[u + 1];
+        const uint32_t vb = F.u_base[u];   // rows carry the sequence's own coordinates
         if (KIND == 0) {
             uint32_t d = F.S[F.g_se[s1 - 1]] - F.E[F.g_ss[s0]];  // mod 2^32; the true value is below 2^32
             for (uint32_t g = s0; g + 1 < s1; g++) d -= F.G[g];
@@ -211,8 +219,8 @@ __global__ void __launch_bounds__(256) counts_rows_kernel(CountsFin F, RowArrays
             // hull over the lines that were hit (depth.rs:198-199)
             for (uint32_t l = F.u_line0[u]; l < F.u_line0[u + 1]; l++)
                 if (F.S[F.l_sfe[l]] - F.E[F.l_sfs[l]] != 0) {
-                    mn = min(mn, F.l_fs[l]);
-                    mx = max(mx, F.l_fe[l]);
+                    mn = min(mn, F.l_fs[l] - vb);
+                    mx = max(mx, F.l_fe[l] - vb);
                 }
         } else {
             if (!F.blk_routed[F.u_blk[u]]) continue;
@@ -220,8 +228,8 @@ __global__ void __launch_bounds__(256) counts_rows_kernel(CountsFin F, RowArrays
             if (chrom == 0xFFFFFFFFu) chrom = F.u_chrom[u];
             const CovSpace cv = F.cov[F.u_space[u]];
             for (uint32_t g = s0; g < s1; g++) value += (uint32_t)(covered_before(F, cv, F.g_e[g]) - covered_before(F, cv, F.g_s[g]));
-            mn = min(mn, F.g_s[s0]);       // hull over ALL lines (coverage.rs:345-346): segments are sorted and disjoint
-            mx = max(mx, F.g_e[s1 - 1]);
+            mn = min(mn, F.g_s[s0] - vb);       // hull over ALL lines (coverage.rs:345-346): segments are sorted and disjoint
+            mx = max(mx, F.g_e[s1 - 1] - vb);
         }
     }
     R.flag[id] = any ? 1 : 0;

@@ -8,7 +8,8 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
     CountsIndexHost& C = *out;
     C = CountsIndexHost();
     const LineTable& L = H.lines;
-    const uint32_t n_seqs = (uint32_t)H.seq_names.size();
+    const VSeqMap& V = H.vmap;
+    const uint32_t n_seqs = (uint32_t)V.n_vseqs();   // spaces 0 .. n_seqs-1 are the engine's VIRTUAL sequences (host_index.h)
     const size_t nb = H.blocks.size();
     C.n_ids = (uint32_t)H.ids.size();
 
@@ -28,7 +29,7 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
     uint32_t n_spaces = n_seqs;
     std::vector<std::vector<uint32_t>> id_units(C.n_ids);
     std::vector<JoinItem> gap_items, irr_items;
-    std::vector<uint32_t> irr_item_grp, irr_item_pos;
+    std::vector<uint32_t> irr_item_grp, irr_item_pos, irr_item_base;
     std::vector<uint32_t> ord;
     C.u_line0.push_back(0);
     C.u_seg0.push_back(0);
@@ -48,8 +49,10 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
         if (regular)
             for (uint32_t i : ord)
                 if (L.fs[i] < r0.start || L.fe[i] > r0.end) { regular = false; break; }
-        uint32_t space;
-        if (regular) space = r0.seq;
+        // a regular block's lines live on its root's virtual sequence, moved by the root sequence's base; a private space keeps
+        // the lines' own coordinates and the regions routed to it are moved back (irr_base / the root join's ent_base)
+        uint32_t space, vbase = 0;
+        if (regular) { space = V.seq[r0.seq].vseq; vbase = V.seq[r0.seq].base; }
         else {
             space = n_spaces++;
             C.blk_space[b] = space;
@@ -57,10 +60,12 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             const uint32_t grp = nroots > 1 ? (uint32_t)(C.grp_off.size() - 1) : NONE32;
             for (uint32_t k = 0; k < nroots; k++) {
                 const RootIv& r = H.roots[br_list[br_off[b] + k]];
-                irr_items.push_back(JoinItem{r.seq, r.start, r.end, space});
+                const VSeqMap::Seq& m = V.seq[r.seq];
+                irr_items.push_back(JoinItem{m.vseq, m.base + r.start, m.base + r.end, space});
                 irr_item_grp.push_back(grp);
                 irr_item_pos.push_back(k);
-                if (grp != NONE32) { C.grp_seq.push_back(r.seq); C.grp_s.push_back(r.start); C.grp_e.push_back(r.end); }
+                irr_item_base.push_back(m.base);
+                if (grp != NONE32) { C.grp_seq.push_back(m.vseq); C.grp_s.push_back(m.base + r.start); C.grp_e.push_back(m.base + r.end); }
             }
             if (grp != NONE32) C.grp_off.push_back((uint32_t)C.grp_seq.size());
         }
@@ -74,15 +79,16 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             C.u_space.push_back(space);
             C.u_chrom.push_back(L.chrom[ord[p]]);  // stable sort: ord[p] is the first line in file order
             C.u_blk.push_back((uint32_t)b);
+            C.u_base.push_back(vbase);
             id_units[L.id[ord[p]]].push_back(u);
             std::sort(ord.begin() + p, ord.begin() + q, [&](uint32_t a, uint32_t c) {
                 if (L.fs[a] != L.fs[c]) return L.fs[a] < L.fs[c];
                 return L.fe[a] < L.fe[c];
             });
             const uint32_t seg_first = (uint32_t)C.g_s.size();
-            uint32_t cs = L.fs[ord[p]], ce = L.fe[ord[p]];
+            uint32_t cs = vbase + L.fs[ord[p]], ce = vbase + L.fe[ord[p]];
             for (size_t k = p; k < q; k++) {
-                const uint32_t s = L.fs[ord[k]], e = L.fe[ord[k]];
+                const uint32_t s = vbase + L.fs[ord[k]], e = vbase + L.fe[ord[k]];
                 C.l_fs.push_back(s);
                 C.l_fe.push_back(e);
                 if (s <= ce) ce = std::max(ce, e);
@@ -169,9 +175,11 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
     build_join_host(n_seqs, irr_items, 16, 8, &C.irr);
     C.irr_grp.resize(C.irr.n_entries());
     C.irr_pos.resize(C.irr.n_entries());
+    C.irr_base.resize(C.irr.n_entries());
     for (size_t k = 0; k < C.irr.n_entries(); k++) {
         C.irr_grp[k] = irr_item_grp[C.irr.ent_item[k]];
         C.irr_pos[k] = irr_item_pos[C.irr.ent_item[k]];
+        C.irr_base[k] = irr_item_base[C.irr.ent_item[k]];
     }
 }
 

@@ -9,8 +9,8 @@
 //   unit    = (block, ID) — the lines of one ID inside one block, sorted by start, plus their merged
 //             segments (touching lines merge; the gaps between segments are what a region must not
 //             fall into to be counted once).
-//   space   = a set of regions + a coordinate set.  Space c < n_seqs is "every valid region on
-//             sequence c" and holds the units of REGULAR blocks (exactly one tree interval, every
+//   space   = a set of regions + a coordinate set.  Space c < n_vseqs is "every valid region on
+//             virtual sequence c" (VSeqMap, host_index.h) and holds the units of REGULAR blocks (exactly one tree interval, every
 //             line nested inside it — then overlapping a line implies being routed).  Every other
 //             block with usable lines gets a private space fed only by the regions routed to it.
 //   X       = per space the sorted distinct line coordinates; slot k of a space = "rank k in X".
@@ -39,6 +39,7 @@ struct CountsIndexHost {
     std::vector<uint32_t> X, dir;
     // units
     std::vector<uint32_t> u_space, u_chrom, u_blk, u_line0, u_seg0;   // u_line0/u_seg0: n_units+1
+    std::vector<uint32_t> u_base;   // what the unit's coordinates below carry on top of the sequence's own (VSeqMap base; 0 in a private space)
     // lines grouped by unit, sorted by start: coordinates and global slots of both ends
     std::vector<uint32_t> l_fs, l_fe, l_sfs, l_sfe;
     // merged segments grouped by unit
@@ -50,6 +51,7 @@ struct CountsIndexHost {
     // tree intervals of irregular blocks: seq = sequence number, payload = private space
     JoinHost irr;
     std::vector<uint32_t> irr_grp, irr_pos;          // per irr entry: duplicate-fid group (NONE32 = single) and rank inside it
+    std::vector<uint32_t> irr_base;                  // per irr entry: VSeqMap base of its sequence (regions are moved back by it)
     std::vector<uint32_t> grp_off, grp_seq, grp_s, grp_e;  // group members in rank order
     std::vector<uint32_t> blk_space;                 // per block: private space of an irregular block, else NONE32
     uint64_t n_irregular = 0;

@@ -46,7 +46,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
@@ -76,7 +76,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
@@ -94,29 +94,37 @@ EngineImpl::~EngineImpl() {
     if (st) cudaStreamDestroy(st);
 }
 
-// Window grid of the partition pass (partition.cuh): windows of 2^shift bases over each sequence's extent
-// (largest root end), the finest grid with at most PART_MAX_WINDOWS windows.  Windows are a locality device
-// only: a region that starts beyond the extent falls into the sequence's last window.
+// Window grid of the partition pass (partition.cuh): windows of 2^shift bases over each VIRTUAL sequence's extent (VSeqMap,
+// host_index.h: the largest root end of a sequence that has a virtual sequence to itself, the laid-out length of a shared
+// one), the finest grid with at most PART_MAX_WINDOWS windows.  Windows are a locality device only: a region that starts
+// beyond the extent falls into the virtual sequence's last window.
 void EngineImpl::build_windows() {
-    const size_t n_seqs = H->seq_names.size();
-    std::vector<uint32_t> extent(n_seqs, 0);
-    for (const auto& r : H->roots) extent[r.seq] = std::max(extent[r.seq], r.end);
+    const VSeqMap& V = H->vmap;
+    const size_t n_seqs = H->seq_names.size(), n_v = V.n_vseqs();
     uint64_t max_win = PART_MAX_WINDOWS;
-    if (const char* e = getenv("GFFX_MAX_WINDOWS")) max_win = std::min<uint64_t>(PART_MAX_WINDOWS, std::max<uint64_t>(n_seqs, strtoull(e, nullptr, 10)));
+    if (const char* e = getenv("GFFX_MAX_WINDOWS")) max_win = std::min<uint64_t>(PART_MAX_WINDOWS, std::max<uint64_t>(n_v, strtoull(e, nullptr, 10)));
     uint32_t shift = 12;
     for (;; shift++) {
         uint64_t tot = 0;
-        for (size_t s = 0; s < n_seqs; s++) tot += ((uint64_t)extent[s] >> shift) + 1;
+        for (size_t v = 0; v < n_v; v++) tot += ((uint64_t)V.v_extent[v] >> shift) + 1;
         if (tot <= max_win || shift == 31) break;
     }
-    h_win0.assign(n_seqs + 1, 0);
-    for (size_t s = 0; s < n_seqs; s++) h_win0[s + 1] = h_win0[s] + (uint32_t)(((uint64_t)extent[s] >> shift) + 1);
-    if (h_win0[n_seqs] > PART_MAX_WINDOWS) throw Err(E_ARG, "index has more sequences than the partition pass supports (511)");
+    h_win0.assign(n_v + 1, 0);
+    for (size_t v = 0; v < n_v; v++) h_win0[v + 1] = h_win0[v] + (uint32_t)(((uint64_t)V.v_extent[v] >> shift) + 1);
+    if (h_win0[n_v] > PART_MAX_WINDOWS) throw Err(E_ARG, "window grid overflow (internal): more virtual sequences than windows");
+    std::vector<uint4> seqmap(std::max<size_t>(n_seqs, 1), make_uint4(0, 0xFFFFFFFFu, 0, 0));
+    for (size_t c = 0; c < n_seqs; c++) {
+        const VSeqMap::Seq& m = V.seq[c];
+        seqmap[c] = make_uint4(m.base, m.clamp, h_win0[m.vseq] | ((h_win0[m.vseq + 1] - h_win0[m.vseq]) << 16), m.vseq);
+    }
     upload(d_win0, h_win0, st);
+    upload(d_seqmap, seqmap, st);
     WG.win0 = d_win0.as<uint32_t>();
+    WG.seqmap = d_seqmap.as<uint4>();
     WG.n_seqs = (uint32_t)n_seqs;
+    WG.n_vseqs = (uint32_t)n_v;
     WG.shift = shift;
-    WG.n_win = h_win0[n_seqs];
+    WG.n_win = h_win0[n_v];
     d_poff.ensure(((size_t)WG.n_win + 2) * 4);
     d_ptot.ensure((size_t)PART_NB_MAX * 4);   // window totals: zero between partition passes (part_offsets_kernel clears them)
     d_pcur.ensure((size_t)PART_NB_MAX * 4);
@@ -154,11 +162,16 @@ uint32_t EngineImpl::partition_into(const uint32_t* dc, const uint32_t* ds, cons
 // Join index over the root intervals (see join_build.h / join.cuh).
 void EngineImpl::build_join() {
     const size_t n_seqs = H->seq_names.size();
+    const VSeqMap& V = H->vmap;
+    const uint32_t n_v = (uint32_t)V.n_vseqs();
     const auto& R = H->roots;
-    std::vector<JoinItem> items(R.size());
-    for (size_t i = 0; i < R.size(); i++) items[i] = JoinItem{R[i].seq, R[i].start, R[i].end, R[i].fid};
+    std::vector<JoinItem> items(R.size());   // in the engine's (virtual) coordinates
+    for (size_t i = 0; i < R.size(); i++) {
+        const VSeqMap::Seq& m = V.seq[R[i].seq];
+        items[i] = JoinItem{m.vseq, m.base + R[i].start, m.base + R[i].end, R[i].fid};
+    }
     JoinHost jh;
-    build_join_host((uint32_t)n_seqs, items, JOIN_LONG_K, JOIN_MAX_LISTS, &jh);
+    build_join_host(n_v, items, JOIN_LONG_K, JOIN_MAX_LISTS, &jh);
     // accessor copy: per sequence (start,end,fid) sorted by (start,end)
     seq_sorted_roots.assign(n_seqs, {});
     {
@@ -175,12 +188,16 @@ void EngineImpl::build_join() {
             for (uint32_t i : ids) { flat.push_back(R[i].start); flat.push_back(R[i].end); flat.push_back(R[i].fid); }
         }
     }
-    std::vector<uint32_t> ent_blk(jh.n_entries());
-    for (size_t k = 0; k < ent_blk.size(); k++) ent_blk[k] = H->root_blk[jh.ent_item[k]];
+    std::vector<uint32_t> ent_blk(jh.n_entries()), ent_base(jh.n_entries());
+    for (size_t k = 0; k < ent_blk.size(); k++) {
+        ent_blk[k] = H->root_blk[jh.ent_item[k]];
+        ent_base[k] = V.seq[R[jh.ent_item[k]].seq].base;
+    }
     dj.upload_from(jh, st, &dev_bytes);
     n_ent = dj.n_ent;
     J = dj.J;
     upload(d_ent_blk, ent_blk, st);
+    upload(d_ent_base, ent_base, st);
     d_ent_hit.ensure(std::max<uint32_t>(n_ent, 1));
     GFFX_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
 
@@ -191,12 +208,15 @@ void EngineImpl::build_join() {
     WinBinsHost bh;
     uint32_t max_sub = 7;  // GFFX_WJ_SUB=0..9; 2^7 bins per window (~65 kb at human scale): 6, 7 and 8 measure the same on the bench
     if (const char* e = getenv("GFFX_WJ_SUB")) max_sub = (uint32_t)std::min(9, std::max(0, atoi(e)));
-    build_win_bins((uint32_t)n_seqs, items, jwin0, jshift, max_sub, 1ull << 27, &bh);
+    build_win_bins(n_v, items, jwin0, jshift, max_sub, 1ull << 27, &bh);
     std::vector<uint4> ent4(bh.n_entries()), list4(std::max<size_t>(bh.list.size(), 1));
     for (size_t i = 0; i < ent4.size(); i++) ent4[i] = make_uint4(bh.ent_start[i], bh.ent_end[i], bh.ent_payload[i], (uint32_t)i);
     for (size_t i = 0; i < bh.list.size(); i++) list4[i] = ent4[bh.list[i]];
-    std::vector<uint32_t> wblk(bh.n_entries());
-    for (size_t k = 0; k < wblk.size(); k++) wblk[k] = bh.ent_item[k] == 0xFFFFFFFFu ? 0xFFFFFFFFu : H->root_blk[bh.ent_item[k]];
+    std::vector<uint32_t> wblk(bh.n_entries()), wbase(bh.n_entries(), 0);
+    for (size_t k = 0; k < wblk.size(); k++) {
+        wblk[k] = bh.ent_item[k] == 0xFFFFFFFFu ? 0xFFFFFFFFu : H->root_blk[bh.ent_item[k]];
+        if (bh.ent_item[k] != 0xFFFFFFFFu) wbase[k] = V.seq[R[bh.ent_item[k]].seq].base;
+    }
     upload(d_wj_win0, jwin0, st);
     upload(d_wj_winseq, bh.win_seq, st);
     upload(d_wj_ent4, ent4, st);
@@ -205,6 +225,7 @@ void EngineImpl::build_join() {
     upload(d_wj_first, bh.first, st);
     upload(d_wj_boff, bh.boff, st);
     upload(d_wj_blk, wblk, st);
+    upload(d_wj_base, wbase, st);
     wj_n_ent = (uint32_t)bh.n_entries();
     d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));   // grown to flag_bytes() once the line table is known (constructor)
     d_wj_cnt.ensure(std::max<uint32_t>(wj_n_ent, 1) * 8ull);
@@ -238,7 +259,15 @@ void EngineImpl::build_blocks() {
 // Lines + the filter rank space (see filter.cuh).
 void EngineImpl::build_lines() {
     const LineTable& L = H->lines;
-    const size_t n = L.size(), n_seqs = H->seq_names.size();
+    const VSeqMap& V = H->vmap;
+    // the rank space lives on the VIRTUAL sequences: a line's sequence, start and end move with its sequence's base
+    const size_t n = L.size(), n_seqs = V.n_vseqs();
+    std::vector<uint32_t> vS(n, 0), vE(n, 0), vseq(n, 0);
+    for (size_t i = 0; i < n; i++)
+        if (L.flags[i] & LN_I_OK) {
+            const VSeqMap::Seq& m = V.seq[L.iseq[i]];
+            vseq[i] = m.vseq; vS[i] = m.base + L.S[i]; vE[i] = m.base + L.E[i];
+        }
     // per sequence: sorted distinct S/E of usable lines (host threads: sequences are sorted side by side, longest first)
     const size_t T = (size_t)std::max(1, H->n_threads);
     auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
@@ -252,10 +281,10 @@ void EngineImpl::build_lines() {
         PhaseTimer t("  rank space: coordinate sets (sort)");
         std::vector<size_t> cnt(n_seqs, 0);
         for (size_t i = 0; i < n; i++)
-            if (L.flags[i] & LN_I_OK) cnt[L.iseq[i]] += 2;
+            if (L.flags[i] & LN_I_OK) cnt[vseq[i]] += 2;
         for (size_t s = 0; s < n_seqs; s++) xs[s].reserve(cnt[s]);
         for (size_t i = 0; i < n; i++)
-            if (L.flags[i] & LN_I_OK) { xs[L.iseq[i]].push_back(L.S[i]); xs[L.iseq[i]].push_back(L.E[i]); }
+            if (L.flags[i] & LN_I_OK) { xs[vseq[i]].push_back(vS[i]); xs[vseq[i]].push_back(vE[i]); }
         std::vector<uint32_t> order(n_seqs);
         for (size_t s = 0; s < n_seqs; s++) order[s] = (uint32_t)s;
         std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return xs[a].size() > xs[b].size(); });
@@ -279,8 +308,8 @@ void EngineImpl::build_lines() {
         r.slot0 = slot;
         slot += r.cnt + 1;
         // a name listed twice in .sqs resolves to its LAST number (intersect.rs:622-625): regions carrying
-        // the earlier number never reach the line filter
-        r.canon = H->seq_num.at(H->seq_names[s]) == s ? 1u : 0u;
+        // the earlier number never reach the line filter (such sequences share virtual sequences among themselves)
+        r.canon = V.v_canon[s];
         r.dir_base = (uint32_t)dir.size();
         if (v.empty()) { r.nb = 0; r.shift = 0; dir.push_back(0); continue; }
         uint32_t maxv = v.back(), shift = 4;
@@ -304,10 +333,10 @@ void EngineImpl::build_lines() {
         const size_t i0 = n * c / n_chunks, i1 = n * (c + 1) / n_chunks;
         for (size_t i = i0; i < i1; i++)
             if (L.flags[i] & LN_I_OK) {
-                const auto& v = xs[L.iseq[i]];
-                const RankSeq& r = seqs[L.iseq[i]];
-                iS[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.S[i]) - v.begin());
-                iE[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), L.E[i]) - v.begin());
+                const auto& v = xs[vseq[i]];
+                const RankSeq& r = seqs[vseq[i]];
+                iS[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), vS[i]) - v.begin());
+                iE[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), vE[i]) - v.begin());
             }
     });
     delete t_rank;
@@ -315,9 +344,9 @@ void EngineImpl::build_lines() {
     upload(d_ln_flags, L.flags, st);
     upload(d_ln_blk, L.blk, st);
     upload(d_ln_type, L.type_id, st);
-    upload(d_ln_iseq, L.iseq, st);
-    upload(d_ln_S, L.S, st);
-    upload(d_ln_E, L.E, st);
+    upload(d_ln_iseq, vseq, st);
+    upload(d_ln_S, vS, st);
+    upload(d_ln_E, vE, st);
     upload(d_ln_iS, iS, st);
     upload(d_ln_iE, iE, st);
     upload(d_ln_off, L.off, st);
@@ -464,7 +493,7 @@ uint32_t EngineImpl::expand_pairs(unsigned long long cap) {
         d_scan_scratch.as<ull>(), nullptr, st);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    wj_expand_kernel<<<(unsigned)sms * 8, WJ_EXP_THREADS, 0, st>>>(d_wj_off.as<ull>(), WC.ent4, wj_n_ent, d_pairs.as<uint32_t>(), cap);
+    wj_expand_kernel<<<(unsigned)sms * 8, WJ_EXP_THREADS, 0, st>>>(d_wj_off.as<ull>(), WC.ent4, d_wj_base.as<uint32_t>(), wj_n_ent, d_pairs.as<uint32_t>(), cap);
     return launches + 1;
 }
 

@@ -133,7 +133,7 @@ int cuda_device_count();
 void build_index_files(const std::string& gff_path, const std::string& attr_key, const std::string& skip_types);
 
 // synthetic workloads (synth.cpp)
-uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes, bool quirks);
+uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes, bool quirks, uint32_t n_scaffolds = 0);
 void synth_regions_host(const HostIndex& H, uint64_t seed, uint64_t first, uint64_t n, uint32_t length, uint32_t* chr,
                         uint32_t* start, uint32_t* end);
 // per-sequence extent table shared by the host and device region generators

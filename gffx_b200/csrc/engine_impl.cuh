@@ -103,13 +103,13 @@ class EngineImpl {
 
     // ---- join index -------------------------------------------------------------------------
     DJoin dj;  // root intervals of the .rit trees; payload = root_fid
-    DBuf d_ent_blk, d_ent_hit;
+    DBuf d_ent_blk, d_ent_hit, d_ent_base;   // d_ent_base: base of the entry's sequence on its virtual sequence (VSeqMap)
     uint32_t n_ent = 0;
     JoinIndex J{};
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
 
     // ---- window-addressed root join (winjoin.cuh): what intersect uses -------------------------
-    DBuf d_wj_win0, d_wj_winseq, d_wj_ent4, d_wj_list4, d_wj_fid, d_wj_first, d_wj_boff, d_wj_blk, d_wj_hit, d_wj_cnt, d_wj_off;
+    DBuf d_wj_win0, d_wj_base, d_wj_winseq, d_wj_ent4, d_wj_list4, d_wj_fid, d_wj_first, d_wj_boff, d_wj_blk, d_wj_hit, d_wj_cnt, d_wj_off;
     WinBins WC{};
     uint32_t wj_n_ent = 0;
 
@@ -130,7 +130,7 @@ class EngineImpl {
     DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_type_allow;
 
     // ---- window grid + partition scratch (partition.cuh) --------------------------------------
-    DBuf d_win0, d_poff, d_ptot, d_pcur, d_bchr, d_bse;
+    DBuf d_seqmap, d_win0, d_poff, d_ptot, d_pcur, d_bchr, d_bse;
     std::vector<uint32_t> h_win0;
     WinGrid WG{};
 

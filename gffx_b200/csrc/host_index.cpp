@@ -2,6 +2,7 @@
 #include <functional>
 #include <algorithm>
 #include <thread>
+#include <cstdlib>
 #include <fcntl.h>
 #include <sys/uio.h>
 #include <unistd.h>
@@ -193,6 +194,80 @@ void HostIndex::finish(const std::vector<uint32_t>& gfid, const std::vector<uint
         root_blk[i] = it == fid_blk.end() ? NONE32 : it->second;
     }
     build_lines(threads);
+    build_vseqs();
+}
+
+// see VSeqMap (host_index.h)
+void HostIndex::build_vseqs() {
+    const size_t n = seq_names.size();
+    vmap = VSeqMap();
+    vmap.seq.assign(n, VSeqMap::Seq{0, 0, 0xFFFFFFFFu});
+    if (n == 0) return;
+    std::vector<uint64_t> ext(n, 0), root_ext(n, 0);
+    for (const RootIv& r : roots) {
+        root_ext[r.seq] = std::max<uint64_t>(root_ext[r.seq], std::max<uint64_t>(r.end, (uint64_t)r.start + 1));
+        ext[r.seq] = std::max(ext[r.seq], root_ext[r.seq]);
+    }
+    const LineTable& L = lines;
+    for (size_t i = 0; i < L.size(); i++)
+        if (L.flags[i] & LN_I_OK) ext[L.iseq[i]] = std::max<uint64_t>(ext[L.iseq[i]], std::max(L.S[i], L.E[i]));
+    if (L.size()) {   // ID lines are compared with the regions routed to their block, whatever their own column 1 says (depth.rs:194-206)
+        std::vector<uint32_t> blk_max(blocks.size(), 0);
+        for (size_t b = 0; b < blocks.size(); b++)
+            for (uint64_t i = blk_line0[b]; i < blk_line0[b + 1]; i++)
+                if (L.flags[i] & LN_D_OK) blk_max[b] = std::max(blk_max[b], L.fe[i]);
+        for (size_t i = 0; i < roots.size(); i++)
+            if (root_blk[i] != NONE32) ext[roots[i].seq] = std::max<uint64_t>(ext[roots[i].seq], blk_max[root_blk[i]]);
+    }
+    std::vector<uint8_t> canon(n);
+    for (size_t c = 0; c < n; c++) canon[c] = seq_num.at(seq_names[c]) == c ? 1 : 0;
+    // capacity of a virtual sequence: at least the longest real sequence by its roots (a human chromosome stays alone or shares
+    // with a smaller one), doubled until the whole index fits on VSEQ_MAX virtual sequences
+    uint64_t cap = 1ull << 27;
+    for (size_t c = 0; c < n; c++) cap = std::max(cap, root_ext[c] + 2);
+    if (const char* e = getenv("GFFX_VSEQ_CAP")) cap = std::max<uint64_t>(16, strtoull(e, nullptr, 10));   // test hook
+    const uint64_t CAP_MAX = 0xFFFFFFFFull;
+    cap = std::min(cap, CAP_MAX);
+    std::vector<uint32_t> vs(n);
+    std::vector<uint64_t> base(n);
+    for (;;) {
+        // two packing streams (canonical names / shadowed duplicates), each greedy in sequence order
+        uint32_t nv = 0;
+        int64_t open_v[2] = {-1, -1};
+        uint64_t fill[2] = {0, 0};
+        for (size_t c = 0; c < n; c++) {
+            const uint64_t len = ext[c] + 2;
+            const int k = canon[c] ? 0 : 1;
+            if (len > cap) { vs[c] = nv++; base[c] = 0; continue; }   // alone, on its own coordinates
+            if (open_v[k] < 0 || fill[k] + len > cap) { open_v[k] = nv++; fill[k] = 0; }
+            vs[c] = (uint32_t)open_v[k];
+            base[c] = fill[k];
+            fill[k] += len;
+        }
+        if (nv <= VSEQ_MAX || cap >= CAP_MAX) {
+            if (nv > VSEQ_MAX)
+                throw Err(E_FORMAT, "index needs " + std::to_string(nv) + " sequences with coordinates near 2^32: more than the engine's " +
+                                        std::to_string(VSEQ_MAX) + " virtual sequences");
+            vmap.v_extent.assign(nv, 0);
+            vmap.v_canon.assign(nv, 1);
+            vmap.v_members.assign(nv, 0);
+            break;
+        }
+        cap = std::min(cap * 2, CAP_MAX);
+    }
+    vmap.capacity = cap;
+    for (size_t c = 0; c < n; c++) vmap.v_members[vs[c]]++;
+    for (size_t c = 0; c < n; c++) {
+        const uint32_t v = vs[c];
+        vmap.v_canon[v] = canon[c];
+        if (vmap.v_members[v] == 1) {
+            vmap.seq[c] = VSeqMap::Seq{v, 0, 0xFFFFFFFFu};
+            vmap.v_extent[v] = (uint32_t)std::min<uint64_t>(root_ext[c], 0xFFFFFFFFull);   // the window grid follows the roots, as regions do
+        } else {
+            vmap.seq[c] = VSeqMap::Seq{v, (uint32_t)base[c], (uint32_t)(ext[c] + 1)};
+            vmap.v_extent[v] = std::max<uint32_t>(vmap.v_extent[v], (uint32_t)(base[c] + ext[c] + 1));
+        }
+    }
 }
 
 namespace {
@@ -471,9 +546,10 @@ bool bed_intersect_line(const uint8_t* line, const uint8_t* q, const std::unorde
         *chr = it == seq_num.end() ? NONE32 : it->second;
     }
     if (*chr == NONE32) return false;  // unknown chromosome: skipped BEFORE the numbers are looked at
-    if (!parse_u32_strict(f[1], fl[1], s))
+    // lexical_core::parse::<u32> (intersect.rs:223-224): decimal digits after at most one '+' (lexical-parse-integer 1.0, parse_sign)
+    if (!parse_u32_rust(std::string_view((const char*)f[1], fl[1]), s))
         throw Err(E_FORMAT, "BED " + path + ": cannot parse start '" + std::string((const char*)f[1], fl[1]) + "' as u32");
-    if (!parse_u32_strict(f[2], fl[2], e))
+    if (!parse_u32_rust(std::string_view((const char*)f[2], fl[2]), e))
         throw Err(E_FORMAT, "BED " + path + ": cannot parse end '" + std::string((const char*)f[2], fl[2]) + "' as u32");
     return true;
 }

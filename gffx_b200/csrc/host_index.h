@@ -59,6 +59,26 @@ struct IdTable {
     std::string_view get(uint32_t i) const { return std::string_view((const char*)base + off[i], len[i]); }
 };
 
+// Virtual sequences (the engine's coordinate system).  The partition pass and every kernel after it address at most
+// a few hundred windows; the reference has no limit on the number of sequences (one tree per .rix offset,
+// src/utils/tree_index.rs:36-82: benchmark/hs.gff.sqs has 583, a scaffold-level assembly thousands).  So the real
+// sequences are laid side by side on a few VIRTUAL sequences: sequence c occupies [base, base + clamp] of virtual
+// sequence vseq, clamp = ext + 1 where ext is the largest coordinate any region of c is ever compared with (root
+// starts / ends of c, raw columns 4/5 of the lines named c, 0-based ends of the ID lines in blocks whose root is on c).
+// A region (c, s, e) becomes (vseq, base + min(s, clamp), base + min(e, clamp)): the clamp sits above every coordinate
+// of c and below the next sequence's base, so every comparison the reference makes (tree.rs:110, intersect.rs:145-158,
+// :500-517, depth.rs:78-82, coverage.rs:349-368) has the same outcome, and regions of c can never meet anything of
+// another sequence.  A sequence alone on its virtual sequence keeps its own coordinates (base 0, clamp = u32::MAX).
+struct VSeqMap {
+    struct Seq { uint32_t vseq, base, clamp; };
+    std::vector<Seq> seq;              // per real sequence
+    std::vector<uint32_t> v_extent;    // per virtual sequence: extent the window grid covers
+    std::vector<uint8_t> v_canon;      // per virtual sequence: its members' names resolve to their own numbers (intersect.rs:622-625)
+    std::vector<uint32_t> v_members;   // per virtual sequence: number of real sequences on it
+    uint64_t capacity = 0;             // packing capacity that was used
+    size_t n_vseqs() const { return v_extent.size(); }
+};
+
 struct HostIndex {
     std::string gff_path;
     std::vector<std::string> seq_names;                     // num_to_seqid
@@ -75,6 +95,7 @@ struct HostIndex {
     StringPool types, chroms;
     IdTable ids;
     int n_threads = 1;   // host threads the loaders were given (the engine's load-time builders use as many)
+    VSeqMap vmap;        // real sequence -> (virtual sequence, base, clamp); built by finish()
 
     // load .sqs/.rix/.rit/.gof beside `path` and (when the text is there) build the line table
     void open(const std::string& path, int threads);
@@ -96,7 +117,10 @@ struct HostIndex {
    private:
     void finish(const std::vector<uint32_t>& gfid, const std::vector<uint64_t>& gs, const std::vector<uint64_t>& ge, int threads);
     void build_lines(int threads);
+    void build_vseqs();
 };
+
+constexpr uint32_t VSEQ_MAX = 192;   // virtual sequences at most (each owns >= 1 of the <= 511 partition windows)
 
 // .rit/.rix decoding: flatten every tree into RootIv records (seq = position in .rix)
 void load_trees_flat(const std::string& rit_path, const std::string& rix_path, std::vector<RootIv>* out, uint32_t* n_trees);

@@ -38,17 +38,16 @@ constexpr int PART_UNROLL = 4;              // independent loads in flight per t
 constexpr uint32_t PART_MAX_WINDOWS = 511;  // + 1 bucket for regions whose sequence number is out of range
 constexpr uint32_t PART_NB_MAX = PART_MAX_WINDOWS + 1;
 
+// seqmap[c] of real sequence c (VSeqMap, host_index.h): x = base on its virtual sequence, y = clamp, z = first window of the
+// virtual sequence | its window count << 16, w = the virtual sequence.  The partition pass is where regions leave the
+// caller's coordinates: (c, s, e) -> virtual (base + min(s, clamp), base + min(e, clamp)) in window z.lo + min(vs >> shift, nw - 1).
 struct WinGrid {
-    const uint32_t* win0;  // n_seqs + 1: windows of sequence s are [win0[s], win0[s+1])
-    uint32_t n_seqs, shift, n_win;
+    const uint32_t* win0;  // n_vseqs + 1: windows of virtual sequence v are [win0[v], win0[v+1])
+    const uint4* seqmap;   // n_seqs
+    uint32_t n_seqs, n_vseqs, shift, n_win;
 };
 
-__device__ __forceinline__ uint32_t window_of(const WinGrid& G, uint32_t c, uint32_t s) {
-    if (c >= G.n_seqs) return G.n_win;  // the join kernels report the error
-    const uint32_t w0 = __ldg(G.win0 + c), nw = __ldg(G.win0 + c + 1) - w0;
-    const uint32_t b = s >> G.shift;
-    return w0 + (b < nw ? b : nw - 1);
-}
+constexpr uint32_t PART_MAP_SMEM = 512;   // sequences whose map entries a CTA keeps in shared memory (8 KB); more: read through L1
 
 // thread t of a tile holds elements 4 * (k * THREADS + t) .. + 3, k < PART_TILE / (4 * THREADS): 16-byte loads when the arrays allow
 constexpr int PART_VEC = PART_TILE / (4 * PART_THREADS);
@@ -62,12 +61,17 @@ __device__ __forceinline__ void part_load4(const uint32_t* __restrict__ a, uint3
     }
 }
 
-// the windows of a sequence from a shared-memory copy of win0 (n_seqs + 1 <= PART_NB_MAX cells: every sequence has a window)
-__device__ __forceinline__ uint32_t window_of_s(const uint32_t* s_win0, uint32_t n_seqs, uint32_t n_win, uint32_t shift, uint32_t c, uint32_t s) {
-    if (c >= n_seqs) return n_win;
-    const uint32_t w0 = s_win0[c], nw = s_win0[c + 1] - w0;
-    const uint32_t b = s >> shift;
-    return w0 + (b < nw ? b : nw - 1);
+__device__ __forceinline__ void part_stage_map(const WinGrid& G, uint4* s_map) {
+    if (G.n_seqs <= PART_MAP_SMEM)
+        for (uint32_t i = threadIdx.x; i < G.n_seqs; i += PART_THREADS) s_map[i] = __ldg(G.seqmap + i);
+}
+// window of region (c, s, .) and its virtual start; c >= n_seqs: the error bucket n_win, coordinates untouched
+__device__ __forceinline__ uint32_t part_window(const WinGrid& G, const uint4* s_map, uint32_t c, uint32_t s, uint4* m_out) {
+    if (c >= G.n_seqs) { *m_out = make_uint4(0u, 0xFFFFFFFFu, 0u, 0xFFFFFFFFu); return G.n_win; }
+    const uint4 m = G.n_seqs <= PART_MAP_SMEM ? s_map[c] : __ldg(G.seqmap + c);
+    *m_out = m;
+    const uint32_t b = (m.x + min(s, m.y)) >> G.shift, nw = m.z >> 16;
+    return (m.z & 0xFFFFu) + (b < nw ? b : nw - 1);
 }
 
 #ifndef GFFX_PART_COUNT_TILES
@@ -78,11 +82,11 @@ constexpr int PART_COUNT_TILES = GFFX_PART_COUNT_TILES;   // tiles per CTA of th
 static __global__ void __launch_bounds__(PART_THREADS)
     part_count_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, uint32_t n, uint32_t* __restrict__ tot) {
     __shared__ uint32_t sh[PART_NB_MAX];
-    __shared__ uint32_t s_win0[PART_NB_MAX + 1];
+    __shared__ uint4 s_map[PART_MAP_SMEM];
     const uint32_t nb = G.n_win + 1;
     const bool al16 = ((reinterpret_cast<uintptr_t>(chr) | reinterpret_cast<uintptr_t>(qs)) & 15u) == 0;
     for (uint32_t i = threadIdx.x; i < nb; i += PART_THREADS) sh[i] = 0;
-    for (uint32_t i = threadIdx.x; i <= G.n_seqs; i += PART_THREADS) s_win0[i] = __ldg(G.win0 + i);
+    part_stage_map(G, s_map);
     __syncthreads();
     for (int t = 0; t < PART_COUNT_TILES; t++) {
         const uint64_t base64 = ((uint64_t)blockIdx.x * PART_COUNT_TILES + t) * PART_TILE;
@@ -100,8 +104,10 @@ static __global__ void __launch_bounds__(PART_THREADS)
         for (int k = 0; k < PART_VEC; k++)
 #pragma unroll
             for (int j = 0; j < 4; j++)
-                if (base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x) + j < end)
-                    atomicAdd(&sh[window_of_s(s_win0, G.n_seqs, G.n_win, G.shift, c[k][j], s[k][j])], 1u);
+                if (base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x) + j < end) {
+                    uint4 m;
+                    atomicAdd(&sh[part_window(G, s_map, c[k][j], s[k][j], &m)], 1u);
+                }
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < nb; i += PART_THREADS)
@@ -132,7 +138,8 @@ static __global__ void __launch_bounds__(PART_NB_MAX) part_offsets_kernel(uint32
 
 constexpr size_t PART_SCATTER_SMEM = (size_t)PART_TILE * 14 + (size_t)PART_NB_MAX * 8;
 
-// oc == nullptr: the consumer does not need the sequence numbers (a window lies in one sequence)
+// ose takes the regions in VIRTUAL coordinates; oc (unless nullptr: a window lies in one virtual sequence) the virtual sequence
+// numbers, 0xFFFFFFFF for a region whose sequence number is out of range
 static __global__ void __launch_bounds__(PART_THREADS, 2)
     part_scatter_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
                         uint32_t n, uint32_t* __restrict__ cursor, uint32_t* __restrict__ oc, uint2* __restrict__ ose) {
@@ -143,14 +150,14 @@ static __global__ void __launch_bounds__(PART_THREADS, 2)
     uint32_t* s_hist = s_c + PART_TILE + PART_TILE / 2;                // regions per window -> first sorted position
     uint32_t* s_delta = s_hist + PART_NB_MAX;                          // global position minus sorted position of the window's run
     __shared__ uint32_t s_warp[PART_THREADS / 32];
-    __shared__ uint32_t s_win0[PART_NB_MAX + 1];
+    __shared__ uint4 s_map[PART_MAP_SMEM];
     const uint32_t nb = G.n_win + 1;
     const uint32_t base = blockIdx.x * (uint32_t)PART_TILE;
     const uint32_t end = min(n, base + (uint32_t)PART_TILE);
     const bool al16 = ((reinterpret_cast<uintptr_t>(chr) | reinterpret_cast<uintptr_t>(qs) | reinterpret_cast<uintptr_t>(qe)) & 15u) == 0;
     static_assert(PART_NB_MAX == PART_THREADS, "one window per thread");
     s_hist[threadIdx.x] = 0;
-    for (uint32_t i = threadIdx.x; i <= G.n_seqs; i += PART_THREADS) s_win0[i] = __ldg(G.win0 + i);
+    part_stage_map(G, s_map);
     uint32_t c[PART_VEC][4], s[PART_VEC][4], e[PART_VEC][4];
 #pragma unroll
     for (int k = 0; k < PART_VEC; k++) {
@@ -167,8 +174,12 @@ static __global__ void __launch_bounds__(PART_THREADS, 2)
         for (int j = 0; j < 4; j++) {
             wr[k][j] = 0xFFFFFFFFu;
             if (base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x) + j < end) {
-                const uint32_t w = window_of_s(s_win0, G.n_seqs, G.n_win, G.shift, c[k][j], s[k][j]);
+                uint4 m;
+                const uint32_t w = part_window(G, s_map, c[k][j], s[k][j], &m);
                 wr[k][j] = (w << 12) | atomicAdd(&s_hist[w], 1u);
+                s[k][j] = m.x + min(s[k][j], m.y);   // from here on: virtual coordinates
+                e[k][j] = m.x + min(e[k][j], m.y);
+                c[k][j] = m.w;
             }
         }
     static_assert(PART_TILE <= 4096, "12 bits of rank");

@@ -8,10 +8,10 @@ namespace gffx {
 
 namespace {
 // GRCh38 primary assembly lengths (chr1..22, X, Y)
-const uint32_t kChromLen[24] = {248956422, 242193529, 198295559, 190214555, 181538259, 170805979, 159345973, 145138636,
+const uint32_t kHsLen[24] = {248956422, 242193529, 198295559, 190214555, 181538259, 170805979, 159345973, 145138636,
                                 138394717, 133797422, 135086622, 133275309, 114364328, 107043718, 101991189, 90338345,
                                 83257441,  80373285,  58617616,  64444167,  46709983,  50818468,  156040895, 57227415};
-const char* kChromName[24] = {"chr1",  "chr2",  "chr3",  "chr4",  "chr5",  "chr6",  "chr7",  "chr8",  "chr9",  "chr10", "chr11", "chr12",
+const char* kHsName[24] = {"chr1",  "chr2",  "chr3",  "chr4",  "chr5",  "chr6",  "chr7",  "chr8",  "chr9",  "chr10", "chr11", "chr12",
                               "chr13", "chr14", "chr15", "chr16", "chr17", "chr18", "chr19", "chr20", "chr21", "chr22", "chrX",  "chrY"};
 
 struct Gene {
@@ -44,13 +44,25 @@ std::string row(const char* chr, const char* type, uint64_t s, uint64_t e, char 
 }
 }  // namespace
 
-// Returns the number of lines written (comments included).
-uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes, bool quirks) {
+// Returns the number of lines written (comments included).  n_scaffolds > 0 appends that many unplaced scaffolds
+// (3-150 kb, one to three genes each) after the 24 chromosomes: the shape of a scaffold-level assembly, or of the 583
+// sequences of the reference's benchmark/hs.gff.sqs.
+uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes, bool quirks, uint32_t n_scaffolds) {
     FILE* f = fopen(path.c_str(), "wb");
     if (!f) throw Err(E_IO, "cannot create " + path);
     Out o{f, std::string(), 0};
     uint64_t total = 0;
-    for (uint32_t l : kChromLen) total += l;
+    for (uint32_t l : kHsLen) total += l;
+    std::vector<std::string> name_store(24 + (size_t)n_scaffolds);
+    std::vector<uint32_t> kChromLen(kHsLen, kHsLen + 24);
+    std::vector<const char*> kChromName(kHsName, kHsName + 24);
+    for (uint32_t k = 0; k < n_scaffolds; k++) {
+        char nm[32];
+        snprintf(nm, sizeof nm, "scaf%05u", k);
+        name_store[24 + k] = nm;
+        kChromLen.push_back(3000 + (uint32_t)(rnd2(seed, 1000000 + k, 7) % 147000));
+    }
+    for (uint32_t k = 0; k < n_scaffolds; k++) kChromName.push_back(name_store[24 + k].c_str());
     std::vector<Gene> genes(n_genes);
     for (uint32_t g = 0; g < n_genes; g++) {
         uint64_t t = mulhi64(rnd2(seed, g, 1), total);
@@ -64,6 +76,15 @@ uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes
         uint32_t s = (uint32_t)t + 1;
         if ((uint64_t)s + L - 1 > kChromLen[c]) s = kChromLen[c] - L + 1;
         genes[g] = Gene{c, s, s + L - 1, g};
+    }
+    for (uint32_t k = 0; k < n_scaffolds; k++) {
+        const uint32_t ng = 1 + (rnd2(seed, 1000000 + k, 8) % 4 == 0 ? (uint32_t)(rnd2(seed, 1000000 + k, 9) % 2) + 1 : 0);
+        for (uint32_t j = 0; j < ng; j++) {
+            const uint32_t len = kChromLen[24 + k];
+            const uint32_t L = std::max<uint32_t>(300, (uint32_t)(rnd2(seed, 1000000 + k, 20 + j) % (len / 2)));
+            const uint32_t s = 1 + (uint32_t)(rnd2(seed, 1000000 + k, 30 + j) % (len - L));
+            genes.push_back(Gene{24 + k, s, s + L - 1, (uint64_t)n_genes + 4ull * k + j});
+        }
     }
     std::sort(genes.begin(), genes.end(), [](const Gene& a, const Gene& b) {
         if (a.chr != b.chr) return a.chr < b.chr;
@@ -165,6 +186,17 @@ uint64_t synth_gff_file(const std::string& path, uint64_t seed, uint32_t n_genes
                     snprintf(tmp, sizeof tmp, "ID=exon-far-T%06llu.%u;Parent=%s", (unsigned long long)k, m + 1, tid);
                     o.line(row(cn, "exon", es, es + 150, strand, tmp));
                 }
+            }
+        }
+        if (quirks && G.chr >= 24) {
+            const uint32_t sc = G.chr - 24;
+            if (sc % 7 == 0) {   // a child that names another sequence and lies far outside its root (App. D.4/5)
+                snprintf(tmp, sizeof tmp, "ID=exon-foreign-%u;Parent=%s", sc, gid);
+                o.line(row("chr1", "exon", 5000000 + 1000 * (sc % 50), 5000150 + 1000 * (sc % 50), strand, tmp));
+            }
+            if (sc % 401 == 5) {  // a coordinate at the top of u32: that sequence cannot share a virtual sequence
+                snprintf(tmp, sizeof tmp, "ID=exon-top-%u;Parent=%s", sc, gid);
+                o.line(row(cn, "exon", 4294960000ull, 4294967295ull, strand, tmp));
             }
         }
         if (quirks) {

@@ -358,8 +358,8 @@ constexpr int WJ_EXP_THREADS = 256;
 constexpr uint32_t WJ_EXP_CHUNK = 2048;   // pairs per warp and step: 24 KB
 
 static __global__ void __launch_bounds__(WJ_EXP_THREADS)
-    wj_expand_kernel(const unsigned long long* __restrict__ off, const uint4* __restrict__ ent4, uint32_t n_ent, uint32_t* __restrict__ pairs,
-                     unsigned long long cap) {
+    wj_expand_kernel(const unsigned long long* __restrict__ off, const uint4* __restrict__ ent4, const uint32_t* __restrict__ ent_base,
+                     uint32_t n_ent, uint32_t* __restrict__ pairs, unsigned long long cap) {
     const unsigned long long total = off[n_ent];
     if (total > cap) return;   // the host grows the buffer and launches again
     const uint32_t lane = threadIdx.x & 31u;
@@ -380,7 +380,8 @@ static __global__ void __launch_bounds__(WJ_EXP_THREADS)
         while (true) {
             const unsigned long long pe = min((unsigned long long)__ldg(off + j + 1), p1);   // this interval's pairs in the chunk: [p, pe)
             const uint4 v = __ldg(ent4 + j);
-            const uint32_t c0 = v.z, c1 = v.x, c2 = v.y;   // word w of the pair array holds component w % 3
+            const uint32_t vb = __ldg(ent_base + j);   // the record leaves the engine in the sequence's own coordinates
+            const uint32_t c0 = v.z, c1 = v.x - vb, c2 = v.y - vb;   // word w of the pair array holds component w % 3
             const unsigned long long w0 = 3ull * p, w1 = 3ull * pe;
             unsigned long long wa = min((w0 + 3ull) & ~3ull, w1);   // first 16-byte boundary at or after w0
             if (w0 + lane < wa) {

@@ -99,6 +99,12 @@ uint64_t gffx_index_n_blocks(const gffx_index* idx);
 uint64_t gffx_index_n_lines(const gffx_index* idx);
 uint64_t gffx_index_n_ids(const gffx_index* idx);
 uint64_t gffx_index_device_bytes(const gffx_index* idx);
+/* Where sequence `seq` sits in the engine's coordinate system (diagnostic).  TreeIndexData holds one tree per sequence
+ * with no limit on their number (src/utils/tree_index.rs:36-82); the engine lays the sequences side by side on at most
+ * a few hundred VIRTUAL sequences: a region (seq, s, e) is processed as (vseq, base + min(s, clamp), base + min(e, clamp)).
+ * clamp exceeds every coordinate of the sequence a region is ever compared with, so results are unchanged; pairs and
+ * depth / coverage rows come back in the sequence's own coordinates.  Any out pointer may be NULL. */
+int gffx_index_vseq(const gffx_index* idx, uint32_t seq, uint32_t* vseq, uint32_t* base, uint32_t* clamp, uint32_t* n_vseqs);
 /* flattened tree intervals of one sequence as (start,end,root_fid) triples, sorted by start */
 int gffx_index_seq_roots(const gffx_index* idx, uint32_t seq, const uint32_t** triples, uint64_t* n);
 
@@ -286,6 +292,9 @@ int gffx_coverage_run(const gffx_counts_args* args);
  * ------------------------------------------------------------------------------------------ */
 /* human-like GFF3 text written to `path`; returns number of lines through *n_lines */
 int gffx_synth_gff(const char* path, uint64_t seed, uint32_t n_genes, int quirks, uint64_t* n_lines);
+/* the same with n_scaffolds unplaced scaffolds (3-150 kb, 1-3 genes each) behind the 24 chromosomes: the shape of a
+ * scaffold-level assembly (the reference's benchmark/hs.gff.sqs lists 583 sequences) */
+int gffx_synth_gff_scaffolds(const char* path, uint64_t seed, uint32_t n_genes, int quirks, uint32_t n_scaffolds, uint64_t* n_lines);
 /* regions for sequences of the index (placement proportional to sequence extent); host arrays */
 int gffx_synth_regions_host(const gffx_index* idx, uint64_t seed, uint64_t first, uint64_t n, uint32_t length,
                             uint32_t* chr, uint32_t* start, uint32_t* end);

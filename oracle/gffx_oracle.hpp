@@ -180,11 +180,12 @@ inline bool parse_u32_digits(const uint8_t* s, size_t n, uint32_t& out) {
     return true;
 }
 
-// lexical_core::parse::<u32> as used at src/commands/intersect.rs:223-224: whole slice must be a
-// decimal u32.  (Leading '+' behaviour of lexical_core is unverified here; treated as an error and
-// kept out of fixtures — SURVEY.md App. A.1.)
+// lexical_core::parse::<u32> as used at src/commands/intersect.rs:223-224: whole slice must be a decimal u32.
+// lexical-parse-integer 1.0's parse_sign accepts ONE leading '+' for unsigned types in the standard format (a '-' is an
+// error, so is a sign without digits) - recalled from the crate's source, which is not vendored here: the same language
+// as str::parse::<u32>.  tests/test_kat_quirks.py::test_bed_dialects holds the KAT line.
 inline bool lexical_parse_u32(std::string_view s, uint32_t& out) {
-    return parse_u32_digits((const uint8_t*)s.data(), s.size(), out);
+    return rust_parse_u32(s, out);
 }
 
 // ---------------------------------------------------------------------------------------------
