@@ -167,9 +167,7 @@ class TreeIndexData:
         d.device = int(device)
         h = C.c_void_p()
         _check(lib.gffx_index_create(C.byref(d), C.byref(h)))
-        obj = cls(h)
-        obj._text_keepalive = buf  # the library borrows the text for the index's lifetime
-        return obj
+        return cls(h)   # the library has copied the text (include/gffx_b200.h: inputs are borrowed for the call only)
 
     def close(self):
         if self._h:

@@ -12,6 +12,19 @@ namespace gffx {
 
 constexpr uint32_t WARN_CAP = 1u << 16;
 
+// The join kernel's dynamic shared memory on top of its static 26 KB exceeds the 48 KB default.  Function attributes belong to
+// the device (context), so every engine sets them for its own device when it is built (one process may hold an engine per GPU).
+template <int MODE, bool INV> static void wj_set_attrs() {
+    GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+}
+static void set_kernel_attributes() {
+    wj_set_attrs<0, false>(); wj_set_attrs<0, true>(); wj_set_attrs<1, false>(); wj_set_attrs<1, true>(); wj_set_attrs<2, false>();
+    GFFX_CUDA(cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PART_SCATTER_SMEM));
+}
+
 // small kernels -------------------------------------------------------------------------------
 struct TileCountLoad {
     const uint32_t* p;
@@ -43,6 +56,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     GFFX_CUDA(cudaStreamCreateWithFlags(&st_copy, cudaStreamNonBlocking));
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
+    set_kernel_attributes();
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
@@ -129,7 +143,6 @@ void EngineImpl::build_windows() {
     d_ptot.ensure((size_t)PART_NB_MAX * 4);   // window totals: zero between partition passes (part_offsets_kernel clears them)
     d_pcur.ensure((size_t)PART_NB_MAX * 4);
     GFFX_CUDA(cudaMemsetAsync(d_ptot.p, 0, (size_t)PART_NB_MAX * 4, st));
-    GFFX_CUDA(cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PART_SCATTER_SMEM));
     GFFX_CUDA(cudaStreamSynchronize(st));
 }
 
@@ -450,11 +463,6 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
 
 template <int MODE, bool INV, bool FILT, bool SMALL>
 static void launch_wj2(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
-    static bool attr_set = false;   // per instantiation: the kernel's dynamic shared memory on top of its static 26 KB exceeds the 48 KB default
-    if (!attr_set) {
-        GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, FILT, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
-        attr_set = true;
-    }
     typedef unsigned long long ull;
     FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48};
     const dim3 grid(tiles, SMALL ? 16u : 1u);   // SMALL: 16 CTAs share a tile's small segments

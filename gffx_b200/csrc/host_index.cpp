@@ -158,8 +158,16 @@ void HostIndex::create(uint32_t n_seqs, const char* const* names, uint64_t n_roo
     seq_names.assign(names, names + n_seqs);
     roots.resize(n_roots);
     for (uint64_t i = 0; i < n_roots; i++) roots[i] = RootIv{rseq[i], rs[i], re[i], rfid[i]};
-    gff = text;
-    gff_len = text ? text_len : 0;
+    // the caller's text is COPIED (include/gffx_b200.h: inputs are borrowed only for the duration of the call): the line table,
+    // the ID strings of depth / coverage rows and the record emission all read it long after gffx_index_create has returned
+    if (text && text_len) {
+        gff_copy.assign(text, text + text_len);
+        gff = gff_copy.data();
+        gff_len = text_len;
+    } else {
+        gff = nullptr;
+        gff_len = 0;
+    }
     finish(std::vector<uint32_t>(gfid, gfid + n_gof), std::vector<uint64_t>(gs, gs + n_gof), std::vector<uint64_t>(ge, ge + n_gof),
            threads);
 }

@@ -50,7 +50,7 @@ struct StringPool {  // append-only dictionary: string -> dense index
 };
 
 // ID dictionary of the depth / coverage view: index = order of first appearance in the GFF; the strings stay where they are,
-// in the GFF text (mapped file or the caller's buffer, both outlive the index)
+// in the GFF text (the mapped file, or the index's own copy of the buffer gffx_index_create was given)
 struct IdTable {
     const uint8_t* base = nullptr;
     std::vector<uint64_t> off;
@@ -89,6 +89,7 @@ struct HostIndex {
     std::vector<uint8_t> blk_utf8;                          // per block: whole slice is valid UTF-8 (depth.rs:131)
     std::vector<uint64_t> blk_line0;                        // per block: first line index (blocks.size()+1 entries)
     Mapped gff_map;                                         // owned mapping when opened from a path
+    std::vector<uint8_t> gff_copy;                          // owned copy when created from a caller's buffer (gffx_index_create)
     const uint8_t* gff = nullptr;
     uint64_t gff_len = 0;
     LineTable lines;

@@ -69,3 +69,22 @@ def test_compute_fails_loudly_without_gpu(gffx, kat_gff):
         with pytest.raises(gffx.GffxError) as ei:
             gffx.TreeIndexData.load_tree_index(kat_gff, device=0)
         assert ei.value.code == -4
+
+
+def test_rust_crate_sources_match_the_makefile():
+    """cuda/build.rs (the crate a GFFx maintainer adds) compiles the very source lists of the Makefile, and
+    cuda/src/lib.rs declares only functions the header has."""
+    mk = open(os.path.join(ROOT, "Makefile")).read()
+    cu = re.findall(r"\$\(SRC\)/(\S+\.cu)\b", re.search(r"^CU_SRCS := (.*)$", mk, re.M).group(1))
+    cpp = re.findall(r"\$\(SRC\)/(\S+\.cpp)\b", re.search(r"^CPP_SRCS := (.*)$", mk, re.M).group(1))
+    rs = open(os.path.join(ROOT, "cuda", "build.rs")).read()
+    got_cu = re.findall(r'"([^"]+\.cu)"', re.search(r"let cu = \[(.*?)\];", rs, re.S).group(1))
+    got_cpp = re.findall(r'"([^"]+\.cpp)"', re.search(r"let cpp = \[(.*?)\];", rs, re.S).group(1))
+    assert sorted(got_cu) == sorted(cu) and sorted(got_cpp) == sorted(cpp)
+    for f in cu + cpp:
+        assert os.path.exists(os.path.join(ROOT, "gffx_b200", "csrc", f)), f
+    assert "sm_100a" in rs
+    lib_rs = open(os.path.join(ROOT, "cuda", "src", "lib.rs")).read()
+    declared = set(re.findall(r"\bfn (gffx_[a-z0-9_]+)\s*\(", lib_rs))
+    assert len(declared) >= 20 and declared <= set(header_symbols()), sorted(declared - set(header_symbols()))
+    assert "window.cu" not in open(os.path.join(ROOT, "INTEGRATION.md")).read()
