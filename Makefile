@@ -9,6 +9,7 @@ SRC := gffx_b200/csrc
 OBJ := build/obj
 LIB := gffx_b200/lib/libgffx_b200.so
 BIN := gffx_b200/bin/gffx-b200
+SYNTH_LIB := gffx_b200/lib/libgffx_synth.so
 
 CU_SRCS := $(SRC)/engine.cu $(SRC)/counts.cu $(SRC)/bedparse.cu
 CPP_SRCS := $(SRC)/util.cpp $(SRC)/join_build.cpp $(SRC)/winjoin_build.cpp $(SRC)/counts_index.cpp $(SRC)/host_index.cpp $(SRC)/index_builder.cpp $(SRC)/synth.cpp $(SRC)/capi.cpp
@@ -16,7 +17,7 @@ CU_OBJS := $(patsubst $(SRC)/%.cu,$(OBJ)/%.cu.o,$(CU_SRCS))
 CPP_OBJS := $(patsubst $(SRC)/%.cpp,$(OBJ)/%.o,$(CPP_SRCS))
 HDRS := $(wildcard $(SRC)/*.h $(SRC)/*.cuh) include/gffx_b200.h
 
-all: $(LIB) $(BIN) oracle
+all: $(LIB) $(BIN) $(SYNTH_LIB) oracle
 
 $(OBJ)/%.cu.o: $(SRC)/%.cu $(HDRS)
 	@mkdir -p $(OBJ)
@@ -33,6 +34,11 @@ $(LIB): $(CU_OBJS) $(CPP_OBJS)
 $(BIN): $(SRC)/cli_main.cpp $(LIB)
 	@mkdir -p gffx_b200/bin
 	$(HOSTCXX) $(CXXFLAGS) -o $@ $(SRC)/cli_main.cpp -Lgffx_b200/lib -lgffx_b200 -Wl,-rpath,'$$ORIGIN/../lib'
+
+# the workload text generator alone (bench.py --impl reference must not map the engine)
+$(SYNTH_LIB): $(OBJ)/synth.o $(OBJ)/synth_capi.o
+	@mkdir -p gffx_b200/lib
+	$(HOSTCXX) -shared -o $@ $^ -Wl,--no-undefined -lm
 
 oracle:
 	$(MAKE) -C oracle

@@ -110,6 +110,8 @@ SIGNATURES = {
     "gffx_free": (None, vp),
     "gffx_query_features": (C.c_int, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int, C.c_uint32, C.POINTER(vp)),
     "gffx_intersect": (C.c_int, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_uint32, C.POINTER(vp)),
+    "gffx_result_wait": (C.c_int, vp),
+    "gffx_result_pending": (C.c_int, vp),
     "gffx_result_n_queries": (C.c_uint64, vp),
     "gffx_result_n_pairs": (C.c_uint64, vp),
     "gffx_result_pairs": (u32p, vp),
@@ -162,6 +164,7 @@ F_WANT_PAIRS = 2
 F_NO_HOST_COPY = 4
 F_PAIRS_ON_DEVICE = 8
 F_STAGE_TIMES = 16
+F_ASYNC = 32
 
 
 def last_error() -> str:

@@ -97,6 +97,34 @@ class Result:
             pass
 
 
+class PendingResult:
+    """A GFFX_F_ASYNC job that has been queued on the engine's stream: wait() blocks until its counters have arrived and
+    returns the Result (device outputs only).  The region tensors are kept alive until then."""
+
+    def __init__(self, h, keep):
+        self._h, self._keep = h, keep
+
+    def wait(self) -> "Result":
+        h, self._h = self._h, None
+        rc = lib.gffx_result_wait(h)
+        if rc != 0:
+            lib.gffx_result_free(h)
+            raise GffxError(rc, _lib.last_error())
+        self._keep = None
+        return _take_result(h, True)
+
+    def close(self):
+        if self._h is not None:
+            h, self._h = self._h, None
+            lib.gffx_result_free(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def _take_result(h, copy: bool = True) -> Result:
     """copy=False: `pairs` / `ranges` are views of the result's page-locked buffers, valid until Result.close() (or its
     collection); the default copies them into ordinary numpy arrays and frees the handle at once."""
@@ -286,6 +314,8 @@ class TreeIndexData:
         h = C.c_void_p()
         _check(lib.gffx_intersect(self._h, pc, ps, pe, n, int(mode), int(bool(invert)), int(bool(entire_group)),
                                   types.encode() if types is not None else None, f, C.byref(h)))
+        if f & _lib.F_ASYNC:   # queued, not finished: the caller waits when it wants the numbers (gffx_result_wait)
+            return PendingResult(h, keep)
         return _take_result(h, copy)
 
     # -- batched / sharded jobs (gffx_shard_*, gffx_job_buffer) ----------------------------------
@@ -322,6 +352,8 @@ class TreeIndexData:
             combine(self.job_buffers())
         h = C.c_void_p()
         _check(lib.gffx_shard_finish(self._h, C.byref(h)))
+        if flags & _lib.F_ASYNC:
+            return PendingResult(h, keep)
         return _take_result(h, copy)
 
     def sync(self):

@@ -17,6 +17,8 @@ struct gffx_index {
 };
 struct gffx_result {
     IntersectResult r;
+    gffx_index* idx = nullptr;   // the handle the job ran on (a GFFX_F_ASYNC result waits on its engine)
+    int wait_rc = 0;             // status of the wait an accessor had to do on its own
 };
 struct gffx_counts {
     gffx_index* idx;
@@ -65,6 +67,15 @@ uint32_t* dup_u32(const std::vector<uint32_t>& v) {
 
 void need(const void* p, const char* what) {
     if (!p) throw Err(E_ARG, std::string(what) + " must not be NULL");
+}
+
+// a GFFX_F_ASYNC result whose counters have not been read yet: wait for them now (accessors call this; gffx_result_wait reports the status)
+int settle(const gffx_result* cr) {
+    gffx_result* r = const_cast<gffx_result*>(cr);
+    if (!r || r->r.pending_slot < 0) return r ? r->wait_rc : GFFX_E_ARG;
+    r->wait_rc = guard([&] { r->idx->engine()->wait(&r->r); });
+    if (r->wait_rc) { IntersectResult z; z.n_queries = r->r.n_queries; r->r = std::move(z); }
+    return r->wait_rc;
 }
 }  // namespace
 
@@ -181,6 +192,7 @@ int gffx_query_features(gffx_index* idx, const uint32_t* chr, const uint32_t* st
     return guard([&] {
         need(idx, "idx"); need(out, "out");
         auto r = std::make_unique<gffx_result>();
+        r->idx = idx;
         idx->engine()->intersect(chr, start, end, n, mode, invert != 0, false, nullptr, flags, true, &r->r);
         *out = r.release();
     });
@@ -191,6 +203,7 @@ int gffx_intersect(gffx_index* idx, const uint32_t* chr, const uint32_t* start, 
     return guard([&] {
         need(idx, "idx"); need(out, "out");
         auto r = std::make_unique<gffx_result>();
+        r->idx = idx;
         idx->engine()->intersect(chr, start, end, n, mode, invert != 0, entire_group != 0, types_csv, flags, false, &r->r);
         *out = r.release();
     });
@@ -214,6 +227,7 @@ int gffx_shard_finish(gffx_index* idx, gffx_result** out) {
     return guard([&] {
         need(idx, "idx"); need(out, "out");
         auto r = std::make_unique<gffx_result>();
+        r->idx = idx;
         idx->engine()->shard_finish(&r->r);
         *out = r.release();
     });
@@ -240,21 +254,27 @@ int gffx_index_sync(gffx_index* idx) {
     });
 }
 
+int gffx_result_wait(gffx_result* r) {
+    if (!r) { g_err = "result must not be NULL"; return GFFX_E_ARG; }
+    return settle(r);
+}
+int gffx_result_pending(const gffx_result* r) { return r && r->r.pending_slot >= 0 ? 1 : 0; }
 uint64_t gffx_result_n_queries(const gffx_result* r) { return r ? r->r.n_queries : 0; }
-uint64_t gffx_result_n_pairs(const gffx_result* r) { return r ? r->r.n_pairs : 0; }
-const uint32_t* gffx_result_pairs(const gffx_result* r) { return r && !r->r.pairs.empty() ? r->r.pairs.data() : nullptr; }
-const uint32_t* gffx_result_pairs_device(const gffx_result* r) { return r ? r->r.d_pairs : nullptr; }
-uint64_t gffx_result_n_roots(const gffx_result* r) { return r ? r->r.n_roots : 0; }
-uint64_t gffx_result_n_ranges(const gffx_result* r) { return r ? r->r.n_ranges : 0; }
-const uint64_t* gffx_result_ranges(const gffx_result* r) { return r && !r->r.ranges.empty() ? r->r.ranges.data() : nullptr; }
-uint64_t gffx_result_bytes_out(const gffx_result* r) { return r ? r->r.bytes_out : 0; }
-uint64_t gffx_result_n_warn(const gffx_result* r) { return r ? r->r.warn_fids.size() : 0; }
-const uint32_t* gffx_result_warn_fids(const gffx_result* r) { return r && !r->r.warn_fids.empty() ? r->r.warn_fids.data() : nullptr; }
-double gffx_result_kernel_ms(const gffx_result* r) { return r ? r->r.kernel_ms : 0; }
+uint64_t gffx_result_n_pairs(const gffx_result* r) { return settle(r) == 0 ? r->r.n_pairs : 0; }
+const uint32_t* gffx_result_pairs(const gffx_result* r) { return settle(r) == 0 && !r->r.pairs.empty() ? r->r.pairs.data() : nullptr; }
+const uint32_t* gffx_result_pairs_device(const gffx_result* r) { return settle(r) == 0 ? r->r.d_pairs : nullptr; }
+uint64_t gffx_result_n_roots(const gffx_result* r) { return settle(r) == 0 ? r->r.n_roots : 0; }
+uint64_t gffx_result_n_ranges(const gffx_result* r) { return settle(r) == 0 ? r->r.n_ranges : 0; }
+const uint64_t* gffx_result_ranges(const gffx_result* r) { return settle(r) == 0 && !r->r.ranges.empty() ? r->r.ranges.data() : nullptr; }
+uint64_t gffx_result_bytes_out(const gffx_result* r) { return settle(r) == 0 ? r->r.bytes_out : 0; }
+uint64_t gffx_result_n_warn(const gffx_result* r) { return settle(r) == 0 ? r->r.warn_fids.size() : 0; }
+const uint32_t* gffx_result_warn_fids(const gffx_result* r) { return settle(r) == 0 && !r->r.warn_fids.empty() ? r->r.warn_fids.data() : nullptr; }
+double gffx_result_kernel_ms(const gffx_result* r) { return settle(r) == 0 ? r->r.kernel_ms : 0; }
 uint32_t gffx_result_launches(const gffx_result* r) { return r ? r->r.launches : 0; }
-double gffx_result_stage_ms(const gffx_result* r, int stage) { return (r && stage >= 0 && stage < 12) ? r->r.stage_ms[stage] : 0; }
+double gffx_result_stage_ms(const gffx_result* r, int stage) { return (settle(r) == 0 && stage >= 0 && stage < 12) ? r->r.stage_ms[stage] : 0; }
 int gffx_result_get_info(const gffx_result* r, gffx_result_info* out) {
     if (!r || !out) return GFFX_E_ARG;
+    if (int rc = settle(r)) return rc;
     const auto& R = r->r;
     out->n_queries = R.n_queries; out->n_pairs = R.n_pairs; out->n_roots = R.n_roots; out->n_ranges = R.n_ranges;
     out->bytes_out = R.bytes_out; out->n_warn = R.warn_fids.size();
@@ -265,7 +285,10 @@ int gffx_result_get_info(const gffx_result* r, gffx_result_info* out) {
     out->launches = R.launches; out->reserved = 0;
     return GFFX_OK;
 }
-void gffx_result_free(gffx_result* r) { delete r; }
+void gffx_result_free(gffx_result* r) {
+    if (r && r->r.pending_slot >= 0 && r->idx) r->idx->engine()->abandon(&r->r);   // never waited for: its slot frees itself when the copy has landed
+    delete r;
+}
 
 int gffx_write_ranges(const gffx_index* idx, const uint64_t* ranges, uint64_t n_ranges, const char* out_path) {
     return guard([&] {

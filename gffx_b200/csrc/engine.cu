@@ -30,10 +30,21 @@ struct TileCountLoad {
     const uint32_t* p;
     __device__ uint64_t operator()(uint64_t i) const { return (uint64_t)p[i]; }
 };
-struct MarkLoad {  // next-set scan input: the cell's own index when marked
+struct MarkLoad {  // next-set scan input: the cell's own index when it carries THIS job's mark (filter.cuh: epochs)
     const uint8_t* m;
-    __device__ uint32_t operator()(uint64_t i) const { return m[i] ? (uint32_t)i : 0xFFFFFFFFu; }
+    uint32_t epoch8;
+    __device__ uint32_t operator()(uint64_t i) const { return m[i] == epoch8 ? (uint32_t)i : 0xFFFFFFFFu; }
 };
+
+// the per-job accumulators that do need zeros — the 256-byte counter block, the per-root hit flags and hit counters — in ONE launch
+// (they were four memset nodes; the rank-space arrays are never cleared: filter.cuh, epochs)
+__global__ void clear_job_kernel(uint4* __restrict__ small, uint4* __restrict__ hit, uint32_t n_hit16, uint4* __restrict__ cnt, uint32_t n_cnt16) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    if (i < 16) small[i] = z;
+    if (i < n_hit16) hit[i] = z;
+    for (uint32_t k = i; k < n_cnt16; k += gridDim.x * blockDim.x) cnt[k] = z;
+}
 
 __global__ void fill_u64_kernel(unsigned long long* p, uint64_t n, unsigned long long v) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -60,7 +71,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
@@ -90,7 +101,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
@@ -99,6 +110,11 @@ EngineImpl::~EngineImpl() {
     dj.release();
     counts_release(this);
     if (h_small) cudaFreeHost(h_small);
+    for (auto& S : slots) {
+        if (S.h) cudaFreeHost(S.h);
+        if (S.ev_start) cudaEventDestroy(S.ev_start);
+        if (S.ev_end) cudaEventDestroy(S.ev_end);
+    }
     for (auto& x : ev) cudaEventDestroy(x);
     for (auto& x : ev_chunk) cudaEventDestroy(x);
     for (auto& x : ev_copy) cudaEventDestroy(x);
@@ -239,6 +255,22 @@ void EngineImpl::build_join() {
     upload(d_wj_boff, bh.boff, st);
     upload(d_wj_blk, wblk, st);
     upload(d_wj_base, wbase, st);
+    {   // block -> the tree intervals that name it (wj_select_blocks_kernel gathers); intervals without a .gof record
+        const uint32_t nb = (uint32_t)H->blocks.size();
+        std::vector<uint32_t> off(nb + 1, 0), ent, orph;
+        for (size_t k = 0; k < wblk.size(); k++)
+            if (bh.ent_item[k] != 0xFFFFFFFFu) { if (wblk[k] != 0xFFFFFFFFu) off[wblk[k] + 1]++; else orph.push_back((uint32_t)k); }
+        for (uint32_t b = 0; b < nb; b++) off[b + 1] += off[b];
+        ent.resize(off[nb]);
+        std::vector<uint32_t> fill(off.begin(), off.end() - 1);
+        for (size_t k = 0; k < wblk.size(); k++)
+            if (bh.ent_item[k] != 0xFFFFFFFFu && wblk[k] != 0xFFFFFFFFu) ent[fill[wblk[k]]++] = (uint32_t)k;
+        n_orphans = (uint32_t)orph.size();
+        upload(d_blk_ent0, off, st);
+        upload(d_blk_ent, ent, st);
+        upload(d_orphans, orph, st);
+        GFFX_CUDA(cudaStreamSynchronize(st));
+    }
     wj_n_ent = (uint32_t)bh.n_entries();
     d_wj_hit.ensure(std::max<uint32_t>(wj_n_ent, 1));   // grown to flag_bytes() once the line table is known (constructor)
     d_wj_cnt.ensure(std::max<uint32_t>(wj_n_ent, 1) * 8ull);
@@ -370,6 +402,16 @@ void EngineImpl::build_lines() {
     const size_t ns = std::max<uint32_t>(f_slots, 1);
     d_A.ensure(ns * 8); d_B.ensure(ns * 8); d_PMX.ensure(ns * 8); d_SMN.ensure((ns + 1) * 8);
     d_Ms.ensure(ns * 2); d_Me.ensure(ns * 2); d_NS.ensure(ns * 8); d_NE.ensure(ns * 8);
+    // cleared ONCE: jobs tag their keys and marks with an epoch instead (filter.cuh)
+    GFFX_CUDA(cudaMemsetAsync(d_A.p, 0, ns * 8, st));
+    GFFX_CUDA(cudaMemsetAsync(d_B.p, 0xFF, ns * 8, st));
+    GFFX_CUDA(cudaMemsetAsync(d_Ms.p, 0, ns * 2, st));
+    GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
+    epoch = 0; epoch8 = 0;
+    if (const char* e = getenv("GFFX_EPOCH_START")) {   // test hook: start close to the wrap of both counters
+        epoch = (uint32_t)std::min<uint64_t>(strtoull(e, nullptr, 10), EPOCH_MAX);
+        epoch8 = epoch % 256u;
+    }
     d_keep.ensure(std::max<size_t>(n, 1));
     d_type_allow.ensure(std::max<size_t>(H->types.size(), 1));
     GFFX_CUDA(cudaStreamSynchronize(st));
@@ -464,7 +506,7 @@ void EngineImpl::stage_queries(const uint32_t* chr, const uint32_t* start, const
 template <int MODE, bool INV, bool FILT, bool SMALL>
 static void launch_wj2(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
     typedef unsigned long long ull;
-    FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48};
+    FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48, E->epoch, E->epoch8};
     const dim3 grid(tiles, SMALL ? 16u : 1u);   // SMALL: 16 CTAs share a tile's small segments
     wj_count_kernel<MODE, INV, FILT, SMALL><<<grid, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(),
                                                                                        E->d_wj_cnt.as<ull>(), n_pairs, err, E->FR, F);
@@ -537,15 +579,32 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
         d_bse.ensure(n_retained * 8 + 32);
     }
     d_poff.ensure((size_t)std::max<uint32_t>(n_chunks, 1) * (WG.n_win + 2) * 4);
-    GFFX_CUDA(cudaMemsetAsync(d_small.p, 0, 256, st));
-    GFFX_CUDA(cudaEventRecord(ev[0], st));
-    if (wj_n_ent) {
-        GFFX_CUDA(cudaMemsetAsync(d_wj_hit.p, 0, wj_n_ent, st));
-        GFFX_CUDA(cudaMemsetAsync(d_wj_cnt.p, 0, wj_n_ent * 8ull, st));
+    jb.async = flags & 32u;   // GFFX_F_ASYNC: the counters are read back into a slot of the engine's ring, the caller waits later
+    if (jb.async) {
+        if (jb.want_pairs_host || !jb.no_host) throw Err(E_ARG, "GFFX_F_ASYNC leaves every output on the device: combine it with GFFX_F_NO_HOST_COPY, not GFFX_F_WANT_PAIRS");
+        if (jb.stage_events) throw Err(E_ARG, "GFFX_F_ASYNC and GFFX_F_STAGE_TIMES exclude each other");
+        jb.slot = slot_acquire();
+    }
+    GFFX_CUDA(cudaEventRecord(jb.async ? slots[jb.slot].ev_start : ev[0], st));
+    {
+        const uint32_t n_hit16 = (wj_n_ent + 15u) / 16u, n_cnt16 = (wj_n_ent + 1u) / 2u;   // both buffers are padded to whole 16-byte words
+        const uint32_t threads = std::max<uint32_t>(std::max(n_hit16, 16u), std::min<uint32_t>(n_cnt16, 148u * 1024u));
+        clear_job_kernel<<<(threads + 255) / 256, 256, 0, st>>>(d_small.as<uint4>(), d_wj_hit.as<uint4>(), n_hit16, d_wj_cnt.as<uint4>(), n_cnt16);
+        jb.launches++;
     }
     if (jb.run_filter) {
         if (jb.have_types) {  // -T: comma-split, trimmed, non-empty tokens (intersect.rs:252-259)
-            std::vector<uint8_t> allow(std::max<size_t>(H->types.size(), 1), 0);
+            const size_t nt = std::max<size_t>(H->types.size(), 1);
+            std::vector<uint8_t> allow_local;
+            uint8_t* allow;
+            if (jb.async) {   // the slot's page-locked bytes: a pageable source would synchronise the stream
+                if (nt > ASYNC_ALLOW_CAP) throw Err(E_ARG, "GFFX_F_ASYNC with -T supports up to 4096 feature types");
+                allow = slots[jb.slot].h + ASYNC_ALLOW_OFF;
+                memset(allow, 0, nt);
+            } else {
+                allow_local.assign(nt, 0);
+                allow = allow_local.data();
+            }
             std::string_view sv(types_csv);
             size_t i = 0;
             while (i <= sv.size()) {
@@ -558,15 +617,24 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
                 }
                 i = j + 1;
             }
-            GFFX_CUDA(cudaMemcpyAsync(d_type_allow.p, allow.data(), allow.size(), cudaMemcpyHostToDevice, st));
-            GFFX_CUDA(cudaStreamSynchronize(st));  // `allow` is a stack-local
+            GFFX_CUDA(cudaMemcpyAsync(d_type_allow.p, allow, nt, cudaMemcpyHostToDevice, st));
+            if (!jb.async) GFFX_CUDA(cudaStreamSynchronize(st));  // `allow_local` is a stack-local
         }
+        // a new epoch instead of clearing the rank-space arrays (filter.cuh); a counter that wraps clears its arrays once
         const uint64_t ns = f_slots;
-        if (mode == 0 || mode == 2) GFFX_CUDA(cudaMemsetAsync(d_A.p, 0, ns * 8, st));
-        if (mode == 1) GFFX_CUDA(cudaMemsetAsync(d_B.p, 0xFF, ns * 8, st));
+        if (epoch == EPOCH_MAX) {
+            GFFX_CUDA(cudaMemsetAsync(d_A.p, 0, ns * 8, st));
+            GFFX_CUDA(cudaMemsetAsync(d_B.p, 0xFF, ns * 8, st));
+            epoch = 0;
+        }
+        epoch++;
         if (mode == 2) {
-            GFFX_CUDA(cudaMemsetAsync(d_Ms.p, 0, ns * 2, st));
-            GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
+            if (epoch8 == 255u) {
+                GFFX_CUDA(cudaMemsetAsync(d_Ms.p, 0, ns * 2, st));
+                GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
+                epoch8 = 0;
+            }
+            epoch8++;
         }
     }
 }
@@ -600,7 +668,8 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
     jb.launches += partition_into(dc, ds, de, n, oc, ose, poff);
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 1], st));
     if (jb.pairs_dev && jb.pair_cap == 0) {
-        d_pairs.ensure(std::max<uint64_t>(2 * std::max<uint64_t>(jb.retained, n), 1024) * 12);  // grow-only; a larger result re-runs the expansion
+        // grow-only; a larger result re-runs the expansion (or, for an asynchronous job, reports its pairs as not materialised)
+        d_pairs.ensure(std::max<uint64_t>({2 * std::max<uint64_t>(jb.retained, n), pairs_hwm + pairs_hwm / 8, (uint64_t)1024}) * 12);
         jb.pair_cap = d_pairs.cap / 12;
     }
     const unsigned tiles = (unsigned)((n + WJ_TILE - 1) / WJ_TILE);
@@ -618,9 +687,9 @@ uint32_t EngineImpl::ix_scans(FilterScans* Pout) {
     const uint64_t ns = f_slots;
     uint32_t launches = 0;
     d_scan_scratch.ensure(scan_scratch_elems(LA.n / LINE_THREADS + 1) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
-    FilterArrays F{d_A.as<ull>(), d_B.as<ull>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>(), d_small.as<uint32_t>() + 48};
+    FilterArrays F{d_A.as<ull>(), d_B.as<ull>(), d_Ms.as<uint8_t>(), d_Me.as<uint8_t>(), d_small.as<uint32_t>() + 48, epoch, epoch8};
     ull* scr = d_scan_scratch.as<ull>();
-    *Pout = FilterScans{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>(), F.any_inv};
+    *Pout = FilterScans{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>(), F.any_inv, epoch};
     if (mode == 0 || mode == 2)
         launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
                                                                                      OpMax(), 0ull, scr, nullptr, st);
@@ -632,9 +701,9 @@ uint32_t EngineImpl::ix_scans(FilterScans* Pout) {
     }
     if (mode == 2) {
         launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
-            MarkLoad{F.Ms}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
+            MarkLoad{F.Ms, epoch8}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
         launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
-            MarkLoad{F.Me}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, F.any_inv);
+            MarkLoad{F.Me, epoch8}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, F.any_inv);
     }
     return launches;
 }
@@ -677,18 +746,20 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     if (jb.stage_events) GFFX_CUDA(cudaEventRecord(ev[3], st));
 
     // ---- root -> block selection, merged ranges (-e) --------------------------------------------
-    if (n_blocks) GFFX_CUDA(cudaMemsetAsync(d_blk_sel.p, 0, n_blocks, st));
     if (!nothing) {
         d_scan_scratch.ensure(scan_scratch_elems(LA.n / LINE_THREADS + 1) * 8 + scan_scratch_elems(2ull * f_slots + 2) * 8);
-        wj_select_blocks_kernel<<<(wj_n_ent + 255) / 256, 256, 0, st>>>(d_wj_hit.as<uint8_t>(), d_wj_blk.as<uint32_t>(), WC.ent_fid, wj_n_ent,
-                                                                       d_blk_sel.as<uint8_t>(), d_warn.as<uint32_t>(), small32 + 13, WARN_CAP);
+        // every block looks at the hit flags of the tree intervals that name it (no flag array to clear first); the intervals
+        // whose fid has no .gof record go to the warn list; the selected blocks are counted here unless the merge does it
+        const bool merge = n_blocks && !jb.match_only && !jb.join_only;
+        const uint32_t n_thr = std::max<uint32_t>(std::max(n_blocks, n_orphans), 1);
+        wj_select_blocks_kernel<<<(n_thr + 255) / 256, 256, 0, st>>>(d_wj_hit.as<uint8_t>(), d_blk_ent0.as<uint32_t>(), d_blk_ent.as<uint32_t>(), n_blocks,
+                                                                     d_bstart.as<uint64_t>(), d_orphans.as<uint32_t>(), n_orphans, WC.ent_fid,
+                                                                     d_blk_sel.as<uint8_t>(), merge ? nullptr : small + 2, d_warn.as<uint32_t>(),
+                                                                     small32 + 13, WARN_CAP);
         launches++;
-        if (n_blocks) {
-            if (!jb.match_only && !jb.join_only)
-                merge_blocks_kernel<<<1, 1024, 0, st>>>(d_bstart.as<uint64_t>(), d_bend.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks,
-                                                       H->gff_len, true, d_ranges.as<ulonglong2>(), small + 1);
-            else
-                count_selected_kernel<<<(n_blocks + 255) / 256, 256, 0, st>>>(d_bstart.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks, small + 1);
+        if (merge) {
+            merge_blocks_kernel<<<1, 1024, 0, st>>>(d_bstart.as<uint64_t>(), d_bend.as<uint64_t>(), d_blk_sel.as<uint8_t>(), n_blocks,
+                                                   H->gff_len, true, d_ranges.as<ulonglong2>(), small + 1);
             launches++;
         }
     }
@@ -736,38 +807,35 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     GFFX_CUDA(cudaEventRecord(ev[9], st));
 
     // ---- results -----------------------------------------------------------------------------
+    out->launches = launches;
+    out->pend = PendingInfo{jb.pairs_dev, jb.join_only, jb.match_only, nothing, jb.no_host, jb.want_pairs_host, jb.pair_cap};
+    if (jb.async) {   // queue the read-back of the counters (and of the head of the warn list) into the job's slot; gffx_result_wait reads it
+        AsyncSlot& S = slots[jb.slot];
+        GFFX_CUDA(cudaMemcpyAsync(S.h, d_small.p, 64, cudaMemcpyDeviceToHost, st));
+        GFFX_CUDA(cudaMemcpyAsync(S.h + ASYNC_WARN_OFF, d_warn.p, ASYNC_WARN_CAP * 4, cudaMemcpyDeviceToHost, st));
+        GFFX_CUDA(cudaEventRecord(S.ev_end, st));
+        {
+            cudaError_t le = cudaGetLastError();
+            if (le != cudaSuccess) { S.state = 0; throw Err(E_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(le)); }
+        }
+        out->pending_slot = jb.slot;
+        return;
+    }
     GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
     GFFX_CUDA(cudaStreamSynchronize(st));
     {
         cudaError_t le = cudaGetLastError();
         if (le != cudaSuccess) throw Err(E_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(le));
     }
-    const uint64_t* hs = (const uint64_t*)h_small;
-    const uint32_t* hs32 = (const uint32_t*)h_small;
-    if (hs32[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
-    out->n_pairs = hs[0];
-    if (jb.pairs_dev && out->n_pairs > jb.pair_cap) {
+    read_counters(out, (const uint8_t*)h_small, nullptr);
+    if (out->pend.pairs_dev && out->n_pairs > out->pend.pair_cap) {
         // the pair buffer was too small for this result: grow it to the exact size and expand again (the counters are intact)
         d_pairs.ensure(out->n_pairs * 12);
-        launches += expand_pairs(d_pairs.cap / 12);
+        out->launches += expand_pairs(d_pairs.cap / 12);
         GFFX_CUDA(cudaStreamSynchronize(st));
         GFFX_CUDA(cudaGetLastError());
+        out->d_pairs = out->n_pairs ? d_pairs.as<uint32_t>() : nullptr;
     }
-    if (jb.pairs_dev && out->n_pairs) out->d_pairs = d_pairs.as<uint32_t>();
-    const uint32_t n_warn = std::min<uint32_t>(hs32[13], WARN_CAP);
-    if (n_warn) {
-        std::vector<uint32_t> w(n_warn);
-        GFFX_CUDA(cudaMemcpy(w.data(), d_warn.p, n_warn * 4ull, cudaMemcpyDeviceToHost));
-        std::sort(w.begin(), w.end());
-        w.erase(std::unique(w.begin(), w.end()), w.end());
-        out->warn_fids = std::move(w);
-    }
-    out->n_roots = hs[2] + out->warn_fids.size();
-    if (!jb.join_only && !nothing) {
-        if (jb.match_only) { out->n_ranges = hs[5]; out->bytes_out = hs[4]; }
-        else { out->n_ranges = hs[1]; out->bytes_out = hs[3]; }
-    }
-    last_n_ranges = out->n_ranges;
     if (out->n_ranges && !jb.no_host) {
         out->ranges.resize(out->n_ranges * 2);
         GFFX_CUDA(cudaMemcpyAsync(out->ranges.data(), d_ranges.p, out->n_ranges * 16, cudaMemcpyDeviceToHost, st));
@@ -799,7 +867,77 @@ void EngineImpl::ix_finish(IntersectResult* out) {
     }
     GFFX_CUDA(cudaEventElapsedTime(&ms, ev[0], ev[9]));
     out->kernel_ms = ms;
-    out->launches = launches;
+}
+
+// the 64-byte counter block of a finished job -> the result's fields.  u64 view: [0] n_pairs [1] n_ranges (-e merge) [2] blocks selected
+// [3] bytes (-e merge) [4] bytes_out [5] n_emit; u32 view: [12] region with a bad sequence number [13] n_warn.
+// warn_head: the first ASYNC_WARN_CAP entries of the device warn list (asynchronous jobs), else it is read from the device here.
+void EngineImpl::read_counters(IntersectResult* out, const uint8_t* h, const uint32_t* warn_head) {
+    const uint64_t* hs = (const uint64_t*)h;
+    const uint32_t* hs32 = (const uint32_t*)h;
+    const PendingInfo& P = out->pend;
+    if (hs32[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
+    out->n_pairs = hs[0];
+    if (out->n_pairs > pairs_hwm) pairs_hwm = out->n_pairs;
+    out->d_pairs = (P.pairs_dev && out->n_pairs && out->n_pairs <= P.pair_cap) ? d_pairs.as<uint32_t>() : nullptr;
+    uint32_t n_warn = std::min<uint32_t>(hs32[13], WARN_CAP);
+    if (n_warn) {
+        std::vector<uint32_t> w(n_warn);
+        if (warn_head) {
+            n_warn = std::min<uint32_t>(n_warn, ASYNC_WARN_CAP);   // an asynchronous job keeps the head of the list only
+            w.assign(warn_head, warn_head + n_warn);
+        } else {
+            GFFX_CUDA(cudaMemcpy(w.data(), d_warn.p, n_warn * 4ull, cudaMemcpyDeviceToHost));
+        }
+        std::sort(w.begin(), w.end());
+        w.erase(std::unique(w.begin(), w.end()), w.end());
+        out->warn_fids = std::move(w);
+    }
+    out->n_roots = hs[2] + out->warn_fids.size();
+    if (!P.join_only && !P.nothing) {
+        if (P.match_only) { out->n_ranges = hs[5]; out->bytes_out = hs[4]; }
+        else { out->n_ranges = hs[1]; out->bytes_out = hs[3]; }
+    }
+    last_n_ranges = out->n_ranges;
+}
+
+// ---- asynchronous jobs: a ring of page-locked slots, each with its own pair of events -------------------------------------
+int EngineImpl::slot_acquire() {
+    for (int pass = 0; pass < 2; pass++)
+        for (size_t k = 0; k < slots.size(); k++) {
+            AsyncSlot& S = slots[k];
+            if (S.state == 2 && cudaEventQuery(S.ev_end) == cudaSuccess) S.state = 0;   // an abandoned result whose copy has landed
+            if (S.state == 0) {
+                if (!S.h) {
+                    GFFX_CUDA(cudaMallocHost((void**)&S.h, ASYNC_SLOT_BYTES));
+                    GFFX_CUDA(cudaEventCreate(&S.ev_start));
+                    GFFX_CUDA(cudaEventCreate(&S.ev_end));
+                }
+                S.state = 1;
+                return (int)k;
+            }
+        }
+    throw Err(E_STATE, "too many asynchronous results pending on this index (" + std::to_string(slots.size()) + "): wait for or free some");
+}
+
+void EngineImpl::ix_wait(IntersectResult* out) {
+    if (out->pending_slot < 0) return;
+    GFFX_CUDA(cudaSetDevice(dev));
+    AsyncSlot& S = slots[(size_t)out->pending_slot];
+    out->pending_slot = -1;
+    cudaError_t e = cudaEventSynchronize(S.ev_end);
+    if (e != cudaSuccess) { S.state = 0; throw Err(E_CUDA, std::string("asynchronous intersect failed: ") + cudaGetErrorString(e)); }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, S.ev_start, S.ev_end);
+    out->kernel_ms = ms;
+    S.state = 0;   // the slot's bytes are read below, before any other call on this handle can take it (one thread per handle)
+    read_counters(out, S.h, (const uint32_t*)(S.h + ASYNC_WARN_OFF));
+}
+
+void EngineImpl::ix_abandon(IntersectResult* out) {
+    if (out->pending_slot < 0) return;
+    slots[(size_t)out->pending_slot].state = 2;
+    out->pending_slot = -1;
 }
 
 void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode, bool invert,
@@ -808,6 +946,7 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
     GFFX_CUDA(cudaSetDevice(dev));
     const bool dev_in = flags & 1u;  // GFFX_F_DEVICE_INPUT
+    if ((flags & 32u) && !dev_in) throw Err(E_ARG, "GFFX_F_ASYNC needs device-resident regions (GFFX_F_DEVICE_INPUT)");
     // host input: the copy is cut into chunks so that chunk i+1 crosses PCIe while chunk i is partitioned and joined
     uint32_t n_chunks = 1;
     if (!dev_in && n >= (1u << 21)) n_chunks = (uint32_t)std::min<uint64_t>(8, n >> 20);
@@ -901,6 +1040,7 @@ void Engine::shard_add(const uint32_t* chr, const uint32_t* start, const uint32_
     EngineImpl* E = impl_.get();
     if (n && (!chr || !start || !end)) throw Err(E_ARG, "NULL region arrays");
     if (!E->job.active) throw Err(E_STATE, "gffx_shard_add without gffx_shard_begin");
+    if (E->job.async && !(flags & 1u)) throw Err(E_ARG, "a GFFX_F_ASYNC job takes device-resident regions only (GFFX_F_DEVICE_INPUT)");
     GFFX_CUDA(cudaSetDevice(E->dev));
     const uint32_t *dc, *ds, *de;
     E->stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
@@ -914,6 +1054,8 @@ void Engine::shard_add(const uint32_t* chr, const uint32_t* start, const uint32_
     if (n_pairs_total) *n_pairs_total = *(const uint64_t*)E->h_small;
 }
 void Engine::shard_finish(IntersectResult* out) { impl_->ix_finish(out); }
+void Engine::wait(IntersectResult* out) { impl_->ix_wait(out); }
+void Engine::abandon(IntersectResult* out) { impl_->ix_abandon(out); }
 void Engine::sync() {
     GFFX_CUDA(cudaSetDevice(impl_->dev));
     GFFX_CUDA(cudaStreamSynchronize(impl_->st));

@@ -42,7 +42,14 @@ template <class T> void HostBlob<T>::release() {
     p_ = nullptr; cap_ = 0; n_ = 0;
 }
 
+struct PendingInfo {   // what turns a job's counter block into result fields (kept with the result while it is pending)
+    bool pairs_dev = false, join_only = false, match_only = true, nothing = false, no_host = false, want_pairs_host = false;
+    unsigned long long pair_cap = 0;
+};
+
 struct IntersectResult {
+    int pending_slot = -1;   // >= 0: an asynchronous job whose counters have not been read yet (Engine::wait)
+    PendingInfo pend;
     uint64_t n_queries = 0;
     uint64_t n_pairs = 0;
     HostBlob<uint32_t> pairs;         // host copy (WANT_PAIRS)
@@ -91,6 +98,10 @@ class Engine {
                      uint32_t batches_expected);
     void shard_add(const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags, uint64_t* n_pairs_total);
     void shard_finish(IntersectResult* out);
+    // GFFX_F_ASYNC jobs: block until the result's counters have arrived and fill its fields (no-op otherwise); abandon() is
+    // for a result that is dropped without having been waited for
+    void wait(IntersectResult* out);
+    void abandon(IntersectResult* out);
     // accumulator k of the running intersect job (which = 0) or depth / coverage job (which = 1): device pointer, element
     // count and how shards combine it (ReduceOp).  false when k is past the last one.
     bool shard_buffer(int which, uint32_t k, void** dptr, uint64_t* n_elems, int* op);

@@ -81,8 +81,21 @@ struct CountsState;  // counts.cu
 struct IxChunk {
     uint64_t off = 0, n = 0;  // position of the batch in the job's bucketed arrays (retained jobs), regions in it
 };
+// an asynchronous job's read-back target: page-locked bytes + the job's own pair of events
+constexpr size_t ASYNC_SLOT_BYTES = 8192;
+constexpr size_t ASYNC_WARN_OFF = 64;        // [0,64) counters, [64, 64 + 4 * ASYNC_WARN_CAP) head of the warn list, [4096, 8192) -T allow bytes
+constexpr uint32_t ASYNC_WARN_CAP = 1000;
+constexpr size_t ASYNC_ALLOW_OFF = 4096, ASYNC_ALLOW_CAP = 4096;
+struct AsyncSlot {
+    uint8_t* h = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_end = nullptr;
+    int state = 0;   // 0 free, 1 owned by a pending result, 2 abandoned (its result was freed before the copy landed)
+};
+
 struct IxJob {  // state of one intersect job between ix_begin and ix_finish
     bool active = false;
+    bool async = false;
+    int slot = -1;
     int mode = 2;
     bool invert = false, entire_group = false, join_only = false, match_only = true, run_filter = false, have_types = false;
     bool pairs_dev = false, want_pairs_host = false, no_host = false, nothing = false, sealed = false;
@@ -140,6 +153,15 @@ class EngineImpl {
     cudaEvent_t ev[12];  // [0..7] stage boundaries of one intersect call, [8],[9] around the pair expansion (K1b), [10] end of the partition pass
 
     IxJob job;
+    std::vector<AsyncSlot> slots = std::vector<AsyncSlot>(32);
+    uint32_t epoch = 0, epoch8 = 0;         // filter.cuh: the rank-space arrays are tagged per job, not cleared
+    unsigned long long pairs_hwm = 0;       // most pairs any job of this engine produced: sizes the pair buffer of the next one
+    DBuf d_blk_ent0, d_blk_ent, d_orphans;  // per block the tree intervals that name it; intervals whose fid has no .gof record
+    uint32_t n_orphans = 0;
+    int slot_acquire();
+    void ix_wait(IntersectResult* out);
+    void ix_abandon(IntersectResult* out);
+    void read_counters(IntersectResult* out, const uint8_t* h, const uint32_t* warn_head);
     std::vector<cudaEvent_t> ev_chunk, ev_copy;  // 4 timing events per batch of a job; one copy-done event per chunk
 
     // ---- counts (depth / coverage) -----------------------------------------------------------

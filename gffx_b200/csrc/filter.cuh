@@ -21,6 +21,11 @@
 // Every clause is the reference's clause translated literally, so inverted regions (qs>qe) and
 // inverted lines (S>E) behave as in the reference.  The sequence tag in the high bits lets one
 // plain (unsegmented) scan serve all sequences.
+//
+// Nothing is cleared between jobs: every key carries the job's EPOCH above the sequence tag (A: epoch << 41, so a newer
+// job's key beats any stale one under max; B: ~epoch << 40, likewise under min) and a mark byte IS the job's 8-bit
+// epoch.  A reader compares the whole tag, so a cell that only holds an older job's value reads as empty.  When a
+// counter wraps (2^23 - 1 jobs; 255 for the marks) the arrays are cleared once and the count restarts (engine.cu).
 #pragma once
 #include "scan.cuh"
 
@@ -76,8 +81,9 @@ __device__ __forceinline__ RankSeq load_rank_seq(const RankSpace& R, uint32_t se
 
 constexpr int FILT_THREADS = 256;
 constexpr int FILT_QPT = 4;
-constexpr uint64_t TAG_MAX_SHIFT = 33;  // A keys: seq<<33 | (qe+1)
-constexpr uint64_t TAG_MIN_SHIFT = 32;  // B keys: seq<<32 | qe
+constexpr uint64_t TAG_MAX_SHIFT = 33;  // A keys: (epoch<<8 | seq)<<33 | (qe+1)
+constexpr uint64_t TAG_MIN_SHIFT = 32;  // B keys: ((~epoch & EPOCH_MAX)<<8 | seq)<<32 | qe
+constexpr uint32_t EPOCH_MAX = (1u << 23) - 1u;   // 23 bits of epoch above 8 bits of (virtual) sequence
 
 struct FilterArrays {
     unsigned long long* A;  // n_slots
@@ -85,7 +91,11 @@ struct FilterArrays {
     uint8_t* Ms;            // 2*n_slots
     uint8_t* Me;            // 2*n_slots
     uint32_t* any_inv;      // set when some region has qs > qe: only then Me holds marks and NE is scanned / consulted
+    uint32_t epoch;         // 1 .. EPOCH_MAX: the job's number since the arrays were last cleared
+    uint32_t epoch8;        // 1 .. 255: the same for the mark bytes
 };
+__device__ __forceinline__ unsigned long long tag_max(uint32_t epoch, uint32_t seq) { return ((unsigned long long)epoch << 8) | seq; }
+__device__ __forceinline__ unsigned long long tag_min(uint32_t epoch, uint32_t seq) { return ((unsigned long long)(~epoch & EPOCH_MAX) << 8) | seq; }
 
 // one region (qs, qe) of sequence `seq` onto the rank space: 1-3 scattered L2 updates
 template <int MODE>
@@ -94,16 +104,16 @@ __device__ __forceinline__ void scatter_region(const RankSpace& R, const RankSeq
     const uint32_t lb = rank_lb(R, S, qs, &eq);
     const uint32_t slot = S.slot0 + lb;
     if (MODE == 0) {
-        atomicMax(F.A + slot, ((unsigned long long)seq << TAG_MAX_SHIFT) | ((unsigned long long)qe + 1ull));
+        atomicMax(F.A + slot, (tag_max(F.epoch, seq) << TAG_MAX_SHIFT) | ((unsigned long long)qe + 1ull));
     } else if (MODE == 1) {
-        atomicMin(F.B + slot + (eq ? 1u : 0u), ((unsigned long long)seq << TAG_MIN_SHIFT) | (unsigned long long)qe);
+        atomicMin(F.B + slot + (eq ? 1u : 0u), (tag_min(F.epoch, seq) << TAG_MIN_SHIFT) | (unsigned long long)qe);
     } else {
-        atomicMax(F.A + slot, ((unsigned long long)seq << TAG_MAX_SHIFT) | ((unsigned long long)qe + 1ull));
-        F.Ms[2ull * slot + (eq ? 1u : 0u)] = 1;
+        atomicMax(F.A + slot, (tag_max(F.epoch, seq) << TAG_MAX_SHIFT) | ((unsigned long long)qe + 1ull));
+        F.Ms[2ull * slot + (eq ? 1u : 0u)] = (uint8_t)F.epoch8;
         if (qs > qe) {
             bool eq2;
             const uint32_t lb2 = rank_lb(R, S, qe, &eq2);
-            F.Me[2ull * (S.slot0 + lb2) + (eq2 ? 1u : 0u)] = 1;
+            F.Me[2ull * (S.slot0 + lb2) + (eq2 ? 1u : 0u)] = (uint8_t)F.epoch8;
             *F.any_inv = 1u;
         }
     }
@@ -129,6 +139,7 @@ struct FilterScans {
     const uint32_t* NS;             // next marked cell >= c in Ms
     const uint32_t* NE;             // same for Me
     const uint32_t* ne_on;          // FilterArrays::any_inv: 0 = no mark in Me, NE was not scanned
+    uint32_t epoch;                 // the job's epoch: part of every key's tag
 };
 
 // The per-line decision in two rounds of independent loads (a thread is latency bound here: one line, a handful of loads):
@@ -142,18 +153,19 @@ __device__ __forceinline__ bool line_matches(const LineCols& c, const FilterScan
     const uint32_t seq = c.seq, S = c.S, E = c.E, iS = c.iS, iE = c.iE;
     if (MODE == 0) {
         const unsigned long long k = P.PMX[iS];
-        return (k >> TAG_MAX_SHIFT) == seq && (k & ((1ull << TAG_MAX_SHIFT) - 1)) >= (unsigned long long)E + 1ull;
+        return (k >> TAG_MAX_SHIFT) == tag_max(P.epoch, seq) && (k & ((1ull << TAG_MAX_SHIFT) - 1)) >= (unsigned long long)E + 1ull;
     } else if (MODE == 1) {
         const unsigned long long k = P.SMN[iS + 1];
-        return (k >> TAG_MIN_SHIFT) == seq && (uint32_t)k <= E;
+        return (k >> TAG_MIN_SHIFT) == tag_min(P.epoch, seq) && (uint32_t)k <= E;
     } else {
         const unsigned long long mask = (1ull << TAG_MAX_SHIFT) - 1;
         const uint32_t c0 = 2u * iS + 1u, c1 = 2u * iE + 1u;
         const unsigned long long k1 = P.PMX[iS], k2 = P.PMX[iE];
         const uint32_t ns = P.NS[c0];
         const bool ne_on = *P.ne_on != 0u;
-        if ((k1 >> TAG_MAX_SHIFT) == seq && (k1 & mask) >= (unsigned long long)S + 1ull) return true;  // qs<=S<=qe
-        if ((k2 >> TAG_MAX_SHIFT) == seq && (k2 & mask) >= (unsigned long long)E + 1ull) return true;  // qs<=E<=qe
+        const unsigned long long tag = tag_max(P.epoch, seq);
+        if ((k1 >> TAG_MAX_SHIFT) == tag && (k1 & mask) >= (unsigned long long)S + 1ull) return true;  // qs<=S<=qe
+        if ((k2 >> TAG_MAX_SHIFT) == tag && (k2 & mask) >= (unsigned long long)E + 1ull) return true;  // qs<=E<=qe
         if (S <= E) {
             if (ns <= c1) return true;  // S<=qs<=E
             if (ne_on && P.NE[c0] <= c1) return true;  // S<=qe<=E

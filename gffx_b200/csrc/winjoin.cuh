@@ -419,19 +419,35 @@ static __global__ void __launch_bounds__(WJ_EXP_THREADS)
     }
 }
 
-// per-entry hit flags -> per-block selection flags; entries whose fid has no .gof record are
-// appended to warn_fids (the reference warns about them, intersect.rs:269-272).
-static __global__ void wj_select_blocks_kernel(const uint8_t* __restrict__ ent_hit, const uint32_t* __restrict__ ent_blk,
-                                               const uint32_t* __restrict__ ent_fid, uint32_t n_ent, uint8_t* __restrict__ blk_sel,
-                                               uint32_t* __restrict__ warn_fids, uint32_t* __restrict__ n_warn, uint32_t warn_cap) {
-    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_ent || !ent_hit[j]) return;
-    uint32_t b = ent_blk[j];
-    if (b != 0xFFFFFFFFu) blk_sel[b] = 1;
-    else {
-        uint32_t k = atomicAdd(n_warn, 1u);
-        if (k < warn_cap) warn_fids[k] = ent_fid[j];
+// per-root hit flags -> per-block selection flags, by GATHER: block b reads the flags of the tree intervals that name it
+// (blk_ent[blk_ent0[b] .. blk_ent0[b+1]): one interval, or several with a duplicate root fid), so no flag array has to be
+// cleared first and no two threads write one byte.  n_sel (may be NULL: the -e merge counts them itself) += selected blocks
+// with a usable start.  Intervals whose fid has no .gof record (`orphans`) are appended to warn_fids when hit (the
+// reference warns about them, intersect.rs:269-272).
+static __global__ void __launch_bounds__(256)
+    wj_select_blocks_kernel(const uint8_t* __restrict__ ent_hit, const uint32_t* __restrict__ blk_ent0, const uint32_t* __restrict__ blk_ent,
+                            uint32_t n_blocks, const uint64_t* __restrict__ bstart, const uint32_t* __restrict__ orphans, uint32_t n_orphans,
+                            const uint32_t* __restrict__ ent_fid, uint8_t* __restrict__ blk_sel, unsigned long long* __restrict__ n_sel,
+                            uint32_t* __restrict__ warn_fids, uint32_t* __restrict__ n_warn, uint32_t warn_cap) {
+    __shared__ uint32_t sm[256 / 32 + 1];
+    const uint32_t b = blockIdx.x * 256 + threadIdx.x;
+    uint32_t k = 0;
+    if (b < n_blocks) {
+        bool sel = false;
+        for (uint32_t i = blk_ent0[b]; i < blk_ent0[b + 1]; i++) sel |= ent_hit[blk_ent[i]] != 0;
+        blk_sel[b] = sel ? 1 : 0;
+        k = (sel && bstart[b] != 0xFFFFFFFFFFFFFFFFull) ? 1u : 0u;
     }
+    if (b < n_orphans) {
+        const uint32_t j = orphans[b];
+        if (ent_hit[j]) {
+            const uint32_t p = atomicAdd(n_warn, 1u);
+            if (p < warn_cap) warn_fids[p] = ent_fid[j];
+        }
+    }
+    uint32_t tot;
+    block_scan_excl(k, OpSum(), 0u, sm, &tot);
+    if (n_sel && threadIdx.x == 0 && tot) atomicAdd(n_sel, (unsigned long long)tot);
 }
 
 }  // namespace gffx

@@ -41,7 +41,8 @@ enum {
     GFFX_F_WANT_PAIRS = 1u << 1,   /* materialise the (root_fid,start,end) pairs and copy them to the host         */
     GFFX_F_NO_HOST_COPY = 1u << 2, /* leave pairs / ranges on the device (bench: kernel-only timing)               */
     GFFX_F_PAIRS_ON_DEVICE = 1u << 3, /* materialise pairs in HBM but do not copy them to the host                 */
-    GFFX_F_STAGE_TIMES = 1u << 4   /* fill gffx_result_stage_ms: a dozen CUDA events inside the call, ~40 us of it  */
+    GFFX_F_STAGE_TIMES = 1u << 4,  /* fill gffx_result_stage_ms: a dozen CUDA events inside the call, ~40 us of it  */
+    GFFX_F_ASYNC = 1u << 5         /* queue the job and return: see gffx_result_wait                                */
 };
 
 typedef struct gffx_index gffx_index;     /* device-resident index: TreeIndexData + GofMap + GFF line table */
@@ -152,6 +153,18 @@ int gffx_query_features(gffx_index* idx, const uint32_t* chr, const uint32_t* st
 int gffx_intersect(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, int mode,
                    int invert, int entire_group, const char* types_csv, uint32_t flags, gffx_result** out);
 
+/* Asynchronous jobs.  The reference's run() is one synchronous pass (src/commands/intersect.rs:586-654); a caller that has
+ * several passes to run (a mode sweep over resident BED sets, the chunks of a huge BED, the ranks of a sharded job) need not
+ * pay a host round trip between them: with GFFX_F_ASYNC (together with GFFX_F_DEVICE_INPUT | GFFX_F_NO_HOST_COPY, on
+ * gffx_query_features / gffx_intersect / gffx_shard_begin) the call returns as soon as the job is QUEUED on the engine's
+ * stream, the 64 bytes of counters travel to a page-locked slot behind it, and the next job can be queued at once.
+ * gffx_result_wait blocks until the counters are there (and reports the job's status, e.g. a bad sequence number); every
+ * gffx_result_* accessor waits by itself when needed.  Device outputs (ranges for gffx_gather_text, pairs) stay valid until
+ * the handle's next job, as always; the region arrays must stay untouched until the wait.  If the pairs outgrow the buffer
+ * sized from earlier jobs, gffx_result_n_pairs is exact but gffx_result_pairs_device is NULL (run that pass synchronously).
+ * At most 32 results may be pending per handle; gffx_result_free on a pending result abandons it. */
+int gffx_result_wait(gffx_result* r);
+int gffx_result_pending(const gffx_result* r);   /* 1 while the counters of a GFFX_F_ASYNC job have not been read */
 uint64_t gffx_result_n_queries(const gffx_result* r);
 uint64_t gffx_result_n_pairs(const gffx_result* r);
 /* n_pairs (root_fid, start, end) u32 triples on the host; NULL unless GFFX_F_WANT_PAIRS */

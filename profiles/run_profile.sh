@@ -8,7 +8,7 @@ SKIP=${3:-24}
 CNT=${4:-8}
 OUT=gpurun_out
 mkdir -p $OUT
-CMD="python bench.py --steps 1 --warmup 3 --e2e-steps 1 --no-cpu"
+CMD="python bench.py --steps 1 --warmup 3 --e2e-steps 1 --no-cpu --parts= --min-seconds 0"
 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_launches.log 2>&1
 $CMD > $OUT/${TAG}_plain2.log 2>&1 &&

@@ -27,16 +27,17 @@ def launches(tag):
     ki, vi = hdr.index("Kernel Name"), hdr.index("Metric Value")
     agg = collections.OrderedDict()
     for r in rows[1:]:
-        a = agg.setdefault(re.sub(r"\(.*", "", r[ki]), [0, 0.0])
+        a = agg.setdefault(re.sub(r"\(.*", "", r[ki]), [0, 0.0, 0.0])
         a[0] += 1
         a[1] += float(r[vi].replace(",", ""))
+        a[2] = max(a[2], float(r[vi].replace(",", "")))
     tot = sum(a[1] for a in agg.values())
     out = io.StringIO()
-    out.write(f"# {tag}: ncu --metrics gpu__time_duration.sum --clock-control none over `python bench.py --steps 1 --warmup 3 --e2e-steps 1 --no-cpu`\n")
+    out.write(f"# {tag}: ncu --metrics gpu__time_duration.sum --clock-control none over `python bench.py --steps 1 --warmup 3 --e2e-steps 1 --no-cpu --parts '' --min-seconds 0`; max_us = the full-size (10 M-region) launch, the e2e arm's chunked launches pull avg_us down\n")
     out.write("# cold-cache, serialised launches: compare SHARES, not absolutes\n")
-    out.write(f"{'kernel':72s} {'n':>5s} {'total_us':>11s} {'avg_us':>9s} {'share':>6s}\n")
-    for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
-        out.write(f"{k[:72]:72s} {n:5d} {t / 1e3:11.1f} {t / 1e3 / n:9.1f} {t / tot:6.3f}\n")
+    out.write(f"{'kernel':72s} {'n':>5s} {'total_us':>11s} {'avg_us':>9s} {'max_us':>9s} {'share':>6s}\n")
+    for k, (n, t, mx) in sorted(agg.items(), key=lambda x: -x[1][1]):
+        out.write(f"{k[:72]:72s} {n:5d} {t / 1e3:11.1f} {t / 1e3 / n:9.1f} {mx / 1e3:9.1f} {t / tot:6.3f}\n")
     return out.getvalue()
 
 

@@ -18,7 +18,7 @@ def full():
     import gffx_b200 as g
     from bench import ensure_workload
 
-    gff = ensure_workload(GENES, g.build_index)
+    gff = ensure_workload(GENES, lambda p, s, n: g.synth_gff(p, seed=s, n_genes=n, quirks=False), g.build_index)
     idx = g.TreeIndexData.load_tree_index(gff, device=0)
     regs = idx.synth_regions_device(SEED, Q, LEN, device=torch.device("cuda", 0))
     yield idx, gff, regs
