@@ -65,6 +65,9 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     sm_count = prop.multiProcessorCount;
     GFFX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     GFFX_CUDA(cudaStreamCreateWithFlags(&st_copy, cudaStreamNonBlocking));
+    lanes[0].st = st;
+    lanes[0].ready = true;
+    if (const char* e = getenv("GFFX_LANES")) n_lanes = atoi(e) >= 2 ? 2 : 1;   // A/B hook: 1 = every job on lane 0
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     set_kernel_attributes();
@@ -97,7 +100,9 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
 
 EngineImpl::~EngineImpl() {
     cudaSetDevice(dev);
-    if (st) cudaStreamSynchronize(st);
+    for (Lane& l : lanes)
+        if (l.st) cudaStreamSynchronize(l.st);
+    for (DBuf& b : lanes[1 - lane_active].bufs) b.release();   // the active lane's buffers are the members, released below
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
@@ -121,7 +126,70 @@ EngineImpl::~EngineImpl() {
     for (auto& x : ev_gather) if (x) cudaEventDestroy(x);
     for (auto& x : ev_bed) if (x) cudaEventDestroy(x);
     if (st_copy) cudaStreamDestroy(st_copy);
-    if (st) cudaStreamDestroy(st);
+    for (Lane& l : lanes)
+        if (l.st) cudaStreamDestroy(l.st);
+}
+
+// ---- job lanes (engine_impl.cuh) ------------------------------------------------------------------------------------
+std::vector<DBuf*> EngineImpl::lane_bufs() {
+    return {&d_wj_hit, &d_wj_cnt, &d_wj_off, &d_blk_sel, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+            &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse, &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn};
+}
+
+DBuf& EngineImpl::lane_buf(int lane, DBuf* member) {
+    if (lane == lane_active) return *member;
+    const std::vector<DBuf*> m = lane_bufs();
+    for (size_t i = 0; i < m.size(); i++)
+        if (m[i] == member && i < lanes[lane].bufs.size()) return lanes[lane].bufs[i];
+    throw Err(E_STATE, "lane buffer (internal)");
+}
+
+// what a lane needs before its first job: the buffers the index sizes once (the others grow on demand)
+void EngineImpl::alloc_job_buffers() {
+    d_poff.ensure(((size_t)WG.n_win + 2) * 4);
+    d_ptot.ensure((size_t)PART_NB_MAX * 4);
+    d_pcur.ensure((size_t)PART_NB_MAX * 4);
+    GFFX_CUDA(cudaMemsetAsync(d_ptot.p, 0, (size_t)PART_NB_MAX * 4, st));
+    d_wj_cnt.ensure(std::max<uint32_t>(wj_n_ent, 1) * 8ull);
+    d_wj_off.ensure(((uint64_t)wj_n_ent + 1) * 8);
+    d_blk_sel.ensure(std::max<uint32_t>(n_blocks, 1));
+    d_ranges.ensure(std::max<uint32_t>(n_blocks, 1) * 16ull);
+    const size_t ns = std::max<uint32_t>(f_slots, 1);
+    d_A.ensure(ns * 8); d_B.ensure(ns * 8); d_PMX.ensure(ns * 8); d_SMN.ensure((ns + 1) * 8);
+    d_Ms.ensure(ns * 2); d_Me.ensure(ns * 2); d_NS.ensure(ns * 8); d_NE.ensure(ns * 8);
+    GFFX_CUDA(cudaMemsetAsync(d_A.p, 0, ns * 8, st));
+    GFFX_CUDA(cudaMemsetAsync(d_B.p, 0xFF, ns * 8, st));
+    GFFX_CUDA(cudaMemsetAsync(d_Ms.p, 0, ns * 2, st));
+    GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
+    epoch = epoch_start; epoch8 = epoch_start % 256u;
+    d_keep.ensure(std::max<size_t>(LA.n, 1));
+    d_type_allow.ensure(std::max<size_t>(H->types.size(), 1));
+    d_wj_hit.ensure(flag_bytes());
+    GFFX_CUDA(cudaMemsetAsync(d_wj_hit.p, 0, flag_bytes(), st));
+    d_small.ensure(256);
+    d_warn.ensure(WARN_CAP * 4);
+}
+
+void EngineImpl::lane_activate(int k) {
+    if (k == lane_active) return;
+    const std::vector<DBuf*> m = lane_bufs();
+    Lane& cur = lanes[lane_active];
+    Lane& nxt = lanes[k];
+    cur.bufs.resize(m.size());
+    if (nxt.bufs.size() != m.size()) {
+        nxt.bufs.assign(m.size(), DBuf());
+        for (DBuf& b : nxt.bufs) b.total = &dev_bytes;
+    }
+    for (size_t i = 0; i < m.size(); i++) { cur.bufs[i] = *m[i]; *m[i] = nxt.bufs[i]; }
+    cur.epoch = epoch; cur.epoch8 = epoch8;
+    epoch = nxt.epoch; epoch8 = nxt.epoch8;
+    if (!nxt.st) GFFX_CUDA(cudaStreamCreateWithFlags(&nxt.st, cudaStreamNonBlocking));
+    st = nxt.st;
+    lane_active = k;
+    if (!nxt.ready) {
+        alloc_job_buffers();
+        nxt.ready = true;
+    }
 }
 
 // Window grid of the partition pass (partition.cuh): windows of 2^shift bases over each VIRTUAL sequence's extent (VSeqMap,
@@ -407,11 +475,10 @@ void EngineImpl::build_lines() {
     GFFX_CUDA(cudaMemsetAsync(d_B.p, 0xFF, ns * 8, st));
     GFFX_CUDA(cudaMemsetAsync(d_Ms.p, 0, ns * 2, st));
     GFFX_CUDA(cudaMemsetAsync(d_Me.p, 0, ns * 2, st));
-    epoch = 0; epoch8 = 0;
-    if (const char* e = getenv("GFFX_EPOCH_START")) {   // test hook: start close to the wrap of both counters
-        epoch = (uint32_t)std::min<uint64_t>(strtoull(e, nullptr, 10), EPOCH_MAX);
-        epoch8 = epoch % 256u;
-    }
+    epoch_start = 0;
+    if (const char* e = getenv("GFFX_EPOCH_START"))   // test hook: start close to the wrap of both counters
+        epoch_start = (uint32_t)std::min<uint64_t>(strtoull(e, nullptr, 10), EPOCH_MAX);
+    epoch = epoch_start; epoch8 = epoch_start % 256u;
     d_keep.ensure(std::max<size_t>(n, 1));
     d_type_allow.ensure(std::max<size_t>(H->types.size(), 1));
     GFFX_CUDA(cudaStreamSynchronize(st));
@@ -557,6 +624,12 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
                           uint64_t n_retained, uint32_t n_chunks) {
     if (mode < 0 || mode > 2) throw Err(E_ARG, "mode must be 0 (contained), 1 (contains-region) or 2 (overlap)");
     GFFX_CUDA(cudaSetDevice(dev));
+    if ((flags & 32u) && n_lanes > 1) {   // queued jobs alternate between the lanes; everything else runs on lane 0
+        lane_activate(lane_next);
+        lane_next ^= 1;
+    } else {
+        lane_activate(0);
+    }
     IxJob& jb = job;
     jb = IxJob();
     jb.mode = mode; jb.invert = invert; jb.entire_group = entire_group; jb.join_only = join_only;
@@ -808,7 +881,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
 
     // ---- results -----------------------------------------------------------------------------
     out->launches = launches;
-    out->pend = PendingInfo{jb.pairs_dev, jb.join_only, jb.match_only, nothing, jb.no_host, jb.want_pairs_host, jb.pair_cap};
+    out->pend = PendingInfo{jb.pairs_dev, jb.join_only, jb.match_only, nothing, jb.no_host, jb.want_pairs_host, jb.pair_cap, d_pairs.as<uint32_t>(), lane_active};
     if (jb.async) {   // queue the read-back of the counters (and of the head of the warn list) into the job's slot; gffx_result_wait reads it
         AsyncSlot& S = slots[jb.slot];
         GFFX_CUDA(cudaMemcpyAsync(S.h, d_small.p, 64, cudaMemcpyDeviceToHost, st));
@@ -819,6 +892,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
             if (le != cudaSuccess) { S.state = 0; throw Err(E_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(le)); }
         }
         out->pending_slot = jb.slot;
+        lane_activate(0);   // outside a job the engine's stream and buffers are lane 0's
         return;
     }
     GFFX_CUDA(cudaMemcpyAsync(h_small, d_small.p, 64, cudaMemcpyDeviceToHost, st));
@@ -879,7 +953,7 @@ void EngineImpl::read_counters(IntersectResult* out, const uint8_t* h, const uin
     if (hs32[12]) throw Err(E_ARG, "region with a chromosome number beyond the index's sequence list");
     out->n_pairs = hs[0];
     if (out->n_pairs > pairs_hwm) pairs_hwm = out->n_pairs;
-    out->d_pairs = (P.pairs_dev && out->n_pairs && out->n_pairs <= P.pair_cap) ? d_pairs.as<uint32_t>() : nullptr;
+    out->d_pairs = (P.pairs_dev && out->n_pairs && out->n_pairs <= P.pair_cap) ? P.d_pairs : nullptr;
     uint32_t n_warn = std::min<uint32_t>(hs32[13], WARN_CAP);
     if (n_warn) {
         std::vector<uint32_t> w(n_warn);
@@ -899,6 +973,7 @@ void EngineImpl::read_counters(IntersectResult* out, const uint8_t* h, const uin
         else { out->n_ranges = hs[1]; out->bytes_out = hs[3]; }
     }
     last_n_ranges = out->n_ranges;
+    lane_last = P.lane;
 }
 
 // ---- asynchronous jobs: a ring of page-locked slots, each with its own pair of events -------------------------------------
@@ -1058,7 +1133,8 @@ void Engine::wait(IntersectResult* out) { impl_->ix_wait(out); }
 void Engine::abandon(IntersectResult* out) { impl_->ix_abandon(out); }
 void Engine::sync() {
     GFFX_CUDA(cudaSetDevice(impl_->dev));
-    GFFX_CUDA(cudaStreamSynchronize(impl_->st));
+    for (const EngineImpl::Lane& l : impl_->lanes)
+        if (l.st) GFFX_CUDA(cudaStreamSynchronize(l.st));
 }
 bool Engine::shard_buffer(int which, uint32_t k, void** dptr, uint64_t* n_elems, int* op) {
     EngineImpl* E = impl_.get();
@@ -1129,7 +1205,7 @@ void EngineImpl::gather_text(const uint64_t* ranges, uint64_t n_ranges, uint32_t
         dr = d_text_ranges.as<ulonglong2>();
     } else {
         if (n_ranges != last_n_ranges) throw Err(E_STATE, "the ranges of that result are no longer on the device: pass them explicitly");
-        dr = d_ranges.as<ulonglong2>();
+        dr = lane_buf(lane_last, &d_ranges).as<ulonglong2>();
     }
     if (n_ranges == 0) return;
     if (!ev_gather[0])

@@ -45,6 +45,8 @@ template <class T> void HostBlob<T>::release() {
 struct PendingInfo {   // what turns a job's counter block into result fields (kept with the result while it is pending)
     bool pairs_dev = false, join_only = false, match_only = true, nothing = false, no_host = false, want_pairs_host = false;
     unsigned long long pair_cap = 0;
+    const uint32_t* d_pairs = nullptr;   // the pair buffer of the job's lane
+    int lane = 0;
 };
 
 struct IntersectResult {

@@ -153,6 +153,25 @@ class EngineImpl {
     cudaEvent_t ev[12];  // [0..7] stage boundaries of one intersect call, [8],[9] around the pair expansion (K1b), [10] end of the partition pass
 
     IxJob job;
+    // ---- job lanes ---------------------------------------------------------------------------
+    // Two sets of the per-job device state (lane_bufs(): accumulators, bucketed regions, scan arrays, outputs) and two streams, so
+    // that two queued GFFX_F_ASYNC jobs run side by side: the partition pass of one fills the issue slots the join of the other
+    // leaves idle (profiles/exp_two_handles.py: -19 %).  The members ARE the active lane's buffers; lane_activate swaps them with
+    // the other lane's saved copies, so the kernels' call sites do not know about lanes.  Synchronous jobs, depth / coverage, the
+    // BED parser and the gather run on lane 0 (`st` outside a job is lane 0's stream, the one gffx_index_cuda_stream reports).
+    struct Lane {
+        std::vector<DBuf> bufs;   // the lane's buffers while it is NOT the active one
+        cudaStream_t st = nullptr;
+        uint32_t epoch = 0, epoch8 = 0;
+        bool ready = false;
+    };
+    Lane lanes[2];
+    int lane_active = 0, lane_next = 0, lane_last = 0, n_lanes = 2;
+    uint32_t epoch_start = 0;
+    std::vector<DBuf*> lane_bufs();
+    void lane_activate(int k);
+    void alloc_job_buffers();
+    DBuf& lane_buf(int lane, DBuf* member);   // `member` as lane `lane` sees it
     std::vector<AsyncSlot> slots = std::vector<AsyncSlot>(32);
     uint32_t epoch = 0, epoch8 = 0;         // filter.cuh: the rank-space arrays are tagged per job, not cleared
     unsigned long long pairs_hwm = 0;       // most pairs any job of this engine produced: sizes the pair buffer of the next one

@@ -88,7 +88,8 @@ class Combiner:
         self.group = group
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
-        self.stream = torch.cuda.ExternalStream(idx.cuda_stream)
+        self._streams = {}
+        self.device = torch.device("cuda", torch.cuda.current_device())
         self.bytes_exchanged = 0
         self._scratch = {}
         self._views = {}
@@ -112,7 +113,11 @@ class Combiner:
         if self.world == 1:
             return
         W, r = self.world, self.rank
-        with torch.cuda.stream(self.stream):
+        sp = self.idx.cuda_stream   # the open job's lane (queued jobs alternate between two streams)
+        stream = self._streams.get(sp)
+        if stream is None:
+            stream = self._streams[sp] = torch.cuda.ExternalStream(sp, device=self.device)
+        with torch.cuda.stream(stream):
             for ptr, n, op in buffers:
                 if n == 0:
                     continue
@@ -120,7 +125,7 @@ class Combiner:
                 seg = -(-n // W)
                 t = self._views.get((ptr, n * es))   # the engine's accumulators keep their addresses from job to job
                 if t is None:
-                    t = self._views[(ptr, n * es)] = torch.as_tensor(_DevView(ptr, n * es), device=self.stream.device)
+                    t = self._views[(ptr, n * es)] = torch.as_tensor(_DevView(ptr, n * es), device=self.device)
                 if op == 0:      # byte flags: NCCL's own MAX
                     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
                     self.bytes_exchanged += 2 * (W - 1) * n // W

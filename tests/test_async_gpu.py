@@ -55,6 +55,26 @@ def test_last_jobs_device_outputs_are_readable(quirk):
     assert len(got) == w.bytes_out and got == idx.gather_text(w.ranges, w.n_ranges)
 
 
+def test_two_lanes_overlap_and_keep_their_outputs(quirk):
+    """queued jobs alternate between two lanes (own buffers, own streams): big enough to really run side by side; the device
+    outputs of a job survive the job queued after it (the other lane's)"""
+    idx = quirk
+    sets = [mixed_regions(idx, 40 + k, 300_000) for k in range(3)]
+    dsets = [dev(s) for s in sets]
+    cases = [(2, False), (0, False), (1, False), (0, True), (2, False), (1, True), (0, False)]
+    want = [idx.intersect(sets[k % 3], m, i, False, None) for k, (m, i) in enumerate(cases)]
+    for rep in range(2):
+        pend = [idx.intersect(dsets[k % 3], m, i, False, None, flags=F) for k, (m, i) in enumerate(cases)]
+        if rep == 0:   # a synchronous job in between runs on lane 0, behind its queued jobs
+            mid = idx.intersect(sets[0], 2, False, False, None)
+            assert mid.n_ranges == want[0].n_ranges and np.array_equal(mid.ranges, want[0].ranges)
+        for k in (5, 6, 0, 1, 2, 3, 4):
+            r = pend[k].wait()
+            assert (r.n_pairs, r.n_roots, r.n_ranges, r.bytes_out) == (want[k].n_pairs, want[k].n_roots, want[k].n_ranges, want[k].bytes_out), (rep, k)
+            if rep == 1 and k >= 5:   # the last job of either lane: its ranges are still on the device
+                assert idx.gather_text(None, r.n_ranges) == idx.gather_text(want[k].ranges, want[k].n_ranges)
+
+
 def test_error_surfaces_at_the_wait_and_ring_limit(gffx, quirk):
     idx = quirk
     bad = (torch.tensor([999], dtype=torch.int32).cuda(), torch.tensor([1], dtype=torch.int32).cuda(), torch.tensor([2], dtype=torch.int32).cuda())
