@@ -422,6 +422,7 @@ def timed_async(c, passes, sets, steps, min_seconds):
 
     # one untimed step to estimate the step time, then loops x steps between two events
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    settle(one_step(None))   # first use of the second lane allocates its buffers
     ev0.record(c.stream)
     settle(one_step(None))
     ev1.record(c.stream)
