@@ -19,6 +19,8 @@ template <int MODE, bool INV> static void wj_set_attrs() {
     GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
     GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
     GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_root_kernel<MODE, INV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_root_kernel<MODE, INV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
 }
 static void set_kernel_attributes() {
     wj_set_attrs<0, false>(); wj_set_attrs<0, true>(); wj_set_attrs<1, false>(); wj_set_attrs<1, true>(); wj_set_attrs<2, false>();
@@ -68,13 +70,15 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     lanes[0].st = st;
     lanes[0].ready = true;
     if (const char* e = getenv("GFFX_LANES")) n_lanes = atoi(e) >= 2 ? 2 : 1;   // A/B hook: 1 = every job on lane 0
+    if (const char* e = getenv("GFFX_WJ_KERNEL")) wj_force = !strcmp(e, "rounds") ? 1 : !strcmp(e, "roots") ? 2 : 0;
+    if (const char* e = getenv("GFFX_WR_TAIL_BINS")) wj_tail_bins = (uint32_t)std::min(1 << 20, std::max(0, atoi(e)));
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     set_kernel_attributes();
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
@@ -106,7 +110,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
@@ -323,6 +327,27 @@ void EngineImpl::build_join() {
     upload(d_wj_boff, bh.boff, st);
     upload(d_wj_blk, wblk, st);
     upload(d_wj_base, wbase, st);
+    {   // rootjoin.cuh: per window, where its root run ends — the first interval of the sequence that starts at or beyond the
+        // window's end + the longest region the kernel's normal part admits (no such region reaches it); the sequence's
+        // sentinel for the last window, whose regions may start anywhere beyond the grid
+        const uint32_t fsh = jshift - WR_FB;
+        const uint64_t taillen = std::min<uint64_t>((uint64_t)wj_tail_bins << fsh, 0xFFFFFFFFull);
+        std::vector<uint32_t> rend(bh.n_win, 0);
+        size_t e0 = 0;   // first entry of the current sequence
+        for (uint32_t v = 0; v < n_v; v++) {
+            size_t sent = e0;
+            while (bh.ent_item[sent] != 0xFFFFFFFFu) sent++;
+            for (uint32_t w = jwin0[v]; w < jwin0[v + 1]; w++) {
+                if (w + 1 == jwin0[v + 1]) { rend[w] = (uint32_t)sent; continue; }
+                const uint64_t lim = ((uint64_t)(w - jwin0[v] + 1) << jshift) + taillen;
+                rend[w] = (uint32_t)(std::lower_bound(bh.ent_start.begin() + (long)e0, bh.ent_start.begin() + (long)sent, lim,
+                                                      [](uint32_t a, uint64_t b) { return (uint64_t)a < b; }) - bh.ent_start.begin());
+            }
+            e0 = sent + 1;
+        }
+        upload(d_wj_rend, rend, st);
+        GFFX_CUDA(cudaStreamSynchronize(st));
+    }
     {   // block -> the tree intervals that name it (wj_select_blocks_kernel gathers); intervals without a .gof record
         const uint32_t nb = (uint32_t)H->blocks.size();
         std::vector<uint32_t> off(nb + 1, 0), ent, orph;
@@ -352,6 +377,7 @@ void EngineImpl::build_join() {
     WC.list4 = d_wj_list4.as<uint4>();
     WC.first = d_wj_first.as<uint32_t>();
     WC.boff = d_wj_boff.as<uint32_t>();
+    WC.run_end = d_wj_rend.as<uint32_t>();
     WC.shift = bh.shift;
     WC.sub = bh.sub;
     WC.n_win = bh.n_win;
@@ -580,9 +606,18 @@ static void launch_wj2(EngineImpl* E, const uint32_t* poff, const uint2* se, uin
 }
 template <int MODE, bool INV, bool FILT>
 static void launch_wj(EngineImpl* E, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles, unsigned long long* n_pairs, uint32_t* err) {
-    // fewer than ~64 regions per window on average: most (tile, window) segments are small
-    if (n < 64ull * std::max<uint32_t>(E->WC.n_win, 1)) launch_wj2<MODE, INV, FILT, true>(E, poff, se, n, tiles, n_pairs, err);
-    else launch_wj2<MODE, INV, FILT, false>(E, poff, se, n, tiles, n_pairs, err);
+    typedef unsigned long long ull;
+    // fewer than ~64 regions per window on average: most (tile, window) segments are small -> the region-parallel kernel's SMALL form;
+    // otherwise the root-parallel kernel (rootjoin.cuh).  GFFX_WJ_KERNEL=rounds|roots forces one of them (tests, A/B runs).
+    const bool small = n < 64ull * std::max<uint32_t>(E->WC.n_win, 1);
+    if (E->wj_force == 1 || (E->wj_force == 0 && small)) {
+        if (small) launch_wj2<MODE, INV, FILT, true>(E, poff, se, n, tiles, n_pairs, err);
+        else launch_wj2<MODE, INV, FILT, false>(E, poff, se, n, tiles, n_pairs, err);
+        return;
+    }
+    FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48, E->epoch, E->epoch8};
+    wj_root_kernel<MODE, INV, FILT><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(), E->d_wj_cnt.as<ull>(), n_pairs, err,
+                                                                                E->FR, F, E->wj_tail_bins);
 }
 // `filt`: the line filter's rank-space scatter (K3a) rides on the same pass
 static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool filt, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles,

@@ -10,6 +10,7 @@
 #include "gather.cuh"
 #include "winjoin.cuh"
 #include "winjoin_build.h"
+#include "rootjoin.cuh"
 
 namespace gffx {
 
@@ -122,9 +123,11 @@ class EngineImpl {
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
 
     // ---- window-addressed root join (winjoin.cuh): what intersect uses -------------------------
-    DBuf d_wj_win0, d_wj_base, d_wj_winseq, d_wj_ent4, d_wj_list4, d_wj_fid, d_wj_first, d_wj_boff, d_wj_blk, d_wj_hit, d_wj_cnt, d_wj_off;
+    DBuf d_wj_win0, d_wj_base, d_wj_winseq, d_wj_ent4, d_wj_list4, d_wj_fid, d_wj_first, d_wj_boff, d_wj_rend, d_wj_blk, d_wj_hit, d_wj_cnt, d_wj_off;
     WinBins WC{};
     uint32_t wj_n_ent = 0;
+    int wj_force = 0;                           // GFFX_WJ_KERNEL: 0 = by job size, 1 = region-parallel rounds, 2 = root-parallel
+    uint32_t wj_tail_bins = WR_TAIL_BINS;       // GFFX_WR_TAIL_BINS: regions longer than this many fine bins take the tail path
 
     // ---- blocks ------------------------------------------------------------------------------
     DBuf d_bstart, d_bend, d_blk_sel;

@@ -63,6 +63,7 @@ struct WinBins {
     const uint4* list4;        // bin lists as records
     const uint32_t* first;     // n_win * (nb + 1)
     const uint32_t* boff;      // n_win * (nb + 1)
+    const uint32_t* run_end;   // n_win: end of the window's root run for the root-parallel kernel (rootjoin.cuh)
     uint32_t shift, sub, n_win, n_ent;
 };
 
