@@ -104,6 +104,14 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
 
 EngineImpl::~EngineImpl() {
     cudaSetDevice(dev);
+#ifdef WR_STATS
+    {
+        unsigned long long h[8];
+        cudaDeviceSynchronize();
+        cudaMemcpyFromSymbol(h, wr_stats, sizeof h);
+        fprintf(stderr, "WR_STATS roots_tested %llu iters %llu nn %llu segs %llu n_roots %llu n1 %llu n_norm %llu maxlen_sum %llu\n", h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+    }
+#endif
     for (Lane& l : lanes)
         if (l.st) cudaStreamSynchronize(l.st);
     for (DBuf& b : lanes[1 - lane_active].bufs) b.release();   // the active lane's buffers are the members, released below

@@ -25,6 +25,7 @@ namespace gffx {
 constexpr int WR_FB = 10;                   // fine bins per window: 2^WR_FB (the partition grid's shift is >= 12)
 constexpr uint32_t WR_NBF = 1u << WR_FB;
 constexpr uint32_t WR_TAIL_BINS = 8;        // a region longer than this many fine bins belongs to the tail part
+constexpr uint32_t WR_SERIAL_MAX = 48;      // a root with more positions to test than this gets the whole warp
 static_assert(2 * WR_NBF == 4 * WJ_THREADS, "the histogram scan gives every thread four counters");
 
 struct WrSmem {
@@ -157,21 +158,11 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
             if (kr[k] != 0xFFFFFFFFu) wj_sorted[S.hist[kr[k] >> 12] + (kr[k] & 0xFFFu)] = make_uint2(s[k], e[k]);
         __syncthreads();
         const uint32_t m_seg = p_hi - p_lo, n_norm = S.hist[WR_NBF];
-        // ---- 2. the rank-space scatter of the line filter (K3a), in sorted order: neighbours share the look-up's cache lines ----
-        if (FILT) {
-            const RankSeq RS = load_rank_seq(R, seq);
-            if (RS.canon && RS.cnt != 0)   // no line of a sequence without rank space can ever match
-                for (uint32_t p = tid; p < m_seg; p += WJ_THREADS) {
-                    const uint2 r = wj_sorted[p];
-                    scatter_region<MODE>(R, RS, F, seq, r.x, r.y);
-                }
-        }
         unsigned long long mytot = 0;   // this lane's part of the segment's hit total
-        // ---- 3. the roots of the window over the normal part ------------------------------------------------------------
-        // Every warp takes an equal share of the window's roots.  The set-up is lane-parallel (lane t: root t of the share — its
-        // bins, the two position ranges to test, the count of the inside bins), then the warp walks its roots: the parameters
-        // come by shuffle, both ranges are tested in ONE sweep of 32 positions where they fit, and lane t keeps root t's sum, so
-        // the global updates are lane-parallel again.
+        // ---- 2. the roots of the window over the normal part ------------------------------------------------------------
+        // One root per lane, 32 consecutive roots per warp: the lane works out its root's bins, the two position ranges to test
+        // and the count of the inside bins, tests its positions (a dozen on average) and updates the root's counter.  The warps
+        // without roots (a window has a few hundred at most) go on to the scatter below.
         if (n_norm) {
             const size_t row = (size_t)w * (nb_old + 1);
             const uint32_t l0 = __ldg(C.boff + row), nl0 = __ldg(C.boff + row + 1) - l0, j0 = __ldg(C.first + row);
@@ -180,10 +171,9 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
             const uint32_t n_roots = nl0 + (__ldg(C.run_end + w) - j0);
             const uint32_t maxlen = S.maxlen, re_max = S.re_max;
             const uint32_t* H = S.hist;
-            const uint32_t per = (n_roots + WJ_WARPS - 1) / WJ_WARPS, i_end = min((warp + 1u) * per, n_roots);
-            for (uint32_t base = warp * per; base < i_end; base += 32) {
+            for (uint32_t base = warp * 32u; base < n_roots; base += WJ_THREADS) {
                 const uint32_t i = base + lane;
-                bool valid = i < i_end;
+                bool valid = i < n_roots;
                 uint4 v = make_uint4(0, 0, 0, 0);
                 if (valid) {
                     if (i < nl0) {   // the roots that reach into the window from the left: members of its first bin's list
@@ -222,15 +212,26 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
                     }
                 }
                 uint32_t mine = 0;   // overlap hits | mode hits << 16 among the tested positions (a segment has <= 4096 regions)
-                for (uint32_t todo = __ballot_sync(0xffffffffu, valid && (ra | rb)); todo; todo &= todo - 1u) {
+                const uint32_t a0 = ra & 0xFFFFu, n1 = (ra >> 16) - a0, b0 = rb & 0xFFFFu, nn = n1 + (rb >> 16) - b0;
+                const bool big = valid && nn > WR_SERIAL_MAX;
+                // a root with few positions to test (the rule: ~a dozen) walks them itself, 32 roots side by side ...
+                if (valid && !big)
+#pragma unroll 1
+                    for (uint32_t l = 0; l < nn; l++) {
+                        const uint2 q = wj_sorted[l < n1 ? a0 + l : b0 + (l - n1)];
+                        const bool ov = rs < q.y && re > q.x;
+                        mine += (ov ? 1u : 0u) + ((ov && wj_mode<MODE>(rs, re, q.x, q.y)) ? 0x10000u : 0u);
+                    }
+                // ... one with many (an inverted root interval, a tile crowded into a few bins) has the warp's 32 lanes test them
+                for (uint32_t todo = __ballot_sync(0xffffffffu, big); todo; todo &= todo - 1u) {
                     const int t = __ffs(todo) - 1;
                     const uint32_t ts = __shfl_sync(0xffffffffu, rs, t), te = __shfl_sync(0xffffffffu, re, t);
-                    const uint32_t ta = __shfl_sync(0xffffffffu, ra, t), tb = __shfl_sync(0xffffffffu, rb, t);
-                    const uint32_t a0 = ta & 0xFFFFu, n1 = (ta >> 16) - a0, b0 = tb & 0xFFFFu, nn = n1 + (tb >> 16) - b0;
+                    const uint32_t ta0 = __shfl_sync(0xffffffffu, a0, t), tn1 = __shfl_sync(0xffffffffu, n1, t);
+                    const uint32_t tb0 = __shfl_sync(0xffffffffu, b0, t), tnn = __shfl_sync(0xffffffffu, nn, t);
                     uint32_t acc = 0;
-                    for (uint32_t off = 0; off < nn; off += 32) {
-                        const uint32_t l = off + lane;
-                        const uint2 q = l < nn ? wj_sorted[l < n1 ? a0 + l : b0 + (l - n1)] : make_uint2(0xFFFFFFFFu, 0u);
+#pragma unroll 1
+                    for (uint32_t l = lane; l < tnn; l += 32) {
+                        const uint2 q = wj_sorted[l < tn1 ? ta0 + l : tb0 + (l - tn1)];
                         const bool ov = ts < q.y && te > q.x;
                         acc += (ov ? 1u : 0u) + ((ov && wj_mode<MODE>(ts, te, q.x, q.y)) ? 0x10000u : 0u);
                     }
@@ -246,7 +247,7 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
                 }
             }
         }
-        // ---- 4. the tail part, region-parallel against the bin lists ------------------------------------------------------
+        // ---- 3. the tail part, region-parallel against the bin lists ------------------------------------------------------
         if (n_norm < m_seg) {
             for (;;) {
                 uint32_t t = 0;
@@ -259,6 +260,15 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
                 const unsigned long long nh = wj_round_global<MODE, INVERT>(C, w, lo, r, have, lane, ent_hit, ent_cnt);
                 if (lane == 0) mytot += nh;
             }
+        }
+        // ---- 4. the rank-space scatter of the line filter (K3a), in sorted order: neighbours share the look-up's cache lines ----
+        if (FILT) {
+            const RankSeq RS = load_rank_seq(R, seq);
+            if (RS.canon && RS.cnt != 0)   // no line of a sequence without rank space can ever match
+                for (uint32_t p = tid; p < m_seg; p += WJ_THREADS) {
+                    const uint2 r = wj_sorted[p];
+                    scatter_region<MODE>(R, RS, F, seq, r.x, r.y);
+                }
         }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) mytot += __shfl_xor_sync(0xffffffffu, mytot, d);
