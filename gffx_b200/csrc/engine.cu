@@ -19,8 +19,9 @@ template <int MODE, bool INV> static void wj_set_attrs() {
     GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
     GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
     GFFX_CUDA(cudaFuncSetAttribute(wj_count_kernel<MODE, INV, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
-    GFFX_CUDA(cudaFuncSetAttribute(wj_root_kernel<MODE, INV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
-    GFFX_CUDA(cudaFuncSetAttribute(wj_root_kernel<MODE, INV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_root_kernel<MODE, INV, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_root_kernel<MODE, INV, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WJ_DYN_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(wj_root_kernel<MODE, INV, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WJ_DYN_SMEM + WR_SLICE_SMEM)));
 }
 static void set_kernel_attributes() {
     wj_set_attrs<0, false>(); wj_set_attrs<0, true>(); wj_set_attrs<1, false>(); wj_set_attrs<1, true>(); wj_set_attrs<2, false>();
@@ -71,13 +72,14 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     lanes[0].ready = true;
     if (const char* e = getenv("GFFX_LANES")) n_lanes = atoi(e) >= 2 ? 2 : 1;   // A/B hook: 1 = every job on lane 0
     if (const char* e = getenv("GFFX_WJ_KERNEL")) wj_force = !strcmp(e, "rounds") ? 1 : !strcmp(e, "roots") ? 2 : 0;
+    if (const char* e = getenv("GFFX_WR_SLICE")) wj_slices = atoi(e) != 0;
     if (const char* e = getenv("GFFX_WR_TAIL_BINS")) wj_tail_bins = (uint32_t)std::min(1 << 20, std::max(0, atoi(e)));
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     set_kernel_attributes();
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
-                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_fX, &d_fdir, &d_fseqs, &d_wr_xw0, &d_wr_xlen, &d_wr_xoff, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
                     &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
@@ -117,7 +119,7 @@ EngineImpl::~EngineImpl() {
     for (DBuf& b : lanes[1 - lane_active].bufs) b.release();   // the active lane's buffers are the members, released below
     for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
-                    &d_fX, &d_fdir, &d_fseqs, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
+                    &d_fX, &d_fdir, &d_fseqs, &d_wr_xw0, &d_wr_xlen, &d_wr_xoff, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
                     &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
@@ -472,6 +474,33 @@ void EngineImpl::build_lines() {
         X.insert(X.end(), v.begin(), v.end());
     }
     f_slots = slot;
+    {   // rootjoin.cuh: per window of the partition grid, its part of X and the fine-bin offsets into it
+        const uint32_t n_win = WG.n_win, fsh = WG.shift - WR_FB;
+        std::vector<uint32_t> xw0(std::max<uint32_t>(n_win, 1), 0), xlen(std::max<uint32_t>(n_win, 1), 0xFFFFFFFFu);
+        std::vector<uint16_t> xoff((size_t)std::max<uint32_t>(n_win, 1) * WR_XOFF_STRIDE, 0);
+        for (size_t v = 0; v < n_seqs; v++) {
+            const auto& xv = xs[v];
+            for (uint32_t w = h_win0[v]; w < h_win0[v + 1]; w++) {
+                const uint64_t lo = (uint64_t)(w - h_win0[v]) << WG.shift;
+                const bool last = w + 1 == h_win0[v + 1];
+                auto below = [&](uint64_t c) { return (size_t)(std::lower_bound(xv.begin(), xv.end(), c, [](uint32_t a, uint64_t b) { return (uint64_t)a < b; }) - xv.begin()); };
+                const size_t i0 = below(lo), i1 = last ? xv.size() : below(lo + (1ull << WG.shift));
+                xw0[w] = seqs[v].x0 + (uint32_t)i0;
+                if (i1 - i0 > WR_SLICE_CAP - 4 || i1 - i0 > 0xFFFFu) continue;   // keeps the global look-up
+                xlen[w] = (uint32_t)(i1 - i0);
+                uint16_t* row = xoff.data() + (size_t)w * WR_XOFF_STRIDE;
+                for (uint32_t b = 0; b < WR_NBF; b++) row[b] = (uint16_t)(std::min(below(lo + ((uint64_t)b << fsh)), i1) - i0);
+                row[WR_NBF] = (uint16_t)(i1 - i0);
+            }
+        }
+        upload(d_wr_xw0, xw0, st);
+        upload(d_wr_xlen, xlen, st);
+        upload(d_wr_xoff, xoff, st);
+        GFFX_CUDA(cudaStreamSynchronize(st));
+        XS.xw0 = d_wr_xw0.as<uint32_t>();
+        XS.xlen = d_wr_xlen.as<uint32_t>();
+        XS.xoff = d_wr_xoff.as<uint16_t>();
+    }
     X.insert(X.end(), 8, 0u);   // rank_lb (filter.cuh) reads up to 4 entries past a bin
     std::vector<uint32_t> iS(n, 0), iE(n, 0);
     const size_t n_chunks = n >= (1u << 16) ? T : 1;
@@ -624,8 +653,12 @@ static void launch_wj(EngineImpl* E, const uint32_t* poff, const uint2* se, uint
         return;
     }
     FilterArrays F{E->d_A.as<ull>(), E->d_B.as<ull>(), E->d_Ms.as<uint8_t>(), E->d_Me.as<uint8_t>(), E->d_small.as<uint32_t>() + 48, E->epoch, E->epoch8};
-    wj_root_kernel<MODE, INV, FILT><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(), E->d_wj_cnt.as<ull>(), n_pairs, err,
-                                                                                E->FR, F, E->wj_tail_bins);
+    if (FILT && E->wj_slices)   // the window's part of the rank space in shared memory (rootjoin.cuh); GFFX_WR_SLICE=0: global look-ups
+        wj_root_kernel<MODE, INV, FILT, FILT><<<tiles, WJ_THREADS, WJ_DYN_SMEM + WR_SLICE_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(), E->d_wj_cnt.as<ull>(),
+                                                                                                       n_pairs, err, E->FR, F, E->wj_tail_bins, E->XS);
+    else
+        wj_root_kernel<MODE, INV, FILT, false><<<tiles, WJ_THREADS, WJ_DYN_SMEM, E->st>>>(E->WC, poff, se, n, E->d_wj_hit.as<uint8_t>(), E->d_wj_cnt.as<ull>(), n_pairs, err,
+                                                                                          E->FR, F, E->wj_tail_bins, E->XS);
 }
 // `filt`: the line filter's rank-space scatter (K3a) rides on the same pass
 static void launch_wj_mode(EngineImpl* E, int mode, bool invert, bool filt, const uint32_t* poff, const uint2* se, uint64_t n, unsigned tiles,

@@ -136,6 +136,9 @@ class EngineImpl {
     // ---- lines + filter rank space -----------------------------------------------------------
     DBuf d_ln_flags, d_ln_blk, d_ln_type, d_ln_iseq, d_ln_S, d_ln_E, d_ln_iS, d_ln_iE, d_ln_off, d_ln_len;
     DBuf d_fX, d_fdir, d_fseqs;
+    DBuf d_wr_xw0, d_wr_xlen, d_wr_xoff;   // rootjoin.cuh: per window its part of X (RankSlices)
+    RankSlices XS{};
+    bool wj_slices = true;                 // GFFX_WR_SLICE=0: the root-parallel kernel looks ranks up in global memory
     uint32_t f_slots = 0;
     RankSpace FR{};
     LineArrays LA{};

@@ -97,11 +97,10 @@ struct FilterArrays {
 __device__ __forceinline__ unsigned long long tag_max(uint32_t epoch, uint32_t seq) { return ((unsigned long long)epoch << 8) | seq; }
 __device__ __forceinline__ unsigned long long tag_min(uint32_t epoch, uint32_t seq) { return ((unsigned long long)(~epoch & EPOCH_MAX) << 8) | seq; }
 
-// one region (qs, qe) of sequence `seq` onto the rank space: 1-3 scattered L2 updates
+// one region (qs, qe) of sequence `seq` onto the rank space: 1-3 scattered L2 updates; (lb, eq) = rank_lb of qs
 template <int MODE>
-__device__ __forceinline__ void scatter_region(const RankSpace& R, const RankSeq& S, const FilterArrays& F, uint32_t seq, uint32_t qs, uint32_t qe) {
-    bool eq;
-    const uint32_t lb = rank_lb(R, S, qs, &eq);
+__device__ __forceinline__ void scatter_apply(const RankSpace& R, const RankSeq& S, const FilterArrays& F, uint32_t seq, uint32_t qs, uint32_t qe,
+                                              uint32_t lb, bool eq) {
     const uint32_t slot = S.slot0 + lb;
     if (MODE == 0) {
         atomicMax(F.A + slot, (tag_max(F.epoch, seq) << TAG_MAX_SHIFT) | ((unsigned long long)qe + 1ull));
@@ -117,6 +116,12 @@ __device__ __forceinline__ void scatter_region(const RankSpace& R, const RankSeq
             *F.any_inv = 1u;
         }
     }
+}
+template <int MODE>
+__device__ __forceinline__ void scatter_region(const RankSpace& R, const RankSeq& S, const FilterArrays& F, uint32_t seq, uint32_t qs, uint32_t qe) {
+    bool eq;
+    const uint32_t lb = rank_lb(R, S, qs, &eq);
+    scatter_apply<MODE>(R, S, F, seq, qs, qe, lb, eq);
 }
 
 struct LineArrays {

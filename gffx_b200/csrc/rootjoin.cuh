@@ -34,7 +34,7 @@ struct WrSmem {
     unsigned long long tot;
     uint32_t w_first, w_last;
     uint32_t maxlen, re_max;         // over the normal part: longest region, largest end
-    uint32_t next_tail;              // tail rounds are handed to the warps in arrival order
+    uint32_t next_tail, next_scat;   // tail rounds and scatter chunks are handed to the warps in arrival order
 };
 
 // mode test of src/commands/intersect.rs:145-158 alone
@@ -71,16 +71,65 @@ __device__ __noinline__ unsigned long long wj_round_global(const WinBins& C, uin
     return tot;
 }
 
+// ---- the window's slice of the rank space in shared memory ---------------------------------------------------------------
+// The line filter's region scatter (filter.cuh) needs lb(qs) = #(X < qs) over the sequence's coordinate set X.  From global
+// memory that is a directory cell and then the values it points at: two dependent L2 (often DRAM) round trips per region,
+// 44 % of this kernel's stall samples (profiles/r02i).  A (tile, window) segment only ever asks about ONE window's part of X
+// (a few thousand values), so the CTA brings that part and a per-fine-bin offset table into shared memory with two bulk
+// asynchronous copies (cp.async.bulk, completion on an mbarrier: the copy engine moves the bytes while the warps sort the
+// tile) and the look-up becomes a short binary search in shared memory.  A window whose part exceeds WR_SLICE_CAP values
+// keeps the global look-up.
+constexpr uint32_t WR_SLICE_CAP = 9216;        // values of X a CTA can hold (36 KB)
+constexpr uint32_t WR_XOFF_STRIDE = 1032;      // u16 cells per window in the offset table: WR_NBF + 1 used, rows 16-byte multiples
+constexpr size_t WR_SLICE_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)WR_XOFF_STRIDE * 2;
+struct RankSlices {
+    const uint32_t* xw0;    // n_win: index into RankSpace::X of the window's first value
+    const uint32_t* xlen;   // n_win: values in the window's part; 0xFFFFFFFF: too many for shared memory
+    const uint16_t* xoff;   // n_win * WR_XOFF_STRIDE: [b] = values of the part below fine bin b's first base, [WR_NBF] = xlen
+};
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {   // 16-byte aligned, bytes % 16 == 0
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes),
+                 "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// lb = #(part < v) for a v of fine bin b; *eq = (part[lb] == v).  sx[k] = value k of the window's part
+__device__ __forceinline__ uint32_t rank_lb_slice(const uint32_t* sx, const uint16_t* soff, uint32_t xlen, uint32_t b, uint32_t v, bool* eq) {
+    uint32_t lo = soff[b], hi = soff[b + 1];
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (sx[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    *eq = lo < xlen && sx[lo] == v;   // beyond the part: the next value lies in a later window, above v
+    return lo;
+}
+
 #ifndef WR_MIN_CTAS
 #define WR_MIN_CTAS 3
 #endif
-template <int MODE, bool INVERT, bool FILT>
-__global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
+template <int MODE, bool INVERT, bool FILT, bool SLICE>
+__global__ void __launch_bounds__(WJ_THREADS, SLICE ? 2 : WR_MIN_CTAS)
     wj_root_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint2* __restrict__ qse, uint64_t n, uint8_t* ent_hit,
                    unsigned long long* ent_cnt, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ err, RankSpace R, FilterArrays F,
-                   uint32_t tail_bins) {
-    extern __shared__ __align__(16) uint2 wj_sorted[];   // WJ_DYN_SMEM bytes: the (tile, window) regions ordered by key
+                   uint32_t tail_bins, RankSlices XS) {
+    extern __shared__ __align__(16) uint2 wj_sorted[];   // WJ_DYN_SMEM bytes: the (tile, window) regions ordered by key; SLICE: + WR_SLICE_SMEM
     __shared__ __align__(16) WrSmem S;
+    __shared__ __align__(8) uint64_t mbar;
+    uint32_t* const sx_raw = reinterpret_cast<uint32_t*>(wj_sorted + WJ_TILE);                  // the window's part of X, from a 16-byte boundary
+    uint16_t* const soff = reinterpret_cast<uint16_t*>(sx_raw + WR_SLICE_CAP + 8);
+    uint32_t mbar_phase = 0;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t tile0 = blockIdx.x * (uint32_t)WJ_TILE;
     const uint32_t m = (uint32_t)min((uint64_t)WJ_TILE, n - tile0);
@@ -95,7 +144,10 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
             nf += __syncthreads_count(o <= tile0);
             nl += __syncthreads_count(o <= tile0 + m - 1);
         }
-        if (tid == 0) { S.w_first = (uint32_t)nf - 1u; S.w_last = (uint32_t)nl - 1u; }
+        if (tid == 0) {
+            S.w_first = (uint32_t)nf - 1u; S.w_last = (uint32_t)nl - 1u;
+            if (SLICE) mbar_init(&mbar, 1);
+        }
     }
     __syncthreads();
     const uint32_t w_first = S.w_first, w_last = S.w_last;
@@ -109,6 +161,25 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
         const uint32_t seq = __ldg(C.win_seq + w);
         const uint32_t lo = (w - __ldg(C.win0 + seq)) << C.shift;
         const bool is_last = w + 1 == __ldg(C.win0 + seq + 1);   // its last bin also holds the regions that start beyond the grid
+        RankSeq RS{};
+        bool filt = false, use_slice = false;   // no line of a sequence without rank space can ever match
+        uint32_t xlen = 0, xw0 = 0;
+        if (FILT) {
+            RS = load_rank_seq(R, seq);
+            filt = RS.canon && RS.cnt != 0;
+            if (SLICE && filt) {
+                xlen = __ldg(XS.xlen + w);
+                xw0 = __ldg(XS.xw0 + w);
+                use_slice = xlen != 0xFFFFFFFFu;
+                if (use_slice && tid == 0) {   // the previous window's readers of the buffers are behind the barrier that ended it
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    const uint32_t bytes = (((xw0 & 3u) + xlen + 1u) * 4u + 15u) & ~15u;   // X is padded: reading a few values on is safe
+                    mbar_expect_tx(&mbar, bytes + WR_XOFF_STRIDE * 2u);
+                    bulk_g2s(sx_raw, R.X + (xw0 & ~3u), bytes, &mbar);
+                    bulk_g2s(soff, XS.xoff + (size_t)w * WR_XOFF_STRIDE, WR_XOFF_STRIDE * 2u, &mbar);
+                }
+            }
+        }
         // thread t holds the tile elements 2 * (k * THREADS + t) and the next one, k < QPT / 2 (as wj_count_kernel does); they are
         // loaded per window — a tile lies in one window but for a few, and the registers are free again after the sort
         uint32_t s[WJ_QPT], e[WJ_QPT];
@@ -126,7 +197,7 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
         }
         // ---- 1. counting sort of the segment by key = fine bin of the start (+ WR_NBF: tail part) -------------------------
         *reinterpret_cast<uint4*>(&S.hist[4 * tid]) = make_uint4(0, 0, 0, 0);
-        if (tid == 0) { S.hist[2 * WR_NBF] = 0; S.maxlen = 0; S.re_max = 0; S.tot = 0; S.next_tail = 0; }
+        if (tid == 0) { S.hist[2 * WR_NBF] = 0; S.maxlen = 0; S.re_max = 0; S.tot = 0; S.next_tail = 0; S.next_scat = 0; }
         __syncthreads();
         uint32_t kr[WJ_QPT];   // key << 12 | rank among the segment's regions of that key
         uint32_t my_len = 0, my_re = 0;
@@ -262,13 +333,35 @@ __global__ void __launch_bounds__(WJ_THREADS, WR_MIN_CTAS)
             }
         }
         // ---- 4. the rank-space scatter of the line filter (K3a), in sorted order: neighbours share the look-up's cache lines ----
-        if (FILT) {
-            const RankSeq RS = load_rank_seq(R, seq);
-            if (RS.canon && RS.cnt != 0)   // no line of a sequence without rank space can ever match
-                for (uint32_t p = tid; p < m_seg; p += WJ_THREADS) {
-                    const uint2 r = wj_sorted[p];
-                    scatter_region<MODE>(R, RS, F, seq, r.x, r.y);
+        // Chunks of 64 positions go to the warps in arrival order (the warps that had roots or tail rounds come later and take
+        // less); a lane looks up two regions side by side, so that two chains of dependent loads are in flight per thread.
+        if (FILT && filt) {
+            const uint32_t* sx = sx_raw + (xw0 & 3u);
+            const uint32_t rank0 = xw0 - RS.x0;   // rank of the part's first value within the sequence
+            if (SLICE && use_slice) {
+                mbar_wait(&mbar, mbar_phase);
+                mbar_phase ^= 1u;
+            }
+            for (;;) {
+                uint32_t c = 0;
+                if (lane == 0) c = atomicAdd(&S.next_scat, 1u);
+                c = __shfl_sync(0xffffffffu, c, 0);
+                const uint32_t p = 64u * c + lane;
+                if (64u * c >= m_seg) break;
+                const bool h0 = p < m_seg, h1 = p + 32u < m_seg;
+                const uint2 r0 = wj_sorted[h0 ? p : 64u * c], r1 = wj_sorted[h1 ? p + 32u : 64u * c];
+                bool eq0, eq1;
+                uint32_t lb0, lb1;
+                if (SLICE && use_slice) {
+                    lb0 = rank0 + rank_lb_slice(sx, soff, xlen, min((r0.x - lo) >> fsh, WR_NBF - 1u), r0.x, &eq0);
+                    lb1 = rank0 + rank_lb_slice(sx, soff, xlen, min((r1.x - lo) >> fsh, WR_NBF - 1u), r1.x, &eq1);
+                } else {
+                    lb0 = rank_lb(R, RS, r0.x, &eq0);
+                    lb1 = rank_lb(R, RS, r1.x, &eq1);
                 }
+                if (h0) scatter_apply<MODE>(R, RS, F, seq, r0.x, r0.y, lb0, eq0);
+                if (h1) scatter_apply<MODE>(R, RS, F, seq, r1.x, r1.y, lb1, eq1);
+            }
         }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) mytot += __shfl_xor_sync(0xffffffffu, mytot, d);
