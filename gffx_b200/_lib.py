@@ -104,6 +104,7 @@ SIGNATURES = {
     "gffx_index_seq_roots": (C.c_int, vp, C.c_uint32, C.POINTER(u32p), u64p),
     "gffx_parse_bed_intersect": (C.c_int, vp, C.c_char_p, C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u32p), u64p),
     "gffx_parse_bed_counts": (C.c_int, vp, C.c_char_p, C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u32p), u64p),
+    "gffx_parse_reads": (C.c_int, vp, C.c_char_p, C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u32p), u64p, u64p),
     "gffx_parse_bed_device": (C.c_int, vp, C.c_char_p, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), u64p),
     "gffx_bed_parse_stat": (C.c_double, vp, C.c_int),
     "gffx_parse_region": (C.c_int, vp, C.c_char_p, u32p, u32p, u32p),

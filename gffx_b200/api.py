@@ -265,6 +265,15 @@ class TreeIndexData:
         """BED dialect of depth/coverage: src/commands/depth.rs:449-495, src/commands/coverage.rs:222-255"""
         return self._parse(lib.gffx_parse_bed_counts, bed_path)
 
+    def parse_reads(self, path, stats: Optional[dict] = None):
+        """Read intervals of a SAM / BAM file: what process_bam (src/commands/depth.rs:297-423) and collect_by_root_from_bam
+        (src/commands/coverage.rs:125-205) take from rust-htslib — (sequence number, pos, reference_end) per kept record."""
+        st = (C.c_uint64 * 5)()
+        out = self._parse(lambda h, p, a, b, c, n: lib.gffx_parse_reads(h, p, a, b, c, n, st), path)
+        if stats is not None:
+            stats.update(records=int(st[0]), unmapped=int(st[1]), unknown_ref=int(st[2]), skipped=int(st[3]), container=int(st[4]))
+        return out
+
     def parse_bed_device(self, bed_path, dialect: int = 0, device: int = 0):
         """The same dialects parsed on the device (K9, bedparse.cuh): dialect 0 = parse_bed_file, 1 = depth / coverage.  Returns three
         torch int32 CUDA tensors (views of engine-owned memory, valid until the next parse on this handle) — pass them as regions."""

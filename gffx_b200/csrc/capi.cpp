@@ -3,6 +3,7 @@
 #include <thread>
 #include "../../include/gffx_b200.h"
 #include "engine.h"
+#include "reads.h"
 
 using namespace gffx;
 
@@ -177,6 +178,17 @@ int gffx_parse_bed_counts(const gffx_index* idx, const char* bed_path, uint32_t*
         parse_bed_counts(bed_path, idx->host().seq_num, host_threads(), &R);
         *chr = dup_u32(R.chr); *start = dup_u32(R.start); *end = dup_u32(R.end);
         *n = R.size();
+    });
+}
+int gffx_parse_reads(const gffx_index* idx, const char* path, uint32_t** chr, uint32_t** start, uint32_t** end, uint64_t* n, uint64_t stats[5]) {
+    return guard([&] {
+        need(idx, "idx"); need(path, "path"); need(chr, "chr"); need(start, "start"); need(end, "end"); need(n, "n");
+        Regions R;
+        ReadStats st;
+        read_alignments(path, idx->host().seq_num, host_threads(), &R, &st);
+        *chr = dup_u32(R.chr); *start = dup_u32(R.start); *end = dup_u32(R.end);
+        *n = R.size();
+        if (stats) { stats[0] = st.records; stats[1] = st.unmapped; stats[2] = st.unknown_ref; stats[3] = st.skipped; stats[4] = (uint64_t)st.format; }
     });
 }
 int gffx_parse_region(const gffx_index* idx, const char* region, uint32_t* chr, uint32_t* start, uint32_t* end) {
@@ -456,9 +468,8 @@ static int counts_run(const gffx_counts_args* a, int kind) {
         size_t dot = src.rfind('.');
         if (dot != std::string::npos) ext = src.substr(dot + 1);
         for (auto& c : ext) c = (char)tolower(c);
-        if (ext == "bam" || ext == "sam" || ext == "cram")
-            throw Err(E_ARG, "BAM/SAM/CRAM sources need htslib, which this build does not link; convert to BED");
-        if (ext != "bed") throw Err(E_ARG, "Unsupported file type: \"" + src + "\". Expected .bam/.sam/.cram or .bed");
+        const bool reads = ext == "bam" || ext == "sam" || ext == "cram";   // depth.rs:589: one reader for the three
+        if (!reads && ext != "bed") throw Err(E_ARG, "Unsupported file type: \"" + src + "\". Expected .bam/.sam/.cram or .bed");
         gffx_index* idx = nullptr;
         if (int rc = gffx_index_open(a->input, a->device, &idx)) throw Err(rc, g_err);
         std::unique_ptr<gffx_index> hold(idx);
@@ -467,7 +478,15 @@ static int counts_run(const gffx_counts_args* a, int kind) {
         const uint32_t *qc = nullptr, *qs = nullptr, *qe = nullptr;
         uint64_t nq = 0;
         uint32_t qflags = 0;
-        if (!getenv("GFFX_HOST_BED")) {   // K9: parsed on the device, the regions stay there
+        if (reads) {
+            ReadStats rs;
+            read_alignments(src, idx->host().seq_num, a->threads > 0 ? a->threads : host_threads(), &R, &rs);
+            qc = R.chr.data(); qs = R.start.data(); qe = R.end.data(); nq = R.size();
+            if (a->verbose)
+                fprintf(stderr, "[INFO] %llu alignment records: %llu kept, %llu unmapped, %llu on sequences the index lacks, %llu without a usable interval\n",
+                        (unsigned long long)rs.records, (unsigned long long)nq, (unsigned long long)rs.unmapped, (unsigned long long)rs.unknown_ref,
+                        (unsigned long long)rs.skipped);
+        } else if (!getenv("GFFX_HOST_BED")) {   // K9: parsed on the device, the regions stay there
             idx->engine()->parse_bed_device(src, 1, &qc, &qs, &qe, &nq);
             qflags = GFFX_F_DEVICE_INPUT;
         } else {

@@ -127,6 +127,15 @@ int gffx_parse_bed_counts(const gffx_index* idx, const char* bed_path, uint32_t*
 int gffx_parse_bed_device(gffx_index* idx, const char* bed_path, int dialect, const uint32_t** d_chr, const uint32_t** d_start,
                           const uint32_t** d_end, uint64_t* n);
 double gffx_bed_parse_stat(const gffx_index* idx, int what);
+/* Alignment files as the read source of depth / coverage: SAM text, BAM, bgzip-ed or gzip-ed SAM (decided by content, as
+ * hts_open does).  Replaces what process_bam (src/commands/depth.rs:297-423) and collect_by_root_from_bam
+ * (src/commands/coverage.rs:125-205) get from rust-htslib: one (sequence number, pos, reference_end) triple per record, with
+ * the skips of depth.rs:335-366 (unmapped, no target, a target name the index lacks, pos < 0, end <= pos), clamped to u32, in
+ * file order.  BGZF blocks are inflated by the library's own decoder on all host threads, CRC-32 checked.  CRAM: GFFX_E_ARG.
+ * stats (may be NULL): [0] records seen, [1] unmapped / no target, [2] unknown target name, [3] pos < 0 or end <= pos,
+ * [4] container (0 text, 1 BGZF, 2 gzip).  Output arrays are library-owned; free with gffx_free(). */
+int gffx_parse_reads(const gffx_index* idx, const char* path, uint32_t** chr, uint32_t** start, uint32_t** end, uint64_t* n,
+                     uint64_t stats[5]);
 /* parse_region, src/commands/intersect.rs:172-198 */
 int gffx_parse_region(const gffx_index* idx, const char* region, uint32_t* chr, uint32_t* start, uint32_t* end);
 void gffx_free(void* p);
@@ -293,7 +302,7 @@ int gffx_intersect_run(const gffx_intersect_args* args);
 
 typedef struct {
     const char* input;   /* -i */
-    const char* source;  /* -s (.bed; .bam/.sam/.cram need htslib: GFFX_E_ARG here) */
+    const char* source;  /* -s: .bed, or .bam / .sam (gffx_parse_reads); .cram: GFFX_E_ARG (not decoded) */
     const char* output;  /* -o, NULL = stdout */
     uint32_t bin_shift;  /* accepted, cannot change results (depth.rs:163-191) */
     int threads;         /* -t: host parse threads */

@@ -2,6 +2,7 @@
 // TEST INFRASTRUCTURE ONLY: loaded by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 // --impl reference legs; never by the product library.
 #include "gffx_oracle.hpp"
+#include "reads_oracle.hpp"
 #include <cstdlib>
 #include <omp.h>
 
@@ -142,6 +143,17 @@ int orc_parse_bed_dc(void* hv, const char* bed, uint32_t** out, uint64_t* n) {
             Region r;
             if (off[i] < off[i + 1] && parse_bed_line_dc(f.data + off[i], off[i + 1] - off[i], h->idx.seqid_to_num, r)) v.push_back(r);
         }
+        uint32_t* p = (uint32_t*)malloc(std::max<size_t>(1, v.size()) * 12);
+        for (size_t i = 0; i < v.size(); i++) { p[3 * i] = v[i].chr; p[3 * i + 1] = v[i].start; p[3 * i + 2] = v[i].end; }
+        *out = p; *n = v.size();
+    });
+}
+
+// read intervals of a SAM / BAM file (reads_oracle.hpp: process_bam's record rules, src/commands/depth.rs:335-366)
+int orc_parse_reads(void* hv, const char* path, uint32_t** out, uint64_t* n) {
+    return guard([&] {
+        Handle* h = (Handle*)hv;
+        auto v = orc_reads::read_alignments(path, h->idx.seqid_to_num);
         uint32_t* p = (uint32_t*)malloc(std::max<size_t>(1, v.size()) * 12);
         for (size_t i = 0; i < v.size(); i++) { p[3 * i] = v[i].chr; p[3 * i + 1] = v[i].start; p[3 * i + 2] = v[i].end; }
         *out = p; *n = v.size();

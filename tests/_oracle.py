@@ -22,6 +22,7 @@ _lib.orc_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
 _lib.orc_seq_intervals.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(_u32p), _u64p]
 _lib.orc_parse_bed_intersect.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(_u32p), _u64p]
 _lib.orc_parse_bed_dc.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(_u32p), _u64p]
+_lib.orc_parse_reads.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(_u32p), _u64p]
 _lib.orc_query_features.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.POINTER(_u32p), _u64p]
 _lib.orc_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_char_p,
                                C.POINTER(_u64p), _u64p, _u64p, _u64p]
@@ -113,6 +114,12 @@ class Oracle:
     def parse_bed_counts(self, bed):
         p, n = _u32p(), C.c_uint64()
         _check(_lib.orc_parse_bed_dc(self._h, str(bed).encode(), C.byref(p), C.byref(n)))
+        t = _take_triples(p, n.value)
+        return t[:, 0].copy(), t[:, 1].copy(), t[:, 2].copy()
+
+    def parse_reads(self, path):
+        p, n = _u32p(), C.c_uint64()
+        _check(_lib.orc_parse_reads(self._h, str(path).encode(), C.byref(p), C.byref(n)))
         t = _take_triples(p, n.value)
         return t[:, 0].copy(), t[:, 1].copy(), t[:, 2].copy()
 
