@@ -13,7 +13,8 @@ struct CountsState {
     DBuf d_rank, d_cov, d_X, d_dir;
     DBuf d_u_space, d_u_chrom, d_u_blk, d_u_base, d_irr_base, d_u_line0, d_u_seg0, d_l_fs, d_l_fe, d_l_sfs, d_l_sfe, d_g_s, d_g_e, d_g_ss, d_g_se;
     DBuf d_id_unit0, d_id_units, d_irr_grp, d_irr_pos, d_grp_off, d_grp_seq, d_grp_s, d_grp_e, d_blk_space;
-    DJoin gaps, irr;
+    DJoin irr;
+    DBuf d_gs_first, d_gap_a, d_gap_b, d_gap_seg, d_irr_blk, d_u_rs, d_u_re;
     // ---- accumulators of the running job ----
     DBuf d_Hs, d_He, d_G, d_S, d_E, d_bits, d_diff, d_P, d_routed, d_scratch, d_err;
     DBuf r_chrom, r_start, r_end, r_value, r_flag, r_pos, o_id, o_chrom, o_start, o_end, o_value;
@@ -26,7 +27,7 @@ struct CountsState {
 
     std::vector<DBuf*> all() {
         return {&d_rank, &d_cov, &d_X, &d_dir, &d_u_space, &d_u_chrom, &d_u_blk, &d_u_base, &d_irr_base, &d_u_line0, &d_u_seg0, &d_l_fs, &d_l_fe, &d_l_sfs,
-                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
+                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_gs_first, &d_gap_a, &d_gap_b, &d_gap_seg, &d_irr_blk, &d_u_rs, &d_u_re, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
                 &d_grp_s, &d_grp_e, &d_blk_space, &d_Hs, &d_He, &d_G, &d_S, &d_E, &d_bits, &d_diff, &d_P, &d_routed, &d_scratch, &d_err,
                 &r_chrom, &r_start, &r_end, &r_value, &r_flag, &r_pos, &o_id, &o_chrom, &o_start, &o_end, &o_value};
     }
@@ -36,7 +37,6 @@ void counts_release(EngineImpl* E) {
     CountsState* C = E->counts;
     if (!C) return;
     for (DBuf* b : C->all()) b->release();
-    C->gaps.release();
     C->irr.release();
     if (C->ev0) cudaEventDestroy(C->ev0);
     if (C->ev1) cudaEventDestroy(C->ev1);
@@ -78,7 +78,13 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     upload(C->d_grp_s, h.grp_s, st);
     upload(C->d_grp_e, h.grp_e, st);
     upload(C->d_blk_space, h.blk_space, st);
-    C->gaps.upload_from(h.gaps, st, &E->dev_bytes);
+    upload(C->d_gs_first, h.gs_first, st);
+    upload(C->d_gap_a, h.gap_a, st);
+    upload(C->d_gap_b, h.gap_b, st);
+    upload(C->d_gap_seg, h.gap_seg, st);
+    upload(C->d_irr_blk, h.irr_blk, st);
+    upload(C->d_u_rs, h.u_rs, st);
+    upload(C->d_u_re, h.u_re, st);
     C->irr.upload_from(h.irr, st, &E->dev_bytes);
     C->d_err.ensure(256);
     GFFX_CUDA(cudaStreamSynchronize(st));
@@ -86,9 +92,8 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     GFFX_CUDA(cudaEventCreate(&C->ev1));
     // keep the scalars, drop the bulk
     for (auto* v : {&h.X, &h.dir, &h.u_space, &h.u_chrom, &h.u_blk, &h.u_base, &h.irr_base, &h.u_line0, &h.u_seg0, &h.l_fs, &h.l_fe, &h.l_sfs, &h.l_sfe, &h.g_s,
-                    &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space})
+                    &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space, &h.gs_first, &h.gap_a, &h.gap_b, &h.gap_seg, &h.irr_blk, &h.u_rs, &h.u_re})
         std::vector<uint32_t>().swap(*v);
-    h.gaps = JoinHost();
     h.irr = JoinHost();
     C->built = true;
 }
@@ -132,7 +137,11 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.R.seqs = C->d_rank.as<RankSeq>();
     D.R.n_seqs = C->host.n_spaces;
     D.cov = C->d_cov.as<CovSpace>();
-    D.JG = C->gaps.J;
+    D.gs_first = C->d_gs_first.as<uint32_t>();
+    D.gap_a = C->d_gap_a.as<uint32_t>();
+    D.gap_b = C->d_gap_b.as<uint32_t>();
+    D.gap_seg = C->d_gap_seg.as<uint32_t>();
+    D.irr_blk = C->d_irr_blk.as<uint32_t>();
     D.JI = C->irr.J;
     D.irr_grp = C->d_irr_grp.as<uint32_t>();
     D.irr_pos = C->d_irr_pos.as<uint32_t>();
@@ -142,9 +151,6 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.grp_seq = C->d_grp_seq.as<uint32_t>();
     D.grp_s = C->d_grp_s.as<uint32_t>();
     D.grp_e = C->d_grp_e.as<uint32_t>();
-    D.JR = E->J;
-    D.ent_blk = E->d_ent_blk.as<uint32_t>();
-    D.blk_space = C->d_blk_space.as<uint32_t>();
     D.n_seqs = (uint32_t)E->H->vmap.n_vseqs();   // the bucketed regions carry virtual sequence numbers (0xFFFFFFFF: unknown sequence)
     D.Hs = C->d_Hs.as<uint32_t>();
     D.He = C->d_He.as<uint32_t>();
@@ -236,7 +242,7 @@ void counts_finish_impl(EngineImpl* E, CountRows* rows) {
     GFFX_CUDA(cudaEventRecord(C->ev0, st));
     CountsFin F{};
     F.id_unit0 = C->d_id_unit0.as<uint32_t>(); F.id_units = C->d_id_units.as<uint32_t>();
-    F.u_space = C->d_u_space.as<uint32_t>(); F.u_chrom = C->d_u_chrom.as<uint32_t>(); F.u_blk = C->d_u_blk.as<uint32_t>(); F.u_base = C->d_u_base.as<uint32_t>();
+    F.u_space = C->d_u_space.as<uint32_t>(); F.u_chrom = C->d_u_chrom.as<uint32_t>(); F.u_blk = C->d_u_blk.as<uint32_t>(); F.u_base = C->d_u_base.as<uint32_t>(); F.u_rs = C->d_u_rs.as<uint32_t>(); F.u_re = C->d_u_re.as<uint32_t>();
     F.u_line0 = C->d_u_line0.as<uint32_t>(); F.u_seg0 = C->d_u_seg0.as<uint32_t>();
     F.l_fs = C->d_l_fs.as<uint32_t>(); F.l_fe = C->d_l_fe.as<uint32_t>(); F.l_sfs = C->d_l_sfs.as<uint32_t>(); F.l_sfe = C->d_l_sfe.as<uint32_t>();
     F.g_s = C->d_g_s.as<uint32_t>(); F.g_e = C->d_g_e.as<uint32_t>(); F.g_ss = C->d_g_ss.as<uint32_t>(); F.g_se = C->d_g_se.as<uint32_t>();

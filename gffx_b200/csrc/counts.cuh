@@ -3,10 +3,16 @@
 // prefix scans, and a per-ID reduction over the units of counts_index.h.
 //
 //   depth     per region and space: Hs[ub(start)]++, He[lb(end)]++ (rank slots of the space's line
-//             coordinates, L2-resident), and G[gap]++ for every inter-segment gap that contains the
-//             region.  With S, E the prefix sums:  #regions overlapping [X_i, X_j) = S[j] - E[i]
-//             (every region has start < end, so "ends at or before X_i" and "starts at or after X_j"
-//             exclude each other), and a multi-segment ID is hit by S[last end] - E[first start] - sum G.
+//             coordinates, L2-resident).  With S, E the prefix sums:  #regions overlapping
+//             [X_i, X_j) = S[j] - E[i] (every region has start < end, so "ends at or before X_i" and
+//             "starts at or after X_j" exclude each other).  An ID of several segments is hit by
+//             sum over its segments (S[end] - E[start]) - sum over its gaps Span[gap], Span = the
+//             regions that reach across the whole gap (start < a && end > b: counted by both
+//             neighbours).  Until r02 the kernel counted the regions lying INSIDE each gap instead
+//             (G = E[b] - S[a] + Span is the same number): every read inside an intron walked the gap
+//             index and bumped a counter, half of the kernel's time (profiles/r02k_counts); a gap
+//             inside a 150-base read is rare, and the walk starts at the slot the start look-up
+//             already found.
 //   coverage  per region and space: the partial first/last 64-base words are OR-ed into a bitmap, the
 //             fully covered words in between go through a word-granular difference array; a scan turns
 //             positive counts into all-ones words, a second scan gives the covered-base prefix P, and
@@ -26,7 +32,10 @@ struct CovSpace {  // 16 B, same layout as CovSpaceHost
 struct CountsDev {
     RankSpace R;            // spaces as "sequences": X, dir, descriptors
     const CovSpace* cov;
-    JoinIndex JG;           // gaps, seq = space, payload = left segment index
+    const uint32_t* gs_first;   // per slot: first gap of the space with a >= the slot's coordinate (counts_index.h)
+    const uint32_t* gap_a;      // gaps by (space, a), one 0xFFFFFFFF sentinel per space
+    const uint32_t* gap_b;
+    const uint32_t* gap_seg;    // left segment of the gap
     JoinIndex JI;           // tree intervals of irregular blocks, seq = sequence, payload = private space
     const uint32_t* irr_grp;
     const uint32_t* irr_pos;
@@ -36,9 +45,8 @@ struct CountsDev {
     const uint32_t* grp_seq;
     const uint32_t* grp_s;
     const uint32_t* grp_e;
-    JoinIndex JR;           // all root intervals (coverage routing)
-    const uint32_t* ent_blk;
-    const uint32_t* blk_space;
+    const uint32_t* irr_blk;    // per JI entry: its block
+
     uint32_t n_seqs;
     // accumulators
     uint32_t* Hs;
@@ -54,13 +62,15 @@ __device__ __forceinline__ void depth_space_update(const CountsDev& D, uint32_t 
     if (S.cnt == 0) return;
     bool eq;
     uint32_t lb = rank_lb(D.R, S, rs, &eq);
-    atomicAdd(D.Hs + S.slot0 + lb + (eq ? 1u : 0u), 1u);  // slot ub(start): counted by S[k] for every X_k > start
+    const uint32_t ub = S.slot0 + lb + (eq ? 1u : 0u);
+    atomicAdd(D.Hs + ub, 1u);                             // slot ub(start): counted by S[k] for every X_k > start
     lb = rank_lb(D.R, S, re, &eq);
     atomicAdd(D.He + S.slot0 + lb, 1u);                   // slot lb(end):   counted by E[k] for every X_k >= end
-    // gaps [a,b] with a <= start and end <= b: the region lies between two segments of that ID
-    join_query<2, false>(D.JG, sp, rs, rs + 1u, [&](uint32_t j, uint2 se) {
-        if (se.y >= re) atomicAdd(D.G + __ldg(D.JG.ent_fid + j), 1u);
-    });
+    // gaps [a,b] the region reaches across: start < a (a is a coordinate of the space: a >= X[ub]) and b < end
+    for (uint32_t j = __ldg(D.gs_first + ub);; j++) {
+        if (__ldg(D.gap_a + j) >= re) break;              // sorted by a; the space's sentinel ends it
+        if (__ldg(D.gap_b + j) < re) atomicAdd(D.G + __ldg(D.gap_seg + j), 1u);
+    }
 }
 
 __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp, uint32_t rs, uint32_t re) {
@@ -124,16 +134,16 @@ __global__ void __launch_bounds__(JOIN_THREADS)
                 depth_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
             });
         } else {
+            // A regular block (one tree interval, its lines inside it, on the sequence's own space) needs no routing: "some
+            // region overlaps its tree interval" is "some base of the interval is covered", which counts_rows_kernel reads off the
+            // bitmap.  Only the tree intervals of irregular blocks are joined (a handful, usually none): their private spaces
+            // take the regions routed to them (OR / +-1 updates tolerate repeats: no dedup needed).
             cov_space_update(D, c, rs, re);
-            join_query<2, false>(D.JR, c, rs, re, [&](uint32_t j, uint2) {
-                const uint32_t blk = __ldg(D.ent_blk + j);
-                if (blk == 0xFFFFFFFFu) return;
+            join_query<2, false>(D.JI, c, rs, re, [&](uint32_t j, uint2) {
+                const uint32_t blk = __ldg(D.irr_blk + j);
                 if (!D.blk_routed[blk]) D.blk_routed[blk] = 1;
-                const uint32_t sp = __ldg(D.blk_space + blk);
-                if (sp != 0xFFFFFFFFu) {   // OR / +-1 updates tolerate repeats: no dedup needed
-                    const uint32_t vb = __ldg(D.ent_base + j);
-                    cov_space_update(D, sp, rs - vb, re - vb);
-                }
+                const uint32_t vb = __ldg(D.irr_base + j);
+                cov_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
             });
         }
     }
@@ -162,6 +172,8 @@ struct CountsFin {
     const uint32_t* u_chrom;
     const uint32_t* u_blk;
     const uint32_t* u_base;
+    const uint32_t* u_rs;       // the one tree interval of a regular block's units (0xFFFFFFFF: irregular block)
+    const uint32_t* u_re;
     const uint32_t* u_line0;
     const uint32_t* u_seg0;
     const uint32_t* l_fs;
@@ -210,8 +222,9 @@ __global__ void __launch_bounds__(256) counts_rows_kernel(CountsFin F, RowArrays
         const uint32_t s0 = F.u_seg0[u], s1 = F.u_seg0[u + 1];
         const uint32_t vb = F.u_base[u];   // rows carry the sequence's own coordinates
         if (KIND == 0) {
-            uint32_t d = F.S[F.g_se[s1 - 1]] - F.E[F.g_ss[s0]];  // mod 2^32; the true value is below 2^32
-            for (uint32_t g = s0; g + 1 < s1; g++) d -= F.G[g];
+            uint32_t d = 0;   // mod 2^32; the true value is below 2^32
+            for (uint32_t g = s0; g < s1; g++) d += F.S[F.g_se[g]] - F.E[F.g_ss[g]];   // regions overlapping segment g
+            for (uint32_t g = s0; g + 1 < s1; g++) d -= F.G[g];                         // ... once, not per segment they reach
             if (d == 0) continue;
             value += d;
             any = true;
@@ -223,10 +236,12 @@ __global__ void __launch_bounds__(256) counts_rows_kernel(CountsFin F, RowArrays
                     mx = max(mx, F.l_fe[l] - vb);
                 }
         } else {
-            if (!F.blk_routed[F.u_blk[u]]) continue;
+            const CovSpace cv = F.cov[F.u_space[u]];
+            const uint32_t rs = F.u_rs[u];
+            // routed: some region overlaps the block's tree interval — covered bases inside it (regular), the scatter's flag (irregular)
+            if (rs != 0xFFFFFFFFu ? covered_before(F, cv, F.u_re[u]) == covered_before(F, cv, rs) : !F.blk_routed[F.u_blk[u]]) continue;
             any = true;
             if (chrom == 0xFFFFFFFFu) chrom = F.u_chrom[u];
-            const CovSpace cv = F.cov[F.u_space[u]];
             for (uint32_t g = s0; g < s1; g++) value += (uint32_t)(covered_before(F, cv, F.g_e[g]) - covered_before(F, cv, F.g_s[g]));
             mn = min(mn, F.g_s[s0] - vb);       // hull over ALL lines (coverage.rs:345-346): segments are sorted and disjoint
             mx = max(mx, F.g_e[s1 - 1] - vb);

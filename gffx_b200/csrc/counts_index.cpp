@@ -29,7 +29,8 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
     uint32_t n_spaces = n_seqs;
     std::vector<std::vector<uint32_t>> id_units(C.n_ids);
     std::vector<JoinItem> gap_items, irr_items;
-    std::vector<uint32_t> irr_item_grp, irr_item_pos, irr_item_base;
+    std::vector<uint32_t> irr_item_grp, irr_item_pos, irr_item_base, irr_item_blk;
+    std::vector<uint32_t> sp_rmin(n_seqs, 0xFFFFFFFFu), sp_rmax(n_seqs, 0);   // hull of the regular blocks' tree intervals per sequence space
     std::vector<uint32_t> ord;
     C.u_line0.push_back(0);
     C.u_seg0.push_back(0);
@@ -52,7 +53,11 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
         // a regular block's lines live on its root's virtual sequence, moved by the root sequence's base; a private space keeps
         // the lines' own coordinates and the regions routed to it are moved back (irr_base / the root join's ent_base)
         uint32_t space, vbase = 0;
-        if (regular) { space = V.seq[r0.seq].vseq; vbase = V.seq[r0.seq].base; }
+        if (regular) {
+            space = V.seq[r0.seq].vseq; vbase = V.seq[r0.seq].base;
+            sp_rmin[space] = std::min(sp_rmin[space], vbase + r0.start);
+            sp_rmax[space] = std::max(sp_rmax[space], vbase + r0.end);
+        }
         else {
             space = n_spaces++;
             C.blk_space[b] = space;
@@ -65,6 +70,7 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
                 irr_item_grp.push_back(grp);
                 irr_item_pos.push_back(k);
                 irr_item_base.push_back(m.base);
+                irr_item_blk.push_back((uint32_t)b);
                 if (grp != NONE32) { C.grp_seq.push_back(m.vseq); C.grp_s.push_back(m.base + r.start); C.grp_e.push_back(m.base + r.end); }
             }
             if (grp != NONE32) C.grp_off.push_back((uint32_t)C.grp_seq.size());
@@ -80,6 +86,8 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             C.u_chrom.push_back(L.chrom[ord[p]]);  // stable sort: ord[p] is the first line in file order
             C.u_blk.push_back((uint32_t)b);
             C.u_base.push_back(vbase);
+            C.u_rs.push_back(regular ? vbase + r0.start : NONE32);
+            C.u_re.push_back(regular ? vbase + r0.end : NONE32);
             id_units[L.id[ord[p]]].push_back(u);
             std::sort(ord.begin() + p, ord.begin() + q, [&](uint32_t a, uint32_t c) {
                 if (L.fs[a] != L.fs[c]) return L.fs[a] < L.fs[c];
@@ -146,7 +154,12 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
         }
         C.X.insert(C.X.end(), v.begin(), v.end());
         cv.lo = v.front();
-        cv.nbits = v.back() - v.front();
+        uint32_t hi = v.back();
+        if (s < n_seqs && sp_rmin[s] != 0xFFFFFFFFu) {   // the bitmap also spans the regular blocks' tree intervals (coverage routing)
+            cv.lo = std::min(cv.lo, sp_rmin[s]);
+            hi = std::max(hi, sp_rmax[s]);
+        }
+        cv.nbits = hi - cv.lo;
         word += (uint64_t)cv.nbits / 64 + 1;
     }
     C.n_slots = slot;
@@ -171,15 +184,47 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
     C.id_units.reserve(C.n_units);
     for (uint32_t i = 0; i < C.n_ids; i++) C.id_units.insert(C.id_units.end(), id_units[i].begin(), id_units[i].end());
 
-    build_join_host(n_spaces, gap_items, 16, 8, &C.gaps);
+    {   // gaps by (space, a) + the per-slot entry point
+        std::vector<uint32_t> ord_g(gap_items.size());
+        std::iota(ord_g.begin(), ord_g.end(), 0u);
+        std::sort(ord_g.begin(), ord_g.end(), [&](uint32_t x, uint32_t y) {
+            const JoinItem &p = gap_items[x], &q = gap_items[y];
+            if (p.seq != q.seq) return p.seq < q.seq;
+            if (p.start != q.start) return p.start < q.start;
+            return p.end < q.end;
+        });
+        C.gs_first.assign(std::max<uint32_t>(C.n_slots, 1), 0);
+        size_t k = 0;
+        for (uint32_t s = 0; s < n_spaces; s++) {
+            const auto& x = xs[s];
+            const RankSeqHost& r = C.rank[s];
+            size_t k1 = k;
+            while (k1 < ord_g.size() && gap_items[ord_g[k1]].seq == s) k1++;
+            const uint32_t g0 = (uint32_t)C.gap_a.size();
+            for (size_t j = k; j < k1; j++) {
+                const JoinItem& g = gap_items[ord_g[j]];
+                C.gap_a.push_back(g.start); C.gap_b.push_back(g.end); C.gap_seg.push_back(g.payload);
+            }
+            C.gap_a.push_back(0xFFFFFFFFu); C.gap_b.push_back(0xFFFFFFFFu); C.gap_seg.push_back(0);
+            uint32_t j = g0;
+            for (uint32_t i = 0; i < r.cnt; i++) {
+                while (C.gap_a[j] < x[i]) j++;   // the sentinel ends it
+                C.gs_first[r.slot0 + i] = j;
+            }
+            C.gs_first[r.slot0 + r.cnt] = (uint32_t)C.gap_a.size() - 1;
+            k = k1;
+        }
+    }
     build_join_host(n_seqs, irr_items, 16, 8, &C.irr);
     C.irr_grp.resize(C.irr.n_entries());
     C.irr_pos.resize(C.irr.n_entries());
     C.irr_base.resize(C.irr.n_entries());
+    C.irr_blk.resize(C.irr.n_entries());
     for (size_t k = 0; k < C.irr.n_entries(); k++) {
         C.irr_grp[k] = irr_item_grp[C.irr.ent_item[k]];
         C.irr_pos[k] = irr_item_pos[C.irr.ent_item[k]];
         C.irr_base[k] = irr_item_base[C.irr.ent_item[k]];
+        C.irr_blk[k] = irr_item_blk[C.irr.ent_item[k]];
     }
 }
 

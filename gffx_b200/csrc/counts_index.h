@@ -46,12 +46,18 @@ struct CountsIndexHost {
     std::vector<uint32_t> g_s, g_e, g_ss, g_se;
     // per ID: its units in ascending block (= file offset) order
     std::vector<uint32_t> id_unit0, id_units;
-    // gaps between consecutive segments of a unit: seq = space, [start,end] = [seg.e, next.s], payload = left segment
-    JoinHost gaps;
+    // gaps between consecutive segments of a unit, [a, b] = [seg.e, next.s], sorted by (space, a), one (0xFFFFFFFF) sentinel after
+    // each space's gaps; gs_first[slot] = the first gap of the slot's space whose a is >= the slot's coordinate (the space's
+    // sentinel when there is none): the gaps INSIDE a read start at gs_first[ub(read start)] (counts.cuh: depth_space_update)
+    std::vector<uint32_t> gap_a, gap_b, gap_seg, gs_first;
+    // regular blocks: the block's one tree interval per unit (NONE32 for a unit of an irregular block): coverage derives
+    // "some read was routed to this block" from the covered bases inside it
+    std::vector<uint32_t> u_rs, u_re;
     // tree intervals of irregular blocks: seq = sequence number, payload = private space
     JoinHost irr;
     std::vector<uint32_t> irr_grp, irr_pos;          // per irr entry: duplicate-fid group (NONE32 = single) and rank inside it
     std::vector<uint32_t> irr_base;                  // per irr entry: VSeqMap base of its sequence (regions are moved back by it)
+    std::vector<uint32_t> irr_blk;                   // per irr entry: its block
     std::vector<uint32_t> grp_off, grp_seq, grp_s, grp_e;  // group members in rank order
     std::vector<uint32_t> blk_space;                 // per block: private space of an irregular block, else NONE32
     uint64_t n_irregular = 0;
