@@ -32,7 +32,8 @@ struct CovSpace {  // 16 B, same layout as CovSpaceHost
 struct CountsDev {
     RankSpace R;            // spaces as "sequences": X, dir, descriptors
     const CovSpace* cov;
-    const uint32_t* gs_first;   // per slot: first gap of the space with a >= the slot's coordinate (counts_index.h)
+    const uint32_t* gsp0;       // per space: its gaps are [gsp0[s], gsp0[s+1]) of the arrays below, the last one a sentinel
+    const uint32_t* gap_bits;   // per rank slot: its coordinate is the `a` of a gap (counts_index.h)
     const uint32_t* gap_a;      // gaps by (space, a), one 0xFFFFFFFF sentinel per space
     const uint32_t* gap_b;
     const uint32_t* gap_seg;    // left segment of the gap
@@ -62,14 +63,34 @@ __device__ __forceinline__ void depth_space_update(const CountsDev& D, uint32_t 
     if (S.cnt == 0) return;
     bool eq;
     uint32_t lb = rank_lb(D.R, S, rs, &eq);
-    const uint32_t ub = S.slot0 + lb + (eq ? 1u : 0u);
+    const uint32_t ubl = lb + (eq ? 1u : 0u), ub = S.slot0 + ubl;
     atomicAdd(D.Hs + ub, 1u);                             // slot ub(start): counted by S[k] for every X_k > start
-    lb = rank_lb(D.R, S, re, &eq);
-    atomicAdd(D.He + S.slot0 + lb, 1u);                   // slot lb(end):   counted by E[k] for every X_k >= end
-    // gaps [a,b] the region reaches across: start < a (a is a coordinate of the space: a >= X[ub]) and b < end
-    for (uint32_t j = __ldg(D.gs_first + ub);; j++) {
-        if (__ldg(D.gap_a + j) >= re) break;              // sorted by a; the space's sentinel ends it
-        if (__ldg(D.gap_b + j) < re) atomicAdd(D.G + __ldg(D.gap_seg + j), 1u);
+    // lb(end) = ub(start) + the coordinates inside (start, end): a short region has none or a few, next to the ones the start
+    // look-up read — walk them instead of a second look-up (which a long region still does)
+    uint32_t lbe = ubl;
+    bool gaps = false;   // some coordinate strictly inside the region starts a gap
+    {
+        const uint32_t* X = D.R.X + S.x0;
+        int steps = 0;
+        while (lbe < S.cnt && steps < 8 && __ldg(X + lbe) < re) {
+            const uint32_t slot = S.slot0 + lbe;
+            gaps = gaps || ((__ldg(D.gap_bits + (slot >> 5)) >> (slot & 31)) & 1u);
+            lbe++; steps++;
+        }
+        if (steps == 8) { lbe = rank_lb(D.R, S, re, &eq); gaps = true; }
+    }
+    atomicAdd(D.He + S.slot0 + lbe, 1u);                  // slot lb(end):   counted by E[k] for every X_k >= end
+    // gaps [a,b] the region reaches across: start < a and b < end; a is a coordinate of the space strictly inside the region
+    if (gaps) {
+        uint32_t lo = __ldg(D.gsp0 + sp), hi = __ldg(D.gsp0 + sp + 1) - 1u;   // first gap with a > start (the sentinel at the latest)
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(D.gap_a + mid) <= rs) lo = mid + 1; else hi = mid;
+        }
+        for (uint32_t j = lo;; j++) {
+            if (__ldg(D.gap_a + j) >= re) break;              // sorted by a; the space's sentinel ends it
+            if (__ldg(D.gap_b + j) < re) atomicAdd(D.G + __ldg(D.gap_seg + j), 1u);
+        }
     }
 }
 

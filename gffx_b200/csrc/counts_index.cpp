@@ -193,7 +193,8 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             if (p.start != q.start) return p.start < q.start;
             return p.end < q.end;
         });
-        C.gs_first.assign(std::max<uint32_t>(C.n_slots, 1), 0);
+        C.gap_bits.assign(((size_t)C.n_slots + 31) / 32 + 1, 0);
+        C.gsp0.assign((size_t)n_spaces + 1, 0);
         size_t k = 0;
         for (uint32_t s = 0; s < n_spaces; s++) {
             const auto& x = xs[s];
@@ -206,12 +207,12 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
                 C.gap_a.push_back(g.start); C.gap_b.push_back(g.end); C.gap_seg.push_back(g.payload);
             }
             C.gap_a.push_back(0xFFFFFFFFu); C.gap_b.push_back(0xFFFFFFFFu); C.gap_seg.push_back(0);
-            uint32_t j = g0;
-            for (uint32_t i = 0; i < r.cnt; i++) {
-                while (C.gap_a[j] < x[i]) j++;   // the sentinel ends it
-                C.gs_first[r.slot0 + i] = j;
+            C.gsp0[s] = g0;
+            C.gsp0[s + 1] = (uint32_t)C.gap_a.size();   // past the sentinel: the next space starts here
+            for (uint32_t j = g0; j + 1 < C.gap_a.size(); j++) {   // a is a coordinate of the space: mark its slot
+                const uint32_t slot = r.slot0 + (uint32_t)(std::lower_bound(x.begin(), x.end(), C.gap_a[j]) - x.begin());
+                C.gap_bits[slot >> 5] |= 1u << (slot & 31);
             }
-            C.gs_first[r.slot0 + r.cnt] = (uint32_t)C.gap_a.size() - 1;
             k = k1;
         }
     }
