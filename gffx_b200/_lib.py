@@ -100,6 +100,7 @@ SIGNATURES = {
     "gffx_index_n_blocks": (C.c_uint64, vp),
     "gffx_index_n_lines": (C.c_uint64, vp),
     "gffx_index_n_ids": (C.c_uint64, vp),
+    "gffx_index_lines_info": (C.c_int, vp, u64p, C.POINTER(C.c_int)),
     "gffx_index_device_bytes": (C.c_uint64, vp),
     "gffx_index_seq_roots": (C.c_int, vp, C.c_uint32, C.POINTER(u32p), u64p),
     "gffx_parse_bed_intersect": (C.c_int, vp, C.c_char_p, C.POINTER(u32p), C.POINTER(u32p), C.POINTER(u32p), u64p),

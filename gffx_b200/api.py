@@ -234,6 +234,12 @@ class TreeIndexData:
     n_blocks = property(lambda self: lib.gffx_index_n_blocks(self._h))
     n_lines = property(lambda self: lib.gffx_index_n_lines(self._h))
     n_ids = property(lambda self: lib.gffx_index_n_ids(self._h))
+
+    def lines_info(self):
+        """(digest of the GFF line table, its source: 0 host scanner, 1 device scanner, 2 side-car cache)"""
+        d, s = C.c_uint64(), C.c_int()
+        _check(lib.gffx_index_lines_info(self._h, C.byref(d), C.byref(s)))
+        return d.value, s.value
     device_bytes = property(lambda self: lib.gffx_index_device_bytes(self._h))
     cuda_stream = property(lambda self: lib.gffx_index_cuda_stream(self._h) or 0)
 

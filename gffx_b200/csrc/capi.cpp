@@ -91,6 +91,7 @@ int gffx_index_open(const char* gff_path, int device, gffx_index** out) {
         need(gff_path, "gff_path");
         need(out, "out");
         auto H = std::make_unique<HostIndex>();
+        H->scan_device = device;   // the line table may be scanned on the device the index is opened on (linescan.cu)
         H->open(gff_path, host_threads());
         auto h = std::make_unique<gffx_index>();
         if (device == -1) h->host_only = std::move(H);
@@ -107,6 +108,7 @@ int gffx_index_create(const gffx_index_desc* d, gffx_index** out) {
         if (d->n_roots && (!d->root_seq || !d->root_start || !d->root_end || !d->root_fid)) throw Err(E_ARG, "root arrays are NULL");
         if (d->n_gof && (!d->gof_fid || !d->gof_start || !d->gof_end)) throw Err(E_ARG, "gof arrays are NULL");
         auto H = std::make_unique<HostIndex>();
+        H->scan_device = d->device;
         H->create(d->n_seqs, d->seq_names, d->n_roots, d->root_seq, d->root_start, d->root_end, d->root_fid, d->n_gof, d->gof_fid,
                   d->gof_start, d->gof_end, d->gff_text, d->gff_len, host_threads());
         auto h = std::make_unique<gffx_index>();
@@ -141,6 +143,13 @@ uint64_t gffx_index_n_roots(const gffx_index* idx) { return idx ? idx->host().ro
 uint64_t gffx_index_n_blocks(const gffx_index* idx) { return idx ? idx->host().blocks.size() : 0; }
 uint64_t gffx_index_n_lines(const gffx_index* idx) { return idx ? idx->host().lines.size() : 0; }
 uint64_t gffx_index_n_ids(const gffx_index* idx) { return idx ? idx->host().ids.size() : 0; }
+int gffx_index_lines_info(const gffx_index* idx, uint64_t* digest, int* source) {
+    return guard([&] {
+        need(idx, "idx");
+        if (digest) *digest = line_table_digest(idx->host());
+        if (source) *source = idx->host().lines_source;
+    });
+}
 uint64_t gffx_index_device_bytes(const gffx_index* idx) { return idx && idx->eng_ ? idx->eng_->device_bytes() : 0; }
 
 int gffx_index_seq_roots(const gffx_index* idx, uint32_t seq, const uint32_t** triples, uint64_t* n) {

@@ -101,6 +101,13 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     }
     d_small.ensure(256);
     d_warn.ensure(WARN_CAP * 4);
+    if (H->dev_text && H->dev_text_device == dev) {   // the device line scanner left the GFF text in HBM: record emission adopts it
+        d_text.p = H->dev_text;
+        d_text.cap = H->dev_text_cap;
+        dev_bytes += d_text.cap;
+        text_resident = true;
+        H->dev_text = nullptr;
+    }
     GFFX_CUDA(cudaStreamSynchronize(st));
 }
 

@@ -203,6 +203,11 @@ void HostIndex::finish(const std::vector<uint32_t>& gfid, const std::vector<uint
     }
     build_lines(threads);
     build_vseqs();
+    if (cache_pending) {
+        cache_pending = false;
+        if (getenv("GFFX_CACHE_SYNC")) line_cache_store(*this);
+        else cache_writer = std::thread([this] { line_cache_store(*this); });
+    }
 }
 
 // see VSeqMap (host_index.h)
@@ -327,14 +332,242 @@ inline bool find_id(const uint8_t* a, size_t n, size_t* vs, size_t* vn) {
 }  // namespace
 
 void HostIndex::build_lines(int threads) {
-    PhaseTimer t_lines("  GFF line table (host scan)");
     const size_t nb = blocks.size();
     blk_utf8.assign(nb, 0);
     blk_line0.assign(nb + 1, 0);
     lines = LineTable();
-    if (!gff || gff_len == 0 || nb == 0) return;
     if (threads < 1) threads = 1;
     n_threads = threads;
+    if (!gff || gff_len == 0 || nb == 0) return;
+    if (line_cache_load(*this, threads)) { lines_source = 2; return; }
+    // GFFX_LINE_SCAN=host|device picks the scanner; by default the device scans texts of 8 MB and more when the index is being
+    // opened on one (below that the host threads are done before the text has crossed PCIe)
+    const char* sel = getenv("GFFX_LINE_SCAN");
+    const bool want_dev = scan_device >= 0 && (sel ? strcmp(sel, "device") == 0 : gff_len >= (8u << 20));
+    bool done = false;
+    if (want_dev) {
+        RawLines R;
+        if (device_scan_lines(*this, scan_device, threads, &R, &dev_text, &dev_text_cap)) {
+            dev_text_device = scan_device;
+            dev_text_release = device_text_release;
+            lines_from_raw(R, threads);
+            lines_source = 1;
+            done = true;
+        }
+    }
+    if (!done) scan_lines(threads);
+    cache_pending = true;   // written by finish() once everything the file holds is final
+}
+
+// The device scanner's columns -> the line table: blocks with non-ASCII bytes re-scanned by the host scanner (it knows UTF-8;
+// their lines keep their places), then the three dictionaries, numbered by first appearance as scan_lines numbers them.
+void HostIndex::lines_from_raw(RawLines& R, int threads) {
+    PhaseTimer t_all("    dictionaries (host)");
+    const size_t nb = blocks.size();
+    LineTable& L = lines;
+    L = std::move(R.t);
+    const size_t total = L.size();
+    for (size_t b = 0; b < nb; b++) blk_line0[b + 1] = blk_line0[b] + R.blk_nlines[b];
+    if (blk_line0[nb] != total) throw Err(E_STATE, "device line scan: line counts do not add up (internal)");
+    for (size_t b = 0; b < nb; b++) {
+        if (!block_scannable(b)) continue;
+        blk_utf8[b] = 1;
+        if (!R.blk_nonascii[b]) continue;
+        Part P;
+        scan_blocks(b, b + 1, &P);
+        const size_t o = (size_t)blk_line0[b], m = P.t.size();
+        if (m != R.blk_nlines[b]) throw Err(E_STATE, "device line scan: a block's line count differs from the host scanner's (internal)");
+        blk_utf8[b] = P.blk_utf8[0];
+        for (size_t i = 0; i < m; i++) {
+            if (L.off[o + i] != P.t.off[i] || L.len[o + i] != P.t.len[i]) throw Err(E_STATE, "device line scan: a line's extent differs from the host scanner's (internal)");
+            L.flags[o + i] = P.t.flags[i];
+            L.S[o + i] = P.t.S[i]; L.E[o + i] = P.t.E[i]; L.iseq[o + i] = P.t.iseq[i]; L.fs[o + i] = P.t.fs[i]; L.fe[o + i] = P.t.fe[i];
+            if (P.t.type_id[i] == NONE32) R.type_len[o + i] = NONE32;   // the field is where the device found it; the host decides whether it is text
+            if (P.t.flags[i] & LN_D_OK) {
+                R.id_off[o + i] = (uint32_t)(P.id_off[i] - P.t.off[i]);
+                R.id_len[o + i] = P.id_len[i];
+                R.id_hash[o + i] = P.id_hash[i];
+            } else {
+                R.chrom_len[o + i] = NONE32;
+            }
+        }
+    }
+    // type / chromosome dictionaries: chunks of lines side by side, each with its own dictionary in order of appearance; the
+    // chunks' dictionaries are merged in chunk order, which numbers every string by its first appearance in the file
+    const size_t nparts = std::max<size_t>(1, std::min<size_t>((size_t)std::max(1, threads), total / 65536 + 1));
+    struct Chunk { LocalDict types, chroms; std::vector<uint32_t> ty, ch; };
+    std::vector<Chunk> chunks(nparts);
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
+        if (n_jobs <= 1 || threads <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
+        std::vector<std::thread> th;
+        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
+        for (auto& t : th) t.join();
+    };
+    run_parallel(nparts, [&](size_t c) {
+        Chunk& C = chunks[c];
+        const size_t i0 = total * c / nparts, i1 = total * (c + 1) / nparts;
+        C.ty.assign(i1 - i0, NONE32);
+        C.ch.assign(i1 - i0, NONE32);
+        for (size_t i = i0; i < i1; i++) {
+            if (R.type_len[i] != NONE32) C.ty[i - i0] = C.types.get(gff + L.off[i] + R.type_off[i], R.type_len[i]);
+            if ((L.flags[i] & LN_D_OK) && R.chrom_len[i] != NONE32) C.ch[i - i0] = C.chroms.get(gff + L.off[i], R.chrom_len[i]);
+        }
+    });
+    std::vector<std::vector<uint32_t>> tmaps(nparts), cmaps(nparts);
+    for (size_t c = 0; c < nparts; c++) {
+        tmaps[c].resize(chunks[c].types.items.size());
+        cmaps[c].resize(chunks[c].chroms.items.size());
+        for (size_t i = 0; i < tmaps[c].size(); i++) tmaps[c][i] = types.intern(chunks[c].types.items[i]);
+        for (size_t i = 0; i < cmaps[c].size(); i++) cmaps[c][i] = chroms.intern(chunks[c].chroms.items[i]);
+    }
+    L.type_id.resize(total);
+    L.chrom.resize(total);
+    std::vector<uint64_t> g_off(total);
+    run_parallel(nparts, [&](size_t c) {
+        const size_t i0 = total * c / nparts, i1 = total * (c + 1) / nparts;
+        for (size_t i = i0; i < i1; i++) {
+            const uint32_t ty = chunks[c].ty[i - i0], ch = chunks[c].ch[i - i0];
+            L.type_id[i] = ty == NONE32 ? NONE32 : tmaps[c][ty];
+            L.chrom[i] = ch == NONE32 ? NONE32 : cmaps[c][ch];
+            const bool d = L.flags[i] & LN_D_OK;
+            g_off[i] = d ? L.off[i] + R.id_off[i] : 0;
+            if (!d) { R.id_len[i] = 0; R.id_hash[i] = 0; }
+        }
+    });
+    number_ids(R.id_hash, g_off, R.id_len, threads);
+}
+
+// ID dictionary: the lines are cut into `nshard` shards by hash; every shard finds, for each of its lines, the FIRST line
+// with the same ID (its own open-addressing table over line numbers, lines visited in file order); an ID's number is then
+// the rank of its first line among all first lines = order of first appearance, as a serial intern loop would number them.
+// g_hash / g_off / g_len: FNV-1a hash, absolute offset and length of the ID value of every LN_D_OK line.
+void HostIndex::number_ids(const std::vector<uint64_t>& g_hash, const std::vector<uint64_t>& g_off, const std::vector<uint32_t>& g_len, int threads) {
+    LineTable& L = lines;
+    const size_t total = L.size();
+    const size_t nshard = std::max<size_t>(1, std::min<size_t>((size_t)threads, 64));
+    std::vector<uint32_t> first(total, NONE32);
+    auto dedup_shard = [&](size_t sh) {
+        size_t cnt = 0;
+        for (size_t i = 0; i < total; i++)
+            if ((L.flags[i] & LN_D_OK) && (g_hash[i] >> 32) % nshard == sh) cnt++;
+        size_t cap = 16;
+        while (cap < 2 * cnt + 2) cap <<= 1;
+        std::vector<uint32_t> tab(cap, 0);   // line number + 1
+        const size_t mask = cap - 1;
+        for (size_t i = 0; i < total; i++) {
+            if (!(L.flags[i] & LN_D_OK)) continue;
+            const uint64_t h = g_hash[i];
+            if ((h >> 32) % nshard != sh) continue;
+            size_t k = (size_t)h & mask;
+            for (;; k = (k + 1) & mask) {
+                if (tab[k] == 0) { tab[k] = (uint32_t)i + 1; first[i] = (uint32_t)i; break; }
+                const size_t j = tab[k] - 1;
+                if (g_hash[j] == h && g_len[j] == g_len[i] && memcmp(gff + g_off[j], gff + g_off[i], g_len[i]) == 0) { first[i] = (uint32_t)j; break; }
+            }
+        }
+    };
+    if (nshard <= 1 || threads <= 1) { for (size_t k = 0; k < nshard; k++) dedup_shard(k); }
+    else {
+        std::vector<std::thread> th;
+        for (size_t k = 0; k < nshard; k++) th.emplace_back(dedup_shard, k);
+        for (auto& t : th) t.join();
+    }
+    ids = IdTable();
+    ids.base = gff;
+    L.id.assign(total, NONE32);
+    for (size_t i = 0; i < total; i++) {   // first[i] <= i: one forward pass numbers the IDs and fills the column
+        if (first[i] == NONE32) continue;
+        if (first[i] == (uint32_t)i) {
+            L.id[i] = (uint32_t)ids.off.size();
+            ids.off.push_back(g_off[i]);
+            ids.len.push_back(g_len[i]);
+        } else {
+            L.id[i] = L.id[first[i]];
+        }
+    }
+}
+
+// the host scanner proper: the lines of blocks [b0, b1) appended to *part (a Part), every rule of the reference's per-block text
+// loops (intersect.rs:284-321 + :441-489, depth.rs:131-157, coverage.rs:296-323)
+void HostIndex::scan_blocks(size_t b0, size_t b1, void* part) const {
+    Part& P = *(Part*)part;
+    P.blk_nlines.assign(b1 - b0, 0);
+    P.blk_utf8.assign(b1 - b0, 0);
+    for (size_t b = b0; b < b1; b++) {
+        if (!block_scannable(b)) continue;
+        const uint64_t bs = blocks[b].start, be = std::min<uint64_t>(blocks[b].end, gff_len);
+        const bool u8ok = utf8_ok(gff + bs, (size_t)(be - bs));
+        P.blk_utf8[b - b0] = u8ok;
+        const bool countable = block_countable(b) && blocks[b].end <= gff_len;
+        const uint8_t* p = gff + bs;
+        const uint8_t* end = gff + be;
+        uint64_t nl_count = 0;
+        while (p < end) {
+            const uint8_t* nl = find_byte(p, end, '\n');
+            const uint8_t* next = nl ? nl + 1 : end;
+            const uint8_t* q = nl ? nl : end;  // line body [p,q)
+            if (q > p && p[0] != '#') {
+                const uint8_t* tab[8];
+                int nt = 0;
+                const uint8_t* c = p;
+                while (nt < 8) {
+                    const uint8_t* t = find_byte(c, q, '\t');
+                    if (!t) break;
+                    tab[nt++] = t;
+                    c = t + 1;
+                }
+                uint8_t fl = 0;
+                uint32_t S = 0, E = 0, iseq = NONE32, ty = NONE32, fs = 0, fe = 0, chrom = NONE32;
+                bool numok = false;
+                if (nt >= 3 && utf8_ok(tab[1] + 1, (size_t)(tab[2] - tab[1] - 1)))
+                    ty = P.types.get(tab[1] + 1, (size_t)(tab[2] - tab[1] - 1));
+                if (nt >= 5) {
+                    numok = parse_u32_strict(tab[2] + 1, (size_t)(tab[3] - tab[2] - 1), &S) &&
+                            parse_u32_strict(tab[3] + 1, (size_t)(tab[4] - tab[3] - 1), &E);
+                    if (numok && utf8_ok(p, (size_t)(tab[0] - p))) {
+                        auto it = seq_num.find(std::string((const char*)p, (size_t)(tab[0] - p)));
+                        if (it != seq_num.end()) { iseq = it->second; fl |= LN_I_OK; }
+                    }
+                }
+                size_t ivs = 0, ivn = 0;
+                if (nt >= 8 && numok && E != 0 && u8ok && countable &&
+                    find_id(tab[7] + 1, (size_t)(q - tab[7] - 1), &ivs, &ivn)) {
+                    uint32_t a = std::min(S, E), z = std::max(S, E);
+                    fs = a == 0 ? 0 : a - 1;
+                    fe = z;
+                    chrom = P.chroms.get(p, (size_t)(tab[0] - p));
+                    fl |= LN_D_OK;
+                }
+                LineTable& t = P.t;
+                t.off.push_back((uint64_t)(p - gff));
+                t.len.push_back((uint32_t)(next - p));
+                t.blk.push_back((uint32_t)b);
+                t.flags.push_back(fl);
+                t.S.push_back(S); t.E.push_back(E); t.iseq.push_back(iseq); t.type_id.push_back(ty);
+                t.fs.push_back(fs); t.fe.push_back(fe); t.chrom.push_back(chrom);
+                if (fl & LN_D_OK) {
+                    const uint8_t* ids0 = tab[7] + 1 + ivs;
+                    uint64_t h = 1469598103934665603ull;
+                    for (size_t z = 0; z < ivn; z++) { h ^= ids0[z]; h *= 1099511628211ull; }
+                    P.id_off.push_back((uint64_t)(ids0 - gff));
+                    P.id_len.push_back((uint32_t)ivn);
+                    P.id_hash.push_back(h);
+                } else {
+                    P.id_off.push_back(0);
+                    P.id_len.push_back(0);
+                    P.id_hash.push_back(0);
+                }
+                nl_count++;
+            }
+            p = next;
+        }
+        P.blk_nlines[b - b0] = nl_count;
+    }
+}
+
+void HostIndex::scan_lines(int threads) {
+    PhaseTimer t_lines("  GFF line table (host scan)");
+    const size_t nb = blocks.size();
     size_t nparts = std::min<size_t>((size_t)threads, std::max<size_t>(1, nb / 64));
     std::vector<Part> parts(nparts);
     // split blocks so that each part scans about the same number of bytes
@@ -352,82 +585,7 @@ void HostIndex::build_lines(int threads) {
         for (size_t j = k + 1; j < nparts; j++) cut[j] = nb;
         cut[nparts] = nb;
     }
-    auto work = [&](size_t pi) {
-        Part& P = parts[pi];
-        size_t b0 = cut[pi], b1 = cut[pi + 1];
-        P.blk_nlines.assign(b1 - b0, 0);
-        P.blk_utf8.assign(b1 - b0, 0);
-        for (size_t b = b0; b < b1; b++) {
-            if (!block_scannable(b)) continue;
-            const uint64_t bs = blocks[b].start, be = std::min<uint64_t>(blocks[b].end, gff_len);
-            const bool u8ok = utf8_ok(gff + bs, (size_t)(be - bs));
-            P.blk_utf8[b - b0] = u8ok;
-            const bool countable = block_countable(b) && blocks[b].end <= gff_len;
-            const uint8_t* p = gff + bs;
-            const uint8_t* end = gff + be;
-            uint64_t nl_count = 0;
-            while (p < end) {
-                const uint8_t* nl = find_byte(p, end, '\n');
-                const uint8_t* next = nl ? nl + 1 : end;
-                const uint8_t* q = nl ? nl : end;  // line body [p,q)
-                if (q > p && p[0] != '#') {
-                    const uint8_t* tab[8];
-                    int nt = 0;
-                    const uint8_t* c = p;
-                    while (nt < 8) {
-                        const uint8_t* t = find_byte(c, q, '\t');
-                        if (!t) break;
-                        tab[nt++] = t;
-                        c = t + 1;
-                    }
-                    uint8_t fl = 0;
-                    uint32_t S = 0, E = 0, iseq = NONE32, ty = NONE32, fs = 0, fe = 0, chrom = NONE32;
-                    bool numok = false;
-                    if (nt >= 3 && utf8_ok(tab[1] + 1, (size_t)(tab[2] - tab[1] - 1)))
-                        ty = P.types.get(tab[1] + 1, (size_t)(tab[2] - tab[1] - 1));
-                    if (nt >= 5) {
-                        numok = parse_u32_strict(tab[2] + 1, (size_t)(tab[3] - tab[2] - 1), &S) &&
-                                parse_u32_strict(tab[3] + 1, (size_t)(tab[4] - tab[3] - 1), &E);
-                        if (numok && utf8_ok(p, (size_t)(tab[0] - p))) {
-                            auto it = seq_num.find(std::string((const char*)p, (size_t)(tab[0] - p)));
-                            if (it != seq_num.end()) { iseq = it->second; fl |= LN_I_OK; }
-                        }
-                    }
-                    size_t ivs = 0, ivn = 0;
-                    if (nt >= 8 && numok && E != 0 && u8ok && countable &&
-                        find_id(tab[7] + 1, (size_t)(q - tab[7] - 1), &ivs, &ivn)) {
-                        uint32_t a = std::min(S, E), z = std::max(S, E);
-                        fs = a == 0 ? 0 : a - 1;
-                        fe = z;
-                        chrom = P.chroms.get(p, (size_t)(tab[0] - p));
-                        fl |= LN_D_OK;
-                    }
-                    LineTable& t = P.t;
-                    t.off.push_back((uint64_t)(p - gff));
-                    t.len.push_back((uint32_t)(next - p));
-                    t.blk.push_back((uint32_t)b);
-                    t.flags.push_back(fl);
-                    t.S.push_back(S); t.E.push_back(E); t.iseq.push_back(iseq); t.type_id.push_back(ty);
-                    t.fs.push_back(fs); t.fe.push_back(fe); t.chrom.push_back(chrom);
-                    if (fl & LN_D_OK) {
-                        const uint8_t* ids0 = tab[7] + 1 + ivs;
-                        uint64_t h = 1469598103934665603ull;
-                        for (size_t z = 0; z < ivn; z++) { h ^= ids0[z]; h *= 1099511628211ull; }
-                        P.id_off.push_back((uint64_t)(ids0 - gff));
-                        P.id_len.push_back((uint32_t)ivn);
-                        P.id_hash.push_back(h);
-                    } else {
-                        P.id_off.push_back(0);
-                        P.id_len.push_back(0);
-                        P.id_hash.push_back(0);
-                    }
-                    nl_count++;
-                }
-                p = next;
-            }
-            P.blk_nlines[b - b0] = nl_count;
-        }
-    };
+    auto work = [&](size_t pi) { scan_blocks(cut[pi], cut[pi + 1], &parts[pi]); };
     {
         PhaseTimer t_scan("    parallel scan");
         if (nparts == 1) work(0);
@@ -476,31 +634,6 @@ void HostIndex::build_lines(int threads) {
         }
         P = Part();
     };
-    // ID dictionary: the lines are cut into `nshard` shards by hash; every shard finds, for each of its lines, the FIRST line
-    // with the same ID (its own open-addressing table over line numbers, lines visited in file order); an ID's number is then
-    // the rank of its first line among all first lines = order of first appearance, as a serial intern loop would number them
-    const size_t nshard = std::max<size_t>(1, std::min<size_t>((size_t)threads, 64));
-    std::vector<uint32_t> first(total, NONE32);
-    auto dedup_shard = [&](size_t sh) {
-        size_t cnt = 0;
-        for (size_t i = 0; i < total; i++)
-            if ((L.flags[i] & LN_D_OK) && (g_hash[i] >> 32) % nshard == sh) cnt++;
-        size_t cap = 16;
-        while (cap < 2 * cnt + 2) cap <<= 1;
-        std::vector<uint32_t> tab(cap, 0);   // line number + 1
-        const size_t mask = cap - 1;
-        for (size_t i = 0; i < total; i++) {
-            if (!(L.flags[i] & LN_D_OK)) continue;
-            const uint64_t h = g_hash[i];
-            if ((h >> 32) % nshard != sh) continue;
-            size_t k = (size_t)h & mask;
-            for (;; k = (k + 1) & mask) {
-                if (tab[k] == 0) { tab[k] = (uint32_t)i + 1; first[i] = (uint32_t)i; break; }
-                const size_t j = tab[k] - 1;
-                if (g_hash[j] == h && g_len[j] == g_len[i] && memcmp(gff + g_off[j], gff + g_off[i], g_len[i]) == 0) { first[i] = (uint32_t)j; break; }
-            }
-        }
-    };
     auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
         if (n_jobs <= 1 || threads <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
         std::vector<std::thread> th;
@@ -509,19 +642,7 @@ void HostIndex::build_lines(int threads) {
     };
     if (total >= (1ull << 32) - 1) throw Err(E_FORMAT, "more than 2^32-2 GFF lines inside blocks");
     run_parallel(nparts, copy_part);
-    run_parallel(nshard, dedup_shard);
-    ids = IdTable();
-    ids.base = gff;
-    for (size_t i = 0; i < total; i++) {   // first[i] <= i: one forward pass numbers the IDs and fills the column
-        if (first[i] == NONE32) continue;
-        if (first[i] == (uint32_t)i) {
-            L.id[i] = (uint32_t)ids.off.size();
-            ids.off.push_back(g_off[i]);
-            ids.len.push_back(g_len[i]);
-        } else {
-            L.id[i] = L.id[first[i]];
-        }
-    }
+    number_ids(g_hash, g_off, g_len, threads);
     for (size_t b = 0; b < nb; b++) blk_line0[b + 1] += blk_line0[b];
 }
 

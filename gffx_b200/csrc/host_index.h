@@ -3,6 +3,7 @@
 // upload in engine.cu.  Reference formats: SURVEY.md App. B; src/utils/tree_io.rs:37-63,
 // src/index_loader/{core.rs:19-34,gof.rs:95-128}, src/utils/tree_index.rs:36-82.
 #pragma once
+#include <thread>
 #include <memory>
 #include <unordered_map>
 #include "util.h"
@@ -79,7 +80,30 @@ struct VSeqMap {
     size_t n_vseqs() const { return v_extent.size(); }
 };
 
+// What a line scanner returns before the dictionaries are built (the device scanner, linescan.cu): the line table's plain
+// columns, and per line where its type field, its column 1 and its ID value lie (offsets relative to the line; len NONE32 =
+// none) with the ID's FNV-1a hash; per block its line count and whether it holds a byte >= 0x80 (such a block is re-scanned
+// by the host scanner, which knows UTF-8).
+struct RawLines {
+    LineTable t;
+    std::vector<uint32_t> type_off, type_len, chrom_len, id_off, id_len;
+    std::vector<uint64_t> id_hash;
+    std::vector<uint32_t> blk_nlines;
+    std::vector<uint8_t> blk_nonascii;
+};
+
 struct HostIndex {
+    ~HostIndex() {
+        if (cache_writer.joinable()) cache_writer.join();
+        if (dev_text && dev_text_release) dev_text_release(dev_text, dev_text_device);
+    }
+    bool cache_pending = false;
+    std::thread cache_writer;   // writes the side-car cache behind the open (the index is immutable once built)
+    // the GFF text on the device, left there by the device scanner for the engine to adopt (record emission reads it)
+    void* dev_text = nullptr;
+    size_t dev_text_cap = 0;
+    int dev_text_device = -1;
+    void (*dev_text_release)(void*, int) = nullptr;
     std::string gff_path;
     std::vector<std::string> seq_names;                     // num_to_seqid
     std::unordered_map<std::string, uint32_t> seq_num;      // seqid_to_num (later duplicate wins)
@@ -96,6 +120,9 @@ struct HostIndex {
     StringPool types, chroms;
     IdTable ids;
     int n_threads = 1;   // host threads the loaders were given (the engine's load-time builders use as many)
+    bool lines_from_cache = false;   // the line table came from the side-car cache (linecache.cpp)
+    int lines_source = 0;            // 0 host scanner, 1 device scanner (linescan.cu), 2 side-car cache
+    int scan_device = -1;            // CUDA device the line scanner may use (-1: host threads only)
     VSeqMap vmap;        // real sequence -> (virtual sequence, base, clamp); built by finish()
 
     // load .sqs/.rix/.rit/.gof beside `path` and (when the text is there) build the line table
@@ -118,8 +145,21 @@ struct HostIndex {
    private:
     void finish(const std::vector<uint32_t>& gfid, const std::vector<uint64_t>& gs, const std::vector<uint64_t>& ge, int threads);
     void build_lines(int threads);
+    void scan_lines(int threads);
+    void scan_blocks(size_t b0, size_t b1, void* part) const;
+    void lines_from_raw(struct RawLines& R, int threads);
+    void number_ids(const std::vector<uint64_t>& g_hash, const std::vector<uint64_t>& g_off, const std::vector<uint32_t>& g_len, int threads);
     void build_vseqs();
 };
+
+// linecache.cpp: `<gff>.b200cache`, the line table of an earlier open (keyed by the GFF's size + mtime and a digest of the block
+// list and sequence names); load returns false when there is no usable cache
+bool line_cache_load(HostIndex& H, int threads);
+void line_cache_store(const HostIndex& H);
+uint64_t line_table_digest(const HostIndex& H);
+// linescan.cu: the line table's columns scanned on CUDA device `device`; false when there is no such device
+bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* out, void** d_text, size_t* d_text_cap);
+void device_text_release(void* p, int device);
 
 constexpr uint32_t VSEQ_MAX = 192;   // virtual sequences at most (each owns >= 1 of the <= 511 partition windows)
 

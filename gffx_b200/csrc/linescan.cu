@@ -1,0 +1,339 @@
+// linescan.cu — the GFF line table built on the device.
+//
+// What it replaces: the reference re-parses the text of every block it touches on every run — split on '\n', skip '#',
+// split on '\t', parse columns 4/5, look for "ID=" (src/commands/intersect.rs:284-321 + :441-489, src/commands/depth.rs:131-157 +
+// fast_id :104-118, src/commands/coverage.rs:296-323).  This engine does that once per index, into the line table; the host
+// scanner (host_index.cpp: scan_lines) spends ~155 ms of a 0.27 s open on it for the 416 MB bench GFF.  Here the text goes to
+// HBM (where record emission, gather.cuh, wants it anyway) and three kernels produce the same columns:
+//   ls_count_kernel   a warp per block: lines of the block (non-empty, not starting with '#'), "has a byte >= 0x80"
+//   device_scan       first line number of every block
+//   ls_starts_kernel  a warp per block again: the byte offset of each of its lines, in order
+//   ls_parse_kernel   a thread per line: tabs, columns 4/5 (digits only, checked u32), column 1 against the sequence names
+//                     (FNV-1a table, verified byte by byte), the type field, the first "ID=" of column 9 and its FNV-1a hash
+// Every rule is the host scanner's; what needs more than bytes — UTF-8 validity — is left to it: a block with a byte >= 0x80 is
+// flagged and the host re-scans just that block (its lines keep their places: counting lines is pure byte work).  The
+// dictionaries (type, chromosome, ID: numbered by first appearance) are built on the host from the (offset, length, hash)
+// triples the kernels return (host_index.cpp: lines_from_raw).
+#include <fcntl.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <thread>
+
+#include "engine_impl.cuh"
+
+namespace gffx {
+
+namespace {
+
+constexpr int LS_THREADS = 256;
+
+struct LsBlocks {
+    const uint64_t* bs;      // block start
+    const uint64_t* be;      // min(block end, text length); == bs for a block that is not scanned
+    const uint8_t* countable;
+    uint32_t n;
+};
+
+// line starts inside [bs, be): p == bs or text[p-1] == '\n'; a line counts when its first byte is neither '\n' nor '#'
+__device__ __forceinline__ bool ls_is_line(const uint8_t* __restrict__ text, uint64_t bs, uint64_t p) {
+    const uint8_t c = text[p];
+    return (p == bs || text[p - 1] == 10) && c != 10 && c != '#';
+}
+
+__global__ void __launch_bounds__(LS_THREADS) ls_count_kernel(const uint8_t* __restrict__ text, LsBlocks B, uint32_t* __restrict__ nlines, uint8_t* __restrict__ nonascii) {
+    const uint32_t b = (blockIdx.x * LS_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (b >= B.n) return;
+    const uint64_t bs = B.bs[b], be = B.be[b];
+    uint32_t cnt = 0, hi = 0;
+    for (uint64_t p = bs + lane; p < be; p += 32) {
+        cnt += ls_is_line(text, bs, p) ? 1u : 0u;
+        hi |= text[p] & 0x80u;
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    hi = __reduce_or_sync(0xffffffffu, hi);
+    if (lane == 0) { nlines[b] = cnt; nonascii[b] = hi ? 1 : 0; }
+}
+
+struct U32Load {
+    const uint32_t* p;
+    __device__ unsigned long long operator()(uint64_t i) const { return p[i]; }
+};
+
+__global__ void __launch_bounds__(LS_THREADS) ls_starts_kernel(const uint8_t* __restrict__ text, LsBlocks B, const unsigned long long* __restrict__ line0,
+                                                               unsigned long long* __restrict__ off, uint32_t* __restrict__ blk) {
+    const uint32_t b = (blockIdx.x * LS_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (b >= B.n) return;
+    const uint64_t bs = B.bs[b], be = B.be[b];
+    unsigned long long k = line0[b];
+    for (uint64_t p0 = bs; p0 < be; p0 += 32) {   // uniform trip count
+        const uint64_t p = p0 + lane;
+        const bool is = p < be && ls_is_line(text, bs, p);
+        const uint32_t m = __ballot_sync(0xffffffffu, is);
+        if (is) {
+            const unsigned long long o = k + __popc(m & ((1u << lane) - 1u));
+            off[o] = p;
+            blk[o] = b;
+        }
+        k += __popc(m);
+    }
+}
+
+struct LsNames {   // open-addressing table over the sequence names (the LAST number of a name listed twice, as seq_num resolves it)
+    const uint64_t* hash;   // 0 = empty
+    const uint32_t* id;
+    const uint32_t* name_off;
+    const uint32_t* name_len;
+    const uint8_t* blob;
+    uint32_t mask;
+};
+
+__host__ __device__ inline uint64_t ls_fnv(const uint8_t* s, uint32_t n) {
+    uint64_t h = 1469598103934665603ull;
+    for (uint32_t i = 0; i < n; i++) { h ^= s[i]; h *= 1099511628211ull; }
+    return h;
+}
+
+__device__ __forceinline__ uint32_t ls_lookup(const LsNames& T, const uint8_t* s, uint32_t n) {
+    uint64_t h = ls_fnv(s, n);
+    if (h == 0) h = 1;
+    for (uint32_t k = (uint32_t)h & T.mask;; k = (k + 1) & T.mask) {
+        const uint64_t hk = T.hash[k];
+        if (hk == 0) return 0xFFFFFFFFu;
+        if (hk == h && T.name_len[k] == n) {
+            const uint8_t* b = T.blob + T.name_off[k];
+            bool eq = true;
+            for (uint32_t i = 0; i < n; i++) eq = eq && b[i] == s[i];
+            if (eq) return T.id[k];
+        }
+    }
+}
+
+// parse_u32_strict (util.cpp): digits only, at least one, checked against u32::MAX; *out is written on success only
+__device__ __forceinline__ bool ls_u32(const uint8_t* s, uint64_t n, uint32_t* out) {
+    if (n == 0) return false;
+    unsigned long long acc = 0;
+    for (uint64_t i = 0; i < n; i++) {
+        const uint32_t d = (uint32_t)s[i] - 48u;
+        if (d > 9u) return false;
+        acc = acc * 10 + d;
+        if (acc > 0xFFFFFFFFull) return false;
+    }
+    *out = (uint32_t)acc;
+    return true;
+}
+
+struct LsOut {
+    uint32_t* len;
+    uint8_t* flags;
+    uint32_t *S, *E, *iseq, *fs, *fe;
+    uint32_t *type_off, *type_len, *chrom_len, *id_off, *id_len;
+    unsigned long long* id_hash;
+};
+
+// one thread per line; the rules are those of host_index.cpp: scan_lines for a block whose bytes are all ASCII
+__global__ void __launch_bounds__(LS_THREADS) ls_parse_kernel(const uint8_t* __restrict__ text, LsBlocks B, const unsigned long long* __restrict__ off,
+                                                              const uint32_t* __restrict__ blk, uint64_t n_lines, LsNames T, LsOut O) {
+    const uint64_t i = (uint64_t)blockIdx.x * LS_THREADS + threadIdx.x;
+    if (i >= n_lines) return;
+    const uint64_t p = off[i];
+    const uint32_t b = blk[i];
+    const uint64_t be = B.be[b];
+    uint64_t tab[8];
+    int nt = 0;
+    uint64_t q = p;
+    for (; q < be; q++) {
+        const uint8_t c = text[q];
+        if (c == 10) break;
+        if (c == 9 && nt < 8) tab[nt++] = q;
+    }
+    const uint64_t next = q < be ? q + 1 : be;
+    uint8_t fl = 0;
+    uint32_t S = 0, E = 0, iseq = 0xFFFFFFFFu, fs = 0, fe = 0;
+    uint32_t type_off = 0, type_len = 0xFFFFFFFFu, chrom_len = 0xFFFFFFFFu, id_off = 0, id_len = 0;
+    unsigned long long id_hash = 0;
+    bool numok = false;
+    if (nt >= 3) { type_off = (uint32_t)(tab[1] + 1 - p); type_len = (uint32_t)(tab[2] - tab[1] - 1); }
+    if (nt >= 5) {
+        numok = ls_u32(text + tab[2] + 1, tab[3] - tab[2] - 1, &S) && ls_u32(text + tab[3] + 1, tab[4] - tab[3] - 1, &E);
+        if (numok) {
+            iseq = ls_lookup(T, text + p, (uint32_t)(tab[0] - p));
+            if (iseq != 0xFFFFFFFFu) fl |= LN_I_OK;
+        }
+    }
+    if (nt >= 8 && numok && E != 0 && B.countable[b]) {
+        // fast_id (depth.rs:104-118): the first "ID=" anywhere in column 9, its value up to ';', ' ' or '\t'
+        const uint64_t a = tab[7] + 1;
+        for (uint64_t k = a; k + 2 < q; k++)
+            if (text[k] == 'I' && text[k + 1] == 'D' && text[k + 2] == '=') {
+                uint64_t j = k + 3;
+                while (j < q && text[j] != ';' && text[j] != ' ' && text[j] != 9) j++;
+                const uint32_t lo = min(S, E), hi = max(S, E);
+                fs = lo == 0 ? 0 : lo - 1;
+                fe = hi;
+                chrom_len = (uint32_t)(tab[0] - p);
+                fl |= LN_D_OK;
+                id_off = (uint32_t)(k + 3 - p);
+                id_len = (uint32_t)(j - (k + 3));
+                id_hash = ls_fnv(text + k + 3, id_len);
+                break;
+            }
+    }
+    O.len[i] = (uint32_t)(next - p);
+    O.flags[i] = fl;
+    O.S[i] = S; O.E[i] = E; O.iseq[i] = (fl & LN_I_OK) ? iseq : 0xFFFFFFFFu; O.fs[i] = fs; O.fe[i] = fe;
+    O.type_off[i] = type_off; O.type_len[i] = type_len; O.chrom_len[i] = chrom_len; O.id_off[i] = id_off; O.id_len[i] = id_len;
+    O.id_hash[i] = id_hash;
+}
+
+template <class T> void download(std::vector<T>& v, const DBuf& b, size_t n, cudaStream_t st) {
+    v.resize(n);
+    if (n) GFFX_CUDA(cudaMemcpyAsync(v.data(), b.p, n * sizeof(T), cudaMemcpyDeviceToHost, st));
+}
+
+}  // namespace
+
+// The scanner proper.  Returns false (and leaves *out untouched) when no usable device is there; throws on CUDA errors.
+// On success the text stays on the device: *d_text / *d_text_cap are handed to the engine (record emission reads it).
+bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* out, void** d_text, size_t* d_text_cap) {
+    int ndev = 0;
+    if (device < 0 || cudaGetDeviceCount(&ndev) != cudaSuccess || device >= ndev) { cudaGetLastError(); return false; }
+    PhaseTimer t_all("  GFF line table (device scan)");
+    GFFX_CUDA(cudaSetDevice(device));
+    cudaStream_t st;
+    GFFX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    const size_t nb = H.blocks.size();
+    const uint64_t n = H.gff_len;
+    DBuf text, bs, be, cnt, nl, na, l0, scratch, off, blk, tot;
+    std::vector<DBuf*> temps = {&bs, &be, &cnt, &nl, &na, &l0, &scratch, &off, &blk, &tot};
+    DBuf o_len, o_flags, o_S, o_E, o_iseq, o_fs, o_fe, o_toff, o_tlen, o_clen, o_ioff, o_ilen, o_ihash, t_hash, t_id, t_off, t_len, t_blob;
+    for (DBuf* b : {&o_len, &o_flags, &o_S, &o_E, &o_iseq, &o_fs, &o_fe, &o_toff, &o_tlen, &o_clen, &o_ioff, &o_ilen, &o_ihash, &t_hash, &t_id, &t_off, &t_len, &t_blob})
+        temps.push_back(b);
+    struct Cleanup {
+        std::vector<DBuf*>& v; cudaStream_t st; DBuf* text; bool keep_text = false;
+        ~Cleanup() { for (DBuf* b : v) b->release(); if (!keep_text) text->release(); cudaStreamDestroy(st); }
+    } cleanup{temps, st, &text};
+    // ---- the text: page-locked staging buffers filled by the host threads, copied as they fill -------------------------------
+    {
+        PhaseTimer t("    text -> HBM");
+        text.ensure(n + 32);
+        GFFX_CUDA(cudaMemsetAsync((uint8_t*)text.p + n, 0, 32, st));
+        constexpr size_t CH = 32u << 20;
+        uint8_t* stage[2] = {nullptr, nullptr};
+        cudaEvent_t ev[2];
+        for (int k = 0; k < 2; k++) { GFFX_CUDA(cudaMallocHost((void**)&stage[k], CH)); GFFX_CUDA(cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming)); }
+        const int T = std::max(1, std::min(threads, 16));
+        const int fd = (H.gff == H.gff_map.data() && !H.gff_path.empty()) ? ::open(H.gff_path.c_str(), O_RDONLY) : -1;
+        int k = 0;
+        for (uint64_t o = 0; o < n; o += CH, k ^= 1) {
+            const size_t m = (size_t)std::min<uint64_t>(CH, n - o);
+            GFFX_CUDA(cudaEventSynchronize(ev[k]));   // the copy that last used this buffer
+            std::vector<std::thread> th;
+            for (int t0 = 0; t0 < T; t0++)
+                th.emplace_back([&, t0] {
+                    const size_t a = m * (size_t)t0 / (size_t)T, z = m * (size_t)(t0 + 1) / (size_t)T;
+                    // from the file itself where there is one: pread copies page cache -> staging without faulting the mapping's
+                    // pages into this process one by one (50 ms -> 15 ms for 416 MB)
+                    size_t done = fd >= 0 ? 0 : z - a;
+                    while (fd >= 0 && done < z - a) {
+                        const ssize_t r = pread(fd, stage[k] + a + done, z - a - done, (off_t)(o + a + done));
+                        if (r <= 0) { done = 0; break; }
+                        done += (size_t)r;
+                    }
+                    if (fd < 0 || done != z - a) memcpy(stage[k] + a, H.gff + o + a, z - a);
+                });
+            for (auto& x : th) x.join();
+            GFFX_CUDA(cudaMemcpyAsync((uint8_t*)text.p + o, stage[k], m, cudaMemcpyHostToDevice, st));
+            GFFX_CUDA(cudaEventRecord(ev[k], st));
+        }
+        GFFX_CUDA(cudaStreamSynchronize(st));
+        for (int j = 0; j < 2; j++) { cudaFreeHost(stage[j]); cudaEventDestroy(ev[j]); }
+        if (fd >= 0) ::close(fd);
+    }
+    PhaseTimer t_k("    kernels + read-back");
+    PhaseTimer* t_pre = new PhaseTimer("      blocks, names, counts");
+    // ---- blocks and sequence names ---------------------------------------------------------------------------------------------
+    std::vector<uint64_t> h_bs(nb), h_be(nb);
+    std::vector<uint8_t> h_countable(nb);
+    for (size_t b = 0; b < nb; b++) {
+        const bool scan = H.block_scannable(b);
+        h_bs[b] = scan ? H.blocks[b].start : 0;
+        h_be[b] = scan ? std::min<uint64_t>(H.blocks[b].end, n) : 0;
+        h_countable[b] = H.block_countable(b) && H.blocks[b].end <= n;
+    }
+    upload(bs, h_bs, st); upload(be, h_be, st); upload(cnt, h_countable, st);
+    size_t cap = 16;
+    while (cap < 2 * H.seq_num.size() + 2) cap <<= 1;
+    std::vector<uint64_t> th(cap, 0);
+    std::vector<uint32_t> tid(cap, 0), toff(cap, 0), tlen(cap, 0);
+    std::vector<uint8_t> blob;
+    for (const auto& kv : H.seq_num) {
+        uint64_t h = ls_fnv((const uint8_t*)kv.first.data(), (uint32_t)kv.first.size());
+        if (h == 0) h = 1;
+        size_t k = (size_t)h & (cap - 1);
+        while (th[k]) k = (k + 1) & (cap - 1);
+        th[k] = h; tid[k] = kv.second; toff[k] = (uint32_t)blob.size(); tlen[k] = (uint32_t)kv.first.size();
+        blob.insert(blob.end(), kv.first.begin(), kv.first.end());
+    }
+    blob.push_back(0);
+    upload(t_hash, th, st); upload(t_id, tid, st); upload(t_off, toff, st); upload(t_len, tlen, st); upload(t_blob, blob, st);
+    const LsNames T{t_hash.as<uint64_t>(), t_id.as<uint32_t>(), t_off.as<uint32_t>(), t_len.as<uint32_t>(), t_blob.as<uint8_t>(), (uint32_t)cap - 1};
+    const LsBlocks B{bs.as<uint64_t>(), be.as<uint64_t>(), cnt.as<uint8_t>(), (uint32_t)nb};
+    // ---- lines per block, their first line numbers, their offsets ------------------------------------------------------------------
+    typedef unsigned long long ull;
+    nl.ensure(nb * 4 + 4); na.ensure(nb + 1); l0.ensure((nb + 1) * 8); tot.ensure(8);
+    const unsigned warps_grid = (unsigned)((nb * 32 + LS_THREADS - 1) / LS_THREADS);
+    ls_count_kernel<<<warps_grid, LS_THREADS, 0, st>>>(text.as<uint8_t>(), B, nl.as<uint32_t>(), na.as<uint8_t>());
+    scratch.ensure(scan_scratch_elems(nb) * 8);
+    device_scan<ull, OpSum, U32Load, PtrStore<ull>, false, false>(U32Load{nl.as<uint32_t>()}, PtrStore<ull>{l0.as<ull>()}, nb, OpSum(), 0ull, scratch.as<ull>(),
+                                                                tot.as<ull>(), st);
+    ull n_lines = 0;
+    GFFX_CUDA(cudaMemcpyAsync(&n_lines, tot.p, 8, cudaMemcpyDeviceToHost, st));
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    GFFX_CUDA(cudaGetLastError());
+    if (n_lines >= (1ull << 32) - 1) throw Err(E_FORMAT, "more than 2^32-2 GFF lines inside blocks");
+    delete t_pre;
+    RawLines R;
+    const size_t L = (size_t)n_lines;
+    PhaseTimer* t_al = new PhaseTimer("      output buffers");
+    off.ensure(std::max<size_t>(L, 1) * 8); blk.ensure(std::max<size_t>(L, 1) * 4);
+    for (DBuf* b : {&o_len, &o_S, &o_E, &o_iseq, &o_fs, &o_fe, &o_toff, &o_tlen, &o_clen, &o_ioff, &o_ilen}) b->ensure(std::max<size_t>(L, 1) * 4);
+    o_flags.ensure(std::max<size_t>(L, 1)); o_ihash.ensure(std::max<size_t>(L, 1) * 8);
+    delete t_al;
+    if (L) {
+        ls_starts_kernel<<<warps_grid, LS_THREADS, 0, st>>>(text.as<uint8_t>(), B, l0.as<ull>(), off.as<ull>(), blk.as<uint32_t>());
+        const LsOut O{o_len.as<uint32_t>(), o_flags.as<uint8_t>(), o_S.as<uint32_t>(), o_E.as<uint32_t>(), o_iseq.as<uint32_t>(), o_fs.as<uint32_t>(),
+                      o_fe.as<uint32_t>(), o_toff.as<uint32_t>(), o_tlen.as<uint32_t>(), o_clen.as<uint32_t>(), o_ioff.as<uint32_t>(), o_ilen.as<uint32_t>(),
+                      o_ihash.as<ull>()};
+        ls_parse_kernel<<<(unsigned)((L + LS_THREADS - 1) / LS_THREADS), LS_THREADS, 0, st>>>(text.as<uint8_t>(), B, off.as<ull>(), blk.as<uint32_t>(), L, T, O);
+    }
+    if (getenv("GFFX_TIMING")) { PhaseTimer tk("      (kernels, synchronised)"); GFFX_CUDA(cudaStreamSynchronize(st)); }
+    // ---- read-back ---------------------------------------------------------------------------------------------------------------------
+    PhaseTimer t_rb("      read-back");
+    static_assert(sizeof(ull) == sizeof(uint64_t), "u64");
+    download(R.t.off, off, L, st); download(R.t.blk, blk, L, st); download(R.t.len, o_len, L, st); download(R.t.flags, o_flags, L, st);
+    download(R.t.S, o_S, L, st); download(R.t.E, o_E, L, st); download(R.t.iseq, o_iseq, L, st); download(R.t.fs, o_fs, L, st); download(R.t.fe, o_fe, L, st);
+    download(R.type_off, o_toff, L, st); download(R.type_len, o_tlen, L, st); download(R.chrom_len, o_clen, L, st);
+    download(R.id_off, o_ioff, L, st); download(R.id_len, o_ilen, L, st); download(R.id_hash, o_ihash, L, st);
+    download(R.blk_nlines, nl, nb, st); download(R.blk_nonascii, na, nb, st);
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    GFFX_CUDA(cudaGetLastError());
+    *out = std::move(R);
+    *d_text = text.p;
+    *d_text_cap = text.cap;
+    cleanup.keep_text = true;
+    return true;
+}
+
+}  // namespace gffx
+namespace gffx {
+void device_text_release(void* p, int device) {
+    if (!p) return;
+    int cur = 0;
+    cudaGetDevice(&cur);
+    cudaSetDevice(device);
+    cudaFree(p);
+    cudaSetDevice(cur);
+}
+}  // namespace gffx

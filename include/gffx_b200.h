@@ -99,6 +99,12 @@ uint64_t gffx_index_n_roots(const gffx_index* idx);
 uint64_t gffx_index_n_blocks(const gffx_index* idx);
 uint64_t gffx_index_n_lines(const gffx_index* idx);
 uint64_t gffx_index_n_ids(const gffx_index* idx);
+/* The GFF line table (what the reference re-parses per run: src/commands/intersect.rs:284-321,
+ * src/commands/depth.rs:131-157): a digest over every column, the type / chromosome / ID dictionaries and the per-block facts,
+ * and where the table came from: 0 the host scanner, 1 the device scanner, 2 the side-car cache `<gff>.b200cache` (written by
+ * the first open of a GFF, keyed by its size + mtime + the block list; GFFX_CACHE=0 disables it, GFFX_LINE_SCAN=host|device
+ * picks the scanner).  Equal digests = equal tables. */
+int gffx_index_lines_info(const gffx_index* idx, uint64_t* digest, int* source);
 uint64_t gffx_index_device_bytes(const gffx_index* idx);
 /* Where sequence `seq` sits in the engine's coordinate system (diagnostic).  TreeIndexData holds one tree per sequence
  * with no limit on their number (src/utils/tree_index.rs:36-82); the engine lays the sequences side by side on at most
