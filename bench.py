@@ -284,7 +284,7 @@ def workload_config(args, n_roots, q):
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------
-JOIN_NAME = "root join + rank-space scatter (wj_count_kernel, offsets scan, wj_expand_kernel)"
+JOIN_NAME = "root join + rank-space scatter (wj_root_kernel, offsets scan, wj_expand_kernel)"
 
 
 def stage_table(q, p, l_sel, e_out):

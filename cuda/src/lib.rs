@@ -49,6 +49,10 @@ extern "C" {
                              d_end: *mut *const u32, n: *mut u64) -> c_int;   // regions stay in HBM: pass them on with GFFX_F_DEVICE_INPUT (flag 1)
     fn gffx_gather_text(idx: *mut GffxIndex, ranges: *const u64, n: u64, flags: u32, text: *mut *const u8, n_bytes: *mut u64) -> c_int;
     fn gffx_write_text(text: *const u8, n_bytes: u64, out_path: *const c_char) -> c_int;
+    fn gffx_parse_reads(idx: *const GffxIndex, path: *const c_char, chr: *mut *mut u32, start: *mut *mut u32, end: *mut *mut u32, n: *mut u64,
+                        stats: *mut u64) -> c_int;
+    fn gffx_index_lines_info(idx: *const GffxIndex, digest: *mut u64, source: *mut c_int) -> c_int;
+    fn gffx_free(p: *mut std::ffi::c_void);
     fn gffx_counts_begin(idx: *mut GffxIndex, kind: c_int, out: *mut *mut GffxCounts) -> c_int;
     fn gffx_counts_add(st: *mut GffxCounts, chr: *const u32, start: *const u32, end: *const u32, n: u64, flags: u32) -> c_int;
     fn gffx_counts_write(st: *mut GffxCounts, out_path: *const c_char) -> c_int;
@@ -84,6 +88,21 @@ impl DeviceIndex {
         let p = unsafe { std::slice::from_raw_parts(gffx_result_pairs(r), 3 * n) };
         let v = p.chunks_exact(3).map(|t| (t[0], t[1], t[2])).collect();
         unsafe { gffx_result_free(r) };
+        Ok(v)
+    }
+
+    /// the read source of depth / coverage from a SAM / BAM file: what process_bam (depth.rs:297-423) and
+    /// collect_by_root_from_bam (coverage.rs:125-205) take from rust-htslib, as (chr_id, start, end) triples in file order
+    pub fn parse_reads(&self, path: &std::path::Path) -> Result<Vec<(u32, u32, u32)>> {
+        let p = CString::new(path.to_string_lossy().as_bytes())?;
+        let (mut c, mut s, mut e, mut n) = (ptr::null_mut(), ptr::null_mut(), ptr::null_mut(), 0u64);
+        check(unsafe { gffx_parse_reads(self.0, p.as_ptr(), &mut c, &mut s, &mut e, &mut n, ptr::null_mut()) })?;
+        let n = n as usize;
+        let v = unsafe {
+            let (cs, ss, es) = (std::slice::from_raw_parts(c, n), std::slice::from_raw_parts(s, n), std::slice::from_raw_parts(e, n));
+            (0..n).map(|i| (cs[i], ss[i], es[i])).collect()
+        };
+        unsafe { gffx_free(c as *mut _); gffx_free(s as *mut _); gffx_free(e as *mut _) };
         Ok(v)
     }
 

@@ -370,52 +370,63 @@ static __global__ void __launch_bounds__(WJ_EXP_THREADS)
     const unsigned long long per = min((unsigned long long)WJ_EXP_CHUNK, max(32ull, (total + n_warps - 1) / n_warps));
     for (uint64_t chunk = (uint64_t)blockIdx.x * (WJ_EXP_THREADS / 32) + (threadIdx.x >> 5); chunk * per < total; chunk += n_warps) {
         const unsigned long long p0 = chunk * per, p1 = min(p0 + per, total);
-        uint32_t lo = 0, hi = n_ent;   // off[lo] <= p0 < off[hi]
+        // the interval of the chunk's first pair: off[lo] <= p0 < off[hi], 32 pivots per step (a lane each), so a table of 60 k
+        // offsets is settled in four dependent loads instead of sixteen
+        uint32_t lo = 0, hi = n_ent;
         while (hi - lo > 1) {
-            const uint32_t mid = lo + ((hi - lo) >> 1);
-            if (__ldg(off + mid) <= p0) lo = mid;
-            else hi = mid;
+            const uint32_t span = hi - lo, step = (span + 32u) / 33u;   // pivots lo + step * (lane + 1), all < hi for the lanes that count
+            const uint32_t piv = lo + step * (lane + 1u);
+            const bool le = piv < hi && __ldg(off + piv) <= p0;
+            const uint32_t m = __ballot_sync(0xffffffffu, le);          // monotone: the lanes with off[piv] <= p0 form a prefix
+            const uint32_t k = (uint32_t)__popc(m);                     // lo moves to the last such pivot, hi to the first other one
+            const uint32_t nlo = k ? lo + step * k : lo, nhi = min(hi, lo + step * (k + 1u));
+            lo = nlo; hi = nhi;
         }
         uint32_t j = lo;   // off[j] <= p0 < off[j + 1]
         unsigned long long p = p0;
-        while (true) {
-            const unsigned long long pe = min((unsigned long long)__ldg(off + j + 1), p1);   // this interval's pairs in the chunk: [p, pe)
-            const uint4 v = __ldg(ent4 + j);
-            const uint32_t vb = __ldg(ent_base + j);   // the record leaves the engine in the sequence's own coordinates
-            const uint32_t c0 = v.z, c1 = v.x - vb, c2 = v.y - vb;   // word w of the pair array holds component w % 3
-            const unsigned long long w0 = 3ull * p, w1 = 3ull * pe;
-            unsigned long long wa = min((w0 + 3ull) & ~3ull, w1);   // first 16-byte boundary at or after w0
-            if (w0 + lane < wa) {
-                const uint32_t k = (uint32_t)((w0 + lane) % 3ull);
-                __stcs(pairs + w0 + lane, k == 0 ? c0 : k == 1 ? c1 : c2);
-            }
-            const unsigned long long wb = wa + ((w1 - wa) & ~3ull);   // end of the whole vectors
-            if (wa < wb) {
-                uint32_t k = (uint32_t)((wa + 4ull * lane) % 3ull);
-                uint4* g = reinterpret_cast<uint4*>(pairs + wa);
-                const uint64_t nv = (wb - wa) >> 2;
-                for (uint64_t u = lane; u < nv; u += 32) {
-                    // components k, k+1, k+2, k (mod 3); the next vector of this lane is 128 words on: k advances by 128 % 3 = 2
-                    const uint4 x = k == 0 ? make_uint4(c0, c1, c2, c0) : k == 1 ? make_uint4(c1, c2, c0, c1) : make_uint4(c2, c0, c1, c2);
-                    __stcs(g + u, x);
-                    k = k >= 1 ? k - 1 : 2;
+        // the records of the next 32 intervals with pairs are fetched lane-parallel (offset, interval, base: three independent
+        // loads per lane) and handed round by shuffle: the chain of dependent loads per interval was most of a warp's time
+        while (p < p1) {
+            // lane t looks at interval j + t: does it own pairs beyond p?
+            const uint32_t jj = j + lane;
+            const unsigned long long oe = jj < n_ent ? (unsigned long long)__ldg(off + jj + 1) : 0ull;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            uint32_t vb = 0;
+            const bool has = jj < n_ent && oe > p;
+            if (has) { v = __ldg(ent4 + jj); vb = __ldg(ent_base + jj); }
+            uint32_t todo = __ballot_sync(0xffffffffu, has);
+            if (!todo) { j += 32; continue; }   // 32 intervals nobody hit
+            for (; todo && p < p1; todo &= todo - 1u) {
+                const int t = __ffs(todo) - 1;
+                const unsigned long long te = __shfl_sync(0xffffffffu, oe, t);
+                const uint32_t c0 = __shfl_sync(0xffffffffu, v.z, t);
+                const uint32_t c1 = __shfl_sync(0xffffffffu, v.x - vb, t), c2 = __shfl_sync(0xffffffffu, v.y - vb, t);   // the sequence's own coordinates
+                const unsigned long long pe = min(te, p1);   // this interval's pairs in the chunk: [p, pe)
+                const unsigned long long w0 = 3ull * p, w1 = 3ull * pe;   // word w of the pair array holds component w % 3
+                unsigned long long wa = min((w0 + 3ull) & ~3ull, w1);   // first 16-byte boundary at or after w0
+                if (w0 + lane < wa) {
+                    const uint32_t k = (uint32_t)((w0 + lane) % 3ull);
+                    __stcs(pairs + w0 + lane, k == 0 ? c0 : k == 1 ? c1 : c2);
                 }
+                const unsigned long long wb = wa + ((w1 - wa) & ~3ull);   // end of the whole vectors
+                if (wa < wb) {
+                    uint32_t k = (uint32_t)((wa + 4ull * lane) % 3ull);
+                    uint4* g = reinterpret_cast<uint4*>(pairs + wa);
+                    const uint64_t nv = (wb - wa) >> 2;
+                    for (uint64_t u = lane; u < nv; u += 32) {
+                        // components k, k+1, k+2, k (mod 3); the next vector of this lane is 128 words on: k advances by 128 % 3 = 2
+                        const uint4 x = k == 0 ? make_uint4(c0, c1, c2, c0) : k == 1 ? make_uint4(c1, c2, c0, c1) : make_uint4(c2, c0, c1, c2);
+                        __stcs(g + u, x);
+                        k = k >= 1 ? k - 1 : 2;
+                    }
+                }
+                if (wb + lane < w1) {
+                    const uint32_t k = (uint32_t)((wb + lane) % 3ull);
+                    __stcs(pairs + wb + lane, k == 0 ? c0 : k == 1 ? c1 : c2);
+                }
+                p = pe;
             }
-            if (wb + lane < w1) {
-                const uint32_t k = (uint32_t)((wb + lane) % 3ull);
-                __stcs(pairs + wb + lane, k == 0 ? c0 : k == 1 ? c1 : c2);
-            }
-            p = pe;
-            if (p >= p1) break;
-            // next interval with pairs: the first j' > j with off[j' + 1] > p (it exists: p < total = off[n_ent])
-            j++;
-            while (true) {
-                const uint32_t jj = j + lane;
-                const bool has = jj < n_ent && __ldg(off + jj + 1) > p;
-                const uint32_t bal = __ballot_sync(0xffffffffu, has);
-                if (bal) { j += (uint32_t)__ffs(bal) - 1u; break; }
-                j += 32;
-            }
+            j += 32;
         }
     }
 }
