@@ -22,11 +22,15 @@
 
 namespace gffx {
 
-constexpr int WR_FB = 10;                   // fine bins per window: 2^WR_FB (the partition grid's shift is >= 12)
+#ifndef GFFX_WR_FB
+#define GFFX_WR_FB 10
+#endif
+constexpr int WR_FB = GFFX_WR_FB;           // fine bins per window: 2^WR_FB (the partition grid's shift is >= 12)
 constexpr uint32_t WR_NBF = 1u << WR_FB;
 constexpr uint32_t WR_TAIL_BINS = 8;        // a region longer than this many fine bins belongs to the tail part
 constexpr uint32_t WR_SERIAL_MAX = 48;      // a root with more positions to test than this gets the whole warp
-static_assert(2 * WR_NBF == 4 * WJ_THREADS, "the histogram scan gives every thread four counters");
+constexpr int WR_CPT = (int)(2 * WR_NBF / WJ_THREADS);   // counters per thread in the histogram scan
+static_assert(WR_CPT * WJ_THREADS == 2 * WR_NBF && (WR_CPT == 2 || WR_CPT == 4), "the histogram scan gives every thread two or four counters");
 
 struct WrSmem {
     uint32_t hist[2 * WR_NBF + 4];   // regions per key (fine bin; + WR_NBF for the tail part) -> first sorted position; [2 * WR_NBF] = all
@@ -79,8 +83,11 @@ __device__ __noinline__ unsigned long long wj_round_global(const WinBins& C, uin
 // asynchronous copies (cp.async.bulk, completion on an mbarrier: the copy engine moves the bytes while the warps sort the
 // tile) and the look-up becomes a short binary search in shared memory.  A window whose part exceeds WR_SLICE_CAP values
 // keeps the global look-up.
-constexpr uint32_t WR_SLICE_CAP = 9216;        // values of X a CTA can hold (36 KB)
-constexpr uint32_t WR_XOFF_STRIDE = 1032;      // u16 cells per window in the offset table: WR_NBF + 1 used, rows 16-byte multiples
+#ifndef GFFX_WR_SLICE_CAP
+#define GFFX_WR_SLICE_CAP 9216
+#endif
+constexpr uint32_t WR_SLICE_CAP = GFFX_WR_SLICE_CAP;   // values of X a CTA can hold (36 KB)
+constexpr uint32_t WR_XOFF_STRIDE = WR_NBF + 8;   // u16 cells per window in the offset table: WR_NBF + 1 used, rows 16-byte multiples
 constexpr size_t WR_SLICE_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)WR_XOFF_STRIDE * 2;
 struct RankSlices {
     const uint32_t* xw0;    // n_win: index into RankSpace::X of the window's first value
@@ -120,7 +127,10 @@ __device__ __forceinline__ uint32_t rank_lb_slice(const uint32_t* sx, const uint
 #define WR_MIN_CTAS 3
 #endif
 template <int MODE, bool INVERT, bool FILT, bool SLICE>
-__global__ void __launch_bounds__(WJ_THREADS, SLICE ? 2 : WR_MIN_CTAS)
+#ifndef WR_SLICE_CTAS
+#define WR_SLICE_CTAS 2
+#endif
+__global__ void __launch_bounds__(WJ_THREADS, SLICE ? WR_SLICE_CTAS : WR_MIN_CTAS)
     wj_root_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint2* __restrict__ qse, uint64_t n, uint8_t* ent_hit,
                    unsigned long long* ent_cnt, unsigned long long* __restrict__ n_pairs, uint32_t* __restrict__ err, RankSpace R, FilterArrays F,
                    uint32_t tail_bins, RankSlices XS) {
@@ -196,7 +206,8 @@ __global__ void __launch_bounds__(WJ_THREADS, SLICE ? 2 : WR_MIN_CTAS)
             s[2 * k] = v.x; e[2 * k] = v.y; s[2 * k + 1] = v.z; e[2 * k + 1] = v.w;
         }
         // ---- 1. counting sort of the segment by key = fine bin of the start (+ WR_NBF: tail part) -------------------------
-        *reinterpret_cast<uint4*>(&S.hist[4 * tid]) = make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int k = 0; k < WR_CPT; k++) S.hist[WR_CPT * tid + k] = 0;
         if (tid == 0) { S.hist[2 * WR_NBF] = 0; S.maxlen = 0; S.re_max = 0; S.tot = 0; S.next_tail = 0; S.next_scat = 0; }
         __syncthreads();
         uint32_t kr[WJ_QPT];   // key << 12 | rank among the segment's regions of that key
@@ -217,10 +228,13 @@ __global__ void __launch_bounds__(WJ_THREADS, SLICE ? 2 : WR_MIN_CTAS)
         if (lane == 0 && my_re) { atomicMax(&S.maxlen, my_len); atomicMax(&S.re_max, my_re); }
         __syncthreads();
         {
-            const uint4 c = *reinterpret_cast<const uint4*>(&S.hist[4 * tid]);
+            uint32_t c[WR_CPT], sum = 0;
+#pragma unroll
+            for (int k = 0; k < WR_CPT; k++) { c[k] = S.hist[WR_CPT * tid + k]; sum += c[k]; }
             uint32_t tot;
-            const uint32_t ex = block_scan_excl(c.x + c.y + c.z + c.w, OpSum(), 0u, S.scan, &tot);
-            *reinterpret_cast<uint4*>(&S.hist[4 * tid]) = make_uint4(ex, ex + c.x, ex + c.x + c.y, ex + c.x + c.y + c.z);
+            uint32_t ex = block_scan_excl(sum, OpSum(), 0u, S.scan, &tot);
+#pragma unroll
+            for (int k = 0; k < WR_CPT; k++) { S.hist[WR_CPT * tid + k] = ex; ex += c[k]; }
             if (tid == 0) S.hist[2 * WR_NBF] = tot;
         }
         __syncthreads();
