@@ -14,7 +14,7 @@ struct CountsState {
     DBuf d_u_space, d_u_chrom, d_u_blk, d_u_base, d_irr_base, d_u_line0, d_u_seg0, d_l_fs, d_l_fe, d_l_sfs, d_l_sfe, d_g_s, d_g_e, d_g_ss, d_g_se;
     DBuf d_id_unit0, d_id_units, d_irr_grp, d_irr_pos, d_grp_off, d_grp_seq, d_grp_s, d_grp_e, d_blk_space;
     DJoin irr;
-    DBuf d_gsp0, d_gap_bits, d_gap_a, d_gap_b, d_gap_seg, d_irr_blk, d_u_rs, d_u_re;
+    DBuf d_gsp0, d_gap_bits, d_gs_first, d_gap_a, d_gap_b, d_gap_seg, d_irr_blk, d_u_rs, d_u_re;
     // ---- accumulators of the running job ----
     DBuf d_Hs, d_He, d_G, d_S, d_E, d_bits, d_diff, d_P, d_routed, d_scratch, d_err;
     DBuf r_chrom, r_start, r_end, r_value, r_flag, r_pos, o_id, o_chrom, o_start, o_end, o_value;
@@ -27,7 +27,7 @@ struct CountsState {
 
     std::vector<DBuf*> all() {
         return {&d_rank, &d_cov, &d_X, &d_dir, &d_u_space, &d_u_chrom, &d_u_blk, &d_u_base, &d_irr_base, &d_u_line0, &d_u_seg0, &d_l_fs, &d_l_fe, &d_l_sfs,
-                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_gsp0, &d_gap_bits, &d_gap_a, &d_gap_b, &d_gap_seg, &d_irr_blk, &d_u_rs, &d_u_re, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
+                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_gsp0, &d_gap_bits, &d_gs_first, &d_gap_a, &d_gap_b, &d_gap_seg, &d_irr_blk, &d_u_rs, &d_u_re, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
                 &d_grp_s, &d_grp_e, &d_blk_space, &d_Hs, &d_He, &d_G, &d_S, &d_E, &d_bits, &d_diff, &d_P, &d_routed, &d_scratch, &d_err,
                 &r_chrom, &r_start, &r_end, &r_value, &r_flag, &r_pos, &o_id, &o_chrom, &o_start, &o_end, &o_value};
     }
@@ -80,6 +80,7 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     upload(C->d_blk_space, h.blk_space, st);
     upload(C->d_gsp0, h.gsp0, st);
     upload(C->d_gap_bits, h.gap_bits, st);
+    upload(C->d_gs_first, h.gs_first, st);
     upload(C->d_gap_a, h.gap_a, st);
     upload(C->d_gap_b, h.gap_b, st);
     upload(C->d_gap_seg, h.gap_seg, st);
@@ -93,7 +94,7 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     GFFX_CUDA(cudaEventCreate(&C->ev1));
     // keep the scalars, drop the bulk
     for (auto* v : {&h.X, &h.dir, &h.u_space, &h.u_chrom, &h.u_blk, &h.u_base, &h.irr_base, &h.u_line0, &h.u_seg0, &h.l_fs, &h.l_fe, &h.l_sfs, &h.l_sfe, &h.g_s,
-                    &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space, &h.gsp0, &h.gap_bits, &h.gap_a, &h.gap_b, &h.gap_seg, &h.irr_blk, &h.u_rs, &h.u_re})
+                    &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space, &h.gsp0, &h.gap_bits, &h.gs_first, &h.gap_a, &h.gap_b, &h.gap_seg, &h.irr_blk, &h.u_rs, &h.u_re})
         std::vector<uint32_t>().swap(*v);
     h.irr = JoinHost();
     C->built = true;
@@ -140,6 +141,7 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.cov = C->d_cov.as<CovSpace>();
     D.gsp0 = C->d_gsp0.as<uint32_t>();
     D.gap_bits = C->d_gap_bits.as<uint32_t>();
+    D.gs_first = C->d_gs_first.as<uint32_t>();
     D.gap_a = C->d_gap_a.as<uint32_t>();
     D.gap_b = C->d_gap_b.as<uint32_t>();
     D.gap_seg = C->d_gap_seg.as<uint32_t>();
@@ -148,7 +150,6 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.irr_grp = C->d_irr_grp.as<uint32_t>();
     D.irr_pos = C->d_irr_pos.as<uint32_t>();
     D.irr_base = C->d_irr_base.as<uint32_t>();
-    D.ent_base = E->d_ent_base.as<uint32_t>();
     D.grp_off = C->d_grp_off.as<uint32_t>();
     D.grp_seq = C->d_grp_seq.as<uint32_t>();
     D.grp_s = C->d_grp_s.as<uint32_t>();

@@ -34,6 +34,7 @@ struct CountsDev {
     const CovSpace* cov;
     const uint32_t* gsp0;       // per space: its gaps are [gsp0[s], gsp0[s+1]) of the arrays below, the last one a sentinel
     const uint32_t* gap_bits;   // per rank slot: its coordinate is the `a` of a gap (counts_index.h)
+    const uint32_t* gs_first;   // per rank slot: first gap of the space with a >= the slot's coordinate
     const uint32_t* gap_a;      // gaps by (space, a), one 0xFFFFFFFF sentinel per space
     const uint32_t* gap_b;
     const uint32_t* gap_seg;    // left segment of the gap
@@ -41,7 +42,6 @@ struct CountsDev {
     const uint32_t* irr_grp;
     const uint32_t* irr_pos;
     const uint32_t* irr_base;   // per JI entry: base of its sequence on the virtual sequence (a private space keeps the lines' own coordinates)
-    const uint32_t* ent_base;   // the same per JR entry
     const uint32_t* grp_off;
     const uint32_t* grp_seq;
     const uint32_t* grp_s;
@@ -82,17 +82,15 @@ __device__ __forceinline__ void depth_space_update(const CountsDev& D, uint32_t 
     atomicAdd(D.He + S.slot0 + lbe, 1u);                  // slot lb(end):   counted by E[k] for every X_k >= end
     // gaps [a,b] the region reaches across: start < a and b < end; a is a coordinate of the space strictly inside the region
     if (gaps) {
-        uint32_t lo = __ldg(D.gsp0 + sp), hi = __ldg(D.gsp0 + sp + 1) - 1u;   // first gap with a > start (the sentinel at the latest)
-        while (lo < hi) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (__ldg(D.gap_a + mid) <= rs) lo = mid + 1; else hi = mid;
-        }
+        const uint32_t lo = __ldg(D.gs_first + ub);   // first gap with a > start: a >= X[ub(start)] (the sentinel at the latest)
         for (uint32_t j = lo;; j++) {
             if (__ldg(D.gap_a + j) >= re) break;              // sorted by a; the space's sentinel ends it
             if (__ldg(D.gap_b + j) < re) atomicAdd(D.G + __ldg(D.gap_seg + j), 1u);
         }
     }
 }
+
+constexpr unsigned long long COV_DIRECT_WORDS = 4;   // whole 64-base words a region may cover and still set them directly
 
 __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp, uint32_t rs, uint32_t re) {
     const uint4 raw = __ldg(reinterpret_cast<const uint4*>(D.cov + sp));
@@ -111,7 +109,14 @@ __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp
     } else {
         if ((__ldcg(D.bits + wa) & ma) != ma) atomicOr(D.bits + wa, ma);
         if ((__ldcg(D.bits + wb) & mb) != mb) atomicOr(D.bits + wb, mb);
-        if (wb > wa + 1) {
+        if (wb - wa - 1 <= COV_DIRECT_WORDS) {
+            // a short region (a read): its few whole words are OR-ed like the partial ones — once a word is full, which at
+            // sequencing depth it is after the first reads, this is a load from the sector the partial words came from, where
+            // the difference array costs two atomics per region whatever the bitmap already holds (profiles/r02v: 1.1 G L2
+            // sectors per 100 M reads, the kernel L2-bound)
+            for (unsigned long long w = wa + 1; w < wb; w++)
+                if (__ldcg(D.bits + w) != ~0ull) atomicOr(D.bits + w, ~0ull);
+        } else {
             atomicAdd(D.diff + wa + 1, 1);
             atomicAdd(D.diff + wb, -1);
         }

@@ -194,6 +194,7 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             return p.end < q.end;
         });
         C.gap_bits.assign(((size_t)C.n_slots + 31) / 32 + 1, 0);
+        C.gs_first.assign(std::max<uint32_t>(C.n_slots, 1), 0);
         C.gsp0.assign((size_t)n_spaces + 1, 0);
         size_t k = 0;
         for (uint32_t s = 0; s < n_spaces; s++) {
@@ -212,6 +213,14 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             for (uint32_t j = g0; j + 1 < C.gap_a.size(); j++) {   // a is a coordinate of the space: mark its slot
                 const uint32_t slot = r.slot0 + (uint32_t)(std::lower_bound(x.begin(), x.end(), C.gap_a[j]) - x.begin());
                 C.gap_bits[slot >> 5] |= 1u << (slot & 31);
+            }
+            {   // entry point per slot: the first gap whose a is >= the slot's coordinate (the space's sentinel when there is none)
+                uint32_t j = g0;
+                for (uint32_t i = 0; i < r.cnt; i++) {
+                    while (C.gap_a[j] < x[i]) j++;
+                    C.gs_first[r.slot0 + i] = j;
+                }
+                C.gs_first[r.slot0 + r.cnt] = (uint32_t)C.gap_a.size() - 1;
             }
             k = k1;
         }

@@ -49,7 +49,8 @@ struct CountsIndexHost {
     // gaps between consecutive segments of a unit, [a, b] = [seg.e, next.s], sorted by (space, a), one (0xFFFFFFFF) sentinel after
     // each space's gaps, space s owning [gsp0[s], gsp0[s+1]); gap_bits: one bit per rank slot, set when the slot's coordinate is
     // the `a` of a gap — a read only looks for the gaps inside it when it steps over such a coordinate (counts.cuh)
-    std::vector<uint32_t> gap_a, gap_b, gap_seg, gsp0, gap_bits;
+    // gs_first[slot] = the first gap of the slot's space whose a is >= the slot's coordinate: where that look starts
+    std::vector<uint32_t> gap_a, gap_b, gap_seg, gsp0, gap_bits, gs_first;
     // regular blocks: the block's one tree interval per unit (NONE32 for a unit of an irregular block): coverage derives
     // "some read was routed to this block" from the covered bases inside it
     std::vector<uint32_t> u_rs, u_re;

@@ -77,10 +77,10 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     set_kernel_attributes();
-    for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
+    for (DBuf* b : {&d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_wr_xw0, &d_wr_xlen, &d_wr_xoff, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
@@ -124,16 +124,15 @@ EngineImpl::~EngineImpl() {
     for (Lane& l : lanes)
         if (l.st) cudaStreamSynchronize(l.st);
     for (DBuf& b : lanes[1 - lane_active].bufs) b.release();   // the active lane's buffers are the members, released below
-    for (DBuf* b : {&d_ent_blk, &d_ent_hit, &d_bstart, &d_bend, &d_blk_sel,
+    for (DBuf* b : {&d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_wr_xw0, &d_wr_xlen, &d_wr_xoff, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_ent_base, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
+                    &d_wj_win0, &d_wj_base, &d_seqmap, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
-    dj.release();
     counts_release(this);
     if (h_small) cudaFreeHost(h_small);
     for (auto& S : slots) {
@@ -277,7 +276,7 @@ uint32_t EngineImpl::partition_into(const uint32_t* dc, const uint32_t* ds, cons
     return 3;
 }
 
-// Join index over the root intervals (see join_build.h / join.cuh).
+// Join index over the root intervals (winjoin_build.h: start-sorted records + per-window bin lists).
 void EngineImpl::build_join() {
     const size_t n_seqs = H->seq_names.size();
     const VSeqMap& V = H->vmap;
@@ -288,8 +287,6 @@ void EngineImpl::build_join() {
         const VSeqMap::Seq& m = V.seq[R[i].seq];
         items[i] = JoinItem{m.vseq, m.base + R[i].start, m.base + R[i].end, R[i].fid};
     }
-    JoinHost jh;
-    build_join_host(n_v, items, JOIN_LONG_K, JOIN_MAX_LISTS, &jh);
     // accessor copy: per sequence (start,end,fid) sorted by (start,end)
     seq_sorted_roots.assign(n_seqs, {});
     {
@@ -306,19 +303,6 @@ void EngineImpl::build_join() {
             for (uint32_t i : ids) { flat.push_back(R[i].start); flat.push_back(R[i].end); flat.push_back(R[i].fid); }
         }
     }
-    std::vector<uint32_t> ent_blk(jh.n_entries()), ent_base(jh.n_entries());
-    for (size_t k = 0; k < ent_blk.size(); k++) {
-        ent_blk[k] = H->root_blk[jh.ent_item[k]];
-        ent_base[k] = V.seq[R[jh.ent_item[k]].seq].base;
-    }
-    dj.upload_from(jh, st, &dev_bytes);
-    n_ent = dj.n_ent;
-    J = dj.J;
-    upload(d_ent_blk, ent_blk, st);
-    upload(d_ent_base, ent_base, st);
-    d_ent_hit.ensure(std::max<uint32_t>(n_ent, 1));
-    GFFX_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
-
     // the window-addressed form of the same intervals (winjoin.cuh), used by intersect: on the PARTITION's grid, so that
     // the bucketed regions of one window find their whole index slice in one contiguous piece (copied to shared memory)
     const std::vector<uint32_t>& jwin0 = h_win0;

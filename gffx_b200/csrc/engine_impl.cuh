@@ -115,11 +115,6 @@ class EngineImpl {
     size_t dev_bytes = 0;
     int sm_count = 148;
 
-    // ---- join index -------------------------------------------------------------------------
-    DJoin dj;  // root intervals of the .rit trees; payload = root_fid
-    DBuf d_ent_blk, d_ent_hit, d_ent_base;   // d_ent_base: base of the entry's sequence on its virtual sequence (VSeqMap)
-    uint32_t n_ent = 0;
-    JoinIndex J{};
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
 
     // ---- window-addressed root join (winjoin.cuh): what intersect uses -------------------------

@@ -336,19 +336,6 @@ static __global__ void __launch_bounds__(LINE_THREADS)
     }
 }
 
-// number of selected blocks with a usable start (what merge_blocks_kernel reports as out_counts[1]) when no
-// merged ranges are wanted: the match-only path and join-only calls
-static __global__ void __launch_bounds__(256)
-    count_selected_kernel(const uint64_t* __restrict__ bstart, const uint8_t* __restrict__ blk_sel, uint32_t n_blocks,
-                          unsigned long long* __restrict__ out_counts) {
-    __shared__ uint32_t sm[256 / 32 + 1];
-    const uint32_t b = blockIdx.x * 256 + threadIdx.x;
-    const uint32_t k = (b < n_blocks && blk_sel[b] && bstart[b] != 0xFFFFFFFFFFFFFFFFull) ? 1u : 0u;
-    uint32_t tot;
-    block_scan_excl(k, OpSum(), 0u, sm, &tot);
-    if (threadIdx.x == 0 && tot) atomicAdd(out_counts + 1, (unsigned long long)tot);
-}
-
 // K5, one CTA: selected blocks (sorted by start) -> merged byte ranges, rules of common.rs:199-245:
 // drop sentinel starts, merge while s <= current_end, keep cs < ce and ce <= file_len.
 // Also counts the selected blocks.  out_counts[0] = n_ranges, [1] = n_selected, [2..3] = bytes (u64).

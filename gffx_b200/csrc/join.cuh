@@ -1,20 +1,12 @@
-// join.cuh — K1: the root-level join, replacing IntervalTree::query_interval (src/utils/tree.rs:98-121)
-// and the per-region loop of query_features (src/commands/intersect.rs:139-165).
+// join.cuh — the small interval-list join left from r01's root join: depth / coverage use it for the tree intervals of
+// IRREGULAR blocks only (blocks with several tree intervals or lines outside their one interval; a handful per index, none in
+// a clean annotation — counts.cuh), plus the tile loader of those two kernels.  The root join itself is rootjoin.cuh /
+// winjoin.cuh.
 //
-// Layout in HBM (built once per index, L2-resident: <= ~20 B per root interval):
-//   per sequence the root intervals are sorted by start and split AIList-style into a few lists so
-//   that no interval in a list spans more than JOIN_K following starts (a chromosome-long root would
-//   otherwise drag every forward scan back to index 0).  Per list:
-//     ent_se[j]  = (start,end)  packed 8 B, sorted by start       -> one 8 B load per candidate
-//     ent_fid[j] = root_fid                                        -> read only for emitted pairs
-//     dir[b]     = first j whose running max-end exceeds b<<shift  -> direct-address replacement of the
-//                  lower_bound on the running max-end: every earlier interval ends at or before the bin
-//   A query (seq, rs, re) probes dir[rs>>shift] and scans forward while start < re, testing end > rs:
-//   exactly `iv.start < end && iv.end > start` (tree.rs:110) for any rs/re, including rs >= re.
-//
-// Two passes: join_count_kernel (per-tile pair counts + per-entry hit flags), a device scan of the
-// tile counts, join_emit_kernel (re-search, CTA-level exclusive scan, shared-memory staging,
-// coalesced 4-byte stores of the 12-byte pairs).
+// Layout (join_build.h): per sequence the intervals sorted by start, split AIList-style into a few lists so that no interval
+// of a list spans more than JOIN_LONG_K following starts; per list ent_se[j] = (start, end), ent_fid[j] = payload, and
+// dir[b] = first j whose running max-end exceeds b << shift.  A query (seq, rs, re) probes dir[rs >> shift] and scans forward
+// while start < re, testing end > rs: exactly `iv.start < end && iv.end > start` (src/utils/tree.rs:110) for any rs / re.
 #pragma once
 #include "scan.cuh"
 
@@ -23,7 +15,6 @@ namespace gffx {
 constexpr int JOIN_THREADS = 256;
 constexpr int JOIN_QPT = 4;                       // consecutive queries per thread (one 16 B load per column)
 constexpr int JOIN_TILE = JOIN_THREADS * JOIN_QPT;
-constexpr int JOIN_STAGE_PAIRS = 3072;            // 36 KB of shared memory for pair staging
 constexpr int JOIN_LONG_K = 16;     // an interval that reaches past the start of its 16th successor is "long"
 constexpr int JOIN_MAX_LISTS = 8;   // per sequence
 
@@ -90,84 +81,6 @@ __device__ __forceinline__ void load_queries(const uint32_t* __restrict__ chr, c
                 Q.c[k] = chr[q0 + k]; Q.s[k] = v.x; Q.e[k] = v.y;
                 Q.n = k + 1;
             }
-    }
-}
-
-template <int MODE, bool INVERT>
-__global__ void __launch_bounds__(JOIN_THREADS)
-    join_count_kernel(JoinIndex J, const uint32_t* __restrict__ chr, const uint2* __restrict__ se,
-                      uint64_t n, uint8_t* __restrict__ ent_hit, uint32_t* __restrict__ tile_count,
-                      uint32_t* __restrict__ err) {
-    __shared__ uint32_t sm[JOIN_THREADS / 32 + 1];
-    const uint64_t q0 = (uint64_t)blockIdx.x * JOIN_TILE + (uint64_t)threadIdx.x * JOIN_QPT;
-    Query4 Q;
-    Q.n = 0;
-    if (q0 < n) load_queries(chr, se, n, q0, Q);
-    uint32_t cnt = 0;
-#pragma unroll
-    for (int k = 0; k < JOIN_QPT; k++) {
-        if (k < Q.n) {
-            if (Q.c[k] >= J.n_seqs) { *err = 1; continue; }
-            join_query<MODE, INVERT>(J, Q.c[k], Q.s[k], Q.e[k], [&](uint32_t j, uint2) {
-                cnt++;
-                // ~230 regions hit every root: test in L2 first so that the byte is stored O(1) times, not O(hits)
-                if (!__ldcg(ent_hit + j)) ent_hit[j] = 1;
-            });
-        }
-    }
-    uint32_t tot;
-    block_scan_excl(cnt, OpSum(), 0u, sm, &tot);
-    if (threadIdx.x == 0) tile_count[blockIdx.x] = tot;
-}
-
-template <int MODE, bool INVERT>
-__global__ void __launch_bounds__(JOIN_THREADS)
-    join_emit_kernel(JoinIndex J, const uint32_t* __restrict__ chr, const uint2* __restrict__ se,
-                     uint64_t n, const uint64_t* __restrict__ tile_off, uint32_t* __restrict__ pairs) {
-    __shared__ uint32_t sm[JOIN_THREADS / 32 + 1];
-    __shared__ uint32_t stage[JOIN_STAGE_PAIRS * 3];
-    const uint64_t q0 = (uint64_t)blockIdx.x * JOIN_TILE + (uint64_t)threadIdx.x * JOIN_QPT;
-    Query4 Q;
-    Q.n = 0;
-    if (q0 < n) load_queries(chr, se, n, q0, Q);
-    uint32_t cnt = 0;
-#pragma unroll
-    for (int k = 0; k < JOIN_QPT; k++)
-        if (k < Q.n && Q.c[k] < J.n_seqs) join_query<MODE, INVERT>(J, Q.c[k], Q.s[k], Q.e[k], [&](uint32_t, uint2) { cnt++; });
-    uint32_t tot;
-    uint32_t pos = block_scan_excl(cnt, OpSum(), 0u, sm, &tot);
-    const uint64_t gbase = tile_off[blockIdx.x];
-    if (tot == 0) return;
-    const bool staged = tot <= JOIN_STAGE_PAIRS;
-    uint32_t* dst = staged ? stage : pairs + 3 * gbase;
-#pragma unroll
-    for (int k = 0; k < JOIN_QPT; k++)
-        if (k < Q.n && Q.c[k] < J.n_seqs)
-            join_query<MODE, INVERT>(J, Q.c[k], Q.s[k], Q.e[k], [&](uint32_t j, uint2 se) {
-                dst[3 * pos + 0] = __ldg(J.ent_fid + j);
-                dst[3 * pos + 1] = se.x;
-                dst[3 * pos + 2] = se.y;
-                pos++;
-            });
-    if (staged) {
-        __syncthreads();
-        uint32_t* g = pairs + 3 * gbase;
-        for (uint32_t i = threadIdx.x; i < 3 * tot; i += JOIN_THREADS) __stcs(g + i, stage[i]);
-    }
-}
-
-// per-entry hit flags -> per-block selection flags; entries whose fid has no .gof record are
-// appended to warn_fids (the reference warns about them, intersect.rs:269-272).
-static __global__ void select_blocks_kernel(const uint8_t* __restrict__ ent_hit, const uint32_t* __restrict__ ent_blk,
-                                     const uint32_t* __restrict__ ent_fid, uint32_t n_ent, uint8_t* __restrict__ blk_sel,
-                                     uint32_t* __restrict__ warn_fids, uint32_t* __restrict__ n_warn, uint32_t warn_cap) {
-    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_ent || !ent_hit[j]) return;
-    uint32_t b = ent_blk[j];
-    if (b != 0xFFFFFFFFu) blk_sel[b] = 1;
-    else {
-        uint32_t k = atomicAdd(n_warn, 1u);
-        if (k < warn_cap) warn_fids[k] = ent_fid[j];
     }
 }
 
