@@ -33,7 +33,10 @@ constexpr int WR_CPT = (int)(2 * WR_NBF / WJ_THREADS);   // counters per thread 
 static_assert(WR_CPT * WJ_THREADS == 2 * WR_NBF && (WR_CPT == 2 || WR_CPT == 4), "the histogram scan gives every thread two or four counters");
 
 struct WrSmem {
-    uint32_t hist[2 * WR_NBF + 4];   // regions per key (fine bin; + WR_NBF for the tail part) -> first sorted position; [2 * WR_NBF] = all
+    // regions per key (fine bin; + WR_NBF for the tail part) -> first sorted position; [2 * WR_NBF] = all.  16-bit cells (a tile has
+    // 4096 regions), counted by 32-bit shared atomics on the word that holds two of them: 4 KB instead of 8, which is what lets
+    // three CTAs share an SM next to the rank slice
+    uint16_t hist[2 * WR_NBF + 8];
     uint32_t scan[WJ_WARPS + 1];
     unsigned long long tot;
     uint32_t w_first, w_last;
@@ -128,7 +131,7 @@ __device__ __forceinline__ uint32_t rank_lb_slice(const uint32_t* sx, const uint
 #endif
 template <int MODE, bool INVERT, bool FILT, bool SLICE>
 #ifndef WR_SLICE_CTAS
-#define WR_SLICE_CTAS 2
+#define WR_SLICE_CTAS 3
 #endif
 __global__ void __launch_bounds__(WJ_THREADS, SLICE ? WR_SLICE_CTAS : WR_MIN_CTAS)
     wj_root_kernel(WinBins C, const uint32_t* __restrict__ poff, const uint2* __restrict__ qse, uint64_t n, uint8_t* ent_hit,
@@ -207,7 +210,7 @@ __global__ void __launch_bounds__(WJ_THREADS, SLICE ? WR_SLICE_CTAS : WR_MIN_CTA
         }
         // ---- 1. counting sort of the segment by key = fine bin of the start (+ WR_NBF: tail part) -------------------------
 #pragma unroll
-        for (int k = 0; k < WR_CPT; k++) S.hist[WR_CPT * tid + k] = 0;
+        for (int k = 0; k < WR_CPT; k++) S.hist[WR_CPT * tid + k] = 0;   // (the compiler joins these into word stores)
         if (tid == 0) { S.hist[2 * WR_NBF] = 0; S.maxlen = 0; S.re_max = 0; S.tot = 0; S.next_tail = 0; S.next_scat = 0; }
         __syncthreads();
         uint32_t kr[WJ_QPT];   // key << 12 | rank among the segment's regions of that key
@@ -219,7 +222,8 @@ __global__ void __launch_bounds__(WJ_THREADS, SLICE ? WR_SLICE_CTAS : WR_MIN_CTA
             if (q >= p_lo && q < p_hi) {
                 const bool tail = s[k] >= e[k] || e[k] - s[k] > taillen;
                 const uint32_t key = min((s[k] - lo) >> fsh, WR_NBF - 1u) + (tail ? WR_NBF : 0u);
-                kr[k] = (key << 12) | atomicAdd(&S.hist[key], 1u);
+                const uint32_t old = atomicAdd(reinterpret_cast<uint32_t*>(S.hist) + (key >> 1), (key & 1u) ? 0x10000u : 1u);
+                kr[k] = (key << 12) | ((key & 1u) ? old >> 16 : old & 0xFFFFu);
                 if (!tail) { my_len = max(my_len, e[k] - s[k]); my_re = max(my_re, e[k]); }
             }
         }
@@ -234,8 +238,8 @@ __global__ void __launch_bounds__(WJ_THREADS, SLICE ? WR_SLICE_CTAS : WR_MIN_CTA
             uint32_t tot;
             uint32_t ex = block_scan_excl(sum, OpSum(), 0u, S.scan, &tot);
 #pragma unroll
-            for (int k = 0; k < WR_CPT; k++) { S.hist[WR_CPT * tid + k] = ex; ex += c[k]; }
-            if (tid == 0) S.hist[2 * WR_NBF] = tot;
+            for (int k = 0; k < WR_CPT; k++) { S.hist[WR_CPT * tid + k] = (uint16_t)ex; ex += c[k]; }
+            if (tid == 0) S.hist[2 * WR_NBF] = (uint16_t)tot;
         }
         __syncthreads();
 #pragma unroll
@@ -255,7 +259,7 @@ __global__ void __launch_bounds__(WJ_THREADS, SLICE ? WR_SLICE_CTAS : WR_MIN_CTA
             // sequence's sentinel): the indices below never leave the sequence's part of the array
             const uint32_t n_roots = nl0 + (__ldg(C.run_end + w) - j0);
             const uint32_t maxlen = S.maxlen, re_max = S.re_max;
-            const uint32_t* H = S.hist;
+            const uint16_t* H = S.hist;
             for (uint32_t base = warp * 32u; base < n_roots; base += WJ_THREADS) {
                 const uint32_t i = base + lane;
                 bool valid = i < n_roots;
@@ -287,12 +291,12 @@ __global__ void __launch_bounds__(WJ_THREADS, SLICE ? WR_SLICE_CTAS : WR_MIN_CTA
                         if (bs >= 0) {
                             const uint32_t sl = rs > maxlen ? rs - maxlen : 0u;   // a region that reaches rs from the left starts after sl
                             const uint32_t bl = sl <= lo ? 0u : min((sl - lo) >> fsh, WR_NBF - 1u);
-                            ra = H[bl] | (H[bs + 1] << 16);
+                            ra = (uint32_t)H[bl] | ((uint32_t)H[bs + 1] << 16);
                         }
                         if (MODE != 0 || INVERT) {   // --contained alone: a region that starts after rs cannot contain the root
-                            mid = H[mend] - H[mstart];
+                            mid = (uint32_t)H[mend] - (uint32_t)H[mstart];
                             const uint32_t b_hi = min(be, WR_NBF - 1u);
-                            if (mend <= b_hi) rb = H[mend] | (H[b_hi + 1] << 16);
+                            if (mend <= b_hi) rb = (uint32_t)H[mend] | ((uint32_t)H[b_hi + 1] << 16);
                         }
                     }
                 }
