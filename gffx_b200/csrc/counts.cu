@@ -14,6 +14,8 @@ struct CountsState {
     DBuf d_u_space, d_u_chrom, d_u_blk, d_u_base, d_irr_base, d_u_line0, d_u_seg0, d_l_fs, d_l_fe, d_l_sfs, d_l_sfe, d_g_s, d_g_e, d_g_ss, d_g_se;
     DBuf d_id_unit0, d_id_units, d_irr_grp, d_irr_pos, d_grp_off, d_grp_seq, d_grp_s, d_grp_e, d_blk_space;
     DJoin irr;
+    DBuf d_cxw0, d_cxlen, d_cxoff;   // depth_window_kernel: the windows' parts of the counts coordinate set (RankSlices)
+    RankSlices CXS{};
     DBuf d_gsp0, d_gap_bits, d_gs_first, d_gap_a, d_gap_b, d_gap_seg, d_irr_blk, d_u_rs, d_u_re;
     // ---- accumulators of the running job ----
     DBuf d_Hs, d_He, d_G, d_S, d_E, d_bits, d_diff, d_P, d_routed, d_scratch, d_err;
@@ -27,7 +29,7 @@ struct CountsState {
 
     std::vector<DBuf*> all() {
         return {&d_rank, &d_cov, &d_X, &d_dir, &d_u_space, &d_u_chrom, &d_u_blk, &d_u_base, &d_irr_base, &d_u_line0, &d_u_seg0, &d_l_fs, &d_l_fe, &d_l_sfs,
-                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_gsp0, &d_gap_bits, &d_gs_first, &d_gap_a, &d_gap_b, &d_gap_seg, &d_irr_blk, &d_u_rs, &d_u_re, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
+                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_cxw0, &d_cxlen, &d_cxoff, &d_gsp0, &d_gap_bits, &d_gs_first, &d_gap_a, &d_gap_b, &d_gap_seg, &d_irr_blk, &d_u_rs, &d_u_re, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
                 &d_grp_s, &d_grp_e, &d_blk_space, &d_Hs, &d_He, &d_G, &d_S, &d_E, &d_bits, &d_diff, &d_P, &d_routed, &d_scratch, &d_err,
                 &r_chrom, &r_start, &r_end, &r_value, &r_flag, &r_pos, &o_id, &o_chrom, &o_start, &o_end, &o_value};
     }
@@ -51,6 +53,33 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     cudaStream_t st = E->st;
     upload(C->d_rank, h.rank, st);
     upload(C->d_cov, h.cov, st);
+    {   // per window of the partition grid: its part of the sequence space's coordinate set + fine-bin offsets (rootjoin.cuh: RankSlices)
+        const uint32_t n_win = E->WG.n_win, shift = E->WG.shift, fsh = shift - WR_FB;
+        const size_t n_v = E->H->vmap.n_vseqs();
+        std::vector<uint32_t> xw0(std::max<uint32_t>(n_win, 1), 0), xlen(std::max<uint32_t>(n_win, 1), 0xFFFFFFFFu);
+        std::vector<uint16_t> xoff((size_t)std::max<uint32_t>(n_win, 1) * WR_XOFF_STRIDE, 0);
+        for (size_t v = 0; v < n_v; v++) {
+            const uint32_t* xv = h.X.data() + h.rank[v].x0;
+            const size_t cnt = h.rank[v].cnt;
+            auto below = [&](uint64_t c) { return (size_t)(std::lower_bound(xv, xv + cnt, c, [](uint32_t a, uint64_t b) { return (uint64_t)a < b; }) - xv); };
+            for (uint32_t w = E->h_win0[v]; w < E->h_win0[v + 1]; w++) {
+                const uint64_t lo = (uint64_t)(w - E->h_win0[v]) << shift;
+                const bool last = w + 1 == E->h_win0[v + 1];
+                const size_t i0 = below(lo), i1 = last ? cnt : below(lo + (1ull << shift));
+                xw0[w] = h.rank[v].x0 + (uint32_t)i0;
+                if (i1 - i0 > WR_SLICE_CAP - 4 || i1 - i0 > 0xFFFFu) continue;   // depth_window_kernel falls back to the global look-ups there
+                xlen[w] = (uint32_t)(i1 - i0);
+                uint16_t* row = xoff.data() + (size_t)w * WR_XOFF_STRIDE;
+                for (uint32_t b = 0; b < WR_NBF; b++) row[b] = (uint16_t)(std::min(below(lo + ((uint64_t)b << fsh)), i1) - i0);
+                row[WR_NBF] = (uint16_t)(i1 - i0);
+            }
+        }
+        upload(C->d_cxw0, xw0, st);
+        upload(C->d_cxlen, xlen, st);
+        upload(C->d_cxoff, xoff, st);
+        GFFX_CUDA(cudaStreamSynchronize(st));
+        C->CXS = RankSlices{C->d_cxw0.as<uint32_t>(), C->d_cxlen.as<uint32_t>(), C->d_cxoff.as<uint16_t>()};
+    }
     h.X.insert(h.X.end(), 8, 0u);   // rank_lb (filter.cuh) reads up to 4 entries past a bin
     upload(C->d_X, h.X, st);
     upload(C->d_dir, h.dir, st);
@@ -89,6 +118,7 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     upload(C->d_u_re, h.u_re, st);
     C->irr.upload_from(h.irr, st, &E->dev_bytes);
     C->d_err.ensure(256);
+    GFFX_CUDA(cudaFuncSetAttribute(depth_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM));
     GFFX_CUDA(cudaStreamSynchronize(st));
     GFFX_CUDA(cudaEventCreate(&C->ev0));
     GFFX_CUDA(cudaEventCreate(&C->ev1));
@@ -168,8 +198,17 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
 static void counts_add_device(EngineImpl* E, CountsState* C, const CountsDev& D, const uint32_t* dc, const uint32_t* ds, const uint32_t* de,
                               uint64_t n, uint32_t* oc, uint2* ose) {
     const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
-    C->launches += E->partition_into(dc, ds, de, n, oc, ose, E->d_poff.as<uint32_t>());
     const uint32_t ks = E->WG.shift > 8 ? E->WG.shift - 8 : 0;
+    static const bool old_depth = getenv("GFFX_DEPTH_KERNEL") && !strcmp(getenv("GFFX_DEPTH_KERNEL"), "tiles");   // A/B and test hook
+    if (C->kind == 0 && !old_depth) {   // a CTA per run of a window's reads, shared-memory histograms (counts.cuh: depth_window_kernel)
+        C->launches += E->partition_into(dc, ds, de, n, nullptr, ose, E->d_poff.as<uint32_t>());
+        const DepthWin W{E->WC.win_seq, E->WC.win0, E->d_poff.as<uint32_t>(), E->WC.shift, E->WC.n_win, C->CXS, C->host.n_irregular != 0};
+        const unsigned grid = (unsigned)(n / DW_RUN) + E->WC.n_win + 1;
+        depth_window_kernel<<<grid, DW_THREADS, DW_SMEM, E->st>>>(D, W, ose, C->d_err.as<uint32_t>());
+        C->launches += 1;
+        return;
+    }
+    C->launches += E->partition_into(dc, ds, de, n, oc, ose, E->d_poff.as<uint32_t>());
     if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, oc, ose, n, ks, C->d_err.as<uint32_t>());
     else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, oc, ose, n, ks, C->d_err.as<uint32_t>());
     C->launches += 1;

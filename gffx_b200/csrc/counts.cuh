@@ -21,6 +21,7 @@
 #include "filter.cuh"
 #include "join.cuh"
 #include "tilesort.cuh"
+#include "rootjoin.cuh"
 
 namespace gffx {
 
@@ -172,6 +173,119 @@ __global__ void __launch_bounds__(JOIN_THREADS)
                 cov_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
             });
         }
+    }
+}
+
+// ---- depth, one CTA per RUN of a window's reads (r02) ----------------------------------------------------------------------
+// counts_scatter_kernel<0> pays ~3.7 scattered L2 operations per read (two histogram atomics, the look-up's sectors): 2.4 ms per
+// 100 M reads, the L2's rate for that many operations (profiles/exp_atomics.cu).  After K0 a window's reads are
+// contiguous, and a window has only a few thousand rank slots — so a CTA takes a RUN of up to 61 440 reads of ONE window, brings
+// the window's part of the coordinate set into shared memory (the bulk copies of rootjoin.cuh), counts into two shared-memory
+// histograms over the window's slots (16-bit cells: a run cannot overflow them) and adds the non-zero cells to the global
+// histograms once: ~0.25 L2 atomics per read instead of two, no global look-ups.  Reads whose end lies beyond the window's part,
+// gap updates (rare, counts.cuh above) and the irregular blocks' join keep their global paths; a window whose part does not fit
+// (WR_SLICE_CAP values) is done read by read with depth_space_update.
+constexpr uint32_t DW_THREADS = 512;
+constexpr uint32_t DW_RUN = 15u * 4096u;   // reads per CTA: below 2^16 (16-bit histogram cells), a multiple of the partition tile
+constexpr size_t DW_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)WR_XOFF_STRIDE * 2 + 2 * (size_t)(WR_SLICE_CAP + 8) * 2;
+
+struct DepthWin {
+    const uint32_t* win_seq;   // window -> (virtual) sequence = space
+    const uint32_t* win0;      // first window of every sequence
+    const uint32_t* poff;      // n_win + 2 window offsets of the bucketed reads
+    uint32_t shift, n_win;
+    RankSlices XS;             // the windows' parts of the COUNTS coordinate set (D.R.X)
+    bool any_irregular;
+};
+
+static __global__ void __launch_bounds__(DW_THREADS, 2)
+    depth_window_kernel(CountsDev D, DepthWin W, const uint2* __restrict__ se, uint32_t* __restrict__ err) {
+    extern __shared__ __align__(16) uint32_t dw_dyn[];
+    uint32_t* const sx_raw = dw_dyn;
+    uint16_t* const soff = reinterpret_cast<uint16_t*>(sx_raw + WR_SLICE_CAP + 8);
+    uint32_t* const hs = reinterpret_cast<uint32_t*>(soff + WR_XOFF_STRIDE);            // pairs of 16-bit cells
+    uint32_t* const he = hs + (WR_SLICE_CAP + 8) / 2;
+    __shared__ uint32_t scan[DW_THREADS / 32 + 1];
+    __shared__ uint32_t s_w, s_run;
+    __shared__ __align__(8) uint64_t mbar;
+    const uint32_t tid = threadIdx.x;
+    // run table: a block scan of the windows' run counts (n_win <= 511: a window per thread)
+    const uint32_t cnt_w = tid < W.n_win ? __ldg(W.poff + tid + 1) - __ldg(W.poff + tid) : 0u, nr = (cnt_w + DW_RUN - 1) / DW_RUN;
+    uint32_t total;
+    const uint32_t r0 = block_scan_excl(nr, OpSum(), 0u, scan, &total);
+    if (tid == 0 && __ldg(W.poff + W.n_win + 1) != __ldg(W.poff + W.n_win) && blockIdx.x == 0) *err = 1;   // reads in the bucket of unknown sequences
+    if (blockIdx.x >= total) return;
+    if (nr != 0 && r0 <= blockIdx.x && blockIdx.x < r0 + nr) { s_w = tid; s_run = blockIdx.x - r0; }
+    if (tid == 0) mbar_init(&mbar, 1);
+    __syncthreads();
+    const uint32_t w = s_w;
+    const uint32_t p_lo = __ldg(W.poff + w) + s_run * DW_RUN, p_hi = min(__ldg(W.poff + w + 1), p_lo + DW_RUN);
+    const uint32_t sp = __ldg(W.win_seq + w);
+    const uint32_t lo = (w - __ldg(W.win0 + sp)) << W.shift, fsh = W.shift - WR_FB;
+    const RankSeq RS = load_rank_seq(D.R, sp);
+    const uint32_t xlen = __ldg(W.XS.xlen + w), xw0 = __ldg(W.XS.xw0 + w);
+    const bool sliced = RS.cnt != 0 && xlen != 0xFFFFFFFFu;
+    if (sliced) {
+        if (tid == 0) {
+            const uint32_t bytes = (((xw0 & 3u) + xlen + 1u) * 4u + 15u) & ~15u;   // X is padded: reading a few values on is safe
+            mbar_expect_tx(&mbar, bytes + WR_XOFF_STRIDE * 2u);
+            bulk_g2s(sx_raw, D.R.X + (xw0 & ~3u), bytes, &mbar);
+            bulk_g2s(soff, W.XS.xoff + (size_t)w * WR_XOFF_STRIDE, WR_XOFF_STRIDE * 2u, &mbar);
+        }
+        for (uint32_t i = tid; i < (xlen + 2u + 1u) / 2u; i += DW_THREADS) { hs[i] = 0; he[i] = 0; }
+        __syncthreads();
+        mbar_wait(&mbar, 0);
+    }
+    const uint32_t* sx = sx_raw + (xw0 & 3u);
+    const uint32_t rank0 = xw0 - RS.x0;   // rank of the part's first value within the space
+    for (uint32_t p = p_lo + tid; p < p_hi; p += DW_THREADS) {
+        const uint2 r = __ldcs(se + p);
+        const uint32_t rs = r.x, re = r.y;
+        if (rs >= re) continue;
+        if (!sliced) {
+            depth_space_update(D, sp, rs, re);
+        } else {
+            bool eq;
+            const uint32_t lb = rank_lb_slice(sx, soff, xlen, min((rs - lo) >> fsh, WR_NBF - 1u), rs, &eq);
+            const uint32_t ub = lb + (eq ? 1u : 0u);   // <= xlen: the slot after the part's last value is the next window's first
+            atomicAdd(hs + (ub >> 1), (ub & 1u) ? 0x10000u : 1u);
+            uint32_t j = ub;
+            bool gaps = false;
+            while (j < xlen && sx[j] < re) {
+                const uint32_t slot = RS.slot0 + rank0 + j;
+                gaps = gaps || ((__ldg(D.gap_bits + (slot >> 5)) >> (slot & 31)) & 1u);
+                j++;
+            }
+            if (j < xlen || rank0 + xlen == RS.cnt) atomicAdd(he + (j >> 1), (j & 1u) ? 0x10000u : 1u);
+            else {   // the read runs past the window's part: its end's rank lies in a later window
+                bool eq2;
+                atomicAdd(D.He + RS.slot0 + rank_lb(D.R, RS, re, &eq2), 1u);
+                gaps = true;
+            }
+            if (gaps)
+                for (uint32_t g = __ldg(D.gs_first + RS.slot0 + rank0 + ub);; g++) {
+                    if (__ldg(D.gap_a + g) >= re) break;              // sorted by a; the space's sentinel ends it
+                    if (__ldg(D.gap_b + g) < re) atomicAdd(D.G + __ldg(D.gap_seg + g), 1u);
+                }
+        }
+        if (W.any_irregular)
+            join_query<2, false>(D.JI, sp, rs, re, [&](uint32_t j, uint2) {
+                const uint32_t g = __ldg(D.irr_grp + j);   // a root fid with several tree intervals is routed once per region (depth.rs:239-241)
+                if (g != 0xFFFFFFFFu) {
+                    const uint32_t m0 = __ldg(D.grp_off + g), m1 = m0 + __ldg(D.irr_pos + j);
+                    for (uint32_t m = m0; m < m1; m++)
+                        if (__ldg(D.grp_seq + m) == sp && __ldg(D.grp_s + m) < re && __ldg(D.grp_e + m) > rs) return;
+                }
+                const uint32_t vb = __ldg(D.irr_base + j);
+                depth_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
+            });
+    }
+    if (!sliced) return;
+    __syncthreads();
+    for (uint32_t i = tid; i <= xlen; i += DW_THREADS) {   // the run's counts into the global histograms: one atomic per non-zero cell
+        const uint32_t a = (hs[i >> 1] >> (16u * (i & 1u))) & 0xFFFFu, b = (he[i >> 1] >> (16u * (i & 1u))) & 0xFFFFu;
+        if (a) atomicAdd(D.Hs + RS.slot0 + rank0 + i, a);
+        if (b) atomicAdd(D.He + RS.slot0 + rank0 + i, b);
     }
 }
 
