@@ -187,7 +187,8 @@ __global__ void __launch_bounds__(JOIN_THREADS)
 // (WR_SLICE_CAP values) is done read by read with depth_space_update.
 constexpr uint32_t DW_THREADS = 512;
 constexpr uint32_t DW_RUN = 15u * 4096u;   // reads per CTA: below 2^16 (16-bit histogram cells), a multiple of the partition tile
-constexpr size_t DW_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)WR_XOFF_STRIDE * 2 + 2 * (size_t)(WR_SLICE_CAP + 8) * 2;
+constexpr uint32_t DW_GAPW = (WR_SLICE_CAP + 8) / 32 + 2;   // words of the window's gap-start bits
+constexpr size_t DW_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)WR_XOFF_STRIDE * 2 + 2 * (size_t)(WR_SLICE_CAP + 8) * 2 + (size_t)DW_GAPW * 4;
 
 struct DepthWin {
     const uint32_t* win_seq;   // window -> (virtual) sequence = space
@@ -205,6 +206,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
     uint16_t* const soff = reinterpret_cast<uint16_t*>(sx_raw + WR_SLICE_CAP + 8);
     uint32_t* const hs = reinterpret_cast<uint32_t*>(soff + WR_XOFF_STRIDE);            // pairs of 16-bit cells
     uint32_t* const he = hs + (WR_SLICE_CAP + 8) / 2;
+    uint32_t* const sgap = he + (WR_SLICE_CAP + 8) / 2;   // bit j: the part's value j starts a gap (counts_index.h: gap_bits)
     __shared__ uint32_t scan[DW_THREADS / 32 + 1];
     __shared__ uint32_t s_w, s_run;
     __shared__ __align__(8) uint64_t mbar;
@@ -233,6 +235,13 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
             bulk_g2s(soff, W.XS.xoff + (size_t)w * WR_XOFF_STRIDE, WR_XOFF_STRIDE * 2u, &mbar);
         }
         for (uint32_t i = tid; i < (xlen + 2u + 1u) / 2u; i += DW_THREADS) { hs[i] = 0; he[i] = 0; }
+        {   // the gap-start bits of the part's slots, realigned to bit 0 = the part's first value
+            const uint32_t s0 = RS.slot0 + (xw0 - RS.x0), sh = s0 & 31u;
+            for (uint32_t i = tid; i < (xlen + 31u) / 32u; i += DW_THREADS) {
+                const uint32_t a = __ldg(D.gap_bits + (s0 >> 5) + i), b = __ldg(D.gap_bits + (s0 >> 5) + i + 1);   // the array has a spare word
+                sgap[i] = __funnelshift_r(a, b, sh);
+            }
+        }
         __syncthreads();
         mbar_wait(&mbar, 0);
     }
@@ -252,8 +261,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
             uint32_t j = ub;
             bool gaps = false;
             while (j < xlen && sx[j] < re) {
-                const uint32_t slot = RS.slot0 + rank0 + j;
-                gaps = gaps || ((__ldg(D.gap_bits + (slot >> 5)) >> (slot & 31)) & 1u);
+                gaps = gaps || ((sgap[j >> 5] >> (j & 31u)) & 1u);
                 j++;
             }
             if (j < xlen || rank0 + xlen == RS.cnt) atomicAdd(he + (j >> 1), (j & 1u) ? 0x10000u : 1u);

@@ -193,7 +193,7 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             if (p.start != q.start) return p.start < q.start;
             return p.end < q.end;
         });
-        C.gap_bits.assign(((size_t)C.n_slots + 31) / 32 + 1, 0);
+        C.gap_bits.assign(((size_t)C.n_slots + 31) / 32 + 3, 0);   // spare words: depth_window_kernel realigns the bits two words at a time
         C.gs_first.assign(std::max<uint32_t>(C.n_slots, 1), 0);
         C.gsp0.assign((size_t)n_spaces + 1, 0);
         size_t k = 0;
