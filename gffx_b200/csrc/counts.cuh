@@ -22,6 +22,7 @@
 #include "join.cuh"
 #include "tilesort.cuh"
 #include "rootjoin.cuh"
+#include "counts_index.h"
 
 namespace gffx {
 
@@ -69,7 +70,7 @@ __device__ __forceinline__ void depth_space_update(const CountsDev& D, uint32_t 
     // lb(end) = ub(start) + the coordinates inside (start, end): a short region has none or a few, next to the ones the start
     // look-up read — walk them instead of a second look-up (which a long region still does)
     uint32_t lbe = ubl;
-    bool gaps = false;   // some coordinate strictly inside the region starts a gap
+    bool gaps = re - rs >= GAP_SHORT;   // some coordinate strictly inside the region starts a gap the region is long enough to reach across
     {
         const uint32_t* X = D.R.X + S.x0;
         int steps = 0;
@@ -247,8 +248,10 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
     }
     const uint32_t* sx = sx_raw + (xw0 & 3u);
     const uint32_t rank0 = xw0 - RS.x0;   // rank of the part's first value within the space
+    uint2 r_next = p_lo + tid < p_hi ? __ldcs(se + p_lo + tid) : make_uint2(0, 0);
     for (uint32_t p = p_lo + tid; p < p_hi; p += DW_THREADS) {
-        const uint2 r = __ldcs(se + p);
+        const uint2 r = r_next;   // the next read is already on its way while this one is counted
+        if (p + DW_THREADS < p_hi) r_next = __ldcs(se + p + DW_THREADS);
         const uint32_t rs = r.x, re = r.y;
         if (rs >= re) continue;
         if (!sliced) {
@@ -259,7 +262,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
             const uint32_t ub = lb + (eq ? 1u : 0u);   // <= xlen: the slot after the part's last value is the next window's first
             atomicAdd(hs + (ub >> 1), (ub & 1u) ? 0x10000u : 1u);
             uint32_t j = ub;
-            bool gaps = false;
+            bool gaps = re - rs >= GAP_SHORT;
             while (j < xlen && sx[j] < re) {
                 gaps = gaps || ((sgap[j >> 5] >> (j & 31u)) & 1u);
                 j++;

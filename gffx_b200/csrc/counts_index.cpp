@@ -211,6 +211,7 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             C.gsp0[s] = g0;
             C.gsp0[s + 1] = (uint32_t)C.gap_a.size();   // past the sentinel: the next space starts here
             for (uint32_t j = g0; j + 1 < C.gap_a.size(); j++) {   // a is a coordinate of the space: mark its slot
+                if (C.gap_b[j] - C.gap_a[j] >= GAP_SHORT) continue;   // only a region at least that long can reach across it: those always look
                 const uint32_t slot = r.slot0 + (uint32_t)(std::lower_bound(x.begin(), x.end(), C.gap_a[j]) - x.begin());
                 C.gap_bits[slot >> 5] |= 1u << (slot & 31);
             }

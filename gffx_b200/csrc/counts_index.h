@@ -31,6 +31,9 @@ struct CovSpaceHost {  // 16 B
     uint64_t word0;       // first 64-bit word of the space; the space owns nbits/64+1 words
 };
 
+// gap_bits marks the coordinates that start a gap SHORTER than this; a region of at least this length looks for gaps regardless
+constexpr uint32_t GAP_SHORT = 1024;
+
 struct CountsIndexHost {
     uint32_t n_spaces = 0, n_slots = 0, n_units = 0, n_ids = 0, n_segs = 0, n_clines = 0;
     uint64_t n_words = 0;
@@ -48,7 +51,8 @@ struct CountsIndexHost {
     std::vector<uint32_t> id_unit0, id_units;
     // gaps between consecutive segments of a unit, [a, b] = [seg.e, next.s], sorted by (space, a), one (0xFFFFFFFF) sentinel after
     // each space's gaps, space s owning [gsp0[s], gsp0[s+1]); gap_bits: one bit per rank slot, set when the slot's coordinate is
-    // the `a` of a gap — a read only looks for the gaps inside it when it steps over such a coordinate (counts.cuh)
+    // the `a` of a gap shorter than GAP_SHORT — a read shorter than that only looks for the gaps inside it when it steps over such
+    // a coordinate (counts.cuh)
     // gs_first[slot] = the first gap of the slot's space whose a is >= the slot's coordinate: where that look starts
     std::vector<uint32_t> gap_a, gap_b, gap_seg, gsp0, gap_bits, gs_first;
     // regular blocks: the block's one tree interval per unit (NONE32 for a unit of an irregular block): coverage derives
