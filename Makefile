@@ -12,7 +12,7 @@ BIN := gffx_b200/bin/gffx-b200
 SYNTH_LIB := gffx_b200/lib/libgffx_synth.so
 
 CU_SRCS := $(SRC)/engine.cu $(SRC)/counts.cu $(SRC)/bedparse.cu $(SRC)/linescan.cu
-CPP_SRCS := $(SRC)/util.cpp $(SRC)/join_build.cpp $(SRC)/winjoin_build.cpp $(SRC)/counts_index.cpp $(SRC)/host_index.cpp $(SRC)/linecache.cpp $(SRC)/reads.cpp $(SRC)/index_builder.cpp $(SRC)/synth.cpp $(SRC)/capi.cpp
+CPP_SRCS := $(SRC)/util.cpp $(SRC)/winjoin_build.cpp $(SRC)/counts_index.cpp $(SRC)/host_index.cpp $(SRC)/linecache.cpp $(SRC)/reads.cpp $(SRC)/index_builder.cpp $(SRC)/synth.cpp $(SRC)/capi.cpp
 CU_OBJS := $(patsubst $(SRC)/%.cu,$(OBJ)/%.cu.o,$(CU_SRCS))
 CPP_OBJS := $(patsubst $(SRC)/%.cpp,$(OBJ)/%.o,$(CPP_SRCS))
 HDRS := $(wildcard $(SRC)/*.h $(SRC)/*.cuh) include/gffx_b200.h

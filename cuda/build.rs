@@ -8,7 +8,7 @@ fn main() {
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".into());
     let src = "native/csrc";
     let cu = ["engine.cu", "counts.cu", "bedparse.cu", "linescan.cu"];
-    let cpp = ["util.cpp", "join_build.cpp", "winjoin_build.cpp", "counts_index.cpp", "host_index.cpp", "linecache.cpp", "reads.cpp", "index_builder.cpp", "synth.cpp", "capi.cpp"];
+    let cpp = ["util.cpp", "winjoin_build.cpp", "counts_index.cpp", "host_index.cpp", "linecache.cpp", "reads.cpp", "index_builder.cpp", "synth.cpp", "capi.cpp"];
     let mut objs = vec![];
     for f in cu.iter().chain(cpp.iter()) {
         let o = out.join(format!("{f}.o"));

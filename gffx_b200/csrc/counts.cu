@@ -13,7 +13,7 @@ struct CountsState {
     DBuf d_rank, d_cov, d_X, d_dir;
     DBuf d_u_space, d_u_chrom, d_u_blk, d_u_base, d_irr_base, d_u_line0, d_u_seg0, d_l_fs, d_l_fe, d_l_sfs, d_l_sfe, d_g_s, d_g_e, d_g_ss, d_g_se;
     DBuf d_id_unit0, d_id_units, d_irr_grp, d_irr_pos, d_grp_off, d_grp_seq, d_grp_s, d_grp_e, d_blk_space;
-    DJoin irr;
+    DBuf d_irr_seq0, d_irr_s, d_irr_e, d_irr_pm, d_irr_space;
     DBuf d_cxw0, d_cxlen, d_cxoff;   // depth_window_kernel: the windows' parts of the counts coordinate set (RankSlices)
     RankSlices CXS{};
     DBuf d_gsp0, d_gap_bits, d_gs_first, d_gap_a, d_gap_b, d_gap_seg, d_irr_blk, d_u_rs, d_u_re;
@@ -29,7 +29,7 @@ struct CountsState {
 
     std::vector<DBuf*> all() {
         return {&d_rank, &d_cov, &d_X, &d_dir, &d_u_space, &d_u_chrom, &d_u_blk, &d_u_base, &d_irr_base, &d_u_line0, &d_u_seg0, &d_l_fs, &d_l_fe, &d_l_sfs,
-                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_cxw0, &d_cxlen, &d_cxoff, &d_gsp0, &d_gap_bits, &d_gs_first, &d_gap_a, &d_gap_b, &d_gap_seg, &d_irr_blk, &d_u_rs, &d_u_re, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
+                &d_l_sfe, &d_g_s, &d_g_e, &d_g_ss, &d_g_se, &d_irr_seq0, &d_irr_s, &d_irr_e, &d_irr_pm, &d_irr_space, &d_cxw0, &d_cxlen, &d_cxoff, &d_gsp0, &d_gap_bits, &d_gs_first, &d_gap_a, &d_gap_b, &d_gap_seg, &d_irr_blk, &d_u_rs, &d_u_re, &d_id_unit0, &d_id_units, &d_irr_grp, &d_irr_pos, &d_grp_off, &d_grp_seq,
                 &d_grp_s, &d_grp_e, &d_blk_space, &d_Hs, &d_He, &d_G, &d_S, &d_E, &d_bits, &d_diff, &d_P, &d_routed, &d_scratch, &d_err,
                 &r_chrom, &r_start, &r_end, &r_value, &r_flag, &r_pos, &o_id, &o_chrom, &o_start, &o_end, &o_value};
     }
@@ -39,7 +39,6 @@ void counts_release(EngineImpl* E) {
     CountsState* C = E->counts;
     if (!C) return;
     for (DBuf* b : C->all()) b->release();
-    C->irr.release();
     if (C->ev0) cudaEventDestroy(C->ev0);
     if (C->ev1) cudaEventDestroy(C->ev1);
     delete C;
@@ -116,7 +115,11 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     upload(C->d_irr_blk, h.irr_blk, st);
     upload(C->d_u_rs, h.u_rs, st);
     upload(C->d_u_re, h.u_re, st);
-    C->irr.upload_from(h.irr, st, &E->dev_bytes);
+    upload(C->d_irr_seq0, h.irr_seq0, st);
+    upload(C->d_irr_s, h.irr_s, st);
+    upload(C->d_irr_e, h.irr_e, st);
+    upload(C->d_irr_pm, h.irr_pm, st);
+    upload(C->d_irr_space, h.irr_space, st);
     C->d_err.ensure(256);
     GFFX_CUDA(cudaFuncSetAttribute(depth_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM));
     GFFX_CUDA(cudaStreamSynchronize(st));
@@ -124,9 +127,8 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     GFFX_CUDA(cudaEventCreate(&C->ev1));
     // keep the scalars, drop the bulk
     for (auto* v : {&h.X, &h.dir, &h.u_space, &h.u_chrom, &h.u_blk, &h.u_base, &h.irr_base, &h.u_line0, &h.u_seg0, &h.l_fs, &h.l_fe, &h.l_sfs, &h.l_sfe, &h.g_s,
-                    &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space, &h.gsp0, &h.gap_bits, &h.gs_first, &h.gap_a, &h.gap_b, &h.gap_seg, &h.irr_blk, &h.u_rs, &h.u_re})
+                    &h.g_e, &h.g_ss, &h.g_se, &h.id_unit0, &h.id_units, &h.irr_grp, &h.irr_pos, &h.blk_space, &h.irr_seq0, &h.irr_s, &h.irr_e, &h.irr_pm, &h.irr_space, &h.gsp0, &h.gap_bits, &h.gs_first, &h.gap_a, &h.gap_b, &h.gap_seg, &h.irr_blk, &h.u_rs, &h.u_re})
         std::vector<uint32_t>().swap(*v);
-    h.irr = JoinHost();
     C->built = true;
 }
 
@@ -176,7 +178,8 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.gap_b = C->d_gap_b.as<uint32_t>();
     D.gap_seg = C->d_gap_seg.as<uint32_t>();
     D.irr_blk = C->d_irr_blk.as<uint32_t>();
-    D.JI = C->irr.J;
+    D.irr_seq0 = C->d_irr_seq0.as<uint32_t>(); D.irr_s = C->d_irr_s.as<uint32_t>(); D.irr_e = C->d_irr_e.as<uint32_t>();
+    D.irr_pm = C->d_irr_pm.as<uint32_t>(); D.irr_space = C->d_irr_space.as<uint32_t>();
     D.irr_grp = C->d_irr_grp.as<uint32_t>();
     D.irr_pos = C->d_irr_pos.as<uint32_t>();
     D.irr_base = C->d_irr_base.as<uint32_t>();
@@ -197,20 +200,16 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
 // one batch of device-resident regions: K0 partition + the scatter kernel; asynchronous on the engine's stream
 static void counts_add_device(EngineImpl* E, CountsState* C, const CountsDev& D, const uint32_t* dc, const uint32_t* ds, const uint32_t* de,
                               uint64_t n, uint32_t* oc, uint2* ose) {
-    const unsigned tiles = (unsigned)((n + JOIN_TILE - 1) / JOIN_TILE);
-    const uint32_t ks = E->WG.shift > 8 ? E->WG.shift - 8 : 0;
-    static const bool old_depth = getenv("GFFX_DEPTH_KERNEL") && !strcmp(getenv("GFFX_DEPTH_KERNEL"), "tiles");   // A/B and test hook
-    if (C->kind == 0 && !old_depth) {   // a CTA per run of a window's reads, shared-memory histograms (counts.cuh: depth_window_kernel)
-        C->launches += E->partition_into(dc, ds, de, n, nullptr, ose, E->d_poff.as<uint32_t>());
+    // both kernels take the sequence from the window: the bucketed sequence numbers are not written
+    C->launches += E->partition_into(dc, ds, de, n, nullptr, ose, E->d_poff.as<uint32_t>());
+    if (C->kind == 0) {   // a CTA per run of a window's reads, shared-memory histograms (counts.cuh: depth_window_kernel)
         const DepthWin W{E->WC.win_seq, E->WC.win0, E->d_poff.as<uint32_t>(), E->WC.shift, E->WC.n_win, C->CXS, C->host.n_irregular != 0};
         const unsigned grid = (unsigned)(n / DW_RUN) + E->WC.n_win + 1;
         depth_window_kernel<<<grid, DW_THREADS, DW_SMEM, E->st>>>(D, W, ose, C->d_err.as<uint32_t>());
-        C->launches += 1;
-        return;
+    } else {
+        coverage_scatter_kernel<<<(unsigned)((n + CV_TILE - 1) / CV_TILE), CV_THREADS, 0, E->st>>>(D, E->WC.win_seq, E->d_poff.as<uint32_t>(), E->WC.n_win, ose, n,
+                                                                                                  C->d_err.as<uint32_t>());
     }
-    C->launches += E->partition_into(dc, ds, de, n, oc, ose, E->d_poff.as<uint32_t>());
-    if (C->kind == 0) counts_scatter_kernel<0><<<tiles, JOIN_THREADS, 0, E->st>>>(D, oc, ose, n, ks, C->d_err.as<uint32_t>());
-    else counts_scatter_kernel<1><<<tiles, JOIN_THREADS, 0, E->st>>>(D, oc, ose, n, ks, C->d_err.as<uint32_t>());
     C->launches += 1;
 }
 

@@ -19,8 +19,6 @@
 //             covered bases in [s,e) = C(e) - C(s) with C(x) = P[word] + popc(bits below x).
 #pragma once
 #include "filter.cuh"
-#include "join.cuh"
-#include "tilesort.cuh"
 #include "rootjoin.cuh"
 #include "counts_index.h"
 
@@ -40,15 +38,20 @@ struct CountsDev {
     const uint32_t* gap_a;      // gaps by (space, a), one 0xFFFFFFFF sentinel per space
     const uint32_t* gap_b;
     const uint32_t* gap_seg;    // left segment of the gap
-    JoinIndex JI;           // tree intervals of irregular blocks, seq = sequence, payload = private space
+    // tree intervals of irregular blocks (counts_index.h): by (sequence, start), with the running maximum of the ends
+    const uint32_t* irr_seq0;
+    const uint32_t* irr_s;
+    const uint32_t* irr_e;
+    const uint32_t* irr_pm;
+    const uint32_t* irr_space;
     const uint32_t* irr_grp;
     const uint32_t* irr_pos;
-    const uint32_t* irr_base;   // per JI entry: base of its sequence on the virtual sequence (a private space keeps the lines' own coordinates)
+    const uint32_t* irr_base;   // per irregular interval: base of its sequence on the virtual sequence (a private space keeps the lines' own coordinates)
     const uint32_t* grp_off;
     const uint32_t* grp_seq;
     const uint32_t* grp_s;
     const uint32_t* grp_e;
-    const uint32_t* irr_blk;    // per JI entry: its block
+    const uint32_t* irr_blk;    // per irregular interval: its block
 
     uint32_t n_seqs;
     // accumulators
@@ -59,6 +62,23 @@ struct CountsDev {
     int* diff;
     uint8_t* blk_routed;
 };
+
+// the irregular tree intervals of sequence `seq` that a region hits: start < re && end > rs (src/utils/tree.rs:110, any rs / re).
+// A handful of intervals per index: the last start below re by binary search, then backwards while the running maximum of the
+// ends still exceeds rs.
+template <class F> __device__ __forceinline__ void irr_query(const CountsDev& D, uint32_t seq, uint32_t rs, uint32_t re, F&& f) {
+    const uint32_t i0 = __ldg(D.irr_seq0 + seq), i1 = __ldg(D.irr_seq0 + seq + 1);
+    if (i0 == i1) return;
+    uint32_t lo = i0, hi = i1;   // first interval with start >= re
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(D.irr_s + mid) < re) lo = mid + 1; else hi = mid;
+    }
+    for (uint32_t j = lo; j-- > i0;) {
+        if (__ldg(D.irr_pm + j) <= rs) break;
+        if (__ldg(D.irr_e + j) > rs) f(j);
+    }
+}
 
 __device__ __forceinline__ void depth_space_update(const CountsDev& D, uint32_t sp, uint32_t rs, uint32_t re) {
     const RankSeq S = load_rank_seq(D.R, sp);
@@ -125,60 +145,54 @@ __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp
     }
 }
 
-// KIND 0 depth, 1 coverage.  Regions with start >= end are ignored (both BED dialects of the
-// counting commands drop them: depth.rs:488, coverage.rs:253).
-template <int KIND>
-__global__ void __launch_bounds__(JOIN_THREADS)
-    counts_scatter_kernel(CountsDev D, const uint32_t* __restrict__ chr, const uint2* __restrict__ se, uint64_t n, uint32_t key_shift,
-                          uint32_t* __restrict__ err) {
-    __shared__ TileSortSmem<JOIN_THREADS, JOIN_QPT> ts;
-    const uint64_t tile0 = (uint64_t)blockIdx.x * JOIN_TILE;
-    const uint32_t tm = (uint32_t)min((uint64_t)JOIN_TILE, n - tile0);
-    const uint64_t q0 = tile0 + (uint64_t)threadIdx.x * JOIN_QPT;
-    Query4 Q;
-    Q.n = 0;
-    if (q0 < n) load_queries(chr, se, n, q0, Q);
-    bool valid[JOIN_QPT];
-    // a warp's 32 regions next to each other on the genome (tilesort.cuh): shared cache lines for every look-up below
-    tile_sort<JOIN_THREADS, JOIN_QPT>(ts, key_shift, tm, Q.n, Q.c, Q.s, Q.e, valid);
-#pragma unroll
-    for (int k = 0; k < JOIN_QPT; k++) {
-        if (!valid[k]) continue;
-        const uint32_t c = Q.c[k], rs = Q.s[k], re = Q.e[k];
-        if (rs >= re) continue;
-        if (c >= D.n_seqs) { *err = 1; continue; }
-        if (KIND == 0) {
-            depth_space_update(D, c, rs, re);
-            join_query<2, false>(D.JI, c, rs, re, [&](uint32_t j, uint2) {
-                // a root fid with several tree intervals is routed once per region (depth.rs:239-241):
-                // only the lowest-ranked interval of the group that the region overlaps does the update
-                const uint32_t g = __ldg(D.irr_grp + j);
-                if (g != 0xFFFFFFFFu) {
-                    const uint32_t m0 = __ldg(D.grp_off + g), m1 = m0 + __ldg(D.irr_pos + j);
-                    for (uint32_t m = m0; m < m1; m++)
-                        if (__ldg(D.grp_seq + m) == c && __ldg(D.grp_s + m) < re && __ldg(D.grp_e + m) > rs) return;
-                }
-                const uint32_t vb = __ldg(D.irr_base + j);
-                depth_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
-            });
-        } else {
-            // A regular block (one tree interval, its lines inside it, on the sequence's own space) needs no routing: "some
-            // region overlaps its tree interval" is "some base of the interval is covered", which counts_rows_kernel reads off the
-            // bitmap.  Only the tree intervals of irregular blocks are joined (a handful, usually none): their private spaces
-            // take the regions routed to them (OR / +-1 updates tolerate repeats: no dedup needed).
-            cov_space_update(D, c, rs, re);
-            join_query<2, false>(D.JI, c, rs, re, [&](uint32_t j, uint2) {
-                const uint32_t blk = __ldg(D.irr_blk + j);
-                if (!D.blk_routed[blk]) D.blk_routed[blk] = 1;
-                const uint32_t vb = __ldg(D.irr_base + j);
-                cov_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
-            });
+// Coverage scatter: a thread per region of the window-bucketed batch; the window gives the sequence (= space).  Regions with
+// start >= end are ignored (both BED dialects of the counting commands drop them: depth.rs:488, coverage.rs:253).
+// A regular block (one tree interval, its lines inside it, on the sequence's own space) needs no routing: "some region
+// overlaps its tree interval" is "some base of the interval is covered", which counts_rows_kernel reads off the bitmap.  Only
+// the tree intervals of irregular blocks are looked up (a handful, usually none): their private spaces take the regions
+// routed to them (OR / +-1 updates tolerate repeats: no dedup needed).
+constexpr uint32_t CV_THREADS = 256;
+constexpr uint32_t CV_TILE = 4096;
+
+static __global__ void __launch_bounds__(CV_THREADS)
+    coverage_scatter_kernel(CountsDev D, const uint32_t* __restrict__ win_seq, const uint32_t* __restrict__ poff, uint32_t n_win, const uint2* __restrict__ se,
+                            uint64_t n, uint32_t* __restrict__ err) {
+    __shared__ uint32_t s_wf, s_wl;
+    const uint32_t tile0 = blockIdx.x * CV_TILE, m = (uint32_t)min((uint64_t)CV_TILE, n - tile0);
+    {   // windows of the tile's first and last region: (number of window offsets <= position) - 1; poff has n_win + 2 cells
+        int nf = 0, nl = 0;
+        for (uint32_t i0 = 0; i0 < n_win + 2; i0 += CV_THREADS) {
+            const uint32_t i = i0 + threadIdx.x;
+            const uint32_t o = i < n_win + 2 ? __ldg(poff + i) : 0xFFFFFFFFu;
+            nf += __syncthreads_count(o <= tile0);
+            nl += __syncthreads_count(o <= tile0 + m - 1);
+        }
+        if (threadIdx.x == 0) { s_wf = (uint32_t)nf - 1u; s_wl = (uint32_t)nl - 1u; }
+    }
+    __syncthreads();
+    for (uint32_t w = s_wf; w <= s_wl; w++) {
+        const uint32_t p_lo = max(__ldg(poff + w), tile0), p_hi = min(__ldg(poff + w + 1), tile0 + m);
+        if (p_lo >= p_hi) continue;
+        if (w >= n_win) { if (threadIdx.x == 0) *err = 1; continue; }   // regions whose sequence number is out of range
+        const uint32_t sp = __ldg(win_seq + w);
+        const bool irr = __ldg(D.irr_seq0 + sp) != __ldg(D.irr_seq0 + sp + 1);
+        for (uint32_t p = p_lo + threadIdx.x; p < p_hi; p += CV_THREADS) {
+            const uint2 r = __ldcs(se + p);
+            if (r.x >= r.y) continue;
+            cov_space_update(D, sp, r.x, r.y);
+            if (irr)
+                irr_query(D, sp, r.x, r.y, [&](uint32_t j) {
+                    const uint32_t blk = __ldg(D.irr_blk + j);
+                    if (!D.blk_routed[blk]) D.blk_routed[blk] = 1;
+                    const uint32_t vb = __ldg(D.irr_base + j);
+                    cov_space_update(D, __ldg(D.irr_space + j), r.x - vb, r.y - vb);
+                });
         }
     }
 }
 
 // ---- depth, one CTA per RUN of a window's reads (r02) ----------------------------------------------------------------------
-// counts_scatter_kernel<0> pays ~3.7 scattered L2 operations per read (two histogram atomics, the look-up's sectors): 2.4 ms per
+// A thread per read against global memory (r01's counts_scatter_kernel<0>) pays ~3.7 scattered L2 operations per read (two histogram atomics, the look-up's sectors): 2.4 ms per
 // 100 M reads, the L2's rate for that many operations (profiles/exp_atomics.cu).  After K0 a window's reads are
 // contiguous, and a window has only a few thousand rank slots — so a CTA takes a RUN of up to 61 440 reads of ONE window, brings
 // the window's part of the coordinate set into shared memory (the bulk copies of rootjoin.cuh), counts into two shared-memory
@@ -280,7 +294,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
                 }
         }
         if (W.any_irregular)
-            join_query<2, false>(D.JI, sp, rs, re, [&](uint32_t j, uint2) {
+            irr_query(D, sp, rs, re, [&](uint32_t j) {
                 const uint32_t g = __ldg(D.irr_grp + j);   // a root fid with several tree intervals is routed once per region (depth.rs:239-241)
                 if (g != 0xFFFFFFFFu) {
                     const uint32_t m0 = __ldg(D.grp_off + g), m1 = m0 + __ldg(D.irr_pos + j);
@@ -288,7 +302,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
                         if (__ldg(D.grp_seq + m) == sp && __ldg(D.grp_s + m) < re && __ldg(D.grp_e + m) > rs) return;
                 }
                 const uint32_t vb = __ldg(D.irr_base + j);
-                depth_space_update(D, __ldg(D.JI.ent_fid + j), rs - vb, re - vb);
+                depth_space_update(D, __ldg(D.irr_space + j), rs - vb, re - vb);
             });
     }
     if (!sliced) return;

@@ -226,16 +226,29 @@ void build_counts_index(const HostIndex& H, CountsIndexHost* out) {
             k = k1;
         }
     }
-    build_join_host(n_seqs, irr_items, 16, 8, &C.irr);
-    C.irr_grp.resize(C.irr.n_entries());
-    C.irr_pos.resize(C.irr.n_entries());
-    C.irr_base.resize(C.irr.n_entries());
-    C.irr_blk.resize(C.irr.n_entries());
-    for (size_t k = 0; k < C.irr.n_entries(); k++) {
-        C.irr_grp[k] = irr_item_grp[C.irr.ent_item[k]];
-        C.irr_pos[k] = irr_item_pos[C.irr.ent_item[k]];
-        C.irr_base[k] = irr_item_base[C.irr.ent_item[k]];
-        C.irr_blk[k] = irr_item_blk[C.irr.ent_item[k]];
+    {   // irregular tree intervals by (sequence, start) with the running maximum of their ends
+        std::vector<uint32_t> ord_i(irr_items.size());
+        std::iota(ord_i.begin(), ord_i.end(), 0u);
+        std::stable_sort(ord_i.begin(), ord_i.end(), [&](uint32_t a, uint32_t b) {
+            const JoinItem &p = irr_items[a], &q = irr_items[b];
+            if (p.seq != q.seq) return p.seq < q.seq;
+            return p.start < q.start;
+        });
+        const size_t m = ord_i.size();
+        C.irr_seq0.assign((size_t)n_seqs + 1, 0);
+        C.irr_s.resize(m); C.irr_e.resize(m); C.irr_pm.resize(m); C.irr_space.resize(m);
+        C.irr_grp.resize(m); C.irr_pos.resize(m); C.irr_base.resize(m); C.irr_blk.resize(m);
+        for (size_t k = 0; k < m; k++) {
+            const JoinItem& it = irr_items[ord_i[k]];
+            C.irr_seq0[it.seq + 1]++;
+            C.irr_s[k] = it.start; C.irr_e[k] = it.end; C.irr_space[k] = it.payload;
+            C.irr_pm[k] = (k && irr_items[ord_i[k - 1]].seq == it.seq) ? std::max(C.irr_pm[k - 1], it.end) : it.end;
+            C.irr_grp[k] = irr_item_grp[ord_i[k]];
+            C.irr_pos[k] = irr_item_pos[ord_i[k]];
+            C.irr_base[k] = irr_item_base[ord_i[k]];
+            C.irr_blk[k] = irr_item_blk[ord_i[k]];
+        }
+        for (uint32_t s = 0; s < n_seqs; s++) C.irr_seq0[s + 1] += C.irr_seq0[s];
     }
 }
 

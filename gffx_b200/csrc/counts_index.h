@@ -19,7 +19,7 @@
 //             coordinate hull gives the covered bases.
 #pragma once
 #include "host_index.h"
-#include "join_build.h"
+#include "winjoin_build.h"
 
 namespace gffx {
 
@@ -59,7 +59,10 @@ struct CountsIndexHost {
     // "some read was routed to this block" from the covered bases inside it
     std::vector<uint32_t> u_rs, u_re;
     // tree intervals of irregular blocks: seq = sequence number, payload = private space
-    JoinHost irr;
+    // the tree intervals of irregular blocks by (sequence, start): sequence v owns [irr_seq0[v], irr_seq0[v+1]); irr_pm = running
+    // maximum of the ends inside the sequence (the walk back from the last start below a region's end stops when it falls to the
+    // region's start); irr_space = the block's private space
+    std::vector<uint32_t> irr_seq0, irr_s, irr_e, irr_pm, irr_space;
     std::vector<uint32_t> irr_grp, irr_pos;          // per irr entry: duplicate-fid group (NONE32 = single) and rank inside it
     std::vector<uint32_t> irr_base;                  // per irr entry: VSeqMap base of its sequence (regions are moved back by it)
     std::vector<uint32_t> irr_blk;                   // per irr entry: its block

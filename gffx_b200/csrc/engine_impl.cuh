@@ -3,8 +3,6 @@
 #include <cuda_runtime.h>
 #include "engine.h"
 #include "filter.cuh"
-#include "join.cuh"
-#include "join_build.h"
 #include "partition.cuh"
 #include "bedparse.cuh"
 #include "gather.cuh"
@@ -48,34 +46,6 @@ template <class T> inline void upload(DBuf& b, const std::vector<T>& v, cudaStre
     b.ensure(std::max<size_t>(v.size(), 1) * sizeof(T));
     if (!v.empty()) GFFX_CUDA(cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st));
 }
-
-// a JoinHost on the device
-struct DJoin {
-    DBuf seq_list0, lists, ent_se, ent_payload, dir;
-    JoinIndex J{};
-    uint32_t n_ent = 0;
-    void upload_from(const JoinHost& h, cudaStream_t st, size_t* total) {
-        for (DBuf* b : {&seq_list0, &lists, &ent_se, &ent_payload, &dir}) b->total = total;
-        std::vector<uint2> se(h.n_entries());
-        for (size_t i = 0; i < se.size(); i++) se[i] = make_uint2(h.ent_start[i], h.ent_end[i]);
-        upload(seq_list0, h.seq_list0, st);
-        upload(lists, h.lists, st);
-        upload(ent_se, se, st);
-        upload(ent_payload, h.ent_payload, st);
-        upload(dir, h.dir, st);
-        GFFX_CUDA(cudaStreamSynchronize(st));  // `se` is a local
-        n_ent = (uint32_t)h.n_entries();
-        J.seq_list0 = seq_list0.as<uint32_t>();
-        J.lists = lists.as<JoinList>();
-        J.ent_se = ent_se.as<uint2>();
-        J.ent_fid = ent_payload.as<uint32_t>();
-        J.dir = dir.as<uint32_t>();
-        J.n_seqs = (uint32_t)(h.seq_list0.size() - 1);
-    }
-    void release() {
-        for (DBuf* b : {&seq_list0, &lists, &ent_se, &ent_payload, &dir}) b->release();
-    }
-};
 
 struct CountsState;  // counts.cu
 

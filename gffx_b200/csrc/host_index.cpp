@@ -205,8 +205,9 @@ void HostIndex::finish(const std::vector<uint32_t>& gfid, const std::vector<uint
     build_vseqs();
     if (cache_pending) {
         cache_pending = false;
-        if (getenv("GFFX_CACHE_SYNC")) line_cache_store(*this);
-        else cache_writer = std::thread([this] { line_cache_store(*this); });
+        const std::string target = line_cache_target(*this);   // decided here: the writer thread must not look at the environment later
+        if (getenv("GFFX_CACHE_SYNC")) line_cache_store(*this, target);
+        else if (!target.empty()) cache_writer = std::thread([this, target] { line_cache_store(*this, target); });
     }
 }
 

@@ -155,7 +155,8 @@ struct HostIndex {
 // linecache.cpp: `<gff>.b200cache`, the line table of an earlier open (keyed by the GFF's size + mtime and a digest of the block
 // list and sequence names); load returns false when there is no usable cache
 bool line_cache_load(HostIndex& H, int threads);
-void line_cache_store(const HostIndex& H);
+std::string line_cache_target(const HostIndex& H);   // where the cache of this index goes ("": nowhere); reads the environment NOW
+void line_cache_store(const HostIndex& H, const std::string& path);
 uint64_t line_table_digest(const HostIndex& H);
 // linescan.cu: the line table's columns scanned on CUDA device `device`; false when there is no such device
 bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* out, void** d_text, size_t* d_text_cap);

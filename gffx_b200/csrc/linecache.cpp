@@ -170,8 +170,10 @@ bool line_cache_load(HostIndex& H, int threads) {
     return true;
 }
 
-void line_cache_store(const HostIndex& H) {
-    if (!enabled(H)) return;
+std::string line_cache_target(const HostIndex& H) { return enabled(H) ? cache_path(H) : std::string(); }
+
+void line_cache_store(const HostIndex& H, const std::string& path) {
+    if (path.empty()) return;
     PhaseTimer t("  GFF line table (writing the side-car cache)");
     Header h{};
     memcpy(h.magic, MAGIC, 8);
@@ -183,7 +185,7 @@ void line_cache_store(const HostIndex& H) {
     h.n_types = (uint32_t)H.types.size(); h.n_chroms = (uint32_t)H.chroms.size();
     const std::string tb = pool_bytes(H.types), cb = pool_bytes(H.chroms);
     h.types_bytes = tb.size(); h.chroms_bytes = cb.size();
-    const std::string path = cache_path(H), tmp = path + ".tmp" + std::to_string((long)getpid());
+    const std::string tmp = path + ".tmp" + std::to_string((long)getpid());
     FILE* f = fopen(tmp.c_str(), "wb");
     if (!f) return;
     bool ok = fwrite(&h, sizeof h, 1, f) == 1;

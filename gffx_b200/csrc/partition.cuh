@@ -15,7 +15,7 @@
 // 2-3 times over (r01d: 338 MB written for 120 MB of output, 310 us).  So every tile is sorted by window in
 // shared memory first and stored run by run with consecutive lanes on consecutive addresses, and the window
 // count is kept small enough (<= 511) for the runs to be whole 32-byte sectors; the kernels that need finer
-// locality than a window sort their own tile again in shared memory (tilesort.cuh).
+// locality than a window sort their own tile again in shared memory (rootjoin.cuh) or count into shared memory (counts.cuh).
 //   part_count_kernel    tile of 4096 regions: shared-memory histogram over the windows, added to the global window totals
 //   part_offsets_kernel  one CTA: exclusive scan of the <= 512 totals = first bucketed position of every window (`poff`)
 //                        and the windows' write cursors

@@ -4,9 +4,12 @@
 #pragma once
 #include <cstdint>
 #include <vector>
-#include "join_build.h"
 
 namespace gffx {
+
+struct JoinItem {   // an interval of (virtual) sequence `seq` with a payload
+    uint32_t seq, start, end, payload;
+};
 
 // Bin-list form (K1, winjoin.cuh).  Every window of the partition grid is cut into 2^sub bins; bin b of window w owns
 //   list[boff[w,b] .. boff[w,b+1])  the intervals that overlap the bin (start < bin end && end > bin start), by start
