@@ -154,9 +154,9 @@ void counts_begin_impl(EngineImpl* E, int kind) {
         GFFX_CUDA(cudaMemsetAsync(C->d_G.p, 0, ng * 4, st));
     } else {
         const size_t nw = std::max<uint64_t>(h.n_words, 1);
-        C->d_bits.ensure(nw * 8); C->d_diff.ensure(nw * 4); C->d_P.ensure(nw * 4);
+        C->d_bits.ensure((nw + 4) * 8); C->d_diff.ensure(nw * 4); C->d_P.ensure(nw * 4);
         C->d_routed.ensure(std::max<uint32_t>(E->n_blocks, 1));
-        GFFX_CUDA(cudaMemsetAsync(C->d_bits.p, 0, nw * 8, st));
+        GFFX_CUDA(cudaMemsetAsync(C->d_bits.p, 0, (nw + 4) * 8, st));   // + the tail of the last group of four words
         GFFX_CUDA(cudaMemsetAsync(C->d_diff.p, 0, nw * 4, st));
         GFFX_CUDA(cudaMemsetAsync(C->d_routed.p, 0, std::max<uint32_t>(E->n_blocks, 1), st));
     }

@@ -125,23 +125,28 @@ __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp
     const unsigned long long wa = word0 + (p0 >> 6), wb = word0 + (p1 >> 6);
     const unsigned long long ma = ~0ull << (p0 & 63), mb = ~0ull >> (63 - (p1 & 63));
     // bits are only ever set during a job, so a word that already shows the mask needs no atomic
-    if (wa == wb) {
-        const unsigned long long m = ma & mb;
-        if ((__ldcg(D.bits + wa) & m) != m) atomicOr(D.bits + wa, m);
+    if (wb - wa - 1 <= COV_DIRECT_WORDS || wa == wb) {
+        // a short region (a read): its few whole words are OR-ed like the partial ones — once a word is full, which at
+        // sequencing depth it is after the first reads, this is a load from the sector the partial words came from, where
+        // the difference array costs two atomics per region whatever the bitmap already holds (profiles/r02v: 1.1 G L2
+        // sectors per 100 M reads, the kernel L2-bound).  The words are read as aligned groups of four — one 32-byte sector,
+        // one request (LDG.256) — so a 150-base read costs one or two L2 requests, not three or four.
+        for (unsigned long long g = wa & ~3ull; g <= wb; g += 4) {
+            unsigned long long q[4];
+            asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(q[0]), "=l"(q[1]), "=l"(q[2]), "=l"(q[3]) : "l"(D.bits + g));
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const unsigned long long w = g + i;
+                if (w < wa || w > wb) continue;
+                const unsigned long long m = (w == wa ? ma : ~0ull) & (w == wb ? mb : ~0ull);
+                if ((q[i] & m) != m) atomicOr(D.bits + w, m);
+            }
+        }
     } else {
         if ((__ldcg(D.bits + wa) & ma) != ma) atomicOr(D.bits + wa, ma);
         if ((__ldcg(D.bits + wb) & mb) != mb) atomicOr(D.bits + wb, mb);
-        if (wb - wa - 1 <= COV_DIRECT_WORDS) {
-            // a short region (a read): its few whole words are OR-ed like the partial ones — once a word is full, which at
-            // sequencing depth it is after the first reads, this is a load from the sector the partial words came from, where
-            // the difference array costs two atomics per region whatever the bitmap already holds (profiles/r02v: 1.1 G L2
-            // sectors per 100 M reads, the kernel L2-bound)
-            for (unsigned long long w = wa + 1; w < wb; w++)
-                if (__ldcg(D.bits + w) != ~0ull) atomicOr(D.bits + w, ~0ull);
-        } else {
-            atomicAdd(D.diff + wa + 1, 1);
-            atomicAdd(D.diff + wb, -1);
-        }
+        atomicAdd(D.diff + wa + 1, 1);
+        atomicAdd(D.diff + wb, -1);
     }
 }
 
