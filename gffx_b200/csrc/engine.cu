@@ -26,6 +26,7 @@ template <int MODE, bool INV> static void wj_set_attrs() {
 static void set_kernel_attributes() {
     wj_set_attrs<0, false>(); wj_set_attrs<0, true>(); wj_set_attrs<1, false>(); wj_set_attrs<1, true>(); wj_set_attrs<2, false>();
     GFFX_CUDA(cudaFuncSetAttribute(part_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PART_SCATTER_SMEM));
+    GFFX_CUDA(cudaFuncSetAttribute(part_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PART_COUNT_SMEM));
 }
 
 // small kernels -------------------------------------------------------------------------------
@@ -270,9 +271,9 @@ uint32_t EngineImpl::partition_into(const uint32_t* dc, const uint32_t* ds, cons
     if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
     const uint32_t nb = WG.n_win + 1;
     const unsigned tiles = (unsigned)((n + PART_TILE - 1) / PART_TILE);
-    part_count_kernel<<<(tiles + PART_COUNT_TILES - 1) / PART_COUNT_TILES, PART_THREADS, 0, st>>>(WG, dc, ds, (uint32_t)n, d_ptot.as<uint32_t>());
+    part_count_kernel<<<std::min(tiles, (unsigned)(sm_count * PART_COUNT_CTAS)), PART_THREADS, PART_COUNT_SMEM, st>>>(WG, dc, ds, (uint32_t)n, d_ptot.as<uint32_t>());
     part_offsets_kernel<<<1, PART_NB_MAX, 0, st>>>(d_ptot.as<uint32_t>(), nb, (uint32_t)n, poff, d_pcur.as<uint32_t>());
-    part_scatter_kernel<<<tiles, PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, d_pcur.as<uint32_t>(), oc, ose);
+    part_scatter_kernel<<<std::min(tiles, (unsigned)(sm_count * PART_SCATTER_CTAS)), PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, d_pcur.as<uint32_t>(), oc, ose);
     return 3;
 }
 

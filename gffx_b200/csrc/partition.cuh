@@ -30,6 +30,8 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 
+#include "bulkcopy.cuh"
+
 namespace gffx {
 
 constexpr int PART_THREADS = 512;           // the scatter kernel runs 2 CTAs of 61 KB shared memory per SM (51 registers per thread)
@@ -47,7 +49,7 @@ struct WinGrid {
     uint32_t n_seqs, n_vseqs, shift, n_win;
 };
 
-constexpr uint32_t PART_MAP_SMEM = 512;   // sequences whose map entries a CTA keeps in shared memory (8 KB); more: read through L1
+constexpr uint32_t PART_MAP_SMEM = 256;   // sequences whose map entries a CTA keeps in shared memory (4 KB); more: read through L1
 
 // thread t of a tile holds elements 4 * (k * THREADS + t) .. + 3, k < PART_TILE / (4 * THREADS): 16-byte loads when the arrays allow
 constexpr int PART_VEC = PART_TILE / (4 * PART_THREADS);
@@ -74,31 +76,68 @@ __device__ __forceinline__ uint32_t part_window(const WinGrid& G, const uint4* s
     return (m.z & 0xFFFFu) + (b < nw ? b : nw - 1);
 }
 
-#ifndef GFFX_PART_COUNT_TILES
-#define GFFX_PART_COUNT_TILES 2
-#endif
-constexpr int PART_COUNT_TILES = GFFX_PART_COUNT_TILES;   // tiles per CTA of the count pass: fewer global atomics on the window totals
+// The count pass is persistent too: a CTA walks tiles blockIdx.x, + gridDim.x, ... with TWO tiles' columns (sequence number,
+// start: 2 x 16 KB each) in flight to shared memory by cp.async.bulk, counts into one shared histogram for all its tiles and adds
+// the non-zero cells to the global window totals once (a CTA per two tiles did that 1221 times per 10 M regions and waited for
+// its loads twice: 26 us where the traffic needs 12).
+constexpr int PART_COUNT_CTAS = 3;   // per SM
+constexpr size_t PART_COUNT_SMEM = (size_t)2 * 2 * PART_TILE * 4;
 
-static __global__ void __launch_bounds__(PART_THREADS)
+static __global__ void __launch_bounds__(PART_THREADS, PART_COUNT_CTAS)
     part_count_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, uint32_t n, uint32_t* __restrict__ tot) {
+    extern __shared__ __align__(16) uint32_t part_dyn[];   // [2 stages][chr, start][PART_TILE]
     __shared__ uint32_t sh[PART_NB_MAX];
     __shared__ uint4 s_map[PART_MAP_SMEM];
+    __shared__ __align__(8) uint64_t mbar[2];
     const uint32_t nb = G.n_win + 1;
+    const uint32_t tiles = (n + PART_TILE - 1) / PART_TILE;
     const bool al16 = ((reinterpret_cast<uintptr_t>(chr) | reinterpret_cast<uintptr_t>(qs)) & 15u) == 0;
+    auto bulk_ok = [&](uint32_t t) { return al16 && t < tiles && (uint64_t)(t + 1) * PART_TILE <= n; };
+    auto issue = [&](uint32_t t, uint32_t st) {   // thread 0
+        const size_t o = (size_t)t * PART_TILE;
+        mbar_expect_tx(&mbar[st], 2u * PART_TILE * 4u);
+        bulk_g2s(part_dyn + st * 2 * PART_TILE, chr + o, PART_TILE * 4u, &mbar[st]);
+        bulk_g2s(part_dyn + st * 2 * PART_TILE + PART_TILE, qs + o, PART_TILE * 4u, &mbar[st]);
+    };
     for (uint32_t i = threadIdx.x; i < nb; i += PART_THREADS) sh[i] = 0;
     part_stage_map(G, s_map);
+    if (threadIdx.x == 0) {
+        mbar_init(&mbar[0], 1);
+        mbar_init(&mbar[1], 1);
+        if (bulk_ok(blockIdx.x)) issue(blockIdx.x, 0);
+        if (bulk_ok(blockIdx.x + gridDim.x)) issue(blockIdx.x + gridDim.x, 1);
+    }
+    uint32_t phases = 0;   // bit st: the parity stage st's barrier completes next
     __syncthreads();
-    for (int t = 0; t < PART_COUNT_TILES; t++) {
-        const uint64_t base64 = ((uint64_t)blockIdx.x * PART_COUNT_TILES + t) * PART_TILE;
-        if (base64 >= n) break;
-        const uint32_t base = (uint32_t)base64;
+    uint32_t st = 0;
+    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, st ^= 1u) {
+        const uint32_t base = tile * (uint32_t)PART_TILE;
         const uint32_t end = min(n, base + (uint32_t)PART_TILE);
         uint32_t c[PART_VEC][4], s[PART_VEC][4];
+        const bool staged = bulk_ok(tile);
+        if (staged) {
+            mbar_wait(&mbar[st], (phases >> st) & 1u);
+            phases ^= 1u << st;
+            const uint32_t* raw = part_dyn + st * 2 * PART_TILE;
 #pragma unroll
-        for (int k = 0; k < PART_VEC; k++) {
-            const uint32_t i = base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
-            part_load4(chr, i, end, al16, c[k]);
-            part_load4(qs, i, end, al16, s[k]);
+            for (int k = 0; k < PART_VEC; k++) {
+                const uint32_t i = 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
+                const uint4 a = *reinterpret_cast<const uint4*>(raw + i), b = *reinterpret_cast<const uint4*>(raw + PART_TILE + i);
+                c[k][0] = a.x; c[k][1] = a.y; c[k][2] = a.z; c[k][3] = a.w;
+                s[k][0] = b.x; s[k][1] = b.y; s[k][2] = b.z; s[k][3] = b.w;
+            }
+            __syncthreads();   // the stage is in registers: hand it back to the copy engine
+            if (threadIdx.x == 0 && bulk_ok(tile + 2 * gridDim.x)) {
+                fence_proxy_async_smem();
+                issue(tile + 2 * gridDim.x, st);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < PART_VEC; k++) {
+                const uint32_t i = base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
+                part_load4(chr, i, end, al16, c[k]);
+                part_load4(qs, i, end, al16, s[k]);
+            }
         }
 #pragma unroll
         for (int k = 0; k < PART_VEC; k++)
@@ -136,11 +175,19 @@ static __global__ void __launch_bounds__(PART_NB_MAX) part_offsets_kernel(uint32
     if (w == 0) poff[nb] = n;
 }
 
-constexpr size_t PART_SCATTER_SMEM = (size_t)PART_TILE * 14 + (size_t)PART_NB_MAX * 8;
+// shared memory of the scatter kernel: the sorted tile (14 bytes per region), the window histogram / deltas, and the NEXT tile's
+// three input columns as the copy engine delivers them (3 x 16 KB): 109 KB, two CTAs per SM
+constexpr size_t PART_SORT_SMEM = (size_t)PART_TILE * 14 + (size_t)PART_NB_MAX * 8;
+constexpr size_t PART_SCATTER_SMEM = PART_SORT_SMEM + (size_t)PART_TILE * 12;
+constexpr int PART_SCATTER_CTAS = 2;   // per SM; the kernel is persistent: grid = min(tiles, SMs * PART_SCATTER_CTAS)
 
 // ose takes the regions in VIRTUAL coordinates; oc (unless nullptr: a window lies in one virtual sequence) the virtual sequence
-// numbers, 0xFFFFFFFF for a region whose sequence number is out of range
-static __global__ void __launch_bounds__(PART_THREADS, 2)
+// numbers, 0xFFFFFFFF for a region whose sequence number is out of range.
+// Persistent (r02): a CTA walks tiles blockIdx.x, + gridDim.x, ...; while it ranks, sorts and stores one tile, the next tile's
+// columns arrive in shared memory by three cp.async.bulk copies (16 KB each, completion on an mbarrier) — the load latency that
+// a CTA per tile paid in front of every tile (r02k: 64 us per 10 M regions, DRAM 28 % busy) is off the critical path.  A tile
+// that the copy engine cannot take (arrays not 16-byte aligned, the partial last tile) is loaded by the threads as before.
+static __global__ void __launch_bounds__(PART_THREADS, PART_SCATTER_CTAS)
     part_scatter_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
                         uint32_t n, uint32_t* __restrict__ cursor, uint32_t* __restrict__ oc, uint2* __restrict__ ose) {
     extern __shared__ __align__(16) uint32_t part_dyn[];  // PART_SCATTER_SMEM bytes
@@ -149,76 +196,115 @@ static __global__ void __launch_bounds__(PART_THREADS, 2)
     uint16_t* s_w = reinterpret_cast<uint16_t*>(s_c + PART_TILE);
     uint32_t* s_hist = s_c + PART_TILE + PART_TILE / 2;                // regions per window -> first sorted position
     uint32_t* s_delta = s_hist + PART_NB_MAX;                          // global position minus sorted position of the window's run
+    uint32_t* s_raw = s_delta + PART_NB_MAX;                           // [3][PART_TILE]: chr, start, end of the tile in flight
     __shared__ uint32_t s_warp[PART_THREADS / 32];
     __shared__ uint4 s_map[PART_MAP_SMEM];
+    __shared__ __align__(8) uint64_t mbar;
     const uint32_t nb = G.n_win + 1;
-    const uint32_t base = blockIdx.x * (uint32_t)PART_TILE;
-    const uint32_t end = min(n, base + (uint32_t)PART_TILE);
+    const uint32_t tiles = (n + PART_TILE - 1) / PART_TILE;
     const bool al16 = ((reinterpret_cast<uintptr_t>(chr) | reinterpret_cast<uintptr_t>(qs) | reinterpret_cast<uintptr_t>(qe)) & 15u) == 0;
     static_assert(PART_NB_MAX == PART_THREADS, "one window per thread");
-    s_hist[threadIdx.x] = 0;
+    auto bulk_ok = [&](uint32_t t) { return al16 && t < tiles && (uint64_t)(t + 1) * PART_TILE <= n; };
+    auto issue = [&](uint32_t t) {   // thread 0
+        const size_t o = (size_t)t * PART_TILE;
+        mbar_expect_tx(&mbar, 3u * PART_TILE * 4u);
+        bulk_g2s(s_raw, chr + o, PART_TILE * 4u, &mbar);
+        bulk_g2s(s_raw + PART_TILE, qs + o, PART_TILE * 4u, &mbar);
+        bulk_g2s(s_raw + 2 * PART_TILE, qe + o, PART_TILE * 4u, &mbar);
+    };
     part_stage_map(G, s_map);
-    uint32_t c[PART_VEC][4], s[PART_VEC][4], e[PART_VEC][4];
-#pragma unroll
-    for (int k = 0; k < PART_VEC; k++) {
-        const uint32_t i = base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
-        part_load4(chr, i, end, al16, c[k]);
-        part_load4(qs, i, end, al16, s[k]);
-        part_load4(qe, i, end, al16, e[k]);
+    if (threadIdx.x == 0) {
+        mbar_init(&mbar, 1);
+        if (bulk_ok(blockIdx.x)) issue(blockIdx.x);
     }
+    uint32_t phase = 0;
     __syncthreads();
-    uint32_t wr[PART_VEC][4];   // window << 12 | rank inside the tile's run of that window
+    for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const uint32_t base = tile * (uint32_t)PART_TILE;
+        const uint32_t end = min(n, base + (uint32_t)PART_TILE);
+        s_hist[threadIdx.x] = 0;
+        uint32_t c[PART_VEC][4], s[PART_VEC][4], e[PART_VEC][4];
+        if (bulk_ok(tile)) {
+            mbar_wait(&mbar, phase);
+            phase ^= 1u;
 #pragma unroll
-    for (int k = 0; k < PART_VEC; k++)
+            for (int k = 0; k < PART_VEC; k++) {
+                const uint32_t i = 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
+                const uint4 a = *reinterpret_cast<const uint4*>(s_raw + i), b = *reinterpret_cast<const uint4*>(s_raw + PART_TILE + i),
+                            d = *reinterpret_cast<const uint4*>(s_raw + 2 * PART_TILE + i);
+                c[k][0] = a.x; c[k][1] = a.y; c[k][2] = a.z; c[k][3] = a.w;
+                s[k][0] = b.x; s[k][1] = b.y; s[k][2] = b.z; s[k][3] = b.w;
+                e[k][0] = d.x; e[k][1] = d.y; e[k][2] = d.z; e[k][3] = d.w;
+            }
+        } else {
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            wr[k][j] = 0xFFFFFFFFu;
-            if (base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x) + j < end) {
-                uint4 m;
-                const uint32_t w = part_window(G, s_map, c[k][j], s[k][j], &m);
-                wr[k][j] = (w << 12) | atomicAdd(&s_hist[w], 1u);
-                s[k][j] = m.x + min(s[k][j], m.y);   // from here on: virtual coordinates
-                e[k][j] = m.x + min(e[k][j], m.y);
-                c[k][j] = m.w;
+            for (int k = 0; k < PART_VEC; k++) {
+                const uint32_t i = base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
+                part_load4(chr, i, end, al16, c[k]);
+                part_load4(qs, i, end, al16, s[k]);
+                part_load4(qe, i, end, al16, e[k]);
             }
         }
-    static_assert(PART_TILE <= 4096, "12 bits of rank");
-    __syncthreads();
-    {   // exclusive scan of the histogram; every window with regions claims its run on the window's cursor
-        const uint32_t w = threadIdx.x, lane = w & 31u;
-        const uint32_t v = s_hist[w];
-        uint32_t x = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, x, d);
-            if (lane >= (uint32_t)d) x += o;
+        __syncthreads();   // the histogram is clear, the staged columns are in registers
+        if (threadIdx.x == 0 && bulk_ok(tile + gridDim.x)) {
+            fence_proxy_async_smem();   // the threads' reads of s_raw come before the copy engine's writes
+            issue(tile + gridDim.x);
         }
-        if (lane == 31) s_warp[w >> 5] = x;
-        const uint32_t g = (v && w < nb) ? atomicAdd(cursor + w, v) : 0u;
+        uint32_t wr[PART_VEC][4];   // window << 12 | rank inside the tile's run of that window
+#pragma unroll
+        for (int k = 0; k < PART_VEC; k++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                wr[k][j] = 0xFFFFFFFFu;
+                if (base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x) + j < end) {
+                    uint4 m;
+                    const uint32_t w = part_window(G, s_map, c[k][j], s[k][j], &m);
+                    wr[k][j] = (w << 12) | atomicAdd(&s_hist[w], 1u);
+                    s[k][j] = m.x + min(s[k][j], m.y);   // from here on: virtual coordinates
+                    e[k][j] = m.x + min(e[k][j], m.y);
+                    c[k][j] = m.w;
+                }
+            }
+        static_assert(PART_TILE <= 4096, "12 bits of rank");
         __syncthreads();
-        uint32_t pre = 0;
-        for (uint32_t k = 0; k < (w >> 5); k++) pre += s_warp[k];
-        const uint32_t ex = pre + x - v;
-        s_hist[w] = ex;
-        s_delta[w] = g - ex;
-    }
-    __syncthreads();
+        uint32_t g, ex;
+        {   // exclusive scan of the histogram; every window with regions claims its run on the window's cursor
+            const uint32_t w = threadIdx.x, lane = w & 31u;
+            const uint32_t v = s_hist[w];
+            uint32_t x = v;
 #pragma unroll
-    for (int k = 0; k < PART_VEC; k++)
-#pragma unroll
-        for (int j = 0; j < 4; j++)
-            if (wr[k][j] != 0xFFFFFFFFu) {
-                const uint32_t w = wr[k][j] >> 12, lp = s_hist[w] + (wr[k][j] & 0xFFFu);
-                s_se[lp] = make_uint2(s[k][j], e[k][j]);
-                s_w[lp] = (uint16_t)w;
-                if (oc) s_c[lp] = c[k][j];
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, x, d);
+                if (lane >= (uint32_t)d) x += o;
             }
-    __syncthreads();
-    const uint32_t cnt = end - base;
-    for (uint32_t i = threadIdx.x; i < cnt; i += PART_THREADS) {
-        const uint32_t g = i + s_delta[s_w[i]];
-        ose[g] = s_se[i];
-        if (oc) oc[g] = s_c[i];
+            if (lane == 31) s_warp[w >> 5] = x;
+            g = (v && w < nb) ? atomicAdd(cursor + w, v) : 0u;   // its answer is first needed after the sort below
+            __syncthreads();
+            uint32_t pre = 0;
+            for (uint32_t k = 0; k < (w >> 5); k++) pre += s_warp[k];
+            ex = pre + x - v;
+            s_hist[w] = ex;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < PART_VEC; k++)
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (wr[k][j] != 0xFFFFFFFFu) {
+                    const uint32_t w = wr[k][j] >> 12, lp = s_hist[w] + (wr[k][j] & 0xFFFu);
+                    s_se[lp] = make_uint2(s[k][j], e[k][j]);
+                    s_w[lp] = (uint16_t)w;
+                    if (oc) s_c[lp] = c[k][j];
+                }
+        s_delta[threadIdx.x] = g - ex;
+        __syncthreads();
+        const uint32_t cnt = end - base;
+        for (uint32_t i = threadIdx.x; i < cnt; i += PART_THREADS) {
+            const uint32_t gp = i + s_delta[s_w[i]];
+            ose[gp] = s_se[i];
+            if (oc) oc[gp] = s_c[i];
+        }
+        __syncthreads();   // the sorted tile and the deltas are read: the next tile may overwrite them
     }
 }
 

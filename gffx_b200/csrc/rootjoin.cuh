@@ -18,6 +18,7 @@
 // sorted into a tail part of the same tile and resolved region-parallel against the bin lists (wj_round_global, the rule
 // of wj_small_segment), so any input gives the reference's counts; roots with end <= start test every region of the tile.
 #pragma once
+#include "bulkcopy.cuh"
 #include "winjoin.cuh"
 
 namespace gffx {
@@ -97,24 +98,6 @@ struct RankSlices {
     const uint32_t* xlen;   // n_win: values in the window's part; 0xFFFFFFFF: too many for shared memory
     const uint16_t* xoff;   // n_win * WR_XOFF_STRIDE: [b] = values of the part below fine bin b's first base, [WR_NBF] = xlen
 };
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {   // 16-byte aligned, bytes % 16 == 0
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes),
-                 "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t ok = 0;
-    while (!ok)
-        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-}
 // lb = #(part < v) for a v of fine bin b; *eq = (part[lb] == v).  sx[k] = value k of the window's part
 __device__ __forceinline__ uint32_t rank_lb_slice(const uint32_t* sx, const uint16_t* soff, uint32_t xlen, uint32_t b, uint32_t v, bool* eq) {
     uint32_t lo = soff[b], hi = soff[b + 1];
