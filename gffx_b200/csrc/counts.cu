@@ -199,9 +199,8 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
 
 // one batch of device-resident regions: K0 partition + the scatter kernel; asynchronous on the engine's stream
 static void counts_add_device(EngineImpl* E, CountsState* C, const CountsDev& D, const uint32_t* dc, const uint32_t* ds, const uint32_t* de,
-                              uint64_t n, uint32_t* oc, uint2* ose) {
-    // both kernels take the sequence from the window: the bucketed sequence numbers are not written
-    C->launches += E->partition_into(dc, ds, de, n, nullptr, ose, E->d_poff.as<uint32_t>());
+                              uint64_t n, uint2* ose) {
+    C->launches += E->partition_into(dc, ds, de, n, ose, E->d_poff.as<uint32_t>());
     if (C->kind == 0) {   // a CTA per run of a window's reads, shared-memory histograms (counts.cuh: depth_window_kernel)
         const DepthWin W{E->WC.win_seq, E->WC.win0, E->d_poff.as<uint32_t>(), E->WC.shift, E->WC.n_win, C->CXS, C->host.n_irregular != 0};
         const unsigned grid = (unsigned)(n / DW_RUN) + E->WC.n_win + 1;
@@ -227,11 +226,10 @@ void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, 
     uint64_t chunk = n;
     if (!dev_in && n >= (1u << 22)) chunk = ((n + 7) / 8 + PART_TILE - 1) / PART_TILE * PART_TILE;
     const uint32_t n_chunks = (uint32_t)((n + chunk - 1) / chunk);
-    E->d_bchr.ensure(chunk * 4 + 16);
     E->d_bse.ensure(chunk * 8 + 32);
     GFFX_CUDA(cudaEventRecord(C->ev0, E->st));
     if (dev_in) {
-        counts_add_device(E, C, D, chr, start, end, n, E->d_bchr.as<uint32_t>(), E->d_bse.as<uint2>());
+        counts_add_device(E, C, D, chr, start, end, n, E->d_bse.as<uint2>());
     } else {
         const uint32_t* src[3] = {chr, start, end};
         for (int k = 0; k < 3; k++) E->d_q[k].ensure(n * 4);
@@ -251,7 +249,7 @@ void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, 
             GFFX_CUDA(cudaStreamWaitEvent(E->st, E->ev_copy[c], 0));
             // the bucketed form of a chunk is scratch: the next chunk's partition overwrites it (stream order)
             counts_add_device(E, C, D, E->d_q[0].as<uint32_t>() + o, E->d_q[1].as<uint32_t>() + o, E->d_q[2].as<uint32_t>() + o, m,
-                              E->d_bchr.as<uint32_t>(), E->d_bse.as<uint2>());
+                              E->d_bse.as<uint2>());
         }
     }
     GFFX_CUDA(cudaEventRecord(C->ev1, E->st));

@@ -84,7 +84,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
                     &d_wj_win0, &d_wj_base, &d_seqmap, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
-                    &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
+                    &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->total = &dev_bytes;
     {
@@ -131,7 +131,7 @@ EngineImpl::~EngineImpl() {
                     &d_wj_win0, &d_wj_base, &d_seqmap, &d_blk_ent0, &d_blk_ent, &d_orphans, &d_wj_winseq, &d_wj_ent4, &d_wj_list4, &d_wj_fid, &d_wj_first, &d_wj_boff, &d_wj_rend, &d_wj_blk, &d_wj_hit, &d_wj_cnt, &d_wj_off, &d_text, &d_text_off, &d_text_out, &d_text_ranges, &d_bed_text, &d_bed_tiles, &d_bed_tfirst, &d_bed_lstart, &d_bed_status,
                     &d_bed_line[0], &d_bed_line[1], &d_bed_line[2], &d_bed_flag, &d_bed_pos, &d_bed_out[0], &d_bed_out[1], &d_bed_out[2],
                     &d_bed_nhash, &d_bed_nid, &d_bed_noff, &d_bed_nlen, &d_bed_nblob,
-                    &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse,
+                    &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
     counts_release(this);
@@ -154,7 +154,7 @@ EngineImpl::~EngineImpl() {
 // ---- job lanes (engine_impl.cuh) ------------------------------------------------------------------------------------
 std::vector<DBuf*> EngineImpl::lane_bufs() {
     return {&d_wj_hit, &d_wj_cnt, &d_wj_off, &d_blk_sel, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-            &d_poff, &d_ptot, &d_pcur, &d_bchr, &d_bse, &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn};
+            &d_poff, &d_ptot, &d_pcur, &d_bse, &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn};
 }
 
 DBuf& EngineImpl::lane_buf(int lane, DBuf* member) {
@@ -234,7 +234,8 @@ void EngineImpl::build_windows() {
     std::vector<uint4> seqmap(std::max<size_t>(n_seqs, 1), make_uint4(0, 0xFFFFFFFFu, 0, 0));
     for (size_t c = 0; c < n_seqs; c++) {
         const VSeqMap::Seq& m = V.seq[c];
-        seqmap[c] = make_uint4(m.base, m.clamp, h_win0[m.vseq] | ((h_win0[m.vseq + 1] - h_win0[m.vseq]) << 16), m.vseq);
+        const uint32_t nw = h_win0[m.vseq + 1] - h_win0[m.vseq];
+        seqmap[c] = make_uint4(m.base, m.clamp, h_win0[m.vseq] | (nw << 16), m.vseq);
     }
     upload(d_win0, h_win0, st);
     upload(d_seqmap, seqmap, st);
@@ -251,29 +252,17 @@ void EngineImpl::build_windows() {
     GFFX_CUDA(cudaStreamSynchronize(st));
 }
 
-uint32_t EngineImpl::partition(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, const uint32_t** bchr,
-                               const uint2** bse) {
-    *bchr = nullptr; *bse = nullptr;
-    if (n == 0) return 0;
-    d_bchr.ensure(n * 4 + 16);
-    d_bse.ensure(n * 8 + 32);
-    const uint32_t launches = partition_into(dc, ds, de, n, d_bchr.as<uint32_t>(), d_bse.as<uint2>(), d_poff.as<uint32_t>());
-    *bchr = d_bchr.as<uint32_t>();
-    *bse = d_bse.as<uint2>();
-    return launches;
-}
-
-// the same pass with caller-chosen outputs: `ose` (and `oc` unless NULL) take the n bucketed regions, `poff` the n_win + 2
+// K0 with caller-chosen outputs: `ose` takes the n bucketed regions, `poff` the n_win + 2
 // window offsets.  The window totals and cursors are scratch that the NEXT call on the stream reuses (stream order keeps that safe).
-uint32_t EngineImpl::partition_into(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, uint32_t* oc, uint2* ose,
-                                    uint32_t* poff) {
+uint32_t EngineImpl::partition_into(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, uint2* ose, uint32_t* poff) {
     if (n == 0) return 0;
     if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
     const uint32_t nb = WG.n_win + 1;
     const unsigned tiles = (unsigned)((n + PART_TILE - 1) / PART_TILE);
     part_count_kernel<<<std::min(tiles, (unsigned)(sm_count * PART_COUNT_CTAS)), PART_THREADS, PART_COUNT_SMEM, st>>>(WG, dc, ds, (uint32_t)n, d_ptot.as<uint32_t>());
     part_offsets_kernel<<<1, PART_NB_MAX, 0, st>>>(d_ptot.as<uint32_t>(), nb, (uint32_t)n, poff, d_pcur.as<uint32_t>());
-    part_scatter_kernel<<<std::min(tiles, (unsigned)(sm_count * PART_SCATTER_CTAS)), PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, d_pcur.as<uint32_t>(), oc, ose);
+    const unsigned stiles = (unsigned)((n + PART_STILE - 1) / PART_STILE);
+    part_scatter_kernel<<<std::min(stiles, (unsigned)(sm_count * PART_SCATTER_CTAS)), PART_THREADS, PART_SCATTER_SMEM, st>>>(WG, dc, ds, de, (uint32_t)n, d_pcur.as<uint32_t>(), ose);
     return 3;
 }
 
@@ -797,7 +786,6 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
     } else {
         d_bse.ensure(n * 8 + 32);
     }
-    uint32_t* oc = nullptr;   // the join and the rank-space scatter take the sequence from the window
     uint2* ose = d_bse.as<uint2>() + ck.off;
     uint32_t* poff = d_poff.as<uint32_t>() + (jb.retained ? (size_t)slot * (WG.n_win + 2) : 0);
     jb.n_total += n;
@@ -806,7 +794,7 @@ void EngineImpl::ix_add(const uint32_t* dc, const uint32_t* ds, const uint32_t* 
     unsigned long long* small = d_small.as<unsigned long long>();
     uint32_t* small32 = d_small.as<uint32_t>();
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot], st));
-    jb.launches += partition_into(dc, ds, de, n, oc, ose, poff);
+    jb.launches += partition_into(dc, ds, de, n, ose, poff);
     if (timed) GFFX_CUDA(cudaEventRecord(ev_chunk[4 * slot + 1], st));
     if (jb.pairs_dev && jb.pair_cap == 0) {
         // grow-only; a larger result re-runs the expansion (or, for an asynchronous job, reports its pairs as not materialised)

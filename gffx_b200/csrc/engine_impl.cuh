@@ -114,7 +114,7 @@ class EngineImpl {
     DBuf d_A, d_B, d_Ms, d_Me, d_PMX, d_SMN, d_NS, d_NE, d_keep, d_type_allow;
 
     // ---- window grid + partition scratch (partition.cuh) --------------------------------------
-    DBuf d_seqmap, d_win0, d_poff, d_ptot, d_pcur, d_bchr, d_bse;
+    DBuf d_seqmap, d_win0, d_poff, d_ptot, d_pcur, d_bse;
     std::vector<uint32_t> h_win0;
     WinGrid WG{};
 
@@ -196,8 +196,7 @@ class EngineImpl {
                        const uint32_t** dc, const uint32_t** ds, const uint32_t** de);
     // K0: bucket n (< 2^31) device-resident regions by window; returns the bucketed arrays (engine-owned
     // scratch, valid until the next call) and the number of kernels launched
-    uint32_t partition(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, const uint32_t** bchr, const uint2** bse);
-    uint32_t partition_into(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, uint32_t* oc, uint2* ose, uint32_t* poff);
+    uint32_t partition_into(const uint32_t* dc, const uint32_t* ds, const uint32_t* de, uint64_t n, uint2* ose, uint32_t* poff);
 };
 
 // counts.cu

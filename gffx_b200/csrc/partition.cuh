@@ -28,6 +28,7 @@
 // strided matrix traffic per 10 M regions.)
 #pragma once
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cstdint>
 
 #include "bulkcopy.cuh"
@@ -49,7 +50,11 @@ struct WinGrid {
     uint32_t n_seqs, n_vseqs, shift, n_win;
 };
 
-constexpr uint32_t PART_MAP_SMEM = 256;   // sequences whose map entries a CTA keeps in shared memory (4 KB); more: read through L1
+// sequences whose map entries a CTA keeps in shared memory (4 KB); more: read through L1.  (A 4-byte "fast" entry per sequence —
+// first window and a limit below which a coordinate is its own virtual coordinate — halves the kernels' shared-memory
+// wavefronts and makes both slower, r02y: 25 -> 28.5 and 61 -> 65 us; they are bound by instruction issue and dependent
+// latency, not by the shared-memory pipe, and the one LDS.128 is the fewest instructions.)
+constexpr uint32_t PART_MAP_SMEM = 256;
 
 // thread t of a tile holds elements 4 * (k * THREADS + t) .. + 3, k < PART_TILE / (4 * THREADS): 16-byte loads when the arrays allow
 constexpr int PART_VEC = PART_TILE / (4 * PART_THREADS);
@@ -67,7 +72,7 @@ __device__ __forceinline__ void part_stage_map(const WinGrid& G, uint4* s_map) {
     if (G.n_seqs <= PART_MAP_SMEM)
         for (uint32_t i = threadIdx.x; i < G.n_seqs; i += PART_THREADS) s_map[i] = __ldg(G.seqmap + i);
 }
-// window of region (c, s, .) and its virtual start; c >= n_seqs: the error bucket n_win, coordinates untouched
+// window of region (c, s, .) and its map entry; c >= n_seqs: the error bucket n_win, coordinates untouched
 __device__ __forceinline__ uint32_t part_window(const WinGrid& G, const uint4* s_map, uint32_t c, uint32_t s, uint4* m_out) {
     if (c >= G.n_seqs) { *m_out = make_uint4(0u, 0xFFFFFFFFu, 0u, 0xFFFFFFFFu); return G.n_win; }
     const uint4 m = G.n_seqs <= PART_MAP_SMEM ? s_map[c] : __ldg(G.seqmap + c);
@@ -175,42 +180,49 @@ static __global__ void __launch_bounds__(PART_NB_MAX) part_offsets_kernel(uint32
     if (w == 0) poff[nb] = n;
 }
 
-// shared memory of the scatter kernel: the sorted tile (14 bytes per region), the window histogram / deltas, and the NEXT tile's
-// three input columns as the copy engine delivers them (3 x 16 KB): 109 KB, two CTAs per SM
-constexpr size_t PART_SORT_SMEM = (size_t)PART_TILE * 14 + (size_t)PART_NB_MAX * 8;
-constexpr size_t PART_SCATTER_SMEM = PART_SORT_SMEM + (size_t)PART_TILE * 12;
-constexpr int PART_SCATTER_CTAS = 2;   // per SM; the kernel is persistent: grid = min(tiles, SMs * PART_SCATTER_CTAS)
+#ifndef GFFX_PART_STILE
+#define GFFX_PART_STILE 4096
+#endif
+constexpr int PART_STILE = GFFX_PART_STILE;   // regions per tile of the scatter pass
+constexpr int PART_SVEC = PART_STILE / (4 * PART_THREADS);
+// shared memory of the scatter kernel: the sorted tile (10 bytes per region), the window histogram / deltas, and the NEXT tile's
+// three input columns as the copy engine delivers them (3 x 16 KB): 92 KB, two CTAs per SM
+constexpr size_t PART_SORT_SMEM = (size_t)PART_STILE * 10 + (size_t)PART_NB_MAX * 8;
+constexpr size_t PART_SCATTER_SMEM = PART_SORT_SMEM + (size_t)PART_STILE * 12;
+#ifndef GFFX_PART_SCTAS
+#define GFFX_PART_SCTAS (GFFX_PART_STILE <= 2048 ? 3 : 2)
+#endif
+constexpr int PART_SCATTER_CTAS = GFFX_PART_SCTAS;   // per SM; the kernel is persistent: grid = min(tiles, SMs * PART_SCATTER_CTAS)
 
-// ose takes the regions in VIRTUAL coordinates; oc (unless nullptr: a window lies in one virtual sequence) the virtual sequence
-// numbers, 0xFFFFFFFF for a region whose sequence number is out of range.
+// ose takes the regions in VIRTUAL coordinates (a window lies in one virtual sequence: the consumers take the sequence from the
+// window; regions whose sequence number is out of range land in the bucket behind the last window).
 // Persistent (r02): a CTA walks tiles blockIdx.x, + gridDim.x, ...; while it ranks, sorts and stores one tile, the next tile's
 // columns arrive in shared memory by three cp.async.bulk copies (16 KB each, completion on an mbarrier) — the load latency that
 // a CTA per tile paid in front of every tile (r02k: 64 us per 10 M regions, DRAM 28 % busy) is off the critical path.  A tile
 // that the copy engine cannot take (arrays not 16-byte aligned, the partial last tile) is loaded by the threads as before.
 static __global__ void __launch_bounds__(PART_THREADS, PART_SCATTER_CTAS)
     part_scatter_kernel(WinGrid G, const uint32_t* __restrict__ chr, const uint32_t* __restrict__ qs, const uint32_t* __restrict__ qe,
-                        uint32_t n, uint32_t* __restrict__ cursor, uint32_t* __restrict__ oc, uint2* __restrict__ ose) {
+                        uint32_t n, uint32_t* __restrict__ cursor, uint2* __restrict__ ose) {
     extern __shared__ __align__(16) uint32_t part_dyn[];  // PART_SCATTER_SMEM bytes
     uint2* s_se = reinterpret_cast<uint2*>(part_dyn);                  // the tile sorted by window
-    uint32_t* s_c = part_dyn + 2 * PART_TILE;
-    uint16_t* s_w = reinterpret_cast<uint16_t*>(s_c + PART_TILE);
-    uint32_t* s_hist = s_c + PART_TILE + PART_TILE / 2;                // regions per window -> first sorted position
+    uint16_t* s_w = reinterpret_cast<uint16_t*>(part_dyn + 2 * PART_STILE);
+    uint32_t* s_hist = part_dyn + 2 * PART_STILE + PART_STILE / 2;       // regions per window -> first sorted position
     uint32_t* s_delta = s_hist + PART_NB_MAX;                          // global position minus sorted position of the window's run
-    uint32_t* s_raw = s_delta + PART_NB_MAX;                           // [3][PART_TILE]: chr, start, end of the tile in flight
+    uint32_t* s_raw = s_delta + PART_NB_MAX;                           // [3][PART_STILE]: chr, start, end of the tile in flight
     __shared__ uint32_t s_warp[PART_THREADS / 32];
     __shared__ uint4 s_map[PART_MAP_SMEM];
     __shared__ __align__(8) uint64_t mbar;
     const uint32_t nb = G.n_win + 1;
-    const uint32_t tiles = (n + PART_TILE - 1) / PART_TILE;
+    const uint32_t tiles = (n + PART_STILE - 1) / PART_STILE;
     const bool al16 = ((reinterpret_cast<uintptr_t>(chr) | reinterpret_cast<uintptr_t>(qs) | reinterpret_cast<uintptr_t>(qe)) & 15u) == 0;
     static_assert(PART_NB_MAX == PART_THREADS, "one window per thread");
-    auto bulk_ok = [&](uint32_t t) { return al16 && t < tiles && (uint64_t)(t + 1) * PART_TILE <= n; };
+    auto bulk_ok = [&](uint32_t t) { return al16 && t < tiles && (uint64_t)(t + 1) * PART_STILE <= n; };
     auto issue = [&](uint32_t t) {   // thread 0
-        const size_t o = (size_t)t * PART_TILE;
-        mbar_expect_tx(&mbar, 3u * PART_TILE * 4u);
-        bulk_g2s(s_raw, chr + o, PART_TILE * 4u, &mbar);
-        bulk_g2s(s_raw + PART_TILE, qs + o, PART_TILE * 4u, &mbar);
-        bulk_g2s(s_raw + 2 * PART_TILE, qe + o, PART_TILE * 4u, &mbar);
+        const size_t o = (size_t)t * PART_STILE;
+        mbar_expect_tx(&mbar, 3u * PART_STILE * 4u);
+        bulk_g2s(s_raw, chr + o, PART_STILE * 4u, &mbar);
+        bulk_g2s(s_raw + PART_STILE, qs + o, PART_STILE * 4u, &mbar);
+        bulk_g2s(s_raw + 2 * PART_STILE, qe + o, PART_STILE * 4u, &mbar);
     };
     part_stage_map(G, s_map);
     if (threadIdx.x == 0) {
@@ -220,25 +232,25 @@ static __global__ void __launch_bounds__(PART_THREADS, PART_SCATTER_CTAS)
     uint32_t phase = 0;
     __syncthreads();
     for (uint32_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const uint32_t base = tile * (uint32_t)PART_TILE;
-        const uint32_t end = min(n, base + (uint32_t)PART_TILE);
+        const uint32_t base = tile * (uint32_t)PART_STILE;
+        const uint32_t end = min(n, base + (uint32_t)PART_STILE);
         s_hist[threadIdx.x] = 0;
-        uint32_t c[PART_VEC][4], s[PART_VEC][4], e[PART_VEC][4];
+        uint32_t c[PART_SVEC][4], s[PART_SVEC][4], e[PART_SVEC][4];
         if (bulk_ok(tile)) {
             mbar_wait(&mbar, phase);
             phase ^= 1u;
 #pragma unroll
-            for (int k = 0; k < PART_VEC; k++) {
+            for (int k = 0; k < PART_SVEC; k++) {
                 const uint32_t i = 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
-                const uint4 a = *reinterpret_cast<const uint4*>(s_raw + i), b = *reinterpret_cast<const uint4*>(s_raw + PART_TILE + i),
-                            d = *reinterpret_cast<const uint4*>(s_raw + 2 * PART_TILE + i);
+                const uint4 a = *reinterpret_cast<const uint4*>(s_raw + i), b = *reinterpret_cast<const uint4*>(s_raw + PART_STILE + i),
+                            d = *reinterpret_cast<const uint4*>(s_raw + 2 * PART_STILE + i);
                 c[k][0] = a.x; c[k][1] = a.y; c[k][2] = a.z; c[k][3] = a.w;
                 s[k][0] = b.x; s[k][1] = b.y; s[k][2] = b.z; s[k][3] = b.w;
                 e[k][0] = d.x; e[k][1] = d.y; e[k][2] = d.z; e[k][3] = d.w;
             }
         } else {
 #pragma unroll
-            for (int k = 0; k < PART_VEC; k++) {
+            for (int k = 0; k < PART_SVEC; k++) {
                 const uint32_t i = base + 4u * ((uint32_t)k * PART_THREADS + threadIdx.x);
                 part_load4(chr, i, end, al16, c[k]);
                 part_load4(qs, i, end, al16, s[k]);
@@ -250,9 +262,9 @@ static __global__ void __launch_bounds__(PART_THREADS, PART_SCATTER_CTAS)
             fence_proxy_async_smem();   // the threads' reads of s_raw come before the copy engine's writes
             issue(tile + gridDim.x);
         }
-        uint32_t wr[PART_VEC][4];   // window << 12 | rank inside the tile's run of that window
+        uint32_t wr[PART_SVEC][4];   // window << 12 | rank inside the tile's run of that window
 #pragma unroll
-        for (int k = 0; k < PART_VEC; k++)
+        for (int k = 0; k < PART_SVEC; k++)
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 wr[k][j] = 0xFFFFFFFFu;
@@ -262,10 +274,9 @@ static __global__ void __launch_bounds__(PART_THREADS, PART_SCATTER_CTAS)
                     wr[k][j] = (w << 12) | atomicAdd(&s_hist[w], 1u);
                     s[k][j] = m.x + min(s[k][j], m.y);   // from here on: virtual coordinates
                     e[k][j] = m.x + min(e[k][j], m.y);
-                    c[k][j] = m.w;
                 }
             }
-        static_assert(PART_TILE <= 4096, "12 bits of rank");
+        static_assert(PART_STILE <= 4096, "12 bits of rank");
         __syncthreads();
         uint32_t g, ex;
         {   // exclusive scan of the histogram; every window with regions claims its run on the window's cursor
@@ -287,14 +298,13 @@ static __global__ void __launch_bounds__(PART_THREADS, PART_SCATTER_CTAS)
         }
         __syncthreads();
 #pragma unroll
-        for (int k = 0; k < PART_VEC; k++)
+        for (int k = 0; k < PART_SVEC; k++)
 #pragma unroll
             for (int j = 0; j < 4; j++)
                 if (wr[k][j] != 0xFFFFFFFFu) {
                     const uint32_t w = wr[k][j] >> 12, lp = s_hist[w] + (wr[k][j] & 0xFFFu);
                     s_se[lp] = make_uint2(s[k][j], e[k][j]);
                     s_w[lp] = (uint16_t)w;
-                    if (oc) s_c[lp] = c[k][j];
                 }
         s_delta[threadIdx.x] = g - ex;
         __syncthreads();
@@ -302,7 +312,6 @@ static __global__ void __launch_bounds__(PART_THREADS, PART_SCATTER_CTAS)
         for (uint32_t i = threadIdx.x; i < cnt; i += PART_THREADS) {
             const uint32_t gp = i + s_delta[s_w[i]];
             ose[gp] = s_se[i];
-            if (oc) oc[gp] = s_c[i];
         }
         __syncthreads();   // the sorted tile and the deltas are read: the next tile may overwrite them
     }
