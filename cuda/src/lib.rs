@@ -53,6 +53,9 @@ extern "C" {
                         stats: *mut u64) -> c_int;
     fn gffx_index_lines_info(idx: *const GffxIndex, digest: *mut u64, source: *mut c_int) -> c_int;
     fn gffx_free(p: *mut std::ffi::c_void);
+    // allocation-free join-pair count of a device-resident batch (no counterpart in the reference; include/gffx_b200.h)
+    pub fn gffx_count_pairs_noalloc(idx: *mut GffxIndex, d_chr: *const u32, d_start: *const u32, d_end: *const u32, n: u64, mode: c_int, invert: c_int,
+                                    d_out: *mut u64, stream: *mut std::ffi::c_void) -> c_int;
     fn gffx_counts_begin(idx: *mut GffxIndex, kind: c_int, out: *mut *mut GffxCounts) -> c_int;
     fn gffx_counts_add(st: *mut GffxCounts, chr: *const u32, start: *const u32, end: *const u32, n: u64, flags: u32) -> c_int;
     fn gffx_counts_write(st: *mut GffxCounts, out_path: *const c_char) -> c_int;

@@ -374,6 +374,12 @@ class TreeIndexData:
     def sync(self):
         _check(lib.gffx_index_sync(self._h))
 
+    def count_pairs_noalloc(self, d_chr: int, d_start: int, d_end: int, n: int, mode: int, invert: bool, d_out: int, stream: int = 0):
+        """gffx_count_pairs_noalloc: device pointers in (n sequence numbers, starts, ends), two uint64 out on the device
+        ([0] pairs, [1] bad sequence number seen); nothing is allocated, the call is asynchronous on `stream` (0: the
+        index's own, wait with sync()).  No counterpart in the reference (include/gffx_b200.h)."""
+        _check(lib.gffx_count_pairs_noalloc(self._h, d_chr, d_start, d_end, n, mode, 1 if invert else 0, d_out, stream or None))
+
     def write_ranges(self, ranges: np.ndarray, out_path: Optional[str]):
         r = np.ascontiguousarray(ranges, dtype=np.uint64)
         _check(lib.gffx_write_ranges(self._h, r.ctypes.data, r.shape[0], str(out_path).encode() if out_path else None))

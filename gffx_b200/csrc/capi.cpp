@@ -274,6 +274,16 @@ int gffx_index_sync(gffx_index* idx) {
         idx->engine()->sync();
     });
 }
+int gffx_count_pairs_noalloc(gffx_index* idx, const uint32_t* d_chr, const uint32_t* d_start, const uint32_t* d_end, uint64_t n, int mode, int invert,
+                             uint64_t* d_out, void* stream) {
+    return guard([&] {
+        need(idx, "idx"); need(d_out, "d_out");
+        if (n) { need(d_chr, "d_chr"); need(d_start, "d_start"); need(d_end, "d_end"); }
+        idx->engine()->count_pairs_noalloc(d_chr, d_start, d_end, n, mode, invert != 0, d_out, stream);
+    });
+}
+uint64_t gffx_noalloc_max_regions(void) { return gffx::Engine::noalloc_max_regions(); }
+uint64_t gffx_noalloc_max_roots(void) { return gffx::Engine::noalloc_max_roots(); }
 
 int gffx_result_wait(gffx_result* r) {
     if (!r) { g_err = "result must not be NULL"; return GFFX_E_ARG; }

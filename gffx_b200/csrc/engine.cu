@@ -12,6 +12,8 @@ namespace gffx {
 
 constexpr uint32_t WARN_CAP = 1u << 16;
 
+static unsigned char* noalloc_scratch_address();   // device address of the allocation-free entry point's static scratch (below)
+
 // The join kernel's dynamic shared memory on top of its static 26 KB exceeds the 48 KB default.  Function attributes belong to
 // the device (context), so every engine sets them for its own device when it is built (one process may hold an engine per GPU).
 template <int MODE, bool INV> static void wj_set_attrs() {
@@ -78,6 +80,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     set_kernel_attributes();
+    noalloc_scratch = noalloc_scratch_address();   // once per engine = per device, this device current
     for (DBuf* b : {&d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_wr_xw0, &d_wr_xlen, &d_wr_xoff, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
@@ -1187,6 +1190,96 @@ void Engine::shard_add(const uint32_t* chr, const uint32_t* start, const uint32_
 void Engine::shard_finish(IntersectResult* out) { impl_->ix_finish(out); }
 void Engine::wait(IntersectResult* out) { impl_->ix_wait(out); }
 void Engine::abandon(IntersectResult* out) { impl_->ix_abandon(out); }
+// ---- the allocation-free entry point (gffx_count_pairs_noalloc) ---------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (CUDA
+// graph capture, tight serving loops).  The join-pair count of ONE device-resident batch — K0 partition + K1 join, the same
+// kernels as gffx_query_features — with every intermediate (the bucketed regions, the window totals / cursors / offsets, the
+// per-root hit counters and flags) in this fixed static device array instead of the engine's grow-on-demand buffers.  Every
+// GPU that loads the library holds the array (10.6 MB) until exit.  All calls on a GPU share it and it keeps the last call's
+// contents: what must start at zero is cleared on the stream at the head of each call, and two calls that overlap on the GPU
+// (different streams, or two indexes on one device) race — serialise them.
+constexpr uint64_t NOALLOC_MAX_REGIONS = 1ull << 20;   // regions per call
+constexpr uint32_t NOALLOC_MAX_ROOTS = 1u << 18;       // root intervals of the index
+constexpr size_t NA_SE = 0;                                                                   // uint2[MAX_REGIONS + 4]
+constexpr size_t NA_CNT = NA_SE + (NOALLOC_MAX_REGIONS + 4) * 8;                              // u64[MAX_ROOTS + 2]
+constexpr size_t NA_HIT = NA_CNT + ((size_t)NOALLOC_MAX_ROOTS + 2) * 8;                       // u8[MAX_ROOTS + 16]
+constexpr size_t NA_TOT = NA_HIT + (size_t)NOALLOC_MAX_ROOTS + 16;                            // u32[PART_NB_MAX]
+constexpr size_t NA_CUR = NA_TOT + (size_t)PART_NB_MAX * 4;                                   // u32[PART_NB_MAX]
+constexpr size_t NA_POFF = NA_CUR + (size_t)PART_NB_MAX * 4;                                  // u32[PART_NB_MAX + 4]
+constexpr size_t NOALLOC_BYTES = (NA_POFF + ((size_t)PART_NB_MAX + 4) * 4 + 255) & ~(size_t)255;
+static_assert(NA_CNT % 16 == 0 && NA_HIT % 16 == 0 && NA_TOT % 16 == 0, "aligned parts");
+static __device__ __align__(256) unsigned char gffx_noalloc_scratch[NOALLOC_BYTES];
+
+// In host code the array's name is a stand-in, not a device address: the address is asked for once per device, with that
+// device current (the engine's constructor), and only that pointer is handed to kernels.
+static unsigned char* noalloc_scratch_address() {
+    unsigned char* ptr = nullptr;
+    GFFX_CUDA(cudaGetSymbolAddress((void**)&ptr, gffx_noalloc_scratch));
+    if (!ptr) throw Err(E_CUDA, "cudaGetSymbolAddress returned no address for the allocation-free scratch array");
+    return ptr;
+}
+
+template <int MODE, bool INV>
+static void launch_wj_noalloc(EngineImpl* E, unsigned char* S, uint64_t n, unsigned long long* n_pairs, uint32_t* err, cudaStream_t s) {
+    typedef unsigned long long ull;
+    const uint32_t* poff = reinterpret_cast<const uint32_t*>(S + NA_POFF);
+    const uint2* se = reinterpret_cast<const uint2*>(S + NA_SE);
+    uint8_t* hit = S + NA_HIT;
+    ull* cnt = reinterpret_cast<ull*>(S + NA_CNT);
+    const unsigned tiles = (unsigned)((n + WJ_TILE - 1) / WJ_TILE);
+    const FilterArrays F{};   // FILT = false: never read
+    const bool small = n < 64ull * std::max<uint32_t>(E->WC.n_win, 1);   // the choice of launch_wj
+    if (E->wj_force == 1 || (E->wj_force == 0 && small)) {
+        if (small) wj_count_kernel<MODE, INV, false, true><<<dim3(tiles, 16u), WJ_THREADS, WJ_DYN_SMEM, s>>>(E->WC, poff, se, n, hit, cnt, n_pairs, err, E->FR, F);
+        else wj_count_kernel<MODE, INV, false, false><<<dim3(tiles, 1u), WJ_THREADS, WJ_DYN_SMEM, s>>>(E->WC, poff, se, n, hit, cnt, n_pairs, err, E->FR, F);
+    } else {
+        wj_root_kernel<MODE, INV, false, false><<<tiles, WJ_THREADS, WJ_DYN_SMEM, s>>>(E->WC, poff, se, n, hit, cnt, n_pairs, err, E->FR, F, E->wj_tail_bins, E->XS);
+    }
+}
+
+uint64_t Engine::noalloc_max_regions() { return NOALLOC_MAX_REGIONS; }
+uint64_t Engine::noalloc_max_roots() { return NOALLOC_MAX_ROOTS; }
+
+void Engine::count_pairs_noalloc(const uint32_t* d_chr, const uint32_t* d_start, const uint32_t* d_end, uint64_t n, int mode, bool invert,
+                                 uint64_t* d_out, void* stream) {
+    EngineImpl* E = impl_.get();
+    if (mode < 0 || mode > 2) throw Err(E_ARG, "mode must be 0 (overlap), 1 (contained) or 2 (contains-region)");
+    if (n > NOALLOC_MAX_REGIONS)
+        throw Err(E_ARG, "gffx_count_pairs_noalloc: " + std::to_string(n) + " regions exceed the fixed scratch array's " + std::to_string(NOALLOC_MAX_REGIONS) +
+                             " per call: split the batch or use gffx_query_features");
+    if (E->wj_n_ent > NOALLOC_MAX_ROOTS)
+        throw Err(E_ARG, "gffx_count_pairs_noalloc: the index has " + std::to_string(E->wj_n_ent) + " root intervals, the fixed scratch array holds counters for " +
+                             std::to_string(NOALLOC_MAX_ROOTS) + ": use gffx_query_features");
+    if (!E->noalloc_scratch) throw Err(E_STATE, "the allocation-free scratch array has no device address on this GPU");
+    GFFX_CUDA(cudaSetDevice(E->dev));
+    cudaStream_t s = stream ? (cudaStream_t)stream : E->st;
+    unsigned char* S = E->noalloc_scratch;
+    GFFX_CUDA(cudaMemsetAsync(d_out, 0, 16, s));
+    if (n == 0 || (mode == 2 && invert) || E->wj_n_ent == 0) return;   // -I with overlap selects nothing (intersect.rs:161)
+    // the array keeps the previous call's contents: the window totals and the per-root counters / flags must start at zero
+    GFFX_CUDA(cudaMemsetAsync(S + NA_TOT, 0, (size_t)PART_NB_MAX * 4, s));
+    GFFX_CUDA(cudaMemsetAsync(S + NA_CNT, 0, ((size_t)E->wj_n_ent + 2) * 8, s));
+    GFFX_CUDA(cudaMemsetAsync(S + NA_HIT, 0, (size_t)E->wj_n_ent + 16, s));
+    uint32_t* tot = reinterpret_cast<uint32_t*>(S + NA_TOT);
+    uint32_t* cur = reinterpret_cast<uint32_t*>(S + NA_CUR);
+    uint32_t* poff = reinterpret_cast<uint32_t*>(S + NA_POFF);
+    const unsigned tiles = (unsigned)((n + PART_TILE - 1) / PART_TILE), stiles = (unsigned)((n + PART_STILE - 1) / PART_STILE);
+    part_count_kernel<<<std::min(tiles, (unsigned)(E->sm_count * PART_COUNT_CTAS)), PART_THREADS, PART_COUNT_SMEM, s>>>(E->WG, d_chr, d_start, (uint32_t)n, tot);
+    part_offsets_kernel<<<1, PART_NB_MAX, 0, s>>>(tot, E->WG.n_win + 1, (uint32_t)n, poff, cur);
+    part_scatter_kernel<<<std::min(stiles, (unsigned)(E->sm_count * PART_SCATTER_CTAS)), PART_THREADS, PART_SCATTER_SMEM, s>>>(
+        E->WG, d_chr, d_start, d_end, (uint32_t)n, cur, reinterpret_cast<uint2*>(S + NA_SE));
+    unsigned long long* n_pairs = reinterpret_cast<unsigned long long*>(d_out);
+    uint32_t* err = reinterpret_cast<uint32_t*>(d_out + 1);   // the kernels store 1 into the low word
+    switch (mode * 2 + (invert ? 1 : 0)) {
+        case 0: launch_wj_noalloc<0, false>(E, S, n, n_pairs, err, s); break;
+        case 1: launch_wj_noalloc<0, true>(E, S, n, n_pairs, err, s); break;
+        case 2: launch_wj_noalloc<1, false>(E, S, n, n_pairs, err, s); break;
+        case 3: launch_wj_noalloc<1, true>(E, S, n, n_pairs, err, s); break;
+        default: launch_wj_noalloc<2, false>(E, S, n, n_pairs, err, s); break;
+    }
+    GFFX_CUDA(cudaGetLastError());
+}
+
 void Engine::sync() {
     GFFX_CUDA(cudaSetDevice(impl_->dev));
     for (const EngineImpl::Lane& l : impl_->lanes)

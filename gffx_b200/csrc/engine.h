@@ -110,6 +110,13 @@ class Engine {
     // dst[i] = op over r < rows of src[r * stride + i], i < n_elems (device pointers on this engine's GPU, engine stream)
     void fold(void* dst, const void* src, uint32_t rows, uint64_t stride_elems, uint64_t n_elems, int op);
     void sync();
+    // join-pair count of a device-resident batch with NO allocation in the call: every intermediate lives in a fixed static
+    // device array (engine.cu: gffx_noalloc_scratch).  d_out[0] = pairs, d_out[1] != 0: a sequence number out of range.
+    // Asynchronous on `stream` (NULL: the engine's stream); overlapping calls on one GPU share the array and race.
+    void count_pairs_noalloc(const uint32_t* d_chr, const uint32_t* d_start, const uint32_t* d_end, uint64_t n, int mode, bool invert,
+                             uint64_t* d_out, void* stream);
+    static uint64_t noalloc_max_regions();
+    static uint64_t noalloc_max_roots();
 
     // depth (kind 0) / coverage (kind 1)
     void counts_begin(int kind);

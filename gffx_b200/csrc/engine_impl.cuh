@@ -84,6 +84,7 @@ class EngineImpl {
     cudaStream_t st = nullptr, st_copy = nullptr;  // st: every kernel; st_copy: host -> device chunks of the regions
     size_t dev_bytes = 0;
     int sm_count = 148;
+    unsigned char* noalloc_scratch = nullptr;   // device address of engine.cu's static scratch array on this engine's GPU
 
     std::vector<std::vector<uint32_t>> seq_sorted_roots;  // per seq: (start,end,fid) triples sorted by start (accessor)
 

@@ -289,6 +289,26 @@ int gffx_fold(gffx_index* idx, void* dst, const void* src, uint32_t rows, uint64
 int gffx_index_sync(gffx_index* idx);
 
 /* ------------------------------------------------------------------------------------------
+ * Allocation-free entry point.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The join-pair count of one device-resident batch — the number gffx_query_features reports as n_pairs, from
+ * the same partition and join kernels — with every intermediate in a fixed static device array inside the library
+ * (10.6 MB; every GPU that loads the library holds it until exit).  The call allocates and frees nothing, on the device
+ * or the host.
+ *   d_chr / d_start / d_end : n sequence numbers / starts / ends, device memory of the handle's GPU
+ *   mode 0 overlap, 1 contained (-c), 2 contains-region (-C); invert: -I
+ *   d_out   : two uint64 in device memory (8-byte aligned): [0] pairs, [1] non-zero when a region's sequence number lies
+ *             beyond the index's sequence list (the count is then that of the other regions)
+ *   stream  : a cudaStream_t, or NULL for the handle's stream (gffx_index_cuda_stream); the call is asynchronous on it
+ * Limits: n <= gffx_noalloc_max_regions() (1 048 576) and an index of at most gffx_noalloc_max_roots() (262 144) root
+ * intervals; beyond either the call returns GFFX_E_ARG with a message that says so.  Every call on a GPU shares the one
+ * array: calls that overlap on the GPU (two streams, two handles on one device) race and must be serialised by the caller. */
+int gffx_count_pairs_noalloc(gffx_index* idx, const uint32_t* d_chr, const uint32_t* d_start, const uint32_t* d_end, uint64_t n,
+                             int mode, int invert, uint64_t* d_out, void* stream);
+uint64_t gffx_noalloc_max_regions(void);
+uint64_t gffx_noalloc_max_roots(void);
+
+/* ------------------------------------------------------------------------------------------
  * Command level: the reference's run() functions (src/commands/intersect.rs:541-655,
  * src/commands/depth.rs:548-635, src/commands/coverage.rs:493-582) with the GPU engine inside.
  * ------------------------------------------------------------------------------------------ */
