@@ -396,11 +396,6 @@ void EngineImpl::build_lines() {
     // the rank space lives on the VIRTUAL sequences: a line's sequence, start and end move with its sequence's base
     const size_t n = L.size(), n_seqs = V.n_vseqs();
     std::vector<uint32_t> vS(n, 0), vE(n, 0), vseq(n, 0);
-    for (size_t i = 0; i < n; i++)
-        if (L.flags[i] & LN_I_OK) {
-            const VSeqMap::Seq& m = V.seq[L.iseq[i]];
-            vseq[i] = m.vseq; vS[i] = m.base + L.S[i]; vE[i] = m.base + L.E[i];
-        }
     // per sequence: sorted distinct S/E of usable lines (host threads: sequences are sorted side by side, longest first)
     const size_t T = (size_t)std::max(1, H->n_threads);
     auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
@@ -409,15 +404,54 @@ void EngineImpl::build_lines() {
         for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
         for (auto& t : th) t.join();
     };
+    // the columns that do not depend on the rank space cross PCIe from a helper thread while the host builds it (pageable
+    // copies occupy their calling thread)
+    d_ln_flags.ensure(std::max<size_t>(n, 1)); d_ln_blk.ensure(std::max<size_t>(n, 1) * 4); d_ln_type.ensure(std::max<size_t>(n, 1) * 4);
+    d_ln_off.ensure(std::max<size_t>(n, 1) * 8); d_ln_len.ensure(std::max<size_t>(n, 1) * 4);
+    cudaError_t up_err = cudaSuccess;
+    struct Joiner { std::thread t; ~Joiner() { if (t.joinable()) t.join(); } } early;
+    early.t = std::thread([&] {
+        auto put = [&](DBuf& b, const void* p, size_t bytes) {
+            if (up_err == cudaSuccess && bytes) up_err = cudaMemcpyAsync(b.p, p, bytes, cudaMemcpyHostToDevice, st_copy);
+        };
+        up_err = cudaSetDevice(dev);
+        put(d_ln_flags, L.flags.data(), n); put(d_ln_blk, L.blk.data(), n * 4); put(d_ln_type, L.type_id.data(), n * 4);
+        put(d_ln_off, L.off.data(), n * 8); put(d_ln_len, L.len.data(), n * 4);
+        if (up_err == cudaSuccess) up_err = cudaStreamSynchronize(st_copy);
+    });
+    const size_t n_chunks = n >= (1u << 16) ? T : 1;   // the line table in T pieces of consecutive lines
+    auto chunk_lo = [&](size_t c) { return n * c / n_chunks; };
+    std::vector<std::vector<uint32_t>> chunk_cnt(n_chunks, std::vector<uint32_t>(n_seqs, 0));   // values a chunk adds to each sequence's set
+    {
+        PhaseTimer t("  rank space: virtual coordinates");
+        run_parallel(n_chunks, [&](size_t c) {
+            std::vector<uint32_t>& cnt = chunk_cnt[c];
+            for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++)
+                if (L.flags[i] & LN_I_OK) {
+                    const VSeqMap::Seq& m = V.seq[L.iseq[i]];
+                    vseq[i] = m.vseq; vS[i] = m.base + L.S[i]; vE[i] = m.base + L.E[i];
+                    cnt[m.vseq] += 2;
+                }
+        });
+    }
     std::vector<std::vector<uint32_t>> xs(n_seqs);
     {
         PhaseTimer t("  rank space: coordinate sets (sort)");
-        std::vector<size_t> cnt(n_seqs, 0);
-        for (size_t i = 0; i < n; i++)
-            if (L.flags[i] & LN_I_OK) cnt[vseq[i]] += 2;
-        for (size_t s = 0; s < n_seqs; s++) xs[s].reserve(cnt[s]);
-        for (size_t i = 0; i < n; i++)
-            if (L.flags[i] & LN_I_OK) { xs[vseq[i]].push_back(vS[i]); xs[vseq[i]].push_back(vE[i]); }
+        // every chunk writes its values straight to its own place in the sequences' arrays
+        for (size_t s = 0; s < n_seqs; s++) {
+            size_t tot = 0;
+            for (size_t c = 0; c < n_chunks; c++) { const uint32_t k = chunk_cnt[c][s]; chunk_cnt[c][s] = (uint32_t)tot; tot += k; }
+            xs[s].resize(tot);
+        }
+        run_parallel(n_chunks, [&](size_t c) {
+            std::vector<uint32_t>& at = chunk_cnt[c];
+            for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++)
+                if (L.flags[i] & LN_I_OK) {
+                    uint32_t* v = xs[vseq[i]].data() + at[vseq[i]];
+                    v[0] = vS[i]; v[1] = vE[i];
+                    at[vseq[i]] += 2;
+                }
+        });
         std::vector<uint32_t> order(n_seqs);
         for (size_t s = 0; s < n_seqs; s++) order[s] = (uint32_t)s;
         std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return xs[a].size() > xs[b].size(); });
@@ -430,53 +464,93 @@ void EngineImpl::build_lines() {
             }
         });
     }
+    PhaseTimer* t_xd = new PhaseTimer("  rank space: X + directories");
     std::vector<RankSeq> seqs(n_seqs);
     std::vector<uint32_t> X, dir;
     uint32_t slot = 0;
-    for (size_t s = 0; s < n_seqs; s++) {
-        auto& v = xs[s];
-        RankSeq& r = seqs[s];
-        r.x0 = (uint32_t)X.size();
-        r.cnt = (uint32_t)v.size();
-        r.slot0 = slot;
-        slot += r.cnt + 1;
-        // a name listed twice in .sqs resolves to its LAST number (intersect.rs:622-625): regions carrying
-        // the earlier number never reach the line filter (such sequences share virtual sequences among themselves)
-        r.canon = V.v_canon[s];
-        r.dir_base = (uint32_t)dir.size();
-        if (v.empty()) { r.nb = 0; r.shift = 0; dir.push_back(0); continue; }
-        uint32_t maxv = v.back(), shift = 4;
-        while (((uint64_t)maxv >> shift) + 1 > std::max<uint64_t>(64, 2ull * v.size())) shift++;
-        r.shift = shift;
-        r.nb = (maxv >> shift) + 1;
-        uint32_t j = 0;
-        for (uint32_t b = 0; b <= r.nb; b++) {  // nb+1 entries: dir[b] = #(X < b<<shift)
-            const uint64_t lo = (uint64_t)b << shift;
-            while (j < v.size() && (uint64_t)v[j] < lo) j++;
-            dir.push_back(j);
+    {
+        size_t nx = 0, nd = 0;
+        for (size_t s = 0; s < n_seqs; s++) {   // layout first, so that the sequences (and pieces of the long ones) fill side by side
+            auto& v = xs[s];
+            RankSeq& r = seqs[s];
+            r.x0 = (uint32_t)nx;
+            r.cnt = (uint32_t)v.size();
+            r.slot0 = slot;
+            slot += r.cnt + 1;
+            // a name listed twice in .sqs resolves to its LAST number (intersect.rs:622-625): regions carrying
+            // the earlier number never reach the line filter (such sequences share virtual sequences among themselves)
+            r.canon = V.v_canon[s];
+            r.dir_base = (uint32_t)nd;
+            if (v.empty()) { r.nb = 0; r.shift = 0; nd += 1; continue; }
+            uint32_t maxv = v.back(), shift = 4;
+            while (((uint64_t)maxv >> shift) + 1 > std::max<uint64_t>(64, 2ull * v.size())) shift++;
+            r.shift = shift;
+            r.nb = (maxv >> shift) + 1;
+            nd += (size_t)r.nb + 1;   // nb+1 entries: dir[b] = #(X < b<<shift)
+            nx += v.size();
         }
-        X.insert(X.end(), v.begin(), v.end());
+        X.assign(nx + 8, 0u);   // rank_lb (filter.cuh) reads up to 4 entries past a bin
+        dir.assign(nd, 0u);
+        struct Piece { uint32_t s, b0, b1; };
+        std::vector<Piece> pieces;
+        constexpr uint32_t PIECE = 1u << 16;   // directory cells per task
+        for (size_t s = 0; s < n_seqs; s++)
+            for (uint32_t b0 = 0; b0 <= seqs[s].nb && !xs[s].empty(); b0 += PIECE) pieces.push_back(Piece{(uint32_t)s, b0, std::min(seqs[s].nb + 1, b0 + PIECE)});
+        std::atomic<size_t> next{0};
+        run_parallel(std::min(T, std::max<size_t>(pieces.size(), 1)), [&](size_t) {
+            for (size_t k; (k = next.fetch_add(1)) < pieces.size();) {
+                const Piece pc = pieces[k];
+                const auto& v = xs[pc.s];
+                const RankSeq& r = seqs[pc.s];
+                uint32_t* d = dir.data() + r.dir_base;
+                size_t j = (size_t)(std::lower_bound(v.begin(), v.end(), (uint64_t)pc.b0 << r.shift, [](uint32_t a, uint64_t c) { return (uint64_t)a < c; }) - v.begin());
+                const size_t j0 = j;
+                for (uint32_t b = pc.b0; b < pc.b1; b++) {
+                    const uint64_t lo = (uint64_t)b << r.shift;
+                    while (j < v.size() && (uint64_t)v[j] < lo) j++;
+                    d[b] = (uint32_t)j;
+                }
+                // the piece's values of X: from its first cell's rank up to the next piece's first cell's (the last piece: the rest)
+                const uint64_t lim = (uint64_t)pc.b1 << r.shift;
+                while (j < v.size() && (uint64_t)v[j] < lim) j++;
+                if (j > j0) memcpy(X.data() + r.x0 + j0, v.data() + j0, (j - j0) * 4);
+            }
+        });
     }
     f_slots = slot;
+    delete t_xd;
     {   // rootjoin.cuh: per window of the partition grid, its part of X and the fine-bin offsets into it
+        PhaseTimer t_xo("  rank space: window slices");
         const uint32_t n_win = WG.n_win, fsh = WG.shift - WR_FB;
         std::vector<uint32_t> xw0(std::max<uint32_t>(n_win, 1), 0), xlen(std::max<uint32_t>(n_win, 1), 0xFFFFFFFFu);
         std::vector<uint16_t> xoff((size_t)std::max<uint32_t>(n_win, 1) * WR_XOFF_STRIDE, 0);
-        for (size_t v = 0; v < n_seqs; v++) {
-            const auto& xv = xs[v];
-            for (uint32_t w = h_win0[v]; w < h_win0[v + 1]; w++) {
+        std::vector<uint32_t> win_v(n_win, 0);
+        for (size_t v = 0; v < n_seqs; v++)
+            for (uint32_t w = h_win0[v]; w < h_win0[v + 1]; w++) win_v[w] = (uint32_t)v;
+        std::atomic<uint32_t> next{0};
+        run_parallel(std::min<size_t>(T, std::max<uint32_t>(n_win, 1)), [&](size_t) {
+            for (uint32_t w; (w = next.fetch_add(1)) < n_win;) {
+                const uint32_t v = win_v[w];
+                const auto& xv = xs[v];
                 const uint64_t lo = (uint64_t)(w - h_win0[v]) << WG.shift;
                 const bool last = w + 1 == h_win0[v + 1];
-                auto below = [&](uint64_t c) { return (size_t)(std::lower_bound(xv.begin(), xv.end(), c, [](uint32_t a, uint64_t b) { return (uint64_t)a < b; }) - xv.begin()); };
-                const size_t i0 = below(lo), i1 = last ? xv.size() : below(lo + (1ull << WG.shift));
+                auto below_in = [&](uint64_t c, size_t a, size_t b) {
+                    return (size_t)(std::lower_bound(xv.begin() + (long)a, xv.begin() + (long)b, c, [](uint32_t x, uint64_t y) { return (uint64_t)x < y; }) - xv.begin());
+                };
+                const size_t i0 = below_in(lo, 0, xv.size()), i1 = last ? xv.size() : below_in(lo + (1ull << WG.shift), i0, xv.size());
                 xw0[w] = seqs[v].x0 + (uint32_t)i0;
                 if (i1 - i0 > WR_SLICE_CAP - 4 || i1 - i0 > 0xFFFFu) continue;   // keeps the global look-up
                 xlen[w] = (uint32_t)(i1 - i0);
                 uint16_t* row = xoff.data() + (size_t)w * WR_XOFF_STRIDE;
-                for (uint32_t b = 0; b < WR_NBF; b++) row[b] = (uint16_t)(std::min(below(lo + ((uint64_t)b << fsh)), i1) - i0);
+                size_t j = i0;   // the fine bins ascend: one walk over the window's part
+                for (uint32_t b = 0; b < WR_NBF; b++) {
+                    const uint64_t c = lo + ((uint64_t)b << fsh);
+                    while (j < i1 && (uint64_t)xv[j] < c) j++;
+                    row[b] = (uint16_t)(j - i0);
+                }
                 row[WR_NBF] = (uint16_t)(i1 - i0);
             }
-        }
+        });
         upload(d_wr_xw0, xw0, st);
         upload(d_wr_xlen, xlen, st);
         upload(d_wr_xoff, xoff, st);
@@ -485,35 +559,38 @@ void EngineImpl::build_lines() {
         XS.xlen = d_wr_xlen.as<uint32_t>();
         XS.xoff = d_wr_xoff.as<uint16_t>();
     }
-    X.insert(X.end(), 8, 0u);   // rank_lb (filter.cuh) reads up to 4 entries past a bin
     std::vector<uint32_t> iS(n, 0), iE(n, 0);
-    const size_t n_chunks = n >= (1u << 16) ? T : 1;
     PhaseTimer* t_rank = new PhaseTimer("  rank space: line ranks");
     run_parallel(n_chunks, [&](size_t c) {
-        const size_t i0 = n * c / n_chunks, i1 = n * (c + 1) / n_chunks;
-        for (size_t i = i0; i < i1; i++)
+        // lb through the sequence's directory: the cell of the value's bin bounds the search to the bin's few values
+        auto rank_of = [&](const RankSeq& r, uint32_t v) {
+            const uint32_t b = v >> r.shift;   // a line's coordinate is in the set: b < nb
+            const uint32_t* x = X.data() + r.x0;
+            const uint32_t lo = dir[r.dir_base + b], hi = dir[r.dir_base + b + 1];
+            return r.slot0 + (uint32_t)(std::lower_bound(x + lo, x + hi, v) - x);
+        };
+        for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++)
             if (L.flags[i] & LN_I_OK) {
-                const auto& v = xs[vseq[i]];
                 const RankSeq& r = seqs[vseq[i]];
-                iS[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), vS[i]) - v.begin());
-                iE[i] = r.slot0 + (uint32_t)(std::lower_bound(v.begin(), v.end(), vE[i]) - v.begin());
+                iS[i] = rank_of(r, vS[i]);
+                iE[i] = rank_of(r, vE[i]);
             }
     });
     delete t_rank;
     PhaseTimer t_up("  line table upload");
-    upload(d_ln_flags, L.flags, st);
-    upload(d_ln_blk, L.blk, st);
-    upload(d_ln_type, L.type_id, st);
     upload(d_ln_iseq, vseq, st);
     upload(d_ln_S, vS, st);
     upload(d_ln_E, vE, st);
     upload(d_ln_iS, iS, st);
     upload(d_ln_iE, iE, st);
-    upload(d_ln_off, L.off, st);
-    upload(d_ln_len, L.len, st);
     upload(d_fX, X, st);
     upload(d_fdir, dir, st);
     upload(d_fseqs, seqs, st);
+    GFFX_CUDA(cudaStreamSynchronize(st));
+    early.t.join();
+    GFFX_CUDA(up_err);
+    t_up.stop();
+    PhaseTimer t_al("  rank space: accumulators (alloc + clear)");
     const size_t ns = std::max<uint32_t>(f_slots, 1);
     d_A.ensure(ns * 8); d_B.ensure(ns * 8); d_PMX.ensure(ns * 8); d_SMN.ensure((ns + 1) * 8);
     d_Ms.ensure(ns * 2); d_Me.ensure(ns * 2); d_NS.ensure(ns * 8); d_NE.ensure(ns * 8);

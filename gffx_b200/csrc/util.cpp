@@ -11,7 +11,8 @@ namespace gffx {
 
 double PhaseTimer::now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 PhaseTimer::PhaseTimer(const char* w) : what(w), t0(0), on(getenv("GFFX_TIMING") != nullptr) { if (on) t0 = now(); }
-PhaseTimer::~PhaseTimer() { if (on) fprintf(stderr, "[gffx timing] %-28s %8.1f ms\n", what, (now() - t0) * 1e3); }
+void PhaseTimer::stop() { if (on) fprintf(stderr, "[gffx timing] %-28s %8.1f ms\n", what, (now() - t0) * 1e3); on = false; }
+PhaseTimer::~PhaseTimer() { stop(); }
 
 
 Mapped::~Mapped() {

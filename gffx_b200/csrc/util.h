@@ -55,6 +55,7 @@ struct PhaseTimer {
     bool on;
     static double now();
     explicit PhaseTimer(const char* w);
+    void stop();   // report now instead of at the end of the scope
     ~PhaseTimer();
 };
 
