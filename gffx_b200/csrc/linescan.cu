@@ -19,6 +19,8 @@
 
 #include <algorithm>
 #include <atomic>
+#include <functional>
+#include <string>
 #include <thread>
 
 #include "engine_impl.cuh"
@@ -205,11 +207,10 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
     GFFX_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     const size_t nb = H.blocks.size();
     const uint64_t n = H.gff_len;
-    DBuf text, bs, be, cnt, nl, na, l0, scratch, off, blk, tot;
-    std::vector<DBuf*> temps = {&bs, &be, &cnt, &nl, &na, &l0, &scratch, &off, &blk, &tot};
+    DBuf text, bs, be, cnt, nl, na, l0, scratch, off, blk, tot, obuf;
+    std::vector<DBuf*> temps = {&bs, &be, &cnt, &nl, &na, &l0, &scratch, &tot, &obuf};
     DBuf o_len, o_flags, o_S, o_E, o_iseq, o_fs, o_fe, o_toff, o_tlen, o_clen, o_ioff, o_ilen, o_ihash, t_hash, t_id, t_off, t_len, t_blob;
-    for (DBuf* b : {&o_len, &o_flags, &o_S, &o_E, &o_iseq, &o_fs, &o_fe, &o_toff, &o_tlen, &o_clen, &o_ioff, &o_ilen, &o_ihash, &t_hash, &t_id, &t_off, &t_len, &t_blob})
-        temps.push_back(b);
+    for (DBuf* b : {&t_hash, &t_id, &t_off, &t_len, &t_blob}) temps.push_back(b);   // the o_* columns are views into obuf
     struct Cleanup {
         std::vector<DBuf*>& v; cudaStream_t st; DBuf* text; bool keep_text = false;
         ~Cleanup() { for (DBuf* b : v) b->release(); if (!keep_text) text->release(); cudaStreamDestroy(st); }
@@ -217,39 +218,63 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
     // ---- the text: page-locked staging buffers filled by the host threads, copied as they fill -------------------------------
     {
         PhaseTimer t("    text -> HBM");
-        text.ensure(n + 32);
-        GFFX_CUDA(cudaMemsetAsync((uint8_t*)text.p + n, 0, 32, st));
-        constexpr size_t CH = 32u << 20;
-        uint8_t* stage[2] = {nullptr, nullptr};
-        cudaEvent_t ev[2];
-        for (int k = 0; k < 2; k++) { GFFX_CUDA(cudaMallocHost((void**)&stage[k], CH)); GFFX_CUDA(cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming)); }
-        const int T = std::max(1, std::min(threads, 16));
-        const int fd = (H.gff == H.gff_map.data() && !H.gff_path.empty()) ? ::open(H.gff_path.c_str(), O_RDONLY) : -1;
-        int k = 0;
-        for (uint64_t o = 0; o < n; o += CH, k ^= 1) {
-            const size_t m = (size_t)std::min<uint64_t>(CH, n - o);
-            GFFX_CUDA(cudaEventSynchronize(ev[k]));   // the copy that last used this buffer
-            std::vector<std::thread> th;
-            for (int t0 = 0; t0 < T; t0++)
-                th.emplace_back([&, t0] {
-                    const size_t a = m * (size_t)t0 / (size_t)T, z = m * (size_t)(t0 + 1) / (size_t)T;
-                    // from the file itself where there is one: pread copies page cache -> staging without faulting the mapping's
-                    // pages into this process one by one (50 ms -> 15 ms for 416 MB)
-                    size_t done = fd >= 0 ? 0 : z - a;
-                    while (fd >= 0 && done < z - a) {
-                        const ssize_t r = pread(fd, stage[k] + a + done, z - a - done, (off_t)(o + a + done));
-                        if (r <= 0) { done = 0; break; }
+        {
+            PhaseTimer ta("      device allocation");
+            text.ensure(n + 32);
+            GFFX_CUDA(cudaMemsetAsync((uint8_t*)text.p + n, 0, 32, st));
+            GFFX_CUDA(cudaStreamSynchronize(st));
+        }
+        // W workers, each with its own stream and two small page-locked buffers, take the text's chunks round robin: pread
+        // (page cache -> staging, no faulting of the mapping's pages into this process) and the copy of the previous chunk overlap
+        // within a worker, the workers' preads run side by side.  Small buffers: page-locking memory costs ~0.25 ms per MB.
+        constexpr size_t CH = 2u << 20;
+        const int W = std::max(1, std::min(threads, 6));
+        const bool from_file = H.gff == H.gff_map.data() && !H.gff_path.empty();
+        const uint64_t n_chunks = (n + CH - 1) / CH;
+        std::vector<cudaError_t> werr((size_t)W, cudaSuccess);
+        // ONE page-locked block for all the workers' buffers, from the library's pool (engine.cu: later results reuse it):
+        // a cudaMallocHost per buffer cost 3 ms apiece under the driver's lock, more than the copies themselves
+        size_t stage_cap = 0;
+        uint8_t* const stage_all = (uint8_t*)pinned_acquire((size_t)W * 2 * CH, &stage_cap);
+        struct StageGuard { void* p; size_t cap; ~StageGuard() { pinned_release(p, cap); } } stage_guard{stage_all, stage_cap};
+        std::vector<std::thread> workers;
+        for (int w = 0; w < W; w++)
+            workers.emplace_back([&, w] {
+                cudaError_t& e = werr[(size_t)w];
+                uint8_t* stage[2] = {stage_all + (size_t)(2 * w) * CH, stage_all + (size_t)(2 * w + 1) * CH};
+                cudaEvent_t ev[2] = {nullptr, nullptr};
+                cudaStream_t ws = nullptr;
+                const int fd = from_file ? ::open(H.gff_path.c_str(), O_RDONLY) : -1;
+                e = cudaSetDevice(device);
+                if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ws, cudaStreamNonBlocking);
+                for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
+                int k = 0;
+                PhaseTimer tw(w == 0 ? "      worker 0: chunks" : "");
+                if (w) tw.on = false;
+                for (uint64_t c = (uint64_t)w; c < n_chunks && e == cudaSuccess; c += (uint64_t)W, k ^= 1) {
+                    const uint64_t o = c * CH;
+                    const size_t m = (size_t)std::min<uint64_t>(CH, n - o);
+                    e = cudaEventSynchronize(ev[k]);   // the copy that last used this buffer
+                    if (e != cudaSuccess) break;
+                    size_t done = 0;
+                    while (fd >= 0 && done < m) {
+                        const ssize_t r = pread(fd, stage[k] + done, m - done, (off_t)(o + done));
+                        if (r <= 0) break;
                         done += (size_t)r;
                     }
-                    if (fd < 0 || done != z - a) memcpy(stage[k] + a, H.gff + o + a, z - a);
-                });
-            for (auto& x : th) x.join();
-            GFFX_CUDA(cudaMemcpyAsync((uint8_t*)text.p + o, stage[k], m, cudaMemcpyHostToDevice, st));
-            GFFX_CUDA(cudaEventRecord(ev[k], st));
-        }
-        GFFX_CUDA(cudaStreamSynchronize(st));
-        for (int j = 0; j < 2; j++) { cudaFreeHost(stage[j]); cudaEventDestroy(ev[j]); }
-        if (fd >= 0) ::close(fd);
+                    if (done != m) memcpy(stage[k], H.gff + o, m);
+                    e = cudaMemcpyAsync((uint8_t*)text.p + o, stage[k], m, cudaMemcpyHostToDevice, ws);
+                    if (e == cudaSuccess) e = cudaEventRecord(ev[k], ws);
+                }
+                if (ws) { const cudaError_t e2 = cudaStreamSynchronize(ws); if (e == cudaSuccess) e = e2; }
+                tw.stop();
+                for (int j = 0; j < 2; j++)
+                    if (ev[j]) cudaEventDestroy(ev[j]);
+                if (ws) cudaStreamDestroy(ws);
+                if (fd >= 0) ::close(fd);
+            });
+        for (auto& x : workers) x.join();
+        for (cudaError_t e : werr) GFFX_CUDA(e);
     }
     PhaseTimer t_k("    kernels + read-back");
     PhaseTimer* t_pre = new PhaseTimer("      blocks, names, counts");
@@ -297,9 +322,22 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
     RawLines R;
     const size_t L = (size_t)n_lines;
     PhaseTimer* t_al = new PhaseTimer("      output buffers");
-    off.ensure(std::max<size_t>(L, 1) * 8); blk.ensure(std::max<size_t>(L, 1) * 4);
-    for (DBuf* b : {&o_len, &o_S, &o_E, &o_iseq, &o_fs, &o_fe, &o_toff, &o_tlen, &o_clen, &o_ioff, &o_ilen}) b->ensure(std::max<size_t>(L, 1) * 4);
-    o_flags.ensure(std::max<size_t>(L, 1)); o_ihash.ensure(std::max<size_t>(L, 1) * 8);
+    // one allocation for the 15 output columns (a cudaMalloc each cost 2 ms apiece next to a 400 MB text allocation)
+    {
+        const size_t Lc = std::max<size_t>(L, 1);
+        struct Col { DBuf* b; size_t width; };
+        const Col cols[] = {{&off, 8}, {&o_ihash, 8}, {&blk, 4}, {&o_len, 4}, {&o_S, 4}, {&o_E, 4}, {&o_iseq, 4}, {&o_fs, 4}, {&o_fe, 4},
+                            {&o_toff, 4}, {&o_tlen, 4}, {&o_clen, 4}, {&o_ioff, 4}, {&o_ilen, 4}, {&o_flags, 1}};
+        size_t total = 0;
+        for (const Col& c : cols) total += (Lc * c.width + 255) & ~(size_t)255;
+        obuf.ensure(total);
+        size_t o = 0;
+        for (const Col& c : cols) {   // views into obuf: not owners (they are not in `temps`)
+            c.b->p = (uint8_t*)obuf.p + o;
+            c.b->cap = 0;
+            o += (Lc * c.width + 255) & ~(size_t)255;
+        }
+    }
     delete t_al;
     if (L) {
         ls_starts_kernel<<<warps_grid, LS_THREADS, 0, st>>>(text.as<uint8_t>(), B, l0.as<ull>(), off.as<ull>(), blk.as<uint32_t>());
@@ -312,13 +350,38 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
     // ---- read-back ---------------------------------------------------------------------------------------------------------------------
     PhaseTimer t_rb("      read-back");
     static_assert(sizeof(ull) == sizeof(uint64_t), "u64");
-    download(R.t.off, off, L, st); download(R.t.blk, blk, L, st); download(R.t.len, o_len, L, st); download(R.t.flags, o_flags, L, st);
-    download(R.t.S, o_S, L, st); download(R.t.E, o_E, L, st); download(R.t.iseq, o_iseq, L, st); download(R.t.fs, o_fs, L, st); download(R.t.fe, o_fe, L, st);
-    download(R.type_off, o_toff, L, st); download(R.type_len, o_tlen, L, st); download(R.chrom_len, o_clen, L, st);
-    download(R.id_off, o_ioff, L, st); download(R.id_len, o_ilen, L, st); download(R.id_hash, o_ihash, L, st);
-    download(R.blk_nlines, nl, nb, st); download(R.blk_nonascii, na, nb, st);
-    GFFX_CUDA(cudaStreamSynchronize(st));
+    GFFX_CUDA(cudaStreamSynchronize(st));   // the kernels
     GFFX_CUDA(cudaGetLastError());
+    {
+        // pageable destinations: a copy occupies its calling thread (driver staging) and the fresh vectors fault their pages in
+        // as they are written, so the columns come back on several threads / streams side by side
+        std::vector<std::function<void(cudaStream_t)>> jobs;
+        auto col = [&](auto& v, const DBuf& b, size_t cnt) { jobs.push_back([&v, &b, cnt](cudaStream_t s) { download(v, b, cnt, s); }); };
+        col(R.t.off, off, L); col(R.id_hash, o_ihash, L); col(R.t.blk, blk, L); col(R.t.len, o_len, L); col(R.t.flags, o_flags, L);
+        col(R.t.S, o_S, L); col(R.t.E, o_E, L); col(R.t.iseq, o_iseq, L); col(R.t.fs, o_fs, L); col(R.t.fe, o_fe, L);
+        col(R.type_off, o_toff, L); col(R.type_len, o_tlen, L); col(R.chrom_len, o_clen, L); col(R.id_off, o_ioff, L); col(R.id_len, o_ilen, L);
+        col(R.blk_nlines, nl, nb); col(R.blk_nonascii, na, nb);
+        const int W = std::max(1, std::min(threads, 6));
+        std::vector<std::string> werr((size_t)W);
+        std::vector<std::thread> workers;
+        std::atomic<size_t> next{0};
+        for (int w = 0; w < W; w++)
+            workers.emplace_back([&, w] {
+                cudaStream_t ws = nullptr;
+                try {
+                    GFFX_CUDA(cudaSetDevice(device));
+                    GFFX_CUDA(cudaStreamCreateWithFlags(&ws, cudaStreamNonBlocking));
+                    for (size_t k; (k = next.fetch_add(1)) < jobs.size();) {
+                        jobs[k](ws);
+                        GFFX_CUDA(cudaStreamSynchronize(ws));
+                    }
+                } catch (const std::exception& e) { werr[(size_t)w] = e.what(); }
+                if (ws) cudaStreamDestroy(ws);
+            });
+        for (auto& x : workers) x.join();
+        for (const std::string& e : werr)
+            if (!e.empty()) throw Err(E_CUDA, e);
+    }
     *out = std::move(R);
     *d_text = text.p;
     *d_text_cap = text.cap;
