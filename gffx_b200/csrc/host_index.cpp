@@ -364,6 +364,7 @@ void HostIndex::build_lines(int threads) {
 // their lines keep their places), then the three dictionaries, numbered by first appearance as scan_lines numbers them.
 void HostIndex::lines_from_raw(RawLines& R, int threads) {
     PhaseTimer t_all("    dictionaries (host)");
+    PhaseTimer t_na("      non-ASCII blocks");
     const size_t nb = blocks.size();
     LineTable& L = lines;
     L = std::move(R.t);
@@ -393,6 +394,8 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
             }
         }
     }
+    t_na.stop();
+    PhaseTimer t_tc("      type / chromosome dictionaries");
     // type / chromosome dictionaries: chunks of lines side by side, each with its own dictionary in order of appearance; the
     // chunks' dictionaries are merged in chunk order, which numbers every string by its first appearance in the file
     const size_t nparts = std::max<size_t>(1, std::min<size_t>((size_t)std::max(1, threads), total / 65536 + 1));
@@ -435,6 +438,8 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
             if (!d) { R.id_len[i] = 0; R.id_hash[i] = 0; }
         }
     });
+    t_tc.stop();
+    PhaseTimer t_id("      ID dictionary");
     number_ids(R.id_hash, g_off, R.id_len, threads);
 }
 
@@ -445,47 +450,77 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
 void HostIndex::number_ids(const std::vector<uint64_t>& g_hash, const std::vector<uint64_t>& g_off, const std::vector<uint32_t>& g_len, int threads) {
     LineTable& L = lines;
     const size_t total = L.size();
-    const size_t nshard = std::max<size_t>(1, std::min<size_t>((size_t)threads, 64));
+    const size_t T = (size_t)std::max(1, std::min(threads, 64));
+    const size_t nshard = T, nchunk = total >= (1u << 16) ? T : 1;
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
+        if (n_jobs <= 1 || T <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
+        std::vector<std::thread> th;
+        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
+        for (auto& t : th) t.join();
+    };
+    auto chunk_lo = [&](size_t c) { return total * c / nchunk; };
+    auto shard_of = [&](uint64_t h) { return (size_t)((h >> 32) % nshard); };
+    // the shards' line lists, in line order: chunks of lines count, then place, their lines side by side (every shard used to
+    // read the whole table twice)
+    std::vector<std::vector<uint32_t>> at(nchunk, std::vector<uint32_t>(nshard, 0));
+    run_parallel(nchunk, [&](size_t c) {
+        for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++)
+            if (L.flags[i] & LN_D_OK) at[c][shard_of(g_hash[i])]++;
+    });
+    std::vector<std::vector<uint32_t>> list(nshard);
+    for (size_t sh = 0; sh < nshard; sh++) {
+        uint32_t tot = 0;
+        for (size_t c = 0; c < nchunk; c++) { const uint32_t k = at[c][sh]; at[c][sh] = tot; tot += k; }
+        list[sh].resize(tot);
+    }
+    run_parallel(nchunk, [&](size_t c) {
+        for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++)
+            if (L.flags[i] & LN_D_OK) { const size_t sh = shard_of(g_hash[i]); list[sh][at[c][sh]++] = (uint32_t)i; }
+    });
     std::vector<uint32_t> first(total, NONE32);
-    auto dedup_shard = [&](size_t sh) {
-        size_t cnt = 0;
-        for (size_t i = 0; i < total; i++)
-            if ((L.flags[i] & LN_D_OK) && (g_hash[i] >> 32) % nshard == sh) cnt++;
+    run_parallel(nshard, [&](size_t sh) {
+        const std::vector<uint32_t>& mine = list[sh];
         size_t cap = 16;
-        while (cap < 2 * cnt + 2) cap <<= 1;
+        while (cap < 2 * mine.size() + 2) cap <<= 1;
         std::vector<uint32_t> tab(cap, 0);   // line number + 1
         const size_t mask = cap - 1;
-        for (size_t i = 0; i < total; i++) {
-            if (!(L.flags[i] & LN_D_OK)) continue;
+        for (const uint32_t i : mine) {
             const uint64_t h = g_hash[i];
-            if ((h >> 32) % nshard != sh) continue;
             size_t k = (size_t)h & mask;
             for (;; k = (k + 1) & mask) {
-                if (tab[k] == 0) { tab[k] = (uint32_t)i + 1; first[i] = (uint32_t)i; break; }
+                if (tab[k] == 0) { tab[k] = i + 1; first[i] = i; break; }
                 const size_t j = tab[k] - 1;
                 if (g_hash[j] == h && g_len[j] == g_len[i] && memcmp(gff + g_off[j], gff + g_off[i], g_len[i]) == 0) { first[i] = (uint32_t)j; break; }
             }
         }
-    };
-    if (nshard <= 1 || threads <= 1) { for (size_t k = 0; k < nshard; k++) dedup_shard(k); }
-    else {
-        std::vector<std::thread> th;
-        for (size_t k = 0; k < nshard; k++) th.emplace_back(dedup_shard, k);
-        for (auto& t : th) t.join();
-    }
+    });
+    // an ID's number = the rank of its first line among all first lines: counted per chunk, numbered side by side
+    std::vector<size_t> n_first(nchunk + 1, 0);
+    run_parallel(nchunk, [&](size_t c) {
+        size_t k = 0;
+        for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++) k += first[i] == (uint32_t)i;
+        n_first[c + 1] = k;
+    });
+    for (size_t c = 0; c < nchunk; c++) n_first[c + 1] += n_first[c];
     ids = IdTable();
     ids.base = gff;
+    ids.off.resize(n_first[nchunk]);
+    ids.len.resize(n_first[nchunk]);
     L.id.assign(total, NONE32);
-    for (size_t i = 0; i < total; i++) {   // first[i] <= i: one forward pass numbers the IDs and fills the column
-        if (first[i] == NONE32) continue;
-        if (first[i] == (uint32_t)i) {
-            L.id[i] = (uint32_t)ids.off.size();
-            ids.off.push_back(g_off[i]);
-            ids.len.push_back(g_len[i]);
-        } else {
-            L.id[i] = L.id[first[i]];
-        }
-    }
+    run_parallel(nchunk, [&](size_t c) {
+        size_t k = n_first[c];
+        for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++)
+            if (first[i] == (uint32_t)i) {
+                L.id[i] = (uint32_t)k;
+                ids.off[k] = g_off[i];
+                ids.len[k] = g_len[i];
+                k++;
+            }
+    });
+    run_parallel(nchunk, [&](size_t c) {   // first[i] < i: its number is in place since the pass above
+        for (size_t i = chunk_lo(c); i < chunk_lo(c + 1); i++)
+            if (first[i] != NONE32 && first[i] != (uint32_t)i) L.id[i] = L.id[first[i]];
+    });
 }
 
 // the host scanner proper: the lines of blocks [b0, b1) appended to *part (a Part), every rule of the reference's per-block text
