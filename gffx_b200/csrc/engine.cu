@@ -452,17 +452,53 @@ void EngineImpl::build_lines() {
                     at[vseq[i]] += 2;
                 }
         });
-        std::vector<uint32_t> order(n_seqs);
-        for (size_t s = 0; s < n_seqs; s++) order[s] = (uint32_t)s;
-        std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return xs[a].size() > xs[b].size(); });
-        std::atomic<size_t> next{0};
-        run_parallel(std::min(T, n_seqs), [&](size_t) {
-            for (size_t k; (k = next.fetch_add(1)) < n_seqs;) {
-                auto& v = xs[order[k]];
-                std::sort(v.begin(), v.end());
-                v.erase(std::unique(v.begin(), v.end()), v.end());
+        // a sequence's array is n_chunks pieces (chunk c's values end at chunk_cnt[c][s] now), each nearly sorted already when the
+        // file is: the pieces are sorted side by side, then merged pairwise in log2(n_chunks) rounds — a long sequence no longer
+        // occupies one thread for the whole sort
+        struct Job { uint32_t s, lo, mid, hi; };
+        auto run_jobs = [&](const std::vector<Job>& jobs, bool merge) {
+            std::atomic<size_t> next{0};
+            run_parallel(std::min(T, std::max<size_t>(jobs.size(), 1)), [&](size_t) {
+                for (size_t k; (k = next.fetch_add(1)) < jobs.size();) {
+                    uint32_t* v = xs[jobs[k].s].data();
+                    if (merge) std::inplace_merge(v + jobs[k].lo, v + jobs[k].mid, v + jobs[k].hi);
+                    else std::sort(v + jobs[k].lo, v + jobs[k].hi);
+                }
+            });
+        };
+        std::vector<std::vector<uint32_t>> cut(n_seqs);   // piece boundaries of every sequence
+        std::vector<Job> jobs;
+        for (size_t s = 0; s < n_seqs; s++) {
+            cut[s].push_back(0);
+            for (size_t c = 0; c < n_chunks; c++)
+                if (chunk_cnt[c][s] != cut[s].back()) cut[s].push_back(chunk_cnt[c][s]);
+            for (size_t k = 0; k + 1 < cut[s].size(); k++) jobs.push_back(Job{(uint32_t)s, cut[s][k], 0, cut[s][k + 1]});
+        }
+        std::sort(jobs.begin(), jobs.end(), [](const Job& a, const Job& b) { return a.hi - a.lo > b.hi - b.lo; });
+        run_jobs(jobs, false);
+        for (;;) {
+            jobs.clear();
+            for (size_t s = 0; s < n_seqs; s++) {
+                std::vector<uint32_t>& c = cut[s];
+                if (c.size() <= 2) continue;
+                std::vector<uint32_t> nc;
+                for (size_t k = 0; k + 2 < c.size(); k += 2) { jobs.push_back(Job{(uint32_t)s, c[k], c[k + 1], c[k + 2]}); nc.push_back(c[k]); }
+                if (c.size() % 2 == 0) nc.push_back(c[c.size() - 2]);   // an odd piece waits for the next round
+                nc.push_back(c.back());
+                c.swap(nc);
             }
-        });
+            if (jobs.empty()) break;
+            run_jobs(jobs, true);
+        }
+        {
+            std::atomic<size_t> next{0};
+            run_parallel(std::min(T, n_seqs), [&](size_t) {
+                for (size_t k; (k = next.fetch_add(1)) < n_seqs;) {
+                    auto& v = xs[k];
+                    v.erase(std::unique(v.begin(), v.end()), v.end());
+                }
+            });
+        }
     }
     PhaseTimer* t_xd = new PhaseTimer("  rank space: X + directories");
     std::vector<RankSeq> seqs(n_seqs);

@@ -223,15 +223,33 @@ void HostIndex::build_vseqs() {
         ext[r.seq] = std::max(ext[r.seq], root_ext[r.seq]);
     }
     const LineTable& L = lines;
-    for (size_t i = 0; i < L.size(); i++)
-        if (L.flags[i] & LN_I_OK) ext[L.iseq[i]] = std::max<uint64_t>(ext[L.iseq[i]], std::max(L.S[i], L.E[i]));
-    if (L.size()) {   // ID lines are compared with the regions routed to their block, whatever their own column 1 says (depth.rs:194-206)
+    {
+        // two passes over the line table, on the host threads when the per-thread copies of the extents are small
+        const size_t T = (L.size() >= (1u << 16) && n <= (1u << 16)) ? (size_t)std::max(1, std::min(n_threads, 32)) : 1;
+        std::vector<std::vector<uint64_t>> ext_t(T, std::vector<uint64_t>(T > 1 ? n : 0, 0));
         std::vector<uint32_t> blk_max(blocks.size(), 0);
-        for (size_t b = 0; b < blocks.size(); b++)
-            for (uint64_t i = blk_line0[b]; i < blk_line0[b + 1]; i++)
-                if (L.flags[i] & LN_D_OK) blk_max[b] = std::max(blk_max[b], L.fe[i]);
-        for (size_t i = 0; i < roots.size(); i++)
-            if (root_blk[i] != NONE32) ext[roots[i].seq] = std::max<uint64_t>(ext[roots[i].seq], blk_max[root_blk[i]]);
+        std::vector<std::thread> th;
+        auto work = [&](size_t t) {
+            uint64_t* e = T > 1 ? ext_t[t].data() : ext.data();
+            for (size_t i = L.size() * t / T; i < L.size() * (t + 1) / T; i++)
+                if (L.flags[i] & LN_I_OK) e[L.iseq[i]] = std::max<uint64_t>(e[L.iseq[i]], std::max(L.S[i], L.E[i]));
+            // ID lines are compared with the regions routed to their block, whatever their own column 1 says (depth.rs:194-206)
+            if (L.size())
+                for (size_t b = blocks.size() * t / T; b < blocks.size() * (t + 1) / T; b++)
+                    for (uint64_t i = blk_line0[b]; i < blk_line0[b + 1]; i++)
+                        if (L.flags[i] & LN_D_OK) blk_max[b] = std::max(blk_max[b], L.fe[i]);
+        };
+        if (T > 1) {
+            for (size_t t = 0; t < T; t++) th.emplace_back(work, t);
+            for (auto& x : th) x.join();
+            for (size_t t = 0; t < T; t++)
+                for (size_t c = 0; c < n; c++) ext[c] = std::max(ext[c], ext_t[t][c]);
+        } else {
+            work(0);
+        }
+        if (L.size())
+            for (size_t i = 0; i < roots.size(); i++)
+                if (root_blk[i] != NONE32) ext[roots[i].seq] = std::max<uint64_t>(ext[roots[i].seq], blk_max[root_blk[i]]);
     }
     std::vector<uint8_t> canon(n);
     for (size_t c = 0; c < n; c++) canon[c] = seq_num.at(seq_names[c]) == c ? 1 : 0;
