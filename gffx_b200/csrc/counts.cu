@@ -22,6 +22,7 @@ struct CountsState {
     DBuf r_chrom, r_start, r_end, r_value, r_flag, r_pos, o_id, o_chrom, o_start, o_end, o_value;
     int kind = -1;
     bool active = false;
+    bool exchanged = false;   // a sharded coverage job handed its accumulators out (counts_buffer_impl)
     uint64_t n_regions = 0;
     double ms = 0;
     uint32_t launches = 0;
@@ -154,14 +155,15 @@ void counts_begin_impl(EngineImpl* E, int kind) {
         GFFX_CUDA(cudaMemsetAsync(C->d_G.p, 0, ng * 4, st));
     } else {
         const size_t nw = std::max<uint64_t>(h.n_words, 1);
-        C->d_bits.ensure((nw + 4) * 8); C->d_diff.ensure(nw * 4); C->d_P.ensure(nw * 4);
+        C->d_bits.ensure((nw + 8) * 8); C->d_diff.ensure(nw * 4); C->d_P.ensure((nw / 8 + 2) * 4);
         C->d_routed.ensure(std::max<uint32_t>(E->n_blocks, 1));
-        GFFX_CUDA(cudaMemsetAsync(C->d_bits.p, 0, (nw + 4) * 8, st));   // + the tail of the last group of four words
+        GFFX_CUDA(cudaMemsetAsync(C->d_bits.p, 0, (nw + 8) * 8, st));   // + the tail of the last group of eight words
         GFFX_CUDA(cudaMemsetAsync(C->d_diff.p, 0, nw * 4, st));
         GFFX_CUDA(cudaMemsetAsync(C->d_routed.p, 0, std::max<uint32_t>(E->n_blocks, 1), st));
     }
     GFFX_CUDA(cudaStreamSynchronize(st));
     C->active = true;
+    C->exchanged = false;
 }
 
 static CountsDev make_dev(EngineImpl* E, CountsState* C) {
@@ -194,6 +196,7 @@ static CountsDev make_dev(EngineImpl* E, CountsState* C) {
     D.bits = C->d_bits.as<unsigned long long>();
     D.diff = C->d_diff.as<int>();
     D.blk_routed = C->d_routed.as<uint8_t>();
+    D.diff_used = C->d_err.as<uint32_t>() + 4;
     return D;
 }
 
@@ -296,10 +299,13 @@ void counts_finish_impl(EngineImpl* E, CountRows* rows) {
         F.S = C->d_S.as<uint32_t>(); F.E = C->d_E.as<uint32_t>(); F.G = C->d_G.as<uint32_t>();
     } else {
         const uint64_t nw = h.n_words;
+        // the difference array is only ever touched by regions longer than COV_DIRECT_WORDS words: while the job's flag says none
+        // came, its scan returns at once (a sharded job's arrays were combined with other shards': always scanned)
         C->launches += device_scan<int, OpSum, DiffLoad, CoverStore, false, true>(DiffLoad{C->d_diff.as<int>()}, CoverStore{C->d_bits.as<ull>()}, nw,
-                                                                                OpSum(), 0, C->d_scratch.as<int>(), nullptr, st);
-        C->launches += device_scan<uint32_t, OpSum, PopcLoad, PtrStore<uint32_t>, false, false>(
-            PopcLoad{C->d_bits.as<ull>()}, PtrStore<uint32_t>{C->d_P.as<uint32_t>()}, nw, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
+                                                                                OpSum(), 0, C->d_scratch.as<int>(), nullptr, st,
+                                                                                C->exchanged ? nullptr : C->d_err.as<uint32_t>() + 4);
+        C->launches += device_scan<uint32_t, OpSum, PopcLoad8, PtrStore<uint32_t>, false, false>(
+            PopcLoad8{C->d_bits.as<ull>()}, PtrStore<uint32_t>{C->d_P.as<uint32_t>()}, (nw + 7) / 8, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
         F.bits = C->d_bits.as<ull>(); F.P = C->d_P.as<uint32_t>(); F.blk_routed = C->d_routed.as<uint8_t>();
     }
     RowArrays R{C->r_chrom.as<uint32_t>(), C->r_start.as<uint32_t>(), C->r_end.as<uint32_t>(), C->r_value.as<ull>(), C->r_flag.as<uint8_t>()};
@@ -351,6 +357,7 @@ bool counts_buffer_impl(EngineImpl* E, uint32_t k, void** dptr, uint64_t* n_elem
     } else {
         v[0] = {C->d_bits.p, h.n_words, RED_OR_U64};  // covered bases (partial words)
         v[1] = {C->d_diff.p, h.n_words, RED_SUM_I32}; // fully covered words, difference array
+        C->exchanged = true;                          // other shards' long regions arrive through it
         v[2] = {C->d_routed.p, E->n_blocks, RED_MAX_U8};
     }
     if (k >= 3) return false;

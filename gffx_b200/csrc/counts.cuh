@@ -60,6 +60,7 @@ struct CountsDev {
     uint32_t* G;
     unsigned long long* bits;
     int* diff;
+    uint32_t* diff_used;   // set once a region went to the difference array: its scan is skipped while this is 0 (reads never get there)
     uint8_t* blk_routed;
 };
 
@@ -147,6 +148,7 @@ __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp
         if ((__ldcg(D.bits + wb) & mb) != mb) atomicOr(D.bits + wb, mb);
         atomicAdd(D.diff + wa + 1, 1);
         atomicAdd(D.diff + wb, -1);
+        if (__ldcg(D.diff_used) == 0u) *D.diff_used = 1u;
     }
 }
 
@@ -330,9 +332,17 @@ struct CoverStore {  // inclusive prefix of the word difference array > 0  =>  t
         if (v > 0) bits[i] = ~0ull;
     }
 };
-struct PopcLoad {
-    const unsigned long long* bits;
-    __device__ uint32_t operator()(uint64_t i) const { return (uint32_t)__popcll(bits[i]); }
+// covered bases per GROUP of eight bitmap words (one 64-byte line): the prefix over groups is an eighth of a per-word prefix
+// to write and to read back, and a query adds the few words of its own group, which share the line of the word it reads anyway
+struct PopcLoad8 {
+    const unsigned long long* bits;   // padded to whole groups
+    __device__ uint32_t operator()(uint64_t g) const {
+        const ulonglong2* p = reinterpret_cast<const ulonglong2*>(bits + 8 * g);
+        uint32_t c = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) { const ulonglong2 v = p[k]; c += (uint32_t)__popcll(v.x) + (uint32_t)__popcll(v.y); }
+        return c;
+    }
 };
 
 struct CountsFin {
@@ -360,7 +370,7 @@ struct CountsFin {
     const uint32_t* E;
     const uint32_t* G;
     const unsigned long long* bits;
-    const uint32_t* P;
+    const uint32_t* P;          // exclusive prefix of the covered bases per group of eight words
     const uint8_t* blk_routed;
     uint32_t n_ids;
 };
@@ -375,8 +385,18 @@ struct RowArrays {
 
 __device__ __forceinline__ uint32_t covered_before(const CountsFin& F, const CovSpace& cv, uint32_t x) {
     const uint32_t p = x - cv.lo;
-    const unsigned long long w = cv.word0 + (p >> 6);
-    return F.P[w] + (uint32_t)__popcll(F.bits[w] & ((1ull << (p & 63)) - 1ull));
+    const unsigned long long w = cv.word0 + (p >> 6), g = w >> 3;
+    const ulonglong2* q = reinterpret_cast<const ulonglong2*>(F.bits + 8 * g);
+    uint32_t c = F.P[g];
+    const uint32_t k = (uint32_t)(w & 7u);   // whole words of the group below w, then the bits of w below x
+#pragma unroll
+    for (uint32_t i = 0; i < 4; i++) {
+        const ulonglong2 v = q[i];
+        const uint32_t a = 2 * i, b = 2 * i + 1;
+        c += (uint32_t)__popcll(a < k ? v.x : a == k ? v.x & ((1ull << (p & 63)) - 1ull) : 0ull);
+        c += (uint32_t)__popcll(b < k ? v.y : b == k ? v.y & ((1ull << (p & 63)) - 1ull) : 0ull);
+    }
+    return c;
 }
 
 // one thread per ID: reduce its units (ascending block order) into one row
