@@ -489,6 +489,43 @@ def e2e_sync(c, passes, host_sets, steps):
     return allmax(c, time.perf_counter() - t0), n_ranges
 
 
+def e2e_queued(c, passes, host_sets, steps):
+    """the same host-in / host-out passes QUEUED (GFFX_F_ASYNC without GFFX_F_DEVICE_INPUT / GFFX_F_NO_HOST_COPY): a pass is
+    waited for after the next one has been queued, so one pass's ranges travel to the host while the next pass's regions travel
+    to the device (the two directions of the link).  Every result is waited for and its host ranges looked at inside the
+    timed region.  -> (seconds, ranges)"""
+    import torch
+
+    from gffx_b200 import _lib
+
+    F = _lib.F_PAIRS_ON_DEVICE | _lib.F_ASYNC
+
+    def settle(p):
+        r = p.wait(copy=False)
+        n = r.n_ranges
+        if n:
+            assert int(r.ranges[n - 1, 1]) > 0   # the host copy is there
+        r.close()
+        return n
+
+    def run(k):
+        n, prev = 0, None
+        for _ in range(k):
+            for (name, mode, inv, entire, types), regs in zip(passes, host_sets):
+                p = c.idx.intersect(regs, mode, inv, entire, types, flags=F)
+                if prev is not None:
+                    n += settle(prev)
+                prev = p
+        return n + settle(prev)
+
+    run(1)
+    c.barrier()
+    t0 = time.perf_counter()
+    n_ranges = run(steps)
+    torch.cuda.synchronize()
+    return allmax(c, time.perf_counter() - t0), n_ranges
+
+
 def h2d_ceiling(c, host_sets):
     """what the box can move: every rank copies its pinned region sets to its GPU at the same time, nothing else running"""
     import torch
@@ -570,7 +607,12 @@ def bench_intersect(c):
     n_steps = loops * args.steps
     acc = staged_sync(c, SWEEP, dev_sets, args.steps)
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    e2e_s, ranges_e2e = e2e_sync(c, SWEEP, host_sets, e2e_steps)
+    e2e_sync_s, ranges_e2e = e2e_sync(c, SWEEP, host_sets, e2e_steps)
+    e2e_s, e2e_api = e2e_sync_s, "gffx_intersect (C ABI) with pinned host region arrays; byte ranges copied back"
+    if c.world == 1:   # one GPU: the same calls queued, two in flight (a sharded job exchanges flags between add and finish and stays synchronous)
+        e2e_s, ranges_q = e2e_queued(c, SWEEP, host_sets, e2e_steps)
+        assert ranges_q == ranges_e2e
+        e2e_api = "gffx_intersect (C ABI) with GFFX_F_ASYNC, pinned host region arrays in, byte ranges copied back to page-locked host memory, two jobs in flight; every result waited for and read inside the timed region"
     ceiling = h2d_ceiling(c, host_sets)
     pairs_total, launches_total, ranges_sum = allsum(c, [sum(a["pairs"] for a in tally.values()), sum(a["launches"] for a in tally.values()), ranges_e2e])
     c.dev_sets, c.host_sets = dev_sets, host_sets
@@ -594,8 +636,10 @@ def bench_intersect(c):
         "roofline": roofline, "clocks": clocks,
         "e2e": {"value": c.world * len(PASSES) * Q * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3, "h2d_ceiling_gbs": ceiling["gbs_aggregate"], "h2d_ceiling": ceiling,
-                "host_affinity": c.affinity,
-                "api": "gffx_intersect (C ABI) with pinned host region arrays; byte ranges copied back"},
+                "host_affinity": c.affinity, "api": e2e_api,
+                "synchronous": {"value": c.world * len(PASSES) * Q * e2e_steps / e2e_sync_s, "ms_per_step": e2e_sync_s / e2e_steps * 1e3,
+                                "d2h_bytes_per_step": int(16 * ranges_sum / c.world / e2e_steps) + 64 * len(PASSES),
+                                "note": "the same passes as plain synchronous gffx_intersect calls, one after the other"}},
         "gpu_launches": int(launches_total),
     }
     return line

@@ -98,20 +98,23 @@ class Result:
 
 
 class PendingResult:
-    """A GFFX_F_ASYNC job that has been queued on the engine's stream: wait() blocks until its counters have arrived and
-    returns the Result (device outputs only).  The region tensors are kept alive until then."""
+    """A GFFX_F_ASYNC job that has been queued on the engine's stream: wait() blocks until its counters (and, unless the job
+    was queued with GFFX_F_NO_HOST_COPY, the host copy of its ranges) have arrived and returns the Result.  The region arrays
+    are kept alive until then."""
 
     def __init__(self, h, keep):
         self._h, self._keep = h, keep
 
-    def wait(self) -> "Result":
+    def wait(self, copy: bool = True) -> "Result":
+        """copy=False: `ranges` (a job queued without GFFX_F_NO_HOST_COPY) is a view of the result's page-locked buffer,
+        valid until Result.close()"""
         h, self._h = self._h, None
         rc = lib.gffx_result_wait(h)
         if rc != 0:
             lib.gffx_result_free(h)
             raise GffxError(rc, _lib.last_error())
         self._keep = None
-        return _take_result(h, True)
+        return _take_result(h, copy)
 
     def close(self):
         if self._h is not None:

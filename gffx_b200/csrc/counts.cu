@@ -236,6 +236,8 @@ void counts_add_impl(EngineImpl* E, const uint32_t* chr, const uint32_t* start, 
     } else {
         const uint32_t* src[3] = {chr, start, end};
         for (int k = 0; k < 3; k++) E->d_q[k].ensure(n * 4);
+        // a queued intersect job of this lane may still be reading its staged regions
+        if (E->lanes[E->lane_active].ev_done) GFFX_CUDA(cudaStreamWaitEvent(E->st_copy, E->lanes[E->lane_active].ev_done, 0));
         while (E->ev_copy.size() < n_chunks) {
             cudaEvent_t e;
             GFFX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));

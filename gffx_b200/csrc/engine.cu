@@ -52,6 +52,15 @@ __global__ void clear_job_kernel(uint4* __restrict__ small, uint4* __restrict__ 
     for (uint32_t k = i; k < n_cnt16; k += gridDim.x * blockDim.x) cnt[k] = z;
 }
 
+// the finished range list -> the result's page-locked host buffer (device-accessible: unified addressing), exactly as many as the
+// job's counter says: a queued job's host copy without the host knowing the count (a cudaMemcpyAsync would need it)
+__global__ void ranges_to_host_kernel(const ulonglong2* __restrict__ src, ulonglong2* __restrict__ dst_host, const unsigned long long* __restrict__ n_ptr,
+                                      unsigned long long cap) {
+    const unsigned long long n = min(*n_ptr, cap);
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x)
+        dst_host[i] = src[i];
+}
+
 __global__ void fill_u64_kernel(unsigned long long* p, uint64_t n, unsigned long long v) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = v;
@@ -150,14 +159,17 @@ EngineImpl::~EngineImpl() {
     for (auto& x : ev_gather) if (x) cudaEventDestroy(x);
     for (auto& x : ev_bed) if (x) cudaEventDestroy(x);
     if (st_copy) cudaStreamDestroy(st_copy);
-    for (Lane& l : lanes)
+    for (Lane& l : lanes) {
+        if (l.ev_done) cudaEventDestroy(l.ev_done);
         if (l.st) cudaStreamDestroy(l.st);
+    }
 }
 
 // ---- job lanes (engine_impl.cuh) ------------------------------------------------------------------------------------
 std::vector<DBuf*> EngineImpl::lane_bufs() {
     return {&d_wj_hit, &d_wj_cnt, &d_wj_off, &d_blk_sel, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
-            &d_poff, &d_ptot, &d_pcur, &d_bse, &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn};
+            &d_poff, &d_ptot, &d_pcur, &d_bse, &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn,
+            &d_q[0], &d_q[1], &d_q[2]};   // a queued job's staged regions stay put while the next job's cross PCIe
 }
 
 DBuf& EngineImpl::lane_buf(int lane, DBuf* member) {
@@ -827,7 +839,7 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
     d_poff.ensure((size_t)std::max<uint32_t>(n_chunks, 1) * (WG.n_win + 2) * 4);
     jb.async = flags & 32u;   // GFFX_F_ASYNC: the counters are read back into a slot of the engine's ring, the caller waits later
     if (jb.async) {
-        if (jb.want_pairs_host || !jb.no_host) throw Err(E_ARG, "GFFX_F_ASYNC leaves every output on the device: combine it with GFFX_F_NO_HOST_COPY, not GFFX_F_WANT_PAIRS");
+        if (jb.want_pairs_host) throw Err(E_ARG, "GFFX_F_ASYNC does not copy pairs to the host: use GFFX_F_PAIRS_ON_DEVICE, not GFFX_F_WANT_PAIRS");
         if (jb.stage_events) throw Err(E_ARG, "GFFX_F_ASYNC and GFFX_F_STAGE_TIMES exclude each other");
         jb.slot = slot_acquire();
     }
@@ -1058,7 +1070,25 @@ void EngineImpl::ix_finish(IntersectResult* out) {
         AsyncSlot& S = slots[jb.slot];
         GFFX_CUDA(cudaMemcpyAsync(S.h, d_small.p, 64, cudaMemcpyDeviceToHost, st));
         GFFX_CUDA(cudaMemcpyAsync(S.h + ASYNC_WARN_OFF, d_warn.p, ASYNC_WARN_CAP * 4, cudaMemcpyDeviceToHost, st));
+        if (!jb.no_host && !nothing && !jb.join_only) {
+            // the host copy of the ranges rides behind the job: their number is not known on the host yet, so a kernel stores the
+            // list (as long as the job's counter says) into the result's page-locked buffer, sized for the upper bound (every
+            // line / every block); wait() trims it.  The next queued job's regions cross PCIe the other way meanwhile.
+            const uint64_t cap = jb.match_only ? LA.n : n_blocks;
+            if (cap) {
+                out->ranges.resize(cap * 2);
+                ranges_to_host_kernel<<<(unsigned)sm_count * 2, 256, 0, st>>>(d_ranges.as<ulonglong2>(), reinterpret_cast<ulonglong2*>(out->ranges.data()),
+                                                                            small + (jb.match_only ? 5 : 1), cap);
+                out->launches++;
+                out->pend.ranges_cap = cap;
+            }
+        }
         GFFX_CUDA(cudaEventRecord(S.ev_end, st));
+        {
+            Lane& ln = lanes[lane_active];
+            if (!ln.ev_done) GFFX_CUDA(cudaEventCreateWithFlags(&ln.ev_done, cudaEventDisableTiming));
+            GFFX_CUDA(cudaEventRecord(ln.ev_done, st));
+        }
         {
             cudaError_t le = cudaGetLastError();
             if (le != cudaSuccess) { S.state = 0; throw Err(E_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(le)); }
@@ -1178,11 +1208,29 @@ void EngineImpl::ix_wait(IntersectResult* out) {
     cudaEventElapsedTime(&ms, S.ev_start, S.ev_end);
     out->kernel_ms = ms;
     S.state = 0;   // the slot's bytes are read below, before any other call on this handle can take it (one thread per handle)
-    read_counters(out, S.h, (const uint32_t*)(S.h + ASYNC_WARN_OFF));
+    const uint64_t cap = out->pend.ranges_cap;
+    out->pend.ranges_cap = 0;
+    try {
+        read_counters(out, S.h, (const uint32_t*)(S.h + ASYNC_WARN_OFF));
+    } catch (...) {
+        out->ranges.release();
+        throw;
+    }
+    if (cap) {   // the copy has landed (it preceded the slot's event): keep the ranges that exist
+        if (out->n_ranges > cap) throw Err(E_STATE, "more ranges than the list's upper bound (internal)");
+        if (out->n_ranges) out->ranges.resize(out->n_ranges * 2);   // shrinks in place
+        else out->ranges.release();
+    }
 }
 
 void EngineImpl::ix_abandon(IntersectResult* out) {
     if (out->pending_slot < 0) return;
+    if (out->pend.ranges_cap || out->pend.host_in) {   // the result's page-locked buffer goes back to the pool with the result, the caller's region
+        // arrays are free to go after this call: let the copies into / out of them finish first
+        cudaSetDevice(dev);
+        cudaEventSynchronize(slots[(size_t)out->pending_slot].ev_end);
+        out->pend.ranges_cap = 0;
+    }
     slots[(size_t)out->pending_slot].state = 2;
     out->pending_slot = -1;
 }
@@ -1193,7 +1241,7 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     if (n >= (1ull << 31)) throw Err(E_ARG, "more than 2^31-1 regions in one call: split the batch");
     GFFX_CUDA(cudaSetDevice(dev));
     const bool dev_in = flags & 1u;  // GFFX_F_DEVICE_INPUT
-    if ((flags & 32u) && !dev_in) throw Err(E_ARG, "GFFX_F_ASYNC needs device-resident regions (GFFX_F_DEVICE_INPUT)");
+    // GFFX_F_ASYNC with host regions: the arrays must stay valid (and should be page-locked) until the result has been waited for
     // host input: the copy is cut into chunks so that chunk i+1 crosses PCIe while chunk i is partitioned and joined
     uint32_t n_chunks = 1;
     if (!dev_in && n >= (1u << 21)) n_chunks = (uint32_t)std::min<uint64_t>(8, n >> 20);
@@ -1207,6 +1255,8 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     } else if (n) {
         const uint32_t* src[3] = {chr, start, end};
         for (int k = 0; k < 3; k++) d_q[k].ensure(n * 4);
+        // the lane's previous queued job may still be reading its staged regions
+        if (lanes[lane_active].ev_done) GFFX_CUDA(cudaStreamWaitEvent(st_copy, lanes[lane_active].ev_done, 0));
         while (ev_copy.size() < n_chunks) {
             cudaEvent_t e;
             GFFX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -1225,6 +1275,7 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
         }
     }
     ix_finish(out);
+    if (!dev_in && out->pending_slot >= 0) out->pend.host_in = true;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -47,6 +47,8 @@ struct PendingInfo {   // what turns a job's counter block into result fields (k
     unsigned long long pair_cap = 0;
     const uint32_t* d_pairs = nullptr;   // the pair buffer of the job's lane
     int lane = 0;
+    bool host_in = false;                // asynchronous job whose regions were host arrays: they are read until the job's copies have run
+    uint64_t ranges_cap = 0;             // asynchronous job with a host copy: ranges in flight to IntersectResult::ranges (an upper bound)
 };
 
 struct IntersectResult {

@@ -136,6 +136,7 @@ class EngineImpl {
         cudaStream_t st = nullptr;
         uint32_t epoch = 0, epoch8 = 0;
         bool ready = false;
+        cudaEvent_t ev_done = nullptr;   // end of the lane's last asynchronous job: its staged regions may be overwritten after it
     };
     Lane lanes[2];
     int lane_active = 0, lane_next = 0, lane_last = 0, n_lanes = 2;

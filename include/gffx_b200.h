@@ -181,7 +181,12 @@ int gffx_intersect(gffx_index* idx, const uint32_t* chr, const uint32_t* start, 
  * next job is queued.  Between gffx_shard_begin and gffx_shard_finish of a queued job gffx_index_cuda_stream reports the
  * job's lane.  If the pairs outgrow the buffer
  * sized from earlier jobs, gffx_result_n_pairs is exact but gffx_result_pairs_device is NULL (run that pass synchronously).
- * At most 32 results may be pending per handle; gffx_result_free on a pending result abandons it. */
+ * At most 32 results may be pending per handle; gffx_result_free on a pending result abandons it.
+ * Host arrays work too (r02): without GFFX_F_DEVICE_INPUT the regions are copied from the caller's arrays behind the call —
+ * they must stay valid and unchanged until the wait (page-locked arrays make the copy asynchronous) — and without
+ * GFFX_F_NO_HOST_COPY the host copy of the ranges follows the job into the result's page-locked buffer, trimmed at the wait;
+ * with two jobs in flight one job's ranges travel to the host while the next job's regions travel to the device.  Pairs are
+ * never copied to the host behind a queued job (GFFX_F_WANT_PAIRS is refused). */
 int gffx_result_wait(gffx_result* r);
 int gffx_result_pending(const gffx_result* r);   /* 1 while the counters of a GFFX_F_ASYNC job have not been read */
 uint64_t gffx_result_n_queries(const gffx_result* r);

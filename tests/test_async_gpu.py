@@ -44,6 +44,40 @@ def test_queued_jobs_equal_synchronous_calls(quirk):
         assert r.kernel_ms > 0 and r.launches > 0
 
 
+def test_queued_jobs_with_host_regions_and_host_ranges(gffx, quirk):
+    """GFFX_F_ASYNC without GFFX_F_NO_HOST_COPY and without GFFX_F_DEVICE_INPUT: host arrays in, the host copy of the ranges
+    behind the job; two jobs in flight, so one job's ranges travel back while the next job's regions travel in"""
+    idx = quirk
+    FH = _lib.F_ASYNC | _lib.F_PAIRS_ON_DEVICE
+    sets = [mixed_regions(idx, 300 + k, 4000) for k in range(4)]
+    cases = [(m, i, e, t) for (m, i) in MODES for (e, t) in ((False, None), (True, None), (False, "gene,mRNA,exon"))]
+    want = [idx.intersect(sets[k % 4], m, i, e, t) for k, (m, i, e, t) in enumerate(cases)]
+
+    def same(r, w, what):
+        assert (r.n_pairs, r.n_roots, r.n_ranges, r.bytes_out) == (w.n_pairs, w.n_roots, w.n_ranges, w.bytes_out), what
+        if w.n_ranges:
+            assert r.ranges is not None and np.array_equal(np.asarray(r.ranges), w.ranges), what
+        r.close()
+
+    for copy in (True, False):
+        pend = []
+        for k, (m, i, e, t) in enumerate(cases):
+            pend.append((k, idx.intersect(sets[k % 4], m, i, e, t, flags=FH)))
+            if len(pend) > 2:
+                j, p = pend.pop(0)
+                same(p.wait(copy=copy), want[j], cases[j])
+        for j, p in pend:
+            same(p.wait(copy=copy), want[j], cases[j])
+    # a result dropped while its ranges are in flight, then the lanes are used again
+    for _ in range(3):
+        idx.intersect(sets[0], 0, False, False, None, flags=FH).close()
+    p = idx.intersect(sets[1], 0, False, False, None, flags=FH)
+    w = idx.intersect(sets[1], 0, False, False, None)       # a synchronous call between queue and wait
+    same(p.wait(), w, "after abandoned results")
+    with pytest.raises(gffx.GffxError):                      # pairs are not copied to the host behind a queued job
+        idx.intersect(sets[0], 0, False, False, None, flags=FH | _lib.F_WANT_PAIRS)
+
+
 def test_last_jobs_device_outputs_are_readable(quirk):
     idx = quirk
     regs = mixed_regions(idx, 77, 3000)
@@ -83,8 +117,6 @@ def test_error_surfaces_at_the_wait_and_ring_limit(gffx, quirk):
         p.wait()
     assert ei.value.code == -1
     regs = dev(mixed_regions(idx, 5, 500))
-    with pytest.raises(gffx.GffxError):                # host regions cannot be queued
-        idx.intersect(mixed_regions(idx, 5, 500), 2, False, False, None, flags=F)
     pend = [idx.intersect(regs, 0, False, False, None, flags=F) for _ in range(32)]
     with pytest.raises(gffx.GffxError) as ei:          # 32 results may be pending per handle
         idx.intersect(regs, 0, False, False, None, flags=F)
