@@ -1245,6 +1245,10 @@ void EngineImpl::intersect(const uint32_t* chr, const uint32_t* start, const uin
     // host input: the copy is cut into chunks so that chunk i+1 crosses PCIe while chunk i is partitioned and joined
     uint32_t n_chunks = 1;
     if (!dev_in && n >= (1u << 21)) n_chunks = (uint32_t)std::min<uint64_t>(8, n >> 20);
+    if (!dev_in && (flags & 32u)) {   // queued: the NEXT job's copy hides this job's kernels; fewer, larger copies cost less per byte
+        static const int async_chunks = getenv("GFFX_ASYNC_CHUNKS") ? std::max(1, atoi(getenv("GFFX_ASYNC_CHUNKS"))) : 2;
+        n_chunks = std::min<uint32_t>(n_chunks, (uint32_t)async_chunks);
+    }
     uint64_t chunk = (n + n_chunks - 1) / std::max<uint32_t>(n_chunks, 1);
     chunk = (chunk + PART_TILE - 1) / PART_TILE * PART_TILE;
     if (chunk == 0) chunk = PART_TILE;
