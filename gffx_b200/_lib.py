@@ -148,6 +148,8 @@ SIGNATURES = {
     "gffx_job_buffer": (C.c_int, vp, vp, C.c_uint32, C.POINTER(vp), u64p, C.POINTER(C.c_int)),
     "gffx_fold": (C.c_int, vp, vp, vp, C.c_uint32, C.c_uint64, C.c_uint64, C.c_int),
     "gffx_index_sync": (C.c_int, vp),
+    "gffx_inflate_raw": (C.c_int64, vp, C.c_uint64, vp, C.c_uint64),
+    "gffx_crc32": (C.c_uint32, vp, C.c_uint64),
     "gffx_count_pairs_noalloc": (C.c_int, vp, vp, vp, vp, C.c_uint64, C.c_int, C.c_int, vp, vp),
     "gffx_noalloc_max_regions": (C.c_uint64,),
     "gffx_noalloc_max_roots": (C.c_uint64,),

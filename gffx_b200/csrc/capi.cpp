@@ -5,6 +5,7 @@
 #include "engine.h"
 #include "reads.h"
 
+#include "inflate.h"
 using namespace gffx;
 
 struct gffx_index {
@@ -268,6 +269,12 @@ int gffx_fold(gffx_index* idx, void* dst, const void* src, uint32_t rows, uint64
         idx->engine()->fold(dst, src, rows, stride_elems, n_elems, op);
     });
 }
+int64_t gffx_inflate_raw(const uint8_t* in, uint64_t in_len, uint8_t* out, uint64_t out_cap) {
+    if ((!in && in_len) || (!out && out_cap)) return -1;
+    static thread_local gffx::InflateTables tab;
+    return (int64_t)gffx::inflate_raw(in, (size_t)in_len, out, (size_t)out_cap, tab);
+}
+uint32_t gffx_crc32(const uint8_t* p, uint64_t n) { return (p || n == 0) ? gffx::crc32_bytes(p, (size_t)n) : 0u; }
 int gffx_index_sync(gffx_index* idx) {
     return guard([&] {
         need(idx, "idx");

@@ -160,6 +160,55 @@ inline long inflate_raw(const uint8_t* in, size_t in_len, uint8_t* out, size_t o
             if (!build(lens, nl, T.lcnt, T.lsym, T.lit, LIT_BITS)) return -1;
             if (!build(lens + 288, nd, T.dcnt, T.dsym, T.dst, DST_BITS)) return -1;
             for (;;) {
+                // fast path, away from both ends (16 input bytes, 320 output bytes): one 8-byte refill (>= 56 valid bits) pays for up to three literals or for one
+                // whole length / distance pair (15 + 5 + 15 + 13 bits); matches are copied eight bytes at a time
+                bool block_end = false;
+                while (B.end - B.p >= 16 && o + 320 <= out_cap) {
+                    uint64_t w;
+                    memcpy(&w, B.p, 8);
+                    B.buf |= w << B.n;
+                    B.p += (63 - B.n) >> 3;
+                    B.n |= 56;
+                    int s = decode(B, T.lit, LIT_BITS, T.lcnt, T.lsym);
+                    if (s < 256) {
+                        if (s < 0) return -1;
+                        out[o++] = (uint8_t)s;
+                        s = decode(B, T.lit, LIT_BITS, T.lcnt, T.lsym);
+                        if (s < 256) {
+                            if (s < 0) return -1;
+                            out[o++] = (uint8_t)s;
+                            s = decode(B, T.lit, LIT_BITS, T.lcnt, T.lsym);
+                            if (s < 256) {
+                                if (s < 0) return -1;
+                                out[o++] = (uint8_t)s;
+                                continue;
+                            }
+                        }
+                        if (B.n < 48) {   // a length / distance pair follows the literals: top the buffer up again (>= 9 input bytes are left)
+                            memcpy(&w, B.p, 8);
+                            B.buf |= w << B.n;
+                            B.p += (63 - B.n) >> 3;
+                            B.n |= 56;
+                        }
+                    }
+                    if (s == 256) { block_end = true; break; }
+                    s -= 257;
+                    if (s >= 29) return -1;
+                    const uint32_t len = LBASE[s] + B.take(LEXT[s]);
+                    const int d = decode(B, T.dst, DST_BITS, T.dcnt, T.dsym);
+                    if (d < 0 || d >= 30) return -1;
+                    const uint32_t dist = DBASE[d] + B.take(DEXT[d]);
+                    if (dist > o) return -1;
+                    const uint8_t* src = out + o - dist;
+                    uint8_t* dstp = out + o;
+                    if (dist >= 8) {
+                        for (uint32_t k = 0; k < len; k += 8) memcpy(dstp + k, src + k, 8);   // may run up to 7 bytes past len: inside the 320-byte margin
+                    } else {
+                        for (uint32_t k = 0; k < len; k++) dstp[k] = src[k];
+                    }
+                    o += len;
+                }
+                if (block_end) break;
                 B.refill();
                 if (B.overrun()) return -1;
                 int s = decode(B, T.lit, LIT_BITS, T.lcnt, T.lsym);
@@ -193,9 +242,9 @@ inline long inflate_raw(const uint8_t* in, size_t in_len, uint8_t* out, size_t o
     return (long)o;
 }
 
-// CRC-32 (IEEE 802.3, the gzip trailer's), slicing by 4
+// CRC-32 (IEEE 802.3, the gzip trailer's), slicing by 8
 struct Crc32Table {
-    uint32_t t[4][256];
+    uint32_t t[8][256];
     Crc32Table() {
         for (uint32_t i = 0; i < 256; i++) {
             uint32_t c = i;
@@ -203,19 +252,23 @@ struct Crc32Table {
             t[0][i] = c;
         }
         for (uint32_t i = 0; i < 256; i++)
-            for (int k = 1; k < 4; k++) t[k][i] = (t[k - 1][i] >> 8) ^ t[0][t[k - 1][i] & 0xFF];
+            for (int k = 1; k < 8; k++) t[k][i] = (t[k - 1][i] >> 8) ^ t[0][t[k - 1][i] & 0xFF];
     }
 };
 inline uint32_t crc32_bytes(const uint8_t* p, size_t n) {
     static const Crc32Table tab;
     const uint32_t(*T)[256] = tab.t;
     uint32_t c = 0xFFFFFFFFu;
-    while (n >= 4) {
-        c ^= (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
-        c = T[3][c & 0xFF] ^ T[2][(c >> 8) & 0xFF] ^ T[1][(c >> 16) & 0xFF] ^ T[0][c >> 24];
-        p += 4; n -= 4;
+    while (n >= 8) {
+        uint32_t a, b;
+        memcpy(&a, p, 4);       // little-endian hosts (x86-64, aarch64 as built here)
+        memcpy(&b, p + 4, 4);
+        a ^= c;
+        c = T[7][a & 0xFF] ^ T[6][(a >> 8) & 0xFF] ^ T[5][(a >> 16) & 0xFF] ^ T[4][a >> 24] ^ T[3][b & 0xFF] ^ T[2][(b >> 8) & 0xFF] ^ T[1][(b >> 16) & 0xFF] ^
+            T[0][b >> 24];
+        p += 8; n -= 8;
     }
-    while (n--) c = (c >> 8) ^ T[0][(c ^ *p++) & 0xFF];
+    while (n--) c = (c >> 1 >> 7) ^ T[0][(c ^ *p++) & 0xFF];
     return ~c;
 }
 

@@ -18,6 +18,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <memory>
 #include <thread>
 
 #include "inflate.h"
@@ -322,9 +323,7 @@ void read_alignments(const std::string& path, const std::unordered_map<std::stri
     std::vector<std::string> names;
     std::vector<int64_t> tid2num;
     bool bam_header_done = false;
-    auto consume = [&](bool final_chunk) {
-        const uint8_t* p = buf.data();
-        const size_t len = buf.size();
+    auto consume_at = [&](const uint8_t* p, const size_t len, bool final_chunk) -> size_t {
         size_t o = 0;
         if (kind < 0 && (len >= 4 || final_chunk)) kind = (len >= 4 && memcmp(p, "BAM\1", 4) == 0) ? 1 : 0;
         if (kind == 1) {
@@ -332,8 +331,7 @@ void read_alignments(const std::string& path, const std::unordered_map<std::stri
                 const size_t h = bam_header(p, len, &names);
                 if (h == 0) {
                     if (final_chunk) throw Err(E_FORMAT, "truncated BAM header");
-                    carry = len;
-                    return;
+                    return 0;   // nothing used: the header continues in the next chunk
                 }
                 tid2num.assign(names.size(), -1);
                 for (size_t i = 0; i < names.size(); i++) {
@@ -354,42 +352,108 @@ void read_alignments(const std::string& path, const std::unordered_map<std::stri
         } else if (kind == 0) {
             sam_text(p, len, final_chunk, S, seq_num, sink, &o);
         }
-        carry = len - o;
+        return o;
+    };
+    auto consume = [&](bool final_chunk) {   // the vector form: what is left moves to the front of `buf`
+        const size_t o = consume_at(buf.data(), buf.size(), final_chunk);
+        carry = buf.size() - o;
         if (carry && o) memmove(buf.data(), buf.data() + o, carry);
     };
     size_t p = 0;
-    constexpr size_t CHUNK = 256u << 20;
-    std::vector<BgzfBlock> blocks;
-    std::vector<size_t> at;
-    while (p < n) {
-        blocks.clear();
-        at.clear();
-        size_t tot = 0, total = 0;
+    // BGZF: chunks of ~16 MB of inflated bytes; while the main thread walks one chunk's records (or lines), the workers inflate
+    // the next chunk into the other buffer.  An incomplete record at a chunk's end is copied in front of the next chunk's bytes
+    // (the buffers keep a head room for it).  The buffers are plain allocations, reused: no zero fill, no page faults per chunk.
+    size_t CHUNK = 16u << 20;
+    if (const char* e = getenv("GFFX_BGZF_CHUNK")) CHUNK = (size_t)std::max<long long>(1, atoll(e));   // test hook: many chunks, small head rooms
+    const size_t HEAD = std::min<size_t>(1u << 20, CHUNK);
+    struct RawBuf {
+        std::unique_ptr<uint8_t[]> mem;
+        size_t cap = 0, head = 0;
+        void need(size_t head_room, size_t bytes) {
+            if (std::max(head, head_room) + bytes + 16 > cap || head_room > head) {
+                head = std::max(head, head_room);
+                cap = head + bytes + bytes / 4 + 16;
+                mem.reset(new uint8_t[cap]);
+            }
+        }
+    };
+    struct Chunk {
+        std::vector<BgzfBlock> blocks;
+        std::vector<size_t> at;   // offset of every block's bytes behind the buffer's head
+        size_t tot = 0;
+    };
+    bool plain = false;   // a gzip member without the BGZF field follows the blocks read so far
+    auto gather = [&](Chunk& c) {
+        c.blocks.clear(); c.at.clear(); c.tot = 0;
+        size_t total = 0;
         BgzfBlock b;
-        bool plain = false;
-        while (p < n && tot < CHUNK) {
+        while (p < n && c.tot < CHUNK) {
             if (!bgzf_member(f, n, p, &total, &b)) { plain = true; break; }
-            at.push_back(carry + tot);
-            blocks.push_back(b);
-            tot += b.isize;
+            c.at.push_back(c.tot);
+            c.blocks.push_back(b);
+            c.tot += b.isize;
             p += total;
         }
-        if (!blocks.empty()) {
-            st.format = 1;
-            buf.resize(carry + tot);
-            std::atomic<size_t> next{0};
-            run_threads(std::min<size_t>((size_t)T, blocks.size()), [&](int) {
-                InflateTables tab;
-                for (size_t k; (k = next.fetch_add(1)) < blocks.size();) {
-                    const BgzfBlock& x = blocks[k];
-                    if (x.isize == 0 && x.clen <= 2) continue;   // the empty end-of-file member
-                    const long r = inflate_raw(f + x.data, x.clen, buf.data() + at[k], x.isize, tab);
-                    if (r != (long)x.isize) throw Err(E_FORMAT, "BGZF block does not inflate to its recorded size: " + path);
-                    if (crc32_bytes(buf.data() + at[k], x.isize) != x.crc) throw Err(E_FORMAT, "BGZF block with a CRC32 mismatch: " + path);
-                }
-            });
-            consume(p >= n && !plain);
+        return !c.blocks.empty();
+    };
+    auto inflate_chunk = [&](const Chunk& c, RawBuf& B) {
+        B.need(HEAD, c.tot);
+        uint8_t* dst = B.mem.get() + B.head;
+        std::atomic<size_t> next{0};
+        run_threads((int)std::min<size_t>((size_t)T, c.blocks.size()), [&](int) {
+            InflateTables tab;
+            for (size_t k; (k = next.fetch_add(1)) < c.blocks.size();) {
+                const BgzfBlock& x = c.blocks[k];
+                if (x.isize == 0 && x.clen <= 2) continue;   // the empty end-of-file member
+                const long r = inflate_raw(f + x.data, x.clen, dst + c.at[k], x.isize, tab);
+                if (r != (long)x.isize) throw Err(E_FORMAT, "BGZF block does not inflate to its recorded size: " + path);
+                if (crc32_bytes(dst + c.at[k], x.isize) != x.crc) throw Err(E_FORMAT, "BGZF block with a CRC32 mismatch: " + path);
+            }
+        });
+    };
+    {
+        Chunk ck[2];
+        RawBuf B[2];
+        int cur = 0;
+        bool have = gather(ck[0]);
+        if (have) { st.format = 1; inflate_chunk(ck[0], B[0]); }
+        size_t carry_len = 0;   // bytes of the previous chunk sitting right in front of B[cur]'s head
+        while (have) {
+            const bool have_next = !plain && p < n && gather(ck[1 - cur]);
+            struct Bg {
+                std::thread t;
+                std::exception_ptr err;
+                ~Bg() { if (t.joinable()) t.join(); }
+            } bg;
+            if (have_next) {
+                bg.t = std::thread([&] {
+                    try { inflate_chunk(ck[1 - cur], B[1 - cur]); } catch (...) { bg.err = std::current_exception(); }
+                });
+            }
+            const uint8_t* data = B[cur].mem.get() + B[cur].head - carry_len;
+            const size_t len = carry_len + ck[cur].tot;
+            const size_t used = consume_at(data, len, !have_next && !plain);
+            const size_t left = len - used;
+            if (bg.t.joinable()) bg.t.join();
+            if (bg.err) std::rethrow_exception(bg.err);
+            if (!have_next) {   // what is left goes to the member-by-member path below (or was an error already)
+                buf.assign(data + used, data + len);
+                carry = left;
+                break;
+            }
+            RawBuf& N = B[1 - cur];
+            if (left > N.head) {   // an incomplete record larger than the head room: a new buffer with room for it
+                RawBuf big;
+                big.need(left + HEAD, ck[1 - cur].tot);
+                memcpy(big.mem.get() + big.head, N.mem.get() + N.head, ck[1 - cur].tot);
+                N = std::move(big);
+            }
+            if (left) memcpy(N.mem.get() + N.head - left, data + used, left);
+            carry_len = left;
+            cur = 1 - cur;
         }
+    }
+    {
         if (plain) {   // a gzip member without the BGZF field (gzip-ed SAM): sequential, the size is found by trial
             st.format = 2;
             const size_t xoff = 10 + ((f[p + 3] & 4) ? 2 + (size_t)le16(f + p + 10) : 0);
@@ -414,7 +478,7 @@ void read_alignments(const std::string& path, const std::unordered_map<std::stri
             consume(true);
         }
     }
-    if (blocks.empty() && kind < 0) consume(true);
+    if (kind < 0) consume(true);   // nothing has been looked at yet (an empty stream)
     if (st_out) *st_out = st;
 }
 

@@ -143,6 +143,11 @@ double gffx_bed_parse_stat(const gffx_index* idx, int what);
 int gffx_parse_reads(const gffx_index* idx, const char* path, uint32_t** chr, uint32_t** start, uint32_t** end, uint64_t* n,
                      uint64_t stats[5]);
 /* parse_region, src/commands/intersect.rs:172-198 */
+/* The reader's own DEFLATE decoder and CRC-32 (inflate.h; the reference gets both from rust-htslib -> htslib -> zlib), exported
+ * for tests and tools: one raw DEFLATE stream (a BGZF block's payload) -> out.  Returns the bytes written, -1 for a malformed
+ * stream, -2 when out_cap is too small. */
+int64_t gffx_inflate_raw(const uint8_t* in, uint64_t in_len, uint8_t* out, uint64_t out_cap);
+uint32_t gffx_crc32(const uint8_t* p, uint64_t n);
 int gffx_parse_region(const gffx_index* idx, const char* region, uint32_t* chr, uint32_t* start, uint32_t* end);
 void gffx_free(void* p);
 

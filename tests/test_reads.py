@@ -76,6 +76,26 @@ def test_readers_agree(host_index, tmp_path, kind):
     assert st["records"] - st["unmapped"] - st["unknown_ref"] - st["skipped"] == want.shape[0]
 
 
+@pytest.mark.parametrize("chunk", [1, 300, 5000, 70000])
+def test_chunked_pipeline(host_index, tmp_path, monkeypatch, chunk):
+    """the reader walks one chunk of inflated bytes while the next one inflates (reads.cpp): tiny chunks put a chunk boundary
+    inside the header, inside records (carried over in the buffers' head room) and inside a record larger than the head room
+    (the 320 KB CIGAR of the CG tag); BAM and bgzip-ed SAM"""
+    idx, o = host_index
+    targets, tid2num = _targets(idx)
+    rng = random.Random(chunk)
+    recs = A.random_records(rng, targets, 3000, 4_000_000)
+    recs.insert(1500, A.Rec("long", 0, 0, 1000, [(1, "M"), (1, "D")] * 40000, tags=b"NMC\x05"))
+    want = _expected(recs, tid2num)
+    monkeypatch.setenv("GFFX_BGZF_CHUNK", str(chunk))
+    p = str(tmp_path / "c.bam")
+    open(p, "wb").write(A.bgzf(A.bam_bytes(targets, recs), block=977, rng=rng))
+    assert _check(idx, o, p, want)["records"] == len(recs)
+    p = str(tmp_path / "c.sam")
+    open(p, "wb").write(A.bgzf(A.sam_text(targets, recs[:1500] + recs[1501:]), block=3000))
+    _check(idx, o, p, _expected(recs[:1500] + recs[1501:], tid2num))
+
+
 def test_long_cigar_in_cg_tag(host_index, tmp_path):
     idx, o = host_index
     targets, tid2num = _targets(idx)
