@@ -410,12 +410,7 @@ void EngineImpl::build_lines() {
     std::vector<uint32_t> vS(n, 0), vE(n, 0), vseq(n, 0);
     // per sequence: sorted distinct S/E of usable lines (host threads: sequences are sorted side by side, longest first)
     const size_t T = (size_t)std::max(1, H->n_threads);
-    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
-        if (n_jobs <= 1 || T <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
-        std::vector<std::thread> th;
-        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
-        for (auto& t : th) t.join();
-    };
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) { parallel_jobs(n_jobs, (int)T, f); };   // util.h: the thread pool
     // the columns that do not depend on the rank space cross PCIe from a helper thread while the host builds it (pageable
     // copies occupy their calling thread)
     d_ln_flags.ensure(std::max<size_t>(n, 1)); d_ln_blk.ensure(std::max<size_t>(n, 1) * 4); d_ln_type.ensure(std::max<size_t>(n, 1) * 4);

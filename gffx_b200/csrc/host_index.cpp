@@ -228,7 +228,6 @@ void HostIndex::build_vseqs() {
         const size_t T = (L.size() >= (1u << 16) && n <= (1u << 16)) ? (size_t)std::max(1, std::min(n_threads, 32)) : 1;
         std::vector<std::vector<uint64_t>> ext_t(T, std::vector<uint64_t>(T > 1 ? n : 0, 0));
         std::vector<uint32_t> blk_max(blocks.size(), 0);
-        std::vector<std::thread> th;
         auto work = [&](size_t t) {
             uint64_t* e = T > 1 ? ext_t[t].data() : ext.data();
             for (size_t i = L.size() * t / T; i < L.size() * (t + 1) / T; i++)
@@ -240,8 +239,7 @@ void HostIndex::build_vseqs() {
                         if (L.flags[i] & LN_D_OK) blk_max[b] = std::max(blk_max[b], L.fe[i]);
         };
         if (T > 1) {
-            for (size_t t = 0; t < T; t++) th.emplace_back(work, t);
-            for (auto& x : th) x.join();
+            parallel_jobs(T, (int)T, work);
             for (size_t t = 0; t < T; t++)
                 for (size_t c = 0; c < n; c++) ext[c] = std::max(ext[c], ext_t[t][c]);
         } else {
@@ -419,12 +417,7 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
     const size_t nparts = std::max<size_t>(1, std::min<size_t>((size_t)std::max(1, threads), total / 65536 + 1));
     struct Chunk { LocalDict types, chroms; std::vector<uint32_t> ty, ch; };
     std::vector<Chunk> chunks(nparts);
-    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
-        if (n_jobs <= 1 || threads <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
-        std::vector<std::thread> th;
-        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
-        for (auto& t : th) t.join();
-    };
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) { parallel_jobs(n_jobs, (int)std::max<size_t>(1, (size_t)threads), f); };   // util.h: the thread pool
     run_parallel(nparts, [&](size_t c) {
         Chunk& C = chunks[c];
         const size_t i0 = total * c / nparts, i1 = total * (c + 1) / nparts;
@@ -470,12 +463,7 @@ void HostIndex::number_ids(const std::vector<uint64_t>& g_hash, const std::vecto
     const size_t total = L.size();
     const size_t T = (size_t)std::max(1, std::min(threads, 64));
     const size_t nshard = T, nchunk = total >= (1u << 16) ? T : 1;
-    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
-        if (n_jobs <= 1 || T <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
-        std::vector<std::thread> th;
-        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
-        for (auto& t : th) t.join();
-    };
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) { parallel_jobs(n_jobs, (int)std::max<size_t>(1, (size_t)T), f); };   // util.h: the thread pool
     auto chunk_lo = [&](size_t c) { return total * c / nchunk; };
     auto shard_of = [&](uint64_t h) { return (size_t)((h >> 32) % nshard); };
     // the shards' line lists, in line order: chunks of lines count, then place, their lines side by side (every shard used to
@@ -642,12 +630,7 @@ void HostIndex::scan_lines(int threads) {
     auto work = [&](size_t pi) { scan_blocks(cut[pi], cut[pi + 1], &parts[pi]); };
     {
         PhaseTimer t_scan("    parallel scan");
-        if (nparts == 1) work(0);
-        else {
-            std::vector<std::thread> th;
-            for (size_t i = 0; i < nparts; i++) th.emplace_back(work, i);
-            for (auto& t : th) t.join();
-        }
+        parallel_jobs(nparts, (int)nparts, work);
     }
     PhaseTimer t_merge("    merge + ID dictionary");
     // concatenate (every part copies its own slice, in parallel), remapping the per-part type / chromosome dictionaries
@@ -688,12 +671,7 @@ void HostIndex::scan_lines(int threads) {
         }
         P = Part();
     };
-    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) {
-        if (n_jobs <= 1 || threads <= 1) { for (size_t k = 0; k < n_jobs; k++) f(k); return; }
-        std::vector<std::thread> th;
-        for (size_t k = 0; k < n_jobs; k++) th.emplace_back(f, k);
-        for (auto& t : th) t.join();
-    };
+    auto run_parallel = [&](size_t n_jobs, const std::function<void(size_t)>& f) { parallel_jobs(n_jobs, (int)std::max<size_t>(1, (size_t)threads), f); };   // util.h: the thread pool
     if (total >= (1ull << 32) - 1) throw Err(E_FORMAT, "more than 2^32-2 GFF lines inside blocks");
     run_parallel(nparts, copy_part);
     number_ids(g_hash, g_off, g_len, threads);
@@ -819,12 +797,7 @@ void parse_bed_counts(const std::string& path, const std::unordered_map<std::str
             p = q;
         }
     };
-    if (nparts == 1) work(0);
-    else {
-        std::vector<std::thread> th;
-        for (size_t k = 0; k < nparts; k++) th.emplace_back(work, k);
-        for (auto& t : th) t.join();
-    }
+    parallel_jobs(nparts, (int)nparts, work);
     for (auto& R : parts) {
         out->chr.insert(out->chr.end(), R.chr.begin(), R.chr.end());
         out->start.insert(out->start.end(), R.start.begin(), R.start.end());

@@ -136,21 +136,21 @@ bool line_cache_load(HostIndex& H, int threads) {
         std::vector<size_t> at(pcs.size());
         size_t o = sizeof h;
         for (size_t i = 0; i < pcs.size(); i++) { at[i] = o; o += pcs[i].n; }
-        std::vector<std::thread> th;
         std::vector<uint8_t> good(pcs.size(), 1);
-        const size_t T = (size_t)std::max(1, std::min(threads, 16));
-        for (size_t t0 = 0; t0 < T; t0++)
-            th.emplace_back([&, t0] {
-                for (size_t i = t0; i < pcs.size(); i += T) {
-                    size_t done = 0;
-                    while (done < pcs[i].n) {
-                        const ssize_t k = pread(fd, (char*)pcs[i].p + done, pcs[i].n - done, (off_t)(at[i] + done));
-                        if (k <= 0) { good[i] = 0; break; }
-                        done += (size_t)k;
-                    }
-                }
-            });
-        for (auto& x : th) x.join();
+        // the large pieces in slices of 4 MB, so that every thread has its share of the bytes
+        struct Slice { size_t i, a, z; };
+        std::vector<Slice> slices;
+        for (size_t i = 0; i < pcs.size(); i++)
+            for (size_t a = 0; a < pcs[i].n; a += 4u << 20) slices.push_back(Slice{i, a, std::min(pcs[i].n, a + (4u << 20))});
+        parallel_jobs(slices.size(), std::max(1, std::min(threads, 16)), [&](size_t k) {
+            const Slice& sl = slices[k];
+            size_t done = sl.a;
+            while (done < sl.z) {
+                const ssize_t r = pread(fd, (char*)pcs[sl.i].p + done, sl.z - done, (off_t)(at[sl.i] + done));
+                if (r <= 0) { good[sl.i] = 0; break; }
+                done += (size_t)r;
+            }
+        });
         for (uint8_t g : good) ok = ok && g;
     }
     ::close(fd);

@@ -237,10 +237,9 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
         size_t stage_cap = 0;
         uint8_t* const stage_all = (uint8_t*)pinned_acquire((size_t)W * 2 * CH, &stage_cap);
         struct StageGuard { void* p; size_t cap; ~StageGuard() { pinned_release(p, cap); } } stage_guard{stage_all, stage_cap};
-        std::vector<std::thread> workers;
-        for (int w = 0; w < W; w++)
-            workers.emplace_back([&, w] {
-                cudaError_t& e = werr[(size_t)w];
+        parallel_jobs((size_t)W, W, [&](size_t w) {
+            {
+                cudaError_t& e = werr[w];
                 uint8_t* stage[2] = {stage_all + (size_t)(2 * w) * CH, stage_all + (size_t)(2 * w + 1) * CH};
                 cudaEvent_t ev[2] = {nullptr, nullptr};
                 cudaStream_t ws = nullptr;
@@ -272,8 +271,8 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
                     if (ev[j]) cudaEventDestroy(ev[j]);
                 if (ws) cudaStreamDestroy(ws);
                 if (fd >= 0) ::close(fd);
-            });
-        for (auto& x : workers) x.join();
+            }
+        });
         for (cudaError_t e : werr) GFFX_CUDA(e);
     }
     PhaseTimer t_k("    kernels + read-back");
@@ -363,10 +362,9 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
         col(R.blk_nlines, nl, nb); col(R.blk_nonascii, na, nb);
         const int W = std::max(1, std::min(threads, 6));
         std::vector<std::string> werr((size_t)W);
-        std::vector<std::thread> workers;
         std::atomic<size_t> next{0};
-        for (int w = 0; w < W; w++)
-            workers.emplace_back([&, w] {
+        parallel_jobs((size_t)W, W, [&](size_t w) {
+            {
                 cudaStream_t ws = nullptr;
                 try {
                     GFFX_CUDA(cudaSetDevice(device));
@@ -375,10 +373,10 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
                         jobs[k](ws);
                         GFFX_CUDA(cudaStreamSynchronize(ws));
                     }
-                } catch (const std::exception& e) { werr[(size_t)w] = e.what(); }
+                } catch (const std::exception& e) { werr[w] = e.what(); }
                 if (ws) cudaStreamDestroy(ws);
-            });
-        for (auto& x : workers) x.join();
+            }
+        });
         for (const std::string& e : werr)
             if (!e.empty()) throw Err(E_CUDA, e);
     }

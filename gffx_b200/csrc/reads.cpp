@@ -16,6 +16,10 @@
 // reader, depth.rs:589).  CRAM is not decoded: its codecs and reference-based sequences are out of this engine's scope.
 #include "reads.h"
 
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <algorithm>
 #include <atomic>
 #include <memory>
@@ -129,12 +133,22 @@ struct BgzfBlock {
     uint32_t isize, crc;
 };
 
-// member at p: its total size, the DEFLATE bytes, ISIZE and CRC; false when this gzip member has no BC field
-bool bgzf_member(const uint8_t* f, size_t n, size_t p, size_t* total, BgzfBlock* b) {
-    if (n - p < 18 || f[p] != 0x1f || f[p + 1] != 0x8b || f[p + 2] != 8) throw Err(E_FORMAT, "corrupt BGZF / gzip member header");
-    if (!(f[p + 3] & 4)) return false;
+void run_threads(int T, const std::function<void(int)>& f);
+
+// member at p of the bytes f[0, n): its total size, the DEFLATE bytes, ISIZE and CRC.  Returns 1, 0 when this gzip member has no
+// BC field (not BGZF), 2 when f ends inside the member and more of the file follows (at_eof false: read on and ask again).
+int bgzf_member(const uint8_t* f, size_t n, size_t p, bool at_eof, size_t* total, BgzfBlock* b) {
+    if (n - p < 18) {
+        if (!at_eof) return 2;
+        throw Err(E_FORMAT, "corrupt BGZF / gzip member header");
+    }
+    if (f[p] != 0x1f || f[p + 1] != 0x8b || f[p + 2] != 8) throw Err(E_FORMAT, "corrupt BGZF / gzip member header");
+    if (!(f[p + 3] & 4)) return 0;
     const size_t xlen = le16(f + p + 10);
-    if (p + 12 + xlen > n) throw Err(E_FORMAT, "truncated BGZF header");
+    if (p + 12 + xlen > n) {
+        if (!at_eof) return 2;
+        throw Err(E_FORMAT, "truncated BGZF header");
+    }
     size_t q = p + 12, qe = q + xlen;
     long bsize = -1;
     while (q + 4 <= qe) {
@@ -142,27 +156,52 @@ bool bgzf_member(const uint8_t* f, size_t n, size_t p, size_t* total, BgzfBlock*
         if (f[q] == 'B' && f[q + 1] == 'C' && slen == 2 && q + 6 <= qe) bsize = (long)le16(f + q + 4);
         q += 4 + slen;
     }
-    if (bsize < 0) return false;
+    if (bsize < 0) return 0;
     *total = (size_t)bsize + 1;
-    if (p + *total > n || *total < 12 + xlen + 8) throw Err(E_FORMAT, "truncated BGZF block");
+    if (*total < 12 + xlen + 8) throw Err(E_FORMAT, "truncated BGZF block");
+    if (p + *total > n) {
+        if (!at_eof) return 2;
+        throw Err(E_FORMAT, "truncated BGZF block");
+    }
     b->data = p + 12 + xlen;
     b->clen = *total - 12 - xlen - 8;
     b->crc = le32(f + p + *total - 8);
     b->isize = le32(f + p + *total - 4);
-    return true;
+    return 1;
 }
 
-void run_threads(int T, const std::function<void(int)>& f) {
-    if (T <= 1) { f(0); return; }
-    std::vector<std::thread> th;
-    std::exception_ptr err;
-    std::mutex mu;
-    for (int t = 0; t < T; t++)
-        th.emplace_back([&, t] {
-            try { f(t); } catch (...) { std::lock_guard<std::mutex> g(mu); if (!err) err = std::current_exception(); }
-        });
-    for (auto& x : th) x.join();
-    if (err) std::rethrow_exception(err);
+// The file is read with pread into plain buffers, never touched through a mapping: page-cache -> buffer copies run at memory
+// speed on any number of threads, where first touches of a mapping are one page fault each and the threads' faults queue up
+// behind each other (r03: eight threads scanning a mapped 111 MB SAM file took as long as one).
+struct FileBytes {
+    int fd = -1;
+    size_t size = 0;
+    explicit FileBytes(const std::string& path) {
+        fd = ::open(path.c_str(), O_RDONLY);
+        struct stat sb;
+        if (fd < 0 || fstat(fd, &sb) != 0) {
+            if (fd >= 0) ::close(fd);
+            throw Err(E_IO, "Failed to open file: \"" + path + "\"");
+        }
+        size = (size_t)sb.st_size;
+    }
+    ~FileBytes() { if (fd >= 0) ::close(fd); }
+    void read(size_t off, uint8_t* dst, size_t len, int T) const {   // all of [off, off + len): the caller stays inside the file
+        auto part = [&](size_t a, size_t z) {
+            while (a < z) {
+                const ssize_t r = pread(fd, dst + a, z - a, (off_t)(off + a));
+                if (r <= 0) throw Err(E_IO, "read error (or the file shrank while it was read)");
+                a += (size_t)r;
+            }
+        };
+        const int W = (len >= (8u << 20)) ? std::max(1, std::min(T, 8)) : 1;
+        if (W == 1) { part(0, len); return; }
+        run_threads(W, [&](int w) { part(len * (size_t)w / (size_t)W, len * (size_t)(w + 1) / (size_t)W); });
+    }
+};
+
+void run_threads(int T, const std::function<void(int)>& f) {   // f(0) .. f(T-1) side by side (util.h: the process's thread pool)
+    parallel_jobs((size_t)std::max(1, T), T, [&](size_t t) { f((int)t); });
 }
 
 // ---- SAM text -------------------------------------------------------------------------------------------------------------
@@ -296,27 +335,102 @@ void sam_text(const uint8_t* p, size_t n, bool final_chunk, SamState& S, const s
     *consumed = (size_t)(q - p);
 }
 
+// The same on T threads: the header lines (and the first record, which closes the header) serially, then the rest of the text cut
+// into T pieces at line ends, each piece into its own interval list and counters, appended in file order.  An error is the one of
+// the earliest piece that failed, as a serial pass would have met it first.
+void sam_text_threads(const uint8_t* p, size_t n, bool final_chunk, SamState& S, const std::unordered_map<std::string, uint32_t>& seq_num, Sink& sink,
+                      size_t* consumed, int T) {
+    size_t par_min = 4u << 20;
+    if (const char* ev = getenv("GFFX_SAM_PAR_MIN")) par_min = (size_t)std::max<long long>(0, atoll(ev));   // test hook
+    if (T <= 1 || n < par_min) { sam_text(p, n, final_chunk, S, seq_num, sink, consumed); return; }
+    const uint8_t* e = p + n;
+    const uint8_t* q = p;
+    while (q < e && !S.header_done) {   // serial until the header is closed
+        const uint8_t* nl = find_byte(q, e, '\n');
+        if (!nl) {
+            if (!final_chunk) { *consumed = (size_t)(q - p); return; }
+            nl = e;
+        }
+        sam_line(q, nl, S, seq_num, sink);
+        q = nl < e ? nl + 1 : e;
+    }
+    // the last complete line's end bounds the parallel part
+    const uint8_t* stop = e;
+    if (!final_chunk) {
+        while (stop > q && stop[-1] != '\n') stop--;
+    }
+    std::vector<const uint8_t*> cut((size_t)T + 1, stop);
+    cut[0] = q;
+    for (int t = 1; t < T; t++) {
+        const uint8_t* c = q + (size_t)(stop - q) * (size_t)t / (size_t)T;
+        if (c < cut[(size_t)t - 1]) c = cut[(size_t)t - 1];
+        const uint8_t* nl = find_byte(c, stop, '\n');
+        cut[(size_t)t] = nl ? nl + 1 : stop;
+    }
+    std::vector<Regions> part((size_t)T);
+    std::vector<ReadStats> pst((size_t)T);
+    std::vector<std::exception_ptr> perr((size_t)T);
+    parallel_jobs((size_t)T, T, [&](size_t t) {
+        try {
+            Regions mine;      // on the thread's own stack: the pieces' list headers and counters side by side in one
+            ReadStats mst{};   // array share cache lines, and every record updates them
+            Sink local{&S.tid2num, &mine, &mst};
+            size_t used;
+            if (cut[t] < cut[t + 1]) sam_text(cut[t], (size_t)(cut[t + 1] - cut[t]), true, S, seq_num, local, &used);
+            part[t] = std::move(mine);
+            pst[t] = mst;
+        } catch (...) { perr[t] = std::current_exception(); }
+    });
+    for (int t = 0; t < T; t++) {
+        // what a serial pass had collected before the first failing piece is of no use to the caller either: fail as it would
+        if (perr[(size_t)t]) std::rethrow_exception(perr[(size_t)t]);
+        Regions& r = part[(size_t)t];
+        sink.out->chr.insert(sink.out->chr.end(), r.chr.begin(), r.chr.end());
+        sink.out->start.insert(sink.out->start.end(), r.start.begin(), r.start.end());
+        sink.out->end.insert(sink.out->end.end(), r.end.begin(), r.end.end());
+        sink.st->records += pst[(size_t)t].records; sink.st->unmapped += pst[(size_t)t].unmapped;
+        sink.st->unknown_ref += pst[(size_t)t].unknown_ref; sink.st->skipped += pst[(size_t)t].skipped;
+    }
+    *consumed = (size_t)(stop - p);
+}
+
 }  // namespace
 
 void read_alignments(const std::string& path, const std::unordered_map<std::string, uint32_t>& seq_num, int threads, Regions* out, ReadStats* st_out) {
     ReadStats st{};
-    Mapped file;
-    file.open(path);
-    const uint8_t* f = file.data();
-    const size_t n = file.size();
+    const FileBytes file(path);
+    const size_t n = file.size;
+    const int T = std::max(1, threads);
     Sink sink{nullptr, out, &st};
     SamState S;
-    if (n >= 4 && memcmp(f, "CRAM", 4) == 0)
+    uint8_t magic[4] = {0, 0, 0, 0};
+    file.read(0, magic, std::min<size_t>(n, 4), 1);
+    if (n >= 4 && memcmp(magic, "CRAM", 4) == 0)
         throw Err(E_ARG, "CRAM input is not supported by this engine (no reference-based decoder); convert to BAM or SAM: " + path);
-    if (!(n >= 2 && f[0] == 0x1f && f[1] == 0x8b)) {   // plain SAM text
+    if (!(n >= 2 && magic[0] == 0x1f && magic[1] == 0x8b)) {   // plain SAM text, in pieces of 8 MB: an incomplete last line waits for the next piece
         st.format = 0;
-        size_t used;
-        sam_text(f, n, true, S, seq_num, sink, &used);
+        size_t piece = 8u << 20;   // small enough to stay in cache-warm, already-faulted memory from piece to piece
+        if (const char* e = getenv("GFFX_BGZF_CHUNK")) piece = (size_t)std::max<long long>(1, atoll(e));   // test hook
+        std::unique_ptr<uint8_t[]> text;
+        size_t cap = 0, have = 0, off = 0;
+        do {
+            const size_t m = std::min(piece, n - off);
+            if (have + m > cap) {
+                std::unique_ptr<uint8_t[]> bigger(new uint8_t[cap = have + m + (have + m) / 4 + 16]);
+                if (have) memcpy(bigger.get(), text.get(), have);
+                text = std::move(bigger);
+            }
+            file.read(off, text.get() + have, m, T);
+            off += m;
+            size_t used = 0;
+            sam_text_threads(text.get(), have + m, off >= n, S, seq_num, sink, &used, T);
+            have = have + m - used;
+            if (have && used) memmove(text.get(), text.get() + used, have);
+        } while (off < n);
         if (st_out) *st_out = st;
         return;
     }
     // ---- gzip family: BGZF members in parallel, anything else member by member -------------------------------------------
-    const int T = std::max(1, threads);
     std::vector<uint8_t> buf;      // carry (an incomplete record / line of the previous chunk) + this chunk's inflated bytes
     size_t carry = 0;
     int kind = -1;                 // 1 BAM, 0 SAM text; decided by the first inflated bytes
@@ -378,23 +492,39 @@ void read_alignments(const std::string& path, const std::unordered_map<std::stri
         }
     };
     struct Chunk {
+        std::unique_ptr<uint8_t[]> comp;   // the piece of the file the chunk's blocks lie in (BgzfBlock::data is relative to it)
+        size_t comp_cap = 0;
         std::vector<BgzfBlock> blocks;
         std::vector<size_t> at;   // offset of every block's bytes behind the buffer's head
         size_t tot = 0;
     };
     bool plain = false;   // a gzip member without the BGZF field follows the blocks read so far
+    // the next piece of the file from p on, and the whole blocks in it, until ~CHUNK inflated bytes; a block cut off by the piece's
+    // end is read again with the next piece
     auto gather = [&](Chunk& c) {
         c.blocks.clear(); c.at.clear(); c.tot = 0;
-        size_t total = 0;
-        BgzfBlock b;
-        while (p < n && c.tot < CHUNK) {
-            if (!bgzf_member(f, n, p, &total, &b)) { plain = true; break; }
-            c.at.push_back(c.tot);
-            c.blocks.push_back(b);
-            c.tot += b.isize;
-            p += total;
+        size_t piece = std::max<size_t>(std::min<size_t>(CHUNK, 8u << 20), 1u << 16);   // at least one whole block
+        for (;;) {
+            const size_t m = std::min(piece, n - p);
+            if (m > c.comp_cap) c.comp.reset(new uint8_t[c.comp_cap = m + 16]);
+            file.read(p, c.comp.get(), m, T);
+            const bool at_eof = p + m >= n;
+            size_t r = 0, total = 0;
+            BgzfBlock b;
+            int rc = 1;
+            while (r < m && c.tot < CHUNK) {
+                rc = bgzf_member(c.comp.get(), m, r, at_eof, &total, &b);
+                if (rc != 1) break;
+                c.at.push_back(c.tot);
+                c.blocks.push_back(b);
+                c.tot += b.isize;
+                r += total;
+            }
+            if (rc == 0) plain = true;
+            if (rc == 2 && c.blocks.empty()) { piece *= 2; continue; }   // not even one block fits: a larger piece (a member is at most 64 KB + extra fields)
+            p += r;
+            return !c.blocks.empty();
         }
-        return !c.blocks.empty();
     };
     auto inflate_chunk = [&](const Chunk& c, RawBuf& B) {
         B.need(HEAD, c.tot);
@@ -405,7 +535,7 @@ void read_alignments(const std::string& path, const std::unordered_map<std::stri
             for (size_t k; (k = next.fetch_add(1)) < c.blocks.size();) {
                 const BgzfBlock& x = c.blocks[k];
                 if (x.isize == 0 && x.clen <= 2) continue;   // the empty end-of-file member
-                const long r = inflate_raw(f + x.data, x.clen, dst + c.at[k], x.isize, tab);
+                const long r = inflate_raw(c.comp.get() + x.data, x.clen, dst + c.at[k], x.isize, tab);
                 if (r != (long)x.isize) throw Err(E_FORMAT, "BGZF block does not inflate to its recorded size: " + path);
                 if (crc32_bytes(dst + c.at[k], x.isize) != x.crc) throw Err(E_FORMAT, "BGZF block with a CRC32 mismatch: " + path);
             }
@@ -456,6 +586,11 @@ void read_alignments(const std::string& path, const std::unordered_map<std::stri
     {
         if (plain) {   // a gzip member without the BGZF field (gzip-ed SAM): sequential, the size is found by trial
             st.format = 2;
+            const size_t base = p;   // the rest of the file in memory; f[x] = file byte x
+            std::unique_ptr<uint8_t[]> rest(new uint8_t[n - base + 16]);
+            file.read(base, rest.get(), n - base, T);
+            const uint8_t* f = rest.get() - base;
+            if (n - p < 18) throw Err(E_FORMAT, "truncated gzip member");
             const size_t xoff = 10 + ((f[p + 3] & 4) ? 2 + (size_t)le16(f + p + 10) : 0);
             size_t q = p + xoff;
             if (f[p + 3] & 8) { while (q < n && f[q]) q++; q++; }

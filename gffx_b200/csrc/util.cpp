@@ -1,4 +1,11 @@
 #include "util.h"
+#include <algorithm>
+#include <thread>
+#include <mutex>
+#include <memory>
+#include <deque>
+#include <condition_variable>
+#include <atomic>
 #include <fcntl.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
@@ -8,6 +15,74 @@
 #include <cstdlib>
 
 namespace gffx {
+
+// ---- the thread pool behind parallel_jobs -----------------------------------------------------------------------------------
+namespace {
+struct PoolCall {   // one parallel_jobs call: shared by the caller and the workers that picked up one of its tickets
+    const std::function<void(size_t)>* job;
+    size_t n;
+    std::atomic<size_t> next{0}, done{0};
+    std::mutex mu;
+    std::condition_variable cv;
+    std::exception_ptr err;
+    void work() {
+        for (size_t i; (i = next.fetch_add(1)) < n;) {
+            try { (*job)(i); } catch (...) { std::lock_guard<std::mutex> g(mu); if (!err) err = std::current_exception(); }
+            if (done.fetch_add(1) + 1 == n) { std::lock_guard<std::mutex> g(mu); cv.notify_all(); }
+        }
+    }
+};
+struct Pool {
+    std::mutex mu;
+    std::condition_variable cv;
+    std::deque<std::shared_ptr<PoolCall>> tickets;
+    size_t n_workers = 0;
+    Pool() {
+        const unsigned hc = std::thread::hardware_concurrency();
+        n_workers = hc > 1 ? std::min<unsigned>(hc - 1, 63) : 0;
+        for (size_t k = 0; k < n_workers; k++)
+            std::thread([this] {
+                for (;;) {
+                    std::shared_ptr<PoolCall> c;
+                    {
+                        std::unique_lock<std::mutex> g(mu);
+                        cv.wait(g, [&] { return !tickets.empty(); });
+                        c = std::move(tickets.front());
+                        tickets.pop_front();
+                    }
+                    c->work();
+                }
+            }).detach();
+    }
+};
+Pool& pool() {
+    static Pool* P = new Pool();   // never destroyed: its threads wait for work until the process ends
+    return *P;
+}
+}  // namespace
+
+void parallel_jobs(size_t n_jobs, int max_threads, const std::function<void(size_t)>& job) {
+    if (n_jobs == 0) return;
+    if (n_jobs == 1 || max_threads <= 1) { for (size_t i = 0; i < n_jobs; i++) job(i); return; }
+    Pool& P = pool();
+    const size_t helpers = std::min<size_t>({(size_t)max_threads - 1, n_jobs - 1, P.n_workers});
+    if (helpers == 0) { for (size_t i = 0; i < n_jobs; i++) job(i); return; }
+    auto c = std::make_shared<PoolCall>();
+    c->job = &job;
+    c->n = n_jobs;
+    {
+        std::lock_guard<std::mutex> g(P.mu);
+        for (size_t k = 0; k < helpers; k++) P.tickets.push_back(c);
+    }
+    if (helpers == 1) P.cv.notify_one(); else P.cv.notify_all();
+    c->work();
+    {
+        std::unique_lock<std::mutex> g(c->mu);
+        c->cv.wait(g, [&] { return c->done.load() == c->n; });
+    }
+    // a ticket nobody picked up yet finds no job left and is dropped; `job` is not touched after this point
+    if (c->err) std::rethrow_exception(c->err);
+}
 
 double PhaseTimer::now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 PhaseTimer::PhaseTimer(const char* w) : what(w), t0(0), on(getenv("GFFX_TIMING") != nullptr) { if (on) t0 = now(); }

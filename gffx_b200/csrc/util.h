@@ -1,6 +1,7 @@
 // util.h — small host-side helpers shared by the engine's C++ sources.
 #pragma once
 #include <cstdint>
+#include <functional>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -47,6 +48,14 @@ std::string_view rtrim_unicode(std::string_view s);          // str::trim_end
 std::string_view trim_unicode(std::string_view s);           // str::trim
 bool parse_u32_strict(const uint8_t* s, size_t n, uint32_t* out);   // digits only, checked (intersect.rs:526-538)
 bool parse_u32_rust(std::string_view s, uint32_t* out);              // str::parse::<u32> ('+' allowed)
+
+// Host-side data parallelism: jobs 0 .. n_jobs-1, each run once, on at most max_threads threads at a time (the caller is one
+// of them), from a pool of threads that live as long as the process.  Threads made for a few milliseconds of work each (the
+// loaders' phases are that short) start on their creator's CPU and are done before the scheduler has spread them: r03 measured
+// eight such threads finishing one after the other.  Pool threads are already spread out and only need waking.  Re-entrant (a job
+// may call parallel_jobs; the caller always works on its own jobs, so nothing waits for a free worker); the first exception of
+// a job is rethrown in the caller once every job has ended.
+void parallel_jobs(size_t n_jobs, int max_threads, const std::function<void(size_t)>& job);
 
 // GFFX_TIMING=1: wall time of the load phases on stderr (profiles/load_time.py)
 struct PhaseTimer {

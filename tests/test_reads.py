@@ -96,6 +96,27 @@ def test_chunked_pipeline(host_index, tmp_path, monkeypatch, chunk):
     _check(idx, o, p, _expected(recs[:1500] + recs[1501:], tid2num))
 
 
+def test_sam_text_on_all_threads(gffx, host_index, tmp_path, monkeypatch):
+    """plain SAM text is cut at line ends and parsed on the host threads (reads.cpp: sam_text_threads): same intervals in file
+    order, same counters, and a bad record still fails the call"""
+    idx, o = host_index
+    targets, tid2num = _targets(idx)
+    rng = random.Random(11)
+    recs = A.random_records(rng, targets, 5000, 4_000_000)
+    monkeypatch.setenv("GFFX_SAM_PAR_MIN", "0")
+    for crlf in (False, True):
+        p = str(tmp_path / "par.sam")
+        open(p, "wb").write(A.sam_text(targets, recs, crlf=crlf))
+        assert _check(idx, o, p, _expected(recs, tid2num))["records"] == len(recs)
+    text = A.sam_text(targets, recs)
+    cutat = text.index(b"\n", len(text) * 3 // 4) + 1
+    open(p, "wb").write(text[:cutat] + b"broken\tline\n" + text[cutat:])
+    with pytest.raises(gffx.GffxError):
+        idx.parse_reads(p)
+    open(p, "wb").write(b"@HD\tVN:1.6\n@SQ\tSN:%s\tLN:10\n" % targets[0][0].encode())   # a header and nothing else
+    assert idx.parse_reads(p)[0].size == 0
+
+
 def test_long_cigar_in_cg_tag(host_index, tmp_path):
     idx, o = host_index
     targets, tid2num = _targets(idx)
