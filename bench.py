@@ -512,7 +512,7 @@ def e2e_queued(c, passes, host_sets, steps):
         n, prev = 0, None
         for _ in range(k):
             for (name, mode, inv, entire, types), regs in zip(passes, host_sets):
-                p = c.idx.intersect(regs, mode, inv, entire, types, flags=F)
+                p = queue_pass(c, regs, mode, inv, entire, types, F)
                 if prev is not None:
                     n += settle(prev)
                 prev = p
@@ -609,10 +609,10 @@ def bench_intersect(c):
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     e2e_sync_s, ranges_e2e = e2e_sync(c, SWEEP, host_sets, e2e_steps)
     e2e_s, e2e_api = e2e_sync_s, "gffx_intersect (C ABI) with pinned host region arrays; byte ranges copied back"
-    if c.world == 1:   # one GPU: the same calls queued, two in flight (a sharded job exchanges flags between add and finish and stays synchronous)
+    if True:   # the same calls queued, two jobs in flight (a sharded job's flag exchange rides on its lane's stream)
         e2e_s, ranges_q = e2e_queued(c, SWEEP, host_sets, e2e_steps)
         assert ranges_q == ranges_e2e
-        e2e_api = "gffx_intersect (C ABI) with GFFX_F_ASYNC, pinned host region arrays in, byte ranges copied back to page-locked host memory, two jobs in flight; every result waited for and read inside the timed region"
+        e2e_api = ("gffx_intersect" if c.world == 1 else "gffx_shard_begin / add / finish") + " (C ABI) with GFFX_F_ASYNC, pinned host region arrays in, byte ranges copied back to page-locked host memory, two jobs in flight; every result waited for and read inside the timed region"
     ceiling = h2d_ceiling(c, host_sets)
     pairs_total, launches_total, ranges_sum = allsum(c, [sum(a["pairs"] for a in tally.values()), sum(a["launches"] for a in tally.values()), ranges_e2e])
     c.dev_sets, c.host_sets = dev_sets, host_sets

@@ -1089,6 +1089,7 @@ void EngineImpl::ix_finish(IntersectResult* out) {
             if (le != cudaSuccess) { S.state = 0; throw Err(E_CUDA, std::string("kernel launch failed: ") + cudaGetErrorString(le)); }
         }
         out->pending_slot = jb.slot;
+        out->pend.host_in = jb.host_in;
         lane_activate(0);   // outside a job the engine's stream and buffers are lane 0's
         return;
     }
@@ -1337,12 +1338,14 @@ void Engine::shard_add(const uint32_t* chr, const uint32_t* start, const uint32_
     EngineImpl* E = impl_.get();
     if (n && (!chr || !start || !end)) throw Err(E_ARG, "NULL region arrays");
     if (!E->job.active) throw Err(E_STATE, "gffx_shard_add without gffx_shard_begin");
-    if (E->job.async && !(flags & 1u)) throw Err(E_ARG, "a GFFX_F_ASYNC job takes device-resident regions only (GFFX_F_DEVICE_INPUT)");
+    // a queued job copies host regions behind the call: no count can be handed back, the arrays stay the caller's until the wait
+    if (E->job.async && !(flags & 1u) && n_pairs_total) throw Err(E_ARG, "a GFFX_F_ASYNC job cannot report pair counts per batch (n_pairs_total must be NULL)");
+    if (E->job.async && !(flags & 1u)) E->job.host_in = true;
     GFFX_CUDA(cudaSetDevice(E->dev));
     const uint32_t *dc, *ds, *de;
     E->stage_queries(chr, start, end, n, flags, &dc, &ds, &de);
     E->ix_add(dc, ds, de, n);
-    if ((flags & 1u) && !n_pairs_total) return;  // device input, no count wanted: stays asynchronous (gffx.h: arrays live until finish / sync)
+    if (((flags & 1u) || E->job.async) && !n_pairs_total) return;  // device input (or a queued job), no count wanted: stays asynchronous (gffx.h: arrays live until finish / sync / wait)
     // the caller's arrays are free again when this returns
     GFFX_CUDA(cudaMemcpyAsync(E->h_small, E->d_small.p, 64, cudaMemcpyDeviceToHost, E->st));
     GFFX_CUDA(cudaStreamSynchronize(E->st));

@@ -70,6 +70,7 @@ struct IxJob {  // state of one intersect job between ix_begin and ix_finish
     int mode = 2;
     bool invert = false, entire_group = false, join_only = false, match_only = true, run_filter = false, have_types = false;
     bool pairs_dev = false, want_pairs_host = false, no_host = false, nothing = false, sealed = false;
+    bool host_in = false;        // a queued job whose regions are copied from host arrays behind the call
     bool stage_events = false;   // GFFX_F_STAGE_TIMES: per-stage CUDA events (stage_ms); otherwise only the call's whole span is timed
     uint64_t n_total = 0, retained = 0;
     unsigned long long pair_cap = 0;

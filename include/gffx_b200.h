@@ -285,7 +285,8 @@ typedef enum {
 } gffx_reduce_op;
 int gffx_shard_begin(gffx_index* idx, int mode, int invert, int entire_group, const char* types_csv, uint32_t flags,
                      uint64_t n_expected, uint32_t batches_expected);
-/* n_pairs_total (may be NULL): pairs counted so far by this shard.  The arrays may be reused when the call returns. */
+/* n_pairs_total (may be NULL): pairs counted so far by this shard.  The arrays may be reused when the call returns — except in a
+ * GFFX_F_ASYNC job, where host arrays are copied behind the call (n_pairs_total must be NULL) and stay the job's until the wait. */
 int gffx_shard_add(gffx_index* idx, const uint32_t* chr, const uint32_t* start, const uint32_t* end, uint64_t n, uint32_t flags,
                    uint64_t* n_pairs_total);
 int gffx_shard_finish(gffx_index* idx, gffx_result** out);

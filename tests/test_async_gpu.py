@@ -76,6 +76,10 @@ def test_queued_jobs_with_host_regions_and_host_ranges(gffx, quirk):
     same(p.wait(), w, "after abandoned results")
     with pytest.raises(gffx.GffxError):                      # pairs are not copied to the host behind a queued job
         idx.intersect(sets[0], 0, False, False, None, flags=FH | _lib.F_WANT_PAIRS)
+    # the batched form (gffx_shard_begin / add / finish), three batches of host regions per job, two jobs in flight
+    pend = [(k, idx.shard_intersect(sets[k % 4], m, i, e, t, batches=3, flags=FH)) for k, (m, i, e, t) in enumerate(cases[:6])]
+    for j, p in pend:
+        same(p.wait(copy=False), want[j], ("batched", cases[j]))
 
 
 def test_last_jobs_device_outputs_are_readable(quirk):
