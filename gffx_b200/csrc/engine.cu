@@ -82,7 +82,7 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     GFFX_CUDA(cudaStreamCreateWithFlags(&st_copy, cudaStreamNonBlocking));
     lanes[0].st = st;
     lanes[0].ready = true;
-    if (const char* e = getenv("GFFX_LANES")) n_lanes = atoi(e) >= 2 ? 2 : 1;   // A/B hook: 1 = every job on lane 0
+    if (const char* e = getenv("GFFX_LANES")) n_lanes = std::min((int)MAX_LANES, std::max(1, atoi(e)));   // A/B hook: 1 = every job on lane 0
     if (const char* e = getenv("GFFX_WJ_KERNEL")) wj_force = !strcmp(e, "rounds") ? 1 : !strcmp(e, "roots") ? 2 : 0;
     if (const char* e = getenv("GFFX_WR_SLICE")) wj_slices = atoi(e) != 0;
     if (const char* e = getenv("GFFX_WR_TAIL_BINS")) wj_tail_bins = (uint32_t)std::min(1 << 20, std::max(0, atoi(e)));
@@ -136,7 +136,9 @@ EngineImpl::~EngineImpl() {
 #endif
     for (Lane& l : lanes)
         if (l.st) cudaStreamSynchronize(l.st);
-    for (DBuf& b : lanes[1 - lane_active].bufs) b.release();   // the active lane's buffers are the members, released below
+    for (int k = 0; k < MAX_LANES; k++)   // the active lane's buffers are the members, released below
+        if (k != lane_active)
+            for (DBuf& b : lanes[k].bufs) b.release();
     for (DBuf* b : {&d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
                     &d_fX, &d_fdir, &d_fseqs, &d_wr_xw0, &d_wr_xlen, &d_wr_xoff, &d_A, &d_B, &d_Ms, &d_Me, &d_PMX, &d_SMN, &d_NS, &d_NE, &d_keep, &d_type_allow,
@@ -806,7 +808,7 @@ void EngineImpl::ix_begin(int mode, bool invert, bool entire_group, const char* 
     GFFX_CUDA(cudaSetDevice(dev));
     if ((flags & 32u) && n_lanes > 1) {   // queued jobs alternate between the lanes; everything else runs on lane 0
         lane_activate(lane_next);
-        lane_next ^= 1;
+        lane_next = (lane_next + 1) % n_lanes;
     } else {
         lane_activate(0);
     }

@@ -179,8 +179,8 @@ int gffx_intersect(gffx_index* idx, const uint32_t* chr, const uint32_t* start, 
  * gffx_query_features / gffx_intersect / gffx_shard_begin) the call returns as soon as the job is QUEUED on the engine's
  * stream, the 64 bytes of counters travel to a page-locked slot behind it, and the next job can be queued at once.
  * gffx_result_wait blocks until the counters are there (and reports the job's status, e.g. a bad sequence number); every
- * gffx_result_* accessor waits by itself when needed.  Queued jobs alternate between two LANES (two sets of the per-job
- * device state, two streams), so two of them run side by side on the GPU: the region arrays of a GFFX_F_ASYNC job must be
+ * gffx_result_* accessor waits by itself when needed.  Queued jobs rotate over three LANES (three sets of the per-job
+ * device state, three streams), so up to three of them run side by side on the GPU: the region arrays of a GFFX_F_ASYNC job must be
  * complete when the call is made (not merely queued on the engine's stream) and stay untouched until the wait.  Device
  * outputs (ranges for gffx_gather_text, pairs) stay valid until the handle's next job on the same lane, i.e. at least until the
  * next job is queued.  Between gffx_shard_begin and gffx_shard_finish of a queued job gffx_index_cuda_stream reports the
