@@ -1074,7 +1074,8 @@ void EngineImpl::ix_finish(IntersectResult* out) {
             const uint64_t cap = jb.match_only ? LA.n : n_blocks;
             if (cap) {
                 out->ranges.resize(cap * 2);
-                ranges_to_host_kernel<<<(unsigned)sm_count * 2, 256, 0, st>>>(d_ranges.as<ulonglong2>(), reinterpret_cast<ulonglong2*>(out->ranges.data()),
+                // a few dozen CTAs keep the link busy (16 to 296 measure the same); the fewer, the fewer thread slots the other lanes' kernels lose
+                ranges_to_host_kernel<<<(unsigned)std::max(1, sm_count / 4), 256, 0, st>>>(d_ranges.as<ulonglong2>(), reinterpret_cast<ulonglong2*>(out->ranges.data()),
                                                                             small + (jb.match_only ? 5 : 1), cap);
                 out->launches++;
                 out->pend.ranges_cap = cap;
