@@ -295,9 +295,9 @@ void counts_finish_impl(EngineImpl* E, CountRows* rows) {
     if (C->kind == 0) {
         const uint64_t ns = h.n_slots;
         C->launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, true>(
-            PtrLoad<uint32_t>{C->d_Hs.as<uint32_t>()}, PtrStore<uint32_t>{C->d_S.as<uint32_t>()}, ns, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
+            PtrLoad<uint32_t>{C->d_Hs.as<uint32_t>()}, PtrStore<uint32_t>{C->d_S.as<uint32_t>()}, ns, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st, nullptr, E->chain());
         C->launches += device_scan<uint32_t, OpSum, PtrLoad<uint32_t>, PtrStore<uint32_t>, false, true>(
-            PtrLoad<uint32_t>{C->d_He.as<uint32_t>()}, PtrStore<uint32_t>{C->d_E.as<uint32_t>()}, ns, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
+            PtrLoad<uint32_t>{C->d_He.as<uint32_t>()}, PtrStore<uint32_t>{C->d_E.as<uint32_t>()}, ns, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st, nullptr, E->chain());
         F.S = C->d_S.as<uint32_t>(); F.E = C->d_E.as<uint32_t>(); F.G = C->d_G.as<uint32_t>();
     } else {
         const uint64_t nw = h.n_words;
@@ -305,9 +305,10 @@ void counts_finish_impl(EngineImpl* E, CountRows* rows) {
         // came, its scan returns at once (a sharded job's arrays were combined with other shards': always scanned)
         C->launches += device_scan<int, OpSum, DiffLoad, CoverStore, false, true>(DiffLoad{C->d_diff.as<int>()}, CoverStore{C->d_bits.as<ull>()}, nw,
                                                                                 OpSum(), 0, C->d_scratch.as<int>(), nullptr, st,
-                                                                                C->exchanged ? nullptr : C->d_err.as<uint32_t>() + 4);
+                                                                                C->exchanged ? nullptr : C->d_err.as<uint32_t>() + 4, E->chain());
         C->launches += device_scan<uint32_t, OpSum, PopcLoad8, PtrStore<uint32_t>, false, false>(
-            PopcLoad8{C->d_bits.as<ull>()}, PtrStore<uint32_t>{C->d_P.as<uint32_t>()}, (nw + 7) / 8, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st);
+            PopcLoad8{C->d_bits.as<ull>()}, PtrStore<uint32_t>{C->d_P.as<uint32_t>()}, (nw + 7) / 8, OpSum(), 0u, C->d_scratch.as<uint32_t>(), nullptr, st, nullptr, E->chain(),
+            1024 /* 64 bytes per element: the bitmap is read once instead of twice */);
         F.bits = C->d_bits.as<ull>(); F.P = C->d_P.as<uint32_t>(); F.blk_routed = C->d_routed.as<uint8_t>();
     }
     RowArrays R{C->r_chrom.as<uint32_t>(), C->r_start.as<uint32_t>(), C->r_end.as<uint32_t>(), C->r_value.as<ull>(), C->r_flag.as<uint8_t>()};
@@ -317,7 +318,7 @@ void counts_finish_impl(EngineImpl* E, CountRows* rows) {
     C->launches++;
     uint32_t* d_total = C->d_err.as<uint32_t>() + 8;
     C->launches += device_scan<uint32_t, OpSum, FlagLoad, PtrStore<uint32_t>, false, false>(FlagLoad{R.flag}, PtrStore<uint32_t>{C->r_pos.as<uint32_t>()}, n_ids,
-                                                                                         OpSum(), 0u, C->d_scratch.as<uint32_t>(), d_total, st);
+                                                                                         OpSum(), 0u, C->d_scratch.as<uint32_t>(), d_total, st, nullptr, E->chain());
     GFFX_CUDA(cudaMemcpyAsync(E->h_small, d_total, 4, cudaMemcpyDeviceToHost, st));
     GFFX_CUDA(cudaStreamSynchronize(st));
     GFFX_CUDA(cudaGetLastError());

@@ -89,6 +89,12 @@ EngineImpl::EngineImpl(std::unique_ptr<HostIndex> host, int device) : H(std::mov
     for (auto& x : ev) GFFX_CUDA(cudaEventCreate(&x));
     GFFX_CUDA(cudaMallocHost(&h_small, 256));
     set_kernel_attributes();
+    if (!getenv("GFFX_SCAN_TWO_PASS")) {   // A/B hook: the reduce-then-scan form everywhere
+        d_chain_flags.total = &dev_bytes;
+        d_chain_flags.ensure((size_t)MAX_LANES * SCAN_CHAIN_TILES * 4);
+        GFFX_CUDA(cudaMemsetAsync(d_chain_flags.p, 0, (size_t)MAX_LANES * SCAN_CHAIN_TILES * 4, st));
+        for (int k = 0; k < MAX_LANES; k++) { chains[k].flags = d_chain_flags.as<uint32_t>() + (size_t)k * SCAN_CHAIN_TILES; chains[k].cap_tiles = SCAN_CHAIN_TILES; }
+    }
     noalloc_scratch = noalloc_scratch_address();   // once per engine = per device, this device current
     for (DBuf* b : {&d_bstart, &d_bend, &d_blk_sel,
                     &d_ln_flags, &d_ln_blk, &d_ln_type, &d_ln_iseq, &d_ln_S, &d_ln_E, &d_ln_iS, &d_ln_iE, &d_ln_off, &d_ln_len,
@@ -148,6 +154,7 @@ EngineImpl::~EngineImpl() {
                     &d_win0, &d_poff, &d_ptot, &d_pcur, &d_bse,
                     &d_q[0], &d_q[1], &d_q[2], &d_tile_count, &d_tile_off, &d_scan_scratch, &d_pairs, &d_ranges, &d_small, &d_warn})
         b->release();
+    d_chain_flags.release();
     counts_release(this);
     if (h_small) cudaFreeHost(h_small);
     for (auto& S : slots) {
@@ -789,7 +796,7 @@ uint32_t EngineImpl::expand_pairs(unsigned long long cap) {
     d_scan_scratch.ensure(scan_scratch_elems((uint64_t)wj_n_ent + 1) * 8);
     uint32_t launches = device_scan<ull, OpSum, WjCntLoad, PtrStore<ull>, false, false>(
         WjCntLoad{d_wj_cnt.as<ull>(), wj_n_ent}, PtrStore<ull>{d_wj_off.as<ull>()}, (uint64_t)wj_n_ent + 1, OpSum(), 0ull,
-        d_scan_scratch.as<ull>(), nullptr, st);
+        d_scan_scratch.as<ull>(), nullptr, st, nullptr, chain());
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     wj_expand_kernel<<<(unsigned)sms * 8, WJ_EXP_THREADS, 0, st>>>(d_wj_off.as<ull>(), WC.ent4, d_wj_base.as<uint32_t>(), wj_n_ent, d_pairs.as<uint32_t>(), cap);
@@ -946,18 +953,18 @@ uint32_t EngineImpl::ix_scans(FilterScans* Pout) {
     *Pout = FilterScans{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>(), F.any_inv, epoch};
     if (mode == 0 || mode == 2)
         launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
-                                                                                     OpMax(), 0ull, scr, nullptr, st);
+                                                                                     OpMax(), 0ull, scr, nullptr, st, nullptr, chain());
     if (mode == 1) {
         launches += device_scan<ull, OpMin, PtrLoad<ull>, PtrStore<ull>, true, true>(PtrLoad<ull>{F.B}, PtrStore<ull>{d_SMN.as<ull>()}, ns,
-                                                                                    OpMin(), ~0ull, scr, nullptr, st);
+                                                                                    OpMin(), ~0ull, scr, nullptr, st, nullptr, chain());
         fill_u64_kernel<<<1, 32, 0, st>>>(d_SMN.as<ull>() + ns, 1, ~0ull);  // SMN[iS+1] may index one past the last slot
         launches++;
     }
     if (mode == 2) {
         launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
-            MarkLoad{F.Ms, epoch8}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st);
+            MarkLoad{F.Ms, epoch8}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, nullptr, chain());
         launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
-            MarkLoad{F.Me, epoch8}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, F.any_inv);
+            MarkLoad{F.Me, epoch8}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, F.any_inv, chain());
     }
     return launches;
 }

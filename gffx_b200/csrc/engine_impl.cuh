@@ -141,6 +141,9 @@ class EngineImpl {
     };
     static constexpr int MAX_LANES = 4;
     Lane lanes[MAX_LANES];
+    ScanChain chains[MAX_LANES];   // the lanes' single-pass scan records (scan.cuh); chain() = the active lane's
+    DBuf d_chain_flags;
+    ScanChain* chain() { return chains[lane_active].flags ? &chains[lane_active] : nullptr; }
     int lane_active = 0, lane_next = 0, lane_last = 0, n_lanes = 3;   // three lanes: 1.15 -> 1.07 ms per four-pass step over two; a fourth adds nothing (r03g)
     uint32_t epoch_start = 0;
     std::vector<DBuf*> lane_bufs();
