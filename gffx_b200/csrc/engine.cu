@@ -410,6 +410,29 @@ void EngineImpl::build_blocks() {
     GFFX_CUDA(cudaStreamSynchronize(st));
 }
 
+// a piece of coordinates, ascending: three counting passes over 11-bit digits (a piece is a few ten thousand values: the digit
+// tables and both buffers stay in cache), std::sort below a few hundred values
+static void radix_sort_u32(uint32_t* v, size_t n) {
+    if (n < 512) { std::sort(v, v + n); return; }
+    static thread_local std::vector<uint32_t> tmp;
+    if (tmp.size() < n) tmp.resize(n);
+    uint32_t* a = v;
+    uint32_t* b = tmp.data();
+    uint32_t cnt[3][2048];
+    memset(cnt, 0, sizeof cnt);
+    for (size_t i = 0; i < n; i++) { const uint32_t x = a[i]; cnt[0][x & 2047u]++; cnt[1][(x >> 11) & 2047u]++; cnt[2][x >> 22]++; }
+    for (int p = 0; p < 3; p++) {
+        uint32_t* c = cnt[p];
+        if (p == 2 && c[a[0] >> 22] == n) break;   // the values share their top digit: two passes were enough
+        uint32_t run = 0;
+        for (int d = 0; d < 2048; d++) { const uint32_t k = c[d]; c[d] = run; run += k; }
+        const int sh = 11 * p;
+        for (size_t i = 0; i < n; i++) { const uint32_t x = a[i]; b[c[(x >> sh) & 2047u]++] = x; }
+        std::swap(a, b);
+    }
+    if (a != v) memcpy(v, a, n * 4);
+}
+
 // Lines + the filter rank space (see filter.cuh).
 void EngineImpl::build_lines() {
     const LineTable& L = H->lines;
@@ -424,8 +447,18 @@ void EngineImpl::build_lines() {
     // copies occupy their calling thread)
     d_ln_flags.ensure(std::max<size_t>(n, 1)); d_ln_blk.ensure(std::max<size_t>(n, 1) * 4); d_ln_type.ensure(std::max<size_t>(n, 1) * 4);
     d_ln_off.ensure(std::max<size_t>(n, 1) * 8); d_ln_len.ensure(std::max<size_t>(n, 1) * 4);
+    d_ln_iseq.ensure(std::max<size_t>(n, 1) * 4); d_ln_S.ensure(std::max<size_t>(n, 1) * 4); d_ln_E.ensure(std::max<size_t>(n, 1) * 4);
     cudaError_t up_err = cudaSuccess;
-    struct Joiner { std::thread t; ~Joiner() { if (t.joinable()) t.join(); } } early;
+    std::atomic<int> coords{0};   // 1: the lines' virtual coordinates are final (the helper uploads them too), -1: given up
+    struct Joiner {
+        std::thread t;
+        std::atomic<int>* coords;
+        ~Joiner() {
+            int none = 0;
+            coords->compare_exchange_strong(none, -1);   // leaving early (an exception): the helper must not wait for them
+            if (t.joinable()) t.join();
+        }
+    } early{std::thread(), &coords};
     early.t = std::thread([&] {
         auto put = [&](DBuf& b, const void* p, size_t bytes) {
             if (up_err == cudaSuccess && bytes) up_err = cudaMemcpyAsync(b.p, p, bytes, cudaMemcpyHostToDevice, st_copy);
@@ -433,6 +466,8 @@ void EngineImpl::build_lines() {
         up_err = cudaSetDevice(dev);
         put(d_ln_flags, L.flags.data(), n); put(d_ln_blk, L.blk.data(), n * 4); put(d_ln_type, L.type_id.data(), n * 4);
         put(d_ln_off, L.off.data(), n * 8); put(d_ln_len, L.len.data(), n * 4);
+        while (coords.load() == 0) std::this_thread::yield();
+        if (coords.load() == 1) { put(d_ln_iseq, vseq.data(), n * 4); put(d_ln_S, vS.data(), n * 4); put(d_ln_E, vE.data(), n * 4); }
         if (up_err == cudaSuccess) up_err = cudaStreamSynchronize(st_copy);
     });
     const size_t n_chunks = n >= (1u << 16) ? T : 1;   // the line table in T pieces of consecutive lines
@@ -450,6 +485,7 @@ void EngineImpl::build_lines() {
                 }
         });
     }
+    coords.store(1);
     std::vector<std::vector<uint32_t>> xs(n_seqs);
     {
         PhaseTimer t("  rank space: coordinate sets (sort)");
@@ -478,7 +514,7 @@ void EngineImpl::build_lines() {
                 for (size_t k; (k = next.fetch_add(1)) < jobs.size();) {
                     uint32_t* v = xs[jobs[k].s].data();
                     if (merge) std::inplace_merge(v + jobs[k].lo, v + jobs[k].mid, v + jobs[k].hi);
-                    else std::sort(v + jobs[k].lo, v + jobs[k].hi);
+                    else radix_sort_u32(v + jobs[k].lo, jobs[k].hi - jobs[k].lo);
                 }
             });
         };
@@ -630,9 +666,6 @@ void EngineImpl::build_lines() {
     });
     delete t_rank;
     PhaseTimer t_up("  line table upload");
-    upload(d_ln_iseq, vseq, st);
-    upload(d_ln_S, vS, st);
-    upload(d_ln_E, vE, st);
     upload(d_ln_iS, iS, st);
     upload(d_ln_iE, iE, st);
     upload(d_fX, X, st);
