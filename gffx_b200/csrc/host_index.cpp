@@ -437,13 +437,15 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
     }
     L.type_id.resize(total);
     L.chrom.resize(total);
-    std::vector<uint64_t> g_off(total);
+    const bool ids_ready = R.ids_ready;   // the device numbered the IDs (linescan.cu): L.id is filled, the entries are R.ids_off / ids_len
+    std::vector<uint64_t> g_off(ids_ready ? 0 : total);
     run_parallel(nparts, [&](size_t c) {
         const size_t i0 = total * c / nparts, i1 = total * (c + 1) / nparts;
         for (size_t i = i0; i < i1; i++) {
             const uint32_t ty = chunks[c].ty[i - i0], ch = chunks[c].ch[i - i0];
             L.type_id[i] = ty == NONE32 ? NONE32 : tmaps[c][ty];
             L.chrom[i] = ch == NONE32 ? NONE32 : cmaps[c][ch];
+            if (ids_ready) continue;
             const bool d = L.flags[i] & LN_D_OK;
             g_off[i] = d ? L.off[i] + R.id_off[i] : 0;
             if (!d) { R.id_len[i] = 0; R.id_hash[i] = 0; }
@@ -451,7 +453,15 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
     });
     t_tc.stop();
     PhaseTimer t_id("      ID dictionary");
-    number_ids(R.id_hash, g_off, R.id_len, threads);
+    if (ids_ready) {
+        if (L.id.size() != total) throw Err(E_STATE, "device line scan: ID column of the wrong length (internal)");
+        ids = IdTable();
+        ids.base = gff;
+        ids.off = std::move(R.ids_off);
+        ids.len = std::move(R.ids_len);
+    } else {
+        number_ids(R.id_hash, g_off, R.id_len, threads);
+    }
 }
 
 // ID dictionary: the lines are cut into `nshard` shards by hash; every shard finds, for each of its lines, the FIRST line

@@ -90,6 +90,11 @@ struct RawLines {
     std::vector<uint64_t> id_hash;
     std::vector<uint32_t> blk_nlines;
     std::vector<uint8_t> blk_nonascii;
+    // the ID dictionary when the device built it (linescan.cu; every block ASCII, no hash collision): t.id is filled, these are
+    // the dictionary's entries, and id_off / id_len / id_hash were not brought back
+    bool ids_ready = false;
+    std::vector<uint64_t> ids_off;
+    std::vector<uint32_t> ids_len;
 };
 
 struct HostIndex {
