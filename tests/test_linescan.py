@@ -90,6 +90,9 @@ def test_device_scanner_builds_the_host_scanners_table(gffx, synth_quirk_gff, sy
     dev = _info(gffx, path, 0, GFFX_CACHE=0, GFFX_LINE_SCAN="device")
     assert host[1] == 0 and dev[1] == 1
     assert dev[0] == host[0] and dev[2:] == host[2:]
+    # the device scan with the ID dictionary built by the host instead of the device kernels (the path a hash collision takes)
+    dev_h = _info(gffx, path, 0, GFFX_CACHE=0, GFFX_LINE_SCAN="device", GFFX_ID_DICT="host")
+    assert dev_h[1] == 1 and dev_h[0] == host[0] and dev_h[2:] == host[2:]
     # cold device scan -> cache -> warm open: the same table a third time
     d = str(tmp_path / "cache")
     os.makedirs(d)
