@@ -96,6 +96,8 @@ def test_last_jobs_device_outputs_are_readable(quirk):
 def test_two_lanes_overlap_and_keep_their_outputs(quirk):
     """queued jobs alternate between two lanes (own buffers, own streams): big enough to really run side by side; the device
     outputs of a job survive the job queued after it (the other lane's)"""
+    if os.environ.get("GFFX_LANES") == "1":
+        pytest.skip("one lane: a queued job's device outputs last until the next job")
     idx = quirk
     sets = [mixed_regions(idx, 40 + k, 300_000) for k in range(3)]
     dsets = [dev(s) for s in sets]
