@@ -411,6 +411,22 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
         }
     }
     t_na.stop();
+    if (R.ids_ready) {
+        // the device built all three dictionaries (linescan.cu: every block ASCII, no two strings under one hash): the lines' id /
+        // type_id / chrom columns are filled, the entries arrive in order of first appearance as (offset, length) into the text
+        PhaseTimer t_dev("      dictionaries (from the device's entries)");
+        if (L.id.size() != total || L.type_id.size() != total || L.chrom.size() != total)
+            throw Err(E_STATE, "device line scan: a dictionary column of the wrong length (internal)");
+        for (size_t k = 0; k < R.types_off.size(); k++)
+            if (types.intern(std::string_view((const char*)gff + R.types_off[k], R.types_len[k])) != k) throw Err(E_STATE, "device line scan: type dictionary out of order (internal)");
+        for (size_t k = 0; k < R.chroms_off.size(); k++)
+            if (chroms.intern(std::string_view((const char*)gff + R.chroms_off[k], R.chroms_len[k])) != k) throw Err(E_STATE, "device line scan: chromosome dictionary out of order (internal)");
+        ids = IdTable();
+        ids.base = gff;
+        ids.off = std::move(R.ids_off);
+        ids.len = std::move(R.ids_len);
+        return;
+    }
     PhaseTimer t_tc("      type / chromosome dictionaries");
     // type / chromosome dictionaries: chunks of lines side by side, each with its own dictionary in order of appearance; the
     // chunks' dictionaries are merged in chunk order, which numbers every string by its first appearance in the file
@@ -437,15 +453,13 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
     }
     L.type_id.resize(total);
     L.chrom.resize(total);
-    const bool ids_ready = R.ids_ready;   // the device numbered the IDs (linescan.cu): L.id is filled, the entries are R.ids_off / ids_len
-    std::vector<uint64_t> g_off(ids_ready ? 0 : total);
+    std::vector<uint64_t> g_off(total);
     run_parallel(nparts, [&](size_t c) {
         const size_t i0 = total * c / nparts, i1 = total * (c + 1) / nparts;
         for (size_t i = i0; i < i1; i++) {
             const uint32_t ty = chunks[c].ty[i - i0], ch = chunks[c].ch[i - i0];
             L.type_id[i] = ty == NONE32 ? NONE32 : tmaps[c][ty];
             L.chrom[i] = ch == NONE32 ? NONE32 : cmaps[c][ch];
-            if (ids_ready) continue;
             const bool d = L.flags[i] & LN_D_OK;
             g_off[i] = d ? L.off[i] + R.id_off[i] : 0;
             if (!d) { R.id_len[i] = 0; R.id_hash[i] = 0; }
@@ -453,15 +467,7 @@ void HostIndex::lines_from_raw(RawLines& R, int threads) {
     });
     t_tc.stop();
     PhaseTimer t_id("      ID dictionary");
-    if (ids_ready) {
-        if (L.id.size() != total) throw Err(E_STATE, "device line scan: ID column of the wrong length (internal)");
-        ids = IdTable();
-        ids.base = gff;
-        ids.off = std::move(R.ids_off);
-        ids.len = std::move(R.ids_len);
-    } else {
-        number_ids(R.id_hash, g_off, R.id_len, threads);
-    }
+    number_ids(R.id_hash, g_off, R.id_len, threads);
 }
 
 // ID dictionary: the lines are cut into `nshard` shards by hash; every shard finds, for each of its lines, the FIRST line

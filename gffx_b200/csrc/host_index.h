@@ -92,9 +92,10 @@ struct RawLines {
     std::vector<uint8_t> blk_nonascii;
     // the ID dictionary when the device built it (linescan.cu; every block ASCII, no hash collision): t.id is filled, these are
     // the dictionary's entries, and id_off / id_len / id_hash were not brought back
+    // (the same for the type and chromosome dictionaries: t.type_id / t.chrom are filled, type_off / type_len / chrom_len stayed behind)
     bool ids_ready = false;
-    std::vector<uint64_t> ids_off;
-    std::vector<uint32_t> ids_len;
+    std::vector<uint64_t> ids_off, types_off, chroms_off;
+    std::vector<uint32_t> ids_len, types_len, chroms_len;
 };
 
 struct HostIndex {

@@ -189,51 +189,70 @@ __global__ void __launch_bounds__(LS_THREADS) ls_parse_kernel(const uint8_t* __r
     O.id_hash[i] = id_hash;
 }
 
-// ---- the ID dictionary on the device (r03i) -----------------------------------------------------------------------------------
-// An ID's number is the rank of its FIRST line among all first lines (host_index.cpp: number_ids).  Open-addressing table keyed
-// by the ID's FNV-1a hash, value = the smallest line number carrying it (atomicMin); every line then looks its first line up and
-// compares its ID bytes with that line's — two different IDs under one 64-bit hash, or anything else that does not compare
-// equal, raises `bad` and the host builds the dictionary instead.  First lines are numbered by a scan.
-struct LsIds {
+// ---- the dictionaries on the device (r03i: IDs, r03k: types and chromosomes) ---------------------------------------------------
+// A string's number is the rank of its FIRST line among all first lines (host_index.cpp: number_ids; the type / chromosome pools
+// number the same way).  Open-addressing table keyed by the string's FNV-1a hash, value = the smallest line number carrying it
+// (atomicMin); every line then looks its first line up and compares its bytes with that line's — two different strings under
+// one 64-bit hash, or anything else that does not compare equal, raises `bad` and the host builds the dictionaries instead.
+// First lines are numbered by a scan.  FIELD: 0 the ID value (lines that count for depth / coverage), 1 the type column (every
+// line that has one), 2 column 1 of the lines that count.
+struct LsDict {
     const uint8_t* text;
     const unsigned long long* off;   // line offsets
     const uint8_t* flags;
     const uint32_t* id_off;
     const uint32_t* id_len;
     const unsigned long long* id_hash;
+    const uint32_t* type_off;
+    const uint32_t* type_len;
+    const uint32_t* chrom_len;
     unsigned long long* keys;        // table: 0 = empty
     uint32_t* vals;                  // table: smallest line number of the key
     uint32_t mask;
-    uint32_t* first;                 // per line: its ID's first line, NONE32 without an ID
+    uint32_t* first;                 // per line: its string's first line, NONE32 without one
     uint64_t n;
 };
-__device__ __forceinline__ unsigned long long ls_id_key(unsigned long long h) { return h ? h : 1ull; }
+template <int FIELD> __device__ __forceinline__ bool ls_field(const LsDict& D, uint64_t i, uint32_t* fo, uint32_t* fl) {
+    if (FIELD == 0) { *fo = D.id_off[i]; *fl = D.id_len[i]; return D.flags[i] & LN_D_OK; }
+    if (FIELD == 1) { *fo = D.type_off[i]; *fl = D.type_len[i]; return *fl != 0xFFFFFFFFu; }
+    *fo = 0; *fl = D.chrom_len[i];
+    return (D.flags[i] & LN_D_OK) && *fl != 0xFFFFFFFFu;
+}
+template <int FIELD> __device__ __forceinline__ unsigned long long ls_field_key(const LsDict& D, uint64_t i, uint32_t fo, uint32_t fl) {
+    const unsigned long long h = FIELD == 0 ? D.id_hash[i] : ls_fnv(D.text + D.off[i] + fo, fl);
+    return h ? h : 1ull;
+}
 
-__global__ void __launch_bounds__(256) ls_ids_insert_kernel(LsIds D) {
+template <int FIELD> __global__ void __launch_bounds__(256) ls_dict_insert_kernel(LsDict D) {
     const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= D.n || !(D.flags[i] & LN_D_OK)) return;
-    const unsigned long long h = ls_id_key(D.id_hash[i]);
+    uint32_t fo, fl;
+    if (i >= D.n || !ls_field<FIELD>(D, i, &fo, &fl)) return;
+    const unsigned long long h = ls_field_key<FIELD>(D, i, fo, fl);
     for (uint32_t s = (uint32_t)h & D.mask;; s = (s + 1) & D.mask) {
-        const unsigned long long prev = atomicCAS(D.keys + s, 0ull, h);
-        if (prev == 0ull || prev == h) { atomicMin(D.vals + s, (uint32_t)i); return; }
+        unsigned long long prev = D.keys[s];   // a few strings on millions of lines (types): most probes find their key already there
+        if (prev == 0ull) prev = atomicCAS(D.keys + s, 0ull, h);
+        if (prev == 0ull || prev == h) {
+            if (D.vals[s] > (uint32_t)i) atomicMin(D.vals + s, (uint32_t)i);
+            return;
+        }
     }
 }
-__global__ void __launch_bounds__(256) ls_ids_first_kernel(LsIds D, uint8_t* __restrict__ is_first, uint32_t* __restrict__ bad) {
+template <int FIELD> __global__ void __launch_bounds__(256) ls_dict_first_kernel(LsDict D, uint8_t* __restrict__ is_first, uint32_t* __restrict__ bad) {
     const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
     if (i >= D.n) return;
-    uint32_t f = 0xFFFFFFFFu;
-    if (D.flags[i] & LN_D_OK) {
-        const unsigned long long h = ls_id_key(D.id_hash[i]);
+    uint32_t f = 0xFFFFFFFFu, fo, fl;
+    if (ls_field<FIELD>(D, i, &fo, &fl)) {
+        const unsigned long long h = ls_field_key<FIELD>(D, i, fo, fl);
         uint32_t s = (uint32_t)h & D.mask;
         while (D.keys[s] != h) s = (s + 1) & D.mask;   // present: inserted by the kernel before
         f = D.vals[s];
-        if (f != (uint32_t)i) {   // the same bytes as the first line's ID?
-            const uint32_t l = D.id_len[i];
-            bool same = f < i && (D.flags[f] & LN_D_OK) && D.id_len[f] == l;
+        if (f != (uint32_t)i) {   // the same bytes as the first line's string?
+            uint32_t go, gl;
+            bool same = f < i && ls_field<FIELD>(D, f, &go, &gl) && gl == fl;
             if (same) {
-                const uint8_t* a = D.text + D.off[i] + D.id_off[i];
-                const uint8_t* b = D.text + D.off[f] + D.id_off[f];
-                for (uint32_t k = 0; k < l; k++) same = same && a[k] == b[k];
+                const uint8_t* a = D.text + D.off[i] + fo;
+                const uint8_t* b = D.text + D.off[f] + go;
+                for (uint32_t k = 0; k < fl; k++) same = same && a[k] == b[k];
             }
             if (!same) *bad = 1;
         }
@@ -245,16 +264,22 @@ struct U8Load {
     const uint8_t* p;
     __device__ uint32_t operator()(uint64_t i) const { return p[i]; }
 };
-// rank[i] = first lines before line i.  Line i's ID number = rank[first[i]]; a first line also files its ID's place in the text
-__global__ void __launch_bounds__(256) ls_ids_number_kernel(LsIds D, const uint32_t* __restrict__ rank, uint32_t* __restrict__ id,
-                                                            unsigned long long* __restrict__ ids_off, uint32_t* __restrict__ ids_len) {
+// rank[i] = first lines before line i.  Line i's number = rank[first[i]]; a first line also files its string's place in the text
+template <int FIELD>
+__global__ void __launch_bounds__(256) ls_dict_number_kernel(LsDict D, const uint32_t* __restrict__ rank, uint32_t* __restrict__ id,
+                                                             unsigned long long* __restrict__ ent_off, uint32_t* __restrict__ ent_len) {
     const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
     if (i >= D.n) return;
     const uint32_t f = D.first[i];
     if (f == 0xFFFFFFFFu) { id[i] = 0xFFFFFFFFu; return; }
     const uint32_t r = rank[f];
     id[i] = r;
-    if (f == (uint32_t)i) { ids_off[r] = D.off[i] + D.id_off[i]; ids_len[r] = D.id_len[i]; }
+    if (f == (uint32_t)i) {
+        uint32_t fo, fl;
+        ls_field<FIELD>(D, i, &fo, &fl);
+        ent_off[r] = D.off[i] + fo;
+        ent_len[r] = fl;
+    }
 }
 
 template <class T> void download(std::vector<T>& v, const DBuf& b, size_t n, cudaStream_t st) {
@@ -421,40 +446,57 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
     GFFX_CUDA(cudaGetLastError());
     // ---- the ID dictionary, on the device when every block is ASCII (a block with other bytes is re-scanned by the host, which
     // may see its ID fields differently) ----------------------------------------------------------------------------------------
-    DBuf i_keys, i_vals, i_first, i_isfirst, i_rank, i_id, i_idsoff, i_idslen, i_bad;
-    for (DBuf* b : {&i_keys, &i_vals, &i_first, &i_isfirst, &i_rank, &i_id, &i_idsoff, &i_idslen, &i_bad}) temps.push_back(b);
+    DBuf ibuf;   // one allocation for everything below (the i_* are views into it)
+    temps.push_back(&ibuf);
+    DBuf i_keys, i_vals, i_first, i_isfirst, i_rank, i_bad, i_id[3], i_entoff[3], i_entlen[3];
     bool dev_ids = false;
-    uint32_t n_ids = 0;
+    uint32_t n_ent[3] = {0, 0, 0};   // IDs, types, chromosomes
     {
-        const char* e = getenv("GFFX_ID_DICT");   // "host": the host builds it (A/B runs, tests)
+        const char* e = getenv("GFFX_ID_DICT");   // "host": the host builds the dictionaries (A/B runs, tests)
         download(R.blk_nonascii, na, nb, st);
         GFFX_CUDA(cudaStreamSynchronize(st));
         bool ascii = true;
         for (uint8_t x : R.blk_nonascii) ascii = ascii && !x;
         if (L && ascii && !(e && !strcmp(e, "host"))) {
-            PhaseTimer t_ids("      ID dictionary (device)");
+            PhaseTimer t_ids("      dictionaries (device)");
             size_t cap = 1024;
             while (cap < 2 * L) cap <<= 1;
-            i_keys.ensure(cap * 8); i_vals.ensure(cap * 4); i_first.ensure(L * 4); i_isfirst.ensure(L); i_rank.ensure(L * 4 + 4); i_id.ensure(L * 4);
-            i_idsoff.ensure(L * 8); i_idslen.ensure(L * 4); i_bad.ensure(8);
-            GFFX_CUDA(cudaMemsetAsync(i_keys.p, 0, cap * 8, st));
-            GFFX_CUDA(cudaMemsetAsync(i_vals.p, 0xFF, cap * 4, st));
-            GFFX_CUDA(cudaMemsetAsync(i_bad.p, 0, 8, st));
-            const LsIds D{text.as<uint8_t>(), off.as<ull>(), o_flags.as<uint8_t>(), o_ioff.as<uint32_t>(), o_ilen.as<uint32_t>(), o_ihash.as<ull>(),
-                          i_keys.as<ull>(), i_vals.as<uint32_t>(), (uint32_t)cap - 1, i_first.as<uint32_t>(), (uint64_t)L};
-            const unsigned g = (unsigned)((L + 255) / 256);
-            ls_ids_insert_kernel<<<g, 256, 0, st>>>(D);
-            ls_ids_first_kernel<<<g, 256, 0, st>>>(D, i_isfirst.as<uint8_t>(), i_bad.as<uint32_t>());
+            {
+                struct Part { DBuf* b; size_t bytes; };
+                const Part parts[] = {{&i_keys, cap * 8}, {&i_vals, cap * 4}, {&i_entoff[0], L * 8}, {&i_entoff[1], L * 8}, {&i_entoff[2], L * 8}, {&i_first, L * 4},
+                                      {&i_rank, L * 4 + 4}, {&i_id[0], L * 4}, {&i_id[1], L * 4}, {&i_id[2], L * 4}, {&i_entlen[0], L * 4}, {&i_entlen[1], L * 4},
+                                      {&i_entlen[2], L * 4}, {&i_isfirst, L}, {&i_bad, 16}};
+                size_t total = 0;
+                for (const Part& q : parts) total += (q.bytes + 255) & ~(size_t)255;
+                ibuf.ensure(total);
+                size_t o = 0;
+                for (const Part& q : parts) { q.b->p = (uint8_t*)ibuf.p + o; q.b->cap = 0; o += (q.bytes + 255) & ~(size_t)255; }
+            }
+            GFFX_CUDA(cudaMemsetAsync(i_bad.p, 0, 16, st));
             scratch.ensure(scan_scratch_elems(L) * 4 + 64);
-            device_scan<uint32_t, OpSum, U8Load, PtrStore<uint32_t>, false, false>(U8Load{i_isfirst.as<uint8_t>()}, PtrStore<uint32_t>{i_rank.as<uint32_t>()}, L, OpSum(),
-                                                                                  0u, scratch.as<uint32_t>(), i_bad.as<uint32_t>() + 1, st);
-            ls_ids_number_kernel<<<g, 256, 0, st>>>(D, i_rank.as<uint32_t>(), i_id.as<uint32_t>(), i_idsoff.as<ull>(), i_idslen.as<uint32_t>());
-            uint32_t res[2] = {1, 0};
-            GFFX_CUDA(cudaMemcpyAsync(res, i_bad.p, 8, cudaMemcpyDeviceToHost, st));
+            const LsDict D{text.as<uint8_t>(), off.as<ull>(), o_flags.as<uint8_t>(), o_ioff.as<uint32_t>(), o_ilen.as<uint32_t>(), o_ihash.as<ull>(),
+                           o_toff.as<uint32_t>(), o_tlen.as<uint32_t>(), o_clen.as<uint32_t>(),
+                           i_keys.as<ull>(), i_vals.as<uint32_t>(), (uint32_t)cap - 1, i_first.as<uint32_t>(), (uint64_t)L};
+            const unsigned g = (unsigned)((L + 255) / 256);
+            uint32_t* bad = i_bad.as<uint32_t>();
+            auto run = [&](int f, auto ins, auto fst, auto num) {
+                GFFX_CUDA(cudaMemsetAsync(i_keys.p, 0, cap * 8, st));
+                GFFX_CUDA(cudaMemsetAsync(i_vals.p, 0xFF, cap * 4, st));
+                ins<<<g, 256, 0, st>>>(D);
+                fst<<<g, 256, 0, st>>>(D, i_isfirst.as<uint8_t>(), bad);
+                device_scan<uint32_t, OpSum, U8Load, PtrStore<uint32_t>, false, false>(U8Load{i_isfirst.as<uint8_t>()}, PtrStore<uint32_t>{i_rank.as<uint32_t>()}, L,
+                                                                                      OpSum(), 0u, scratch.as<uint32_t>(), bad + 1 + f, st);
+                num<<<g, 256, 0, st>>>(D, i_rank.as<uint32_t>(), i_id[f].as<uint32_t>(), i_entoff[f].as<ull>(), i_entlen[f].as<uint32_t>());
+            };
+            run(0, ls_dict_insert_kernel<0>, ls_dict_first_kernel<0>, ls_dict_number_kernel<0>);
+            run(1, ls_dict_insert_kernel<1>, ls_dict_first_kernel<1>, ls_dict_number_kernel<1>);
+            run(2, ls_dict_insert_kernel<2>, ls_dict_first_kernel<2>, ls_dict_number_kernel<2>);
+            uint32_t res[4] = {1, 0, 0, 0};
+            GFFX_CUDA(cudaMemcpyAsync(res, i_bad.p, 16, cudaMemcpyDeviceToHost, st));
             GFFX_CUDA(cudaStreamSynchronize(st));
             GFFX_CUDA(cudaGetLastError());
-            dev_ids = res[0] == 0;   // otherwise: two IDs under one hash — the host's dictionary compares bytes on every probe
-            n_ids = res[1];
+            dev_ids = res[0] == 0;   // otherwise: two strings under one hash — the host's dictionaries compare bytes on every probe
+            for (int f = 0; f < 3; f++) n_ent[f] = res[1 + f];
         }
     }
     {
@@ -463,10 +505,15 @@ bool device_scan_lines(const HostIndex& H, int device, int threads, RawLines* ou
         std::vector<std::function<void(cudaStream_t)>> jobs;
         auto col = [&](auto& v, const DBuf& b, size_t cnt) { jobs.push_back([&v, &b, cnt](cudaStream_t s) { download(v, b, cnt, s); }); };
         col(R.t.off, off, L); col(R.t.blk, blk, L); col(R.t.len, o_len, L); col(R.t.flags, o_flags, L);
-        if (dev_ids) { col(R.t.id, i_id, L); col(R.ids_off, i_idsoff, n_ids); col(R.ids_len, i_idslen, n_ids); }
-        else { col(R.id_hash, o_ihash, L); col(R.id_off, o_ioff, L); col(R.id_len, o_ilen, L); }
+        if (dev_ids) {
+            col(R.t.id, i_id[0], L); col(R.ids_off, i_entoff[0], n_ent[0]); col(R.ids_len, i_entlen[0], n_ent[0]);
+            col(R.t.type_id, i_id[1], L); col(R.types_off, i_entoff[1], n_ent[1]); col(R.types_len, i_entlen[1], n_ent[1]);
+            col(R.t.chrom, i_id[2], L); col(R.chroms_off, i_entoff[2], n_ent[2]); col(R.chroms_len, i_entlen[2], n_ent[2]);
+        } else {
+            col(R.id_hash, o_ihash, L); col(R.id_off, o_ioff, L); col(R.id_len, o_ilen, L);
+            col(R.type_off, o_toff, L); col(R.type_len, o_tlen, L); col(R.chrom_len, o_clen, L);
+        }
         col(R.t.S, o_S, L); col(R.t.E, o_E, L); col(R.t.iseq, o_iseq, L); col(R.t.fs, o_fs, L); col(R.t.fe, o_fe, L);
-        col(R.type_off, o_toff, L); col(R.type_len, o_tlen, L); col(R.chrom_len, o_clen, L);
         col(R.blk_nlines, nl, nb);
         const int W = std::max(1, std::min(threads, 6));
         std::vector<std::string> werr((size_t)W);
