@@ -209,7 +209,7 @@ static void counts_add_device(EngineImpl* E, CountsState* C, const CountsDev& D,
         const unsigned grid = (unsigned)(n / DW_RUN) + E->WC.n_win + 1;
         depth_window_kernel<<<grid, DW_THREADS, DW_SMEM, E->st>>>(D, W, ose, C->d_err.as<uint32_t>());
     } else {
-        coverage_scatter_kernel<<<(unsigned)((n + CV_TILE - 1) / CV_TILE), CV_THREADS, 0, E->st>>>(D, E->WC.win_seq, E->d_poff.as<uint32_t>(), E->WC.n_win, ose, n,
+        coverage_scatter_kernel<<<(unsigned)((n + CV_TILE - 1) / CV_TILE), CV_THREADS, 0, E->st>>>(D, E->WC.win_seq, E->WC.win0, E->WC.shift, E->d_poff.as<uint32_t>(), E->WC.n_win, ose, n,
                                                                                                   C->d_err.as<uint32_t>());
     }
     C->launches += 1;

@@ -158,13 +158,15 @@ __device__ __forceinline__ void cov_space_update(const CountsDev& D, uint32_t sp
 // overlaps its tree interval" is "some base of the interval is covered", which counts_rows_kernel reads off the bitmap.  Only
 // the tree intervals of irregular blocks are looked up (a handful, usually none): their private spaces take the regions
 // routed to them (OR / +-1 updates tolerate repeats: no dedup needed).
+constexpr uint32_t CV_IRR_CAP = 16;
 constexpr uint32_t CV_THREADS = 256;
 constexpr uint32_t CV_TILE = 4096;
 
 static __global__ void __launch_bounds__(CV_THREADS)
-    coverage_scatter_kernel(CountsDev D, const uint32_t* __restrict__ win_seq, const uint32_t* __restrict__ poff, uint32_t n_win, const uint2* __restrict__ se,
-                            uint64_t n, uint32_t* __restrict__ err) {
+    coverage_scatter_kernel(CountsDev D, const uint32_t* __restrict__ win_seq, const uint32_t* __restrict__ win0, uint32_t shift,
+                            const uint32_t* __restrict__ poff, uint32_t n_win, const uint2* __restrict__ se, uint64_t n, uint32_t* __restrict__ err) {
     __shared__ uint32_t s_wf, s_wl;
+    __shared__ uint32_t s_irr_j[CV_IRR_CAP], s_irr_s[CV_IRR_CAP], s_irr_e[CV_IRR_CAP], s_nirr;   // the irregular tree intervals that touch the window at hand
     const uint32_t tile0 = blockIdx.x * CV_TILE, m = (uint32_t)min((uint64_t)CV_TILE, n - tile0);
     {   // windows of the tile's first and last region: (number of window offsets <= position) - 1; poff has n_win + 2 cells
         int nf = 0, nl = 0;
@@ -183,17 +185,41 @@ static __global__ void __launch_bounds__(CV_THREADS)
         if (w >= n_win) { if (threadIdx.x == 0) *err = 1; continue; }   // regions whose sequence number is out of range
         const uint32_t sp = __ldg(win_seq + w);
         const bool irr = __ldg(D.irr_seq0 + sp) != __ldg(D.irr_seq0 + sp + 1);
+        // a region that ends inside the window can only hit irregular tree intervals that touch the window: found once per
+        // (tile, window) instead of a search over the sequence's list per region (depth_window_kernel does the same)
+        const uint32_t lo_w = (w - __ldg(win0 + sp)) << shift;
+        const uint32_t hi_w = (w + 1 == __ldg(win0 + sp + 1)) ? 0xFFFFFFFFu : lo_w + (1u << shift);
+        if (irr) {
+            __syncthreads();   // the previous window's candidates are no longer read
+            if (threadIdx.x == 0) {
+                uint32_t k = 0;
+                irr_query(D, sp, lo_w, hi_w, [&](uint32_t j) {
+                    if (k < CV_IRR_CAP) { s_irr_j[k] = j; s_irr_s[k] = __ldg(D.irr_s + j); s_irr_e[k] = __ldg(D.irr_e + j); }
+                    k++;
+                });
+                s_nirr = k;
+            }
+            __syncthreads();
+        }
         for (uint32_t p = p_lo + threadIdx.x; p < p_hi; p += CV_THREADS) {
             const uint2 r = __ldcs(se + p);
             if (r.x >= r.y) continue;
             cov_space_update(D, sp, r.x, r.y);
-            if (irr)
-                irr_query(D, sp, r.x, r.y, [&](uint32_t j) {
+            if (irr) {
+                auto hit = [&](uint32_t j) {
                     const uint32_t blk = __ldg(D.irr_blk + j);
                     if (!D.blk_routed[blk]) D.blk_routed[blk] = 1;
                     const uint32_t vb = __ldg(D.irr_base + j);
                     cov_space_update(D, __ldg(D.irr_space + j), r.x - vb, r.y - vb);
-                });
+                };
+                const uint32_t nirr = s_nirr;
+                if (nirr <= CV_IRR_CAP && r.y <= hi_w) {
+                    for (uint32_t k = 0; k < nirr; k++)
+                        if (s_irr_s[k] < r.y && s_irr_e[k] > r.x) hit(s_irr_j[k]);
+                } else {
+                    irr_query(D, sp, r.x, r.y, hit);
+                }
+            }
         }
     }
 }
@@ -211,6 +237,8 @@ constexpr uint32_t DW_THREADS = 512;
 constexpr uint32_t DW_RUN = 15u * 4096u;   // reads per CTA: below 2^16 (16-bit histogram cells), a multiple of the partition tile
 constexpr uint32_t DW_GAPW = (WR_SLICE_CAP + 8) / 32 + 2;   // words of the window's gap-start bits
 constexpr size_t DW_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)WR_XOFF_STRIDE * 2 + 2 * (size_t)(WR_SLICE_CAP + 8) * 2 + (size_t)DW_GAPW * 4;
+
+constexpr uint32_t DW_IRR_CAP = 16;   // irregular tree intervals of one window kept in shared memory (more: every read searches the sequence's list)
 
 struct DepthWin {
     const uint32_t* win_seq;   // window -> (virtual) sequence = space
@@ -231,6 +259,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
     uint32_t* const sgap = he + (WR_SLICE_CAP + 8) / 2;   // bit j: the part's value j starts a gap (counts_index.h: gap_bits)
     __shared__ uint32_t scan[DW_THREADS / 32 + 1];
     __shared__ uint32_t s_w, s_run;
+    __shared__ uint32_t s_irr_j[DW_IRR_CAP], s_irr_s[DW_IRR_CAP], s_irr_e[DW_IRR_CAP], s_nirr;   // the irregular tree intervals that touch this window
     __shared__ __align__(8) uint64_t mbar;
     const uint32_t tid = threadIdx.x;
     // run table: a block scan of the windows' run counts (n_win <= 511: a window per thread)
@@ -247,6 +276,18 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
     const uint32_t sp = __ldg(W.win_seq + w);
     const uint32_t lo = (w - __ldg(W.win0 + sp)) << W.shift, fsh = W.shift - WR_FB;
     const RankSeq RS = load_rank_seq(D.R, sp);
+    // a read that ends inside the window can only hit irregular tree intervals that touch the window: usually none, a few at most —
+    // found once per CTA instead of a binary search over the sequence's list per read (10 % of the kernel's instructions, r03j)
+    const uint32_t hi_w = (w + 1 == __ldg(W.win0 + sp + 1)) ? 0xFFFFFFFFu : lo + (1u << W.shift);   // the last window takes every later start
+    if (W.any_irregular && tid == 0) {
+        uint32_t k = 0;
+        irr_query(D, sp, lo, hi_w, [&](uint32_t j) {
+            if (k < DW_IRR_CAP) { s_irr_j[k] = j; s_irr_s[k] = __ldg(D.irr_s + j); s_irr_e[k] = __ldg(D.irr_e + j); }
+            k++;
+        });
+        s_nirr = k;
+    }
+    if (W.any_irregular) __syncthreads();
     const uint32_t xlen = __ldg(W.XS.xlen + w), xw0 = __ldg(W.XS.xw0 + w);
     const bool sliced = RS.cnt != 0 && xlen != 0xFFFFFFFFu;
     if (sliced) {
@@ -300,8 +341,8 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
                     if (__ldg(D.gap_b + g) < re) atomicAdd(D.G + __ldg(D.gap_seg + g), 1u);
                 }
         }
-        if (W.any_irregular)
-            irr_query(D, sp, rs, re, [&](uint32_t j) {
+        if (W.any_irregular) {
+            auto hit = [&](uint32_t j) {
                 const uint32_t g = __ldg(D.irr_grp + j);   // a root fid with several tree intervals is routed once per region (depth.rs:239-241)
                 if (g != 0xFFFFFFFFu) {
                     const uint32_t m0 = __ldg(D.grp_off + g), m1 = m0 + __ldg(D.irr_pos + j);
@@ -310,7 +351,15 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
                 }
                 const uint32_t vb = __ldg(D.irr_base + j);
                 depth_space_update(D, __ldg(D.irr_space + j), rs - vb, re - vb);
-            });
+            };
+            const uint32_t nirr = s_nirr;
+            if (nirr <= DW_IRR_CAP && re <= hi_w) {   // start >= the window's first base: only the window's own candidates can be hit
+                for (uint32_t k = 0; k < nirr; k++)
+                    if (s_irr_s[k] < re && s_irr_e[k] > rs) hit(s_irr_j[k]);
+            } else {
+                irr_query(D, sp, rs, re, hit);
+            }
+        }
     }
     if (!sliced) return;
     __syncthreads();
