@@ -54,10 +54,10 @@ static void build_counts(EngineImpl* E, CountsState* C) {
     upload(C->d_rank, h.rank, st);
     upload(C->d_cov, h.cov, st);
     {   // per window of the partition grid: its part of the sequence space's coordinate set + fine-bin offsets (rootjoin.cuh: RankSlices)
-        const uint32_t n_win = E->WG.n_win, shift = E->WG.shift, fsh = shift - WR_FB;
+        const uint32_t n_win = E->WG.n_win, shift = E->WG.shift, fsh = shift - DW_FB;
         const size_t n_v = E->H->vmap.n_vseqs();
         std::vector<uint32_t> xw0(std::max<uint32_t>(n_win, 1), 0), xlen(std::max<uint32_t>(n_win, 1), 0xFFFFFFFFu);
-        std::vector<uint16_t> xoff((size_t)std::max<uint32_t>(n_win, 1) * WR_XOFF_STRIDE, 0);
+        std::vector<uint16_t> xoff((size_t)std::max<uint32_t>(n_win, 1) * DW_XOFF_STRIDE, 0);
         for (size_t v = 0; v < n_v; v++) {
             const uint32_t* xv = h.X.data() + h.rank[v].x0;
             const size_t cnt = h.rank[v].cnt;
@@ -69,9 +69,9 @@ static void build_counts(EngineImpl* E, CountsState* C) {
                 xw0[w] = h.rank[v].x0 + (uint32_t)i0;
                 if (i1 - i0 > WR_SLICE_CAP - 4 || i1 - i0 > 0xFFFFu) continue;   // depth_window_kernel falls back to the global look-ups there
                 xlen[w] = (uint32_t)(i1 - i0);
-                uint16_t* row = xoff.data() + (size_t)w * WR_XOFF_STRIDE;
-                for (uint32_t b = 0; b < WR_NBF; b++) row[b] = (uint16_t)(std::min(below(lo + ((uint64_t)b << fsh)), i1) - i0);
-                row[WR_NBF] = (uint16_t)(i1 - i0);
+                uint16_t* row = xoff.data() + (size_t)w * DW_XOFF_STRIDE;
+                for (uint32_t b = 0; b < DW_NBF; b++) row[b] = (uint16_t)(std::min(below(lo + ((uint64_t)b << fsh)), i1) - i0);
+                row[DW_NBF] = (uint16_t)(i1 - i0);
             }
         }
         upload(C->d_cxw0, xw0, st);

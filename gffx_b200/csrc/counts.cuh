@@ -233,10 +233,17 @@ static __global__ void __launch_bounds__(CV_THREADS)
 // histograms once: ~0.25 L2 atomics per read instead of two, no global look-ups.  Reads whose end lies beyond the window's part,
 // gap updates (rare, counts.cuh above) and the irregular blocks' join keep their global paths; a window whose part does not fit
 // (WR_SLICE_CAP values) is done read by read with depth_space_update.
+// the counts coordinate set is twice as dense as the line filter's (every counted line's start and end): its windows' offset tables
+// take one more bit of fine bin, so that a look-up's binary search has as few steps as the join's
+#ifndef GFFX_DW_FB
+#define GFFX_DW_FB (GFFX_WR_FB + 1)
+#endif
+constexpr uint32_t DW_FB = GFFX_DW_FB, DW_NBF = 1u << DW_FB;
+constexpr uint32_t DW_XOFF_STRIDE = DW_NBF + 8;   // u16 cells per window: DW_NBF + 1 used, rows 16-byte multiples
 constexpr uint32_t DW_THREADS = 512;
 constexpr uint32_t DW_RUN = 15u * 4096u;   // reads per CTA: below 2^16 (16-bit histogram cells), a multiple of the partition tile
 constexpr uint32_t DW_GAPW = (WR_SLICE_CAP + 8) / 32 + 2;   // words of the window's gap-start bits
-constexpr size_t DW_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)WR_XOFF_STRIDE * 2 + 2 * (size_t)(WR_SLICE_CAP + 8) * 2 + (size_t)DW_GAPW * 4;
+constexpr size_t DW_SMEM = (size_t)(WR_SLICE_CAP + 8) * 4 + (size_t)DW_XOFF_STRIDE * 2 + 2 * (size_t)(WR_SLICE_CAP + 8) * 2 + (size_t)DW_GAPW * 4;
 
 constexpr uint32_t DW_IRR_CAP = 16;   // irregular tree intervals of one window kept in shared memory (more: every read searches the sequence's list)
 
@@ -254,7 +261,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
     extern __shared__ __align__(16) uint32_t dw_dyn[];
     uint32_t* const sx_raw = dw_dyn;
     uint16_t* const soff = reinterpret_cast<uint16_t*>(sx_raw + WR_SLICE_CAP + 8);
-    uint32_t* const hs = reinterpret_cast<uint32_t*>(soff + WR_XOFF_STRIDE);            // pairs of 16-bit cells
+    uint32_t* const hs = reinterpret_cast<uint32_t*>(soff + DW_XOFF_STRIDE);            // pairs of 16-bit cells
     uint32_t* const he = hs + (WR_SLICE_CAP + 8) / 2;
     uint32_t* const sgap = he + (WR_SLICE_CAP + 8) / 2;   // bit j: the part's value j starts a gap (counts_index.h: gap_bits)
     __shared__ uint32_t scan[DW_THREADS / 32 + 1];
@@ -274,7 +281,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
     const uint32_t w = s_w;
     const uint32_t p_lo = __ldg(W.poff + w) + s_run * DW_RUN, p_hi = min(__ldg(W.poff + w + 1), p_lo + DW_RUN);
     const uint32_t sp = __ldg(W.win_seq + w);
-    const uint32_t lo = (w - __ldg(W.win0 + sp)) << W.shift, fsh = W.shift - WR_FB;
+    const uint32_t lo = (w - __ldg(W.win0 + sp)) << W.shift, fsh = W.shift - DW_FB;
     const RankSeq RS = load_rank_seq(D.R, sp);
     // a read that ends inside the window can only hit irregular tree intervals that touch the window: usually none, a few at most —
     // found once per CTA instead of a binary search over the sequence's list per read (10 % of the kernel's instructions, r03j)
@@ -293,9 +300,9 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
     if (sliced) {
         if (tid == 0) {
             const uint32_t bytes = (((xw0 & 3u) + xlen + 1u) * 4u + 15u) & ~15u;   // X is padded: reading a few values on is safe
-            mbar_expect_tx(&mbar, bytes + WR_XOFF_STRIDE * 2u);
+            mbar_expect_tx(&mbar, bytes + DW_XOFF_STRIDE * 2u);
             bulk_g2s(sx_raw, D.R.X + (xw0 & ~3u), bytes, &mbar);
-            bulk_g2s(soff, W.XS.xoff + (size_t)w * WR_XOFF_STRIDE, WR_XOFF_STRIDE * 2u, &mbar);
+            bulk_g2s(soff, W.XS.xoff + (size_t)w * DW_XOFF_STRIDE, DW_XOFF_STRIDE * 2u, &mbar);
         }
         for (uint32_t i = tid; i < (xlen + 2u + 1u) / 2u; i += DW_THREADS) { hs[i] = 0; he[i] = 0; }
         {   // the gap-start bits of the part's slots, realigned to bit 0 = the part's first value
@@ -320,7 +327,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 2)
             depth_space_update(D, sp, rs, re);
         } else {
             bool eq;
-            const uint32_t lb = rank_lb_slice(sx, soff, xlen, min((rs - lo) >> fsh, WR_NBF - 1u), rs, &eq);
+            const uint32_t lb = rank_lb_slice(sx, soff, xlen, min((rs - lo) >> fsh, DW_NBF - 1u), rs, &eq);
             const uint32_t ub = lb + (eq ? 1u : 0u);   // <= xlen: the slot after the part's last value is the next window's first
             atomicAdd(hs + (ub >> 1), (ub & 1u) ? 0x10000u : 1u);
             uint32_t j = ub;
