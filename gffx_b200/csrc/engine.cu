@@ -985,18 +985,18 @@ uint32_t EngineImpl::ix_scans(FilterScans* Pout) {
     ull* scr = d_scan_scratch.as<ull>();
     *Pout = FilterScans{d_PMX.as<ull>(), d_SMN.as<ull>(), d_NS.as<uint32_t>(), d_NE.as<uint32_t>(), F.any_inv, epoch};
     if (mode == 0 || mode == 2)
-        launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
+        launches += device_scan<ull, OpMax, PtrLoad<ull>, PtrStore<ull>, false, true, 16>(PtrLoad<ull>{F.A}, PtrStore<ull>{d_PMX.as<ull>()}, ns,
                                                                                      OpMax(), 0ull, scr, nullptr, st, nullptr, chain());
     if (mode == 1) {
-        launches += device_scan<ull, OpMin, PtrLoad<ull>, PtrStore<ull>, true, true>(PtrLoad<ull>{F.B}, PtrStore<ull>{d_SMN.as<ull>()}, ns,
+        launches += device_scan<ull, OpMin, PtrLoad<ull>, PtrStore<ull>, true, true, 16>(PtrLoad<ull>{F.B}, PtrStore<ull>{d_SMN.as<ull>()}, ns,
                                                                                     OpMin(), ~0ull, scr, nullptr, st, nullptr, chain());
         fill_u64_kernel<<<1, 32, 0, st>>>(d_SMN.as<ull>() + ns, 1, ~0ull);  // SMN[iS+1] may index one past the last slot
         launches++;
     }
     if (mode == 2) {
-        launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
+        launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true, 16>(
             MarkLoad{F.Ms, epoch8}, PtrStore<uint32_t>{d_NS.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, nullptr, chain());
-        launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true>(
+        launches += device_scan<uint32_t, OpMin, MarkLoad, PtrStore<uint32_t>, true, true, 16>(
             MarkLoad{F.Me, epoch8}, PtrStore<uint32_t>{d_NE.as<uint32_t>()}, 2 * ns, OpMin(), 0xFFFFFFFFu, (uint32_t*)scr, nullptr, st, F.any_inv, chain());
     }
     return launches;

@@ -9,6 +9,7 @@
 // hundred MB); the streaming kernels do their own block scans in registers/shared memory.
 #pragma once
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cstdint>
 
 namespace gffx {
@@ -82,15 +83,15 @@ template <class T, class Op> __device__ __forceinline__ T block_scan_excl(T v, O
 // ---- device-wide scan -----------------------------------------------------------------------
 // Load(i) -> T gives element i; REVERSE scans from the high end (suffix scan).  Element j of the
 // scan order is array index (REVERSE ? n-1-j : j).
-template <class T, class Op, class Load, bool REVERSE>
+template <class T, class Op, class Load, bool REVERSE, int ITEMS = SCAN_ITEMS>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(Load load, uint64_t n, Op op, T identity, T* __restrict__ agg,
                                                                    const uint32_t* __restrict__ gate) {
     __shared__ T sm[SCAN_THREADS / 32 + 1];
     if (gate && *gate == 0) return;   // the whole scan is switched off by a device-side flag (uniform)
-    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
+    const uint64_t base = (uint64_t)blockIdx.x * (SCAN_THREADS * ITEMS);
     T acc = identity;
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         uint64_t j = base + (uint64_t)k * SCAN_THREADS + threadIdx.x;
         if (j < n) acc = op(acc, load(REVERSE ? n - 1 - j : j));
     }
@@ -118,7 +119,7 @@ __global__ void __launch_bounds__(1024) scan_agg_kernel(T* __restrict__ agg, uin
     if (threadIdx.x == 0) agg[m] = carry;
 }
 
-template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE>
+template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE, int ITEMS = SCAN_ITEMS>
 __global__ void __launch_bounds__(SCAN_THREADS)
     scan_apply_kernel(Load load, Store store, uint64_t n, Op op, T identity, const T* __restrict__ agg, const uint32_t* __restrict__ gate,
                       bool fold, T* __restrict__ total_out) {
@@ -140,16 +141,16 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     // (a blocked arrangement, 64 bytes per thread, costs four times the L1 wavefronts); the price is one warp scan per k
     // instead of one per thread, a few dozen shuffles that nothing here waits for
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint64_t wbase = (uint64_t)blockIdx.x * SCAN_TILE + (uint64_t)warp * (32 * SCAN_ITEMS) + lane;
-    T v[SCAN_ITEMS];
+    const uint64_t wbase = (uint64_t)blockIdx.x * (SCAN_THREADS * ITEMS) + (uint64_t)warp * (32 * ITEMS) + lane;
+    T v[ITEMS];
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         const uint64_t j = wbase + 32u * k;
         v[k] = j < n ? load(REVERSE ? n - 1 - j : j) : identity;
     }
     T run = identity;   // this warp's elements before row k, combined
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         const T inc = warp_scan_incl(v[k], op);
         const T row = shfl_idx_any(inc, 31);
         T ex = shfl_up_any(inc, 1);
@@ -170,7 +171,7 @@ __global__ void __launch_bounds__(SCAN_THREADS)
     const T pre = op(carry, wpre);
     if (fold && total_out && blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *total_out = op(carry, tot);
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         const uint64_t j = wbase + 32u * k;
         if (j < n) store(REVERSE ? n - 1 - j : j, op(pre, v[k]));
     }
@@ -309,7 +310,8 @@ template <class T> struct PtrStore {
 // Scans n elements; `scratch` holds scan_scratch_elems(n) Ts.  If total_out != nullptr the grand
 // total (device pointer) is written there.  gate != nullptr: a device-side word; when it is 0 the kernels return at once
 // and nothing is written (the consumer checks the same word).  Returns the number of kernels launched.
-template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE>
+// ITEMS: elements per thread of the reduce / rescan kernels (16 for the big rank-space scans: half the CTAs, -7 % of their time)
+template <class T, class Op, class Load, class Store, bool REVERSE, bool INCLUSIVE, int ITEMS = SCAN_ITEMS>
 int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratch, T* total_out, cudaStream_t st, const uint32_t* gate = nullptr,
                 ScanChain* chain = nullptr, uint64_t chain_from_tiles = 8192) {   // chain_from_tiles: lower it when a tile's load is heavy (a long tile hides the look-back)
     int launches = 0;
@@ -328,11 +330,12 @@ int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratc
                                                                                                             scratch + tiles + 1, chain->epoch, gate, total_out);
         return 1;
     }
+    if (ITEMS != SCAN_ITEMS) tiles = std::max<uint64_t>(1, (n + (uint64_t)SCAN_THREADS * ITEMS - 1) / ((uint64_t)SCAN_THREADS * ITEMS));
     T* agg = scratch;
-    scan_reduce_kernel<T, Op, Load, REVERSE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, n, op, identity, agg, gate);
+    scan_reduce_kernel<T, Op, Load, REVERSE, ITEMS><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, n, op, identity, agg, gate);
     launches++;
     if (tiles <= SCAN_FOLD_TILES) {   // two launches: the rescan folds the raw tile totals itself and writes the grand total
-        scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate,
+        scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE, ITEMS><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate,
                                                                                                             true, total_out);
         return launches + 1;
     }
@@ -345,7 +348,7 @@ int device_scan(Load load, Store store, uint64_t n, Op op, T identity, T* scratc
         launches += device_scan<T, Op, PtrLoad<T>, PtrStore<T>, false, false>(PtrLoad<T>{agg}, PtrStore<T>{agg}, tiles, op, identity,
                                                                              next, agg + tiles, st, gate);
     }
-    scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate,
+    scan_apply_kernel<T, Op, Load, Store, REVERSE, INCLUSIVE, ITEMS><<<(unsigned)tiles, SCAN_THREADS, 0, st>>>(load, store, n, op, identity, agg, gate,
                                                                                                         false, nullptr);
     launches++;
     if (total_out) {
