@@ -159,7 +159,8 @@ static __global__ void __launch_bounds__(PART_THREADS, PART_COUNT_CTAS)
 }
 
 // one CTA of PART_NB_MAX threads: poff[w] = cursor[w] = first bucketed position of window w, poff[nb] = n; the totals are
-// zeroed for the next partition pass on the stream
+// zeroed for the next partition pass on the stream.  (Folding this into the count pass — its last CTA to finish, found by a
+// ticket, does the scan — removes the launch and measures the same, r03o: the count pass's tail grows by what the launch cost.)
 static __global__ void __launch_bounds__(PART_NB_MAX) part_offsets_kernel(uint32_t* __restrict__ tot, uint32_t nb, uint32_t n,
                                                                          uint32_t* __restrict__ poff, uint32_t* __restrict__ cursor) {
     __shared__ uint32_t warp_tot[PART_NB_MAX / 32];
